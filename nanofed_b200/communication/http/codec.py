@@ -1,0 +1,121 @@
+"""Tensor encodings for the cross-host transport.
+
+Two encodings share the same endpoints and the same envelope fields:
+
+* **JSON lists** — the reference's only format (``server.py:140-149``,
+  ``client.py:132-135``): ``tensor.cpu().numpy().tolist()``, arbitrary nesting, 0-d ⇒
+  bare number, decoded with ``torch.tensor(value)``.  22.7 bytes per parameter
+  for the MNIST CNN (27.3 MB vs 4.8 MB raw — SURVEY §0.3) and it cannot carry
+  bf16/fp16 (``.numpy()`` raises).  Kept for compatibility; bf16/fp16 tensors
+  are widened to fp32 instead of failing.
+* **Binary frame** (opt-in, ``application/octet-stream``):
+
+      u64 little-endian  header_len
+      header_len bytes   UTF-8 JSON envelope; ``"tensors": [{name,dtype,shape,offset,nbytes}]``
+      payload            raw little-endian tensor bytes, 64-byte aligned per tensor
+
+  4 (or 2, for bf16) bytes per parameter, zero parsing, and the payload can be
+  ``torch.frombuffer``-viewed straight into a pinned staging buffer for the H2D copy.
+"""
+
+from __future__ import annotations
+
+import json
+import struct
+from typing import Any, Mapping
+
+import numpy as np
+import torch
+
+BINARY_CONTENT_TYPE = "application/octet-stream"
+_ALIGN = 64
+
+_DTYPE_NAMES: dict[torch.dtype, str] = {
+    torch.float32: "float32",
+    torch.float64: "float64",
+    torch.float16: "float16",
+    torch.bfloat16: "bfloat16",
+    torch.int64: "int64",
+    torch.int32: "int32",
+    torch.int16: "int16",
+    torch.int8: "int8",
+    torch.uint8: "uint8",
+    torch.bool: "bool",
+}
+_DTYPES_BY_NAME = {v: k for k, v in _DTYPE_NAMES.items()}
+
+
+# -- JSON lists ------------------------------------------------------------------
+def tensor_to_jsonable(value: Any) -> Any:
+    """Reference-compatible list encoding of one state entry."""
+    if isinstance(value, torch.Tensor):
+        t = value.detach()
+        if t.dtype in (torch.bfloat16, torch.float16):
+            t = t.to(torch.float32)
+        return t.cpu().numpy().tolist()
+    if isinstance(value, np.ndarray):
+        return value.tolist()
+    if isinstance(value, (int, float)) and not isinstance(value, bool):
+        return [float(value)]
+    return value
+
+
+def state_to_jsonable(state: Mapping[str, Any]) -> dict[str, Any]:
+    return {name: tensor_to_jsonable(v) for name, v in state.items()}
+
+
+def state_from_jsonable(payload: Mapping[str, Any]) -> dict[str, torch.Tensor]:
+    """``torch.tensor(value)`` per entry: float lists → fp32, int lists → int64."""
+    return {name: torch.tensor(v) for name, v in payload.items()}
+
+
+# -- binary frame ------------------------------------------------------------------
+def encode_frame(envelope: Mapping[str, Any], state: Mapping[str, torch.Tensor] | None) -> bytes:
+    table: list[dict[str, Any]] = []
+    chunks: list[bytes] = []
+    cursor = 0
+    for name, value in (state or {}).items():
+        t = value.detach().contiguous().cpu() if isinstance(value, torch.Tensor) else torch.as_tensor(value)
+        if t.dtype not in _DTYPE_NAMES:
+            t = t.to(torch.float32)
+        raw = t.view(torch.uint8).numpy().tobytes() if t.numel() else b""
+        if t.dim() == 0 and t.numel():
+            raw = t.reshape(1).view(torch.uint8).numpy().tobytes()
+        pad = (-cursor) % _ALIGN
+        if pad:
+            chunks.append(b"\0" * pad)
+            cursor += pad
+        table.append({"name": name, "dtype": _DTYPE_NAMES[t.dtype], "shape": list(t.shape),
+                      "offset": cursor, "nbytes": len(raw)})
+        chunks.append(raw)
+        cursor += len(raw)
+    header = dict(envelope)
+    header["tensors"] = table if state is not None else None
+    head = json.dumps(header).encode("utf-8")
+    return struct.pack("<Q", len(head)) + head + b"".join(chunks)
+
+
+def decode_frame(blob: bytes | bytearray | memoryview) -> tuple[dict[str, Any], dict[str, torch.Tensor] | None]:
+    view = memoryview(blob)
+    if len(view) < 8:
+        raise ValueError("binary frame too short")
+    (head_len,) = struct.unpack("<Q", view[:8])
+    if head_len > len(view) - 8:
+        raise ValueError("binary frame header length exceeds body")
+    header = json.loads(bytes(view[8 : 8 + head_len]).decode("utf-8"))
+    table = header.pop("tensors", None)
+    if table is None:
+        return header, None
+    payload = view[8 + head_len :]
+    state: dict[str, torch.Tensor] = {}
+    for entry in table:
+        dtype = _DTYPES_BY_NAME[entry["dtype"]]
+        start, n = int(entry["offset"]), int(entry["nbytes"])
+        if start + n > len(payload):
+            raise ValueError(f"tensor {entry['name']!r} exceeds frame payload")
+        if n == 0:
+            state[entry["name"]] = torch.zeros(entry["shape"], dtype=dtype)
+            continue
+        raw = torch.frombuffer(bytearray(payload[start : start + n]), dtype=torch.uint8)
+        state[entry["name"]] = raw.view(dtype).reshape(entry["shape"])
+    return header, state
