@@ -1,0 +1,341 @@
+// K-AGG + K-BCAST, multi-GPU form: ONE kernel per rank that
+//   A. reduces this GPU's clients into an unnormalised partial  P_r = sum_k n_k m_k c_k x_k
+//      (same column_reduce as the single-GPU kernel; HBM-bound, K_g*N*b bytes),
+//   B. crosses a flag barrier with the other ranks (release/acquire on words in peer
+//      memory — no NCCL, no host),
+//   C. reduce-scatters over NVLink from inside the kernel: rank r owns columns
+//      [r*N/G, (r+1)*N/G) and pulls that shard of every peer's partial — either with
+//      plain P2P loads (ld.relaxed.sys on mapped peer pointers) or, through NVSwitch,
+//      with ONE multimem.ld_reduce per 16 bytes that returns the sum already reduced in
+//      the switch (NVLS),
+//   D. finishes the FedAvg math on the shard (1/sum n, folded DP noise, casts) and
+//      all-gathers by STORING the result into every rank's global-model buffers (P2P
+//      st.global to each peer, or one multimem.st that the switch replicates) — this is
+//      the broadcast of the new global model, so no separate K-BCAST transfer exists,
+//   E. crosses a second flag barrier so every rank owns the complete new model on exit.
+//
+// Per-GPU NVLink traffic: 4N(G-1)/G bytes in (C) and 4N(G-1)/G (+2N(G-1)/G bf16) out (D).
+//
+// Emulation: `ranks_in_grid` > 1 runs G emulated ranks as blockIdx.y of ONE cooperative
+// launch on one GPU (all pointers then refer to the same device).  This is how the kernel
+// is tested on a single B200 without launching kernels that wait on each other.
+//
+// Safety: every spin is bounded by `spin_limit_ns` of %globaltimer; on expiry the kernel
+// sets status[0] = 1 and returns instead of hanging the GPU.
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "fedavg_device.cuh"
+#include "philox.cuh"
+
+namespace nfb {
+
+struct RankView {
+  // local inputs (only dereferenced by the owning rank)
+  const void* slots;
+  const float* counts;
+  const float* mask;
+  const float* sumsq;
+  // peer-visible buffers (dereferenced by every rank)
+  float* partial;        // [N]
+  float* scal;           // [4]: sum n, sum n^2
+  unsigned* flags;       // [2*G]: barrier words written by peers
+  float* master;         // [N] new global model
+  __nv_bfloat16* lowp;   // [N] bf16 copy (may be null)
+  unsigned long long* grid_ctr;  // [1] local grid-barrier arrival counter (monotonic)
+};
+
+struct AllreduceArgs {
+  int G, K, x_dtype;
+  int64_t N, row_stride;
+  float clip_norm, noise_std;
+  const uint8_t* noise_mask;  // local copy on each rank (same content)
+  uint64_t seed, group0;
+  unsigned epoch;             // barrier generation, strictly increasing per call
+  unsigned long long ctr_base;  // grid_ctr value before this call (host-tracked)
+  unsigned long long spin_limit_ns;
+  const float* mc_partial;    // multicast address of partial[] (null = P2P loads)
+  float* mc_master;           // multicast address of master[]  (null = P2P stores)
+  __nv_bfloat16* mc_lowp;
+  int* status;                // [1] local: set to 1 on barrier timeout
+};
+
+__device__ __forceinline__ unsigned long long now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_relaxed_sys_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc),
+               "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(mc),
+               "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y))
+               : "memory");
+}
+
+// Barrier among the CTAs of ONE rank (gridDim.x CTAs, all co-resident).
+__device__ __forceinline__ bool rank_grid_barrier(unsigned long long* ctr,
+                                                  unsigned long long target,
+                                                  unsigned long long limit, int* status) {
+  __shared__ int s_ok;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s_ok = 1;
+    __threadfence();
+    atomicAdd(ctr, 1ull);
+    const unsigned long long t0 = now_ns();
+    while (ld_acquire_gpu_u64(ctr) < target) {
+      if (now_ns() - t0 > limit) { *status = 1; s_ok = 0; break; }
+    }
+  }
+  __syncthreads();
+  return s_ok != 0;
+}
+
+// Cross-rank barrier, executed by CTA 0 of each rank after its rank_grid_barrier.
+__device__ __forceinline__ void cross_rank_signal_wait(const RankView* views, int rank, int G,
+                                                       int slot, unsigned epoch,
+                                                       unsigned long long limit, int* status) {
+  if (threadIdx.x < G) {
+    const int peer = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(views[peer].flags + slot * G + rank, epoch);
+    const unsigned* mine = views[rank].flags + slot * G + peer;
+    const unsigned long long t0 = now_ns();
+    while (ld_acquire_sys(mine) < epoch) {
+      if (now_ns() - t0 > limit) { *status = 1; break; }
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    fedavg_allreduce_kernel(const RankView* __restrict__ views, int my_rank, AllreduceArgs a) {
+  extern __shared__ float coef[];
+  __shared__ float red[33];
+  constexpr int V = Vec16<T>::N;
+  const int rank = (gridDim.y > 1) ? static_cast<int>(blockIdx.y) : my_rank;
+  const RankView me = views[rank];
+  const int G = a.G;
+  const unsigned nblk = gridDim.x;
+
+  // ---- A. local unnormalised partial -------------------------------------------------
+  // normalise=false: coef = n_k m_k c_k ; returned value = sum (n_k m_k)^2
+  const float q_local = agg_prologue(coef, a.K, me.counts, me.sumsq, me.mask, a.clip_norm,
+                                     /*normalise=*/false, red);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float s = 0.f;
+    for (int k = 0; k < a.K; ++k) s += me.counts[k] * (me.mask ? me.mask[k] : 1.f);
+    me.scal[0] = s;
+    me.scal[1] = q_local;
+  }
+  const T* x = static_cast<const T*>(me.slots);
+  const int64_t groups = a.N / V;
+  for (int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; g < groups;
+       g += static_cast<int64_t>(nblk) * blockDim.x) {
+    float acc[V];
+    column_reduce<T>(x, a.row_stride, a.K, coef, g * V, acc);
+#pragma unroll
+    for (int q = 0; q < V / 4; ++q)
+      *reinterpret_cast<float4*>(me.partial + g * V + 4 * q) =
+          make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+  }
+
+  // ---- B. barrier 1: every rank's partial is complete and visible ----------------------
+  __threadfence_system();
+  if (!rank_grid_barrier(me.grid_ctr, a.ctr_base + 1ull * nblk, a.spin_limit_ns, a.status))
+    return;
+  if (blockIdx.x == 0)
+    cross_rank_signal_wait(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
+  if (!rank_grid_barrier(me.grid_ctr, a.ctr_base + 2ull * nblk, a.spin_limit_ns, a.status))
+    return;
+
+  // ---- C+D. reduce my shard across ranks, finish, store to every rank ------------------
+  float s_tot = 0.f, q_tot = 0.f;
+  for (int r = 0; r < G; ++r) {
+    const float* sc = views[r].scal;
+    float s_r, q_r;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r) : "l"(sc) : "memory");
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r) : "l"(sc + 1) : "memory");
+    s_tot += s_r;
+    q_tot += q_r;
+  }
+  const float inv = s_tot > 0.f ? 1.f / s_tot : 0.f;
+  const float sigma = a.noise_std > 0.f ? a.noise_std * sqrtf(q_tot) * inv : 0.f;
+
+  const int64_t quads = a.N >> 2;
+  const int64_t per = (quads + G - 1) / G;
+  const int64_t q_lo = per * rank;
+  const int64_t q_hi = (q_lo + per < quads) ? q_lo + per : quads;
+  for (int64_t q = q_lo + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < q_hi;
+       q += static_cast<int64_t>(nblk) * blockDim.x) {
+    const int64_t col = q << 2;
+    float4 sum;
+    if (a.mc_partial) {
+      sum = multimem_ld_reduce_f4(a.mc_partial + col);
+    } else {
+      sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      // fixed rank order => identical bits on every run; start at my own rank+1 so the
+      // G ranks do not all hammer peer 0 first
+      for (int i = 0; i < G; ++i) {
+        const int r = (i + rank + 1) % G;
+        const float4 v = ld_relaxed_sys_f4(views[r].partial + col);
+        sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+      }
+    }
+    float o[4] = {sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv};
+    if (sigma > 0.f) {
+      const float4 z = Philox::normal4(a.group0 + q, a.seed);
+      float zz[4] = {z.x, z.y, z.z, z.w};
+      if (a.noise_mask) {
+        const uchar4 m = *reinterpret_cast<const uchar4*>(a.noise_mask + col);
+        zz[0] *= m.x ? 1.f : 0.f; zz[1] *= m.y ? 1.f : 0.f;
+        zz[2] *= m.z ? 1.f : 0.f; zz[3] *= m.w ? 1.f : 0.f;
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o[e] = fmaf(sigma, zz[e], o[e]);
+    }
+    const float4 ov = make_float4(o[0], o[1], o[2], o[3]);
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(o[0], o[1]);
+    const __nv_bfloat162 hi = __floats2bfloat162_rn(o[2], o[3]);
+    uint2 packed;
+    packed.x = *reinterpret_cast<const uint32_t*>(&lo);
+    packed.y = *reinterpret_cast<const uint32_t*>(&hi);
+    if (a.mc_master) {
+      multimem_st_f4(a.mc_master + col, ov);
+      if (a.mc_lowp) multimem_st_b64(a.mc_lowp + col, packed);
+    } else {
+      for (int i = 0; i < G; ++i) {
+        const int r = (i + rank) % G;
+        *reinterpret_cast<float4*>(views[r].master + col) = ov;
+        if (views[r].lowp) *reinterpret_cast<uint2*>(views[r].lowp + col) = packed;
+      }
+    }
+  }
+
+  // ---- E. barrier 2: the new global model is complete on every rank ---------------------
+  __threadfence_system();
+  if (!rank_grid_barrier(me.grid_ctr, a.ctr_base + 3ull * nblk, a.spin_limit_ns, a.status))
+    return;
+  if (blockIdx.x == 0)
+    cross_rank_signal_wait(views, rank, G, 1, a.epoch, a.spin_limit_ns, a.status);
+  rank_grid_barrier(me.grid_ctr, a.ctr_base + 4ull * nblk, a.spin_limit_ns, a.status);
+}
+
+// Host-side mirror of RankView for the C ABI (10 pointers, same order).
+static_assert(sizeof(RankView) == 10 * sizeof(void*), "RankView must stay 10 pointers");
+
+template <typename T>
+static int launch_allreduce(const RankView* views, int my_rank, int ranks_in_grid,
+                            int grid_blocks, const AllreduceArgs& a, cudaStream_t st) {
+  const size_t smem = static_cast<size_t>(a.K) * sizeof(float);
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+      &per_sm, fedavg_allreduce_kernel<T>, 256, smem);
+  if (e != cudaSuccess) return fail(static_cast<int>(e), "allreduce occupancy query: %s",
+                                    cudaGetErrorString(e));
+  const int64_t resident = static_cast<int64_t>(per_sm) * sm_count();
+  if (static_cast<int64_t>(grid_blocks) * ranks_in_grid > resident)
+    return fail(NFB_ERANGE, "fedavg_allreduce: %d x %d CTAs exceed the %lld that can be "
+                "co-resident", grid_blocks, ranks_in_grid, static_cast<long long>(resident));
+  dim3 grid(static_cast<unsigned>(grid_blocks), static_cast<unsigned>(ranks_in_grid));
+  AllreduceArgs args = a;
+  void* params[] = {const_cast<RankView**>(&views), &my_rank, &args};
+  e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(fedavg_allreduce_kernel<T>), grid,
+                                  dim3(256), params, smem, st);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(static_cast<int>(e), "fedavg_allreduce launch: %s", cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+}  // namespace nfb
+
+extern "C" int nfb_allreduce_max_blocks(int x_dtype, int64_t K) {
+  using namespace nfb;
+  const size_t smem = static_cast<size_t>(K) * sizeof(float);
+  int per_sm = 0;
+  cudaError_t e;
+  if (x_dtype == NFB_DT_F32)
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fedavg_allreduce_kernel<float>,
+                                                      256, smem);
+  else if (x_dtype == NFB_DT_BF16)
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+        &per_sm, fedavg_allreduce_kernel<__nv_bfloat16>, 256, smem);
+  else
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fedavg_allreduce_kernel<__half>,
+                                                      256, smem);
+  if (e != cudaSuccess) return fail(-static_cast<int>(e), "occupancy query: %s",
+                                    cudaGetErrorString(e));
+  return per_sm * sm_count();
+}
+
+extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, int ranks_in_grid,
+                                    int x_dtype, int64_t K, int64_t N, int64_t row_stride,
+                                    float clip_norm, float noise_std, const uint8_t* noise_mask,
+                                    uint64_t seed, uint64_t offset, uint32_t epoch,
+                                    uint64_t ctr_base, int grid_blocks, const float* mc_partial,
+                                    float* mc_master, void* mc_lowp, int* status,
+                                    uint64_t spin_limit_ns, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(views_dev && status, NFB_EINVAL, "fedavg_allreduce: null pointer");
+  NFB_REQUIRE(G >= 1 && G <= 32 && my_rank >= 0 && my_rank < G, NFB_EINVAL,
+              "fedavg_allreduce: bad rank %d of %d", my_rank, G);
+  NFB_REQUIRE(ranks_in_grid == 1 || ranks_in_grid == G, NFB_EINVAL,
+              "fedavg_allreduce: ranks_in_grid must be 1 or G");
+  NFB_REQUIRE(K >= 1 && K <= 12000, NFB_ERANGE, "fedavg_allreduce: K outside [1, 12000]");
+  NFB_REQUIRE((N & 7) == 0 && (row_stride & 7) == 0 && N > 0, NFB_EINVAL,
+              "fedavg_allreduce: N and row_stride must be positive multiples of 8");
+  NFB_REQUIRE((offset & 3u) == 0, NFB_EINVAL, "fedavg_allreduce: offset must be multiple of 4");
+  NFB_REQUIRE(epoch >= 1 && grid_blocks >= 1, NFB_EINVAL, "fedavg_allreduce: bad epoch/grid");
+  AllreduceArgs a;
+  a.G = G; a.K = static_cast<int>(K); a.x_dtype = x_dtype;
+  a.N = N; a.row_stride = row_stride;
+  a.clip_norm = clip_norm; a.noise_std = noise_std; a.noise_mask = noise_mask;
+  a.seed = seed; a.group0 = offset >> 2;
+  a.epoch = epoch; a.ctr_base = ctr_base;
+  a.spin_limit_ns = spin_limit_ns ? spin_limit_ns : 5000000000ull;
+  a.mc_partial = mc_partial; a.mc_master = mc_master;
+  a.mc_lowp = static_cast<__nv_bfloat16*>(mc_lowp);
+  a.status = status;
+  const RankView* views = static_cast<const RankView*>(views_dev);
+  cudaStream_t st = as_stream(stream);
+  return dispatch_dtype(x_dtype, [&](auto tag) {
+    using T = decltype(tag);
+    return launch_allreduce<T>(views, my_rank, ranks_in_grid, grid_blocks, a, st);
+  });
+}

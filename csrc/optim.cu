@@ -1,0 +1,149 @@
+// K-OPT: fused SGD / Adam(W) on flat fp32 buffers, optional DP-SGD front end
+// (device-side clip factor + Philox Gaussian noise) and bf16 working-copy write-back.
+// One pass: reads p, g (+ state), writes p (+ state, + bf16 copy).  HBM-bound.
+#include "common.cuh"
+#include "philox.cuh"
+
+namespace nfb {
+
+struct SgdArgs {
+  float lr, momentum, dampening, weight_decay, noise_std;
+  int nesterov, first_step;
+  const float* grad_scale;
+  uint64_t seed, group0;
+};
+
+template <typename G>
+__global__ void __launch_bounds__(256)
+    sgd_kernel(float* __restrict__ p, const G* __restrict__ g, float* __restrict__ mom,
+               __nv_bfloat16* __restrict__ lowp, int64_t n, SgdArgs a) {
+  const float gs = a.grad_scale ? *a.grad_scale : 1.f;
+  const int64_t groups = (n + 3) >> 2;
+  for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < groups;
+       q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t base = q << 2;
+    const int cnt = (n - base) >= 4 ? 4 : static_cast<int>(n - base);
+    float pv[4], gv[4], mv[4] = {0, 0, 0, 0};
+    if (cnt == 4) {
+      const float4 t = *reinterpret_cast<const float4*>(p + base);
+      pv[0] = t.x; pv[1] = t.y; pv[2] = t.z; pv[3] = t.w;
+    } else {
+      for (int e = 0; e < 4; ++e) pv[e] = e < cnt ? p[base + e] : 0.f;
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) gv[e] = e < cnt ? to_f32(g[base + e]) * gs : 0.f;
+    if (a.noise_std > 0.f) {
+      const float4 z = Philox::normal4(a.group0 + q, a.seed);
+      gv[0] = fmaf(a.noise_std, z.x, gv[0]); gv[1] = fmaf(a.noise_std, z.y, gv[1]);
+      gv[2] = fmaf(a.noise_std, z.z, gv[2]); gv[3] = fmaf(a.noise_std, z.w, gv[3]);
+    }
+    if (a.weight_decay != 0.f) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) gv[e] = fmaf(a.weight_decay, pv[e], gv[e]);
+    }
+    if (mom) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        if (e < cnt) {
+          mv[e] = a.first_step ? gv[e]
+                               : fmaf(a.momentum, mom[base + e], (1.f - a.dampening) * gv[e]);
+          mom[base + e] = mv[e];
+          gv[e] = a.nesterov ? fmaf(a.momentum, mv[e], gv[e]) : mv[e];
+        }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) pv[e] = fmaf(-a.lr, gv[e], pv[e]);
+    if (cnt == 4) {
+      *reinterpret_cast<float4*>(p + base) = make_float4(pv[0], pv[1], pv[2], pv[3]);
+    } else {
+      for (int e = 0; e < cnt; ++e) p[base + e] = pv[e];
+    }
+    if (lowp) {
+      for (int e = 0; e < cnt; ++e) lowp[base + e] = __float2bfloat16_rn(pv[e]);
+    }
+  }
+}
+
+struct AdamArgs {
+  float lr, beta1, beta2, eps, weight_decay, bc1, bc2;
+  int decoupled;
+  const float* grad_scale;
+};
+
+template <typename G>
+__global__ void __launch_bounds__(256)
+    adam_kernel(float* __restrict__ p, const G* __restrict__ g, float* __restrict__ m,
+                float* __restrict__ v, __nv_bfloat16* __restrict__ lowp, int64_t n, AdamArgs a) {
+  const float gs = a.grad_scale ? *a.grad_scale : 1.f;
+  const float inv_sqrt_bc2 = rsqrtf(a.bc2);
+  const float step = a.lr / a.bc1;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    float pv = p[i];
+    float gv = to_f32(g[i]) * gs;
+    if (a.weight_decay != 0.f) {
+      if (a.decoupled) pv *= (1.f - a.lr * a.weight_decay);
+      else gv = fmaf(a.weight_decay, pv, gv);
+    }
+    const float mv = fmaf(a.beta1, m[i], (1.f - a.beta1) * gv);
+    const float vv = fmaf(a.beta2, v[i], (1.f - a.beta2) * gv * gv);
+    m[i] = mv;
+    v[i] = vv;
+    pv -= step * mv / (sqrtf(vv) * inv_sqrt_bc2 + a.eps);
+    p[i] = pv;
+    if (lowp) lowp[i] = __float2bfloat16_rn(pv);
+  }
+}
+
+static int flat_grid(int64_t items) {
+  int64_t b = (items + 255) / 256;
+  const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+  if (b > cap) b = cap;
+  return static_cast<int>(b < 1 ? 1 : b);
+}
+
+}  // namespace nfb
+
+extern "C" int nfb_fused_sgd(float* p, const void* g, int g_dtype, float* momentum_buf,
+                             void* lowp_out, int64_t n, float lr, float momentum,
+                             float dampening, float weight_decay, int nesterov, int first_step,
+                             const float* grad_scale, float noise_std, uint64_t seed,
+                             uint64_t offset, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
+  NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
+  NFB_REQUIRE((offset & 3u) == 0, NFB_EINVAL, "fused_sgd: offset must be a multiple of 4");
+  if (n <= 0) return 0;
+  SgdArgs a{lr, momentum, dampening, weight_decay, noise_std, nesterov, first_step,
+            grad_scale, seed, offset >> 2};
+  float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
+  cudaStream_t st = as_stream(stream);
+  return dispatch_dtype(g_dtype, [&](auto tag) {
+    using G = decltype(tag);
+    sgd_kernel<G><<<flat_grid((n + 3) / 4), 256, 0, st>>>(
+        p, static_cast<const G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
+    return launch_status("fused_sgd");
+  });
+}
+
+extern "C" int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg,
+                              float* exp_avg_sq, void* lowp_out, int64_t n, float lr,
+                              float beta1, float beta2, float eps, float weight_decay,
+                              float bias_corr1, float bias_corr2, int decoupled,
+                              const float* grad_scale, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(p && g && exp_avg && exp_avg_sq, NFB_EINVAL, "fused_adam: null pointer");
+  NFB_REQUIRE(bias_corr1 > 0.f && bias_corr2 > 0.f, NFB_EINVAL,
+              "fused_adam: bias corrections must be positive (step >= 1)");
+  if (n <= 0) return 0;
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, bias_corr1, bias_corr2, decoupled, grad_scale};
+  cudaStream_t st = as_stream(stream);
+  return dispatch_dtype(g_dtype, [&](auto tag) {
+    using G = decltype(tag);
+    adam_kernel<G><<<flat_grid(n), 256, 0, st>>>(p, static_cast<const G*>(g), exp_avg,
+                                                 exp_avg_sq,
+                                                 static_cast<__nv_bfloat16*>(lowp_out), n, a);
+    return launch_status("fused_adam");
+  });
+}

@@ -1,0 +1,230 @@
+// K-STATS: deterministic sum-of-squares / non-finite reductions.
+//
+// Shape of every kernel here: `rows` independent reductions, each split over
+// SLICES thread blocks.  A block writes its partial into scratch, bumps the row's
+// arrival counter, and the LAST block to arrive adds the SLICES partials in index
+// order — so the result does not depend on block scheduling (no float atomics) —
+// then zeroes the counter again so the scratch can be reused by the next launch.
+//
+// Scratch layout for `rows` rows:  float partial[rows][SLICES] | int bad[rows][SLICES]
+//                                  | unsigned arrived[rows]      (arrived[] must be 0 on entry)
+#include "common.cuh"
+
+namespace nfb {
+
+constexpr int kSlices = 32;      // blocks per reduction row
+constexpr int kThreads = 256;
+
+struct Scratch {
+  float* partial;
+  int* bad;
+  unsigned* arrived;
+};
+
+static size_t scratch_bytes(int64_t rows) {
+  return static_cast<size_t>(rows) * kSlices * (sizeof(float) + sizeof(int)) +
+         static_cast<size_t>(rows) * sizeof(unsigned);
+}
+
+static Scratch carve(void* base, int64_t rows) {
+  Scratch s;
+  s.partial = static_cast<float*>(base);
+  s.bad = reinterpret_cast<int*>(s.partial + rows * kSlices);
+  s.arrived = reinterpret_cast<unsigned*>(s.bad + rows * kSlices);
+  return s;
+}
+
+// Sum of squares of `len` elements at `p` handled by slice `slice` of kSlices.
+// Vector body over the 16-byte-aligned middle, scalar head/tail.
+template <typename T>
+__device__ __forceinline__ void slice_sumsq(const T* __restrict__ p, int64_t len, int slice,
+                                            float& acc, int& bad) {
+  constexpr int V = Vec16<T>::N;
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+  int64_t head = ((16 - (addr & 15)) & 15) / sizeof(T);
+  if (head > len) head = len;
+  const int64_t nvec = (len - head) / V;
+  const int64_t tail0 = head + nvec * V;
+
+  // scalar head + tail belong to slice 0
+  if (slice == 0) {
+    for (int64_t i = threadIdx.x; i < head; i += blockDim.x) {
+      const float v = to_f32(p[i]);
+      acc += v * v;
+      bad |= !finite_f(v);
+    }
+    for (int64_t i = tail0 + threadIdx.x; i < len; i += blockDim.x) {
+      const float v = to_f32(p[i]);
+      acc += v * v;
+      bad |= !finite_f(v);
+    }
+  }
+  const uint4* vp = reinterpret_cast<const uint4*>(p + head);
+  const int64_t stride = static_cast<int64_t>(kSlices) * blockDim.x;
+  int64_t i = static_cast<int64_t>(slice) * blockDim.x + threadIdx.x;
+  // 4 independent 16-byte loads in flight per thread
+  for (; i + 3 * stride < nvec; i += 4 * stride) {
+    uint4 r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = ld_stream(vp + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float f[V];
+      unpack<T>(r[u], f);
+#pragma unroll
+      for (int e = 0; e < V; ++e) {
+        acc += f[e] * f[e];
+        bad |= !finite_f(f[e]);
+      }
+    }
+  }
+  for (; i < nvec; i += stride) {
+    float f[V];
+    unpack<T>(ld_stream(vp + i), f);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      acc += f[e] * f[e];
+      bad |= !finite_f(f[e]);
+    }
+  }
+}
+
+// Publish this block's partial; the last block of the row finalises in fixed order.
+__device__ __forceinline__ void finish_row(float acc, int bad, int64_t row, int slice,
+                                           Scratch s, float* __restrict__ out_sum,
+                                           int* __restrict__ out_bad, float* smem) {
+  const float total = block_sum(acc, smem);
+  const int any_bad = __syncthreads_or(bad);
+  __shared__ bool is_last;
+  if (threadIdx.x == 0) {
+    s.partial[row * kSlices + slice] = total;
+    s.bad[row * kSlices + slice] = any_bad;
+    __threadfence();
+    const unsigned ticket = atomicAdd(&s.arrived[row], 1u);
+    is_last = (ticket == kSlices - 1);
+  }
+  __syncthreads();
+  if (is_last && threadIdx.x < 32) {
+    __threadfence();
+    // kSlices == 32: one partial per lane, summed by a fixed shuffle tree.
+    const volatile float* part = s.partial + row * kSlices;
+    const volatile int* pb = s.bad + row * kSlices;
+    float v = part[threadIdx.x];
+    int b = pb[threadIdx.x];
+    v = warp_sum(v);
+    b = __any_sync(0xffffffffu, b != 0);
+    if (threadIdx.x == 0) {
+      out_sum[row] = v;
+      if (out_bad) out_bad[row] = b ? 1 : 0;
+      s.arrived[row] = 0u;  // self-clean for the next launch
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) rows_sumsq_kernel(const T* __restrict__ x,
+                                                              int64_t n, int64_t row_stride,
+                                                              float* __restrict__ sumsq,
+                                                              int* __restrict__ bad, Scratch s) {
+  __shared__ float smem[33];
+  const int64_t row = blockIdx.y;
+  float acc = 0.f;
+  int b = 0;
+  slice_sumsq<T>(x + row * row_stride, n, blockIdx.x, acc, b);
+  finish_row(acc, b, row, blockIdx.x, s, sumsq, bad, smem);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) table_sumsq_kernel(const void* const* __restrict__ ptrs,
+                                                               const int64_t* __restrict__ lens,
+                                                               float* __restrict__ sumsq,
+                                                               int* __restrict__ bad, Scratch s) {
+  __shared__ float smem[33];
+  const int64_t t = blockIdx.y;
+  float acc = 0.f;
+  int b = 0;
+  slice_sumsq<T>(static_cast<const T*>(ptrs[t]), lens[t], blockIdx.x, acc, b);
+  finish_row(acc, b, t, blockIdx.x, s, sumsq, bad, smem);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) segment_sumsq_kernel(const T* __restrict__ x,
+                                                                 int64_t row_stride,
+                                                                 const int64_t* __restrict__ segs,
+                                                                 int S, float* __restrict__ out,
+                                                                 Scratch s) {
+  __shared__ float smem[33];
+  const int64_t k = blockIdx.z, seg = blockIdx.y;
+  float acc = 0.f;
+  int b = 0;
+  slice_sumsq<T>(x + k * row_stride + segs[2 * seg], segs[2 * seg + 1], blockIdx.x, acc, b);
+  finish_row(acc, b, k * S + seg, blockIdx.x, s, out, nullptr, smem);
+}
+
+}  // namespace nfb
+
+extern "C" size_t nfb_stats_scratch_bytes(int64_t rows) {
+  return nfb::scratch_bytes(rows < 1 ? 1 : rows);
+}
+
+extern "C" int nfb_update_stats(const void* x, int x_dtype, int64_t K, int64_t N,
+                                int64_t row_stride, float* sumsq, int* nonfinite, void* scratch,
+                                size_t scratch_bytes, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(x && sumsq && scratch, NFB_EINVAL, "update_stats: null pointer");
+  NFB_REQUIRE(K >= 1 && K <= 65535, NFB_ERANGE, "update_stats: K=%lld outside [1, 65535]",
+              static_cast<long long>(K));
+  NFB_REQUIRE(N >= 0 && row_stride >= N, NFB_EINVAL, "update_stats: bad N/row_stride");
+  NFB_REQUIRE(scratch_bytes >= nfb::scratch_bytes(K), NFB_ERANGE,
+              "update_stats: scratch has %zu bytes, needs %zu", scratch_bytes,
+              nfb::scratch_bytes(K));
+  const Scratch s = carve(scratch, K);
+  const dim3 grid(kSlices, static_cast<unsigned>(K));
+  cudaStream_t st = as_stream(stream);
+  return dispatch_dtype(x_dtype, [&](auto tag) {
+    using T = decltype(tag);
+    rows_sumsq_kernel<T><<<grid, kThreads, 0, st>>>(static_cast<const T*>(x), N, row_stride,
+                                                    sumsq, nonfinite, s);
+    return launch_status("update_stats");
+  });
+}
+
+extern "C" int nfb_multi_sumsq(const void* const* ptrs, const int64_t* lens, int T_, int dtype,
+                               float* sumsq, int* nonfinite, void* scratch, size_t scratch_bytes,
+                               void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(ptrs && lens && sumsq && scratch, NFB_EINVAL, "multi_sumsq: null pointer");
+  NFB_REQUIRE(T_ >= 1 && T_ <= 65535, NFB_ERANGE, "multi_sumsq: T=%d outside [1, 65535]", T_);
+  NFB_REQUIRE(scratch_bytes >= nfb::scratch_bytes(T_), NFB_ERANGE,
+              "multi_sumsq: scratch has %zu bytes, needs %zu", scratch_bytes,
+              nfb::scratch_bytes(T_));
+  const Scratch s = carve(scratch, T_);
+  const dim3 grid(kSlices, static_cast<unsigned>(T_));
+  cudaStream_t st = as_stream(stream);
+  return dispatch_dtype(dtype, [&](auto tag) {
+    using T = decltype(tag);
+    table_sumsq_kernel<T><<<grid, kThreads, 0, st>>>(ptrs, lens, sumsq, nonfinite, s);
+    return launch_status("multi_sumsq");
+  });
+}
+
+extern "C" int nfb_segment_sumsq(const void* x, int x_dtype, int64_t K, int64_t row_stride,
+                                 const int64_t* segs, int S, float* out, void* scratch,
+                                 size_t scratch_bytes, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(x && segs && out && scratch, NFB_EINVAL, "segment_sumsq: null pointer");
+  NFB_REQUIRE(K >= 1 && K <= 65535 && S >= 1 && S <= 65535, NFB_ERANGE,
+              "segment_sumsq: K or S outside [1, 65535]");
+  NFB_REQUIRE(scratch_bytes >= nfb::scratch_bytes(K * S), NFB_ERANGE,
+              "segment_sumsq: scratch has %zu bytes, needs %zu", scratch_bytes,
+              nfb::scratch_bytes(K * S));
+  const Scratch s = carve(scratch, K * S);
+  const dim3 grid(kSlices, static_cast<unsigned>(S), static_cast<unsigned>(K));
+  cudaStream_t st = as_stream(stream);
+  return dispatch_dtype(x_dtype, [&](auto tag) {
+    using T = decltype(tag);
+    segment_sumsq_kernel<T><<<grid, kThreads, 0, st>>>(static_cast<const T*>(x), row_stride,
+                                                       segs, S, out, s);
+    return launch_status("segment_sumsq");
+  });
+}

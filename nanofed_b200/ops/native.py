@@ -75,6 +75,7 @@ _i64 = C.c_int64
 _i32 = C.c_int
 _f32 = C.c_float
 _u64 = C.c_uint64
+_sz = C.c_size_t
 
 
 def _ptr(t: torch.Tensor | None) -> int | None:
@@ -105,11 +106,13 @@ def _declare(L: C.CDLL) -> None:
     L.nfb_last_error.restype = C.c_char_p
     L.nfb_last_error.argtypes = []
     L.nfb_version.restype = C.c_int
+    L.nfb_stats_scratch_bytes.restype = C.c_size_t
+    L.nfb_stats_scratch_bytes.argtypes = [_i64]
     sigs = {
         "nfb_philox_fill": [_vp, _i32, _i64, _i32, _f32, _u64, _u64, _vp],
-        "nfb_update_stats": [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _vp],
-        "nfb_multi_sumsq": [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp],
-        "nfb_segment_sumsq": [_vp, _i32, _i64, _i64, _vp, _i32, _vp, _vp],
+        "nfb_update_stats": [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _vp, _sz, _vp],
+        "nfb_multi_sumsq": [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _sz, _vp],
+        "nfb_segment_sumsq": [_vp, _i32, _i64, _i64, _vp, _i32, _vp, _vp, _sz, _vp],
         "nfb_fedavg_reduce": [_vp, _i32, _i64, _i64, _i64, _vp, _vp, _vp, _f32, _f32, _vp,
                               _vp, _u64, _u64, _vp, _vp, _i32, _i32, _vp, _vp],
         "nfb_bcast_global": [_vp, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
@@ -144,17 +147,33 @@ def philox_fill_(out: torch.Tensor, kind: int, scale: float, seed: int, offset: 
 # ---------------------------------------------------------------------------
 # K-STATS
 # ---------------------------------------------------------------------------
-def _partials(device: torch.device, n: int) -> torch.Tensor:
-    return torch.empty(n, dtype=torch.float32, device=device)
+_scratch: dict[tuple[int, int], torch.Tensor] = {}
+
+
+def stats_scratch(device: torch.device, rows: int) -> torch.Tensor:
+    """Zero-initialised reduction scratch for ``rows`` rows, cached per (device, stream).
+
+    The kernels leave it zeroed ("self-cleaning"), so it is zero-filled only when it is
+    (re)allocated.  Keyed by stream because two launches that overlap must not share it.
+    """
+    need = int(lib().nfb_stats_scratch_bytes(rows))
+    key = (device.index or 0, torch.cuda.current_stream(device).cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
 
 
 def update_stats(x: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     assert x.dim() == 2 and x.stride(1) == 1
     k, n = x.shape
-    sumsq = torch.zeros(k, dtype=torch.float32, device=x.device)
-    bad = torch.zeros(k, dtype=torch.int32, device=x.device)
+    sumsq = torch.empty(k, dtype=torch.float32, device=x.device)
+    bad = torch.empty(k, dtype=torch.int32, device=x.device)
+    scratch = stats_scratch(x.device, k)
     _check(lib().nfb_update_stats(x.data_ptr(), _dt(x), k, n, x.stride(0), sumsq.data_ptr(),
-                                  bad.data_ptr(), _stream(x)), "update_stats")
+                                  bad.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                  _stream(x)), "update_stats")
     _count()
     return sumsq, bad
 
@@ -172,29 +191,28 @@ def _ptr_table(tensors: Sequence[torch.Tensor]) -> tuple[torch.Tensor, torch.Ten
     return table[0], table[1], _dt(tensors[0])
 
 
+def _multi(ptrs, lens, dt, count, dev):
+    out = torch.empty(count, dtype=torch.float32, device=dev)
+    bad = torch.empty(count, dtype=torch.int32, device=dev)
+    scratch = stats_scratch(dev, count)
+    _check(lib().nfb_multi_sumsq(ptrs.data_ptr(), lens.data_ptr(), count, dt, out.data_ptr(),
+                                 bad.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                 torch.cuda.current_stream(dev).cuda_stream), "multi_sumsq")
+    _count()
+    return out, bad
+
+
 def sumsq_multi(tensors: Sequence[torch.Tensor]) -> torch.Tensor:
     ptrs, lens, dt = _ptr_table(tensors)
     dev = tensors[0].device
-    out = torch.zeros(len(tensors), dtype=torch.float32, device=dev)
-    bad = torch.zeros(len(tensors), dtype=torch.int32, device=dev)
-    total = torch.zeros((), dtype=torch.float32, device=dev)
-    _check(lib().nfb_multi_sumsq(ptrs.data_ptr(), lens.data_ptr(), None, len(tensors), dt,
-                                 out.data_ptr(), bad.data_ptr(),
-                                 torch.cuda.current_stream(dev).cuda_stream), "multi_sumsq")
-    _count()
+    out, _ = _multi(ptrs, lens, dt, len(tensors), dev)
     return out.sum()
 
 
 def per_tensor_stats(tensors: Sequence[torch.Tensor]) -> tuple[torch.Tensor, torch.Tensor]:
     ptrs, lens, dt = _ptr_table(tensors)
     dev = tensors[0].device
-    out = torch.zeros(len(tensors), dtype=torch.float32, device=dev)
-    bad = torch.zeros(len(tensors), dtype=torch.int32, device=dev)
-    _check(lib().nfb_multi_sumsq(ptrs.data_ptr(), lens.data_ptr(), None, len(tensors), dt,
-                                 out.data_ptr(), bad.data_ptr(),
-                                 torch.cuda.current_stream(dev).cuda_stream), "multi_sumsq")
-    _count()
-    return out, bad
+    return _multi(ptrs, lens, dt, len(tensors), dev)
 
 
 def segment_sumsq(x: torch.Tensor, segments: torch.Tensor) -> torch.Tensor:
@@ -204,8 +222,10 @@ def segment_sumsq(x: torch.Tensor, segments: torch.Tensor) -> torch.Tensor:
     s = seg.shape[0]
     out = torch.zeros(k, s, dtype=torch.float32, device=x.device)
     if s:
+        scratch = stats_scratch(x.device, k * s)
         _check(lib().nfb_segment_sumsq(x.data_ptr(), _dt(x), k, x.stride(0), seg.data_ptr(), s,
-                                       out.data_ptr(), _stream(x)), "segment_sumsq")
+                                       out.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                       _stream(x)), "segment_sumsq")
         _count()
     return out
 

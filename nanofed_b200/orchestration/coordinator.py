@@ -332,7 +332,7 @@ class Coordinator:
     async def _engine_round(self, start_time: datetime) -> RoundMetrics:
         """In-box round: the cohort engine trains and aggregates on the GPUs."""
         loop = asyncio.get_running_loop()
-        outcome = await loop.run_in_executor(None, self._engine.run_round, self._current_round)
+        outcome = await loop.run_in_executor(None, getattr(self._engine, "run_round_for_coordinator", getattr(self._engine, "run_round", None)), self._current_round)
         self._status = RoundStatus.AGGREGATING
         for cm in outcome.client_metrics:
             self._clients[cm["client_id"]] = ClientInfo(

@@ -1,0 +1,500 @@
+"""Cohort scheduler: simulated clients packed onto the GPUs of one box.
+
+No reference counterpart — the reference's "clients" are coroutines that train
+one after another on a shared event loop (``run_experiment.py:126-131``;
+``tutorial.ipynb:406-506``) and exchange models as JSON over HTTP.  Here:
+
+* a **client** is a row of the arena (weights, gradients, optimiser state,
+  sample count, participation flag) plus a shard of a device-resident dataset;
+* a **cohort** is the set of clients of one GPU; they train in lock-step, so each
+  local step is a bounded number of launches regardless of the client count;
+* a **round** is ``K-BCAST → local steps → K-STATS → K-AGG`` enqueued without a
+  single host sync; per-round metrics come back in one tiny D2H copy;
+* across GPUs (one process per GPU) the aggregation is one fused kernel over
+  peer memory (``parallel.peer``), NCCL being the baseline only.
+
+Two engines implement ``local_steps()``:
+
+* ``MnistCohortNet`` (``models.mnist_cohort``) — the flagship: hand-written
+  sm_100a kernels, clients as the GEMM group dimension;
+* ``AutogradCohort`` (this file) — any ``nn.Module``: per-client autograd on a
+  pool of CUDA streams, parameters and gradients bound to arena views, the whole
+  local epoch captured in ONE CUDA graph, with K-XENT / K-OPT hand-written.
+
+``FedSimulation`` is the public entry point (``bench.py`` and the CLI use it) and
+plugs into ``Coordinator(engine=…)`` for checkpointing with the reference's
+on-disk layout.
+"""
+
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Any, Callable
+
+import torch
+import torch.nn as nn
+
+from nanofed_b200 import ops
+from nanofed_b200.data.synthetic import ClientShards, make_client_shards
+from nanofed_b200.privacy.accountant import GaussianAccountant
+from nanofed_b200.privacy.config import PrivacyConfig
+from nanofed_b200.runtime import dist as rdist
+from nanofed_b200.runtime.arena import Arena
+from nanofed_b200.runtime.flat import FlatLayout
+from nanofed_b200.utils import Logger, PhaseTimer
+
+
+@dataclass
+class CohortConfig:
+    """How to pack and train simulated clients (SURVEY §5.6 'one new config')."""
+
+    model: str = "mnist_cnn"            # "mnist_cnn" | "resnet18" | "resnet18_gn"
+    clients_per_gpu: int = 32
+    samples_per_client: int = 512
+    batch_size: int = 64
+    local_epochs: int = 1
+    learning_rate: float = 0.1
+    momentum: float = 0.0
+    weight_decay: float = 0.0
+    compute_dtype: str = "bf16"         # "bf16" | "fp32"
+    engine: str = "auto"                # "auto" | "grouped" | "autograd"
+    streams_per_gpu: int = 4
+    use_cuda_graph: bool = True
+    transport: str = "peer"             # "peer" (fused kernel) | "nccl" (baseline)
+    privacy: PrivacyConfig | None = None  # central DP fused into K-AGG
+    seed: int = 0
+    device: str | None = None
+    max_steps_per_epoch: int | None = None
+    sample_counts: list[int] | None = None  # per-client n_k on this rank (≤ samples_per_client)
+
+    @property
+    def steps_per_epoch(self) -> int:
+        steps = self.samples_per_client // self.batch_size
+        if self.max_steps_per_epoch is not None:
+            steps = min(steps, self.max_steps_per_epoch)
+        return max(steps, 1)
+
+    @property
+    def local_steps(self) -> int:
+        return self.steps_per_epoch * self.local_epochs
+
+
+@dataclass
+class RoundOutcome:
+    round_id: int
+    num_clients: int
+    agg_metrics: dict[str, float]
+    client_metrics: list[dict[str, Any]]
+    samples: int
+    phase_ms: dict[str, float] = field(default_factory=dict)
+
+
+def build_model(name: str) -> nn.Module:
+    from nanofed_b200.models import MNISTModel, ResNet18
+
+    if name == "mnist_cnn":
+        return MNISTModel()
+    if name == "resnet18":
+        return ResNet18(norm="batch")
+    if name == "resnet18_gn":
+        return ResNet18(norm="group")
+    raise ValueError(f"unknown model {name!r}")
+
+
+# ---------------------------------------------------------------------------
+# K-XENT as an autograd node (AutogradCohort's loss)
+# ---------------------------------------------------------------------------
+class _FusedXent(torch.autograd.Function):
+    """Mean cross-entropy whose forward already produced ``dlogits`` and device stats."""
+
+    @staticmethod
+    def forward(ctx, logits: torch.Tensor, targets: torch.Tensor, stats: torch.Tensor | None):
+        lg = logits.contiguous()
+        loss_sum, _, dlogits = ops.xent_fused(lg.unsqueeze(0), targets.unsqueeze(0), stats=stats)
+        ctx.save_for_backward(dlogits.squeeze(0))
+        return loss_sum.squeeze(0) / lg.shape[0]
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits * grad_out, None, None
+
+
+def fused_cross_entropy(logits, targets, stats=None):
+    return _FusedXent.apply(logits, targets, stats)
+
+
+# ---------------------------------------------------------------------------
+# Generic engine: any nn.Module, autograd per client, flat arena + fused ops
+# ---------------------------------------------------------------------------
+def _locate(module: nn.Module, dotted: str) -> tuple[nn.Module, str]:
+    owner = module
+    parts = dotted.split(".")
+    for p in parts[:-1]:
+        owner = getattr(owner, p)
+    return owner, parts[-1]
+
+
+class AutogradCohort:
+    """Local training for C clients of one GPU through PyTorch autograd.
+
+    Every client's parameters/buffers are *views* of its arena row and its
+    gradients are views of the gradient slab, so (a) the optimiser is one fused
+    K-OPT launch over the whole ``[C·N]`` slab per step, (b) K-AGG reads the
+    trained weights in place, and (c) nothing is copied at round boundaries.
+    ``streams_per_gpu`` worker modules run clients concurrently on separate CUDA
+    streams; the whole local epoch (all clients × all steps) is captured once in
+    a CUDA graph and replayed each round — the launch-bound inner loop costs one
+    ``cudaGraphLaunch``.
+    """
+
+    def __init__(self, cfg: CohortConfig, arena: Arena, shards: ClientShards) -> None:
+        self.cfg = cfg
+        self.arena = arena
+        self.shards = shards
+        self.device = arena.device
+        self.cuda = self.device.type == "cuda"
+        self.logger = Logger()
+        n_workers = max(1, min(cfg.streams_per_gpu, arena.num_clients)) if self.cuda else 1
+        self.workers = [build_model(cfg.model).to(self.device).train() for _ in range(n_workers)]
+        self.streams = (
+            [torch.cuda.Stream(device=self.device) for _ in range(n_workers)] if self.cuda else []
+        )
+        layout = arena.layout
+        self._param_names = [n for n, _ in self.workers[0].named_parameters()]
+        self._float_buffers = [
+            n for n, b in self.workers[0].named_buffers() if b.is_floating_point() and n in layout
+        ]
+        self._int_buffers = [
+            n for n, b in self.workers[0].named_buffers()
+            if not b.is_floating_point() and n in layout
+        ]
+        # integer state (e.g. BatchNorm counters) lives outside the fp32 arena
+        self._int_state = [
+            {n: torch.zeros(layout[n].shape, dtype=layout[n].dtype, device=self.device)
+             for n in self._int_buffers}
+            for _ in range(arena.num_clients)
+        ]
+        self._slot_views = [arena.client_views(k) for k in range(arena.num_clients)]
+        self._grad_views = [arena.grad_views(k) for k in range(arena.num_clients)]
+        self._graph: "torch.cuda.CUDAGraph | None" = None
+        self._autocast = cfg.compute_dtype == "bf16" and self.cuda
+        self.launches_per_round = 0
+
+    # -- binding ---------------------------------------------------------------
+    def _bind(self, worker: nn.Module, k: int) -> None:
+        slots, grads = self._slot_views[k], self._grad_views[k]
+        for name in self._param_names:
+            owner, attr = _locate(worker, name)
+            p = owner._parameters[attr]
+            p.data = slots[name]
+            p.grad = grads[name]
+        for name in self._float_buffers:
+            owner, attr = _locate(worker, name)
+            owner._buffers[attr] = slots[name]
+        for name in self._int_buffers:
+            owner, attr = _locate(worker, name)
+            owner._buffers[attr] = self._int_state[k][name]
+
+    def after_broadcast(self) -> None:
+        """Integer entries: arena (fp32) → per-client integer tensors."""
+        if not self._int_buffers:
+            return
+        master = self.arena.layout.views(self.arena.master)
+        for state in self._int_state:
+            for name, t in state.items():
+                t.copy_(master[name].to(t.dtype))
+
+    def before_aggregate(self) -> None:
+        """Integer entries: per-client integer tensors → arena rows (as fp32)."""
+        if not self._int_buffers:
+            return
+        for k, state in enumerate(self._int_state):
+            for name, t in state.items():
+                self._slot_views[k][name].copy_(t.to(torch.float32))
+
+    # -- one lock-step local step for all clients ----------------------------------
+    def _client_step(self, worker: nn.Module, k: int, step: int) -> None:
+        cfg = self.cfg
+        lo = (step % cfg.steps_per_epoch) * cfg.batch_size
+        x = self.shards.images[k, lo : lo + cfg.batch_size]
+        y = self.shards.labels[k, lo : lo + cfg.batch_size]
+        self._bind(worker, k)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self._autocast):
+            logits = worker(x)
+        loss = fused_cross_entropy(logits.float(), y, self.arena.stats[k : k + 1])
+        loss.backward()
+
+    def _all_steps(self) -> None:
+        cfg, arena = self.cfg, self.arena
+        c = arena.num_clients
+        main = torch.cuda.current_stream(self.device) if self.cuda else None
+        for step in range(cfg.local_steps):
+            arena.grads.zero_()
+            if self.cuda:
+                for s in self.streams:
+                    s.wait_stream(main)
+                for k in range(c):
+                    w = k % len(self.workers)
+                    with torch.cuda.stream(self.streams[w]):
+                        self._client_step(self.workers[w], k, step)
+                for s in self.streams:
+                    main.wait_stream(s)
+            else:
+                for k in range(c):
+                    self._client_step(self.workers[0], k, step)
+            ops.fused_sgd_(
+                arena.slots.view(-1), arena.grads.view(-1), cfg.learning_rate,
+                momentum_buf=None if arena.momentum is None else arena.momentum.view(-1),
+                momentum=cfg.momentum, weight_decay=cfg.weight_decay,
+                first_step=(step == 0),
+            )
+
+    def local_steps(self) -> None:
+        """Enqueue the whole local epoch(s) for every client of this GPU."""
+        if not (self.cuda and self.cfg.use_cuda_graph):
+            self._all_steps()
+            return
+        if self._graph is None:
+            self._capture()
+        self._graph.replay()
+
+    def _capture(self) -> None:
+        # Warm up eagerly (cuDNN heuristics, lazy inits) on a side stream, restoring
+        # the arena afterwards so warm-up leaves no trace in the model state.
+        arena = self.arena
+        keep = (arena.slots.clone(), arena.stats.clone(),
+                None if arena.momentum is None else arena.momentum.clone(),
+                [{n: t.clone() for n, t in s.items()} for s in self._int_state])
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            # one eager step per client is enough to initialise every lazy path
+            old_cap, old_epochs = self.cfg.max_steps_per_epoch, self.cfg.local_epochs
+            self.cfg.max_steps_per_epoch, self.cfg.local_epochs = 1, 1
+            try:
+                self._all_steps()
+            finally:
+                self.cfg.max_steps_per_epoch, self.cfg.local_epochs = old_cap, old_epochs
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+
+        def restore() -> None:
+            arena.slots.copy_(keep[0])
+            arena.stats.copy_(keep[1])
+            if keep[2] is not None:
+                arena.momentum.copy_(keep[2])
+            for s, saved in zip(self._int_state, keep[3]):
+                for n, t in s.items():
+                    t.copy_(saved[n])
+
+        restore()
+        from nanofed_b200.ops import native
+
+        before = native.LAUNCHES
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            self._all_steps()
+        self.launches_per_round = native.LAUNCHES - before
+        restore()
+        torch.cuda.synchronize(self.device)
+        self._graph = graph
+
+
+# ---------------------------------------------------------------------------
+# Public entry point
+# ---------------------------------------------------------------------------
+class FedSimulation:
+    """Runs federated rounds for ``clients_per_gpu × world_size`` simulated clients.
+
+    >>> sim = FedSimulation(CohortConfig(model="mnist_cnn", clients_per_gpu=32))
+    >>> out = sim.run_round()            # one FedAvg round, metrics as Python floats
+    >>> sim.global_state()               # CPU state_dict, reference-loadable
+
+    ``run_round(host_inputs=(images, labels))`` additionally stages that round's
+    inputs from (pinned) host memory — the end-to-end path ``bench.py`` times.
+    """
+
+    def __init__(
+        self,
+        cfg: CohortConfig,
+        shards: ClientShards | None = None,
+        initial_state: dict[str, torch.Tensor] | None = None,
+    ) -> None:
+        self.cfg = cfg
+        self.rank = rdist.init(cfg.device)
+        self.device = self.rank.device
+        self.logger = Logger()
+        self.timer = PhaseTimer(enabled=True)
+        torch.manual_seed(cfg.seed)  # same initial model on every rank
+
+        template = build_model(cfg.model)
+        if initial_state is not None:
+            template.load_state_dict(initial_state)
+        self.template = template
+        self.layout = FlatLayout.from_module(template)
+        c = cfg.clients_per_gpu
+
+        engine = cfg.engine
+        if engine == "auto":
+            engine = "grouped" if (cfg.model == "mnist_cnn" and self.device.type == "cuda"
+                                   and _grouped_available()) else "autograd"
+        self.engine_name = engine
+
+        self.arena = Arena(
+            self.layout, c, self.device,
+            with_momentum=cfg.momentum != 0.0,
+            with_lowp=(engine == "grouped"),
+            with_grads=(engine == "autograd"),
+        )
+        self.arena.load_global(template.state_dict())
+
+        if shards is None:
+            shards = make_client_shards(
+                c, cfg.samples_per_client,
+                input_shape=tuple(getattr(template, "INPUT_SHAPE", (1, 28, 28))),
+                num_classes=int(getattr(template, "NUM_CLASSES", 10)),
+                seed=cfg.seed * 1000 + self.rank.rank, sample_counts=cfg.sample_counts,
+            )
+        self.shards = shards.to(self.device)
+        self.arena.counts.copy_(self.shards.sample_counts.to(torch.float32))
+        self._counts_host = [float(v) for v in shards.sample_counts.tolist()]
+
+        if engine == "grouped":
+            from nanofed_b200.models.mnist_cohort import MnistCohortNet
+
+            self.engine: Any = MnistCohortNet(cfg, self.arena, self.shards)
+        else:
+            self.engine = AutogradCohort(cfg, self.arena, self.shards)
+
+        self.reducer = None
+        if self.rank.distributed:
+            from nanofed_b200.parallel.peer import make_reducer
+
+            self.reducer = make_reducer(cfg.transport, self.arena, self.rank)
+
+        self.accountant = GaussianAccountant(cfg.privacy) if cfg.privacy else None
+        self._noise_offset = 0
+        self._round = 0
+        self._stats_host = torch.zeros(c, 3, pin_memory=self.device.type == "cuda")
+        self.coordinator = None
+
+    # -- properties ------------------------------------------------------------
+    @property
+    def num_clients(self) -> int:
+        return self.cfg.clients_per_gpu * self.rank.world_size
+
+    @property
+    def samples_per_round(self) -> int:
+        """Client-samples trained per round over the whole job."""
+        return self.num_clients * self.cfg.local_steps * self.cfg.batch_size
+
+    def attach(self, coordinator: Any) -> None:
+        self.coordinator = coordinator
+
+    # -- one round -------------------------------------------------------------
+    def stage_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> int:
+        """H2D copy of this round's inputs into the resident shard tensors; returns bytes."""
+        self.shards.images.copy_(images, non_blocking=True)
+        self.shards.labels.copy_(labels, non_blocking=True)
+        return images.numel() * images.element_size() + labels.numel() * labels.element_size()
+
+    def enqueue_round(self) -> None:
+        """Enqueue one full round on the current stream.  No host synchronisation."""
+        arena, cfg = self.arena, self.cfg
+        arena.stats.zero_()
+        with self.timer.phase("bcast"):
+            ops.bcast_global(arena.master, arena.slots, arena.slots_lowp, arena.momentum)
+            self.engine.after_broadcast()
+        with self.timer.phase("local_train"):
+            self.engine.local_steps()
+        with self.timer.phase("aggregate"):
+            self.engine.before_aggregate()
+            dp = cfg.privacy
+            kw: dict[str, Any] = {}
+            if dp is not None:
+                ss, bad = ops.update_stats(arena.slots)
+                arena.sumsq.copy_(ss)
+                arena.nonfinite.copy_(bad)
+                k_total = self.num_clients
+                kw = dict(sumsq=arena.sumsq, clip_norm=float(dp.max_gradient_norm),
+                          noise_std=dp.noise_multiplier * dp.max_gradient_norm / k_total,
+                          noise_mask=arena.noise_mask, seed=cfg.seed + 7919,
+                          offset=self._noise_offset)
+                self._noise_offset += arena.layout.total
+            if self.reducer is None:
+                ops.fedavg_reduce(arena.slots, arena.counts, out=arena.master,
+                                  out_lowp=arena.master_lowp, mask=arena.mask, **kw)
+            else:
+                self.reducer.reduce(arena, **kw)
+
+    def run_round(
+        self, host_inputs: tuple[torch.Tensor, torch.Tensor] | None = None
+    ) -> RoundOutcome:
+        if host_inputs is not None:
+            self.stage_inputs(*host_inputs)
+        self.enqueue_round()
+        # the round's only device→host transfer: per-client (loss_sum, correct, samples)
+        self._stats_host.copy_(self.arena.stats, non_blocking=True)
+        if self.device.type == "cuda":
+            torch.cuda.current_stream(self.device).synchronize()
+        outcome = self._summarise(self._round)
+        if self.accountant is not None:
+            for _ in range(self.num_clients):
+                self.accountant.add_noise_event(self.cfg.privacy.noise_multiplier,
+                                                self.num_clients)
+            spent = self.accountant.get_privacy_spent()
+            outcome.agg_metrics["privacy_epsilon"] = spent.epsilon_spent
+            outcome.agg_metrics["privacy_delta"] = spent.delta_spent
+        self._round += 1
+        return outcome
+
+    def _summarise(self, round_id: int) -> RoundOutcome:
+        stats = self._stats_host
+        counts = self._counts_host
+        total = sum(counts)
+        base = self.rank.rank * self.cfg.clients_per_gpu
+        client_metrics = []
+        agg = {"loss": 0.0, "accuracy": 0.0, "samples_processed": 0.0}
+        per_epoch = self.cfg.steps_per_epoch * self.cfg.batch_size
+        for k in range(self.cfg.clients_per_gpu):
+            loss_sum, correct, seen = (float(v) for v in stats[k])
+            seen = max(seen, 1.0)
+            m = {"loss": loss_sum / seen, "accuracy": correct / seen,
+                 "samples_processed": int(min(seen, per_epoch))}
+            w = counts[k] / total
+            client_metrics.append({"client_id": f"client_{base + k}", "metrics": m, "weight": w})
+            for name in agg:
+                agg[name] += w * float(m[name])
+        return RoundOutcome(round_id, self.cfg.clients_per_gpu, agg, client_metrics,
+                            samples=self.cfg.clients_per_gpu * self.cfg.local_steps
+                            * self.cfg.batch_size)
+
+    # -- checkpoints -------------------------------------------------------------
+    def global_state(self) -> dict[str, torch.Tensor]:
+        return self.arena.global_state()
+
+    def sync_model(self, model: nn.Module | None = None) -> nn.Module:
+        """Copy the arena's global model into ``model`` (default: the template)."""
+        model = model or self.template
+        model.load_state_dict(self.global_state())
+        return model
+
+    # ``Coordinator(engine=sim)`` calls this from a worker thread.
+    def run_round_for_coordinator(self, round_id: int) -> RoundOutcome:
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+        outcome = self.run_round()
+        if self.coordinator is not None:
+            self.sync_model(self.coordinator.model_manager.model)
+        return outcome
+
+
+def _grouped_available() -> bool:
+    try:
+        from nanofed_b200.models import mnist_cohort  # noqa: F401
+
+        return mnist_cohort.AVAILABLE
+    except Exception:
+        return False

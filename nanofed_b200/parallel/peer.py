@@ -1,0 +1,268 @@
+"""In-box transport: cross-GPU aggregation + broadcast over peer memory.
+
+Replaces, for clients that live on the GPUs of one box, the reference's whole
+HTTP round trip (``POST /update`` → ``Coordinator`` list→tensor rebuild →
+``FedAvgAggregator`` → ``GET /model``).  Two reducers share one
+interface, ``reduce(arena, **dp_kwargs)``:
+
+* ``PeerReducer`` — the product path.  One launch of
+  ``csrc/fedavg_allreduce.cu`` per rank does local weighted reduce → flag
+  barrier → in-kernel reduce-scatter over NVLink (P2P loads or NVLS
+  ``multimem.ld_reduce``) → FedAvg epilogue (1/Σn, DP noise, bf16 cast) →
+  all-gather by storing the shard into every rank's global-model buffers (P2P
+  stores or ``multimem.st``) → flag barrier.  Buffers live in a symmetric
+  allocation obtained from ``torch.distributed._symmetric_memory`` (allocation +
+  handle exchange only; every byte is moved by our kernel).
+* ``NcclReducer`` — the baseline the north star names: per-rank weighted partial
+  sum, ``dist.all_reduce``, then separate scale / noise / cast kernels.  Also the
+  path used on CPU (gloo) for the host-logic tests.
+
+``emulate_allreduce`` runs G emulated ranks of the fused kernel as ONE
+cooperative launch on a single GPU, which is how it is unit-tested without
+co-scheduling kernels that wait on each other.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Any
+
+import torch
+import torch.distributed as dist
+
+from nanofed_b200 import ops
+from nanofed_b200.runtime.arena import Arena
+from nanofed_b200.runtime.dist import RankInfo
+from nanofed_b200.utils import Logger
+
+_ALIGN = 256
+_SPIN_NS = 10_000_000_000  # 10 s: far above any legitimate wait, far below a gpurun limit
+
+
+def _round_up(v: int, a: int = _ALIGN) -> int:
+    return (v + a - 1) // a * a
+
+
+def _declare(lib: C.CDLL) -> None:
+    if getattr(lib, "_nfb_allreduce_declared", False):
+        return
+    vp, i32, i64, f32, u64, u32 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64, C.c_uint32
+    lib.nfb_fedavg_allreduce.restype = i32
+    lib.nfb_fedavg_allreduce.argtypes = [vp, i32, i32, i32, i32, i64, i64, i64, f32, f32, vp, u64,
+                                         u64, u32, u64, i32, vp, vp, vp, vp, u64, vp]
+    lib.nfb_allreduce_max_blocks.restype = i32
+    lib.nfb_allreduce_max_blocks.argtypes = [i32, i64]
+    lib._nfb_allreduce_declared = True
+
+
+class _Layout:
+    """Byte offsets of the symmetric buffer's regions."""
+
+    def __init__(self, n: int, g: int) -> None:
+        self.n, self.g = n, g
+        self.partial = 0
+        self.master = _round_up(self.partial + 4 * n)
+        self.lowp = _round_up(self.master + 4 * n)
+        self.scal = _round_up(self.lowp + 2 * n)
+        self.flags = self.scal + _ALIGN
+        self.total = self.flags + _round_up(4 * 2 * g)
+
+
+class NcclReducer:
+    """Baseline: torch partial sum + ``all_reduce`` + separate elementwise kernels."""
+
+    path = "nccl_allreduce"
+
+    def __init__(self, arena: Arena, rank: RankInfo) -> None:
+        self.rank = rank
+        self.partial = torch.zeros_like(arena.master)
+        self.scal = torch.zeros(2, dtype=torch.float32, device=arena.device)
+
+    def reduce(self, arena: Arena, *, sumsq=None, clip_norm: float = 0.0, noise_std: float = 0.0,
+               noise_mask=None, seed: int = 0, offset: int = 0) -> None:
+        ops.fedavg_reduce(arena.slots, arena.counts, out=self.partial, mask=arena.mask,
+                          sumsq=sumsq, clip_norm=clip_norm, normalize=False)
+        eff = arena.counts * arena.mask
+        self.scal[0] = eff.sum()
+        self.scal[1] = (eff * eff).sum()
+        if dist.is_initialized():
+            dist.all_reduce(self.partial)
+            dist.all_reduce(self.scal)
+        torch.div(self.partial, self.scal[0], out=arena.master)
+        if noise_std > 0:
+            z = torch.empty_like(arena.master)
+            ops.philox_normal_(z, 1.0, seed, offset)
+            if noise_mask is not None:
+                z.mul_(noise_mask.to(z.dtype))
+            arena.master.add_(z * (noise_std * self.scal[1].sqrt() / self.scal[0]))
+        arena.master_lowp.copy_(arena.master)
+
+
+class PeerReducer:
+    """Product path: the fused kernel over symmetric (peer-mapped) memory."""
+
+    path = "fused_peer_kernel"
+
+    def __init__(self, arena: Arena, rank: RankInfo, use_multicast: bool | None = None) -> None:
+        import torch.distributed._symmetric_memory as symm
+
+        from nanofed_b200.ops import native
+
+        self.lib = native.lib()
+        _declare(self.lib)
+        self.rank = rank
+        g, n, dev = rank.world_size, arena.layout.total, arena.device
+        self.lay = _Layout(n, g)
+        self.buf = symm.empty(self.lay.total, dtype=torch.uint8, device=dev)
+        self.buf.zero_()
+        group = dist.group.WORLD
+        self.handle = symm.rendezvous(self.buf, group.group_name)
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        if use_multicast is None:
+            use_multicast = os.environ.get("NANOFED_B200_NVLS", "0") == "1"
+        self.mc_base = mc if (use_multicast and mc) else 0
+        if self.mc_base:
+            self.path = "fused_peer_kernel_nvls"
+
+        lay = self.lay
+        self.master = self.buf[lay.master : lay.master + 4 * n].view(torch.float32)
+        self.lowp = self.buf[lay.lowp : lay.lowp + 2 * n].view(torch.bfloat16)
+        self.master.copy_(arena.master)
+        self.lowp.copy_(arena.master_lowp)
+        arena.master, arena.master_lowp = self.master, self.lowp
+
+        self.grid_ctr = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.sumsq_dummy = None
+        rows = []
+        for r in range(g):
+            base = ptrs[r]
+            mine = r == rank.rank
+            rows.append([
+                arena.slots.data_ptr() if mine else 0,
+                arena.counts.data_ptr() if mine else 0,
+                arena.mask.data_ptr() if mine else 0,
+                0,  # sumsq: filled per call
+                base + lay.partial, base + lay.scal, base + lay.flags,
+                base + lay.master, base + lay.lowp,
+                self.grid_ctr.data_ptr() if mine else 0,
+            ])
+        self.views_host = torch.tensor(rows, dtype=torch.int64)
+        self.views = self.views_host.to(dev)
+        self.epoch = 0
+        self.ctr_base = 0
+        max_blocks = int(self.lib.nfb_allreduce_max_blocks(0, arena.num_clients))
+        if max_blocks <= 0:
+            raise RuntimeError("fedavg_allreduce: occupancy query failed")
+        # one wave, at most 4 CTAs per SM: enough loads in flight to saturate HBM/NVLink
+        self.grid = max(1, min(max_blocks, 4 * torch.cuda.get_device_properties(dev).multi_processor_count))
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def reduce(self, arena: Arena, *, sumsq=None, clip_norm: float = 0.0, noise_std: float = 0.0,
+               noise_mask=None, seed: int = 0, offset: int = 0) -> None:
+        from nanofed_b200.ops import native
+
+        r = self.rank.rank
+        want = sumsq.data_ptr() if sumsq is not None else 0
+        if int(self.views_host[r, 3]) != want:
+            self.views_host[r, 3] = want
+            self.views[r, 3] = want
+        self.epoch += 1
+        lay, mc = self.lay, self.mc_base
+        code = self.lib.nfb_fedavg_allreduce(
+            self.views.data_ptr(), r, self.rank.world_size, 1, 0,
+            arena.num_clients, arena.layout.total, arena.slots.stride(0),
+            float(clip_norm), float(noise_std),
+            noise_mask.data_ptr() if noise_mask is not None else None,
+            seed & (2**64 - 1), offset, self.epoch, self.ctr_base, self.grid,
+            (mc + lay.partial) if mc else None, (mc + lay.master) if mc else None,
+            (mc + lay.lowp) if mc else None, self.status.data_ptr(), _SPIN_NS,
+            torch.cuda.current_stream(arena.device).cuda_stream,
+        )
+        native._check(code, "fedavg_allreduce")
+        native._count()
+        self.ctr_base += 4 * self.grid
+
+    def check(self) -> None:
+        """Raise if any barrier timed out (reads one int from the device)."""
+        if int(self.status.item()) != 0:
+            raise RuntimeError("fedavg_allreduce: cross-GPU barrier timed out")
+
+
+def make_reducer(transport: str, arena: Arena, rank: RankInfo) -> Any:
+    log = Logger()
+    if transport == "nccl" or arena.device.type != "cuda":
+        return NcclReducer(arena, rank)
+    try:
+        return PeerReducer(arena, rank)
+    except Exception as exc:  # symmetric memory unavailable on this box
+        log.error(f"peer transport unavailable ({exc!r}); FALLING BACK to the NCCL baseline path")
+        red = NcclReducer(arena, rank)
+        red.path = "nccl_allreduce(fallback)"
+        return red
+
+
+def emulate_allreduce(
+    slots: torch.Tensor,      # [G, K, N] on one GPU
+    counts: torch.Tensor,     # [G, K]
+    *,
+    mask: torch.Tensor | None = None,
+    sumsq: torch.Tensor | None = None,
+    clip_norm: float = 0.0,
+    noise_std: float = 0.0,
+    noise_mask: torch.Tensor | None = None,
+    seed: int = 0,
+    offset: int = 0,
+    calls: int = 1,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """Run G emulated ranks of the fused kernel in one cooperative launch.
+
+    Returns ``(master [G, N] fp32, lowp [G, N] bf16)`` — every row must be equal.
+    """
+    from nanofed_b200.ops import native
+
+    lib = native.lib()
+    _declare(lib)
+    g, k, n = slots.shape
+    dev = slots.device
+    lay = _Layout(n, g)
+    bufs = torch.zeros(g, lay.total, dtype=torch.uint8, device=dev)
+    ctr = torch.zeros(g, dtype=torch.int64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    counts = counts.to(torch.float32).contiguous()
+    mask = torch.ones_like(counts) if mask is None else mask.to(torch.float32).contiguous()
+    rows = []
+    for r in range(g):
+        base = bufs[r].data_ptr()
+        rows.append([
+            slots[r].data_ptr(), counts[r].data_ptr(), mask[r].data_ptr(),
+            sumsq[r].data_ptr() if sumsq is not None else 0,
+            base + lay.partial, base + lay.scal, base + lay.flags, base + lay.master,
+            base + lay.lowp, ctr[r : r + 1].data_ptr(),
+        ])
+    views = torch.tensor(rows, dtype=torch.int64).to(dev)
+    max_blocks = int(lib.nfb_allreduce_max_blocks(native._dt(slots), k))
+    grid = max(1, min(max_blocks // g, 64))
+    base_ctr = 0
+    for call in range(1, calls + 1):
+        code = lib.nfb_fedavg_allreduce(
+            views.data_ptr(), 0, g, g, native._dt(slots), k, n, slots.stride(1),
+            float(clip_norm), float(noise_std),
+            noise_mask.data_ptr() if noise_mask is not None else None,
+            seed & (2**64 - 1), offset, call, base_ctr, grid, None, None, None,
+            status.data_ptr(), 2_000_000_000, torch.cuda.current_stream(dev).cuda_stream,
+        )
+        native._check(code, "fedavg_allreduce(emulated)")
+        native._count()
+        base_ctr += 4 * grid
+    torch.cuda.synchronize(dev)
+    if int(status.item()) != 0:
+        raise RuntimeError("emulated fedavg_allreduce: barrier timed out")
+    master = torch.stack([bufs[r, lay.master : lay.master + 4 * n].view(torch.float32)
+                          for r in range(g)])
+    lowp = torch.stack([bufs[r, lay.lowp : lay.lowp + 2 * n].view(torch.bfloat16)
+                        for r in range(g)])
+    return master, lowp

@@ -1,0 +1,54 @@
+"""Host-side multi-process logic on gloo (world_size 2): NCCL-baseline reducer semantics."""
+
+import os
+import socket
+import sys
+from pathlib import Path
+
+import torch
+import torch.multiprocessing as mp
+
+ROOT = str(Path(__file__).resolve().parent.parent)
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank: int, world: int, port: int, out_dir: str) -> None:
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import logging
+
+    logging.getLogger("nanofed").setLevel(logging.ERROR)
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    cfg = CohortConfig(model="mnist_cnn", clients_per_gpu=2, samples_per_client=16, batch_size=8,
+                       compute_dtype="fp32", engine="autograd", device="cpu", transport="nccl",
+                       sample_counts=[16, 8] if rank == 0 else [4, 16])
+    sim = FedSimulation(cfg)
+    # make local training deterministic: no dropout
+    for w in sim.engine.workers:
+        w.dropout1.p = 0.0
+        w.dropout2.p = 0.0
+    sim.run_round()
+    torch.save({"master": sim.arena.master.clone(), "slots": sim.arena.slots.clone(),
+                "counts": sim.arena.counts.clone()}, f"{out_dir}/r{rank}.pt")
+    from nanofed_b200.runtime import dist as rdist
+
+    rdist.shutdown()
+
+
+def test_two_rank_round_equals_global_fedavg(tmp_path):
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    a = torch.load(tmp_path / "r0.pt")
+    b = torch.load(tmp_path / "r1.pt")
+    assert torch.equal(a["master"], b["master"])  # every rank holds the same global model
+    slots = torch.cat([a["slots"], b["slots"]])
+    counts = torch.cat([a["counts"], b["counts"]])
+    want = (counts / counts.sum()).view(-1, 1).mul(slots).sum(0)
+    torch.testing.assert_close(a["master"], want, rtol=1e-5, atol=1e-6)

@@ -1,0 +1,223 @@
+"""sm_100a kernels vs the pure-PyTorch fp32 oracle (``ops.reference``)."""
+
+import math
+
+import pytest
+import torch
+
+from nanofed_b200 import ops
+from nanofed_b200.ops import reference as ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def test_native_library_is_loaded():
+    from nanofed_b200.ops import native
+
+    assert native.lib().nfb_version() >= 100
+
+
+@pytest.mark.parametrize("kind", ["normal", "laplace", "uniform"])
+def test_philox_matches_host_replica(kind):
+    n, seed, off = 100_003, 1234567, 64
+    out = torch.empty(n, device=DEV)
+    if kind == "normal":
+        ops.philox_normal_(out, 2.0, seed, off)
+        want = ops.philox.normal(n, seed, off) * 2.0
+    elif kind == "laplace":
+        ops.philox_laplace_(out, 0.5, seed, off)
+        want = ops.philox.laplace(n, seed, off) * 0.5
+    else:
+        ops.philox_uniform_(out, seed, off)
+        want = ops.philox.uniform(n, seed, off)
+    torch.testing.assert_close(out.cpu(), want, rtol=2e-4, atol=2e-5)
+
+
+def test_philox_statistics():
+    z = torch.empty(1 << 20, device=DEV)
+    ops.philox_normal_(z, 3.0, 99, 0)
+    assert abs(float(z.mean())) < 0.02 and abs(float(z.std()) - 3.0) < 0.02
+    ops.philox_laplace_(z, 2.0, 99, 0)
+    assert abs(float(z.abs().mean()) - 2.0) < 0.02
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("k,n", [(1, 64), (3, 1024), (32, 1_199_936), (40, 8_000)])
+def test_update_stats(dtype, k, n):
+    x = (torch.randn(k, n, device=DEV) * 0.1).to(dtype)
+    ss, bad = ops.update_stats(x)
+    want, _ = ref.update_stats(x.float().cpu())
+    torch.testing.assert_close(ss.cpu(), want, rtol=1e-4, atol=1e-6)
+    assert int(bad.sum()) == 0
+    # deterministic: two launches, identical bits
+    ss2, _ = ops.update_stats(x)
+    assert torch.equal(ss, ss2)
+    x[k - 1, n // 2] = float("nan")
+    _, bad = ops.update_stats(x)
+    assert bad.tolist() == [0] * (k - 1) + [1]
+
+
+def test_sumsq_multi_and_per_tensor():
+    ts = [torch.randn(s, device=DEV) for s in [(5,), (128, 9216), (10,), (3, 3, 7), ()]]
+    total = ops.sumsq_multi(ts)
+    want = sum(float(t.double().pow(2).sum()) for t in ts)
+    assert math.isclose(float(total), want, rel_tol=1e-5)
+    ss, bad = ops.per_tensor_stats([t for t in ts if t.numel()])
+    assert ss.shape[0] == 5 and int(bad.sum()) == 0
+
+
+def test_segment_sumsq():
+    x = torch.randn(4, 4096, device=DEV)
+    segs = torch.tensor([[0, 100], [128, 1000], [2048, 2048], [5, 1]])
+    got = ops.segment_sumsq(x, segs)
+    want = ref.segment_sumsq(x.cpu(), segs)
+    torch.testing.assert_close(got.cpu(), want, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("k,n", [(1, 64), (3, 640), (7, 4096), (32, 1_199_936), (19, 50_048)])
+def test_fedavg_reduce_plain(dtype, k, n):
+    x = torch.randn(k, n, device=DEV).to(dtype)
+    counts = torch.randint(1, 1000, (k,), device=DEV).float()
+    out = ops.fedavg_reduce(x, counts)
+    want = ref.fedavg_reduce(x.float().cpu(), counts.cpu())
+    torch.testing.assert_close(out.cpu(), want, rtol=1e-5, atol=1e-5)
+
+
+def test_fedavg_reduce_full_dp_path():
+    k, n = 9, 65_536
+    x = torch.randn(k, n, device=DEV) * 0.05
+    counts = torch.arange(1, k + 1, device=DEV).float()
+    mask = torch.ones(k, device=DEV)
+    mask[3] = 0
+    x[3] = float("nan")  # masked-out client may hold garbage
+    ss, _ = ops.update_stats(x)
+    noise_mask = (torch.rand(n, device=DEV) > 0.1).to(torch.uint8)
+    lowp = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    kw = dict(sumsq=ss, mask=mask, clip_norm=1.0, noise_std=0.3, noise_mask=noise_mask,
+              seed=42, offset=128)
+    out = ops.fedavg_reduce(x, counts, out_lowp=lowp, **kw)
+    xc = x.cpu().clone()
+    want = ref.fedavg_reduce(xc, counts.cpu(), sumsq=ss.cpu(), mask=mask.cpu(), clip_norm=1.0,
+                             noise_std=0.3, noise_mask=noise_mask.cpu(), seed=42, offset=128)
+    torch.testing.assert_close(out.cpu(), want, rtol=1e-4, atol=2e-5)
+    torch.testing.assert_close(lowp.float().cpu(), want.bfloat16().float(), rtol=1e-2, atol=1e-2)
+    # injected noise: exact algebra
+    z = torch.randn(n, device=DEV)
+    out2 = ops.fedavg_reduce(x, counts, unit_noise=z, **kw)
+    want2 = ref.fedavg_reduce(xc, counts.cpu(), sumsq=ss.cpu(), mask=mask.cpu(), clip_norm=1.0,
+                              noise_std=0.3, noise_mask=noise_mask.cpu(), unit_noise=z.cpu())
+    torch.testing.assert_close(out2.cpu(), want2, rtol=1e-5, atol=1e-5)
+
+
+def test_fedavg_reduce_accumulate_waves():
+    k, n = 8, 4096
+    x = torch.randn(k, n, device=DEV)
+    c = torch.rand(k, device=DEV) + 0.5
+    acc = torch.zeros(n, device=DEV)
+    ops.fedavg_reduce(x[:4], c[:4], out=acc, normalize=False, accumulate=True)
+    ops.fedavg_reduce(x[4:], c[4:], out=acc, normalize=False, accumulate=True)
+    want = (c.view(-1, 1) * x).sum(0)
+    torch.testing.assert_close(acc, want, rtol=1e-5, atol=1e-5)
+
+
+def test_bcast_global():
+    n, k = 8192, 5
+    g = torch.randn(n, device=DEV)
+    slots = torch.empty(k, n, device=DEV)
+    lowp = torch.empty(k, n, device=DEV, dtype=torch.bfloat16)
+    mom = torch.ones(k, n, device=DEV)
+    ops.bcast_global(g, slots, lowp, mom)
+    assert torch.equal(slots, g.expand(k, n))
+    assert torch.equal(lowp, g.bfloat16().expand(k, n))
+    assert float(mom.abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("momentum,nesterov,wd", [(0.0, False, 0.0), (0.9, False, 1e-3),
+                                                  (0.9, True, 0.0)])
+def test_fused_sgd_matches_torch(momentum, nesterov, wd):
+    n = 10_007
+    p0 = torch.randn(n, device=DEV)
+    pt = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.SGD([pt], lr=0.1, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    p = torch.empty(n + 1, device=DEV)[:n]  # keep 16B alignment of base
+    p = p0.clone()
+    buf = torch.zeros(n, device=DEV)
+    lowp = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    for step in range(3):
+        g = torch.randn(n, device=DEV)
+        pt.grad = g.clone()
+        opt.step()
+        ops.fused_sgd_(p, g, 0.1, momentum_buf=buf, momentum=momentum, nesterov=nesterov,
+                       weight_decay=wd, first_step=(step == 0), lowp_out=lowp)
+    torch.testing.assert_close(p, pt.data, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(lowp.float(), p.bfloat16().float())
+
+
+def test_fused_sgd_dp_front_end():
+    n = 4096
+    p = torch.zeros(n, device=DEV)
+    g = torch.ones(n, device=DEV)
+    scale = torch.tensor(0.5, device=DEV)
+    ops.fused_sgd_(p, g, 1.0, grad_scale=scale, noise_std=2.0, seed=5, offset=0)
+    want = -(0.5 + 2.0 * ops.philox.normal(n, 5, 0))
+    torch.testing.assert_close(p.cpu(), want, rtol=1e-4, atol=1e-4)
+
+
+def test_fused_adam_matches_torch():
+    n = 5000
+    p0 = torch.randn(n, device=DEV)
+    pt = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([pt], lr=1e-2, weight_decay=0.01)
+    p, m, v = p0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    for step in range(1, 4):
+        g = torch.randn(n, device=DEV)
+        pt.grad = g.clone()
+        opt.step()
+        ops.fused_adam_(p, g, m, v, step, 1e-2, weight_decay=0.01, decoupled=True)
+    torch.testing.assert_close(p, pt.data, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_xent_fused(dtype):
+    g, b, c = 6, 64, 10
+    logits = (torch.randn(g, b, c, device=DEV) * 3).to(dtype)
+    t = torch.randint(0, c, (g, b), device=DEV)
+    stats = torch.zeros(g, 3, device=DEV)
+    loss, hit, dl = ops.xent_fused(logits, t, stats=stats)
+    rl, rh, rd = ref.xent_fused(logits.float().cpu(), t.cpu())
+    torch.testing.assert_close(loss.cpu(), rl, rtol=1e-4, atol=1e-3)
+    torch.testing.assert_close(hit.cpu(), rh)
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    torch.testing.assert_close(dl.float().cpu(), rd, rtol=tol, atol=tol)
+    torch.testing.assert_close(stats[:, 2].cpu(), torch.full((g,), float(b)))
+    # torch cross-check
+    want = torch.nn.functional.cross_entropy(logits[0].float(), t[0], reduction="sum")
+    assert math.isclose(float(loss[0]), float(want), rel_tol=1e-4)
+
+
+def test_linear_psgn_matches_autograd():
+    b, fin, fout = 16, 96, 24
+    a = torch.randn(b, fin, device=DEV)
+    d = torch.randn(b, fout, device=DEV)
+    got = ops.linear_per_sample_grad_sqnorms(a, d, bias=True)
+    per = torch.einsum("bi,bo->boi", a, d).flatten(1).pow(2).sum(1) + d.pow(2).sum(1)
+    torch.testing.assert_close(got, per, rtol=1e-4, atol=1e-4)
+
+
+def test_mask_add():
+    x = torch.zeros(1001, device=DEV)
+    cum = torch.zeros(1001, device=DEV)
+    ops.mask_add_(x, cum, 77, 0)
+    torch.testing.assert_close(x.cpu(), ops.philox.uniform(1001, 77, 0), rtol=1e-6, atol=1e-7)
+    assert torch.equal(x, cum)
+
+
+def test_cuda_tensor_without_library_is_loud(monkeypatch):
+    from nanofed_b200.ops import native
+
+    monkeypatch.setattr(native, "_lib", None)
+    monkeypatch.setenv("NANOFED_B200_LIB", "/nonexistent/lib.so")
+    with pytest.raises(native.NativeLibraryError):
+        ops.update_stats(torch.zeros(1, 64, device=DEV))
