@@ -6,8 +6,10 @@
 // order — so the result does not depend on block scheduling (no float atomics) —
 // then zeroes the counter again so the scratch can be reused by the next launch.
 //
-// Scratch layout for `rows` rows:  float partial[rows][SLICES] | int bad[rows][SLICES]
-//                                  | unsigned arrived[rows]      (arrived[] must be 0 on entry)
+// Scratch layout depends only on the BUFFER SIZE, never on the call's row count, so a
+// buffer stays valid ("arrived[] all zero") across calls with different shapes:
+//   cap = bytes / (4 + SLICES*8) rows ;  unsigned arrived[cap] | float partial[cap][SLICES]
+//   | int bad[cap][SLICES].   Always pass the same (pointer, size) pair for one buffer.
 #include "common.cuh"
 
 namespace nfb {
@@ -26,11 +28,16 @@ static size_t scratch_bytes(int64_t rows) {
          static_cast<size_t>(rows) * sizeof(unsigned);
 }
 
-static Scratch carve(void* base, int64_t rows) {
+static int64_t scratch_capacity(size_t bytes) {
+  return static_cast<int64_t>(bytes / (sizeof(unsigned) + kSlices * (sizeof(float) + sizeof(int))));
+}
+
+static Scratch carve(void* base, size_t bytes) {
+  const int64_t cap = scratch_capacity(bytes);
   Scratch s;
-  s.partial = static_cast<float*>(base);
-  s.bad = reinterpret_cast<int*>(s.partial + rows * kSlices);
-  s.arrived = reinterpret_cast<unsigned*>(s.bad + rows * kSlices);
+  s.arrived = static_cast<unsigned*>(base);
+  s.partial = reinterpret_cast<float*>(s.arrived + cap);
+  s.bad = reinterpret_cast<int*>(s.partial + cap * kSlices);
   return s;
 }
 
@@ -178,7 +185,7 @@ extern "C" int nfb_update_stats(const void* x, int x_dtype, int64_t K, int64_t N
   NFB_REQUIRE(scratch_bytes >= nfb::scratch_bytes(K), NFB_ERANGE,
               "update_stats: scratch has %zu bytes, needs %zu", scratch_bytes,
               nfb::scratch_bytes(K));
-  const Scratch s = carve(scratch, K);
+  const Scratch s = carve(scratch, scratch_bytes);
   const dim3 grid(kSlices, static_cast<unsigned>(K));
   cudaStream_t st = as_stream(stream);
   return dispatch_dtype(x_dtype, [&](auto tag) {
@@ -198,7 +205,7 @@ extern "C" int nfb_multi_sumsq(const void* const* ptrs, const int64_t* lens, int
   NFB_REQUIRE(scratch_bytes >= nfb::scratch_bytes(T_), NFB_ERANGE,
               "multi_sumsq: scratch has %zu bytes, needs %zu", scratch_bytes,
               nfb::scratch_bytes(T_));
-  const Scratch s = carve(scratch, T_);
+  const Scratch s = carve(scratch, scratch_bytes);
   const dim3 grid(kSlices, static_cast<unsigned>(T_));
   cudaStream_t st = as_stream(stream);
   return dispatch_dtype(dtype, [&](auto tag) {
@@ -218,7 +225,7 @@ extern "C" int nfb_segment_sumsq(const void* x, int x_dtype, int64_t K, int64_t 
   NFB_REQUIRE(scratch_bytes >= nfb::scratch_bytes(K * S), NFB_ERANGE,
               "segment_sumsq: scratch has %zu bytes, needs %zu", scratch_bytes,
               nfb::scratch_bytes(K * S));
-  const Scratch s = carve(scratch, K * S);
+  const Scratch s = carve(scratch, scratch_bytes);
   const dim3 grid(kSlices, static_cast<unsigned>(S), static_cast<unsigned>(K));
   cudaStream_t st = as_stream(stream);
   return dispatch_dtype(x_dtype, [&](auto tag) {

@@ -1,0 +1,443 @@
+// K-GEMM / K-CONV: one warp-specialised tcgen05 kernel family for every GEMM-shaped op of
+// the cohort training step, with the CLIENT as the group dimension (grid.z) so that C
+// clients' identical-shape, different-weight problems run as one launch.
+//
+//   D_t[g][m, n] = sum over k-blocks of  A[g][m + a_mn(t), k + a_k(t)] * B[g][n + b_mn(t), k + b_k(t)]
+//
+// * operands arrive by TMA (cp.async.bulk.tensor, 3-D maps: element, row, client) into a
+//   STAGES-deep shared-memory ring with 64/128-byte hardware swizzle; either operand may be
+//   K-major ([rows = M or N][K contiguous]) or MN-major ([rows = K][M or N contiguous]), so
+//   forward, dgrad and wgrad all read the SAME activation/weight tensors without transposes;
+// * one elected thread issues tcgen05.mma (UMMA 128 x BN x 16, bf16 -> fp32) into TMEM;
+// * "taps" shift the TMA coordinates per k-block: a 3x3 convolution on a row-flattened
+//   NHWC image grid is 9 shifted GEMMs accumulated in TMEM (implicit GEMM without im2col);
+//   for weight gradients the 9 taps own 9 TMEM accumulators that share one A tile;
+// * 4 epilogue warps read TMEM with tcgen05.ld and apply bias / ReLU / ReLU-mask, then
+//   store (fp32 or bf16, arbitrary element strides => free transposes/permutations) or
+//   atomically accumulate (split-K, weight gradients).
+//
+// Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator,
+// 4..7 = epilogue (warp w owns TMEM lanes 32*(w-4) .. +31).
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace nfb {
+namespace tc {
+
+constexpr int kMaxTaps = 9;
+constexpr int BM = 128;       // UMMA M (TMEM lanes)
+constexpr int UMMA_K = 16;    // bf16
+
+struct Tap {
+  int a_k, a_mn, b_k, b_mn;
+};
+
+struct GemmArgs {
+  int taps;          // 1..9
+  int inner;         // k-blocks per tap (TPS == 1) or total k-blocks (TPS > 1)
+  int k_split;       // K range split over this many CTAs (needs atomic epilogue if > 1)
+  Tap tap[kMaxTaps];
+  // epilogue
+  void* out;
+  int out_bf16;      // 0: fp32, 1: bf16
+  int atomic;        // fp32 atomicAdd instead of store
+  long long out_gs, out_ms, out_ns, out_ts;  // element strides: group, m, n, tap
+  const float* bias; // optional
+  long long bias_gs;
+  int bias_on_m;     // bias index = m (1) or n (0)
+  int relu;
+  const __nv_bfloat16* mask_src;  // optional: out = 0 where mask_src[same index] <= 0
+  int m_valid, n_valid;
+  int vec_store;     // n contiguous (out_ns == 1), non-atomic, 16-byte aligned rows
+  int* status;       // set to 1 if a pipeline wait timed out
+};
+
+template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES>
+struct Cfg {
+  static constexpr int A_TILE = BM * BK * 2;                 // bytes
+  static constexpr int B_TILE = BN * BK * 2;
+  static constexpr int STAGE = A_TILE + TPS * B_TILE;
+  static constexpr int A_ATOM = A_SWZ / 2;                   // MN elements per swizzle atom
+  static constexpr int B_ATOM = B_SWZ / 2;
+  static constexpr int TMEM_NEED = BN * TPS;
+  static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64
+                                   : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
+  static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + 1024 /*align*/ + 256;
+  static_assert(A_MN || A_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
+  static_assert(B_MN || B_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
+  static_assert(A_TILE % 1024 == 0 && B_TILE % 1024 == 0, "tiles must keep 1024-B alignment");
+  static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N");
+  static_assert(TMEM_NEED <= 512, "TMEM columns");
+};
+
+template <bool MN, int SWZ, int BK_, int ROWS>
+__device__ __forceinline__ void load_operand(uint8_t* dst, const CUtensorMap* map, uint64_t* bar,
+                                             int k0, int mn0, int g) {
+  if constexpr (!MN) {
+    tma_load_3d(dst, map, bar, k0, mn0, g);  // box [BK, ROWS, 1]
+  } else {
+    constexpr int ATOM = SWZ / 2;
+#pragma unroll
+    for (int a = 0; a < ROWS / ATOM; ++a)    // box [ATOM, BK, 1] per swizzle atom
+      tma_load_3d(dst + a * (BK_ * SWZ), map, bar, mn0 + a * ATOM, k0, g);
+  }
+}
+
+template <bool MN, int SWZ, int BK_>
+__device__ __forceinline__ uint64_t operand_desc(uint32_t tile_addr, int kk) {
+  if constexpr (!MN) {
+    // K-major: 8-row groups are 8*SWZ bytes apart; one atom along K; step K by 32 bytes
+    return make_smem_desc(tile_addr + kk * (UMMA_K * 2), 0, 8 * SWZ, swizzle_code_for_bytes(SWZ));
+  } else {
+    // MN-major: SBO = 8 K-rows, LBO = next MN atom (BK rows further); step K by 16 rows
+    return make_smem_desc(tile_addr + kk * (UMMA_K * SWZ), BK_ * SWZ, 8 * SWZ,
+                          swizzle_code_for_bytes(SWZ));
+  }
+}
+
+template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES>
+__global__ void __launch_bounds__(256, 1)
+    tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
+                   const __grid_constant__ CUtensorMap map_b, const GemmArgs args) {
+  using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* acc_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int g = blockIdx.z / args.k_split;
+  const int split = blockIdx.z % args.k_split;
+
+  // iteration space: TPS == 1 -> (tap, k-block) pairs ; TPS > 1 -> k-blocks (all taps each)
+  const int iters_total = (TPS == 1) ? args.taps * args.inner : args.inner;
+  const int per = (iters_total + args.k_split - 1) / args.k_split;
+  const int it_lo = split * per;
+  const int it_hi = min(it_lo + per, iters_total);
+  const int n_iters = max(it_hi - it_lo, 0);
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&map_a);
+    prefetch_tmap(&map_b);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      for (int i = 0; i < n_iters; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; break; }
+        uint8_t* stage = smem + s * C::STAGE;
+        mbar_expect_tx(&full_bar[s], C::STAGE);
+        const int it = it_lo + i;
+        if constexpr (TPS == 1) {
+          const int t = it / args.inner, c = it % args.inner;
+          const Tap tp = args.tap[t];
+          load_operand<A_MN, A_SWZ, BK, BM>(stage, &map_a, &full_bar[s], tp.a_k + c * BK,
+                                            m0 + tp.a_mn, g);
+          load_operand<B_MN, B_SWZ, BK, BN>(stage + C::A_TILE, &map_b, &full_bar[s],
+                                            tp.b_k + c * BK, n0 + tp.b_mn, g);
+        } else {
+          const Tap t0 = args.tap[0];
+          load_operand<A_MN, A_SWZ, BK, BM>(stage, &map_a, &full_bar[s], t0.a_k + it * BK,
+                                            m0 + t0.a_mn, g);
+          for (int t = 0; t < TPS; ++t) {
+            const Tap tp = args.tap[t];
+            load_operand<B_MN, B_SWZ, BK, BN>(stage + C::A_TILE + t * C::B_TILE, &map_b,
+                                              &full_bar[s], tp.b_k + it * BK, n0 + tp.b_mn, g);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1u : 0u, B_MN ? 1u : 0u);
+      bool ok = true;
+      for (int i = 0; i < n_iters && ok; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * C::STAGE);
+#pragma unroll
+        for (int t = 0; t < TPS; ++t) {
+          const uint32_t b_addr = a_addr + C::A_TILE + t * C::B_TILE;
+#pragma unroll
+          for (int kk = 0; kk < BK / UMMA_K; ++kk) {
+            const uint64_t da = operand_desc<A_MN, A_SWZ, BK>(a_addr, kk);
+            const uint64_t db = operand_desc<B_MN, B_SWZ, BK>(b_addr, kk);
+            umma_f16(tmem_base + t * BN, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty_bar[s]);  // frees the smem slot when these MMAs retire
+      }
+      umma_commit(acc_bar);          // accumulators complete
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int sub = warp - 4;                 // TMEM sub-partition == warp % 4
+    const int m = m0 + sub * 32 + lane;       // this thread's output row
+    bool ok = true;
+    if (n_iters > 0) ok = mbar_wait(acc_bar, 0);
+    if (!ok && lane == 0) *args.status = 1;
+    tc_fence_after();
+    const bool row_ok = ok && n_iters > 0 && m < args.m_valid;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
+#pragma unroll 1
+    for (int t = 0; t < TPS; ++t) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(lane_addr + t * BN + c0, r);   // warp-collective: all lanes execute
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        const long long row_off = static_cast<long long>(g) * args.out_gs +
+                                  static_cast<long long>(m) * args.out_ms +
+                                  static_cast<long long>(t) * args.out_ts;
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          v[j] = __uint_as_float(r[j]);
+          if (args.bias && split == 0)
+            v[j] += args.bias[static_cast<long long>(g) * args.bias_gs +
+                              (args.bias_on_m ? m : (n0 + c0 + j))];
+          if (args.relu) v[j] = fmaxf(v[j], 0.f);
+        }
+        const long long idx0 = row_off + static_cast<long long>(n0 + c0) * args.out_ns;
+        if (args.vec_store && n0 + c0 + 16 <= args.n_valid) {
+          // n is the contiguous output dimension and everything is 16-byte aligned
+          if (args.mask_src) {
+            const uint4 mk0 = *reinterpret_cast<const uint4*>(args.mask_src + idx0);
+            const uint4 mk1 = *reinterpret_cast<const uint4*>(args.mask_src + idx0 + 8);
+            float mf[16];
+            unpack<__nv_bfloat16>(mk0, mf);
+            unpack<__nv_bfloat16>(mk1, mf + 8);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (!(mf[j] > 0.f)) v[j] = 0.f;
+          }
+          if (args.out_bf16) {
+            __nv_bfloat16* o = static_cast<__nv_bfloat16*>(args.out) + idx0;
+            st_vec(o, pack<__nv_bfloat16>(v));
+            st_vec(o + 8, pack<__nv_bfloat16>(v + 8));
+          } else {
+            float* o = static_cast<float*>(args.out) + idx0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<float4*>(o + 4 * q) =
+                  make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          }
+          continue;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int n = n0 + c0 + j;
+          if (n >= args.n_valid) break;
+          const long long idx = idx0 + static_cast<long long>(j) * args.out_ns;
+          float o = v[j];
+          if (args.mask_src && !(__bfloat162float(args.mask_src[idx]) > 0.f)) o = 0.f;
+          if (args.atomic) {
+            atomicAdd(static_cast<float*>(args.out) + idx, o);
+          } else if (args.out_bf16) {
+            static_cast<__nv_bfloat16*>(args.out)[idx] = __float2bfloat16_rn(o);
+          } else {
+            static_cast<float*>(args.out)[idx] = o;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+}  // namespace tc
+}  // namespace nfb
+
+// =====================================================================================
+// Host side: tensor-map cache, variant table, C entry point
+// =====================================================================================
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace nfb {
+namespace tc {
+
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                              const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                              const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeFn encode_fn() {
+  static EncodeFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeFn>(p);
+  });
+  return fn;
+}
+
+struct Operand {  // mirrors nfb_tc_operand
+  const void* ptr;
+  long long inner, rows, groups, row_stride, group_stride;  // elements (bf16)
+};
+
+using MapKey = std::tuple<const void*, long long, long long, long long, long long, long long,
+                          int, int, int>;
+static std::map<MapKey, CUtensorMap> g_maps;
+static std::mutex g_maps_mu;
+
+static int get_map(const Operand& op, int box_inner, int box_rows, int swz_bytes,
+                   CUtensorMap* out) {
+  MapKey key{op.ptr, op.inner, op.rows, op.groups, op.row_stride, op.group_stride,
+             box_inner, box_rows, swz_bytes};
+  std::lock_guard<std::mutex> lock(g_maps_mu);
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) { *out = it->second; return 0; }
+  EncodeFn enc = encode_fn();
+  if (!enc) return fail(NFB_ESTATE, "tc_gemm: cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(op.inner), static_cast<cuuint64_t>(op.rows),
+                        static_cast<cuuint64_t>(op.groups)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(op.row_stride) * 2,
+                           static_cast<cuuint64_t>(op.group_stride) * 2};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_rows), 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  if (op.groups == 1) strides[1] = static_cast<cuuint64_t>(op.rows) * strides[0];
+  if ((strides[0] & 15) || (strides[1] & 15) || (reinterpret_cast<uintptr_t>(op.ptr) & 15))
+    return fail(NFB_EINVAL, "tc_gemm: operand base/strides must be 16-byte aligned");
+  const CUtensorMapSwizzle sw = swz_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                : swz_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                  : CU_TENSOR_MAP_SWIZZLE_32B;
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(op.ptr), dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(NFB_EINVAL, "tc_gemm: cuTensorMapEncodeTiled failed (%d)",
+                                     static_cast<int>(r));
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[key] = m;
+  *out = m;
+  return 0;
+}
+
+template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES>
+static int launch(const Operand& a, const Operand& b, int m_tiles, int n_tiles, int groups,
+                  const GemmArgs& args, cudaStream_t st) {
+  using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
+  CUtensorMap ma, mb;
+  int rc = A_MN ? get_map(a, C::A_ATOM, BK, A_SWZ, &ma) : get_map(a, BK, BM, A_SWZ, &ma);
+  if (rc) return rc;
+  rc = B_MN ? get_map(b, C::B_ATOM, BK, B_SWZ, &mb) : get_map(b, BK, BN, B_SWZ, &mb);
+  if (rc) return rc;
+  auto kern = tc_gemm_kernel<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(C::SMEM));
+    if (e != cudaSuccess) return fail(static_cast<int>(e), "tc_gemm: smem attribute: %s",
+                                      cudaGetErrorString(e));
+    attr_set = true;
+  }
+  dim3 grid(m_tiles, n_tiles, groups * args.k_split);
+  kern<<<grid, 256, C::SMEM, st>>>(ma, mb, args);
+  return launch_status("tc_gemm");
+}
+
+}  // namespace tc
+}  // namespace nfb
+
+extern "C" {
+
+typedef struct {
+  const void* ptr;
+  long long inner, rows, groups, row_stride, group_stride;
+} nfb_tc_operand;
+
+typedef struct {
+  void* out;
+  int out_bf16, atomic;
+  long long out_gs, out_ms, out_ns, out_ts;
+  const float* bias;
+  long long bias_gs;
+  int bias_on_m, relu;
+  const void* mask_src;
+  int m_valid, n_valid;
+} nfb_tc_epilogue;
+
+// variant: 0 conv_fwd, 1 conv_dgrad, 2 conv_wgrad, 3 fc_fwd, 4 fc_dgrad, 5 fc_wgrad
+int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, int m_tiles,
+                int n_tiles, int groups, int taps, int inner, int k_split, const int* tap_table,
+                const nfb_tc_epilogue* epi, int* status, void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(A && B && epi && status && epi->out, NFB_EINVAL, "tc_gemm: null pointer");
+  NFB_REQUIRE(taps >= 1 && taps <= kMaxTaps && inner >= 1 && k_split >= 1, NFB_EINVAL,
+              "tc_gemm: bad taps/inner/k_split");
+  NFB_REQUIRE(m_tiles >= 1 && n_tiles >= 1 && groups >= 1 &&
+                  static_cast<long long>(groups) * k_split <= 65535, NFB_ERANGE,
+              "tc_gemm: bad grid");
+  NFB_REQUIRE(k_split == 1 || epi->atomic, NFB_EINVAL, "tc_gemm: split-K needs atomic epilogue");
+  GemmArgs g{};
+  g.taps = taps; g.inner = inner; g.k_split = k_split;
+  for (int t = 0; t < taps; ++t) {
+    if (tap_table) g.tap[t] = Tap{tap_table[4 * t], tap_table[4 * t + 1], tap_table[4 * t + 2],
+                                  tap_table[4 * t + 3]};
+    else g.tap[t] = Tap{0, 0, 0, 0};
+  }
+  g.out = epi->out; g.out_bf16 = epi->out_bf16; g.atomic = epi->atomic;
+  g.out_gs = epi->out_gs; g.out_ms = epi->out_ms; g.out_ns = epi->out_ns; g.out_ts = epi->out_ts;
+  g.bias = epi->bias; g.bias_gs = epi->bias_gs; g.bias_on_m = epi->bias_on_m;
+  g.relu = epi->relu;
+  g.mask_src = static_cast<const __nv_bfloat16*>(epi->mask_src);
+  g.m_valid = epi->m_valid; g.n_valid = epi->n_valid;
+  g.status = status;
+  const int esz = epi->out_bf16 ? 2 : 4;
+  g.vec_store = (!epi->atomic && epi->out_ns == 1 &&
+                 (reinterpret_cast<uintptr_t>(epi->out) & 15) == 0 &&
+                 ((epi->out_gs * esz) & 15) == 0 && ((epi->out_ms * esz) & 15) == 0 &&
+                 ((epi->out_ts * esz) & 15) == 0 &&
+                 (!epi->mask_src || (reinterpret_cast<uintptr_t>(epi->mask_src) & 15) == 0))
+                    ? 1 : 0;
+  Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
+  Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};
+  cudaStream_t st = as_stream(stream);
+  switch (variant) {
+    case 0: return launch<false, 64, false, 64, 32, 64, 1, 6>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 1: return launch<false, 128, true, 64, 64, 32, 1, 4>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 2:
+      NFB_REQUIRE(taps == 9, NFB_EINVAL, "tc_gemm: conv_wgrad needs 9 taps");
+      return launch<true, 128, true, 64, 64, 32, 9, 4>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 3: return launch<false, 128, false, 128, 64, 64, 1, 6>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 4: return launch<true, 128, false, 128, 64, 64, 1, 4>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 5: return launch<true, 128, true, 128, 64, 128, 1, 4>(a, b, m_tiles, n_tiles, groups, g, st);
+    default: return fail(NFB_EINVAL, "tc_gemm: unknown variant %d", variant);
+  }
+}
+
+}  // extern "C"

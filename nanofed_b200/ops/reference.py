@@ -86,7 +86,8 @@ def agg_coefficients(
     coef = w
     if clip_norm > 0 and sumsq is not None:
         c = (clip_norm / (sumsq.to(torch.float32).sqrt() + _CLIP_EPS)).clamp(max=1.0)
-        coef = w * c
+        # an absent client (w == 0) may carry NaN statistics; it must not poison the sum
+        coef = torch.where(w > 0, w * torch.nan_to_num(c, nan=1.0), torch.zeros_like(w))
     return coef, (w * w).sum()
 
 

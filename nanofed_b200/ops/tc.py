@@ -1,0 +1,189 @@
+"""Python face of the tcgen05 grouped GEMM / implicit-conv kernel (``csrc/tc_gemm.cu``).
+
+All functions take *views into the arena* (bf16 activations/weights with the client
+as leading dimension) and launch ONE kernel for all clients.  The image grid
+convention for the conv ops: an activation is stored NHWC, row-flattened, as
+``[C, R, ch]`` with ``R = B·H·W`` rows per client (``W`` = grid width, 26 for the
+MNIST CNN); a 3×3 tap ``(kh, kw)`` is the row shift ``s = kh·W + kw``; outputs are
+produced on the same grid (positions whose window leaves the image hold
+don't-care values that consumers never read / are kept zero in gradients).
+
+Replaces (reference): ``nn.Conv2d`` / ``nn.Linear`` forward and autograd backward
+of ``nanofed/models/mnist.py:9-14,17-27`` as executed by ``trainer/base.py:145-150``.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import native
+
+CONV_FWD, CONV_DGRAD, CONV_WGRAD, FC_FWD, FC_DGRAD, FC_WGRAD = range(6)
+_BM = 128
+_BN = {CONV_FWD: 64, CONV_DGRAD: 32, CONV_WGRAD: 32, FC_FWD: 64, FC_DGRAD: 64, FC_WGRAD: 128}
+_BK = {CONV_FWD: 32, CONV_DGRAD: 64, CONV_WGRAD: 64, FC_FWD: 64, FC_DGRAD: 64, FC_WGRAD: 64}
+
+
+class _Operand(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("inner", C.c_longlong), ("rows", C.c_longlong),
+                ("groups", C.c_longlong), ("row_stride", C.c_longlong),
+                ("group_stride", C.c_longlong)]
+
+
+class _Epilogue(C.Structure):
+    _fields_ = [("out", C.c_void_p), ("out_bf16", C.c_int), ("atomic", C.c_int),
+                ("out_gs", C.c_longlong), ("out_ms", C.c_longlong), ("out_ns", C.c_longlong),
+                ("out_ts", C.c_longlong), ("bias", C.c_void_p), ("bias_gs", C.c_longlong),
+                ("bias_on_m", C.c_int), ("relu", C.c_int), ("mask_src", C.c_void_p),
+                ("m_valid", C.c_int), ("n_valid", C.c_int)]
+
+
+_declared = False
+_status: dict[int, torch.Tensor] = {}
+
+
+def _lib() -> C.CDLL:
+    global _declared
+    lib = native.lib()
+    if not _declared:
+        lib.nfb_tc_gemm.restype = C.c_int
+        lib.nfb_tc_gemm.argtypes = [C.c_int, C.POINTER(_Operand), C.POINTER(_Operand), C.c_int,
+                                    C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.POINTER(C.c_int), C.POINTER(_Epilogue), C.c_void_p,
+                                    C.c_void_p]
+        _declared = True
+    return lib
+
+
+def status_word(device: torch.device) -> torch.Tensor:
+    """Per-device int32 that the kernels set to 1 if a pipeline wait times out."""
+    idx = device.index or 0
+    if idx not in _status:
+        _status[idx] = torch.zeros(1, dtype=torch.int32, device=device)
+    return _status[idx]
+
+
+def check_status(device: torch.device) -> None:
+    if int(status_word(device).item()) != 0:
+        raise RuntimeError("tc_gemm: a TMA/MMA pipeline wait timed out (status word set)")
+
+
+def _operand(t: torch.Tensor) -> _Operand:
+    """``t``: bf16 ``[G, rows, inner]`` view with unit inner stride."""
+    assert t.dtype == torch.bfloat16 and t.dim() == 3 and t.stride(2) == 1, (t.dtype, t.shape)
+    return _Operand(t.data_ptr(), t.shape[2], t.shape[1], t.shape[0], t.stride(1), t.stride(0))
+
+
+def gemm(
+    variant: int,
+    a: torch.Tensor,
+    b: torch.Tensor,
+    out: torch.Tensor,
+    *,
+    m: int,
+    n: int,
+    strides: tuple[int, int, int, int],      # element strides of out: (group, m, n, tap)
+    taps: list[tuple[int, int, int, int]] | None = None,
+    inner: int,
+    k_split: int = 1,
+    atomic: bool = False,
+    bias: torch.Tensor | None = None,
+    bias_gs: int = 0,
+    bias_on_m: bool = False,
+    relu: bool = False,
+    mask_src: torch.Tensor | None = None,
+) -> None:
+    lib = _lib()
+    groups = a.shape[0]
+    oa, ob = _operand(a), _operand(b)
+    taps = taps or [(0, 0, 0, 0)]
+    table = (C.c_int * (4 * len(taps)))(*[v for tap in taps for v in tap])
+    assert out.dtype in (torch.float32, torch.bfloat16)
+    if atomic:
+        assert out.dtype == torch.float32
+    epi = _Epilogue(out.data_ptr(), 1 if out.dtype == torch.bfloat16 else 0, 1 if atomic else 0,
+                    strides[0], strides[1], strides[2], strides[3],
+                    bias.data_ptr() if bias is not None else None, bias_gs,
+                    1 if bias_on_m else 0, 1 if relu else 0,
+                    mask_src.data_ptr() if mask_src is not None else None, m, n)
+    m_tiles = (m + _BM - 1) // _BM
+    n_tiles = (n + _BN[variant] - 1) // _BN[variant]
+    st = status_word(a.device)
+    code = lib.nfb_tc_gemm(variant, C.byref(oa), C.byref(ob), m_tiles, n_tiles, groups,
+                           len(taps), inner, k_split, table, C.byref(epi), st.data_ptr(),
+                           torch.cuda.current_stream(a.device).cuda_stream)
+    native._check(code, f"tc_gemm(variant={variant})")
+    native._count()
+
+
+def _shifts(width: int) -> list[int]:
+    return [kh * width + kw for kh in range(3) for kw in range(3)]
+
+
+# ---- 3x3 convolution on the flattened grid -------------------------------------------
+def conv3x3_fwd(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, out: torch.Tensor,
+                width: int, relu: bool = True) -> None:
+    """``out[c, q, co] = act(Σ_t Σ_ci x[c, q + s_t, ci]·w[c, co, t·Cin + ci] + bias[c, co])``.
+
+    x ``[C, R, 32]``, w ``[C, 64, 288]`` (tap-major, channel-minor), out ``[C, R, 64]`` bf16.
+    """
+    cin = x.shape[2]
+    assert cin == 32 and w.shape[1] == 64 and w.shape[2] == 9 * cin
+    taps = [(0, s, t * cin, 0) for t, s in enumerate(_shifts(width))]
+    gemm(CONV_FWD, x, w, out, m=x.shape[1], n=64,
+         strides=(out.stride(0), out.stride(1), 1, 0), taps=taps, inner=1,
+         bias=bias, bias_gs=bias.stride(0) if bias is not None else 0, relu=relu)
+
+
+def conv3x3_dgrad(dy: torch.Tensor, w: torch.Tensor, out: torch.Tensor, width: int,
+                  relu_mask: torch.Tensor | None = None) -> None:
+    """``out[c, q, ci] = Σ_t Σ_co dy[c, q − s_t, co]·w[c, co, t·Cin + ci]`` (× ``relu_mask > 0``).
+
+    dy ``[C, R, 64]`` (zero outside the valid output window), out ``[C, R, 32]`` bf16.
+    """
+    cin = out.shape[2]
+    assert dy.shape[2] == 64 and cin == 32
+    taps = [(0, -s, 0, t * cin) for t, s in enumerate(_shifts(width))]
+    gemm(CONV_DGRAD, dy, w, out, m=dy.shape[1], n=cin,
+         strides=(out.stride(0), out.stride(1), 1, 0), taps=taps, inner=1, mask_src=relu_mask)
+
+
+def conv3x3_wgrad(dy: torch.Tensor, x: torch.Tensor, grad: torch.Tensor, width: int,
+                  grad_group_stride: int, k_split: int = 8) -> None:
+    """``grad[c, co, ci, t] += Σ_q dy[c, q, co]·x[c, q + s_t, ci]`` (PyTorch OIHW layout, fp32).
+
+    ``grad`` points at the first client's conv weight gradient inside the flat gradient
+    slab; ``grad_group_stride`` is the slab's row length.
+    """
+    rows = dy.shape[1]
+    cin = x.shape[2]
+    taps = [(0, 0, s, 0) for s in _shifts(width)]
+    inner = (rows + 63) // 64
+    gemm(CONV_WGRAD, dy, x, grad, m=64, n=cin,
+         strides=(grad_group_stride, cin * 9, 9, 1), taps=taps, inner=inner,
+         k_split=min(k_split, inner), atomic=True)
+
+
+# ---- linear layers ---------------------------------------------------------------------
+def linear_fwd(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, k_split: int = 8) -> None:
+    """``out[c, b, j] += Σ_i x[c, b, i]·w[c, j, i]`` (fp32 atomics; zero ``out`` first)."""
+    j, i = w.shape[1], w.shape[2]
+    gemm(FC_FWD, w, x, out, m=j, n=x.shape[1], strides=(out.stride(0), 1, out.stride(1), 0),
+         inner=i // 64, k_split=k_split, atomic=True)
+
+
+def linear_dgrad(w: torch.Tensor, dy: torch.Tensor, out: torch.Tensor) -> None:
+    """``out[c, b, i] = Σ_j dy[c, b, j]·w[c, j, i]`` (bf16)."""
+    j, i = w.shape[1], w.shape[2]
+    gemm(FC_DGRAD, w, dy, out, m=i, n=dy.shape[1], strides=(out.stride(0), 1, out.stride(1), 0),
+         inner=j // 64)
+
+
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, grad: torch.Tensor,
+                 grad_group_stride: int) -> None:
+    """``grad[c, j, i] = Σ_b dy[c, b, j]·x[c, b, i]`` (fp32 store into the gradient slab)."""
+    j, i = dy.shape[2], x.shape[2]
+    gemm(FC_WGRAD, dy, x, grad, m=j, n=i, strides=(grad_group_stride, i, 1, 0),
+         inner=(dy.shape[1] + 63) // 64)

@@ -1,0 +1,152 @@
+"""Numerics check of every tcgen05 GEMM/conv variant against plain PyTorch fp32.
+
+    python tools/tc_check.py            # each variant in its own subprocess (60 s timeout)
+    python tools/tc_check.py conv_fwd   # one variant in-process
+
+Used while bringing the kernels up (a bad descriptor can fault the context, so variants
+are isolated); ``tests/test_tc_gpu.py`` runs the same functions under pytest.
+"""
+import subprocess
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+W = 26  # grid width
+
+
+def _bf(*shape, scale=1.0):
+    return (torch.randn(*shape, device="cuda") * scale).bfloat16()
+
+
+def _shift_rows(x, s):
+    """y[:, q] = x[:, q + s] with zero fill outside (per client)."""
+    c, r, ch = x.shape
+    y = torch.zeros_like(x)
+    if s >= 0:
+        y[:, : r - s] = x[:, s:]
+    else:
+        y[:, -s:] = x[:, : r + s]
+    return y
+
+
+def check_conv_fwd():
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 3, 2, 32, 64
+    r = b * W * W
+    x, w = _bf(c, r, cin), _bf(c, cout, 9 * cin, scale=0.05)
+    bias = torch.randn(c, cout, device="cuda")
+    out = torch.zeros(c, r, cout, device="cuda", dtype=torch.bfloat16)
+    tc.conv3x3_fwd(x, w, bias, out, W, relu=True)
+    ref = torch.zeros(c, r, cout, device="cuda")
+    for t, s in enumerate(tc._shifts(W)):
+        ref += torch.einsum("crk,cok->cro", _shift_rows(x, s).float(),
+                            w[:, :, t * cin:(t + 1) * cin].float())
+    ref = (ref + bias[:, None, :]).relu()
+    return out.float(), ref
+
+
+def check_conv_dgrad():
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 2, 2, 32, 64
+    r = b * W * W
+    dy, w = _bf(c, r, cout), _bf(c, cout, 9 * cin, scale=0.05)
+    a1 = _bf(c, r, cin)
+    out = torch.zeros(c, r, cin, device="cuda", dtype=torch.bfloat16)
+    tc.conv3x3_dgrad(dy, w, out, W, relu_mask=a1)
+    ref = torch.zeros(c, r, cin, device="cuda")
+    for t, s in enumerate(tc._shifts(W)):
+        ref += torch.einsum("cro,cok->crk", _shift_rows(dy, -s).float(),
+                            w[:, :, t * cin:(t + 1) * cin].float())
+    ref = ref * (a1.float() > 0)
+    return out.float(), ref
+
+
+def check_conv_wgrad():
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 2, 3, 32, 64
+    r = b * W * W
+    dy, x = _bf(c, r, cout, scale=0.1), _bf(c, r, cin)
+    n_total = 64 * 32 * 9 + 128
+    grad = torch.zeros(c, n_total, device="cuda")
+    tc.conv3x3_wgrad(dy, x, grad[:, 64:], W, n_total, k_split=4)
+    got = grad[:, 64:64 + 64 * 32 * 9].reshape(c, cout, cin, 9)
+    ref = torch.stack([torch.einsum("cro,crk->cok", dy.float(), _shift_rows(x, s).float())
+                       for s in tc._shifts(W)], dim=-1)
+    return got, ref
+
+
+def check_fc_fwd():
+    from nanofed_b200.ops import tc
+    c, b, j, i = 3, 64, 128, 9216
+    w, x = _bf(c, j, i, scale=0.02), _bf(c, b, i)
+    out = torch.zeros(c, b, j, device="cuda")
+    tc.linear_fwd(w, x, out, k_split=8)
+    return out, torch.einsum("cbi,cji->cbj", x.float(), w.float())
+
+
+def check_fc_dgrad():
+    from nanofed_b200.ops import tc
+    c, b, j, i = 2, 64, 128, 9216
+    w, dy = _bf(c, j, i, scale=0.02), _bf(c, b, j)
+    out = torch.zeros(c, b, i, device="cuda", dtype=torch.bfloat16)
+    tc.linear_dgrad(w, dy, out)
+    return out.float(), torch.einsum("cbj,cji->cbi", dy.float(), w.float())
+
+
+def check_fc_wgrad():
+    from nanofed_b200.ops import tc
+    c, b, j, i = 2, 64, 128, 9216
+    dy, x = _bf(c, b, j, scale=0.1), _bf(c, b, i)
+    n_total = j * i + 256
+    grad = torch.zeros(c, n_total, device="cuda")
+    tc.linear_wgrad(dy, x, grad[:, 128:], n_total)
+    got = grad[:, 128:128 + j * i].reshape(c, j, i)
+    return got, torch.einsum("cbj,cbi->cji", dy.float(), x.float())
+
+
+CHECKS = {"conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
+          "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad,
+          "fc_wgrad": check_fc_wgrad}
+
+
+def run_one(name: str) -> bool:
+    from nanofed_b200.ops import tc
+    torch.manual_seed(0)
+    got, ref = CHECKS[name]()
+    torch.cuda.synchronize()
+    tc.check_status(got.device)
+    err = (got - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    rel = err / max(scale, 1e-6)
+    bad = int(((got - ref).abs() > 0.02 * scale + 0.02).sum())
+    ok = rel < 0.02 and bad == 0 and torch.isfinite(got).all().item()
+    print(f"{name:12s} max_abs_err={err:.4e} ref_max={scale:.3e} rel={rel:.3e} "
+          f"mismatches={bad}/{got.numel()} {'OK' if ok else 'FAIL'}", flush=True)
+    if not ok:
+        d = (got - ref).abs()
+        idx = torch.nonzero(d > 0.02 * scale + 0.02)[:5].tolist()
+        for ix in idx:
+            print("   at", ix, "got", got[tuple(ix)].item(), "want", ref[tuple(ix)].item())
+    return ok
+
+
+if __name__ == "__main__":
+    if len(sys.argv) > 1:
+        sys.exit(0 if run_one(sys.argv[1]) else 1)
+    failed = []
+    for name in CHECKS:
+        try:
+            p = subprocess.run([sys.executable, __file__, name], timeout=90, capture_output=True,
+                               text=True)
+            print(p.stdout.strip() or f"{name}: no output")
+            if p.returncode != 0:
+                failed.append(name)
+                print(p.stderr.strip()[-800:])
+        except subprocess.TimeoutExpired:
+            failed.append(name)
+            print(f"{name}: TIMEOUT")
+    print("FAILED:", failed if failed else "none")
+    sys.exit(1 if failed else 0)
