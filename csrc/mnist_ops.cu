@@ -1,0 +1,418 @@
+// K-ELT / K-XENT for the flagship MNIST-CNN cohort step: every non-GEMM op of
+// nanofed/models/mnist.py:16-28 and its backward, written for C clients at once.
+//
+// Layout conventions (shared with ops/tc.py and models/mnist_cohort.py):
+//   x     [C, B, 28, 28]        fp32 input images
+//   a1    [C, B*676, 32]  bf16  conv1+ReLU output, NHWC on a 26x26 grid (row = b*676+oh*26+ow)
+//   a2    [C, B*676, 64]  bf16  conv2+bias+ReLU on the SAME grid (valid for oh,ow < 24)
+//   p     [C, B, 9216]    bf16  maxpool+dropout output in PyTorch flatten order ch*144+ph*12+pw
+//   pidx  [C, B, 144, 64] u8    bits 0-1 argmax in the 2x2 window, bit 2 max>0, bit 3 dropout keep
+//   hpre  [C, B, 128]     fp32  fc1 pre-activation (without bias)
+//   dh    [C, B, 128]     bf16  gradient w.r.t. hpre
+//   dp    [C, B, 9216]    bf16  gradient w.r.t. p
+//   da2   [C, B*676, 64]  bf16  gradient w.r.t. conv2 pre-activation, ZERO outside oh,ow < 24
+//   da1   [C, B*676, 32]  bf16  gradient w.r.t. conv1 pre-activation (ReLU mask applied)
+// Weights/gradients are addressed inside the flat arena rows through element offsets.
+#include "common.cuh"
+#include "philox.cuh"
+
+namespace nfb {
+
+constexpr int kG = 26;          // grid width/height after conv1
+constexpr int kGrid = kG * kG;  // 676 positions per image
+constexpr int kPool = 12;
+
+// -------------------------------------------------------------------------------------
+// conv2 weight permutation: arena fp32 [co][ci][t] -> bf16 [co][t*32+ci]
+// -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    prep_conv2_weight_kernel(const float* __restrict__ slots, int64_t row_stride, int64_t w_off,
+                             __nv_bfloat16* __restrict__ w2p) {
+  const int c = blockIdx.y;
+  const float* w = slots + c * row_stride + w_off;
+  __nv_bfloat16* o = w2p + static_cast<int64_t>(c) * 64 * 288;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 64 * 288; i += gridDim.x * blockDim.x) {
+    const int co = i / 288, rem = i % 288, t = rem / 32, ci = rem % 32;
+    o[i] = __float2bfloat16_rn(w[co * 288 + ci * 9 + t]);
+  }
+}
+
+// -------------------------------------------------------------------------------------
+// conv1 (1 -> 32, 3x3) + bias + ReLU, direct on CUDA cores (K = 9 is too thin for UMMA)
+// one thread = one grid position x 8 output channels; one block = 256 threads
+// -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    conv1_fwd_kernel(const float* __restrict__ x, int64_t x_cstride,
+                     const float* __restrict__ slots, int64_t row_stride, int64_t w_off,
+                     int64_t b_off, int B, __nv_bfloat16* __restrict__ a1) {
+  __shared__ float sw[32 * 9];
+  __shared__ float sb[32];
+  const int c = blockIdx.y;
+  const float* w = slots + c * row_stride + w_off;
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
+  if (threadIdx.x < 32) sb[threadIdx.x] = slots[c * row_stride + b_off + threadIdx.x];
+  __syncthreads();
+  const int64_t items = static_cast<int64_t>(B) * kGrid * 4;  // (position, channel-octet)
+  const float* xc = x + static_cast<int64_t>(c) * x_cstride;
+  __nv_bfloat16* oc = a1 + static_cast<int64_t>(c) * B * kGrid * 32;
+  for (int64_t it = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; it < items;
+       it += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int oct = static_cast<int>(it & 3);
+    const int64_t pos = it >> 2;
+    const int b = static_cast<int>(pos / kGrid), q = static_cast<int>(pos % kGrid);
+    const int oh = q / kG, ow = q % kG;
+    const float* px = xc + b * 784 + oh * 28 + ow;
+    float in[9];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) in[kh * 3 + kw] = px[kh * 28 + kw];
+    float out[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int co = oct * 8 + j;
+      float acc = sb[co];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) acc = fmaf(in[t], sw[co * 9 + t], acc);
+      out[j] = fmaxf(acc, 0.f);
+    }
+    st_vec(oc + pos * 32 + oct * 8, pack<__nv_bfloat16>(out));
+  }
+}
+
+// -------------------------------------------------------------------------------------
+// 2x2 max-pool + dropout(p1) forward; one block per image, staged through shared memory so
+// that both the NHWC read and the PyTorch-order (ch*144 + pos) write are coalesced
+// -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    pool_fwd_kernel(const __nv_bfloat16* __restrict__ a2, int B, float drop_p,
+                    const unsigned long long* __restrict__ rng_state, uint64_t seed,
+                    __nv_bfloat16* __restrict__ p, uint8_t* __restrict__ pidx) {
+  __shared__ __nv_bfloat16 sp[144 * 66];  // [pos][ch], row padded to 66 to avoid bank conflicts
+  const int b = blockIdx.x, c = blockIdx.y;
+  const int64_t img = static_cast<int64_t>(c) * B + b;
+  const __nv_bfloat16* src = a2 + img * kGrid * 64;
+  uint8_t* idx = pidx + img * 144 * 64;
+  const uint64_t step = rng_state ? *rng_state : 0ull;
+  const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  // item = (pooled position, channel octet): 144 * 8 items
+  for (int it = threadIdx.x; it < 144 * 8; it += blockDim.x) {
+    const int oct = it & 7, pos = it >> 3;
+    const int ph = pos / kPool, pw = pos % kPool;
+    const int q = (2 * ph) * kG + 2 * pw;
+    float v[4][8];
+    unpack<__nv_bfloat16>(ld_plain(src + (q)*64 + oct * 8), v[0]);
+    unpack<__nv_bfloat16>(ld_plain(src + (q + 1) * 64 + oct * 8), v[1]);
+    unpack<__nv_bfloat16>(ld_plain(src + (q + kG) * 64 + oct * 8), v[2]);
+    unpack<__nv_bfloat16>(ld_plain(src + (q + kG + 1) * 64 + oct * 8), v[3]);
+    // dropout keep bits: one Philox group (4 uniforms) per 4 channels
+    const uint64_t elem = (img * 144 + pos) * 64 + oct * 8;
+    float u[8];
+    if (drop_p > 0.f) {
+      const float4 u0 = Philox::uniform4((step << 34) + (elem >> 2), seed);
+      const float4 u1 = Philox::uniform4((step << 34) + (elem >> 2) + 1, seed);
+      u[0] = u0.x; u[1] = u0.y; u[2] = u0.z; u[3] = u0.w;
+      u[4] = u1.x; u[5] = u1.y; u[6] = u1.z; u[7] = u1.w;
+    }
+    uint8_t code[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float m = v[0][j];
+      int a = 0;
+#pragma unroll
+      for (int w = 1; w < 4; ++w)
+        if (v[w][j] > m) { m = v[w][j]; a = w; }
+      const bool keep = drop_p > 0.f ? (u[j] >= drop_p) : true;
+      code[j] = static_cast<uint8_t>(a | (m > 0.f ? 4 : 0) | (keep ? 8 : 0));
+      sp[pos * 66 + oct * 8 + j] = __float2bfloat16_rn(keep ? m * keep_scale : 0.f);
+    }
+    *reinterpret_cast<uint2*>(idx + pos * 64 + oct * 8) = *reinterpret_cast<const uint2*>(code);
+  }
+  __syncthreads();
+  // write out in PyTorch flatten order: out[ch*144 + pos]
+  __nv_bfloat16* dst = p + img * 9216;
+  for (int i = threadIdx.x; i < 9216; i += blockDim.x) {
+    const int ch = i / 144, pos = i % 144;
+    dst[i] = sp[pos * 66 + ch];
+  }
+}
+
+// -------------------------------------------------------------------------------------
+// backward of dropout + max-pool + ReLU: dp -> da2 on the 26-grid (zeros elsewhere),
+// plus conv2 bias gradient (column sums, atomics into the gradient slab)
+// -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    pool_bwd_kernel(const __nv_bfloat16* __restrict__ dp, const uint8_t* __restrict__ pidx, int B,
+                    float drop_p, __nv_bfloat16* __restrict__ da2, float* __restrict__ grads,
+                    int64_t row_stride, int64_t b2_off) {
+  __shared__ __nv_bfloat16 sd[144 * 66];  // [pos][ch] (padded rows) gradient w.r.t. pooled pre-dropout value
+  __shared__ float sbias[64];
+  const int b = blockIdx.x, c = blockIdx.y;
+  const int64_t img = static_cast<int64_t>(c) * B + b;
+  const __nv_bfloat16* src = dp + img * 9216;
+  const uint8_t* idx = pidx + img * 144 * 64;
+  const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  if (threadIdx.x < 64) sbias[threadIdx.x] = 0.f;
+  for (int i = threadIdx.x; i < 9216; i += blockDim.x) {
+    const int ch = i / 144, pos = i % 144;
+    sd[pos * 66 + ch] = src[i];
+  }
+  __syncthreads();
+  __nv_bfloat16* dst = da2 + img * kGrid * 64;
+  // item = (grid position, channel octet): 676 * 8 items, every position is written
+  for (int it = threadIdx.x; it < kGrid * 8; it += blockDim.x) {
+    const int oct = it & 7, q = it >> 3;
+    const int oh = q / kG, ow = q % kG;
+    float out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (oh < 24 && ow < 24) {
+      const int pos = (oh >> 1) * kPool + (ow >> 1);
+      const int me = (oh & 1) * 2 + (ow & 1);
+      const uint2 codes = *reinterpret_cast<const uint2*>(idx + pos * 64 + oct * 8);
+      const uint8_t* code = reinterpret_cast<const uint8_t*>(&codes);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint8_t cd = code[j];
+        if ((cd & 3) == me && (cd & 4) && (cd & 8))
+          out[j] = __bfloat162float(sd[pos * 66 + oct * 8 + j]) * keep_scale;
+      }
+    }
+    st_vec(dst + q * 64 + oct * 8, pack<__nv_bfloat16>(out));
+    // bias gradient: sum over positions (values are bf16-rounded exactly as conv wgrad sees them)
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (out[j] != 0.f) atomicAdd(&sbias[oct * 8 + j], __bfloat162float(__float2bfloat16_rn(out[j])));
+  }
+  __syncthreads();
+  if (threadIdx.x < 64 && sbias[threadIdx.x] != 0.f)
+    atomicAdd(grads + c * row_stride + b2_off + threadIdx.x, sbias[threadIdx.x]);
+}
+
+// -------------------------------------------------------------------------------------
+// The classifier head, one block per client:
+//   h = dropout(relu(hpre + b_fc1)) ; logits = h Wfc2^T + b_fc2 ; log-softmax / NLL / accuracy
+//   dlogits = (softmax - onehot)/B ; dWfc2, dbfc2 ; dh = (dlogits Wfc2) * relu'(.) * dropout ;
+//   dbfc1 = colsum(dh).   Accumulates (loss_sum, correct, B) into stats[c] — the device-side
+// counters that replace the reference's two .item() syncs per batch — and bumps the
+// per-step dropout counter.
+// -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    fc_head_kernel(const float* __restrict__ hpre, const int64_t* __restrict__ labels,
+                   int64_t label_stride, int B, const float* __restrict__ slots,
+                   float* __restrict__ grads, int64_t row_stride, int64_t b1_off, int64_t w2_off,
+                   int64_t b2_off, float drop_p, unsigned long long* __restrict__ rng_state,
+                   uint64_t seed, __nv_bfloat16* __restrict__ dh, float* __restrict__ stats) {
+  extern __shared__ float smem[];
+  float* h = smem;                 // [B][128]   (later reused for dh in fp32)
+  float* w2 = h + B * 128;         // [10][128]
+  float* lg = w2 + 1280;           // [B][10] logits -> dlogits
+  float* red = lg + B * 10;        // [64]
+  const int c = blockIdx.x;
+  const float* row = slots + c * row_stride;
+  float* grow = grads + c * row_stride;
+  const uint64_t step = rng_state ? *rng_state : 0ull;
+  const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+
+  for (int i = threadIdx.x; i < 1280; i += blockDim.x) w2[i] = row[w2_off + i];
+  const float* hp = hpre + static_cast<int64_t>(c) * B * 128;
+  for (int i = threadIdx.x; i < B * 128; i += blockDim.x) {
+    float v = hp[i] + row[b1_off + (i & 127)];
+    v = fmaxf(v, 0.f);
+    if (drop_p > 0.f) {
+      const uint64_t elem = static_cast<uint64_t>(c) * B * 128 + i;
+      const float4 u = Philox::uniform4((step << 34) + (1ull << 33) + (elem >> 2), seed);
+      const float uu = (elem & 3) == 0 ? u.x : (elem & 3) == 1 ? u.y : (elem & 3) == 2 ? u.z : u.w;
+      v = uu >= drop_p ? v * keep_scale : 0.f;
+    }
+    h[i] = v;
+  }
+  __syncthreads();
+  // logits
+  for (int i = threadIdx.x; i < B * 10; i += blockDim.x) {
+    const int b = i / 10, k = i % 10;
+    float acc = row[b2_off + k];
+    const float* hb = h + b * 128;
+    const float* wk = w2 + k * 128;
+#pragma unroll 8
+    for (int j = 0; j < 128; ++j) acc = fmaf(hb[j], wk[j], acc);
+    lg[i] = acc;
+  }
+  __syncthreads();
+  // softmax / loss / accuracy / dlogits : one thread per sample
+  float my_loss = 0.f, my_hit = 0.f;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float* l = lg + b * 10;
+    const int t = static_cast<int>(labels[c * label_stride + b]);
+    float mx = l[0];
+    int arg = 0;
+    for (int k = 1; k < 10; ++k)
+      if (l[k] > mx) { mx = l[k]; arg = k; }
+    float se = 0.f;
+    for (int k = 0; k < 10; ++k) se += __expf(l[k] - mx);
+    const float lse = mx + __logf(se);
+    my_loss += lse - l[t];
+    my_hit += (arg == t) ? 1.f : 0.f;
+    const float inv = 1.f / se, sc = 1.f / static_cast<float>(B);
+    for (int k = 0; k < 10; ++k) l[k] = (__expf(l[k] - mx) * inv - (k == t ? 1.f : 0.f)) * sc;
+  }
+  my_loss = block_sum(my_loss, red);
+  my_hit = block_sum(my_hit, red);
+  if (threadIdx.x == 0) {
+    stats[3 * c + 0] += my_loss;
+    stats[3 * c + 1] += my_hit;
+    stats[3 * c + 2] += static_cast<float>(B);
+  }
+  // fc2 gradients (plain stores: this block owns client c's rows)
+  for (int i = threadIdx.x; i < 1280; i += blockDim.x) {
+    const int k = i >> 7, j = i & 127;
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc = fmaf(lg[b * 10 + k], h[b * 128 + j], acc);
+    grow[w2_off + i] = acc;
+  }
+  if (threadIdx.x < 10) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += lg[b * 10 + threadIdx.x];
+    grow[b2_off + threadIdx.x] = acc;
+  }
+  __syncthreads();
+  // dh (gradient w.r.t. hpre), written in place over h
+  __nv_bfloat16* dhc = dh + static_cast<int64_t>(c) * B * 128;
+  for (int i = threadIdx.x; i < B * 128; i += blockDim.x) {
+    const int b = i >> 7, j = i & 127;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < 10; ++k) acc = fmaf(lg[b * 10 + k], w2[k * 128 + j], acc);
+    const float g = h[i] > 0.f ? acc * keep_scale : 0.f;  // relu' and dropout share h > 0
+    const __nv_bfloat16 gb = __float2bfloat16_rn(g);
+    dhc[i] = gb;
+    h[i] = __bfloat162float(gb);
+  }
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += h[b * 128 + threadIdx.x];
+    grow[b1_off + threadIdx.x] = acc;
+  }
+  if (c == 0 && threadIdx.x == 0 && rng_state) *rng_state = step + 1;
+}
+
+// -------------------------------------------------------------------------------------
+// conv1 weight/bias gradient, one block per image:
+//   dW1[co][t] += sum_q da1[q][co] * x[q + s_t] ;  db1[co] += sum_q da1[q][co]
+// -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ da1, const float* __restrict__ x,
+                       int64_t x_cstride, int B, float* __restrict__ grads, int64_t row_stride, int64_t w_off,
+                       int64_t b_off) {
+  __shared__ float sx[784];
+  __shared__ float part[8][32][10];
+  const int b = blockIdx.x, c = blockIdx.y;
+  const int64_t img = static_cast<int64_t>(c) * B + b;
+  for (int i = threadIdx.x; i < 784; i += blockDim.x) sx[i] = x[c * x_cstride + static_cast<int64_t>(b) * 784 + i];
+  __syncthreads();
+  const int co = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const __nv_bfloat16* d = da1 + img * kGrid * 32;
+  float acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int q = slice; q < kGrid; q += 8) {
+    const float g = __bfloat162float(d[q * 32 + co]);
+    const int oh = q / kG, ow = q % kG;
+    const float* px = sx + oh * 28 + ow;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) acc[kh * 3 + kw] = fmaf(g, px[kh * 28 + kw], acc[kh * 3 + kw]);
+    acc[9] += g;
+  }
+#pragma unroll
+  for (int t = 0; t < 10; ++t) part[slice][co][t] = acc[t];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 320; i += blockDim.x) {
+    const int cc = i / 10, t = i % 10;
+    float s = 0.f;
+#pragma unroll
+    for (int sl = 0; sl < 8; ++sl) s += part[sl][cc][t];
+    float* dst = grads + c * row_stride + (t < 9 ? w_off + cc * 9 + t : b_off + cc);
+    atomicAdd(dst, s);
+  }
+}
+
+}  // namespace nfb
+
+// =====================================================================================
+// C entry points
+// =====================================================================================
+extern "C" {
+
+int nfb_mnist_prep_conv2(const float* slots, int64_t row_stride, int64_t w_off, int C,
+                         void* w2p, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(slots && w2p && C >= 1, NFB_EINVAL, "mnist_prep_conv2: bad argument");
+  prep_conv2_weight_kernel<<<dim3(18, C), 256, 0, as_stream(stream)>>>(
+      slots, row_stride, w_off, static_cast<__nv_bfloat16*>(w2p));
+  return launch_status("mnist_prep_conv2");
+}
+
+int nfb_mnist_conv1_fwd(const float* x, int64_t x_cstride, const float* slots, int64_t row_stride,
+                        int64_t w_off, int64_t b_off, int C, int B, void* a1, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(x && slots && a1 && C >= 1 && B >= 1, NFB_EINVAL, "mnist_conv1_fwd: bad argument");
+  const int64_t items = static_cast<int64_t>(B) * kGrid * 4;
+  int bx = static_cast<int>((items + 255) / 256);
+  if (bx > 1024) bx = 1024;
+  conv1_fwd_kernel<<<dim3(bx, C), 256, 0, as_stream(stream)>>>(
+      x, x_cstride, slots, row_stride, w_off, b_off, B, static_cast<__nv_bfloat16*>(a1));
+  return launch_status("mnist_conv1_fwd");
+}
+
+int nfb_mnist_pool_fwd(const void* a2, int C, int B, float drop_p, const void* rng_state,
+                       uint64_t seed, void* p, uint8_t* pidx, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(a2 && p && pidx && C >= 1 && B >= 1, NFB_EINVAL, "mnist_pool_fwd: bad argument");
+  pool_fwd_kernel<<<dim3(B, C), 256, 0, as_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(a2), B, drop_p,
+      static_cast<const unsigned long long*>(rng_state), seed, static_cast<__nv_bfloat16*>(p),
+      pidx);
+  return launch_status("mnist_pool_fwd");
+}
+
+int nfb_mnist_pool_bwd(const void* dp, const uint8_t* pidx, int C, int B, float drop_p, void* da2,
+                       float* grads, int64_t row_stride, int64_t b2_off, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(dp && pidx && da2 && grads, NFB_EINVAL, "mnist_pool_bwd: null pointer");
+  pool_bwd_kernel<<<dim3(B, C), 256, 0, as_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dp), pidx, B, drop_p, static_cast<__nv_bfloat16*>(da2),
+      grads, row_stride, b2_off);
+  return launch_status("mnist_pool_bwd");
+}
+
+int nfb_mnist_fc_head(const float* hpre, const int64_t* labels, int64_t label_stride, int C,
+                      int B, const float* slots, float* grads, int64_t row_stride,
+                      int64_t b1_off, int64_t w2_off, int64_t b2_off, float drop_p,
+                      void* rng_state, uint64_t seed, void* dh, float* stats, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(hpre && labels && slots && grads && dh && stats, NFB_EINVAL,
+              "mnist_fc_head: null pointer");
+  NFB_REQUIRE(B >= 1 && B <= 256, NFB_ERANGE, "mnist_fc_head: batch %d outside [1, 256]", B);
+  const size_t smem = (static_cast<size_t>(B) * 128 + 1280 + static_cast<size_t>(B) * 10 + 64) *
+                      sizeof(float);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(fc_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    attr = true;
+  }
+  fc_head_kernel<<<C, 256, smem, as_stream(stream)>>>(
+      hpre, labels, label_stride, B, slots, grads, row_stride, b1_off, w2_off, b2_off, drop_p,
+      static_cast<unsigned long long*>(rng_state), seed, static_cast<__nv_bfloat16*>(dh), stats);
+  return launch_status("mnist_fc_head");
+}
+
+int nfb_mnist_conv1_wgrad(const void* da1, const float* x, int64_t x_cstride, int C, int B,
+                          float* grads,
+                          int64_t row_stride, int64_t w_off, int64_t b_off, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(da1 && x && grads, NFB_EINVAL, "mnist_conv1_wgrad: null pointer");
+  conv1_wgrad_kernel<<<dim3(B, C), 256, 0, as_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(da1), x, x_cstride, B, grads, row_stride, w_off, b_off);
+  return launch_status("mnist_conv1_wgrad");
+}
+
+}  // extern "C"

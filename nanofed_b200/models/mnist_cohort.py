@@ -1,0 +1,211 @@
+"""Flagship engine: the MNIST CNN for a whole cohort of clients, on hand-written kernels.
+
+Same math as ``MNISTModel`` (reference ``nanofed/models/mnist.py:6-28``) and the same
+training step as the reference's client loop (``trainer/base.py:134-160`` with
+``torch.optim.SGD``, ``examples/mnist/run_experiment.py:70-78``), but expressed
+for C clients at once — the client index is the *group* dimension of every launch,
+so a local step is 14 launches no matter how many clients share the GPU:
+
+    prep        conv2 weights fp32 [co][ci][3][3] → bf16 [co][tap·32+ci]            (K-ELT)
+    conv1       direct 3×3, 1→32, +bias +ReLU → NHWC bf16 on a 26×26 grid             (K-CONV, CUDA cores: K=9)
+    conv2       implicit GEMM, 9 shifted TMA tiles → tcgen05 → TMEM, +bias +ReLU      (K-CONV)
+    pool        2×2 max-pool + dropout(.25) → PyTorch flatten order, 1 B/elem argmax  (K-ELT)
+    fc1         grouped tcgen05 GEMM, split-K, fp32 accumulate                        (K-GEMM)
+    head        +bias ReLU dropout(.5) → fc2 → log-softmax/NLL/accuracy → dlogits
+                → fc2 grads → dh → fc1 bias grad; device-side loss/acc counters      (K-XENT)
+    fc1 wgrad   tcgen05 GEMM, both operands MN-major                                  (K-GEMM)
+    fc1 dgrad   tcgen05 GEMM, A MN-major                                              (K-GEMM)
+    pool bwd    scatter through argmax/ReLU/dropout → grid gradient + conv2 bias grad (K-ELT)
+    conv2 wgrad 9 TMEM accumulators sharing one A tile, fp32 atomics into OIHW        (K-CONV)
+    conv2 dgrad implicit GEMM with negative shifts, ReLU mask in the epilogue         (K-CONV)
+    conv1 wgrad direct reduction + bias grad                                          (K-CONV)
+    K-OPT       fused SGD over the whole [C·N] slab, bf16 working copy written back
+
+No autograd, no cuDNN/cuBLAS, no host sync; the local epoch is captured in a CUDA
+graph.  Activations are bf16, accumulation and master weights fp32.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Any
+
+import torch
+
+from nanofed_b200 import ops
+from nanofed_b200.ops import native, tc
+
+AVAILABLE = True
+_GRID = 26 * 26
+
+_declared = False
+
+
+def _lib() -> C.CDLL:
+    global _declared
+    lib = native.lib()
+    if not _declared:
+        vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64
+        sigs = {
+            "nfb_mnist_prep_conv2": [vp, i64, i64, i32, vp, vp],
+            "nfb_mnist_conv1_fwd": [vp, i64, vp, i64, i64, i64, i32, i32, vp, vp],
+            "nfb_mnist_pool_fwd": [vp, i32, i32, f32, vp, u64, vp, vp, vp],
+            "nfb_mnist_pool_bwd": [vp, vp, i32, i32, f32, vp, vp, i64, i64, vp],
+            "nfb_mnist_fc_head": [vp, vp, i64, i32, i32, vp, vp, i64, i64, i64, i64, f32, vp,
+                                  u64, vp, vp, vp],
+            "nfb_mnist_conv1_wgrad": [vp, vp, i64, i32, i32, vp, i64, i64, i64, vp],
+        }
+        for name, args in sigs.items():
+            fn = getattr(lib, name)
+            fn.restype = i32
+            fn.argtypes = args
+        _declared = True
+    return lib
+
+
+class MnistCohortNet:
+    """Lock-step local training of ``arena.num_clients`` MNIST CNNs on one GPU."""
+
+    def __init__(self, cfg: Any, arena: Any, shards: Any, dropout: bool = True) -> None:
+        assert arena.device.type == "cuda", "MnistCohortNet needs a CUDA device"
+        assert arena.slots_lowp is not None, "arena must be created with with_lowp=True"
+        self.cfg, self.arena, self.shards = cfg, arena, shards
+        self.lib = _lib()
+        dev = arena.device
+        self.device = dev
+        c, b = arena.num_clients, cfg.batch_size
+        self.c, self.b = c, b
+        self.rows = b * _GRID
+        lay = arena.layout
+        self.off = {name: lay[name].offset for name in lay.names}
+        self.n_total = lay.total
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        self.w2p = torch.zeros(c, 64, 288, **bf)
+        self.a1 = torch.zeros(c, self.rows, 32, **bf)
+        self.a2 = torch.zeros(c, self.rows, 64, **bf)
+        self.p = torch.zeros(c, b, 9216, **bf)
+        self.pidx = torch.zeros(c, b, 144, 64, dtype=torch.uint8, device=dev)
+        self.hpre = torch.zeros(c, b, 128, dtype=torch.float32, device=dev)
+        self.dh = torch.zeros(c, b, 128, **bf)
+        self.dp = torch.zeros(c, b, 9216, **bf)
+        self.da2 = torch.zeros(c, self.rows, 64, **bf)
+        self.da1 = torch.zeros(c, self.rows, 32, **bf)
+        self.grads = torch.zeros(c, self.n_total, dtype=torch.float32, device=dev)
+        self.rng_state = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.p1 = 0.25 if dropout else 0.0
+        self.p2 = 0.5 if dropout else 0.0
+        self.seed = int(cfg.seed) * 7919 + 13
+        # fc1 weights: bf16 working copy, viewed [C, 128, 9216] inside the arena rows
+        o = self.off["fc1.weight"]
+        self.fc1_w = arena.slots_lowp[:, o : o + 128 * 9216].view(c, 128, 9216)
+        self.fc1_g = self.grads[:, o:]
+        self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
+        # atomic-accumulated gradient entries (conv1.*, conv2.*) sit in front of fc1.weight
+        self._atomic_prefix = self.off["fc1.weight"]
+        self._conv2_bias = arena.slots[:, self.off["conv2.bias"] : self.off["conv2.bias"] + 64]
+        self._graph: "torch.cuda.CUDAGraph | None" = None
+        self.launches_per_round = 0
+        self.k_split_fc = 8
+        self.k_split_wgrad = max(1, min(16, (4 * 148) // max(c, 1)))
+
+    # -- hooks used by FedSimulation -------------------------------------------------
+    def after_broadcast(self) -> None:
+        pass
+
+    def before_aggregate(self) -> None:
+        pass
+
+    # -- one local step for every client ------------------------------------------------
+    def _check(self, code: int, what: str) -> None:
+        native._check(code, what)
+        native._count()
+
+    def step(self, step: int) -> None:
+        cfg, a, lib = self.cfg, self.arena, self.lib
+        c, b, n = self.c, self.b, self.n_total
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        lo = (step % cfg.steps_per_epoch) * b
+        x = self.shards.images[:, lo : lo + b]
+        y = self.shards.labels[:, lo : lo + b]
+        assert x.stride(0) == self.shards.images.stride(0)
+        slots, grads = a.slots, self.grads
+        off = self.off
+        # x / y are [C, b, ...] slices of [C, S, ...]: the client stride stays S·784 / S.
+        xs = x.stride(0)
+        # ---- forward ----
+        self._check(lib.nfb_mnist_prep_conv2(slots.data_ptr(), n, off["conv2.weight"], c,
+                                             self.w2p.data_ptr(), st), "prep_conv2")
+        self._check(lib.nfb_mnist_conv1_fwd(x.data_ptr(), xs, slots.data_ptr(), n,
+                                            off["conv1.weight"], off["conv1.bias"], c, b,
+                                            self.a1.data_ptr(), st), "conv1_fwd")
+        tc.conv3x3_fwd(self.a1, self.w2p, self._conv2_bias, self.a2, 26, relu=True)
+        self._check(lib.nfb_mnist_pool_fwd(self.a2.data_ptr(), c, b, self.p1,
+                                           self.rng_state.data_ptr(), self.seed,
+                                           self.p.data_ptr(), self.pidx.data_ptr(), st),
+                    "pool_fwd")
+        self.hpre.zero_()
+        tc.linear_fwd(self.fc1_w, self.p, self.hpre, k_split=self.k_split_fc)
+        grads[:, : self._atomic_prefix].zero_()
+        self._check(lib.nfb_mnist_fc_head(self.hpre.data_ptr(), y.data_ptr(), y.stride(0), c, b,
+                                          slots.data_ptr(), grads.data_ptr(), n, off["fc1.bias"],
+                                          off["fc2.weight"], off["fc2.bias"], self.p2,
+                                          self.rng_state.data_ptr(), self.seed,
+                                          self.dh.data_ptr(), a.stats.data_ptr(), st), "fc_head")
+        # ---- backward ----
+        tc.linear_wgrad(self.dh, self.p, self.fc1_g, n)
+        tc.linear_dgrad(self.fc1_w, self.dh, self.dp)
+        self._check(lib.nfb_mnist_pool_bwd(self.dp.data_ptr(), self.pidx.data_ptr(), c, b,
+                                           self.p1, self.da2.data_ptr(), grads.data_ptr(), n,
+                                           off["conv2.bias"], st), "pool_bwd")
+        tc.conv3x3_wgrad(self.da2, self.a1, self.conv2_g, 26, n, k_split=self.k_split_wgrad)
+        tc.conv3x3_dgrad(self.da2, self.w2p, self.da1, 26, relu_mask=self.a1)
+        self._check(lib.nfb_mnist_conv1_wgrad(self.da1.data_ptr(), x.data_ptr(), xs, c, b,
+                                              grads.data_ptr(), n, off["conv1.weight"],
+                                              off["conv1.bias"], st), "conv1_wgrad")
+        # ---- optimiser: one fused launch over all clients ----
+        ops.fused_sgd_(slots.view(-1), grads.view(-1), cfg.learning_rate,
+                       momentum_buf=None if a.momentum is None else a.momentum.view(-1),
+                       momentum=cfg.momentum, weight_decay=cfg.weight_decay,
+                       first_step=(step == 0), lowp_out=a.slots_lowp.view(-1))
+
+    def _all_steps(self) -> None:
+        for s in range(self.cfg.local_steps):
+            self.step(s)
+
+    def local_steps(self) -> None:
+        if not self.cfg.use_cuda_graph:
+            self._all_steps()
+            return
+        if self._graph is None:
+            self._capture()
+        self._graph.replay()
+
+    def _capture(self) -> None:
+        a = self.arena
+        keep = (a.slots.clone(), a.slots_lowp.clone(), a.stats.clone(), self.rng_state.clone(),
+                None if a.momentum is None else a.momentum.clone())
+
+        def restore() -> None:
+            a.slots.copy_(keep[0])
+            a.slots_lowp.copy_(keep[1])
+            a.stats.copy_(keep[2])
+            self.rng_state.copy_(keep[3])
+            if keep[4] is not None:
+                a.momentum.copy_(keep[4])
+
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            self.step(0)  # eager warm-up: tensor maps, function attributes, lazy inits
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        tc.check_status(self.device)
+        restore()
+        before = native.LAUNCHES
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            self._all_steps()
+        self.launches_per_round = native.LAUNCHES - before
+        restore()
+        torch.cuda.synchronize(self.device)
+        self._graph = graph
