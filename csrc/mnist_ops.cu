@@ -45,11 +45,11 @@ __global__ void __launch_bounds__(256)
     conv1_fwd_kernel(const float* __restrict__ x, int64_t x_cstride,
                      const float* __restrict__ slots, int64_t row_stride, int64_t w_off,
                      int64_t b_off, int B, __nv_bfloat16* __restrict__ a1) {
-  __shared__ float sw[32 * 9];
+  __shared__ __align__(16) float swt[9 * 32];  // [tap][co] so 8 channels of one tap are 2 x LDS.128
   __shared__ float sb[32];
   const int c = blockIdx.y;
   const float* w = slots + c * row_stride + w_off;
-  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) swt[(i % 9) * 32 + i / 9] = w[i];
   if (threadIdx.x < 32) sb[threadIdx.x] = slots[c * row_stride + b_off + threadIdx.x];
   __syncthreads();
   const int64_t items = static_cast<int64_t>(B) * kGrid * 4;  // (position, channel-octet)
@@ -69,13 +69,18 @@ __global__ void __launch_bounds__(256)
       for (int kw = 0; kw < 3; ++kw) in[kh * 3 + kw] = px[kh * 28 + kw];
     float out[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int co = oct * 8 + j;
-      float acc = sb[co];
+    for (int j = 0; j < 8; ++j) out[j] = sb[oct * 8 + j];
 #pragma unroll
-      for (int t = 0; t < 9; ++t) acc = fmaf(in[t], sw[co * 9 + t], acc);
-      out[j] = fmaxf(acc, 0.f);
+    for (int t = 0; t < 9; ++t) {
+      const float4 w0 = *reinterpret_cast<const float4*>(swt + t * 32 + oct * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(swt + t * 32 + oct * 8 + 4);
+      out[0] = fmaf(in[t], w0.x, out[0]); out[1] = fmaf(in[t], w0.y, out[1]);
+      out[2] = fmaf(in[t], w0.z, out[2]); out[3] = fmaf(in[t], w0.w, out[3]);
+      out[4] = fmaf(in[t], w1.x, out[4]); out[5] = fmaf(in[t], w1.y, out[5]);
+      out[6] = fmaf(in[t], w1.z, out[6]); out[7] = fmaf(in[t], w1.w, out[7]);
     }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) out[j] = fmaxf(out[j], 0.f);
     st_vec(oc + pos * 32 + oct * 8, pack<__nv_bfloat16>(out));
   }
 }
@@ -159,7 +164,10 @@ __global__ void __launch_bounds__(256)
   }
   __syncthreads();
   __nv_bfloat16* dst = da2 + img * kGrid * 64;
-  // item = (grid position, channel octet): 676 * 8 items, every position is written
+  // item = (grid position, channel octet): 676 * 8 items, every position is written.
+  // blockDim.x % 8 == 0, so a thread keeps the same channel octet for all its items and can
+  // accumulate the bias gradient in registers.
+  float bsum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   for (int it = threadIdx.x; it < kGrid * 8; it += blockDim.x) {
     const int oct = it & 7, q = it >> 3;
     const int oh = q / kG, ow = q % kG;
@@ -177,10 +185,20 @@ __global__ void __launch_bounds__(256)
       }
     }
     st_vec(dst + q * 64 + oct * 8, pack<__nv_bfloat16>(out));
-    // bias gradient: sum over positions (values are bf16-rounded exactly as conv wgrad sees them)
+    // bias gradient: sum over positions (values bf16-rounded exactly as conv wgrad sees them)
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (out[j] != 0.f) atomicAdd(&sbias[oct * 8 + j], __bfloat162float(__float2bfloat16_rn(out[j])));
+    for (int j = 0; j < 8; ++j) bsum[j] += __bfloat162float(__float2bfloat16_rn(out[j]));
+  }
+  {
+    const int oct = threadIdx.x & 7;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      // lanes with equal (lane & 7) share an octet: reduce over lane bits 3,4 first
+      float v = bsum[j];
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      if ((threadIdx.x & 31) < 8 && v != 0.f) atomicAdd(&sbias[oct * 8 + j], v);
+    }
   }
   __syncthreads();
   if (threadIdx.x < 64 && sbias[threadIdx.x] != 0.f)
@@ -195,7 +213,7 @@ __global__ void __launch_bounds__(256)
 // counters that replace the reference's two .item() syncs per batch — and bumps the
 // per-step dropout counter.
 // -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
     fc_head_kernel(const float* __restrict__ hpre, const int64_t* __restrict__ labels,
                    int64_t label_stride, int B, const float* __restrict__ slots,
                    float* __restrict__ grads, int64_t row_stride, int64_t b1_off, int64_t w2_off,
@@ -214,16 +232,21 @@ __global__ void __launch_bounds__(256)
 
   for (int i = threadIdx.x; i < 1280; i += blockDim.x) w2[i] = row[w2_off + i];
   const float* hp = hpre + static_cast<int64_t>(c) * B * 128;
-  for (int i = threadIdx.x; i < B * 128; i += blockDim.x) {
-    float v = hp[i] + row[b1_off + (i & 127)];
-    v = fmaxf(v, 0.f);
+  for (int i4 = threadIdx.x; i4 < B * 32; i4 += blockDim.x) {   // 4 elements per Philox draw
+    const int i = i4 * 4;
+    const float4 hv = *reinterpret_cast<const float4*>(hp + i);
+    const float4 bv = *reinterpret_cast<const float4*>(row + b1_off + (i & 127));
+    float v[4] = {fmaxf(hv.x + bv.x, 0.f), fmaxf(hv.y + bv.y, 0.f), fmaxf(hv.z + bv.z, 0.f),
+                  fmaxf(hv.w + bv.w, 0.f)};
     if (drop_p > 0.f) {
-      const uint64_t elem = static_cast<uint64_t>(c) * B * 128 + i;
-      const float4 u = Philox::uniform4((step << 34) + (1ull << 33) + (elem >> 2), seed);
-      const float uu = (elem & 3) == 0 ? u.x : (elem & 3) == 1 ? u.y : (elem & 3) == 2 ? u.z : u.w;
-      v = uu >= drop_p ? v * keep_scale : 0.f;
+      const uint64_t grp = static_cast<uint64_t>(c) * B * 32 + i4;
+      const float4 u = Philox::uniform4((step << 34) + (1ull << 33) + grp, seed);
+      v[0] = u.x >= drop_p ? v[0] * keep_scale : 0.f;
+      v[1] = u.y >= drop_p ? v[1] * keep_scale : 0.f;
+      v[2] = u.z >= drop_p ? v[2] * keep_scale : 0.f;
+      v[3] = u.w >= drop_p ? v[3] * keep_scale : 0.f;
     }
-    h[i] = v;
+    *reinterpret_cast<float4*>(h + i) = make_float4(v[0], v[1], v[2], v[3]);
   }
   __syncthreads();
   // logits
@@ -399,7 +422,7 @@ int nfb_mnist_fc_head(const float* hpre, const int64_t* labels, int64_t label_st
     cudaFuncSetAttribute(fc_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     attr = true;
   }
-  fc_head_kernel<<<C, 256, smem, as_stream(stream)>>>(
+  fc_head_kernel<<<C, 1024, smem, as_stream(stream)>>>(
       hpre, labels, label_stride, B, slots, grads, row_stride, b1_off, w2_off, b2_off, drop_p,
       static_cast<unsigned long long*>(rng_state), seed, static_cast<__nv_bfloat16*>(dh), stats);
   return launch_status("mnist_fc_head");

@@ -1,0 +1,555 @@
+// K-CONV, persistent form: 3x3 convolution forward / data-gradient on the row-flattened
+// NHWC grid, one CTA per (client, contiguous range of 128-position tiles).
+//
+// Why a second kernel next to tc_gemm.cu: there, each of the 9 taps re-loads a 128-row A
+// tile (9x redundant L2->SMEM traffic, measured L2-bound).  Here
+//   * the client's 9 weight tiles (36 KB bf16) are loaded ONCE per CTA and stay in SMEM;
+//   * per output tile ONE slab of 128+54 activation rows is loaded by a single 4-D TMA
+//     (box 8 ch x 182 rows x CH/8 chunks) in the un-swizzled "interleaved" UMMA layout
+//     [channel-chunk][row][16 B], in which a row shift is just +16 B on the descriptor
+//     start address — so the 9 taps are 9 descriptors into the same slab;
+//   * two TMEM accumulators alternate, so the epilogue (tcgen05.ld, bias/ReLU/ReLU-mask,
+//     bf16 pack, 16-byte stores) of tile i overlaps the MMAs of tile i+1.
+//
+// MODE 0 (forward):  out[q, co] = relu(sum_t sum_ci x[q + s_t, ci] w[co, t*32+ci] + b[co])
+//                    A = x [C,R,32] (4 chunks), B_t = w[:, t*32:(t+1)*32] K-major SW64, N = 64
+// MODE 1 (dgrad):    out[q, ci] = (sum_t sum_co dy[q - s_t, co] w[co, t*32+ci]) * (mask[q,ci] > 0)
+//                    A = dy [C,R,64] (8 chunks), B_t = same weights read MN-major SW64, N = 32
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace nfb {
+namespace tc {
+
+constexpr int kTaps = 9;
+constexpr int kHalo = 54;            // 2*26 + 2 : largest tap shift on the 26-wide grid
+constexpr int kSlabRows = 128 + kHalo;
+constexpr int kConvStages = 4;
+
+struct ConvArgs {
+  int tiles_per_client;   // ceil(R / 128)
+  int ctas_per_client;
+  int rows;               // R
+  int shift[kTaps];       // slab-relative row shift per tap
+  void* out;              // bf16 [C, R, N]
+  long long out_gs;       // elements between clients
+  const float* bias;      // MODE 0: [C][64] with stride bias_gs
+  long long bias_gs;
+  const __nv_bfloat16* mask;  // MODE 1: [C, R, 32] ReLU mask source (same strides as out)
+  int* status;
+};
+
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar,
+                                            int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+template <int MODE>
+struct ConvCfg {
+  static constexpr int CH = MODE == 0 ? 32 : 64;       // A channels (K per tap)
+  static constexpr int BN = MODE == 0 ? 64 : 32;       // output channels
+  static constexpr int CHUNKS = CH / 8;
+  static constexpr int SLAB = kSlabRows * CH * 2;      // bytes per stage
+  static constexpr int SLAB_PAD = (SLAB + 1023) / 1024 * 1024;
+  static constexpr int W_TILE = 64 * 32 * 2;           // one tap's weights (4 KB) either way
+  static constexpr int W_BYTES = kTaps * W_TILE;
+  static constexpr int TMEM_COLS = 2 * BN;             // 128 or 64 (both powers of two)
+  static constexpr size_t SMEM = W_BYTES + kConvStages * SLAB_PAD + 1024 + 256;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256, 1)
+    tc_conv_kernel(const __grid_constant__ CUtensorMap map_a,   // 4-D slab map
+                   const __grid_constant__ CUtensorMap map_w,   // 3-D weight map (SW64)
+                   const ConvArgs args) {
+  using C = ConvCfg<MODE>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* w_smem = smem;                              // 9 x 4 KB, 1024-aligned
+  uint8_t* slabs = smem + C::W_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kConvStages * C::SLAB_PAD);
+  uint64_t* full_bar = bars;                           // [stages]
+  uint64_t* empty_bar = bars + kConvStages;            // [stages]
+  uint64_t* acc_full = bars + 2 * kConvStages;         // [2]
+  uint64_t* acc_empty = acc_full + 2;                  // [2]
+  uint64_t* w_bar = acc_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x / args.ctas_per_client;
+  const int part = blockIdx.x % args.ctas_per_client;
+  const int per = (args.tiles_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
+  const int tile_lo = part * per;
+  const int tile_hi = min(tile_lo + per, args.tiles_per_client);
+  const int n_tiles = max(tile_hi - tile_lo, 0);
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&map_a);
+    prefetch_tmap(&map_w);
+    for (int s = 0; s < kConvStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+    mbar_init(w_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== producer =====================
+    if (elect_one() && n_tiles > 0) {
+      mbar_expect_tx(w_bar, C::W_BYTES);
+      for (int t = 0; t < kTaps; ++t) {
+        if (MODE == 0)  // K-major box [32 k, 64 co]
+          tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
+        else            // MN-major box [32 ci, 64 co-rows]: same bytes, read as B^T
+          tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
+      }
+      for (int i = 0; i < n_tiles; ++i) {
+        const int s = i % kConvStages;
+        const uint32_t ph = (i / kConvStages) & 1;
+        if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; break; }
+        mbar_expect_tx(&full_bar[s], C::SLAB);
+        const int m0 = (tile_lo + i) * 128;
+        const int row0 = MODE == 0 ? m0 : m0 - kHalo;
+        tma_load_4d(slabs + s * C::SLAB_PAD, &map_a, &full_bar[s], 0, row0, 0, g);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one() && n_tiles > 0) {
+      // fwd: A K-major, B K-major ; dgrad: A K-major, B MN-major
+      constexpr uint32_t idesc = make_idesc_bf16(128, C::BN, 0u, MODE == 0 ? 0u : 1u);
+      bool ok = mbar_wait(w_bar, 0);
+      if (!ok) *args.status = 1;
+      const uint32_t w_addr = smem_u32(w_smem);
+      for (int i = 0; i < n_tiles && ok; ++i) {
+        const int s = i % kConvStages;
+        const int acc = i & 1;
+        const uint32_t ph = (i / kConvStages) & 1;
+        const uint32_t aph = (i >> 1) & 1;
+        if (!mbar_wait(&acc_empty[acc], aph ^ 1)) { *args.status = 1; ok = false; break; }
+        if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
+        tc_fence_after();
+        const uint32_t slab = smem_u32(slabs + s * C::SLAB_PAD);
+        const uint32_t d_tmem = tmem_base + acc * C::BN;
+#pragma unroll
+        for (int t = 0; t < kTaps; ++t) {
+#pragma unroll
+          for (int kk = 0; kk < C::CH / 16; ++kk) {
+            // A: interleaved layout, chunk pitch = kSlabRows*16 B, 8-row group pitch = 128 B
+            const uint64_t da = make_smem_desc(
+                slab + args.shift[t] * 16 + kk * (2 * kSlabRows * 16), kSlabRows * 16, 128, 0);
+            uint64_t db;
+            if (MODE == 0)   // K-major SW64 tile [64 co][32 k]: step K by 32 B
+              db = make_smem_desc(w_addr + t * C::W_TILE + kk * 32, 0, 8 * 64, 4);
+            else             // MN-major SW64 tile [64 k-rows][32 ci]: step K by 16 rows
+              db = make_smem_desc(w_addr + t * C::W_TILE + kk * (16 * 64), 64 * 64, 8 * 64, 4);
+            umma_f16(d_tmem, da, db, idesc, (t > 0 || kk > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty_bar[s]);
+        umma_commit(&acc_full[acc]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int sub = warp - 4;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
+    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(args.out) + static_cast<long long>(g) * args.out_gs;
+    const __nv_bfloat16* mask = args.mask ? args.mask + static_cast<long long>(g) * args.out_gs : nullptr;
+    const float* bias = args.bias ? args.bias + static_cast<long long>(g) * args.bias_gs : nullptr;
+    bool ok = true;
+    for (int i = 0; i < n_tiles && ok; ++i) {
+      const int acc = i & 1;
+      const uint32_t aph = (i >> 1) & 1;
+      if (!mbar_wait(&acc_full[acc], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }
+      tc_fence_after();
+      const int m = (tile_lo + i) * 128 + sub * 32 + lane;
+#pragma unroll
+      for (int c0 = 0; c0 < C::BN; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(lane_addr + acc * C::BN + c0, r);
+        tmem_ld_wait();
+        if (m < args.rows) {
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+          const long long idx = static_cast<long long>(m) * C::BN + c0;
+          if (MODE == 0) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + (bias ? bias[c0 + j] : 0.f), 0.f);
+          } else if (mask) {
+            float mf[16];
+            unpack<__nv_bfloat16>(ld_plain(mask + idx), mf);
+            unpack<__nv_bfloat16>(ld_plain(mask + idx + 8), mf + 8);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (!(mf[j] > 0.f)) v[j] = 0.f;
+          }
+          st_vec(out + idx, pack<__nv_bfloat16>(v));
+          st_vec(out + idx + 8, pack<__nv_bfloat16>(v + 8));
+        }
+      }
+      // this warp is done reading accumulator `acc`
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+// -------------------------------------------------------------------------------------
+// Weight gradient, persistent form: one CTA per (client, contiguous range of 64-row
+// k-blocks).  D_t[co, ci] += sum_q dy[q, co] * x[q + s_t, ci] for the 9 taps, held in 9 TMEM
+// accumulators (9 x 32 columns) for the CTA's whole k-range; per k-block ONE dy tile
+// (MN-major, 128-B swizzle) and ONE x slab of 64+54 rows (interleaved layout, so the 9 taps
+// are 9 descriptors into it).  M is padded 64 -> 128 with a zeroed second swizzle atom that
+// TMA never touches.  Epilogue: fp32 atomics into the OIHW gradient inside the flat slab.
+// -------------------------------------------------------------------------------------
+constexpr int kWgSlabRows = 64 + kHalo;              // 118
+constexpr int kWgStages = 4;
+constexpr int kWgATile = 128 * 64 * 2;               // 16 KB (second 8 KB stays zero)
+constexpr int kWgSlab = kWgSlabRows * 32 * 2;        // 7552 B
+constexpr int kWgSlabPad = 8192;
+constexpr int kWgStage = kWgATile + kWgSlabPad;
+constexpr size_t kWgSmem = static_cast<size_t>(kWgStages) * kWgStage + 1024 + 256;
+
+struct WgradArgs {
+  int kblocks_per_client;  // ceil(R / 64)
+  int ctas_per_client;
+  int shift[kTaps];
+  float* grad;             // first client's [64][32][3][3] block inside the gradient slab
+  long long grad_gs;
+  int* status;
+};
+
+__global__ void __launch_bounds__(256, 1)
+    tc_conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy,  // 3-D, box [64, 64, 1], SW128
+                         const __grid_constant__ CUtensorMap map_x,   // 4-D slab, box (8,118,4,1)
+                         const WgradArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStage);
+  uint64_t* empty_bar = full_bar + kWgStages;
+  uint64_t* acc_bar = empty_bar + kWgStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x / args.ctas_per_client;
+  const int part = blockIdx.x % args.ctas_per_client;
+  const int per = (args.kblocks_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
+  const int kb_lo = part * per;
+  const int kb_hi = min(kb_lo + per, args.kblocks_per_client);
+  const int n_kb = max(kb_hi - kb_lo, 0);
+
+  // zero the padding half (co 64..127) of every A stage once
+  for (int s = 0; s < kWgStages; ++s) {
+    uint4* z = reinterpret_cast<uint4*>(smem + s * kWgStage + kWgATile / 2);
+    for (int i = threadIdx.x; i < kWgATile / 2 / 16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async();
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&map_dy);
+    prefetch_tmap(&map_x);
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      for (int i = 0; i < n_kb; ++i) {
+        const int s = i % kWgStages;
+        const uint32_t ph = (i / kWgStages) & 1;
+        if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; break; }
+        uint8_t* stage = smem + s * kWgStage;
+        mbar_expect_tx(&full_bar[s], kWgATile / 2 + kWgSlab);
+        const int q0 = (kb_lo + i) * 64;
+        tma_load_3d(stage, &map_dy, &full_bar[s], 0, q0, g);               // [64 co x 64 rows]
+        tma_load_4d(stage + kWgATile, &map_x, &full_bar[s], 0, q0, 0, g);  // 118-row slab
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, 32, 1u, 1u);
+      bool ok = true;
+      for (int i = 0; i < n_kb && ok; ++i) {
+        const int s = i % kWgStages;
+        const uint32_t ph = (i / kWgStages) & 1;
+        if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * kWgStage);
+        const uint32_t slab = a_addr + kWgATile;
+#pragma unroll
+        for (int t = 0; t < kTaps; ++t) {
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            // A: MN-major SW128, atoms [64 rows x 128 B] 8 KB apart, 16 k-rows per step
+            const uint64_t da = make_smem_desc(a_addr + kk * (16 * 128), 64 * 128, 8 * 128, 2);
+            // B: MN-major interleaved: 8-k-row groups 128 B apart, ci chunks one slab plane apart
+            const uint64_t db = make_smem_desc(slab + (args.shift[t] + kk * 16) * 16, 128,
+                                               kWgSlabRows * 16, 0);
+            umma_f16(tmem_base + t * 32, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      umma_commit(acc_bar);
+    }
+  } else if (warp >= 4) {
+    const int sub = warp - 4;
+    bool ok = true;
+    if (n_kb > 0) ok = mbar_wait(acc_bar, 0);
+    if (!ok && lane == 0) *args.status = 1;
+    tc_fence_after();
+    const int co = sub * 32 + lane;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
+    float* gout = args.grad + static_cast<long long>(g) * args.grad_gs;
+    if (sub < 2) {  // rows 64..127 are padding
+#pragma unroll 1
+      for (int t = 0; t < kTaps; ++t) {
+#pragma unroll
+        for (int c0 = 0; c0 < 32; c0 += 16) {
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(lane_addr + t * 32 + c0, r);
+          tmem_ld_wait();
+          if (ok && n_kb > 0) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              atomicAdd(gout + co * 288 + (c0 + j) * 9 + t, __uint_as_float(r[j]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace tc
+}  // namespace nfb
+
+// =====================================================================================
+// Host side
+// =====================================================================================
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace nfb {
+namespace tc {
+
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                              const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                              const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeFn conv_encode_fn() {
+  static EncodeFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeFn>(p);
+  });
+  return fn;
+}
+
+using ConvKey = std::tuple<const void*, long long, long long, long long, int, int>;
+static std::map<ConvKey, CUtensorMap> g_conv_maps;
+static std::mutex g_conv_mu;
+
+// 4-D slab map over a bf16 [C, rows, ch] tensor: (8 elems, rows, ch/8 chunks, clients)
+static int slab_map(const void* ptr, long long rows, long long groups, long long group_stride,
+                    int ch, int box_rows, CUtensorMap* out) {
+  ConvKey key{ptr, rows, groups, group_stride, ch, box_rows};
+  std::lock_guard<std::mutex> lock(g_conv_mu);
+  auto it = g_conv_maps.find(key);
+  if (it != g_conv_maps.end()) { *out = it->second; return 0; }
+  EncodeFn enc = conv_encode_fn();
+  if (!enc) return fail(NFB_ESTATE, "tc_conv: cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[4] = {8, static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(ch / 8),
+                        static_cast<cuuint64_t>(groups)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(ch) * 2, 16,
+                           static_cast<cuuint64_t>(group_stride) * 2};
+  cuuint32_t box[4] = {8, static_cast<cuuint32_t>(box_rows), static_cast<cuuint32_t>(ch / 8), 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(NFB_EINVAL, "tc_conv: slab tensor map rejected (CUresult %d)", static_cast<int>(r));
+  if (g_conv_maps.size() > 1024) g_conv_maps.clear();
+  g_conv_maps[key] = m;
+  *out = m;
+  return 0;
+}
+
+static int weight_map(const void* ptr, long long groups, long long group_stride, CUtensorMap* out) {
+  ConvKey key{ptr, 64, groups, group_stride, -1, 0};
+  std::lock_guard<std::mutex> lock(g_conv_mu);
+  auto it = g_conv_maps.find(key);
+  if (it != g_conv_maps.end()) { *out = it->second; return 0; }
+  EncodeFn enc = conv_encode_fn();
+  if (!enc) return fail(NFB_ESTATE, "tc_conv: cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[3] = {288, 64, static_cast<cuuint64_t>(groups)};
+  cuuint64_t strides[2] = {288 * 2, static_cast<cuuint64_t>(group_stride) * 2};
+  cuuint32_t box[3] = {32, 64, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(NFB_EINVAL, "tc_conv: weight tensor map rejected (CUresult %d)", static_cast<int>(r));
+  g_conv_maps[key] = m;
+  *out = m;
+  return 0;
+}
+
+template <int MODE>
+static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, int ctas, const ConvArgs& a,
+                       cudaStream_t st) {
+  using C = ConvCfg<MODE>;
+  auto kern = tc_conv_kernel<MODE>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(C::SMEM));
+    if (e != cudaSuccess)
+      return fail(static_cast<int>(e), "tc_conv: smem attribute: %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  kern<<<ctas, 256, C::SMEM, st>>>(ma, mw, a);
+  return launch_status("tc_conv");
+}
+
+}  // namespace tc
+}  // namespace nfb
+
+// mode 0: forward (x [C,R,32] -> out [C,R,64], bias+ReLU); mode 1: dgrad (dy [C,R,64] -> out
+// [C,R,32], optional ReLU mask).  w = bf16 [C][64][288] (tap-major, channel-minor).
+extern "C" int nfb_tc_conv3x3(int mode, const void* a, long long rows, long long a_group_stride,
+                              const void* w, long long w_group_stride, int clients, int width,
+                              void* out, long long out_group_stride, const float* bias,
+                              long long bias_group_stride, const void* mask, int* status,
+                              void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(a && w && out && status, NFB_EINVAL, "tc_conv3x3: null pointer");
+  NFB_REQUIRE(mode == 0 || mode == 1, NFB_EINVAL, "tc_conv3x3: mode must be 0 or 1");
+  NFB_REQUIRE(clients >= 1 && rows >= 1, NFB_EINVAL, "tc_conv3x3: bad sizes");
+  NFB_REQUIRE(2 * width + 2 <= kHalo, NFB_ERANGE,
+              "tc_conv3x3: grid width %d needs a halo of %d rows, kernel has %d", width,
+              2 * width + 2, kHalo);
+  const int ch = mode == 0 ? 32 : 64;
+  CUtensorMap ma, mw;
+  int rc = slab_map(a, rows, clients, a_group_stride, ch, kSlabRows, &ma);
+  if (rc) return rc;
+  rc = weight_map(w, clients, w_group_stride, &mw);
+  if (rc) return rc;
+  ConvArgs args{};
+  args.tiles_per_client = static_cast<int>((rows + 127) / 128);
+  int per_client = sm_count() / clients;
+  if (per_client < 1) per_client = 1;
+  if (per_client > args.tiles_per_client) per_client = args.tiles_per_client;
+  args.ctas_per_client = per_client;
+  args.rows = static_cast<int>(rows);
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kw = 0; kw < 3; ++kw) {
+      const int s = kh * width + kw;
+      args.shift[kh * 3 + kw] = mode == 0 ? s : kHalo - s;
+    }
+  args.out = out;
+  args.out_gs = out_group_stride;
+  args.bias = bias;
+  args.bias_gs = bias_group_stride;
+  args.mask = static_cast<const __nv_bfloat16*>(mask);
+  args.status = status;
+  const int ctas = clients * per_client;
+  cudaStream_t st = as_stream(stream);
+  return mode == 0 ? launch_conv<0>(ma, mw, ctas, args, st) : launch_conv<1>(ma, mw, ctas, args, st);
+}
+
+// Weight gradient: grad[c][co][ci][t] += sum_q dy[c,q,co] * x[c,q+s_t,ci]  (fp32 atomics; the
+// caller zeroes the target).  dy = bf16 [C,R,64] (zero outside the valid window), x = bf16 [C,R,32].
+extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long rows,
+                                    long long dy_group_stride, long long x_group_stride,
+                                    int clients, int width, float* grad, long long grad_group_stride,
+                                    int* status, void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(dy && x && grad && status, NFB_EINVAL, "tc_conv3x3_wgrad: null pointer");
+  NFB_REQUIRE(clients >= 1 && rows >= 1, NFB_EINVAL, "tc_conv3x3_wgrad: bad sizes");
+  NFB_REQUIRE(2 * width + 2 <= kHalo, NFB_ERANGE, "tc_conv3x3_wgrad: grid width %d too large", width);
+  CUtensorMap mdy, mx;
+  {
+    // dy as MN-major operand: 3-D map (64 co, rows, clients), box [64, 64, 1], 128-B swizzle
+    ConvKey key{dy, rows, clients, dy_group_stride, -2, 0};
+    std::lock_guard<std::mutex> lock(g_conv_mu);
+    auto it = g_conv_maps.find(key);
+    if (it != g_conv_maps.end()) {
+      mdy = it->second;
+    } else {
+      EncodeFn enc = conv_encode_fn();
+      if (!enc) return fail(NFB_ESTATE, "tc_conv3x3_wgrad: cuTensorMapEncodeTiled unavailable");
+      cuuint64_t dims[3] = {64, static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(clients)};
+      cuuint64_t strides[2] = {128, static_cast<cuuint64_t>(dy_group_stride) * 2};
+      cuuint32_t box[3] = {64, 64, 1};
+      cuuint32_t estr[3] = {1, 1, 1};
+      CUresult r = enc(&mdy, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(dy), dims,
+                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS)
+        return fail(NFB_EINVAL, "tc_conv3x3_wgrad: dy tensor map rejected (%d)", static_cast<int>(r));
+      g_conv_maps[key] = mdy;
+    }
+  }
+  int rc = slab_map(x, rows, clients, x_group_stride, 32, kWgSlabRows, &mx);
+  if (rc) return rc;
+  WgradArgs a{};
+  a.kblocks_per_client = static_cast<int>((rows + 63) / 64);
+  int per_client = sm_count() / clients;
+  if (per_client < 1) per_client = 1;
+  if (per_client > a.kblocks_per_client) per_client = a.kblocks_per_client;
+  a.ctas_per_client = per_client;
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kw = 0; kw < 3; ++kw) a.shift[kh * 3 + kw] = kh * width + kw;
+  a.grad = grad;
+  a.grad_gs = grad_group_stride;
+  a.status = status;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tc_conv_wgrad_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(kWgSmem));
+    if (e != cudaSuccess)
+      return fail(static_cast<int>(e), "tc_conv3x3_wgrad: smem attribute: %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  tc_conv_wgrad_kernel<<<clients * per_client, 256, kWgSmem, as_stream(stream)>>>(mdy, mx, a);
+  return launch_status("tc_conv3x3_wgrad");
+}

@@ -138,7 +138,7 @@ class MnistCohortNet:
         self._check(lib.nfb_mnist_conv1_fwd(x.data_ptr(), xs, slots.data_ptr(), n,
                                             off["conv1.weight"], off["conv1.bias"], c, b,
                                             self.a1.data_ptr(), st), "conv1_fwd")
-        tc.conv3x3_fwd(self.a1, self.w2p, self._conv2_bias, self.a2, 26, relu=True)
+        tc.conv3x3_fwd_persistent(self.a1, self.w2p, self._conv2_bias, self.a2, 26)
         self._check(lib.nfb_mnist_pool_fwd(self.a2.data_ptr(), c, b, self.p1,
                                            self.rng_state.data_ptr(), self.seed,
                                            self.p.data_ptr(), self.pidx.data_ptr(), st),
@@ -157,8 +157,8 @@ class MnistCohortNet:
         self._check(lib.nfb_mnist_pool_bwd(self.dp.data_ptr(), self.pidx.data_ptr(), c, b,
                                            self.p1, self.da2.data_ptr(), grads.data_ptr(), n,
                                            off["conv2.bias"], st), "pool_bwd")
-        tc.conv3x3_wgrad(self.da2, self.a1, self.conv2_g, 26, n, k_split=self.k_split_wgrad)
-        tc.conv3x3_dgrad(self.da2, self.w2p, self.da1, 26, relu_mask=self.a1)
+        tc.conv3x3_wgrad_persistent(self.da2, self.a1, self.conv2_g, 26, n)
+        tc.conv3x3_dgrad_persistent(self.da2, self.w2p, self.da1, 26, relu_mask=self.a1)
         self._check(lib.nfb_mnist_conv1_wgrad(self.da1.data_ptr(), x.data_ptr(), xs, c, b,
                                               grads.data_ptr(), n, off["conv1.weight"],
                                               off["conv1.bias"], st), "conv1_wgrad")

@@ -64,6 +64,36 @@ def check_conv_dgrad():
     return out.float(), ref
 
 
+def check_conv_fwd_p():
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 3, 5, 32, 64
+    r = b * W * W
+    x, w = _bf(c, r, cin), _bf(c, cout, 9 * cin, scale=0.05)
+    bias = torch.randn(c, cout, device="cuda")
+    out = torch.zeros(c, r, cout, device="cuda", dtype=torch.bfloat16)
+    tc.conv3x3_fwd_persistent(x, w, bias, out, W)
+    ref = torch.zeros(c, r, cout, device="cuda")
+    for t, s in enumerate(tc._shifts(W)):
+        ref += torch.einsum("crk,cok->cro", _shift_rows(x, s).float(),
+                            w[:, :, t * cin:(t + 1) * cin].float())
+    return out.float(), (ref + bias[:, None, :]).relu()
+
+
+def check_conv_dgrad_p():
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 2, 5, 32, 64
+    r = b * W * W
+    dy, w = _bf(c, r, cout), _bf(c, cout, 9 * cin, scale=0.05)
+    a1 = _bf(c, r, cin)
+    out = torch.zeros(c, r, cin, device="cuda", dtype=torch.bfloat16)
+    tc.conv3x3_dgrad_persistent(dy, w, out, W, relu_mask=a1)
+    ref = torch.zeros(c, r, cin, device="cuda")
+    for t, s in enumerate(tc._shifts(W)):
+        ref += torch.einsum("cro,cok->crk", _shift_rows(dy, -s).float(),
+                            w[:, :, t * cin:(t + 1) * cin].float())
+    return out.float(), ref * (a1.float() > 0)
+
+
 def check_conv_wgrad():
     from nanofed_b200.ops import tc
     c, b, cin, cout = 2, 3, 32, 64
@@ -72,6 +102,20 @@ def check_conv_wgrad():
     n_total = 64 * 32 * 9 + 128
     grad = torch.zeros(c, n_total, device="cuda")
     tc.conv3x3_wgrad(dy, x, grad[:, 64:], W, n_total, k_split=4)
+    got = grad[:, 64:64 + 64 * 32 * 9].reshape(c, cout, cin, 9)
+    ref = torch.stack([torch.einsum("cro,crk->cok", dy.float(), _shift_rows(x, s).float())
+                       for s in tc._shifts(W)], dim=-1)
+    return got, ref
+
+
+def check_conv_wgrad_p():
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 3, 7, 32, 64
+    r = b * W * W
+    dy, x = _bf(c, r, cout, scale=0.1), _bf(c, r, cin)
+    n_total = 64 * 32 * 9 + 128
+    grad = torch.zeros(c, n_total, device="cuda")
+    tc.conv3x3_wgrad_persistent(dy, x, grad[:, 64:], W, n_total)
     got = grad[:, 64:64 + 64 * 32 * 9].reshape(c, cout, cin, 9)
     ref = torch.stack([torch.einsum("cro,crk->cok", dy.float(), _shift_rows(x, s).float())
                        for s in tc._shifts(W)], dim=-1)
@@ -107,7 +151,8 @@ def check_fc_wgrad():
     return got, torch.einsum("cbj,cbi->cji", dy.float(), x.float())
 
 
-CHECKS = {"conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
+CHECKS = {"conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
+          "conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
           "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad,
           "fc_wgrad": check_fc_wgrad}
 
