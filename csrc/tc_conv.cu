@@ -15,6 +15,8 @@
 //                    A = x [C,R,32] (4 chunks), B_t = w[:, t*32:(t+1)*32] K-major SW64, N = 64
 // MODE 1 (dgrad):    out[q, ci] = (sum_t sum_co dy[q - s_t, co] w[co, t*32+ci]) * (mask[q,ci] > 0)
 //                    A = dy [C,R,64] (8 chunks), B_t = same weights read MN-major SW64, N = 32
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -24,7 +26,6 @@ namespace tc {
 constexpr int kTaps = 9;
 constexpr int kHalo = 54;            // 2*26 + 2 : largest tap shift on the 26-wide grid
 constexpr int kSlabRows = 128 + kHalo;
-constexpr int kConvStages = 4;
 
 struct ConvArgs {
   int tiles_per_client;   // ceil(R / 128)
@@ -37,6 +38,7 @@ struct ConvArgs {
   long long bias_gs;
   const __nv_bfloat16* mask;  // MODE 1: [C, R, 32] ReLU mask source (same strides as out)
   int* status;
+  int debug;  // bottleneck probes (env NFB_CONV_DEBUG): 1 = reuse first slabs, 2 = no MMA, 4 = no stores
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar,
@@ -48,6 +50,21 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
+// TMA store of a [BN x 32 rows] tile from shared memory (bulk_group completion).
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0,
+                                             int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+      "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+constexpr int kEpiWarps = 8;   // two epilogue warpgroups, alternating tiles / accumulators
+
 template <int MODE>
 struct ConvCfg {
   static constexpr int CH = MODE == 0 ? 32 : 64;       // A channels (K per tap)
@@ -58,13 +75,17 @@ struct ConvCfg {
   static constexpr int W_TILE = 64 * 32 * 2;           // one tap's weights (4 KB) either way
   static constexpr int W_BYTES = kTaps * W_TILE;
   static constexpr int TMEM_COLS = 2 * BN;             // 128 or 64 (both powers of two)
-  static constexpr size_t SMEM = W_BYTES + kConvStages * SLAB_PAD + 1024 + 256;
+  static constexpr int STAGES = MODE == 0 ? 10 : 6;    // slab loads in flight per CTA
+  static constexpr int OUT_ROW = BN * 2;               // bytes per output row (128 / 64)
+  static constexpr int STAGING = 32 * OUT_ROW;         // per epilogue warp (4 KB / 2 KB)
+  static constexpr size_t SMEM = W_BYTES + STAGES * SLAB_PAD + kEpiWarps * 4096 + 1024 + 256;
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     tc_conv_kernel(const __grid_constant__ CUtensorMap map_a,   // 4-D slab map
                    const __grid_constant__ CUtensorMap map_w,   // 3-D weight map (SW64)
+                   const __grid_constant__ CUtensorMap map_o,   // 3-D output map, box [BN,32,1]
                    const ConvArgs args) {
   using C = ConvCfg<MODE>;
   extern __shared__ uint8_t smem_raw[];
@@ -72,10 +93,11 @@ __global__ void __launch_bounds__(256, 1)
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* w_smem = smem;                              // 9 x 4 KB, 1024-aligned
   uint8_t* slabs = smem + C::W_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kConvStages * C::SLAB_PAD);
+  uint8_t* staging = slabs + C::STAGES * C::SLAB_PAD;   // kEpiWarps x 4 KB, 1024-aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + kEpiWarps * 4096);
   uint64_t* full_bar = bars;                           // [stages]
-  uint64_t* empty_bar = bars + kConvStages;            // [stages]
-  uint64_t* acc_full = bars + 2 * kConvStages;         // [2]
+  uint64_t* empty_bar = bars + C::STAGES;            // [stages]
+  uint64_t* acc_full = bars + 2 * C::STAGES;         // [2]
   uint64_t* acc_empty = acc_full + 2;                  // [2]
   uint64_t* w_bar = acc_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
@@ -91,7 +113,8 @@ __global__ void __launch_bounds__(256, 1)
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_a);
     prefetch_tmap(&map_w);
-    for (int s = 0; s < kConvStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    prefetch_tmap(&map_o);
+    for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
     mbar_init(w_bar, 1);
     fence_barrier_init();
@@ -113,9 +136,10 @@ __global__ void __launch_bounds__(256, 1)
           tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
       }
       for (int i = 0; i < n_tiles; ++i) {
-        const int s = i % kConvStages;
-        const uint32_t ph = (i / kConvStages) & 1;
+        const int s = i % C::STAGES;
+        const uint32_t ph = (i / C::STAGES) & 1;
         if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; break; }
+        if ((args.debug & 1) && i >= C::STAGES) { mbar_arrive(&full_bar[s]); continue; }
         mbar_expect_tx(&full_bar[s], C::SLAB);
         const int m0 = (tile_lo + i) * 128;
         const int row0 = MODE == 0 ? m0 : m0 - kHalo;
@@ -131,17 +155,19 @@ __global__ void __launch_bounds__(256, 1)
       if (!ok) *args.status = 1;
       const uint32_t w_addr = smem_u32(w_smem);
       for (int i = 0; i < n_tiles && ok; ++i) {
-        const int s = i % kConvStages;
+        const int s = i % C::STAGES;
         const int acc = i & 1;
-        const uint32_t ph = (i / kConvStages) & 1;
+        const uint32_t ph = (i / C::STAGES) & 1;
         const uint32_t aph = (i >> 1) & 1;
         if (!mbar_wait(&acc_empty[acc], aph ^ 1)) { *args.status = 1; ok = false; break; }
         if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
         tc_fence_after();
         const uint32_t slab = smem_u32(slabs + s * C::SLAB_PAD);
         const uint32_t d_tmem = tmem_base + acc * C::BN;
+        const int n_taps = (args.debug & 2) ? 1 : kTaps;
 #pragma unroll
         for (int t = 0; t < kTaps; ++t) {
+          if (t >= n_taps) break;
 #pragma unroll
           for (int kk = 0; kk < C::CH / 16; ++kk) {
             // A: interleaved layout, chunk pitch = kSlabRows*16 B, 8-row group pitch = 128 B
@@ -161,48 +187,74 @@ __global__ void __launch_bounds__(256, 1)
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
-    const int sub = warp - 4;
+    // Warps 4..7 take even tiles (accumulator 0), warps 8..11 odd tiles (accumulator 1).
+    const int sub = warp & 3;                       // TMEM lane quarter this warp may read
+    const int grp = (warp - 4) >> 2;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
-    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(args.out) + static_cast<long long>(g) * args.out_gs;
     const __nv_bfloat16* mask = args.mask ? args.mask + static_cast<long long>(g) * args.out_gs : nullptr;
     const float* bias = args.bias ? args.bias + static_cast<long long>(g) * args.bias_gs : nullptr;
+    uint8_t* my_stage = staging + (warp - 4) * 4096;
     bool ok = true;
-    for (int i = 0; i < n_tiles && ok; ++i) {
-      const int acc = i & 1;
+    for (int i = grp; i < n_tiles && ok; i += 2) {
+      const int acc = grp;
       const uint32_t aph = (i >> 1) & 1;
+      const int row0 = (tile_lo + i) * 128 + sub * 32;
+      const int m = row0 + lane;
+      const bool row_ok = m < args.rows;
+      // the ReLU mask of this row depends only on the tile index: fetch it BEFORE waiting for
+      // the accumulator so its DRAM latency hides behind this tile's MMAs
+      uint4 mk[C::BN / 8];
+      if (MODE == 1 && mask && row_ok) {
+#pragma unroll
+        for (int j = 0; j < C::BN / 8; ++j)
+          mk[j] = ld_stream(mask + static_cast<long long>(m) * C::BN + 8 * j);
+      }
       if (!mbar_wait(&acc_full[acc], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }
       tc_fence_after();
-      const int m = (tile_lo + i) * 128 + sub * 32 + lane;
+      uint32_t r[C::BN];
 #pragma unroll
-      for (int c0 = 0; c0 < C::BN; c0 += 16) {
-        uint32_t r[16];
-        tmem_ld_32x32b_x16(lane_addr + acc * C::BN + c0, r);
-        tmem_ld_wait();
-        if (m < args.rows) {
-          float v[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-          const long long idx = static_cast<long long>(m) * C::BN + c0;
-          if (MODE == 0) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + (bias ? bias[c0 + j] : 0.f), 0.f);
-          } else if (mask) {
-            float mf[16];
-            unpack<__nv_bfloat16>(ld_plain(mask + idx), mf);
-            unpack<__nv_bfloat16>(ld_plain(mask + idx + 8), mf + 8);
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (!(mf[j] > 0.f)) v[j] = 0.f;
-          }
-          st_vec(out + idx, pack<__nv_bfloat16>(v));
-          st_vec(out + idx + 8, pack<__nv_bfloat16>(v + 8));
-        }
-      }
-      // this warp is done reading accumulator `acc`
+      for (int c0 = 0; c0 < C::BN; c0 += 16)
+        tmem_ld_32x32b_x16(lane_addr + acc * C::BN + c0, r + c0);
+      tmem_ld_wait();
+      // accumulator is in registers: hand it back to the MMA warp right away
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      if (lane == 0) {
+        mbar_arrive(&acc_empty[acc]);
+        bulk_wait_read0();          // previous TMA store has finished reading my staging tile
+      }
+      __syncwarp();
+      if (!(args.debug & 4)) {
+        // stage this warp's 32 rows in shared memory with the TMA swizzle (conflict-free
+        // 16-byte stores), then ONE bulk tensor store writes them as full lines
+#pragma unroll
+        for (int c0 = 0; c0 < C::BN; c0 += 8) {
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c0 + j]);
+          if (MODE == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j] + (bias ? __ldg(bias + c0 + j) : 0.f), 0.f);
+          } else if (mask && row_ok) {
+            float mf[8];
+            unpack<__nv_bfloat16>(mk[c0 / 8], mf);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (!(mf[j] > 0.f)) v[j] = 0.f;
+          }
+          const int chunk = c0 / 8;
+          const int sw = MODE == 0 ? (chunk ^ (lane & 7)) : (chunk ^ ((lane >> 1) & 3));
+          st_vec(my_stage + lane * C::OUT_ROW + sw * 16, pack<__nv_bfloat16>(v));
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(&map_o, my_stage, 0, row0, g);   // rows >= R are clipped by the map
+          bulk_commit();
+        }
+      }
     }
+    if (lane == 0) bulk_wait_read0();
   }
 
   tc_fence_before();
@@ -218,18 +270,24 @@ __global__ void __launch_bounds__(256, 1)
 // are 9 descriptors into it).  M is padded 64 -> 128 with a zeroed second swizzle atom that
 // TMA never touches.  Epilogue: fp32 atomics into the OIHW gradient inside the flat slab.
 // -------------------------------------------------------------------------------------
-constexpr int kWgSlabRows = 64 + kHalo;              // 118
-constexpr int kWgStages = 4;
+// B slab: 12 planes (kw = 0..2 x 4 channel chunks) of 64+52 rows x 16 B.  Plane group kw is
+// the x tile shifted by kw rows (3 TMA loads of the same rows), so the three taps of one
+// kernel row form ONE N = 96 operand and a kernel-row shift kh*26 is a start-address offset:
+// 12 MMAs of 128x96x16 per k-block instead of 36 of 128x32x16 (3x fewer A-operand reads).
+constexpr int kWgSlabRows = 64 + 52;                 // 116
+constexpr int kWgStages = 5;
 constexpr int kWgATile = 128 * 64 * 2;               // 16 KB (second 8 KB stays zero)
-constexpr int kWgSlab = kWgSlabRows * 32 * 2;        // 7552 B
-constexpr int kWgSlabPad = 8192;
+constexpr int kWgPlaneGroup = kWgSlabRows * 32 * 2;  // one kw group: 4 planes = 7424 B
+constexpr int kWgSlab = 3 * kWgPlaneGroup;           // 22272 B
+constexpr int kWgSlabPad = 22528;
 constexpr int kWgStage = kWgATile + kWgSlabPad;
 constexpr size_t kWgSmem = static_cast<size_t>(kWgStages) * kWgStage + 1024 + 256;
 
 struct WgradArgs {
   int kblocks_per_client;  // ceil(R / 64)
   int ctas_per_client;
-  int shift[kTaps];
+  int shift[kTaps];        // [kh] = kh * width (entries 0..2 used)
+  int kw_step;             // row shift between kw plane groups (1)
   float* grad;             // first client's [64][32][3][3] block inside the gradient slab
   long long grad_gs;
   int* status;
@@ -284,12 +342,15 @@ __global__ void __launch_bounds__(256, 1)
         mbar_expect_tx(&full_bar[s], kWgATile / 2 + kWgSlab);
         const int q0 = (kb_lo + i) * 64;
         tma_load_3d(stage, &map_dy, &full_bar[s], 0, q0, g);               // [64 co x 64 rows]
-        tma_load_4d(stage + kWgATile, &map_x, &full_bar[s], 0, q0, 0, g);  // 118-row slab
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw)                                     // x rows shifted by kw
+          tma_load_4d(stage + kWgATile + kw * kWgPlaneGroup, &map_x, &full_bar[s], 0,
+                      q0 + kw * args.kw_step, 0, g);
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, 32, 1u, 1u);
+      constexpr uint32_t idesc = make_idesc_bf16(128, 96, 1u, 1u);
       bool ok = true;
       for (int i = 0; i < n_kb && ok; ++i) {
         const int s = i % kWgStages;
@@ -299,15 +360,16 @@ __global__ void __launch_bounds__(256, 1)
         const uint32_t a_addr = smem_u32(smem + s * kWgStage);
         const uint32_t slab = a_addr + kWgATile;
 #pragma unroll
-        for (int t = 0; t < kTaps; ++t) {
+        for (int kh = 0; kh < 3; ++kh) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             // A: MN-major SW128, atoms [64 rows x 128 B] 8 KB apart, 16 k-rows per step
             const uint64_t da = make_smem_desc(a_addr + kk * (16 * 128), 64 * 128, 8 * 128, 2);
-            // B: MN-major interleaved: 8-k-row groups 128 B apart, ci chunks one slab plane apart
-            const uint64_t db = make_smem_desc(slab + (args.shift[t] + kk * 16) * 16, 128,
+            // B: MN-major interleaved, N = 96 = 12 planes one plane pitch apart; 8-k-row
+            // groups 128 B apart; kernel row kh = +kh*width rows
+            const uint64_t db = make_smem_desc(slab + (args.shift[kh] + kk * 16) * 16, 128,
                                                kWgSlabRows * 16, 0);
-            umma_f16(tmem_base + t * 32, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+            umma_f16(tmem_base + kh * 96, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
           }
         }
         umma_commit(&empty_bar[s]);
@@ -325,11 +387,11 @@ __global__ void __launch_bounds__(256, 1)
     float* gout = args.grad + static_cast<long long>(g) * args.grad_gs;
     if (sub < 2) {  // rows 64..127 are padding
 #pragma unroll 1
-      for (int t = 0; t < kTaps; ++t) {
+      for (int t = 0; t < kTaps; ++t) {   // accumulator kh = t/3, columns (t%3)*32 .. +31
 #pragma unroll
         for (int c0 = 0; c0 < 32; c0 += 16) {
           uint32_t r[16];
-          tmem_ld_32x32b_x16(lane_addr + t * 32 + c0, r);
+          tmem_ld_32x32b_x16(lane_addr + (t / 3) * 96 + (t % 3) * 32 + c0, r);
           tmem_ld_wait();
           if (ok && n_kb > 0) {
 #pragma unroll
@@ -429,9 +491,36 @@ static int weight_map(const void* ptr, long long groups, long long group_stride,
   return 0;
 }
 
+// 3-D output map over bf16 [C, rows, bn]: box [bn, 32, 1], swizzle = row bytes (128 / 64)
+static int out_map(const void* ptr, long long rows, long long groups, long long group_stride,
+                   int bn, CUtensorMap* out) {
+  ConvKey key{ptr, rows, groups, group_stride, -3, bn};
+  std::lock_guard<std::mutex> lock(g_conv_mu);
+  auto it = g_conv_maps.find(key);
+  if (it != g_conv_maps.end()) { *out = it->second; return 0; }
+  EncodeFn enc = conv_encode_fn();
+  if (!enc) return fail(NFB_ESTATE, "tc_conv: cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(bn), static_cast<cuuint64_t>(rows),
+                        static_cast<cuuint64_t>(groups)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(bn) * 2,
+                           static_cast<cuuint64_t>(group_stride) * 2};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(bn), 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   bn == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(NFB_EINVAL, "tc_conv: output tensor map rejected (CUresult %d)", static_cast<int>(r));
+  g_conv_maps[key] = m;
+  *out = m;
+  return 0;
+}
+
 template <int MODE>
-static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, int ctas, const ConvArgs& a,
-                       cudaStream_t st) {
+static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mo,
+                       int ctas, const ConvArgs& a, cudaStream_t st) {
   using C = ConvCfg<MODE>;
   auto kern = tc_conv_kernel<MODE>;
   static bool attr_set = false;
@@ -442,7 +531,7 @@ static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, int ctas, c
       return fail(static_cast<int>(e), "tc_conv: smem attribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<ctas, 256, C::SMEM, st>>>(ma, mw, a);
+  kern<<<ctas, 128 + 32 * kEpiWarps, C::SMEM, st>>>(ma, mw, mo, a);
   return launch_status("tc_conv");
 }
 
@@ -470,6 +559,9 @@ extern "C" int nfb_tc_conv3x3(int mode, const void* a, long long rows, long long
   if (rc) return rc;
   rc = weight_map(w, clients, w_group_stride, &mw);
   if (rc) return rc;
+  CUtensorMap mo;
+  rc = out_map(out, rows, clients, out_group_stride, mode == 0 ? 64 : 32, &mo);
+  if (rc) return rc;
   ConvArgs args{};
   args.tiles_per_client = static_cast<int>((rows + 127) / 128);
   int per_client = sm_count() / clients;
@@ -488,9 +580,14 @@ extern "C" int nfb_tc_conv3x3(int mode, const void* a, long long rows, long long
   args.bias_gs = bias_group_stride;
   args.mask = static_cast<const __nv_bfloat16*>(mask);
   args.status = status;
+  {
+    const char* dbg = getenv("NFB_CONV_DEBUG");
+    args.debug = dbg ? atoi(dbg) : 0;
+  }
   const int ctas = clients * per_client;
   cudaStream_t st = as_stream(stream);
-  return mode == 0 ? launch_conv<0>(ma, mw, ctas, args, st) : launch_conv<1>(ma, mw, ctas, args, st);
+  return mode == 0 ? launch_conv<0>(ma, mw, mo, ctas, args, st)
+                   : launch_conv<1>(ma, mw, mo, ctas, args, st);
 }
 
 // Weight gradient: grad[c][co][ci][t] += sum_q dy[c,q,co] * x[c,q+s_t,ci]  (fp32 atomics; the
@@ -503,7 +600,7 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
   using namespace nfb::tc;
   NFB_REQUIRE(dy && x && grad && status, NFB_EINVAL, "tc_conv3x3_wgrad: null pointer");
   NFB_REQUIRE(clients >= 1 && rows >= 1, NFB_EINVAL, "tc_conv3x3_wgrad: bad sizes");
-  NFB_REQUIRE(2 * width + 2 <= kHalo, NFB_ERANGE, "tc_conv3x3_wgrad: grid width %d too large", width);
+  NFB_REQUIRE(2 * width <= 52, NFB_ERANGE, "tc_conv3x3_wgrad: grid width %d too large", width);
   CUtensorMap mdy, mx;
   {
     // dy as MN-major operand: 3-D map (64 co, rows, clients), box [64, 64, 1], 128-B swizzle
@@ -536,8 +633,8 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
   if (per_client < 1) per_client = 1;
   if (per_client > a.kblocks_per_client) per_client = a.kblocks_per_client;
   a.ctas_per_client = per_client;
-  for (int kh = 0; kh < 3; ++kh)
-    for (int kw = 0; kw < 3; ++kw) a.shift[kh * 3 + kw] = kh * width + kw;
+  for (int kh = 0; kh < 3; ++kh) a.shift[kh] = kh * width;
+  a.kw_step = 1;
   a.grad = grad;
   a.grad_gs = grad_group_stride;
   a.status = status;
