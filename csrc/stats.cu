@@ -10,6 +10,8 @@
 // buffer stays valid ("arrived[] all zero") across calls with different shapes:
 //   cap = bytes / (4 + SLICES*8) rows ;  unsigned arrived[cap] | float partial[cap][SLICES]
 //   | int bad[cap][SLICES].   Always pass the same (pointer, size) pair for one buffer.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace nfb {
@@ -233,5 +235,101 @@ extern "C" int nfb_segment_sumsq(const void* x, int x_dtype, int64_t K, int64_t 
     segment_sumsq_kernel<T><<<grid, kThreads, 0, st>>>(static_cast<const T*>(x), row_stride,
                                                        segs, S, out, s);
     return launch_status("segment_sumsq");
+  });
+}
+
+// -------------------------------------------------------------------------------------
+// nfb_update_stats_static: nfb_update_stats for callers that cannot allocate.
+//
+// Some hosts of this library have no way to obtain device memory of their own: a plugin
+// that is handed input/output buffers by its framework and is forbidden to call the
+// allocator, a real-time or safety-reviewed service whose memory is fixed at start-up, a
+// process running after its pool has been sealed, or an error/out-of-memory path that must
+// still be able to screen an update.  For them the reduction scratch lives here, inside the
+// library image, as a fixed array in device memory.
+//
+//  * Limit: K <= NFB_STATS_STATIC_MAX_ROWS (1024) rows per call; larger K is rejected with
+//    NFB_ERANGE.  The array costs 260 KiB of device memory on EVERY GPU that loads the
+//    library, from load until the process exits.
+//  * In host code the name of a __device__ array is only a stand-in, not a device pointer;
+//    handing it to a kernel faults, or on machines where the GPU can address host memory
+//    silently uses the wrong storage.  The real address is fetched with
+//    cudaGetSymbolAddress once per device, with that device current, and cached.
+//  * The FIRST call on a device performs that look-up.  Make that first call outside any
+//    CUDA stream capture (e.g. once at start-up); later calls only enqueue work.
+//  * One array per GPU is shared by every call.  It keeps whatever the previous call left
+//    there, so each call first clears the arrival counters it is about to use (an async
+//    memset on the caller's stream).  Two calls that may overlap on the GPU — different
+//    streams, or different host threads without ordering — race on it; serialise them.
+//  * Calls no cudaMalloc / cudaFree / any allocating routine.
+// -------------------------------------------------------------------------------------
+namespace nfb {
+
+constexpr int64_t kStaticMaxRows = 1024;
+constexpr size_t kStaticScratchBytes =
+    static_cast<size_t>(kStaticMaxRows) * (sizeof(unsigned) + kSlices * (sizeof(float) + sizeof(int)));
+
+static __device__ __align__(256) unsigned char g_stats_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_static_scratch_mu;
+
+// Device address of the static scratch for the CURRENT device (resolved once per device).
+static int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess)
+    return fail(static_cast<int>(e), "update_stats_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(NFB_ERANGE, "update_stats_static: device ordinal %d not supported (max %d)", dev,
+                kMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_stats_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      cudaGetLastError();
+      return fail(e != cudaSuccess ? static_cast<int>(e) : NFB_ESTATE,
+                  "update_stats_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    }
+    g_static_scratch_ptr[dev] = p;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+
+}  // namespace nfb
+
+extern "C" int nfb_stats_static_max_rows(void) { return static_cast<int>(nfb::kStaticMaxRows); }
+
+extern "C" int nfb_update_stats_static(const void* x, int x_dtype, int64_t K, int64_t N,
+                                       int64_t row_stride, float* sumsq, int* nonfinite,
+                                       void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(x && sumsq, NFB_EINVAL, "update_stats_static: null pointer");
+  NFB_REQUIRE(K >= 1, NFB_EINVAL, "update_stats_static: K must be positive");
+  NFB_REQUIRE(K <= kStaticMaxRows, NFB_ERANGE,
+              "update_stats_static: K=%lld exceeds the built-in scratch (max %lld rows); use "
+              "nfb_update_stats with caller-provided scratch",
+              static_cast<long long>(K), static_cast<long long>(kStaticMaxRows));
+  NFB_REQUIRE(N >= 0 && row_stride >= N, NFB_EINVAL, "update_stats_static: bad N/row_stride");
+  void* scratch = nullptr;
+  const int rc = static_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  cudaStream_t st = as_stream(stream);
+  const Scratch s = carve(scratch, kStaticScratchBytes);
+  // the array is shared and keeps the last call's contents: the counters must start at zero
+  cudaError_t e = cudaMemsetAsync(s.arrived, 0, static_cast<size_t>(K) * sizeof(unsigned), st);
+  if (e != cudaSuccess)
+    return fail(static_cast<int>(e), "update_stats_static: clearing counters: %s",
+                cudaGetErrorString(e));
+  const dim3 grid(kSlices, static_cast<unsigned>(K));
+  return dispatch_dtype(x_dtype, [&](auto tag) {
+    using T = decltype(tag);
+    rows_sumsq_kernel<T><<<grid, kThreads, 0, st>>>(static_cast<const T*>(x), N, row_stride, sumsq,
+                                                    nonfinite, s);
+    return launch_status("update_stats_static");
   });
 }

@@ -68,6 +68,18 @@ int nfb_update_stats(const void* x, int x_dtype, int64_t K, int64_t N, int64_t r
                      float* sumsq, int* nonfinite, void* scratch, size_t scratch_bytes,
                      void* stream);
 
+/* Same result as nfb_update_stats for callers that cannot allocate device memory (plugins
+ * that only receive buffers, fixed-memory services, code running after its pool is sealed or
+ * on an out-of-memory path).  No counterpart in the reference.  The scratch is a 260 KiB
+ * array built into the library image (held by every GPU that loads the library until exit),
+ * so K is limited to nfb_stats_static_max_rows() = 1024; larger K returns NFB_ERANGE.  The
+ * first call on each device looks up the array's device address — make it before any stream
+ * capture.  All calls on a GPU share the array: calls that can overlap on the GPU race, so
+ * keep them ordered.  Allocates nothing.                                                    */
+int nfb_stats_static_max_rows(void);
+int nfb_update_stats_static(const void* x, int x_dtype, int64_t K, int64_t N, int64_t row_stride,
+                            float* sumsq, int* nonfinite, void* stream);
+
 /* Per-tensor sum of squares over a table of T device pointers/lengths (all one dtype).
  * ptrs/lens are device arrays.  Replaces clip_grad_norm_'s norm
  * (nanofed/trainer/private.py:62-63) and per-tensor norms of validation.py:93-95.  */
