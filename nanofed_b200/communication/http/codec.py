@@ -78,9 +78,7 @@ def encode_frame(envelope: Mapping[str, Any], state: Mapping[str, torch.Tensor] 
         t = value.detach().contiguous().cpu() if isinstance(value, torch.Tensor) else torch.as_tensor(value)
         if t.dtype not in _DTYPE_NAMES:
             t = t.to(torch.float32)
-        raw = t.view(torch.uint8).numpy().tobytes() if t.numel() else b""
-        if t.dim() == 0 and t.numel():
-            raw = t.reshape(1).view(torch.uint8).numpy().tobytes()
+        raw = t.reshape(-1).view(torch.uint8).numpy().tobytes() if t.numel() else b""
         pad = (-cursor) % _ALIGN
         if pad:
             chunks.append(b"\0" * pad)

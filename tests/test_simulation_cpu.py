@@ -1,0 +1,60 @@
+"""FedSimulation on CPU (autograd engine, oracle ops) incl. Coordinator integration and DP."""
+
+import asyncio
+import json
+
+import torch
+
+from nanofed_b200 import Coordinator, CoordinatorConfig, FedAvgAggregator, ModelManager
+from nanofed_b200.models import MNISTModel
+from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+from nanofed_b200.privacy import PrivacyConfig
+
+
+def _cfg(**kw):
+    base = dict(model="mnist_cnn", clients_per_gpu=3, samples_per_client=16, batch_size=8,
+                compute_dtype="fp32", engine="autograd", device="cpu", sample_counts=[16, 8, 4])
+    base.update(kw)
+    return CohortConfig(**base)
+
+
+def test_round_equals_weighted_mean_of_client_models():
+    sim = FedSimulation(_cfg())
+    out = sim.run_round()
+    counts = torch.tensor([16.0, 8, 4])
+    want = (counts / counts.sum()).view(-1, 1).mul(sim.arena.slots).sum(0)
+    torch.testing.assert_close(sim.arena.master, want, rtol=1e-5, atol=1e-6)
+    assert out.num_clients == 3 and abs(sum(c["weight"] for c in out.client_metrics) - 1) < 1e-9
+    assert set(out.agg_metrics) == {"loss", "accuracy", "samples_processed"}
+    state = sim.global_state()
+    MNISTModel().load_state_dict(state)                      # reference-shaped state_dict
+
+
+def test_dp_round_clips_and_accounts():
+    sim = FedSimulation(_cfg(privacy=PrivacyConfig(epsilon=10.0, noise_multiplier=0.5,
+                                                   max_gradient_norm=1.0)))
+    out = sim.run_round()
+    assert out.agg_metrics["privacy_epsilon"] > 0
+    # every client row has norm >> 1, so the aggregate of clipped rows has norm <= ~1 (+ noise)
+    assert float(sim.arena.sumsq.sqrt().min()) > 1.0
+    noise_free = float(sim.arena.master.norm())
+    assert noise_free < 1.0 + 0.5 * 1.0 / 3 * (sim.layout.total ** 0.5) * 1.2
+
+
+def test_coordinator_drives_simulation_and_writes_reference_layout(tmp_path):
+    sim = FedSimulation(_cfg())
+    model = MNISTModel()
+    coord = Coordinator(ModelManager(model), FedAvgAggregator(), None,
+                        CoordinatorConfig(num_rounds=2, min_clients=3, min_completion_rate=1.0,
+                                          round_timeout=30, base_dir=tmp_path), engine=sim)
+
+    async def run():
+        return [m async for m in coord.start_training()]
+
+    metrics = asyncio.run(run())
+    assert [m.round_id for m in metrics] == [0, 1] and metrics[0].num_clients == 3
+    assert len(list((tmp_path / "models" / "models").glob("*.pt"))) == 3
+    rec = json.loads((tmp_path / "metrics" / "metrics_round_1.json").read_text())
+    assert rec["status"] == "COMPLETED" and len(rec["client_metrics"]) == 3
+    torch.testing.assert_close(model.fc1.weight,
+                               sim.layout.views(sim.arena.master)["fc1.weight"])
