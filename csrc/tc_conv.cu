@@ -63,6 +63,9 @@ __device__ __forceinline__ void bulk_wait_read0() {
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
+// Measured alternatives (B200, 32 clients x 64 images): 1 CTA/SM with 8 epilogue warps:
+// fwd 77 us / dgrad 109 us; 2 CTAs/SM with 4 epilogue warps each: 84 / 120 us.  Both kernels
+// move ~300-430 MB per launch (3.9 TB/s): they are DRAM-bound, not latency-bound.
 constexpr int kEpiWarps = 8;   // two epilogue warpgroups, alternating tiles / accumulators
 
 template <int MODE>

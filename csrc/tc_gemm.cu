@@ -18,6 +18,8 @@
 //
 // Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator,
 // 4..7 = epilogue (warp w owns TMEM lanes 32*(w-4) .. +31).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -49,6 +51,7 @@ struct GemmArgs {
   const __nv_bfloat16* mask_src;  // optional: out = 0 where mask_src[same index] <= 0
   int m_valid, n_valid;
   int vec_store;     // n contiguous (out_ns == 1), non-atomic, 16-byte aligned rows
+  int tma_store;     // stage 32-row x 128-byte chunks in smem and write them with TMA (map_o)
   int* status;       // set to 1 if a pipeline wait timed out
 };
 
@@ -62,7 +65,8 @@ struct Cfg {
   static constexpr int TMEM_NEED = BN * TPS;
   static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64
                                    : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
-  static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + 1024 /*align*/ + 256;
+  static constexpr int STAGING = 4 * 4096;                   // 4 epilogue warps x [32 rows x 128 B]
+  static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + STAGING + 1024 /*align*/ + 256;
   static_assert(A_MN || A_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
   static_assert(B_MN || B_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
   static_assert(A_TILE % 1024 == 0 && B_TILE % 1024 == 0, "tiles must keep 1024-B alignment");
@@ -95,15 +99,18 @@ __device__ __forceinline__ uint64_t operand_desc(uint32_t tile_addr, int kk) {
   }
 }
 
-template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES>
-__global__ void __launch_bounds__(256, 1)
+template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES,
+          int MINB = 1>
+__global__ void __launch_bounds__(256, MINB)
     tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
-                   const __grid_constant__ CUtensorMap map_b, const GemmArgs args) {
+                   const __grid_constant__ CUtensorMap map_b,
+                   const __grid_constant__ CUtensorMap map_o, const GemmArgs args) {
   using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE);
+  uint8_t* staging = smem + STAGES * C::STAGE;          // 1024-aligned (stage sizes are)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + C::STAGING);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* acc_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
@@ -202,6 +209,54 @@ __global__ void __launch_bounds__(256, 1)
     tc_fence_after();
     const bool row_ok = ok && n_iters > 0 && m < args.m_valid;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
+    if (args.tma_store) {
+      // Row-per-thread global stores touch 32 different lines per instruction; instead each
+      // warp stages [32 rows x 128 B] chunks in swizzled shared memory (conflict-free 16-byte
+      // stores) and a bulk tensor store writes them as whole lines.
+      uint8_t* my_stage = staging + sub * 4096;
+      const int cols = args.out_bf16 ? 64 : 32;           // columns per 128-byte chunk
+      const bool live = ok && n_iters > 0;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += cols) {
+        if (n0 + c0 >= args.n_valid) break;
+        uint32_t r[64];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (q * 16 < cols) tmem_ld_32x32b_x16(lane_addr + c0 + q * 16, r + q * 16);
+        tmem_ld_wait();
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+        float v[64];
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+          if (j < cols) {
+            v[j] = __uint_as_float(r[j]);
+            if (args.bias && split == 0)
+              v[j] += args.bias[static_cast<long long>(g) * args.bias_gs +
+                                (args.bias_on_m ? m : (n0 + c0 + j))];
+            if (args.relu) v[j] = fmaxf(v[j], 0.f);
+          }
+        }
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {                    // eight 16-byte pieces per row
+          uint4 piece;
+          if (args.out_bf16) piece = pack<__nv_bfloat16>(v + 8 * p);
+          else piece = pack<float>(v + 4 * p);
+          st_vec(my_stage + lane * 128 + ((p ^ (lane & 7)) * 16), piece);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0 && live) {
+          asm volatile(
+              "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                  &map_o),
+              "r"(smem_u32(my_stage)), "r"(n0 + c0), "r"(m0 + sub * 32), "r"(g)
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    } else
 #pragma unroll 1
     for (int t = 0; t < TPS; ++t) {
 #pragma unroll 1
@@ -346,16 +401,45 @@ static int get_map(const Operand& op, int box_inner, int box_rows, int swz_bytes
   return 0;
 }
 
-template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES>
+// Output map for the TMA-store epilogue: [groups][m rows][n cols], n contiguous.
+static int get_out_map(void* ptr, long long n, long long m, long long groups, long long ms,
+                       long long gs, bool bf16, CUtensorMap* out) {
+  const int esz = bf16 ? 2 : 4;
+  MapKey key{ptr, n, m, groups, ms, gs, bf16 ? -64 : -32, 32, 128};
+  std::lock_guard<std::mutex> lock(g_maps_mu);
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) { *out = it->second; return 0; }
+  EncodeFn enc = encode_fn();
+  if (!enc) return fail(NFB_ESTATE, "tc_gemm: cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(n), static_cast<cuuint64_t>(m),
+                        static_cast<cuuint64_t>(groups)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ms) * esz, static_cast<cuuint64_t>(gs) * esz};
+  if (groups == 1) strides[1] = static_cast<cuuint64_t>(m) * strides[0];
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(bf16 ? 64 : 32), 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap mo;
+  CUresult r = enc(&mo, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                   3, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(NFB_EINVAL, "tc_gemm: output tensor map rejected (%d)",
+                                     static_cast<int>(r));
+  g_maps[key] = mo;
+  *out = mo;
+  return 0;
+}
+
+template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES,
+          int MINB = 1>
 static int launch(const Operand& a, const Operand& b, int m_tiles, int n_tiles, int groups,
-                  const GemmArgs& args, cudaStream_t st) {
+                  GemmArgs args, cudaStream_t st) {
   using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mo;
   int rc = A_MN ? get_map(a, C::A_ATOM, BK, A_SWZ, &ma) : get_map(a, BK, BM, A_SWZ, &ma);
   if (rc) return rc;
   rc = B_MN ? get_map(b, C::B_ATOM, BK, B_SWZ, &mb) : get_map(b, BK, BN, B_SWZ, &mb);
   if (rc) return rc;
-  auto kern = tc_gemm_kernel<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
+  auto kern = tc_gemm_kernel<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES, MINB>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -364,8 +448,18 @@ static int launch(const Operand& a, const Operand& b, int m_tiles, int n_tiles, 
                                       cudaGetErrorString(e));
     attr_set = true;
   }
+  // TMA-store epilogue when the output is a plain row-major [m][n] tile with 128-byte chunks
+  const int chunk_cols = args.out_bf16 ? 64 : 32;
+  args.tma_store = (args.vec_store && TPS == 1 && args.k_split == 1 && !args.mask_src &&
+                    BN % chunk_cols == 0 && getenv("NFB_GEMM_NO_TMA_STORE") == nullptr) ? 1 : 0;
+  mo = ma;
+  if (args.tma_store) {
+    rc = get_out_map(args.out, args.n_valid, args.m_valid, groups, args.out_ms, args.out_gs,
+                     args.out_bf16 != 0, &mo);
+    if (rc) return rc;
+  }
   dim3 grid(m_tiles, n_tiles, groups * args.k_split);
-  kern<<<grid, 256, C::SMEM, st>>>(ma, mb, args);
+  kern<<<grid, 256, C::SMEM, st>>>(ma, mb, mo, args);
   return launch_status("tc_gemm");
 }
 
@@ -390,7 +484,8 @@ typedef struct {
   int m_valid, n_valid;
 } nfb_tc_epilogue;
 
-// variant: 0 conv_fwd, 1 conv_dgrad, 2 conv_wgrad, 3 fc_fwd, 4 fc_dgrad, 5 fc_wgrad
+// variant: 0 conv_fwd, 1 conv_dgrad, 2 conv_wgrad, 3 fc_fwd, 4 fc_dgrad, 5 fc_wgrad,
+//          6 fc_dgrad with M = batch (row-major bf16 output, TMA-store epilogue)
 int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, int m_tiles,
                 int n_tiles, int groups, int taps, int inner, int k_split, const int* tap_table,
                 const nfb_tc_epilogue* epi, int* status, void* stream) {
@@ -435,7 +530,11 @@ int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, i
       return launch<true, 128, true, 64, 64, 32, 9, 4>(a, b, m_tiles, n_tiles, groups, g, st);
     case 3: return launch<false, 128, false, 128, 64, 64, 1, 6>(a, b, m_tiles, n_tiles, groups, g, st);
     case 4: return launch<true, 128, false, 128, 64, 64, 1, 4>(a, b, m_tiles, n_tiles, groups, g, st);
-    case 5: return launch<true, 128, true, 128, 64, 128, 1, 4>(a, b, m_tiles, n_tiles, groups, g, st);
+    // variants 5/6 have only 1-2 k-blocks per tile: every CTA is one latency-bound chain
+    // (setup -> TMA -> MMA -> epilogue), so two CTAs per SM (2 stages, <=128 registers) are what
+    // overlaps them; measured 107 us at 1 CTA/SM for the 128x9216 weight gradient.
+    case 5: return launch<true, 128, true, 128, 64, 128, 1, 2, 2>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 6: return launch<false, 128, true, 128, 64, 128, 1, 2, 2>(a, b, m_tiles, n_tiles, groups, g, st);
     default: return fail(NFB_EINVAL, "tc_gemm: unknown variant %d", variant);
   }
 }

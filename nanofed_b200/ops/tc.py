@@ -20,9 +20,10 @@ import torch
 
 from . import native
 
-CONV_FWD, CONV_DGRAD, CONV_WGRAD, FC_FWD, FC_DGRAD, FC_WGRAD = range(6)
+CONV_FWD, CONV_DGRAD, CONV_WGRAD, FC_FWD, FC_DGRAD, FC_WGRAD, FC_DGRAD_ROWS = range(7)
 _BM = 128
-_BN = {CONV_FWD: 64, CONV_DGRAD: 32, CONV_WGRAD: 32, FC_FWD: 64, FC_DGRAD: 64, FC_WGRAD: 128}
+_BN = {CONV_FWD: 64, CONV_DGRAD: 32, CONV_WGRAD: 32, FC_FWD: 64, FC_DGRAD: 64, FC_WGRAD: 128,
+       FC_DGRAD_ROWS: 128}
 _BK = {CONV_FWD: 32, CONV_DGRAD: 64, CONV_WGRAD: 64, FC_FWD: 64, FC_DGRAD: 64, FC_WGRAD: 64}
 
 
@@ -230,6 +231,11 @@ def linear_fwd(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, k_split: int
 def linear_dgrad(w: torch.Tensor, dy: torch.Tensor, out: torch.Tensor) -> None:
     """``out[c, b, i] = Σ_j dy[c, b, j]·w[c, j, i]`` (bf16)."""
     j, i = w.shape[1], w.shape[2]
+    if dy.shape[1] <= 128 and out.is_contiguous():
+        # M = batch rows (zero-padded to 128 by TMA), N = i: row-major output, TMA-store epilogue
+        gemm(FC_DGRAD_ROWS, dy, w, out, m=dy.shape[1], n=i,
+             strides=(out.stride(0), out.stride(1), 1, 0), inner=j // 64)
+        return
     gemm(FC_DGRAD, w, dy, out, m=i, n=dy.shape[1], strides=(out.stride(0), 1, out.stride(1), 0),
          inner=j // 64)
 
