@@ -267,38 +267,40 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
 
 // -------------------------------------------------------------------------------------
 // Weight gradient, persistent form: one CTA per (client, contiguous range of 64-row
-// k-blocks).  D_t[co, ci] += sum_q dy[q, co] * x[q + s_t, ci] for the 9 taps, held in 9 TMEM
-// accumulators (9 x 32 columns) for the CTA's whole k-range; per k-block ONE dy tile
-// (MN-major, 128-B swizzle) and ONE x slab of 64+54 rows (interleaved layout, so the 9 taps
-// are 9 descriptors into it).  M is padded 64 -> 128 with a zeroed second swizzle atom that
-// TMA never touches.  Epilogue: fp32 atomics into the OIHW gradient inside the flat slab.
+// k-blocks).  For kernel row kh:   D_kh[(kw,ci), co] += sum_q x[q + kh*W + kw, ci] * dy[q, co]
+//   A (M = 96 -> 128): x, MN-major, 64-byte swizzle.  The three kw taps are three N... M atoms of
+//     32 channels: the SAME 116 rows loaded three times, shifted by kw rows (three TMA boxes of
+//     64-byte rows), so one descriptor covers kw = 0..2 and the kernel row is a start-address
+//     offset of kh*W rows.  (Shifting a swizzled tile by whole rows is legal because the
+//     hardware swizzle is a function of the absolute shared-memory address — verified on B200:
+//     a 128-B-swizzled slab read at start + s*128 B gives exact results with base_offset = 0.)
+//   B (N = 64): dy, MN-major, 128-byte swizzle, one atom.
+// 3 accumulators x 64 TMEM columns live for the CTA's whole k-range; 12 MMAs of 128x64x16 per
+// k-block.  History (B200, 32 clients x 64 images): generic kernel 256 us -> x as 16-byte-piece
+// interleaved slabs 166 us (TMA piece rate ~1.4/ns was the limit) -> this form.
+// Epilogue: fp32 atomics into the OIHW gradient inside the flat slab.
 // -------------------------------------------------------------------------------------
-// B slab: 12 planes (kw = 0..2 x 4 channel chunks) of 64+52 rows x 16 B.  Plane group kw is
-// the x tile shifted by kw rows (3 TMA loads of the same rows), so the three taps of one
-// kernel row form ONE N = 96 operand and a kernel-row shift kh*26 is a start-address offset:
-// 12 MMAs of 128x96x16 per k-block instead of 36 of 128x32x16 (3x fewer A-operand reads).
-constexpr int kWgSlabRows = 64 + 52;                 // 116
-constexpr int kWgStages = 5;
-constexpr int kWgATile = 128 * 64 * 2;               // 16 KB (second 8 KB stays zero)
-constexpr int kWgPlaneGroup = kWgSlabRows * 32 * 2;  // one kw group: 4 planes = 7424 B
-constexpr int kWgSlab = 3 * kWgPlaneGroup;           // 22272 B
-constexpr int kWgSlabPad = 22528;
-constexpr int kWgStage = kWgATile + kWgSlabPad;
+constexpr int kWgRows = 64 + 52;                     // k-block rows + 2 kernel rows of halo
+constexpr int kWgStages = 4;
+constexpr int kWgGroup = 7680;                       // one kw group: 116 rows x 64 B, padded to 512
+constexpr int kWgA = 4 * kWgGroup;                   // 3 groups + 1 pad group (M 96 -> 128)
+constexpr int kWgB = 64 * 128;                       // dy tile [64 rows x 128 B]
+constexpr int kWgStage = kWgA + kWgB;                // 38912
 constexpr size_t kWgSmem = static_cast<size_t>(kWgStages) * kWgStage + 1024 + 256;
 
 struct WgradArgs {
   int kblocks_per_client;  // ceil(R / 64)
   int ctas_per_client;
   int shift[kTaps];        // [kh] = kh * width (entries 0..2 used)
-  int kw_step;             // row shift between kw plane groups (1)
   float* grad;             // first client's [64][32][3][3] block inside the gradient slab
   long long grad_gs;
   int* status;
+  int debug;               // probes (env NFB_CONV_DEBUG): 1 = reuse first stages, 2 = 1/12 MMAs
 };
 
 __global__ void __launch_bounds__(256, 1)
     tc_conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy,  // 3-D, box [64, 64, 1], SW128
-                         const __grid_constant__ CUtensorMap map_x,   // 4-D slab, box (8,118,4,1)
+                         const __grid_constant__ CUtensorMap map_x,   // 3-D, box [32, 116, 1], SW64
                          const WgradArgs args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -316,10 +318,11 @@ __global__ void __launch_bounds__(256, 1)
   const int kb_hi = min(kb_lo + per, args.kblocks_per_client);
   const int n_kb = max(kb_hi - kb_lo, 0);
 
-  // zero the padding half (co 64..127) of every A stage once
+  // the pad group (M rows 96..127) is never written by TMA: zero it once so the unused
+  // accumulator rows stay finite
   for (int s = 0; s < kWgStages; ++s) {
-    uint4* z = reinterpret_cast<uint4*>(smem + s * kWgStage + kWgATile / 2);
-    for (int i = threadIdx.x; i < kWgATile / 2 / 16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+    uint4* z = reinterpret_cast<uint4*>(smem + s * kWgStage + 3 * kWgGroup);
+    for (int i = threadIdx.x; i < kWgGroup / 16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
   }
   fence_proxy_async();
   if (threadIdx.x == 0) {
@@ -329,7 +332,7 @@ __global__ void __launch_bounds__(256, 1)
     mbar_init(acc_bar, 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  if (warp == 2) tmem_alloc<256>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -342,18 +345,18 @@ __global__ void __launch_bounds__(256, 1)
         const uint32_t ph = (i / kWgStages) & 1;
         if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; break; }
         uint8_t* stage = smem + s * kWgStage;
-        mbar_expect_tx(&full_bar[s], kWgATile / 2 + kWgSlab);
+        if ((args.debug & 1) && i >= kWgStages) { mbar_arrive(&full_bar[s]); continue; }
         const int q0 = (kb_lo + i) * 64;
-        tma_load_3d(stage, &map_dy, &full_bar[s], 0, q0, g);               // [64 co x 64 rows]
+        mbar_expect_tx(&full_bar[s], kWgB + 3 * kWgRows * 64);
+        tma_load_3d(stage + kWgA, &map_dy, &full_bar[s], 0, q0, g);          // dy [64 co x 64 rows]
 #pragma unroll
-        for (int kw = 0; kw < 3; ++kw)                                     // x rows shifted by kw
-          tma_load_4d(stage + kWgATile + kw * kWgPlaneGroup, &map_x, &full_bar[s], 0,
-                      q0 + kw * args.kw_step, 0, g);
+        for (int kw = 0; kw < 3; ++kw)                                       // x rows shifted by kw
+          tma_load_3d(stage + kw * kWgGroup, &map_x, &full_bar[s], 0, q0 + kw, g);
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, 96, 1u, 1u);
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1u, 1u);
       bool ok = true;
       for (int i = 0; i < n_kb && ok; ++i) {
         const int s = i % kWgStages;
@@ -361,18 +364,20 @@ __global__ void __launch_bounds__(256, 1)
         if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + s * kWgStage);
-        const uint32_t slab = a_addr + kWgATile;
+        const uint32_t b_addr = a_addr + kWgA;
 #pragma unroll
         for (int kh = 0; kh < 3; ++kh) {
+          if ((args.debug & 2) && kh > 0) break;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
-            // A: MN-major SW128, atoms [64 rows x 128 B] 8 KB apart, 16 k-rows per step
-            const uint64_t da = make_smem_desc(a_addr + kk * (16 * 128), 64 * 128, 8 * 128, 2);
-            // B: MN-major interleaved, N = 96 = 12 planes one plane pitch apart; 8-k-row
-            // groups 128 B apart; kernel row kh = +kh*width rows
-            const uint64_t db = make_smem_desc(slab + (args.shift[kh] + kk * 16) * 16, 128,
-                                               kWgSlabRows * 16, 0);
-            umma_f16(tmem_base + kh * 96, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+            if ((args.debug & 2) && kk > 0) break;
+            // A: MN-major SW64; M atoms (kw groups) kWgGroup apart, 8-k-row groups 512 B apart;
+            // kernel row kh and the K step are row offsets of 64 B
+            const uint64_t da = make_smem_desc(a_addr + (args.shift[kh] + kk * 16) * 64, kWgGroup,
+                                               8 * 64, 4);
+            // B: MN-major SW128, single 64-wide atom; K step = 16 rows of 128 B
+            const uint64_t db = make_smem_desc(b_addr + kk * (16 * 128), 64 * 128, 8 * 128, 2);
+            umma_f16(tmem_base + kh * 64, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
           }
         }
         umma_commit(&empty_bar[s]);
@@ -385,29 +390,31 @@ __global__ void __launch_bounds__(256, 1)
     if (n_kb > 0) ok = mbar_wait(acc_bar, 0);
     if (!ok && lane == 0) *args.status = 1;
     tc_fence_after();
-    const int co = sub * 32 + lane;
+    const int row = sub * 32 + lane;            // (kw, ci) = (row / 32, row % 32)
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
     float* gout = args.grad + static_cast<long long>(g) * args.grad_gs;
-    if (sub < 2) {  // rows 64..127 are padding
+    if (sub < 3) {  // rows 96..127 are padding
+      const int kw = sub, ci = lane;
 #pragma unroll 1
-      for (int t = 0; t < kTaps; ++t) {   // accumulator kh = t/3, columns (t%3)*32 .. +31
+      for (int kh = 0; kh < 3; ++kh) {
 #pragma unroll
-        for (int c0 = 0; c0 < 32; c0 += 16) {
+        for (int c0 = 0; c0 < 64; c0 += 16) {
           uint32_t r[16];
-          tmem_ld_32x32b_x16(lane_addr + (t / 3) * 96 + (t % 3) * 32 + c0, r);
+          tmem_ld_32x32b_x16(lane_addr + kh * 64 + c0, r);
           tmem_ld_wait();
           if (ok && n_kb > 0) {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-              atomicAdd(gout + co * 288 + (c0 + j) * 9 + t, __uint_as_float(r[j]));
+              atomicAdd(gout + (c0 + j) * 288 + ci * 9 + kh * 3 + kw, __uint_as_float(r[j]));
           }
         }
       }
     }
+    (void)row;
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<512>(tmem_base);
+  if (warp == 2) tmem_dealloc<256>(tmem_base);
 }
 
 }  // namespace tc
@@ -628,8 +635,28 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
       g_conv_maps[key] = mdy;
     }
   }
-  int rc = slab_map(x, rows, clients, x_group_stride, 32, kWgSlabRows, &mx);
-  if (rc) return rc;
+  {
+    ConvKey key{x, rows, clients, x_group_stride, -5, kWgRows};
+    std::lock_guard<std::mutex> lock(g_conv_mu);
+    auto it = g_conv_maps.find(key);
+    if (it != g_conv_maps.end()) {
+      mx = it->second;
+    } else {
+      EncodeFn enc = conv_encode_fn();
+      if (!enc) return fail(NFB_ESTATE, "tc_conv3x3_wgrad: cuTensorMapEncodeTiled unavailable");
+      cuuint64_t dims[3] = {32, static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(clients)};
+      cuuint64_t strides[2] = {64, static_cast<cuuint64_t>(x_group_stride) * 2};
+      cuuint32_t box[3] = {32, static_cast<cuuint32_t>(kWgRows), 1};
+      cuuint32_t estr[3] = {1, 1, 1};
+      CUresult r = enc(&mx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(x), dims,
+                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                       CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS)
+        return fail(NFB_EINVAL, "tc_conv3x3_wgrad: x tensor map rejected (%d)", static_cast<int>(r));
+      g_conv_maps[key] = mx;
+    }
+  }
   WgradArgs a{};
   a.kblocks_per_client = static_cast<int>((rows + 63) / 64);
   int per_client = sm_count() / clients;
@@ -637,10 +664,13 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
   if (per_client > a.kblocks_per_client) per_client = a.kblocks_per_client;
   a.ctas_per_client = per_client;
   for (int kh = 0; kh < 3; ++kh) a.shift[kh] = kh * width;
-  a.kw_step = 1;
   a.grad = grad;
   a.grad_gs = grad_group_stride;
   a.status = status;
+  {
+    const char* dbg = getenv("NFB_CONV_DEBUG");
+    a.debug = dbg ? atoi(dbg) : 0;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(tc_conv_wgrad_kernel,

@@ -23,3 +23,7 @@ def t(fn):
 print("debug", os.environ.get("NFB_CONV_DEBUG", "0"),
       "fwd %.1f us" % t(lambda: tc.conv3x3_fwd_persistent(x, w, bias, o64, 26)),
       "dgrad %.1f us" % t(lambda: tc.conv3x3_dgrad_persistent(dy, w, o32, 26, relu_mask=x)))
+n_total = 64 * 32 * 9 + 64
+grad = torch.zeros(c, n_total, device="cuda")
+print("debug", os.environ.get("NFB_CONV_DEBUG", "0"),
+      "wgrad %.1f us" % t(lambda: tc.conv3x3_wgrad_persistent(dy, x, grad, 26, n_total)))
