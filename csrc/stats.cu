@@ -71,13 +71,14 @@ __device__ __forceinline__ void slice_sumsq(const T* __restrict__ p, int64_t len
   const uint4* vp = reinterpret_cast<const uint4*>(p + head);
   const int64_t stride = static_cast<int64_t>(kSlices) * blockDim.x;
   int64_t i = static_cast<int64_t>(slice) * blockDim.x + threadIdx.x;
-  // 4 independent 16-byte loads in flight per thread
-  for (; i + 3 * stride < nvec; i += 4 * stride) {
-    uint4 r[4];
+  // 8 independent 16-byte loads in flight per thread (few rows => few CTAs: the bytes in
+  // flight per SM must come from the unroll depth)
+  for (; i + 7 * stride < nvec; i += 8 * stride) {
+    uint4 r[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) r[u] = ld_stream(vp + i + u * stride);
+    for (int u = 0; u < 8; ++u) r[u] = ld_stream(vp + i + u * stride);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 8; ++u) {
       float f[V];
       unpack<T>(r[u], f);
 #pragma unroll

@@ -64,9 +64,25 @@ def state_to_jsonable(state: Mapping[str, Any]) -> dict[str, Any]:
     return {name: tensor_to_jsonable(v) for name, v in state.items()}
 
 
+def tensor_from_jsonable(value: Any) -> torch.Tensor:
+    """Same result as the reference's ``torch.tensor(value)`` (float lists → fp32, int lists →
+    int64, bare numbers → 0-d) but through NumPy, which parses nested lists ~4x faster."""
+    if isinstance(value, torch.Tensor):
+        return value
+    try:
+        arr = np.asarray(value)
+        if arr.dtype == np.float64:
+            arr = arr.astype(np.float32)
+        elif arr.dtype == np.object_ or arr.dtype.kind not in "fiub":
+            return torch.tensor(value)
+        return torch.from_numpy(np.ascontiguousarray(arr))
+    except (ValueError, TypeError):
+        return torch.tensor(value)
+
+
 def state_from_jsonable(payload: Mapping[str, Any]) -> dict[str, torch.Tensor]:
-    """``torch.tensor(value)`` per entry: float lists → fp32, int lists → int64."""
-    return {name: torch.tensor(v) for name, v in payload.items()}
+    """Decode the reference's list encoding: float lists → fp32, int lists → int64."""
+    return {name: tensor_from_jsonable(v) for name, v in payload.items()}
 
 
 # -- binary frame ------------------------------------------------------------------

@@ -65,7 +65,9 @@ class CoordinatorConfig:
 
 
 def _as_tensor_state(raw: dict[str, Any]) -> dict[str, torch.Tensor]:
-    return {k: (v if isinstance(v, torch.Tensor) else torch.tensor(v)) for k, v in raw.items()}
+    from nanofed_b200.communication.http.codec import tensor_from_jsonable
+
+    return {k: tensor_from_jsonable(v) for k, v in raw.items()}
 
 
 def _as_time(value: Any) -> datetime:
