@@ -224,7 +224,7 @@ def run_ours(args: argparse.Namespace) -> None:
             "vs_baseline_rounds": (1e3 / ms_per_step) / BASELINE_ROUNDS_PER_SEC,
             "dtype": args.dtype, "data": "synthetic", "impl": "ours",
             "config": {
-                "model": args.model + " (1199882 params, random init)",
+                "model": f"{args.model} ({sim.layout.num_values} state elements, random init)",
                 "global_batch": args.clients_per_gpu * args.gpus * BATCH,
                 "seq_len": None, "clients": sim.num_clients,
                 "clients_per_gpu": args.clients_per_gpu,

@@ -39,10 +39,10 @@ struct RankView {
   // peer-visible buffers (dereferenced by every rank)
   float* partial;        // [N]
   float* scal;           // [4]: sum n, sum n^2
-  unsigned* flags;       // [2*G]: barrier words written by peers
+  unsigned* flags;       // [(1 + kMaxChunks) * G]: epoch words written by peers (slot 0 = done)
   float* master;         // [N] new global model
   __nv_bfloat16* lowp;   // [N] bf16 copy (may be null)
-  unsigned long long* grid_ctr;  // [1] local grid-barrier arrival counter (monotonic)
+  unsigned* counters;    // [1 + kMaxChunks] local arrival counters (done, per-chunk), zero between calls
 };
 
 struct AllreduceArgs {
@@ -51,8 +51,10 @@ struct AllreduceArgs {
   float clip_norm, noise_std;
   const uint8_t* noise_mask;  // local copy on each rank (same content)
   uint64_t seed, group0;
-  unsigned epoch;             // barrier generation, strictly increasing per call
-  unsigned long long ctr_base;  // grid_ctr value before this call (host-tracked)
+  unsigned epoch;             // generation, strictly increasing per call
+  int producers;              // CTAs [0, producers) reduce locally, the rest reduce across ranks
+  int n_chunks;               // column chunks (<= kMaxChunks)
+  int64_t chunk_elems;        // elements per chunk (multiple of 8)
   unsigned long long spin_limit_ns;
   const float* mc_partial;    // multicast address of partial[] (null = P2P loads)
   float* mc_master;           // multicast address of master[]  (null = P2P stores)
@@ -105,18 +107,26 @@ __device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
                : "memory");
 }
 
-// Barrier among the CTAs of ONE rank (gridDim.x CTAs, all co-resident).
-__device__ __forceinline__ bool rank_grid_barrier(unsigned long long* ctr,
-                                                  unsigned long long target,
-                                                  unsigned long long limit, int* status) {
+constexpr int kMaxChunks = 64;
+
+// One thread per peer: publish `value` into slot `slot` of every peer's flag array.
+__device__ __forceinline__ void signal_peers(const RankView* views, int rank, int G, int slot,
+                                             unsigned value) {
+  if (threadIdx.x < G) {
+    __threadfence_system();
+    st_release_sys(views[threadIdx.x].flags + slot * G + rank, value);
+  }
+}
+// One thread per peer: wait until every peer has published `value` into my slot `slot`.
+__device__ __forceinline__ bool wait_peers(const RankView* views, int rank, int G, int slot,
+                                           unsigned value, unsigned long long limit, int* status) {
   __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    s_ok = 1;
-    __threadfence();
-    atomicAdd(ctr, 1ull);
+  if (threadIdx.x < G) {
+    const unsigned* mine = views[rank].flags + slot * G + threadIdx.x;
     const unsigned long long t0 = now_ns();
-    while (ld_acquire_gpu_u64(ctr) < target) {
+    while (ld_acquire_sys(mine) < value) {
       if (now_ns() - t0 > limit) { *status = 1; s_ok = 0; break; }
     }
   }
@@ -124,137 +134,167 @@ __device__ __forceinline__ bool rank_grid_barrier(unsigned long long* ctr,
   return s_ok != 0;
 }
 
-// Cross-rank barrier, executed by CTA 0 of each rank after its rank_grid_barrier.
-__device__ __forceinline__ void cross_rank_signal_wait(const RankView* views, int rank, int G,
-                                                       int slot, unsigned epoch,
-                                                       unsigned long long limit, int* status) {
-  if (threadIdx.x < G) {
-    const int peer = threadIdx.x;
-    __threadfence_system();
-    st_release_sys(views[peer].flags + slot * G + rank, epoch);
-    const unsigned* mine = views[rank].flags + slot * G + peer;
-    const unsigned long long t0 = now_ns();
-    while (ld_acquire_sys(mine) < epoch) {
-      if (now_ns() - t0 > limit) { *status = 1; break; }
-    }
-  }
-  __syncthreads();
-}
-
+// The kernel.  gridDim.x = P producer CTAs followed by Q consumer CTAs (all co-resident):
+//   producers walk the column chunks in order: weighted reduce of this GPU's clients into the
+//     (peer-visible) partial buffer; the LAST producer CTA to finish chunk c publishes flag
+//     1+c to every peer — no grid-wide barrier, just one arrival counter per chunk;
+//   consumers wait for flag 1+c from every peer, then reduce THIS rank's shard of chunk c over
+//     all ranks (P2P loads or multimem.ld_reduce), apply 1/sum(n), the folded DP noise and the
+//     casts, and store the result into every rank's model buffers (P2P stores or multimem.st);
+//   so chunk c crosses NVLink while chunk c+1 is still being read from HBM;
+//   the last consumer CTA to finish publishes flag 0 ("my stores are done") and waits for flag
+//   0 from every peer, which keeps the kernel alive until this rank owns the complete model.
 template <typename T>
 __global__ void __launch_bounds__(256)
     fedavg_allreduce_kernel(const RankView* __restrict__ views, int my_rank, AllreduceArgs a) {
   extern __shared__ float coef[];
   __shared__ float red[33];
+  __shared__ unsigned s_last;
   constexpr int V = Vec16<T>::N;
   const int rank = (gridDim.y > 1) ? static_cast<int>(blockIdx.y) : my_rank;
   const RankView me = views[rank];
   const int G = a.G;
-  const unsigned nblk = gridDim.x;
+  const int P = a.producers, Q = static_cast<int>(gridDim.x) - P;
+  const bool producer = static_cast<int>(blockIdx.x) < P;
+  const int64_t chunk = a.chunk_elems;              // multiple of 8*G... see host wrapper
+  const int n_chunks = a.n_chunks;
 
-  // ---- A. local unnormalised partial -------------------------------------------------
-  // normalise=false: coef = n_k m_k c_k ; returned value = sum (n_k m_k)^2
-  const float q_local = agg_prologue(coef, a.K, me.counts, me.sumsq, me.mask, a.clip_norm,
-                                     /*normalise=*/false, red);
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    float s = 0.f;
-    for (int k = 0; k < a.K; ++k) s += me.counts[k] * (me.mask ? me.mask[k] : 1.f);
-    me.scal[0] = s;
-    me.scal[1] = q_local;
-  }
-  const T* x = static_cast<const T*>(me.slots);
-  const int64_t groups = a.N / V;
-  for (int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; g < groups;
-       g += static_cast<int64_t>(nblk) * blockDim.x) {
-    float acc[V];
-    column_reduce<T>(x, a.row_stride, a.K, coef, g * V, acc);
+  if (producer) {
+    // ---- A. local unnormalised partial, chunk by chunk -----------------------------------
+    const float q_local = agg_prologue(coef, a.K, me.counts, me.sumsq, me.mask, a.clip_norm,
+                                       /*normalise=*/false, red);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      float s = 0.f;
+      for (int k = 0; k < a.K; ++k) s += me.counts[k] * (me.mask ? me.mask[k] : 1.f);
+      me.scal[0] = s;
+      me.scal[1] = q_local;
+    }
+    const T* x = static_cast<const T*>(me.slots);
+    for (int c = 0; c < n_chunks; ++c) {
+      const int64_t lo = c * chunk, hi = min(lo + chunk, a.N);
+      const int64_t g_lo = lo / V, groups = (hi - lo) / V;
+      for (int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; g < groups;
+           g += static_cast<int64_t>(P) * blockDim.x) {
+        float acc[V];
+        column_reduce<T>(x, a.row_stride, a.K, coef, (g_lo + g) * V, acc);
 #pragma unroll
-    for (int q = 0; q < V / 4; ++q)
-      *reinterpret_cast<float4*>(me.partial + g * V + 4 * q) =
-          make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+        for (int q = 0; q < V / 4; ++q)
+          *reinterpret_cast<float4*>(me.partial + (g_lo + g) * V + 4 * q) =
+              make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+      }
+      __threadfence_system();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        const unsigned prev = atomicAdd(me.counters + 1 + c, 1u);
+        s_last = (prev == static_cast<unsigned>(P) - 1u) ? 1u : 0u;
+        if (s_last) me.counters[1 + c] = 0u;       // self-clean for the next call
+      }
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        signal_peers(views, rank, G, 1 + c, a.epoch);
+      }
+      __syncthreads();
+    }
+    return;
   }
 
-  // ---- B. barrier 1: every rank's partial is complete and visible ----------------------
-  __threadfence_system();
-  if (!rank_grid_barrier(me.grid_ctr, a.ctr_base + 1ull * nblk, a.spin_limit_ns, a.status))
-    return;
-  if (blockIdx.x == 0)
-    cross_rank_signal_wait(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
-  if (!rank_grid_barrier(me.grid_ctr, a.ctr_base + 2ull * nblk, a.spin_limit_ns, a.status))
-    return;
-
-  // ---- C+D. reduce my shard across ranks, finish, store to every rank ------------------
+  // ---- consumers -----------------------------------------------------------------------------
+  const int cb = static_cast<int>(blockIdx.x) - P;
   float s_tot = 0.f, q_tot = 0.f;
-  for (int r = 0; r < G; ++r) {
-    const float* sc = views[r].scal;
-    float s_r, q_r;
-    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r) : "l"(sc) : "memory");
-    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r) : "l"(sc + 1) : "memory");
-    s_tot += s_r;
-    q_tot += q_r;
-  }
-  const float inv = s_tot > 0.f ? 1.f / s_tot : 0.f;
-  const float sigma = a.noise_std > 0.f ? a.noise_std * sqrtf(q_tot) * inv : 0.f;
-
-  const int64_t quads = a.N >> 2;
-  const int64_t per = (quads + G - 1) / G;
-  const int64_t q_lo = per * rank;
-  const int64_t q_hi = (q_lo + per < quads) ? q_lo + per : quads;
-  for (int64_t q = q_lo + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < q_hi;
-       q += static_cast<int64_t>(nblk) * blockDim.x) {
-    const int64_t col = q << 2;
-    float4 sum;
-    if (a.mc_partial) {
-      sum = multimem_ld_reduce_f4(a.mc_partial + col);
-    } else {
-      sum = make_float4(0.f, 0.f, 0.f, 0.f);
-      // fixed rank order => identical bits on every run; start at my own rank+1 so the
-      // G ranks do not all hammer peer 0 first
-      for (int i = 0; i < G; ++i) {
-        const int r = (i + rank + 1) % G;
-        const float4 v = ld_relaxed_sys_f4(views[r].partial + col);
-        sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+  bool have_scal = false;
+  bool ok = true;
+  for (int c = 0; c < n_chunks && ok; ++c) {
+    ok = wait_peers(views, rank, G, 1 + c, a.epoch, a.spin_limit_ns, a.status);
+    if (!ok) break;
+    if (!have_scal) {
+      for (int r = 0; r < G; ++r) {
+        const float* sc = views[r].scal;
+        float s_r, q_r;
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r) : "l"(sc) : "memory");
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r) : "l"(sc + 1) : "memory");
+        s_tot += s_r;
+        q_tot += q_r;
       }
+      have_scal = true;
     }
-    float o[4] = {sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv};
-    if (sigma > 0.f) {
-      const float4 z = Philox::normal4(a.group0 + q, a.seed);
-      float zz[4] = {z.x, z.y, z.z, z.w};
-      if (a.noise_mask) {
-        const uchar4 m = *reinterpret_cast<const uchar4*>(a.noise_mask + col);
-        zz[0] *= m.x ? 1.f : 0.f; zz[1] *= m.y ? 1.f : 0.f;
-        zz[2] *= m.z ? 1.f : 0.f; zz[3] *= m.w ? 1.f : 0.f;
-      }
+    const float inv = s_tot > 0.f ? 1.f / s_tot : 0.f;
+    const float sigma = a.noise_std > 0.f ? a.noise_std * sqrtf(q_tot) * inv : 0.f;
+
+    const int64_t lo = c * chunk, hi = min(lo + chunk, a.N);
+    const int64_t quads = (hi - lo) >> 2;
+    const int64_t per = (quads + G - 1) / G;
+    const int64_t q_lo = (lo >> 2) + per * rank;
+    const int64_t q_hi = min(q_lo + per, (lo >> 2) + quads);
+    for (int64_t q = q_lo + cb * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < q_hi;
+         q += static_cast<int64_t>(Q) * blockDim.x) {
+      const int64_t col = q << 2;
+      float4 sum;
+      if (a.mc_partial) {
+        sum = multimem_ld_reduce_f4(a.mc_partial + col);
+      } else {
+        float4 v[8];
+        sum = make_float4(0.f, 0.f, 0.f, 0.f);
+        // fixed rank order => identical bits on every rank; up to 8 peer loads in flight
+        for (int i0 = 0; i0 < G; i0 += 8) {
 #pragma unroll
-      for (int e = 0; e < 4; ++e) o[e] = fmaf(sigma, zz[e], o[e]);
-    }
-    const float4 ov = make_float4(o[0], o[1], o[2], o[3]);
-    const __nv_bfloat162 lo = __floats2bfloat162_rn(o[0], o[1]);
-    const __nv_bfloat162 hi = __floats2bfloat162_rn(o[2], o[3]);
-    uint2 packed;
-    packed.x = *reinterpret_cast<const uint32_t*>(&lo);
-    packed.y = *reinterpret_cast<const uint32_t*>(&hi);
-    if (a.mc_master) {
-      multimem_st_f4(a.mc_master + col, ov);
-      if (a.mc_lowp) multimem_st_b64(a.mc_lowp + col, packed);
-    } else {
-      for (int i = 0; i < G; ++i) {
-        const int r = (i + rank) % G;
-        *reinterpret_cast<float4*>(views[r].master + col) = ov;
-        if (views[r].lowp) *reinterpret_cast<uint2*>(views[r].lowp + col) = packed;
+          for (int i = 0; i < 8; ++i)
+            if (i0 + i < G) v[i] = ld_relaxed_sys_f4(views[i0 + i].partial + col);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (i0 + i < G) { sum.x += v[i].x; sum.y += v[i].y; sum.z += v[i].z; sum.w += v[i].w; }
+        }
+      }
+      float o[4] = {sum.x * inv, sum.y * inv, sum.z * inv, sum.w * inv};
+      if (sigma > 0.f) {
+        const float4 z = Philox::normal4(a.group0 + q, a.seed);
+        float zz[4] = {z.x, z.y, z.z, z.w};
+        if (a.noise_mask) {
+          const uchar4 m = *reinterpret_cast<const uchar4*>(a.noise_mask + col);
+          zz[0] *= m.x ? 1.f : 0.f; zz[1] *= m.y ? 1.f : 0.f;
+          zz[2] *= m.z ? 1.f : 0.f; zz[3] *= m.w ? 1.f : 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[e] = fmaf(sigma, zz[e], o[e]);
+      }
+      const float4 ov = make_float4(o[0], o[1], o[2], o[3]);
+      const __nv_bfloat162 lo2 = __floats2bfloat162_rn(o[0], o[1]);
+      const __nv_bfloat162 hi2 = __floats2bfloat162_rn(o[2], o[3]);
+      uint2 packed;
+      packed.x = *reinterpret_cast<const uint32_t*>(&lo2);
+      packed.y = *reinterpret_cast<const uint32_t*>(&hi2);
+      if (a.mc_master) {
+        multimem_st_f4(a.mc_master + col, ov);
+        if (a.mc_lowp) multimem_st_b64(a.mc_lowp + col, packed);
+      } else {
+        for (int i = 0; i < G; ++i) {
+          const int r = (i + rank) % G;
+          *reinterpret_cast<float4*>(views[r].master + col) = ov;
+          if (views[r].lowp) *reinterpret_cast<uint2*>(views[r].lowp + col) = packed;
+        }
       }
     }
   }
 
-  // ---- E. barrier 2: the new global model is complete on every rank ---------------------
+  // ---- E. completion: last consumer CTA tells the peers and waits for theirs ---------------
   __threadfence_system();
-  if (!rank_grid_barrier(me.grid_ctr, a.ctr_base + 3ull * nblk, a.spin_limit_ns, a.status))
-    return;
-  if (blockIdx.x == 0)
-    cross_rank_signal_wait(views, rank, G, 1, a.epoch, a.spin_limit_ns, a.status);
-  rank_grid_barrier(me.grid_ctr, a.ctr_base + 4ull * nblk, a.spin_limit_ns, a.status);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(me.counters, 1u);
+    s_last = (prev == static_cast<unsigned>(Q) - 1u) ? 1u : 0u;
+    if (s_last) me.counters[0] = 0u;
+  }
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    signal_peers(views, rank, G, 0, a.epoch);
+    wait_peers(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
+  }
 }
 
+}  // namespace nfb
+
+namespace nfb {
 // Host-side mirror of RankView for the C ABI (10 pointers, same order).
 static_assert(sizeof(RankView) == 10 * sizeof(void*), "RankView must stay 10 pointers");
 
@@ -308,7 +348,8 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
                                     int x_dtype, int64_t K, int64_t N, int64_t row_stride,
                                     float clip_norm, float noise_std, const uint8_t* noise_mask,
                                     uint64_t seed, uint64_t offset, uint32_t epoch,
-                                    uint64_t ctr_base, int grid_blocks, const float* mc_partial,
+                                    int producers, int64_t chunk_elems, int grid_blocks,
+                                    const float* mc_partial,
                                     float* mc_master, void* mc_lowp, int* status,
                                     uint64_t spin_limit_ns, void* stream) {
   using namespace nfb;
@@ -321,13 +362,22 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
   NFB_REQUIRE((N & 7) == 0 && (row_stride & 7) == 0 && N > 0, NFB_EINVAL,
               "fedavg_allreduce: N and row_stride must be positive multiples of 8");
   NFB_REQUIRE((offset & 3u) == 0, NFB_EINVAL, "fedavg_allreduce: offset must be multiple of 4");
-  NFB_REQUIRE(epoch >= 1 && grid_blocks >= 1, NFB_EINVAL, "fedavg_allreduce: bad epoch/grid");
+  NFB_REQUIRE(epoch >= 1 && grid_blocks >= 2, NFB_EINVAL, "fedavg_allreduce: bad epoch/grid");
+  NFB_REQUIRE(producers >= 1 && producers < grid_blocks, NFB_EINVAL,
+              "fedavg_allreduce: need at least one producer and one consumer CTA");
+  NFB_REQUIRE(chunk_elems >= 8 && (chunk_elems & 7) == 0 &&
+                  (N + chunk_elems - 1) / chunk_elems <= kMaxChunks,
+              NFB_ERANGE, "fedavg_allreduce: chunk size must be a multiple of 8 giving <= %d chunks",
+              kMaxChunks);
   AllreduceArgs a;
   a.G = G; a.K = static_cast<int>(K); a.x_dtype = x_dtype;
   a.N = N; a.row_stride = row_stride;
   a.clip_norm = clip_norm; a.noise_std = noise_std; a.noise_mask = noise_mask;
   a.seed = seed; a.group0 = offset >> 2;
-  a.epoch = epoch; a.ctr_base = ctr_base;
+  a.epoch = epoch;
+  a.producers = producers;
+  a.chunk_elems = chunk_elems;
+  a.n_chunks = static_cast<int>((N + chunk_elems - 1) / chunk_elems);
   a.spin_limit_ns = spin_limit_ns ? spin_limit_ns : 5000000000ull;
   a.mc_partial = mc_partial; a.mc_master = mc_master;
   a.mc_lowp = static_cast<__nv_bfloat16*>(mc_lowp);

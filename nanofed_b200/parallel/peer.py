@@ -37,11 +37,19 @@ from nanofed_b200.runtime.dist import RankInfo
 from nanofed_b200.utils import Logger
 
 _ALIGN = 256
+_MAX_CHUNKS = 64
+_CHUNK_TARGET = 4 << 20  # elements per pipeline chunk (16 MB of fp32 partials)
 _SPIN_NS = 10_000_000_000  # 10 s: far above any legitimate wait, far below a gpurun limit
 
 
 def _round_up(v: int, a: int = _ALIGN) -> int:
     return (v + a - 1) // a * a
+
+
+def chunk_elems_for(n: int) -> int:
+    """Pipeline chunk: ~4 M elements, at most 64 chunks, multiple of 1024 elements."""
+    chunk = max(_CHUNK_TARGET, -(-n // _MAX_CHUNKS))
+    return min(_round_up(chunk, 1024), _round_up(n, 1024))
 
 
 def _declare(lib: C.CDLL) -> None:
@@ -50,7 +58,7 @@ def _declare(lib: C.CDLL) -> None:
     vp, i32, i64, f32, u64, u32 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64, C.c_uint32
     lib.nfb_fedavg_allreduce.restype = i32
     lib.nfb_fedavg_allreduce.argtypes = [vp, i32, i32, i32, i32, i64, i64, i64, f32, f32, vp, u64,
-                                         u64, u32, u64, i32, vp, vp, vp, vp, u64, vp]
+                                         u64, u32, i32, i64, i32, vp, vp, vp, vp, u64, vp]
     lib.nfb_allreduce_max_blocks.restype = i32
     lib.nfb_allreduce_max_blocks.argtypes = [i32, i64]
     lib._nfb_allreduce_declared = True
@@ -66,7 +74,7 @@ class _Layout:
         self.lowp = _round_up(self.master + 4 * n)
         self.scal = _round_up(self.lowp + 2 * n)
         self.flags = self.scal + _ALIGN
-        self.total = self.flags + _round_up(4 * 2 * g)
+        self.total = self.flags + _round_up(4 * (1 + _MAX_CHUNKS) * g)
 
 
 class NcclReducer:
@@ -133,7 +141,7 @@ class PeerReducer:
         self.lowp.copy_(arena.master_lowp)
         arena.master, arena.master_lowp = self.master, self.lowp
 
-        self.grid_ctr = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.grid_ctr = torch.zeros(1 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
         self.sumsq_dummy = None
         rows = []
@@ -152,12 +160,12 @@ class PeerReducer:
         self.views_host = torch.tensor(rows, dtype=torch.int64)
         self.views = self.views_host.to(dev)
         self.epoch = 0
-        self.ctr_base = 0
+        self.chunk = chunk_elems_for(n)
         max_blocks = int(self.lib.nfb_allreduce_max_blocks(0, arena.num_clients))
         if max_blocks <= 0:
             raise RuntimeError("fedavg_allreduce: occupancy query failed")
         # one wave, at most 4 CTAs per SM: enough loads in flight to saturate HBM/NVLink
-        self.grid = max(1, min(max_blocks, 4 * torch.cuda.get_device_properties(dev).multi_processor_count))
+        self.grid = max(2, min(max_blocks, 4 * torch.cuda.get_device_properties(dev).multi_processor_count))
         dist.barrier()
         torch.cuda.synchronize(dev)
 
@@ -177,14 +185,13 @@ class PeerReducer:
             arena.num_clients, arena.layout.total, arena.slots.stride(0),
             float(clip_norm), float(noise_std),
             noise_mask.data_ptr() if noise_mask is not None else None,
-            seed & (2**64 - 1), offset, self.epoch, self.ctr_base, self.grid,
+            seed & (2**64 - 1), offset, self.epoch, self.grid // 2, self.chunk, self.grid,
             (mc + lay.partial) if mc else None, (mc + lay.master) if mc else None,
             (mc + lay.lowp) if mc else None, self.status.data_ptr(), _SPIN_NS,
             torch.cuda.current_stream(arena.device).cuda_stream,
         )
         native._check(code, "fedavg_allreduce")
         native._count()
-        self.ctr_base += 4 * self.grid
 
     def check(self) -> None:
         """Raise if any barrier timed out (reads one int from the device)."""
@@ -217,6 +224,7 @@ def emulate_allreduce(
     seed: int = 0,
     offset: int = 0,
     calls: int = 1,
+    chunk_elems: int = 0,
 ) -> tuple[torch.Tensor, torch.Tensor]:
     """Run G emulated ranks of the fused kernel in one cooperative launch.
 
@@ -230,7 +238,7 @@ def emulate_allreduce(
     dev = slots.device
     lay = _Layout(n, g)
     bufs = torch.zeros(g, lay.total, dtype=torch.uint8, device=dev)
-    ctr = torch.zeros(g, dtype=torch.int64, device=dev)
+    ctr = torch.zeros(g, 1 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     counts = counts.to(torch.float32).contiguous()
     mask = torch.ones_like(counts) if mask is None else mask.to(torch.float32).contiguous()
@@ -241,23 +249,22 @@ def emulate_allreduce(
             slots[r].data_ptr(), counts[r].data_ptr(), mask[r].data_ptr(),
             sumsq[r].data_ptr() if sumsq is not None else 0,
             base + lay.partial, base + lay.scal, base + lay.flags, base + lay.master,
-            base + lay.lowp, ctr[r : r + 1].data_ptr(),
+            base + lay.lowp, ctr[r].data_ptr(),
         ])
     views = torch.tensor(rows, dtype=torch.int64).to(dev)
     max_blocks = int(lib.nfb_allreduce_max_blocks(native._dt(slots), k))
-    grid = max(1, min(max_blocks // g, 64))
-    base_ctr = 0
+    grid = max(2, min(max_blocks // g, 64))
+    chunk = chunk_elems if chunk_elems else chunk_elems_for(n)
     for call in range(1, calls + 1):
         code = lib.nfb_fedavg_allreduce(
             views.data_ptr(), 0, g, g, native._dt(slots), k, n, slots.stride(1),
             float(clip_norm), float(noise_std),
             noise_mask.data_ptr() if noise_mask is not None else None,
-            seed & (2**64 - 1), offset, call, base_ctr, grid, None, None, None,
+            seed & (2**64 - 1), offset, call, grid // 2, chunk, grid, None, None, None,
             status.data_ptr(), 2_000_000_000, torch.cuda.current_stream(dev).cuda_stream,
         )
         native._check(code, "fedavg_allreduce(emulated)")
         native._count()
-        base_ctr += 4 * grid
     torch.cuda.synchronize(dev)
     if int(status.item()) != 0:
         raise RuntimeError("emulated fedavg_allreduce: barrier timed out")

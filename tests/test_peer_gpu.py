@@ -23,6 +23,17 @@ def test_emulated_allreduce_matches_flat_fedavg(g, k, n):
     torch.testing.assert_close(lowp[0].float().cpu(), want.bfloat16().float(), rtol=1e-2, atol=1e-2)
 
 
+def test_emulated_allreduce_chunk_pipeline():
+    """Several pipeline chunks (incl. a ragged last one): producers and consumers overlap."""
+    g, k, n = 4, 3, 70_016
+    slots = torch.randn(g, k, n, device="cuda")
+    counts = torch.randint(1, 50, (g, k), device="cuda").float()
+    master, _ = emulate_allreduce(slots, counts, calls=3, chunk_elems=8192)
+    want = ref.fedavg_reduce(slots.view(g * k, n).cpu(), counts.view(-1).cpu())
+    torch.testing.assert_close(master[0].cpu(), want, rtol=1e-5, atol=1e-5)
+    assert all(torch.equal(master[r], master[0]) for r in range(g))
+
+
 def test_emulated_allreduce_dp_matches_single_gpu_kernel():
     g, k, n = 4, 5, 32_768
     slots = torch.randn(g, k, n, device="cuda") * 0.02
