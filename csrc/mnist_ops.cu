@@ -226,7 +226,8 @@ __global__ void __launch_bounds__(1024)
                    int64_t label_stride, int B, const float* __restrict__ slots,
                    float* __restrict__ grads, int64_t row_stride, int64_t b1_off, int64_t w2_off,
                    int64_t b2_off, float drop_p, unsigned long long* __restrict__ rng_state,
-                   uint64_t seed, __nv_bfloat16* __restrict__ dh, float* __restrict__ stats) {
+                   int advance_rng, uint64_t seed, __nv_bfloat16* __restrict__ dh,
+                   float* __restrict__ stats) {
   extern __shared__ float smem[];
   float* h = smem;                 // [B][128]   (later reused for dh in fp32)
   float* w2 = h + B * 128;         // [10][128]
@@ -323,7 +324,7 @@ __global__ void __launch_bounds__(1024)
     for (int b = 0; b < B; ++b) acc += h[b * 128 + threadIdx.x];
     grow[b1_off + threadIdx.x] = acc;
   }
-  if (c == 0 && threadIdx.x == 0 && rng_state) *rng_state = step + 1;
+  if (advance_rng && c == 0 && threadIdx.x == 0 && rng_state) *rng_state = step + 1;
 }
 
 // -------------------------------------------------------------------------------------
@@ -433,7 +434,8 @@ int nfb_mnist_pool_bwd(const void* dp, const uint8_t* pidx, int C, int B, float 
 int nfb_mnist_fc_head(const float* hpre, const int64_t* labels, int64_t label_stride, int C,
                       int B, const float* slots, float* grads, int64_t row_stride,
                       int64_t b1_off, int64_t w2_off, int64_t b2_off, float drop_p,
-                      void* rng_state, uint64_t seed, void* dh, float* stats, void* stream) {
+                      void* rng_state, int advance_rng, uint64_t seed, void* dh, float* stats,
+                      void* stream) {
   using namespace nfb;
   NFB_REQUIRE(hpre && labels && slots && grads && dh && stats, NFB_EINVAL,
               "mnist_fc_head: null pointer");
@@ -447,7 +449,8 @@ int nfb_mnist_fc_head(const float* hpre, const int64_t* labels, int64_t label_st
   }
   fc_head_kernel<<<C, 1024, smem, as_stream(stream)>>>(
       hpre, labels, label_stride, B, slots, grads, row_stride, b1_off, w2_off, b2_off, drop_p,
-      static_cast<unsigned long long*>(rng_state), seed, static_cast<__nv_bfloat16*>(dh), stats);
+      static_cast<unsigned long long*>(rng_state), advance_rng, seed,
+      static_cast<__nv_bfloat16*>(dh), stats);
   return launch_status("mnist_fc_head");
 }
 
