@@ -400,6 +400,39 @@ class FedSimulation:
         self.shards.labels.copy_(labels, non_blocking=True)
         return images.numel() * images.element_size() + labels.numel() * labels.element_size()
 
+    # -- input pipeline: H2D of round r+1 overlaps the training of round r -------------------
+    def prefetch_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> int:
+        """Start the H2D copy of the NEXT round's inputs (pinned host tensors) on a copy stream.
+
+        The data lands in a staging buffer; ``run_round(use_staged=True)`` moves it into the
+        resident shards with a device-to-device copy (the CUDA graph of the local epoch has the
+        shard addresses baked in).  Returns the number of bytes that will cross PCIe.
+        """
+        if self.device.type != "cuda":
+            return self.stage_inputs(images, labels)
+        if getattr(self, "_stage_images", None) is None:
+            self._stage_images = torch.empty_like(self.shards.images)
+            self._stage_labels = torch.empty_like(self.shards.labels)
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._staged = torch.cuda.Event()
+            self._consumed = torch.cuda.Event()
+            self._consumed.record()
+        self._copy_stream.wait_event(self._consumed)      # staging is free again
+        with torch.cuda.stream(self._copy_stream):
+            self._stage_images.copy_(images, non_blocking=True)
+            self._stage_labels.copy_(labels, non_blocking=True)
+            self._staged.record(self._copy_stream)
+        self._has_staged = True
+        return images.numel() * images.element_size() + labels.numel() * labels.element_size()
+
+    def _adopt_staged(self) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._staged)
+        self.shards.images.copy_(self._stage_images, non_blocking=True)
+        self.shards.labels.copy_(self._stage_labels, non_blocking=True)
+        self._consumed.record(cur)
+        self._has_staged = False
+
     def enqueue_round(self) -> None:
         """Enqueue one full round on the current stream.  No host synchronisation."""
         arena, cfg = self.arena, self.cfg
@@ -430,10 +463,24 @@ class FedSimulation:
                 self.reducer.reduce(arena, **kw)
 
     def run_round(
-        self, host_inputs: tuple[torch.Tensor, torch.Tensor] | None = None
+        self,
+        host_inputs: tuple[torch.Tensor, torch.Tensor] | None = None,
+        use_staged: bool = False,
+        prefetch_next: tuple[torch.Tensor, torch.Tensor] | None = None,
     ) -> RoundOutcome:
+        """One federated round; returns metrics as Python floats (one stream sync).
+
+        ``host_inputs``: copy this round's inputs from host memory first (blocking the
+        compute stream).  ``use_staged``: use inputs previously sent with ``prefetch_inputs``.
+        ``prefetch_next``: start the H2D copy of the following round's inputs, overlapped
+        with this round's training.
+        """
         if host_inputs is not None:
             self.stage_inputs(*host_inputs)
+        elif use_staged and getattr(self, "_has_staged", False):
+            self._adopt_staged()
+        if prefetch_next is not None:
+            self.prefetch_inputs(*prefetch_next)
         self.enqueue_round()
         # the round's only device→host transfer: per-client (loss_sum, correct, samples)
         self._stats_host.copy_(self.arena.stats, non_blocking=True)

@@ -100,3 +100,26 @@ def test_full_round_through_fedsimulation():
     state = sim.global_state()
     assert set(state) == set(sim.template.state_dict())
     assert all(torch.isfinite(v).all() for v in state.values())
+
+
+def test_prefetched_inputs_match_direct_staging():
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    def run(pipelined: bool):
+        sim = FedSimulation(CohortConfig(clients_per_gpu=2, samples_per_client=64, batch_size=32,
+                                         engine="grouped", seed=5))
+        gen = torch.Generator().manual_seed(9)
+        rounds = [(torch.randn(2, 64, 1, 28, 28, generator=gen).pin_memory(),
+                   torch.randint(0, 10, (2, 64), generator=gen).pin_memory()) for _ in range(3)]
+        if pipelined:
+            sim.prefetch_inputs(*rounds[0])
+            for r in range(3):
+                nxt = rounds[r + 1] if r + 1 < 3 else None
+                sim.run_round(use_staged=True, prefetch_next=nxt)
+        else:
+            for r in range(3):
+                sim.run_round(host_inputs=rounds[r])
+        return sim.arena.master.clone()
+
+    a, b = run(False), run(True)
+    torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-4)
