@@ -67,6 +67,7 @@ class CohortConfig:
     device: str | None = None
     max_steps_per_epoch: int | None = None
     sample_counts: list[int] | None = None  # per-client n_k on this rank (≤ samples_per_client)
+    screen_nonfinite: bool = False  # K-STATS every round; clients with NaN/Inf weights are masked out
 
     @property
     def steps_per_epoch(self) -> int:
@@ -444,23 +445,36 @@ class FedSimulation:
             self.engine.local_steps()
         with self.timer.phase("aggregate"):
             self.engine.before_aggregate()
+            for k in getattr(self, "_poison", []):
+                arena.slots[k, :16] = float("nan")
+            self._poison = []
             dp = cfg.privacy
             kw: dict[str, Any] = {}
-            if dp is not None:
+            if dp is not None or cfg.screen_nonfinite:
                 ss, bad = ops.update_stats(arena.slots)
                 arena.sumsq.copy_(ss)
                 arena.nonfinite.copy_(bad)
+                if cfg.screen_nonfinite:
+                    # device-side failure detection: a diverged client drops out of this
+                    # round's average without any host round trip (K-AGG never reads its row)
+                    self._round_mask = arena.mask * (bad == 0).to(arena.mask.dtype)
+            if dp is not None:
                 k_total = self.num_clients
                 kw = dict(sumsq=arena.sumsq, clip_norm=float(dp.max_gradient_norm),
                           noise_std=dp.noise_multiplier * dp.max_gradient_norm / k_total,
                           noise_mask=arena.noise_mask, seed=cfg.seed + 7919,
                           offset=self._noise_offset)
                 self._noise_offset += arena.layout.total
+            mask = getattr(self, "_round_mask", None)
+            if mask is not None and cfg.screen_nonfinite:
+                saved, arena.mask = arena.mask, mask
             if self.reducer is None:
                 ops.fedavg_reduce(arena.slots, arena.counts, out=arena.master,
                                   out_lowp=arena.master_lowp, mask=arena.mask, **kw)
             else:
                 self.reducer.reduce(arena, **kw)
+            if mask is not None and cfg.screen_nonfinite:
+                arena.mask = saved
 
     def run_round(
         self,
@@ -518,7 +532,33 @@ class FedSimulation:
                             samples=self.cfg.clients_per_gpu * self.cfg.local_steps
                             * self.cfg.batch_size)
 
+    # -- participation / fault injection ----------------------------------
+    def set_participation(self, active: list[bool] | torch.Tensor) -> None:
+        """Per-client participation flags for the coming rounds (device tensor read by K-AGG;
+        weights are renormalised over the participants on the device)."""
+        flags = torch.as_tensor(active, dtype=torch.float32).to(self.device)
+        self.arena.mask.copy_(flags)
+
+    def drop_clients(self, indices: list[int]) -> None:
+        self.arena.mask[torch.as_tensor(indices, device=self.device)] = 0.0
+
+    def inject_fault(self, kind: str, client: int) -> None:
+        """Test hook: ``"drop"`` masks the client out, ``"nan"`` poisons its weights AFTER the
+        next local training (use with ``screen_nonfinite=True`` to see it rejected)."""
+        if kind == "drop":
+            self.drop_clients([client])
+        elif kind == "nan":
+            self._poison = getattr(self, "_poison", []) + [client]
+        else:
+            raise ValueError(f"unknown fault kind {kind!r}")
+
     # -- checkpoints -------------------------------------------------------------
+    def load_global_state(self, state: dict[str, torch.Tensor]) -> None:
+        """Resume: overwrite the global model (e.g. ``ModelManager.load_model`` + ``state_dict``)."""
+        host = self.layout.flatten(state, device="cpu")
+        self.arena.master.copy_(host.to(self.device))
+        self.arena.master_lowp.copy_(self.arena.master)
+
     def global_state(self) -> dict[str, torch.Tensor]:
         return self.arena.global_state()
 

@@ -58,3 +58,28 @@ def test_coordinator_drives_simulation_and_writes_reference_layout(tmp_path):
     assert rec["status"] == "COMPLETED" and len(rec["client_metrics"]) == 3
     torch.testing.assert_close(model.fc1.weight,
                                sim.layout.views(sim.arena.master)["fc1.weight"])
+
+
+def test_participation_mask_and_nonfinite_screening():
+    sim = FedSimulation(_cfg(screen_nonfinite=True, sample_counts=[8, 8, 8]))
+    sim.inject_fault("drop", 0)
+    sim.inject_fault("nan", 1)          # client 1 diverges this round
+    sim.run_round()
+    # only client 2 is left: the global model equals its weights, and it is finite
+    torch.testing.assert_close(sim.arena.master, sim.arena.slots[2])
+    assert torch.isfinite(sim.arena.master).all()
+    assert sim.arena.nonfinite.tolist() == [0, 1, 0]
+    sim.set_participation([True, True, True])
+    sim.run_round()
+    want = sim.arena.slots.mean(0)
+    torch.testing.assert_close(sim.arena.master, want, rtol=1e-5, atol=1e-6)
+
+
+def test_resume_from_checkpoint(tmp_path):
+    sim = FedSimulation(_cfg())
+    sim.run_round()
+    state = sim.global_state()
+    torch.save(state, tmp_path / "g.pt")
+    again = FedSimulation(_cfg(seed=3))
+    again.load_global_state(torch.load(tmp_path / "g.pt", weights_only=True))
+    torch.testing.assert_close(again.arena.master, sim.arena.master)
