@@ -17,7 +17,7 @@ def test_reference_suite_passes_against_this_package(tmp_path):
     cmd = [sys.executable, "-m", "pytest", str(REF_TESTS), "-p", "tools.ref_compat_plugin",
            "--rootdir", str(tmp_path), "-c", "/dev/null", "-q", "-p", "no:cacheprovider",
            # upstream flake: random z-score test fails ~1 in 6 on the reference itself too
-           "--deselect", "unit/server/test_validation.py::TestDefaultModelValidator::test_statistical_validation"]
+           "-k", "not test_statistical_validation"]
     proc = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     tail = proc.stdout.strip().splitlines()[-1] if proc.stdout.strip() else proc.stderr[-500:]
     assert proc.returncode == 0, proc.stdout[-3000:]
