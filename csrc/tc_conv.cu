@@ -13,11 +13,16 @@
 //
 // MODE 0 (forward):  out[q, co] = relu(sum_t sum_ci x[q + s_t, ci] w[co, t*32+ci] + b[co])
 //                    A = x [C,R,32] (4 chunks), B_t = w[:, t*32:(t+1)*32] K-major SW64, N = 64
+// MODE 2 (forward + pool): MODE 0's math on tiles of 4 grid rows (104 positions), with bias,
+//                    ReLU, 2x2 max-pool and dropout in the epilogue: the conv output never
+//                    reaches memory — only the pooled activations (PyTorch flatten order) and a
+//                    1-byte argmax/ReLU/keep code per pooled element are written.
 // MODE 1 (dgrad):    out[q, ci] = (sum_t sum_co dy[q - s_t, co] w[co, t*32+ci]) * (mask[q,ci] > 0)
 //                    A = dy [C,R,64] (8 chunks), B_t = same weights read MN-major SW64, N = 32
 #include <cstdlib>
 
 #include "common.cuh"
+#include "philox.cuh"
 #include "tc_common.cuh"
 
 namespace nfb {
@@ -37,6 +42,14 @@ struct ConvArgs {
   const float* bias;      // MODE 0: [C][64] with stride bias_gs
   long long bias_gs;
   const __nv_bfloat16* mask;  // MODE 1: [C, R, 32] ReLU mask source (same strides as out)
+  // MODE 2 (fused pool) only
+  __nv_bfloat16* pool_out;  // [C, B, 9216]   ch*144 + ph*12 + pw
+  uint8_t* pool_idx;        // [C, B, 144, 64]
+  int images;               // B
+  int grid_w;               // 26
+  float drop_p;
+  const unsigned long long* rng_state;
+  unsigned long long seed;
   int* status;
   int debug;  // bottleneck probes (env NFB_CONV_DEBUG): 1 = reuse first slabs, 2 = no MMA, 4 = no stores
 };
@@ -70,18 +83,21 @@ constexpr int kEpiWarps = 8;   // two epilogue warpgroups, alternating tiles / a
 
 template <int MODE>
 struct ConvCfg {
-  static constexpr int CH = MODE == 0 ? 32 : 64;       // A channels (K per tap)
-  static constexpr int BN = MODE == 0 ? 64 : 32;       // output channels
+  static constexpr int CH = MODE != 1 ? 32 : 64;       // A channels (K per tap)
+  static constexpr int BN = MODE != 1 ? 64 : 32;       // output channels
   static constexpr int CHUNKS = CH / 8;
   static constexpr int SLAB = kSlabRows * CH * 2;      // bytes per stage
   static constexpr int SLAB_PAD = (SLAB + 1023) / 1024 * 1024;
   static constexpr int W_TILE = 64 * 32 * 2;           // one tap's weights (4 KB) either way
   static constexpr int W_BYTES = kTaps * W_TILE;
   static constexpr int TMEM_COLS = 2 * BN;             // 128 or 64 (both powers of two)
-  static constexpr int STAGES = MODE == 0 ? 10 : 6;    // slab loads in flight per CTA
+  static constexpr int STAGES = MODE != 1 ? 10 : 6;    // slab loads in flight per CTA
   static constexpr int OUT_ROW = BN * 2;               // bytes per output row (128 / 64)
   static constexpr int STAGING = 32 * OUT_ROW;         // per epilogue warp (4 KB / 2 KB)
-  static constexpr size_t SMEM = W_BYTES + STAGES * SLAB_PAD + kEpiWarps * 4096 + 1024 + 256;
+  // MODE 2: per epilogue group a [128 x 64] bf16 tile (16 KB = the 4 warps' 4 KB areas) plus a
+  // pooled [64 ch x 24] bf16 tile (3 KB)
+  static constexpr int POOL_STAGE = MODE == 2 ? 2 * 3072 : 0;
+  static constexpr size_t SMEM = W_BYTES + STAGES * SLAB_PAD + kEpiWarps * 4096 + POOL_STAGE + 1024 + 256;
 };
 
 template <int MODE>
@@ -97,7 +113,8 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
   uint8_t* w_smem = smem;                              // 9 x 4 KB, 1024-aligned
   uint8_t* slabs = smem + C::W_BYTES;
   uint8_t* staging = slabs + C::STAGES * C::SLAB_PAD;   // kEpiWarps x 4 KB, 1024-aligned
-  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + kEpiWarps * 4096);
+  uint8_t* pool_stage = staging + kEpiWarps * 4096;    // MODE 2: 2 x 3 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(pool_stage + C::POOL_STAGE);
   uint64_t* full_bar = bars;                           // [stages]
   uint64_t* empty_bar = bars + C::STAGES;            // [stages]
   uint64_t* acc_full = bars + 2 * C::STAGES;         // [2]
@@ -105,9 +122,13 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
   uint64_t* w_bar = acc_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
 
+  __shared__ float s_bias[64];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = blockIdx.x / args.ctas_per_client;
   const int part = blockIdx.x % args.ctas_per_client;
+  if (threadIdx.x < 64)
+    s_bias[threadIdx.x] = (MODE != 1 && args.bias)
+                              ? args.bias[static_cast<long long>(g) * args.bias_gs + threadIdx.x] : 0.f;
   const int per = (args.tiles_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
   const int tile_lo = part * per;
   const int tile_hi = min(tile_lo + per, args.tiles_per_client);
@@ -133,7 +154,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     if (elect_one() && n_tiles > 0) {
       mbar_expect_tx(w_bar, C::W_BYTES);
       for (int t = 0; t < kTaps; ++t) {
-        if (MODE == 0)  // K-major box [32 k, 64 co]
+        if (MODE != 1)  // K-major box [32 k, 64 co]
           tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
         else            // MN-major box [32 ci, 64 co-rows]: same bytes, read as B^T
           tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
@@ -144,8 +165,11 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
         if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; break; }
         if ((args.debug & 1) && i >= C::STAGES) { mbar_arrive(&full_bar[s]); continue; }
         mbar_expect_tx(&full_bar[s], C::SLAB);
-        const int m0 = (tile_lo + i) * 128;
-        const int row0 = MODE == 0 ? m0 : m0 - kHalo;
+        const int tile = tile_lo + i;
+        // MODE 2 tiles are 4 grid rows of one image: 6 per image, 104 positions apart
+        const int m0 = MODE == 2 ? (tile / 6) * (args.grid_w * args.grid_w) + (tile % 6) * (4 * args.grid_w)
+                                 : tile * 128;
+        const int row0 = MODE != 1 ? m0 : m0 - kHalo;
         tma_load_4d(slabs + s * C::SLAB_PAD, &map_a, &full_bar[s], 0, row0, 0, g);
       }
     }
@@ -153,7 +177,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     // ===================== MMA issuer =====================
     if (elect_one() && n_tiles > 0) {
       // fwd: A K-major, B K-major ; dgrad: A K-major, B MN-major
-      constexpr uint32_t idesc = make_idesc_bf16(128, C::BN, 0u, MODE == 0 ? 0u : 1u);
+      constexpr uint32_t idesc = make_idesc_bf16(128, C::BN, 0u, MODE != 1 ? 0u : 1u);
       bool ok = mbar_wait(w_bar, 0);
       if (!ok) *args.status = 1;
       const uint32_t w_addr = smem_u32(w_smem);
@@ -177,7 +201,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
             const uint64_t da = make_smem_desc(
                 slab + args.shift[t] * 16 + kk * (2 * kSlabRows * 16), kSlabRows * 16, 128, 0);
             uint64_t db;
-            if (MODE == 0)   // K-major SW64 tile [64 co][32 k]: step K by 32 B
+            if (MODE != 1)   // K-major SW64 tile [64 co][32 k]: step K by 32 B
               db = make_smem_desc(w_addr + t * C::W_TILE + kk * 32, 0, 8 * 64, 4);
             else             // MN-major SW64 tile [64 k-rows][32 ci]: step K by 16 rows
               db = make_smem_desc(w_addr + t * C::W_TILE + kk * (16 * 64), 64 * 64, 8 * 64, 4);
@@ -201,7 +225,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     for (int i = grp; i < n_tiles && ok; i += 2) {
       const int acc = grp;
       const uint32_t aph = (i >> 1) & 1;
-      const int row0 = (tile_lo + i) * 128 + sub * 32;
+      const int row0 = (tile_lo + i) * 128 + sub * 32;   // (MODE 0/1 tiling; MODE 2 indexes by image)
       const int m = row0 + lane;
       const bool row_ok = m < args.rows;
       // the ReLU mask of this row depends only on the tile index: fetch it BEFORE waiting for
@@ -227,6 +251,85 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
         bulk_wait_read0();          // previous TMA store has finished reading my staging tile
       }
       __syncwarp();
+      if (MODE == 2) {
+        // ---- fused bias + ReLU + 2x2 max-pool + dropout --------------------------------------
+        // (1) the group's 4 warps stage the post-ReLU [128 x 64] tile (bf16, chunk-swizzled).
+        //     No barrier is needed before overwriting it: its last readers (phase 2 of this
+        //     group's previous tile) are ordered before that tile's second barrier.
+        uint8_t* tile_s = staging + grp * (4 * 4096);
+        __nv_bfloat16* pooled = reinterpret_cast<__nv_bfloat16*>(pool_stage + grp * 3072);
+        const int gt = threadIdx.x - 128 - grp * 128;           // 0..127 within the group
+        const int trow = sub * 32 + lane;
+#pragma unroll
+        for (int c0 = 0; c0 < 64; c0 += 8) {
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c0 + j]);
+          // raw accumulators are staged; bias + ReLU are applied AFTER the max (both are
+          // monotonic, so max(relu(x+b)) == relu(max(x)+b)) on a quarter of the elements
+          st_vec(tile_s + trow * 128 + (((c0 >> 3) ^ (trow & 7)) * 16), pack<__nv_bfloat16>(v));
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+        // (2) pool: 24 pooled positions x 16 channel quads = 384 items, 3 per thread
+        const int tile = tile_lo + i;
+        const long long img = static_cast<long long>(g) * args.images + tile / 6;
+        const int prow0 = (tile % 6) * 2;
+        const unsigned long long step = args.rng_state ? *args.rng_state : 0ull;
+        const float keep_scale = args.drop_p > 0.f ? 1.f / (1.f - args.drop_p) : 1.f;
+        // dropout: ONE Philox draw per thread and tile = 16 random bytes, one per pooled element
+        // this thread produces (12 used); keep <=> byte >= round(p*256).  The keep bit is stored
+        // in the code byte, so the backward pass never regenerates the stream.
+        uint4 rnd = make_uint4(~0u, ~0u, ~0u, ~0u);
+        if (args.drop_p > 0.f)
+          rnd = Philox::draw((step << 40) + (static_cast<unsigned long long>(blockIdx.x) << 20) +
+                                 static_cast<unsigned long long>(i) * 256 + (threadIdx.x - 128),
+                             args.seed);
+        const uint32_t thresh = static_cast<uint32_t>(args.drop_p * 256.f + 0.5f);
+        const uint32_t rwords[3] = {rnd.x, rnd.y, rnd.z};
+#pragma unroll
+        for (int rep = 0; rep < 3; ++rep) {
+          const int it = gt + rep * 128;
+          const int quad = it & 15, pp = it >> 4;             // pp = prow*12 + pcol
+          const int prow = pp / 12, pcol = pp % 12;
+          const int r0 = (2 * prow) * args.grid_w + 2 * pcol;
+          const int rows4[4] = {r0, r0 + 1, r0 + args.grid_w, r0 + args.grid_w + 1};
+          float v[4][4];
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            const uint2 raw = *reinterpret_cast<const uint2*>(
+                tile_s + rows4[w] * 128 + (((quad >> 1) ^ (rows4[w] & 7)) * 16) + (quad & 1) * 8);
+            v[w][0] = __uint_as_float(raw.x << 16); v[w][1] = __uint_as_float(raw.x & 0xffff0000u);
+            v[w][2] = __uint_as_float(raw.y << 16); v[w][3] = __uint_as_float(raw.y & 0xffff0000u);
+          }
+          const int pos = (prow0 + prow) * 12 + pcol;
+          uint32_t codes = 0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float m = v[0][j];
+            uint32_t a = 0;
+#pragma unroll
+            for (int w = 1; w < 4; ++w)
+              if (v[w][j] > m) { m = v[w][j]; a = w; }
+            m = fmaxf(m + s_bias[quad * 4 + j], 0.f);
+            const bool keep = ((rwords[rep] >> (8 * j)) & 0xffu) >= thresh;
+            codes |= (a | (m > 0.f ? 4u : 0u) | (keep ? 8u : 0u)) << (8 * j);
+            pooled[(quad * 4 + j) * 24 + pp] = __float2bfloat16_rn(keep ? m * keep_scale : 0.f);
+          }
+          *reinterpret_cast<uint32_t*>(args.pool_idx + (img * 144 + pos) * 64 + quad * 4) = codes;
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+        // (3) write the pooled tile: per channel 24 consecutive bf16 (48 B) in flatten order
+        {
+          const int ch = gt >> 1, half = gt & 1;               // 64 channels x 2 halves of 12
+          const uint2* src = reinterpret_cast<const uint2*>(pooled + ch * 24 + half * 12);
+          uint2* dst = reinterpret_cast<uint2*>(args.pool_out + img * 9216 + ch * 144 + prow0 * 12 + half * 12);
+          const uint2 a0 = src[0], a1 = src[1], a2 = src[2];
+          dst[0] = a0; dst[1] = a1; dst[2] = a2;
+        }
+        // `pooled` is rewritten only after the next tile's first barrier, i.e. after every
+        // thread of the group has finished the reads above.
+        continue;
+      }
       if (!(args.debug & 4)) {
         // stage this warp's 32 rows in shared memory with the TMA swizzle (conflict-free
         // 16-byte stores), then ONE bulk tensor store writes them as full lines
@@ -237,7 +340,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
           for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[c0 + j]);
           if (MODE == 0) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j] + (bias ? __ldg(bias + c0 + j) : 0.f), 0.f);
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j] + s_bias[c0 + j], 0.f);
           } else if (mask && row_ok) {
             float mf[8];
             unpack<__nv_bfloat16>(mk[c0 / 8], mf);
@@ -682,4 +785,49 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
   }
   tc_conv_wgrad_kernel<<<clients * per_client, 256, kWgSmem, as_stream(stream)>>>(mdy, mx, a);
   return launch_status("tc_conv3x3_wgrad");
+}
+
+// Forward 3x3 conv (32 -> 64 ch) + bias + ReLU + 2x2 max-pool + dropout in ONE kernel; the conv
+// output is never written.  x = bf16 [C, B*26*26, 32] on the 26x26 grid; pool_out = bf16
+// [C, B, 9216] in PyTorch flatten order (ch*144 + ph*12 + pw); pool_idx = u8 [C, B, 144, 64]
+// (bits 0-1 argmax, bit 2 max > 0, bit 3 dropout keep) for the backward pass.
+extern "C" int nfb_tc_conv3x3_pool_fwd(const void* x, long long rows, long long x_group_stride,
+                                       const void* w, long long w_group_stride, int clients,
+                                       int images, int width, const float* bias,
+                                       long long bias_group_stride, void* pool_out,
+                                       uint8_t* pool_idx, float drop_p, const void* rng_state,
+                                       unsigned long long seed, int* status, void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(x && w && pool_out && pool_idx && status, NFB_EINVAL,
+              "tc_conv3x3_pool_fwd: null pointer");
+  NFB_REQUIRE(width == 26 && rows == static_cast<long long>(images) * 26 * 26, NFB_ERANGE,
+              "tc_conv3x3_pool_fwd: only the 26x26 grid (24x24 conv output, 12x12 pooled) is "
+              "implemented (got width %d, rows %lld for %d images)", width, rows, images);
+  CUtensorMap ma, mw;
+  int rc = slab_map(x, rows, clients, x_group_stride, 32, kSlabRows, &ma);
+  if (rc) return rc;
+  rc = weight_map(w, clients, w_group_stride, &mw);
+  if (rc) return rc;
+  ConvArgs args{};
+  args.tiles_per_client = images * 6;
+  int per_client = sm_count() / clients;
+  if (per_client < 1) per_client = 1;
+  if (per_client > args.tiles_per_client) per_client = args.tiles_per_client;
+  args.ctas_per_client = per_client;
+  args.rows = static_cast<int>(rows);
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kw = 0; kw < 3; ++kw) args.shift[kh * 3 + kw] = kh * width + kw;
+  args.bias = bias;
+  args.bias_gs = bias_group_stride;
+  args.pool_out = static_cast<__nv_bfloat16*>(pool_out);
+  args.pool_idx = pool_idx;
+  args.images = images;
+  args.grid_w = width;
+  args.drop_p = drop_p;
+  args.rng_state = static_cast<const unsigned long long*>(rng_state);
+  args.seed = seed;
+  args.status = status;
+  return launch_conv<2>(ma, mw, ma /*unused output map*/, clients * per_client, args,
+                        as_stream(stream));
 }

@@ -4,12 +4,12 @@ Same math as ``MNISTModel`` (reference ``nanofed/models/mnist.py:6-28``) and the
 training step as the reference's client loop (``trainer/base.py:134-160`` with
 ``torch.optim.SGD``, ``examples/mnist/run_experiment.py:70-78``), but expressed
 for C clients at once — the client index is the *group* dimension of every launch,
-so a local step is 14 launches no matter how many clients share the GPU:
+so a local step is 13 launches no matter how many clients share the GPU:
 
     prep        conv2 weights fp32 [co][ci][3][3] → bf16 [co][tap·32+ci]            (K-ELT)
     conv1       direct 3×3, 1→32, +bias +ReLU → NHWC bf16 on a 26×26 grid             (K-CONV, CUDA cores: K=9)
-    conv2       implicit GEMM, 9 shifted TMA tiles → tcgen05 → TMEM, +bias +ReLU      (K-CONV)
-    pool        2×2 max-pool + dropout(.25) → PyTorch flatten order, 1 B/elem argmax  (K-ELT)
+    conv2+pool  implicit GEMM (9 taps = 9 descriptors into one TMA slab) → tcgen05 → TMEM,
+                epilogue: +bias, ReLU, 2×2 max-pool, dropout(.25), 1 B/elem argmax code   (K-CONV)
     fc1         grouped tcgen05 GEMM, split-K, fp32 accumulate                        (K-GEMM)
     head        +bias ReLU dropout(.5) → fc2 → log-softmax/NLL/accuracy → dlogits
                 → fc2 grads → dh → fc1 bias grad; device-side loss/acc counters      (K-XENT)
@@ -93,7 +93,6 @@ class MnistCohortNet:
         bf = dict(dtype=torch.bfloat16, device=dev)
         self.w2p = torch.zeros(c, 64, 288, **bf)
         self.a1 = torch.zeros(c, self.rows, 32, **bf)
-        self.a2 = torch.zeros(c, self.rows, 64, **bf)
         self.p = torch.zeros(c, b, 9216, **bf)
         self.pidx = torch.zeros(c, b, 144, 64, dtype=torch.uint8, device=dev)
         self.hpre = torch.zeros(c, b, 128, dtype=torch.float32, device=dev)
@@ -160,11 +159,10 @@ class MnistCohortNet:
         self._check(lib.nfb_mnist_conv1_fwd(x.data_ptr(), xs, slots.data_ptr(), n,
                                             off["conv1.weight"], off["conv1.bias"], c, b,
                                             self.a1.data_ptr(), st), "conv1_fwd")
-        tc.conv3x3_fwd_persistent(self.a1, self.w2p, self._conv2_bias[g0:g1], self.a2, 26)
-        self._check(lib.nfb_mnist_pool_fwd(self.a2.data_ptr(), c, b, self.p1,
-                                           self.rng_state.data_ptr(), self.seed + 7 * g0,
-                                           self.p.data_ptr(), self.pidx.data_ptr(), st),
-                    "pool_fwd")
+        # conv2 + bias + ReLU + max-pool + dropout in one kernel: the 24x24x64 conv output
+        # (177 MB per step for 32 clients) never exists in memory
+        tc.conv3x3_pool_fwd(self.a1, self.w2p, self._conv2_bias[g0:g1], self.p, self.pidx, b, 26,
+                            self.p1, self.rng_state, self.seed + 7 * g0)
         self.hpre.zero_()
         tc.linear_fwd(self.fc1_w[g0:g1], self.p, self.hpre, k_split=self.k_split_fc)
         grads[:, : self._atomic_prefix].zero_()

@@ -147,6 +147,34 @@ def conv3x3_fwd_persistent(x, w, bias, out, width: int) -> None:
     _conv_persistent(0, x, w, out, width, bias, None)
 
 
+def conv3x3_pool_fwd(x, w, bias, pool_out, pool_idx, images: int, width: int, drop_p: float,
+                     rng_state, seed: int) -> None:
+    """conv3x3 (32→64) + bias + ReLU + 2×2 max-pool + dropout fused (``tc_conv.cu`` MODE 2).
+
+    x ``[C, B·26·26, 32]`` bf16 → ``pool_out [C, B, 9216]`` bf16 (PyTorch flatten order) and
+    ``pool_idx [C, B, 144, 64]`` uint8 codes; the conv output itself is never materialised.
+    """
+    lib = _lib()
+    if not getattr(lib, "_pool_declared", False):
+        ll = C.c_longlong
+        lib.nfb_tc_conv3x3_pool_fwd.restype = C.c_int
+        lib.nfb_tc_conv3x3_pool_fwd.argtypes = [C.c_void_p, ll, ll, C.c_void_p, ll, C.c_int, C.c_int,
+                                                C.c_int, C.c_void_p, ll, C.c_void_p, C.c_void_p,
+                                                C.c_float, C.c_void_p, C.c_ulonglong, C.c_void_p,
+                                                C.c_void_p]
+        lib._pool_declared = True
+    assert x.is_contiguous() and w.is_contiguous() and pool_out.is_contiguous()
+    st = status_word(x.device)
+    code = lib.nfb_tc_conv3x3_pool_fwd(
+        x.data_ptr(), x.shape[1], x.stride(0), w.data_ptr(), w.stride(0), x.shape[0], images, width,
+        bias.data_ptr() if bias is not None else None, bias.stride(0) if bias is not None else 0,
+        pool_out.data_ptr(), pool_idx.data_ptr(), float(drop_p),
+        rng_state.data_ptr() if rng_state is not None else None, seed, st.data_ptr(),
+        torch.cuda.current_stream(x.device).cuda_stream)
+    native._check(code, "tc_conv3x3_pool_fwd")
+    native._count()
+
+
 def conv3x3_dgrad_persistent(dy, w, out, width: int, relu_mask=None) -> None:
     """Same contract as ``conv3x3_dgrad``, persistent slab kernel (``tc_conv.cu``)."""
     _conv_persistent(1, dy, w, out, width, None, relu_mask)

@@ -79,6 +79,31 @@ def check_conv_fwd_p():
     return out.float(), (ref + bias[:, None, :]).relu()
 
 
+def check_conv_pool():
+    """Fused conv+bias+ReLU+maxpool (no dropout) vs F.conv2d + F.max_pool2d on NCHW."""
+    import torch.nn.functional as F
+    from nanofed_b200.ops import tc
+    c, b = 3, 5
+    r = b * W * W
+    x = _bf(c, r, 32)
+    w = _bf(c, 64, 288, scale=0.05)
+    bias = torch.randn(c, 64, device="cuda")
+    p = torch.zeros(c, b, 9216, device="cuda", dtype=torch.bfloat16)
+    idx = torch.zeros(c, b, 144, 64, device="cuda", dtype=torch.uint8)
+    tc.conv3x3_pool_fwd(x, w, bias, p, idx, b, W, 0.0, None, 0)
+    outs = []
+    for k in range(c):
+        xin = x[k].float().view(b, W, W, 32).permute(0, 3, 1, 2)            # NCHW
+        wk = w[k].float().view(64, 9, 32).permute(0, 2, 1).reshape(64, 32, 3, 3)
+        y = F.relu(F.conv2d(xin, wk, bias[k]))
+        y = y.bfloat16().float()        # the kernel pools bf16-rounded activations
+        outs.append(F.max_pool2d(y, 2).flatten(1))
+    ref = torch.stack(outs)
+    # argmax codes must point at a maximal element and carry the ReLU flag
+    assert int((idx & 8).min()) == 8, "keep bit must be set without dropout"
+    return p.float(), ref
+
+
 def check_conv_dgrad_p():
     from nanofed_b200.ops import tc
     c, b, cin, cout = 2, 5, 32, 64
@@ -151,7 +176,7 @@ def check_fc_wgrad():
     return got, torch.einsum("cbj,cbi->cji", dy.float(), x.float())
 
 
-CHECKS = {"conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
+CHECKS = {"conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
           "conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
           "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad,
           "fc_wgrad": check_fc_wgrad}
