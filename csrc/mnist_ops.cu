@@ -45,43 +45,60 @@ __global__ void __launch_bounds__(256)
     conv1_fwd_kernel(const float* __restrict__ x, int64_t x_cstride,
                      const float* __restrict__ slots, int64_t row_stride, int64_t w_off,
                      int64_t b_off, int B, __nv_bfloat16* __restrict__ a1) {
-  __shared__ __align__(16) float swt[9 * 32];  // [tap][co] so 8 channels of one tap are 2 x LDS.128
+  // item = (image row-pair slot: b, oh, ow-pair (13 per row), channel octet): two horizontally
+  // adjacent outputs share their 3x4 input window and every weight read (the kernel is
+  // LSU-bound: ncu showed l1tex at 88 % with one output per item).
+  __shared__ __align__(16) float swt[9 * 32];  // [tap][co]
   __shared__ float sb[32];
   const int c = blockIdx.y;
   const float* w = slots + c * row_stride + w_off;
   for (int i = threadIdx.x; i < 288; i += blockDim.x) swt[(i % 9) * 32 + i / 9] = w[i];
   if (threadIdx.x < 32) sb[threadIdx.x] = slots[c * row_stride + b_off + threadIdx.x];
   __syncthreads();
-  const int64_t items = static_cast<int64_t>(B) * kGrid * 4;  // (position, channel-octet)
+  const int64_t items = static_cast<int64_t>(B) * kG * 13 * 4;
   const float* xc = x + static_cast<int64_t>(c) * x_cstride;
   __nv_bfloat16* oc = a1 + static_cast<int64_t>(c) * B * kGrid * 32;
   for (int64_t it = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; it < items;
        it += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int oct = static_cast<int>(it & 3);
-    const int64_t pos = it >> 2;
-    const int b = static_cast<int>(pos / kGrid), q = static_cast<int>(pos % kGrid);
-    const int oh = q / kG, ow = q % kG;
+    const int64_t pr = it >> 2;                       // (b, oh, pair)
+    const int pair = static_cast<int>(pr % 13);
+    const int64_t rowi = pr / 13;                     // b * 26 + oh
+    const int b = static_cast<int>(rowi / kG), oh = static_cast<int>(rowi % kG);
+    const int ow = pair * 2;
     const float* px = xc + b * 784 + oh * 28 + ow;
-    float in[9];
+    float in[3][4];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const float2 lo = *reinterpret_cast<const float2*>(px + kh * 28);      // ow even => 8-B aligned
+      const float2 hi = *reinterpret_cast<const float2*>(px + kh * 28 + 2);
+      in[kh][0] = lo.x; in[kh][1] = lo.y; in[kh][2] = hi.x; in[kh][3] = hi.y;
+    }
+    float o0[8], o1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o0[j] = o1[j] = sb[oct * 8 + j];
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) in[kh * 3 + kw] = px[kh * 28 + kw];
-    float out[8];
+      for (int kw = 0; kw < 3; ++kw) {
+        const int t = kh * 3 + kw;
+        const float4 w0 = *reinterpret_cast<const float4*>(swt + t * 32 + oct * 8);
+        const float4 w1 = *reinterpret_cast<const float4*>(swt + t * 32 + oct * 8 + 4);
+        const float a = in[kh][kw], bb = in[kh][kw + 1];
+        o0[0] = fmaf(a, w0.x, o0[0]); o0[1] = fmaf(a, w0.y, o0[1]);
+        o0[2] = fmaf(a, w0.z, o0[2]); o0[3] = fmaf(a, w0.w, o0[3]);
+        o0[4] = fmaf(a, w1.x, o0[4]); o0[5] = fmaf(a, w1.y, o0[5]);
+        o0[6] = fmaf(a, w1.z, o0[6]); o0[7] = fmaf(a, w1.w, o0[7]);
+        o1[0] = fmaf(bb, w0.x, o1[0]); o1[1] = fmaf(bb, w0.y, o1[1]);
+        o1[2] = fmaf(bb, w0.z, o1[2]); o1[3] = fmaf(bb, w0.w, o1[3]);
+        o1[4] = fmaf(bb, w1.x, o1[4]); o1[5] = fmaf(bb, w1.y, o1[5]);
+        o1[6] = fmaf(bb, w1.z, o1[6]); o1[7] = fmaf(bb, w1.w, o1[7]);
+      }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) out[j] = sb[oct * 8 + j];
-#pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      const float4 w0 = *reinterpret_cast<const float4*>(swt + t * 32 + oct * 8);
-      const float4 w1 = *reinterpret_cast<const float4*>(swt + t * 32 + oct * 8 + 4);
-      out[0] = fmaf(in[t], w0.x, out[0]); out[1] = fmaf(in[t], w0.y, out[1]);
-      out[2] = fmaf(in[t], w0.z, out[2]); out[3] = fmaf(in[t], w0.w, out[3]);
-      out[4] = fmaf(in[t], w1.x, out[4]); out[5] = fmaf(in[t], w1.y, out[5]);
-      out[6] = fmaf(in[t], w1.z, out[6]); out[7] = fmaf(in[t], w1.w, out[7]);
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) out[j] = fmaxf(out[j], 0.f);
-    st_vec(oc + pos * 32 + oct * 8, pack<__nv_bfloat16>(out));
+    for (int j = 0; j < 8; ++j) { o0[j] = fmaxf(o0[j], 0.f); o1[j] = fmaxf(o1[j], 0.f); }
+    const int64_t pos = rowi * kG + ow;               // == b*676 + oh*26 + ow
+    st_vec(oc + pos * 32 + oct * 8, pack<__nv_bfloat16>(o0));
+    st_vec(oc + (pos + 1) * 32 + oct * 8, pack<__nv_bfloat16>(o1));
   }
 }
 
@@ -335,45 +352,49 @@ __global__ void __launch_bounds__(256)
     conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ da1, const float* __restrict__ x,
                        int64_t x_cstride, int B, float* __restrict__ grads, int64_t row_stride,
                        int64_t w_off, int64_t b_off) {
-  // lane = output channel (a warp reads one 64-byte NHWC row per position, fully used);
-  // warp w takes positions w, w+8, ...; four positions are in flight per thread.
-  // (A 16-byte-load / 80-accumulator variant measured slower: 80 us vs 68 us.)
+  // half-warp = one position (16 lanes x 2 channels, one 4-byte load each: a full 64-byte NHWC
+  // row); every x-window value read from shared memory feeds two channels (the one-channel
+  // version was LSU-bound: 9 LDS per 10 FMA, l1tex 73 % in ncu).  16 position slots per block.
   __shared__ float sx[784];
-  __shared__ float part[8][32][10];
+  __shared__ float part[16][32][10];
   const int b = blockIdx.x, c = blockIdx.y;
   const int64_t img = static_cast<int64_t>(c) * B + b;
   for (int i = threadIdx.x; i < 784; i += blockDim.x)
     sx[i] = x[c * x_cstride + static_cast<int64_t>(b) * 784 + i];
   __syncthreads();
-  const int co = threadIdx.x & 31, slice = threadIdx.x >> 5;
-  const __nv_bfloat16* d = da1 + img * kGrid * 32 + co;
-  float acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-  auto tap = [&](int q, float g) {
+  const int cp = threadIdx.x & 15, slot = threadIdx.x >> 4;     // channels 2cp, 2cp+1
+  const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(da1 + img * kGrid * 32) + cp;
+  float a0[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, a1[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  auto tap = [&](int q, __nv_bfloat162 gv) {
+    const float2 g = __bfloat1622float2(gv);
     const int oh = q / kG, ow = q % kG;
     const float* px = sx + oh * 28 + ow;
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) acc[kh * 3 + kw] = fmaf(g, px[kh * 28 + kw], acc[kh * 3 + kw]);
-    acc[9] += g;
+      for (int kw = 0; kw < 3; ++kw) {
+        const float xv = px[kh * 28 + kw];
+        a0[kh * 3 + kw] = fmaf(g.x, xv, a0[kh * 3 + kw]);
+        a1[kh * 3 + kw] = fmaf(g.y, xv, a1[kh * 3 + kw]);
+      }
+    a0[9] += g.x;
+    a1[9] += g.y;
   };
-  int q = slice;
-  for (; q + 24 < kGrid; q += 32) {
-    const float g0 = __bfloat162float(d[(q)*32]);
-    const float g1 = __bfloat162float(d[(q + 8) * 32]);
-    const float g2 = __bfloat162float(d[(q + 16) * 32]);
-    const float g3 = __bfloat162float(d[(q + 24) * 32]);
-    tap(q, g0); tap(q + 8, g1); tap(q + 16, g2); tap(q + 24, g3);
+  int q = slot;
+  for (; q + 48 < kGrid; q += 64) {                 // 4 positions in flight per thread
+    const __nv_bfloat162 g0 = d[(q)*16], g1 = d[(q + 16) * 16], g2 = d[(q + 32) * 16],
+                         g3 = d[(q + 48) * 16];
+    tap(q, g0); tap(q + 16, g1); tap(q + 32, g2); tap(q + 48, g3);
   }
-  for (; q < kGrid; q += 8) tap(q, __bfloat162float(d[q * 32]));
+  for (; q < kGrid; q += 16) tap(q, d[q * 16]);
 #pragma unroll
-  for (int t = 0; t < 10; ++t) part[slice][co][t] = acc[t];
+  for (int t = 0; t < 10; ++t) { part[slot][2 * cp][t] = a0[t]; part[slot][2 * cp + 1][t] = a1[t]; }
   __syncthreads();
   for (int i = threadIdx.x; i < 320; i += blockDim.x) {
     const int cc = i / 10, t = i % 10;
     float s = 0.f;
 #pragma unroll
-    for (int sl = 0; sl < 8; ++sl) s += part[sl][cc][t];
+    for (int sl = 0; sl < 16; ++sl) s += part[sl][cc][t];
     float* dst = grads + c * row_stride + (t < 9 ? w_off + cc * 9 + t : b_off + cc);
     atomicAdd(dst, s);
   }
@@ -399,7 +420,7 @@ int nfb_mnist_conv1_fwd(const float* x, int64_t x_cstride, const float* slots, i
                         int64_t w_off, int64_t b_off, int C, int B, void* a1, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(x && slots && a1 && C >= 1 && B >= 1, NFB_EINVAL, "mnist_conv1_fwd: bad argument");
-  const int64_t items = static_cast<int64_t>(B) * kGrid * 4;
+  const int64_t items = static_cast<int64_t>(B) * kG * 13 * 4;
   // ~8 items per thread: the per-block weight staging is amortised, and 148*8/C blocks per
   // client still fill the machine
   int bx = static_cast<int>((items + 2047) / 2048);
