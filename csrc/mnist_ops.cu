@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(256)
 // per-step dropout counter.
 // -------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024)
-    fc_head_kernel(const float* __restrict__ hpre, const int64_t* __restrict__ labels,
+    fc_head_kernel(float* __restrict__ hpre, const int64_t* __restrict__ labels,
                    int64_t label_stride, int B, const float* __restrict__ slots,
                    float* __restrict__ grads, int64_t row_stride, int64_t b1_off, int64_t w2_off,
                    int64_t b2_off, float drop_p, unsigned long long* __restrict__ rng_state,
@@ -257,10 +257,12 @@ __global__ void __launch_bounds__(1024)
   const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
 
   for (int i = threadIdx.x; i < 1280; i += blockDim.x) w2[i] = row[w2_off + i];
-  const float* hp = hpre + static_cast<int64_t>(c) * B * 128;
+  float* hp = hpre + static_cast<int64_t>(c) * B * 128;
   for (int i4 = threadIdx.x; i4 < B * 32; i4 += blockDim.x) {   // 4 elements per Philox draw
     const int i = i4 * 4;
     const float4 hv = *reinterpret_cast<const float4*>(hp + i);
+    // hpre is a split-K atomic accumulator: leave it zeroed for the next step's fc1 forward
+    *reinterpret_cast<float4*>(hp + i) = make_float4(0.f, 0.f, 0.f, 0.f);
     const float4 bv = *reinterpret_cast<const float4*>(row + b1_off + (i & 127));
     float v[4] = {fmaxf(hv.x + bv.x, 0.f), fmaxf(hv.y + bv.y, 0.f), fmaxf(hv.z + bv.z, 0.f),
                   fmaxf(hv.w + bv.w, 0.f)};
@@ -452,7 +454,7 @@ int nfb_mnist_pool_bwd(const void* dp, const uint8_t* pidx, int C, int B, float 
   return launch_status("mnist_pool_bwd");
 }
 
-int nfb_mnist_fc_head(const float* hpre, const int64_t* labels, int64_t label_stride, int C,
+int nfb_mnist_fc_head(float* hpre, const int64_t* labels, int64_t label_stride, int C,
                       int B, const float* slots, float* grads, int64_t row_stride,
                       int64_t b1_off, int64_t w2_off, int64_t b2_off, float drop_p,
                       void* rng_state, int advance_rng, uint64_t seed, void* dh, float* stats,

@@ -11,11 +11,13 @@ struct SgdArgs {
   int nesterov, first_step;
   const float* grad_scale;
   uint64_t seed, group0;
+  int64_t row_len;      // > 0: the flat buffer is [rows][row_len] ...
+  int64_t zero_prefix;  // ... and g[row][0 : zero_prefix) is zeroed after use (atomic accumulators)
 };
 
 template <typename G>
 __global__ void __launch_bounds__(256)
-    sgd_kernel(float* __restrict__ p, const G* __restrict__ g, float* __restrict__ mom,
+    sgd_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ mom,
                __nv_bfloat16* __restrict__ lowp, int64_t n, SgdArgs a) {
   const float gs = a.grad_scale ? *a.grad_scale : 1.f;
   const int64_t groups = (n + 3) >> 2;
@@ -32,6 +34,11 @@ __global__ void __launch_bounds__(256)
     }
 #pragma unroll
     for (int e = 0; e < 4; ++e) gv[e] = e < cnt ? to_f32(g[base + e]) * gs : 0.f;
+    if (a.zero_prefix > 0 && (base % a.row_len) < a.zero_prefix) {
+      // gradient entries that the next step accumulates into with atomics: hand them back zeroed
+      for (int e = 0; e < cnt; ++e)
+        if ((base + e) % a.row_len < a.zero_prefix) g[base + e] = from_f32<G>(0.f);
+    }
     if (a.noise_std > 0.f) {
       const float4 z = Philox::normal4(a.group0 + q, a.seed);
       gv[0] = fmaf(a.noise_std, z.x, gv[0]); gv[1] = fmaf(a.noise_std, z.y, gv[1]);
@@ -105,24 +112,26 @@ static int flat_grid(int64_t items) {
 
 }  // namespace nfb
 
-extern "C" int nfb_fused_sgd(float* p, const void* g, int g_dtype, float* momentum_buf,
+extern "C" int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf,
                              void* lowp_out, int64_t n, float lr, float momentum,
                              float dampening, float weight_decay, int nesterov, int first_step,
                              const float* grad_scale, float noise_std, uint64_t seed,
-                             uint64_t offset, void* stream) {
+                             uint64_t offset, int64_t row_len, int64_t zero_prefix, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
   NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
   NFB_REQUIRE((offset & 3u) == 0, NFB_EINVAL, "fused_sgd: offset must be a multiple of 4");
   if (n <= 0) return 0;
+  NFB_REQUIRE(zero_prefix == 0 || (row_len > 0 && zero_prefix <= row_len && n % row_len == 0),
+              NFB_EINVAL, "fused_sgd: bad row_len/zero_prefix");
   SgdArgs a{lr, momentum, dampening, weight_decay, noise_std, nesterov, first_step,
-            grad_scale, seed, offset >> 2};
+            grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix};
   float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
   cudaStream_t st = as_stream(stream);
   return dispatch_dtype(g_dtype, [&](auto tag) {
     using G = decltype(tag);
     sgd_kernel<G><<<flat_grid((n + 3) / 4), 256, 0, st>>>(
-        p, static_cast<const G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
+        p, static_cast<G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
     return launch_status("fused_sgd");
   });
 }

@@ -125,11 +125,15 @@ int nfb_bcast_global(const float* master, int64_t N, int64_t K, float* slots,
  * torch.optim.SGD / Adam(W) semantics on flat buffers, optional DP-SGD front end
  * (g' = g*grad_scale[0] + noise_std*z) and bf16 working-copy write-back.
  * Replaces the user-supplied optimizer (examples/mnist/run_experiment.py:70-73) and
- * clip + per-param noise of nanofed/trainer/private.py:54-86.                       */
-int nfb_fused_sgd(float* p, const void* g, int g_dtype, float* momentum_buf, void* lowp_out,
+ * clip + per-param noise of nanofed/trainer/private.py:54-86.
+ * row_len / zero_prefix: when zero_prefix > 0 the buffers are [n/row_len][row_len] and
+ * g[r][0:zero_prefix) is set to zero after it has been consumed (gradient entries that the next
+ * step accumulates into with atomics); pass 0, 0 otherwise.                               */
+int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf, void* lowp_out,
                   int64_t n, float lr, float momentum, float dampening, float weight_decay,
                   int nesterov, int first_step, const float* grad_scale, float noise_std,
-                  uint64_t seed, uint64_t offset, void* stream);
+                  uint64_t seed, uint64_t offset, int64_t row_len, int64_t zero_prefix,
+                  void* stream);
 int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg, float* exp_avg_sq,
                    void* lowp_out, int64_t n, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float bias_corr1, float bias_corr2, int decoupled,

@@ -135,11 +135,17 @@ class MnistCohortNet:
         cfg, a = self.cfg, self.arena
         for g0 in range(0, self.c_all, self.group):
             self._step_group(step, g0)
-        # ---- optimiser: one fused launch over all clients ----
+        self._apply_optimizer(step)
+
+    def _apply_optimizer(self, step: int) -> None:
+        """One fused K-OPT launch over all clients; also hands the atomically accumulated
+        gradient entries (conv1.*, conv2.*) back zeroed for the next step."""
+        cfg, a = self.cfg, self.arena
         ops.fused_sgd_(a.slots.view(-1), self.grads.view(-1), cfg.learning_rate,
                        momentum_buf=None if a.momentum is None else a.momentum.view(-1),
                        momentum=cfg.momentum, weight_decay=cfg.weight_decay,
-                       first_step=(step == 0), lowp_out=a.slots_lowp.view(-1))
+                       first_step=(step == 0), lowp_out=a.slots_lowp.view(-1),
+                       row_len=self.n_total, zero_grad_prefix=self._atomic_prefix)
 
     def _step_group(self, step: int, g0: int) -> None:
         cfg, a, lib = self.cfg, self.arena, self.lib
@@ -163,9 +169,8 @@ class MnistCohortNet:
         # (177 MB per step for 32 clients) never exists in memory
         tc.conv3x3_pool_fwd(self.a1, self.w2p, self._conv2_bias[g0:g1], self.p, self.pidx, b, 26,
                             self.p1, self.rng_state, self.seed + 7 * g0)
-        self.hpre.zero_()
+        # (hpre and the atomic gradient prefix arrive zeroed: fc_head / K-OPT clear them after use)
         tc.linear_fwd(self.fc1_w[g0:g1], self.p, self.hpre, k_split=self.k_split_fc)
-        grads[:, : self._atomic_prefix].zero_()
         last = 1 if g1 >= self.c_all else 0
         self._check(lib.nfb_mnist_fc_head(self.hpre.data_ptr(), y.data_ptr(), y.stride(0), c, b,
                                           slots.data_ptr(), grads.data_ptr(), n, off["fc1.bias"],

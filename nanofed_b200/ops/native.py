@@ -117,7 +117,7 @@ def _declare(L: C.CDLL) -> None:
                               _vp, _u64, _u64, _vp, _vp, _i32, _i32, _vp, _vp],
         "nfb_bcast_global": [_vp, _i64, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
         "nfb_fused_sgd": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
-                          _vp, _f32, _u64, _u64, _vp],
+                          _vp, _f32, _u64, _u64, _i64, _i64, _vp],
         "nfb_fused_adam": [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32,
                            _f32, _f32, _i32, _vp, _vp],
         "nfb_xent_fused": [_vp, _i32, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _f32, _vp, _vp,
@@ -332,6 +332,8 @@ def fused_sgd_(
     seed: int = 0,
     offset: int = 0,
     lowp_out: torch.Tensor | None = None,
+    row_len: int = 0,
+    zero_grad_prefix: int = 0,
 ) -> torch.Tensor:
     assert p.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous()
     assert p.numel() == g.numel()
@@ -344,7 +346,7 @@ def fused_sgd_(
             p.data_ptr(), g.data_ptr(), _dt(g), _ptr(momentum_buf), _ptr(lowp_out), p.numel(),
             float(lr), float(momentum), float(dampening), float(weight_decay),
             1 if nesterov else 0, 1 if first_step else 0, _ptr(grad_scale), float(noise_std),
-            seed & (2**64 - 1), offset, _stream(p),
+            seed & (2**64 - 1), offset, int(row_len), int(zero_grad_prefix), _stream(p),
         ),
         "fused_sgd",
     )

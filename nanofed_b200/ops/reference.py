@@ -176,6 +176,8 @@ def fused_sgd_(
     seed: int = 0,
     offset: int = 0,
     lowp_out: torch.Tensor | None = None,
+    row_len: int = 0,
+    zero_grad_prefix: int = 0,
 ) -> torch.Tensor:
     """torch.optim.SGD semantics on flat buffers, with optional DP-SGD pre-processing.
 
@@ -199,6 +201,8 @@ def fused_sgd_(
     p.add_(gf.to(p.dtype), alpha=-lr)
     if lowp_out is not None:
         lowp_out.copy_(p.to(lowp_out.dtype))
+    if zero_grad_prefix > 0:
+        g.view(-1, row_len)[:, :zero_grad_prefix] = 0
     return p
 
 

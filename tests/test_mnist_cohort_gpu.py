@@ -35,9 +35,14 @@ def test_one_step_matches_autograd():
 
     cfg, model, layout, arena, shards, eng = _setup()
     c, b = cfg.clients_per_gpu, cfg.batch_size
-    eng.step(0)
+    eng._step_group(0, 0)                  # forward + backward: gradients only
     torch.cuda.synchronize()
     tc.check_status(arena.device)
+    grads_before_opt = eng.grads.clone()
+    eng._apply_optimizer(0)                # fused SGD (and it zeroes the atomic gradient prefix)
+    torch.cuda.synchronize()
+    assert float(eng.grads[:, : eng._atomic_prefix].abs().sum()) == 0.0
+    assert float(eng.hpre.abs().sum()) == 0.0      # split-K accumulator handed back clean
     ref = model.cuda().eval()
     for k in range(c):
         x, y = shards.images[k, :b], shards.labels[k, :b]
@@ -51,7 +56,7 @@ def test_one_step_matches_autograd():
         out = ref(x)
         loss = F.cross_entropy(out, y)
         loss.backward()
-        got = layout.views(eng.grads[k])
+        got = layout.views(grads_before_opt[k])
         for name, p in ref.named_parameters():
             g, r = got[name].float(), p.grad
             rel = (g - r).norm() / (r.norm() + 1e-12)
