@@ -43,8 +43,10 @@ class PrivateTrainer(TorchTrainer):
         accountant: GaussianAccountant | None = None,
         noise_generator: GaussianNoiseGenerator | None = None,
         callbacks: list[Callback] | None = None,
+        per_sample_clipping: bool = False,
     ) -> None:
         super().__init__(training_config, callbacks)
+        self._per_sample = per_sample_clipping
         self._privacy_config = privacy_config
         self._accountant = accountant or GaussianAccountant(privacy_config)
         self._noise_gen = noise_generator or GaussianNoiseGenerator()
@@ -80,8 +82,85 @@ class PrivateTrainer(TorchTrainer):
         self._clip_gradients(model)
         self._add_noise(model, batch_size)
 
+    # -- per-sample clipping (north-star extension, K-PSGN) ---------------------------------
+    def per_sample_grad_norms(
+        self, model: nn.Module, data: torch.Tensor, target: torch.Tensor
+    ) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+        """``(norms [B], per-sample losses [B], output)`` WITHOUT materialising per-sample
+        gradients ("ghost norms").  For ``nn.Linear`` ``‖∂L_i/∂W‖² = ‖a_i‖²‖δ_i‖²`` (hand-written
+        kernel ``ops.linear_per_sample_grad_sqnorms``); for ``nn.Conv2d`` the Frobenius product of
+        the unfolded-input and output-gradient Gram matrices.  Other parametrised layers are
+        rejected (their per-sample gradients need the full Jacobian).  The autograd graph is
+        kept so the caller can run the re-weighted second backward."""
+        import torch.nn.functional as F
+
+        from nanofed_b200 import ops
+
+        acts: dict[nn.Module, torch.Tensor] = {}
+        sq = torch.zeros(len(data), device=data.device, dtype=torch.float32)
+        handles = []
+
+        def fwd_hook(mod, inputs, _out):
+            acts[mod] = inputs[0].detach()
+
+        armed = {"on": True}   # hooks baked into the retained graph fire again on the 2nd backward
+
+        def bwd_hook(mod, _gin, gout):
+            nonlocal sq
+            if not armed["on"] or mod not in acts:
+                return
+            a, d = acts.pop(mod), gout[0].detach()
+            if isinstance(mod, nn.Linear):
+                if a.dim() != 2:
+                    a2, d2 = a.flatten(1, -2), d.flatten(1, -2)       # [B, T, in] sequences
+                    sq = sq + ops.conv_per_sample_grad_sqnorms(a2, d2, bias=mod.bias is not None)
+                else:
+                    sq = sq + ops.linear_per_sample_grad_sqnorms(a, d, bias=mod.bias is not None)
+            else:  # Conv2d
+                if mod.groups != 1:
+                    raise NotImplementedError("per-sample clipping: grouped convolutions")
+                unf = F.unfold(a, mod.kernel_size, mod.dilation, mod.padding, mod.stride)
+                sq = sq + ops.conv_per_sample_grad_sqnorms(
+                    unf.transpose(1, 2), d.flatten(2).transpose(1, 2), bias=mod.bias is not None)
+
+        for mod in model.modules():
+            own = [p for p in mod.parameters(recurse=False) if p.requires_grad]
+            if not own:
+                continue
+            if not isinstance(mod, (nn.Linear, nn.Conv2d)):
+                raise NotImplementedError(
+                    f"per-sample clipping supports Linear and Conv2d layers, found {type(mod).__name__}")
+            handles.append(mod.register_forward_hook(fwd_hook))
+            handles.append(mod.register_full_backward_hook(bwd_hook))
+        try:
+            output = model(data)
+            losses = F.cross_entropy(output, target, reduction="none")
+            losses.sum().backward(retain_graph=True)
+        finally:
+            armed["on"] = False
+            for h in handles:
+                h.remove()
+        return sq.clamp_min(0).sqrt(), losses, output
+
+    def _per_sample_step(self, model, data, target, optimizer):
+        cfg = self._privacy_config
+        optimizer.zero_grad(set_to_none=True)
+        norms, losses, output = self.per_sample_grad_norms(model, data, target)
+        coef = (cfg.max_gradient_norm / (norms + 1e-6)).clamp(max=1.0)
+        optimizer.zero_grad(set_to_none=True)
+        (losses * coef.detach()).sum().backward()            # Σ_i c_i ∇L_i, one more backward
+        batch = len(data)
+        self._add_noise(model, batch)                          # N(0, (σC)²) on the clipped SUM
+        for p in model.parameters():
+            if p.grad is not None:
+                p.grad.div_(batch)
+        optimizer.step()
+        return losses.detach().mean(), output
+
     # -- training ------------------------------------------------------------
     def _step(self, model, data, target, optimizer):  # type: ignore[override]
+        if self._per_sample:
+            return self._per_sample_step(model, data, target, optimizer)
         optimizer.zero_grad(set_to_none=True)
         output = model(data)
         loss = self.compute_loss(output, target)

@@ -124,3 +124,32 @@ def test_logger_context_is_per_task_and_log_exec_times(caplog):
         return x * 2
 
     assert f(1) == 2 and asyncio.run(g(2)) == 4
+
+
+def test_per_sample_clipping_matches_explicit_per_sample_gradients():
+    torch.manual_seed(0)
+    model = nn.Sequential(nn.Conv2d(1, 4, 3), nn.ReLU(), nn.Flatten(), nn.Linear(4 * 6 * 6, 5))
+    x, y = torch.randn(6, 1, 8, 8), torch.randint(0, 5, (6,))
+    cfg = PrivacyConfig(max_gradient_norm=0.7, noise_multiplier=1e-9)       # ~no noise
+    t = PrivateTrainer(TrainingConfig(1, 6, 0.1), cfg, per_sample_clipping=True)
+    norms, _, _ = t.per_sample_grad_norms(model, x, y)
+    # explicit per-sample gradients
+    explicit, clipped_sum = [], [torch.zeros_like(p) for p in model.parameters()]
+    for i in range(6):
+        model.zero_grad()
+        nn.functional.cross_entropy(model(x[i : i + 1]), y[i : i + 1]).backward()
+        g = [p.grad.clone() for p in model.parameters()]
+        n = torch.sqrt(sum(v.pow(2).sum() for v in g))
+        explicit.append(n)
+        c = min(0.7 / (float(n) + 1e-6), 1.0)
+        for acc, v in zip(clipped_sum, g):
+            acc += c * v
+    torch.testing.assert_close(norms, torch.stack(explicit), rtol=1e-4, atol=1e-5)
+    before = [p.detach().clone() for p in model.parameters()]
+    opt = torch.optim.SGD(model.parameters(), lr=1.0)
+    model.zero_grad()
+    t.train_batch(model, (x, y), opt)
+    for p, b0, g in zip(model.parameters(), before, clipped_sum):
+        torch.testing.assert_close(b0 - p.detach(), g / 6, rtol=1e-3, atol=1e-5)
+    with pytest.raises(NotImplementedError):
+        t.per_sample_grad_norms(nn.Sequential(nn.Flatten(), nn.Linear(64, 5), nn.LayerNorm(5)), x, y)
