@@ -1,0 +1,88 @@
+"""Worker for tests/test_multi_gpu.py (launched by torch.distributed.run, one rank per GPU).
+
+Checks, on real peer memory:
+  1. PeerReducer (fused reduce + FedAvg epilogue + all-gather kernel) == NcclReducer baseline,
+     with and without the DP path, on repeated calls; every rank ends with identical bits.
+  2. A FedSimulation round with transport="peer" equals the same round with transport="nccl".
+Exits non-zero on any mismatch.
+"""
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+import torch
+import torch.distributed as dist
+
+from nanofed_b200 import ops
+from nanofed_b200.models import MNISTModel
+from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+from nanofed_b200.parallel.peer import NcclReducer, PeerReducer
+from nanofed_b200.runtime import dist as rdist
+from nanofed_b200.runtime.arena import Arena
+from nanofed_b200.runtime.flat import FlatLayout
+
+
+def fail(msg):
+    print(f"[rank {rdist_info.rank}] FAIL: {msg}", flush=True)
+    sys.exit(1)
+
+
+rdist_info = rdist.init()
+info, dev = rdist_info, rdist_info.device
+layout = FlatLayout.from_module(MNISTModel())
+C = 4
+
+
+def make_arena():
+    torch.manual_seed(100 + info.rank)
+    a = Arena(layout, C, dev, with_grads=False)
+    a.slots.normal_(0, 0.02)
+    a.counts.copy_(torch.randint(1, 500, (C,), device=dev).float())
+    a.mask[info.rank % C] = 0
+    return a
+
+
+ref_arena, peer_arena = make_arena(), make_arena()
+nccl = NcclReducer(ref_arena, info)
+peer = PeerReducer(peer_arena, info, use_multicast=False)
+for dp in (False, True):
+    kw = {}
+    if dp:
+        ss, _ = ops.update_stats(ref_arena.slots)
+        kw = dict(sumsq=ss, clip_norm=1.0, noise_std=0.01, noise_mask=ref_arena.noise_mask,
+                  seed=5, offset=64)
+    nccl.reduce(ref_arena, **kw)
+    for _ in range(3):
+        peer.reduce(peer_arena, **kw)
+    torch.cuda.synchronize()
+    peer.check()
+    scale = ref_arena.master.abs().max().item()
+    err = (peer_arena.master - ref_arena.master).abs().max().item()
+    if not err <= 1e-5 * max(scale, 1.0) + 1e-6:
+        fail(f"dp={dp}: fused kernel differs from NCCL baseline by {err:.3e}")
+    gathered = [torch.zeros_like(peer_arena.master) for _ in range(info.world_size)]
+    dist.all_gather(gathered, peer_arena.master)
+    if not all(torch.equal(g, gathered[0]) for g in gathered):
+        fail(f"dp={dp}: ranks hold different global models")
+    if not torch.equal(peer_arena.master_lowp, peer_arena.master.bfloat16()):
+        fail(f"dp={dp}: bf16 copy is not the rounded master")
+
+# 2. full simulated rounds, peer vs nccl transport
+states = {}
+for transport in ("peer", "nccl"):
+    cfg = CohortConfig(model="mnist_cnn", clients_per_gpu=2, samples_per_client=64, batch_size=32,
+                       local_epochs=1, learning_rate=0.05, seed=11, transport=transport)
+    sim = FedSimulation(cfg)
+    for _ in range(2):
+        out = sim.run_round()
+    loss = out.agg_metrics["loss"]
+    if not (loss == loss):
+        fail(f"{transport}: NaN loss")
+    states[transport] = sim.arena.master.clone()
+d = (states["peer"] - states["nccl"]).abs().max().item()
+if d > 2e-4:
+    fail(f"peer vs nccl transports diverge after 2 rounds: {d:.3e}")
+if info.is_main:
+    print(f"MULTI_GPU_OK world={info.world_size} transport_diff={d:.2e}", flush=True)
+rdist.shutdown()
