@@ -13,6 +13,7 @@ struct SgdArgs {
   uint64_t seed, group0;
   int64_t row_len;      // > 0: the flat buffer is [rows][row_len] ...
   int64_t zero_prefix;  // ... and g[row][0 : zero_prefix) is zeroed after use (atomic accumulators)
+  int64_t skip_lo, skip_len;  // columns [skip_lo, skip_lo + skip_len) of every row are left alone
 };
 
 template <typename G>
@@ -20,10 +21,17 @@ __global__ void __launch_bounds__(256)
     sgd_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ mom,
                __nv_bfloat16* __restrict__ lowp, int64_t n, SgdArgs a) {
   const float gs = a.grad_scale ? *a.grad_scale : 1.f;
-  const int64_t groups = (n + 3) >> 2;
+  // with a skipped column range the thread index runs over the remaining columns only
+  const int64_t eff_row = a.row_len - a.skip_len;
+  const int64_t groups = a.skip_len > 0 ? (n / a.row_len) * (eff_row >> 2) : (n + 3) >> 2;
   for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < groups;
        q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int64_t base = q << 2;
+    int64_t base = q << 2;
+    if (a.skip_len > 0) {
+      const int64_t row = base / eff_row;
+      const int64_t col = base - row * eff_row;
+      base = row * a.row_len + (col < a.skip_lo ? col : col + a.skip_len);
+    }
     const int cnt = (n - base) >= 4 ? 4 : static_cast<int>(n - base);
     float pv[4], gv[4], mv[4] = {0, 0, 0, 0};
     if (cnt == 4) {
@@ -40,7 +48,7 @@ __global__ void __launch_bounds__(256)
         if ((base + e) % a.row_len < a.zero_prefix) g[base + e] = from_f32<G>(0.f);
     }
     if (a.noise_std > 0.f) {
-      const float4 z = Philox::normal4(a.group0 + q, a.seed);
+      const float4 z = Philox::normal4(a.group0 + (base >> 2), a.seed);
       gv[0] = fmaf(a.noise_std, z.x, gv[0]); gv[1] = fmaf(a.noise_std, z.y, gv[1]);
       gv[2] = fmaf(a.noise_std, z.z, gv[2]); gv[3] = fmaf(a.noise_std, z.w, gv[3]);
     }
@@ -112,11 +120,12 @@ static int flat_grid(int64_t items) {
 
 }  // namespace nfb
 
-extern "C" int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf,
-                             void* lowp_out, int64_t n, float lr, float momentum,
-                             float dampening, float weight_decay, int nesterov, int first_step,
-                             const float* grad_scale, float noise_std, uint64_t seed,
-                             uint64_t offset, int64_t row_len, int64_t zero_prefix, void* stream) {
+static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, void* lowp_out,
+                          int64_t n, float lr, float momentum, float dampening,
+                          float weight_decay, int nesterov, int first_step,
+                          const float* grad_scale, float noise_std, uint64_t seed,
+                          uint64_t offset, int64_t row_len, int64_t zero_prefix, int64_t skip_lo,
+                          int64_t skip_hi, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
   NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
@@ -124,16 +133,49 @@ extern "C" int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf
   if (n <= 0) return 0;
   NFB_REQUIRE(zero_prefix == 0 || (row_len > 0 && zero_prefix <= row_len && n % row_len == 0),
               NFB_EINVAL, "fused_sgd: bad row_len/zero_prefix");
+  const int64_t skip_len = skip_hi - skip_lo;
+  NFB_REQUIRE(skip_len == 0 ||
+                  (row_len > 0 && n % row_len == 0 && skip_lo >= 0 && skip_len > 0 &&
+                   skip_hi <= row_len && ((row_len | skip_lo | skip_len) & 3) == 0),
+              NFB_EINVAL, "fused_sgd: skipped range must lie in a row, multiples of 4");
   SgdArgs a{lr, momentum, dampening, weight_decay, noise_std, nesterov, first_step,
-            grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix};
+            grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix, skip_lo,
+            skip_len};
   float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
   cudaStream_t st = as_stream(stream);
+  const int64_t work = skip_len > 0 ? (n / row_len) * (row_len - skip_len) : n;
+  if (work <= 0) return 0;
   return dispatch_dtype(g_dtype, [&](auto tag) {
     using G = decltype(tag);
-    sgd_kernel<G><<<flat_grid((n + 3) / 4), 256, 0, st>>>(
+    sgd_kernel<G><<<flat_grid((work + 3) / 4), 256, 0, st>>>(
         p, static_cast<G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
     return launch_status("fused_sgd");
   });
+}
+
+extern "C" int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf,
+                             void* lowp_out, int64_t n, float lr, float momentum,
+                             float dampening, float weight_decay, int nesterov, int first_step,
+                             const float* grad_scale, float noise_std, uint64_t seed,
+                             uint64_t offset, int64_t row_len, int64_t zero_prefix, void* stream) {
+  return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
+                        weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
+                        row_len, zero_prefix, 0, 0, stream);
+}
+
+// Same update, except that columns [skip_lo, skip_hi) of every row are not touched (neither
+// read nor written): they belong to a parameter whose update was already applied by the kernel
+// that produced its gradient (nfb_tc_linear_wgrad_sgd).
+extern "C" int nfb_fused_sgd_skip(float* p, void* g, int g_dtype, float* momentum_buf,
+                                  void* lowp_out, int64_t n, float lr, float momentum,
+                                  float dampening, float weight_decay, int nesterov,
+                                  int first_step, const float* grad_scale, float noise_std,
+                                  uint64_t seed, uint64_t offset, int64_t row_len,
+                                  int64_t zero_prefix, int64_t skip_lo, int64_t skip_hi,
+                                  void* stream) {
+  return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
+                        weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
+                        row_len, zero_prefix, skip_lo, skip_hi, stream);
 }
 
 extern "C" int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg,

@@ -52,10 +52,14 @@ struct GemmArgs {
   int m_valid, n_valid;
   int vec_store;     // n contiguous (out_ns == 1), non-atomic, 16-byte aligned rows
   int tma_store;     // stage 32-row x 128-byte chunks in smem and write them with TMA (map_o)
+  float sgd_lr, sgd_wd;  // EPI == 1: w <- w - lr * (acc + wd * w), w addressed by map_o
   int* status;       // set to 1 if a pipeline wait timed out
 };
 
-template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES>
+// EPI: 0 = store / accumulate the product, 1 = the product is a weight gradient that is applied
+// to the fp32 master weights in the epilogue (SGD) and never written to memory.
+template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES,
+          int EPI = 0>
 struct Cfg {
   static constexpr int A_TILE = BM * BK * 2;                 // bytes
   static constexpr int B_TILE = BN * BK * 2;
@@ -65,13 +69,16 @@ struct Cfg {
   static constexpr int TMEM_NEED = BN * TPS;
   static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64
                                    : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
-  static constexpr int STAGING = 4 * 4096;                   // 4 epilogue warps x [32 rows x 128 B]
+  // 4 epilogue warps x [32 rows x 128 B]; EPI 1: two weight buffers per warp (load c+1 while
+  // c is updated) plus a [32 rows x 64 B] bf16 tile per warp
+  static constexpr int STAGING = EPI == 1 ? 4 * (2 * 4096 + 2048) : 4 * 4096;
   static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + STAGING + 1024 /*align*/ + 256;
   static_assert(A_MN || A_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
   static_assert(B_MN || B_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
   static_assert(A_TILE % 1024 == 0 && B_TILE % 1024 == 0, "tiles must keep 1024-B alignment");
   static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N");
   static_assert(TMEM_NEED <= 512, "TMEM columns");
+  static_assert(EPI == 0 || (TPS == 1 && BN % 32 == 0), "SGD epilogue: one accumulator, 32-col chunks");
 };
 
 template <bool MN, int SWZ, int BK_, int ROWS>
@@ -100,12 +107,14 @@ __device__ __forceinline__ uint64_t operand_desc(uint32_t tile_addr, int kk) {
 }
 
 template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES,
-          int MINB = 1>
+          int MINB = 1, int EPI = 0>
 __global__ void __launch_bounds__(256, MINB)
     tc_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                    const __grid_constant__ CUtensorMap map_b,
-                   const __grid_constant__ CUtensorMap map_o, const GemmArgs args) {
-  using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
+                   const __grid_constant__ CUtensorMap map_o,
+                   const __grid_constant__ CUtensorMap map_l,   // EPI 1: bf16 copy of the weights
+                   const GemmArgs args) {
+  using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES, EPI>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -114,6 +123,7 @@ __global__ void __launch_bounds__(256, MINB)
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* acc_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+  uint64_t* w_bar = acc_bar + 2;                        // EPI 1: [4 warps][2 buffers]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -137,6 +147,11 @@ __global__ void __launch_bounds__(256, MINB)
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(acc_bar, 1);
+    if constexpr (EPI == 1) {
+      prefetch_tmap(&map_o);
+      prefetch_tmap(&map_l);
+      for (int i = 0; i < 8; ++i) mbar_init(&w_bar[i], 1);
+    }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
@@ -204,12 +219,86 @@ __global__ void __launch_bounds__(256, MINB)
     const int sub = warp - 4;                 // TMEM sub-partition == warp % 4
     const int m = m0 + sub * 32 + lane;       // this thread's output row
     bool ok = true;
+    [[maybe_unused]] int sgd_chunks = 0;
+    if constexpr (EPI == 1) {
+      // the weight tiles do not depend on the MMA: start fetching the first two 32-column
+      // chunks of this warp's 32 rows before waiting for the accumulator
+      sgd_chunks = min(BN, args.n_valid - n0) / 32;
+      if (lane == 0) {
+        for (int c = 0; c < 2 && c < sgd_chunks; ++c) {
+          mbar_expect_tx(&w_bar[sub * 2 + c], 4096);
+          tma_load_3d(staging + sub * 8192 + c * 4096, &map_o, &w_bar[sub * 2 + c], n0 + c * 32,
+                      m0 + sub * 32, g);
+        }
+      }
+    }
     if (n_iters > 0) ok = mbar_wait(acc_bar, 0);
     if (!ok && lane == 0) *args.status = 1;
     tc_fence_after();
     const bool row_ok = ok && n_iters > 0 && m < args.m_valid;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
-    if (args.tma_store) {
+    if constexpr (EPI == 1) {
+      // ---- weight gradient applied in place: w <- w - lr * (dW + wd * w) ----
+      // Per 32-column chunk: the fp32 weights arrive by TMA in a 128-byte-swizzled [32 x 128 B]
+      // buffer, each thread updates its own row in place, and the same buffer is the source of
+      // the TMA store back; the bf16 working copy goes out through a 64-byte-swizzled tile.
+      // The gradient itself never reaches memory.
+      uint8_t* lstage = staging + 4 * 8192 + sub * 2048;
+      const float lr = args.sgd_lr, wd = args.sgd_wd;
+      const bool live = ok && n_iters > 0;
+#pragma unroll 1
+      for (int c = 0; c < sgd_chunks; ++c) {
+        const int buf = c & 1;
+        uint8_t* wbuf = staging + sub * 8192 + buf * 4096;
+        uint32_t r[32];
+        __syncwarp();                         // lane 0 may come late from the refill below
+        tmem_ld_32x32b_x16(lane_addr + c * 32, r);
+        tmem_ld_32x32b_x16(lane_addr + c * 32 + 16, r + 16);
+        tmem_ld_wait();
+        if (!mbar_wait(&w_bar[sub * 2 + buf], (c >> 1) & 1)) { *args.status = 1; break; }
+        // bf16 tile of the previous chunk must have been read by its store before we overwrite it
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+        float nw[32];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          uint8_t* addr = wbuf + lane * 128 + ((p ^ (lane & 7)) * 16);
+          float w4[4];
+          unpack<float>(*reinterpret_cast<const uint4*>(addr), w4);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float gr = fmaf(wd, w4[e], __uint_as_float(r[4 * p + e]));
+            nw[4 * p + e] = fmaf(-lr, gr, w4[e]);
+          }
+          st_vec(addr, pack<float>(nw + 4 * p));
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          st_vec(lstage + lane * 64 + ((q ^ ((lane >> 1) & 3)) * 16), pack<__nv_bfloat16>(nw + 8 * q));
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0 && live) {
+          asm volatile(
+              "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                  &map_o),
+              "r"(smem_u32(wbuf)), "r"(n0 + c * 32), "r"(m0 + sub * 32), "r"(g)
+              : "memory");
+          asm volatile(
+              "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                  &map_l),
+              "r"(smem_u32(lstage)), "r"(n0 + c * 32), "r"(m0 + sub * 32), "r"(g)
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          if (c + 2 < sgd_chunks) {
+            // refill this buffer with chunk c+2 once the store above has read it
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            mbar_expect_tx(&w_bar[sub * 2 + buf], 4096);
+            tma_load_3d(wbuf, &map_o, &w_bar[sub * 2 + buf], n0 + (c + 2) * 32, m0 + sub * 32, g);
+          }
+        }
+      }
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    } else if (args.tma_store) {
       // Row-per-thread global stores touch 32 different lines per instruction; instead each
       // warp stages [32 rows x 128 B] chunks in swizzled shared memory (conflict-free 16-byte
       // stores) and a bulk tensor store writes them as whole lines.
@@ -429,17 +518,46 @@ static int get_out_map(void* ptr, long long n, long long m, long long groups, lo
   return 0;
 }
 
+// bf16 [groups][m rows][n cols] map with box [32 cols, 32 rows] and 64-byte swizzle: the working
+// copy of the weights written by the SGD epilogue.
+static int get_lowp_map(void* ptr, long long n, long long m, long long groups, long long ms,
+                        long long gs, CUtensorMap* out) {
+  MapKey key{ptr, n, m, groups, ms, gs, -16, 32, 64};
+  std::lock_guard<std::mutex> lock(g_maps_mu);
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) { *out = it->second; return 0; }
+  EncodeFn enc = encode_fn();
+  if (!enc) return fail(NFB_ESTATE, "tc_gemm: cuTensorMapEncodeTiled unavailable");
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(n), static_cast<cuuint64_t>(m),
+                        static_cast<cuuint64_t>(groups)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ms) * 2, static_cast<cuuint64_t>(gs) * 2};
+  if (groups == 1) strides[1] = static_cast<cuuint64_t>(m) * strides[0];
+  if ((strides[0] & 15) || (strides[1] & 15) || (reinterpret_cast<uintptr_t>(ptr) & 15))
+    return fail(NFB_EINVAL, "tc_gemm: bf16 weight copy must be 16-byte aligned");
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap ml;
+  CUresult r = enc(&ml, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ptr, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(NFB_EINVAL, "tc_gemm: bf16 weight map rejected (%d)",
+                                     static_cast<int>(r));
+  g_maps[key] = ml;
+  *out = ml;
+  return 0;
+}
+
 template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES,
-          int MINB = 1>
+          int MINB = 1, int EPI = 0>
 static int launch(const Operand& a, const Operand& b, int m_tiles, int n_tiles, int groups,
-                  GemmArgs args, cudaStream_t st) {
-  using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES>;
-  CUtensorMap ma, mb, mo;
+                  GemmArgs args, cudaStream_t st, void* lowp = nullptr, long long lowp_gs = 0) {
+  using C = Cfg<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES, EPI>;
+  CUtensorMap ma, mb, mo, ml;
   int rc = A_MN ? get_map(a, C::A_ATOM, BK, A_SWZ, &ma) : get_map(a, BK, BM, A_SWZ, &ma);
   if (rc) return rc;
   rc = B_MN ? get_map(b, C::B_ATOM, BK, B_SWZ, &mb) : get_map(b, BK, BN, B_SWZ, &mb);
   if (rc) return rc;
-  auto kern = tc_gemm_kernel<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES, MINB>;
+  auto kern = tc_gemm_kernel<A_MN, A_SWZ, B_MN, B_SWZ, BK, BN, TPS, STAGES, MINB, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -453,13 +571,21 @@ static int launch(const Operand& a, const Operand& b, int m_tiles, int n_tiles, 
   args.tma_store = (args.vec_store && TPS == 1 && args.k_split == 1 && !args.mask_src &&
                     BN % chunk_cols == 0 && getenv("NFB_GEMM_NO_TMA_STORE") == nullptr) ? 1 : 0;
   mo = ma;
+  ml = ma;
+  if constexpr (EPI == 1) {
+    if (!args.tma_store || args.out_bf16 || !lowp || args.n_valid % 32)
+      return fail(NFB_EINVAL, "tc_gemm: SGD epilogue needs a dense fp32 [m][n] weight tile, "
+                              "n a multiple of 32, and a bf16 copy");
+    rc = get_lowp_map(lowp, args.n_valid, args.m_valid, groups, args.out_ms, lowp_gs, &ml);
+    if (rc) return rc;
+  }
   if (args.tma_store) {
     rc = get_out_map(args.out, args.n_valid, args.m_valid, groups, args.out_ms, args.out_gs,
                      args.out_bf16 != 0, &mo);
     if (rc) return rc;
   }
   dim3 grid(m_tiles, n_tiles, groups * args.k_split);
-  kern<<<grid, 256, C::SMEM, st>>>(ma, mb, mo, args);
+  kern<<<grid, 256, C::SMEM, st>>>(ma, mb, mo, ml, args);
   return launch_status("tc_gemm");
 }
 
@@ -537,6 +663,39 @@ int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, i
     case 6: return launch<false, 128, true, 128, 64, 128, 1, 2, 2>(a, b, m_tiles, n_tiles, groups, g, st);
     default: return fail(NFB_EINVAL, "tc_gemm: unknown variant %d", variant);
   }
+}
+
+
+// fc weight gradient fused with the optimizer step (momentum-free SGD):
+//   w[g][j][i] <- w - lr * (sum_b dy[g][b][j] * x[g][b][i] + wd * w),  w_lowp <- bf16(w)
+// A = dy [groups][batch][j] and B = x [groups][batch][i] (both MN-major), w fp32 rows of length i
+// `w_gs` / `lowp_gs` elements apart per group.  The gradient is never written.  The caller must
+// have finished every read of the OLD weights (e.g. the data gradient) on this stream.
+int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* A, const nfb_tc_operand* B, int groups, int j,
+                            int i, int inner, float* w, long long w_gs, void* w_lowp,
+                            long long lowp_gs, float lr, float weight_decay, int* status,
+                            void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(A && B && w && w_lowp && status, NFB_EINVAL, "linear_wgrad_sgd: null pointer");
+  NFB_REQUIRE(groups >= 1 && groups <= 65535 && j >= 1 && i >= 32 && i % 32 == 0 && inner >= 1,
+              NFB_EINVAL, "linear_wgrad_sgd: bad shape");
+  NFB_REQUIRE((reinterpret_cast<uintptr_t>(w) & 15) == 0 && (w_gs & 3) == 0, NFB_EINVAL,
+              "linear_wgrad_sgd: weights must be 16-byte aligned");
+  GemmArgs g{};
+  g.taps = 1; g.inner = inner; g.k_split = 1;
+  g.tap[0] = Tap{0, 0, 0, 0};
+  g.out = w; g.out_bf16 = 0; g.atomic = 0;
+  g.out_gs = w_gs; g.out_ms = i; g.out_ns = 1; g.out_ts = 0;
+  g.m_valid = j; g.n_valid = i;
+  g.vec_store = 1;
+  g.sgd_lr = lr; g.sgd_wd = weight_decay;
+  g.status = status;
+  Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
+  Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};
+  return launch<true, 128, true, 128, 64, 128, 1, 2, 2, 1>(a, b, (j + BM - 1) / BM, (i + 127) / 128,
+                                                         groups, g, as_stream(stream), w_lowp,
+                                                         lowp_gs);
 }
 
 }  // extern "C"

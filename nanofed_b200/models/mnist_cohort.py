@@ -109,6 +109,10 @@ class MnistCohortNet:
         o = self.off["fc1.weight"]
         self.fc1_w = arena.slots_lowp[:, o : o + 128 * 9216].unflatten(1, (128, 9216))
         self.fc1_g = self.grads[:, o:]
+        self.fc1_master = arena.slots[:, o : o + 128 * 9216].unflatten(1, (128, 9216))
+        self._fc1_range = (o, o + 128 * 9216)
+        # momentum needs the gradient history in a buffer: only plain SGD is fused
+        self.fuse_fc1_sgd = (cfg.momentum == 0.0 and os.environ.get("NFB_NO_FUSED_SGD") is None)
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
         # atomic-accumulated gradient entries (conv1.*, conv2.*) sit in front of fc1.weight
         self._atomic_prefix = self.off["fc1.weight"]
@@ -145,7 +149,8 @@ class MnistCohortNet:
                        momentum_buf=None if a.momentum is None else a.momentum.view(-1),
                        momentum=cfg.momentum, weight_decay=cfg.weight_decay,
                        first_step=(step == 0), lowp_out=a.slots_lowp.view(-1),
-                       row_len=self.n_total, zero_grad_prefix=self._atomic_prefix)
+                       row_len=self.n_total, zero_grad_prefix=self._atomic_prefix,
+                       skip_range=self._fc1_range if self.fuse_fc1_sgd else None)
 
     def _step_group(self, step: int, g0: int) -> None:
         cfg, a, lib = self.cfg, self.arena, self.lib
@@ -179,8 +184,15 @@ class MnistCohortNet:
                                           self.seed + 7 * g0 + 3, self.dh.data_ptr(),
                                           stats.data_ptr(), st), "fc_head")
         # ---- backward ----
-        tc.linear_wgrad(self.dh, self.p, self.fc1_g[g0:g1], n)
         tc.linear_dgrad(self.fc1_w[g0:g1], self.dh, self.dp)
+        if self.fuse_fc1_sgd:
+            # 96% of the parameters are fc1.weight: its gradient is applied inside the GEMM
+            # epilogue (after the data gradient above has read the old weights) and never
+            # written; K-OPT then skips that range
+            tc.linear_wgrad_sgd(self.dh, self.p, self.fc1_master[g0:g1], self.fc1_w[g0:g1],
+                                cfg.learning_rate, cfg.weight_decay)
+        else:
+            tc.linear_wgrad(self.dh, self.p, self.fc1_g[g0:g1], n)
         self._check(lib.nfb_mnist_pool_bwd(self.dp.data_ptr(), self.pidx.data_ptr(), c, b,
                                            self.p1, self.da2.data_ptr(), grads.data_ptr(), n,
                                            off["conv2.bias"], st), "pool_bwd")

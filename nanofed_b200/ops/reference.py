@@ -178,13 +178,21 @@ def fused_sgd_(
     lowp_out: torch.Tensor | None = None,
     row_len: int = 0,
     zero_grad_prefix: int = 0,
+    skip_range: tuple[int, int] | None = None,
 ) -> torch.Tensor:
     """torch.optim.SGD semantics on flat buffers, with optional DP-SGD pre-processing.
 
     ``g' = g·grad_scale + noise_std·z`` (clip factor and Gaussian noise, both optional),
     then ``g' += wd·p``; momentum buffer ``b = g'`` on the first step else
     ``b = μ·b + (1-dampening)·g'``; ``p -= lr·(g' + μ·b if nesterov else b)``.
+    ``skip_range=(lo, hi)``: columns ``[lo, hi)`` of every ``row_len`` row keep their values
+    (parameters, momentum and low-precision copy): they were updated elsewhere.
     """
+    keep = None
+    if skip_range is not None:
+        lo, hi = skip_range
+        keep = [(t, t.view(-1, row_len)[:, lo:hi].clone())
+                for t in (p, momentum_buf, lowp_out) if t is not None]
     gf = g.to(torch.float32)
     if grad_scale is not None:
         gf = gf * grad_scale.to(torch.float32)
@@ -203,6 +211,9 @@ def fused_sgd_(
         lowp_out.copy_(p.to(lowp_out.dtype))
     if zero_grad_prefix > 0:
         g.view(-1, row_len)[:, :zero_grad_prefix] = 0
+    if keep is not None:
+        for t, saved in keep:
+            t.view(-1, row_len)[:, skip_range[0]:skip_range[1]] = saved
     return p
 
 

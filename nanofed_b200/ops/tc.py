@@ -256,6 +256,36 @@ def linear_fwd(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, k_split: int
          inner=i // 64, k_split=k_split, atomic=True)
 
 
+def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp: torch.Tensor,
+                     lr: float, weight_decay: float = 0.0) -> None:
+    """``w[c, j, i] -= lr·(Σ_b dy[c, b, j]·x[c, b, i] + wd·w)`` and ``w_lowp = bf16(w)`` in ONE
+    kernel: the weight gradient is consumed in the tcgen05 epilogue and never written.  ``w`` (fp32)
+    and ``w_lowp`` (bf16) are ``[C, j, i]`` views with contiguous ``[j, i]`` blocks and arbitrary
+    client strides (rows of the parameter arena).  Everything that reads the OLD weights in this
+    step (the data gradient) must already be enqueued."""
+    lib = _lib()
+    if not getattr(lib, "_wgrad_sgd_declared", False):
+        ll = C.c_longlong
+        lib.nfb_tc_linear_wgrad_sgd.restype = C.c_int
+        lib.nfb_tc_linear_wgrad_sgd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                                C.c_int, C.c_void_p, ll, C.c_void_p, ll, C.c_float,
+                                                C.c_float, C.c_void_p, C.c_void_p]
+        lib._wgrad_sgd_declared = True
+    c, j, i = w.shape
+    assert w.dtype == torch.float32 and w_lowp.dtype == torch.bfloat16 and w_lowp.shape == w.shape
+    assert w.stride(2) == 1 and w.stride(1) == i and w_lowp.stride(2) == 1 and w_lowp.stride(1) == i
+    assert dy.shape[0] == c and x.shape[0] == c and dy.shape[2] == j and x.shape[2] == i
+    oa, ob = _operand(dy), _operand(x)
+    st = status_word(dy.device)
+    code = lib.nfb_tc_linear_wgrad_sgd(C.byref(oa), C.byref(ob), c, j, i, (dy.shape[1] + 63) // 64,
+                                       w.data_ptr(), w.stride(0), w_lowp.data_ptr(),
+                                       w_lowp.stride(0), float(lr), float(weight_decay),
+                                       st.data_ptr(),
+                                       torch.cuda.current_stream(dy.device).cuda_stream)
+    native._check(code, "tc_linear_wgrad_sgd")
+    native._count()
+
+
 def linear_dgrad(w: torch.Tensor, dy: torch.Tensor, out: torch.Tensor) -> None:
     """``out[c, b, i] = Σ_j dy[c, b, j]·w[c, j, i]`` (bf16)."""
     j, i = w.shape[1], w.shape[2]

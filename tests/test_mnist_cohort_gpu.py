@@ -34,6 +34,7 @@ def test_one_step_matches_autograd():
     from nanofed_b200.ops import tc
 
     cfg, model, layout, arena, shards, eng = _setup()
+    eng.fuse_fc1_sgd = False               # keep the fc1 weight gradient observable
     c, b = cfg.clients_per_gpu, cfg.batch_size
     eng._step_group(0, 0)                  # forward + backward: gradients only
     torch.cuda.synchronize()
@@ -76,6 +77,30 @@ def test_one_step_matches_autograd():
             want = p.data - cfg.learning_rate * got[name].float()
             torch.testing.assert_close(new[name], want, rtol=1e-5, atol=1e-6)
     assert torch.equal(arena.slots_lowp, arena.slots.bfloat16())
+
+
+def test_fc1_update_fused_into_the_wgrad_epilogue_matches_separate_optimizer():
+    from nanofed_b200.ops import tc
+
+    results = []
+    for fused in (True, False):
+        cfg, model, layout, arena, shards, eng = _setup(c=3, b=16, steps=2)
+        assert eng.fuse_fc1_sgd, "plain SGD must take the fused path by default"
+        eng.fuse_fc1_sgd = fused
+        for s in range(2):
+            eng.step(s)
+        torch.cuda.synchronize()
+        tc.check_status(arena.device)
+        assert torch.equal(arena.slots_lowp, arena.slots.bfloat16())
+        if fused:   # the gradient of fc1.weight is never written
+            lo, hi = eng._fc1_range
+            assert float(eng.grads[:, lo:hi].abs().sum()) == 0.0
+        results.append(arena.slots.clone())
+    # same fp32 accumulators, same update formula; the atomically accumulated conv gradients
+    # differ in summation order between runs
+    torch.testing.assert_close(results[0], results[1], rtol=1e-4, atol=2e-6)
+    moved = (results[0] - arena.master[None]).abs().max().item()
+    assert moved > 1e-4                    # and the step did move the weights
 
 
 def test_graph_replay_trains_and_dropout_masks_advance():

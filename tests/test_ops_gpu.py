@@ -165,6 +165,22 @@ def test_fused_sgd_dp_front_end():
     torch.testing.assert_close(p.cpu(), want, rtol=1e-4, atol=1e-4)
 
 
+def test_fused_sgd_skips_a_column_range_and_zeroes_the_atomic_prefix():
+    rows, row_len, lo, hi, prefix = 5, 1024, 128, 896, 64
+    p = torch.randn(rows * row_len, device=DEV)
+    g = torch.randn(rows * row_len, device=DEV)
+    lowp = torch.full((rows * row_len,), 7.0, device=DEV, dtype=torch.bfloat16)
+    pr, gr, lr_ = p.cpu().clone(), g.cpu().clone(), lowp.cpu().clone()
+    kw = dict(weight_decay=0.01, row_len=row_len, zero_grad_prefix=prefix, skip_range=(lo, hi),
+              noise_std=0.3, seed=11, offset=8)
+    ops.fused_sgd_(p, g, 0.1, lowp_out=lowp, **kw)
+    ref.fused_sgd_(pr, gr, 0.1, lowp_out=lr_, **kw)
+    torch.testing.assert_close(p.cpu(), pr, rtol=1e-5, atol=1e-6)
+    assert torch.equal(g.cpu(), gr)
+    torch.testing.assert_close(lowp.cpu().float(), lr_.float(), rtol=0, atol=1e-2)
+    assert float((lowp.view(rows, row_len)[:, lo:hi] - 7.0).abs().max()) == 0.0   # untouched
+
+
 def test_fused_adam_matches_torch():
     n = 5000
     p0 = torch.randn(n, device=DEV)

@@ -85,3 +85,19 @@ def test_conv_psgn_reference_matches_vmap():
     dy = y.flatten(2).transpose(1, 2)
     got = ops.conv_per_sample_grad_sqnorms(unf, dy, bias=False)
     torch.testing.assert_close(got, torch.stack(per), rtol=1e-4, atol=1e-4)
+
+
+def test_fused_sgd_skip_range_leaves_columns_alone():
+    from nanofed_b200.ops import reference as ref
+
+    rows, row_len = 3, 32
+    p = torch.arange(rows * row_len, dtype=torch.float32)
+    g = torch.ones(rows * row_len)
+    lowp = torch.zeros(rows * row_len, dtype=torch.bfloat16)
+    p0 = p.clone()
+    ref.fused_sgd_(p, g, 0.5, lowp_out=lowp, row_len=row_len, zero_grad_prefix=4, skip_range=(8, 24))
+    pv, p0v = p.view(rows, row_len), p0.view(rows, row_len)
+    assert torch.equal(pv[:, 8:24], p0v[:, 8:24])
+    assert torch.equal(pv[:, :8], p0v[:, :8] - 0.5) and torch.equal(pv[:, 24:], p0v[:, 24:] - 0.5)
+    assert float(lowp.view(rows, row_len)[:, 8:24].abs().sum()) == 0.0
+    assert float(g.view(rows, row_len)[:, :4].abs().sum()) == 0.0

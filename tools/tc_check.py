@@ -176,7 +176,31 @@ def check_fc_wgrad():
     return got, torch.einsum("cbj,cbi->cji", dy.float(), x.float())
 
 
-CHECKS = {"conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
+def check_fc_wgrad_sgd():
+    """Weight gradient consumed by the SGD epilogue: compare the updated fp32 weights."""
+    from nanofed_b200.ops import tc
+    c, b, j, i = 3, 64, 128, 9216
+    lr, wd = 0.5, 0.01
+    dy, x = _bf(c, b, j, scale=0.1), _bf(c, b, i)
+    n_total = j * i + 256                      # weights live inside longer arena rows
+    w = torch.randn(c, n_total, device="cuda")
+    lowp = torch.zeros(c, n_total, device="cuda", dtype=torch.bfloat16)
+    w0 = w.clone()
+    wv = w[:, 128:128 + j * i].unflatten(1, (j, i))
+    lv = lowp[:, 128:128 + j * i].unflatten(1, (j, i))
+    tc.linear_wgrad_sgd(dy, x, wv, lv, lr, wd)
+    torch.cuda.synchronize()
+    old = w0[:, 128:128 + j * i].unflatten(1, (j, i))
+    grad = torch.einsum("cbj,cbi->cji", dy.float(), x.float())
+    want = old - lr * (grad + wd * old)
+    # nothing outside the weight block may change, and the bf16 copy is the rounded result
+    assert torch.equal(w[:, :128], w0[:, :128]) and torch.equal(w[:, 128 + j * i:], w0[:, 128 + j * i:])
+    assert torch.equal(lv, wv.bfloat16()), "bf16 working copy is not the rounded fp32 weights"
+    assert float(lowp[:, :128].abs().sum()) == 0 and float(lowp[:, 128 + j * i:].abs().sum()) == 0
+    return wv.clone(), want
+
+
+CHECKS = {"fc_wgrad_sgd": check_fc_wgrad_sgd, "conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
           "conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
           "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad,
           "fc_wgrad": check_fc_wgrad}
