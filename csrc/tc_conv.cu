@@ -50,6 +50,12 @@ struct ConvArgs {
   float drop_p;
   const unsigned long long* rng_state;
   unsigned long long seed;
+  // MODE 3 (dgrad + conv1 weight gradient) only: the layer-1 input images and gradient slab
+  const float* x1;          // [C][B][img_w * img_w] fp32, img_w = grid_w + 2
+  long long x1_gs;          // elements between clients
+  float* grad1;             // gradient slab rows [C][grad1_gs]
+  long long grad1_gs;
+  long long w1_off, b1_off; // conv1.weight [32][9] / conv1.bias [32] inside a row
   int* status;
   int debug;  // bottleneck probes (env NFB_CONV_DEBUG): 1 = reuse first slabs, 2 = no MMA, 4 = no stores
 };
@@ -81,17 +87,23 @@ __device__ __forceinline__ void bulk_wait_read0() {
 // move ~300-430 MB per launch (3.9 TB/s): they are DRAM-bound, not latency-bound.
 constexpr int kEpiWarps = 8;   // two epilogue warpgroups, alternating tiles / accumulators
 
+// MODE 3 = MODE 1 (dgrad) whose epilogue also accumulates the conv1 weight/bias gradient
+template <int MODE>
+constexpr bool kDgrad = (MODE == 1 || MODE == 3);
+
 template <int MODE>
 struct ConvCfg {
-  static constexpr int CH = MODE != 1 ? 32 : 64;       // A channels (K per tap)
-  static constexpr int BN = MODE != 1 ? 64 : 32;       // output channels
+  static constexpr int CH = !kDgrad<MODE> ? 32 : 64;   // A channels (K per tap)
+  static constexpr int BN = !kDgrad<MODE> ? 64 : 32;   // output channels
   static constexpr int CHUNKS = CH / 8;
   static constexpr int SLAB = kSlabRows * CH * 2;      // bytes per stage
   static constexpr int SLAB_PAD = (SLAB + 1023) / 1024 * 1024;
   static constexpr int W_TILE = 64 * 32 * 2;           // one tap's weights (4 KB) either way
   static constexpr int W_BYTES = kTaps * W_TILE;
-  static constexpr int TMEM_COLS = 2 * BN;             // 128 or 64 (both powers of two)
-  static constexpr int STAGES = MODE != 1 ? 10 : 6;    // slab loads in flight per CTA
+  // 128 or 64 (both powers of two); MODE 3 adds one [128 x 32] fp32 accumulator per epilogue
+  // warp behind the two tile accumulators (64 + 8 * 32 = 320 -> 512)
+  static constexpr int TMEM_COLS = MODE == 3 ? 512 : 2 * BN;
+  static constexpr int STAGES = !kDgrad<MODE> ? 10 : 6;  // slab loads in flight per CTA
   static constexpr int OUT_ROW = BN * 2;               // bytes per output row (128 / 64)
   static constexpr int STAGING = 32 * OUT_ROW;         // per epilogue warp (4 KB / 2 KB)
   // MODE 2: per epilogue group a [128 x 64] bf16 tile (16 KB = the 4 warps' 4 KB areas) plus a
@@ -121,13 +133,15 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
   uint64_t* acc_empty = acc_full + 2;                  // [2]
   uint64_t* w_bar = acc_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
+  uint64_t* wg_bar = w_bar + 2;                        // MODE 3: [kEpiWarps]
 
   __shared__ float s_bias[64];
+  __shared__ int s_wg_valid[kEpiWarps];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = blockIdx.x / args.ctas_per_client;
   const int part = blockIdx.x % args.ctas_per_client;
   if (threadIdx.x < 64)
-    s_bias[threadIdx.x] = (MODE != 1 && args.bias)
+    s_bias[threadIdx.x] = (!kDgrad<MODE> && args.bias)
                               ? args.bias[static_cast<long long>(g) * args.bias_gs + threadIdx.x] : 0.f;
   const int per = (args.tiles_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
   const int tile_lo = part * per;
@@ -141,6 +155,8 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
     mbar_init(w_bar, 1);
+    if (MODE == 3)
+      for (int w = 0; w < kEpiWarps; ++w) mbar_init(&wg_bar[w], 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
@@ -154,7 +170,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     if (elect_one() && n_tiles > 0) {
       mbar_expect_tx(w_bar, C::W_BYTES);
       for (int t = 0; t < kTaps; ++t) {
-        if (MODE != 1)  // K-major box [32 k, 64 co]
+        if (!kDgrad<MODE>)  // K-major box [32 k, 64 co]
           tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
         else            // MN-major box [32 ci, 64 co-rows]: same bytes, read as B^T
           tma_load_3d(w_smem + t * C::W_TILE, &map_w, w_bar, t * 32, 0, g);
@@ -169,7 +185,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
         // MODE 2 tiles are 4 grid rows of one image: 6 per image, 104 positions apart
         const int m0 = MODE == 2 ? (tile / 6) * (args.grid_w * args.grid_w) + (tile % 6) * (4 * args.grid_w)
                                  : tile * 128;
-        const int row0 = MODE != 1 ? m0 : m0 - kHalo;
+        const int row0 = !kDgrad<MODE> ? m0 : m0 - kHalo;
         tma_load_4d(slabs + s * C::SLAB_PAD, &map_a, &full_bar[s], 0, row0, 0, g);
       }
     }
@@ -177,7 +193,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     // ===================== MMA issuer =====================
     if (elect_one() && n_tiles > 0) {
       // fwd: A K-major, B K-major ; dgrad: A K-major, B MN-major
-      constexpr uint32_t idesc = make_idesc_bf16(128, C::BN, 0u, MODE != 1 ? 0u : 1u);
+      constexpr uint32_t idesc = make_idesc_bf16(128, C::BN, 0u, !kDgrad<MODE> ? 0u : 1u);
       bool ok = mbar_wait(w_bar, 0);
       if (!ok) *args.status = 1;
       const uint32_t w_addr = smem_u32(w_smem);
@@ -201,7 +217,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
             const uint64_t da = make_smem_desc(
                 slab + args.shift[t] * 16 + kk * (2 * kSlabRows * 16), kSlabRows * 16, 128, 0);
             uint64_t db;
-            if (MODE != 1)   // K-major SW64 tile [64 co][32 k]: step K by 32 B
+            if (!kDgrad<MODE>)   // K-major SW64 tile [64 co][32 k]: step K by 32 B
               db = make_smem_desc(w_addr + t * C::W_TILE + kk * 32, 0, 8 * 64, 4);
             else             // MN-major SW64 tile [64 k-rows][32 ci]: step K by 16 rows
               db = make_smem_desc(w_addr + t * C::W_TILE + kk * (16 * 64), 64 * 64, 8 * 64, 4);
@@ -222,6 +238,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     const float* bias = args.bias ? args.bias + static_cast<long long>(g) * args.bias_gs : nullptr;
     uint8_t* my_stage = staging + (warp - 4) * 4096;
     bool ok = true;
+    [[maybe_unused]] int my_tiles = 0;              // MODE 3: tiles this warp has fed to its own MMA
     for (int i = grp; i < n_tiles && ok; i += 2) {
       const int acc = grp;
       const uint32_t aph = (i >> 1) & 1;
@@ -231,10 +248,29 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
       // the ReLU mask of this row depends only on the tile index: fetch it BEFORE waiting for
       // the accumulator so its DRAM latency hides behind this tile's MMAs
       uint4 mk[C::BN / 8];
-      if (MODE == 1 && mask && row_ok) {
+      if (kDgrad<MODE> && mask && row_ok) {
 #pragma unroll
         for (int j = 0; j < C::BN / 8; ++j)
           mk[j] = ld_stream(mask + static_cast<long long>(m) * C::BN + 8 * j);
+      }
+      // MODE 3: this position's 3x3 window of the layer-1 input (+ a 1 for the bias column) is
+      // the B row of the conv1 weight-gradient MMA; it too only depends on the tile index
+      [[maybe_unused]] float xv[16];
+      if (MODE == 3) {
+#pragma unroll
+        for (int t = 0; t < 16; ++t) xv[t] = 0.f;
+        if (row_ok) {
+          const int gsz = args.grid_w * args.grid_w, iw = args.grid_w + 2;
+          const int b = m / gsz, rem = m - b * gsz;
+          const int oh = rem / args.grid_w, ow = rem - oh * args.grid_w;
+          const float* px = args.x1 + static_cast<long long>(g) * args.x1_gs +
+                            static_cast<long long>(b) * (iw * iw) + oh * iw + ow;
+#pragma unroll
+          for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) xv[kh * 3 + kw] = __ldg(px + kh * iw + kw);
+          xv[9] = 1.f;
+        }
       }
       if (!mbar_wait(&acc_full[acc], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }
       tc_fence_after();
@@ -331,6 +367,14 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
         continue;
       }
       if (!(args.debug & 4)) {
+        if (MODE == 3 && my_tiles > 0) {
+          // the tensor core must have read this warp's previous operand tiles
+          if (!mbar_wait(&wg_bar[warp - 4], (my_tiles - 1) & 1)) {
+            if (lane == 0) *args.status = 1;
+            ok = false;
+            break;
+          }
+        }
         // stage this warp's 32 rows in shared memory with the TMA swizzle (conflict-free
         // 16-byte stores), then ONE bulk tensor store writes them as full lines
 #pragma unroll
@@ -348,9 +392,42 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
             for (int j = 0; j < 8; ++j)
               if (!(mf[j] > 0.f)) v[j] = 0.f;
           }
+          if (MODE == 3 && !row_ok) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 0.f;     // rows past R must not reach the MMA
+          }
           const int chunk = c0 / 8;
           const int sw = MODE == 0 ? (chunk ^ (lane & 7)) : (chunk ^ ((lane >> 1) & 3));
           st_vec(my_stage + lane * C::OUT_ROW + sw * 16, pack<__nv_bfloat16>(v));
+        }
+        if (MODE == 3) {
+          // ---- conv1 weight/bias gradient on the tensor core ---------------------------------
+          //   dW1[ch, t] += sum_q da1[q, ch] * x[q + s_t],   t = 9 is the bias column (x = 1)
+          // The staged rows ARE an MN-major 64-byte-swizzled operand (K = 32 positions, M = 32
+          // channels); the windows are written next to them in the same layout (N = 32, columns
+          // 0..9 used).  UMMA M is 128: the three extra 32-channel atoms alias bytes inside this
+          // warp's 4 KB area (LBO 512) and only produce accumulator lanes 32..127, never read.
+          uint8_t* xs = my_stage + 2048;
+          st_vec(xs + lane * 64 + ((0 ^ ((lane >> 1) & 3)) * 16), pack<__nv_bfloat16>(xv));
+          st_vec(xs + lane * 64 + ((1 ^ ((lane >> 1) & 3)) * 16), pack<__nv_bfloat16>(xv + 8));
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tc_fence_after();
+            constexpr uint32_t idesc_w = make_idesc_bf16(128, 32, 1u, 1u);
+            const uint32_t a0 = smem_u32(my_stage), b0 = smem_u32(xs);
+            const uint32_t d_w = tmem_base + 2 * C::BN + (warp - 4) * 32;
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {           // 16 positions per MMA
+              const uint64_t da = make_smem_desc(a0 + kk * 1024, 512, 8 * 64, 4);
+              const uint64_t db = make_smem_desc(b0 + kk * 1024, 512, 8 * 64, 4);
+              umma_f16(d_w, da, db, idesc_w, (my_tiles > 0 || kk > 0) ? 1u : 0u);
+            }
+            umma_commit(&wg_bar[warp - 4]);
+          }
+          __syncwarp();
+          ++my_tiles;
+          continue;                                     // da1 itself is never written
         }
         fence_proxy_async();
         __syncwarp();
@@ -361,6 +438,35 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
       }
     }
     if (lane == 0) bulk_wait_read0();
+    if (MODE == 3) {
+      // every warp's accumulator is complete; warps 4 and 8 (TMEM lanes 0..31 = channels) add up
+      // their group's four accumulators and flush 32 x 10 values with atomics
+      if (my_tiles > 0 && ok && !mbar_wait(&wg_bar[warp - 4], (my_tiles - 1) & 1)) {
+        if (lane == 0) *args.status = 1;
+        ok = false;
+      }
+      if (lane == 0) s_wg_valid[warp - 4] = (ok && my_tiles > 0) ? 1 : 0;
+      tc_fence_before();
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      tc_fence_after();
+      if (sub == 0) {
+        float sum[10];
+#pragma unroll
+        for (int t = 0; t < 10; ++t) sum[t] = 0.f;
+        for (int w = grp * 4; w < grp * 4 + 4; ++w) {
+          if (!s_wg_valid[w]) continue;                 // warp-uniform
+          uint32_t rr[16];
+          tmem_ld_32x32b_x16(tmem_base + 2 * C::BN + w * 32, rr);
+          tmem_ld_wait();
+#pragma unroll
+          for (int t = 0; t < 10; ++t) sum[t] += __uint_as_float(rr[t]);
+        }
+        float* gd = args.grad1 + static_cast<long long>(g) * args.grad1_gs;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) atomicAdd(gd + args.w1_off + lane * 9 + t, sum[t]);
+        atomicAdd(gd + args.b1_off + lane, sum[9]);
+      }
+    }
   }
 
   tc_fence_before();
@@ -701,6 +807,63 @@ extern "C" int nfb_tc_conv3x3(int mode, const void* a, long long rows, long long
   cudaStream_t st = as_stream(stream);
   return mode == 0 ? launch_conv<0>(ma, mw, mo, ctas, args, st)
                    : launch_conv<1>(ma, mw, mo, ctas, args, st);
+}
+
+// Data gradient of the 32->64 3x3 convolution fused with the weight/bias gradient of the
+// 1->32 3x3 convolution in front of it (mode 3 of the persistent kernel):
+//   da1[q, ci]  = (sum_t sum_co dy[q - s_t, co] w[co, t*32+ci]) * (mask[q, ci] > 0)      (not stored)
+//   grad1[c][w1_off + ci*9 + t] += sum_q da1[q, ci] * x1[c, image(q), pixel(q) + tap t]
+//   grad1[c][b1_off + ci]       += sum_q da1[q, ci]
+// x1 = fp32 [C][B][(width+2)^2] layer-1 inputs, B = rows / width^2.  The caller zeroes grad1's
+// target entries; accumulation is fp32 (tensor core, then 320 atomics per CTA).
+extern "C" int nfb_tc_conv3x3_dgrad_wgrad1(const void* dy, long long rows,
+                                           long long dy_group_stride, const void* w,
+                                           long long w_group_stride, int clients, int width,
+                                           const void* mask, long long mask_group_stride,
+                                           const float* x1, long long x1_group_stride,
+                                           float* grad1, long long grad1_group_stride,
+                                           long long w1_off, long long b1_off, int* status,
+                                           void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(dy && w && mask && x1 && grad1 && status, NFB_EINVAL,
+              "tc_conv3x3_dgrad_wgrad1: null pointer");
+  NFB_REQUIRE(clients >= 1 && rows >= 1 && width >= 1 && rows % (width * width) == 0, NFB_EINVAL,
+              "tc_conv3x3_dgrad_wgrad1: rows must be whole width x width images");
+  NFB_REQUIRE(2 * width + 2 <= kHalo, NFB_ERANGE,
+              "tc_conv3x3_dgrad_wgrad1: grid width %d needs a halo of %d rows, kernel has %d",
+              width, 2 * width + 2, kHalo);
+  CUtensorMap ma, mw;
+  int rc = slab_map(dy, rows, clients, dy_group_stride, 64, kSlabRows, &ma);
+  if (rc) return rc;
+  rc = weight_map(w, clients, w_group_stride, &mw);
+  if (rc) return rc;
+  ConvArgs args{};
+  args.tiles_per_client = static_cast<int>((rows + 127) / 128);
+  int per_client = sm_count() / clients;
+  if (per_client < 1) per_client = 1;
+  if (per_client > args.tiles_per_client) per_client = args.tiles_per_client;
+  args.ctas_per_client = per_client;
+  args.rows = static_cast<int>(rows);
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kw = 0; kw < 3; ++kw) args.shift[kh * 3 + kw] = kHalo - (kh * width + kw);
+  args.out = nullptr;
+  args.out_gs = mask_group_stride;       // the kernel addresses the mask with the output strides
+  args.mask = static_cast<const __nv_bfloat16*>(mask);
+  args.grid_w = width;
+  args.x1 = x1;
+  args.x1_gs = x1_group_stride;
+  args.grad1 = grad1;
+  args.grad1_gs = grad1_group_stride;
+  args.w1_off = w1_off;
+  args.b1_off = b1_off;
+  args.status = status;
+  {
+    const char* dbg = getenv("NFB_CONV_DEBUG");
+    args.debug = dbg ? atoi(dbg) : 0;
+  }
+  return launch_conv<3>(ma, mw, ma /*no output map*/, clients * per_client, args,
+                        as_stream(stream));
 }
 
 // Weight gradient: grad[c][co][ci][t] += sum_q dy[c,q,co] * x[c,q+s_t,ci]  (fp32 atomics; the

@@ -111,6 +111,7 @@ class MnistCohortNet:
         self.fc1_g = self.grads[:, o:]
         self.fc1_master = arena.slots[:, o : o + 128 * 9216].unflatten(1, (128, 9216))
         self._fc1_range = (o, o + 128 * 9216)
+        self.fuse_conv1_wgrad = os.environ.get("NFB_NO_FUSED_WGRAD1") is None
         # momentum needs the gradient history in a buffer: only plain SGD is fused
         self.fuse_fc1_sgd = (cfg.momentum == 0.0 and os.environ.get("NFB_NO_FUSED_SGD") is None)
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
@@ -197,10 +198,16 @@ class MnistCohortNet:
                                            self.p1, self.da2.data_ptr(), grads.data_ptr(), n,
                                            off["conv2.bias"], st), "pool_bwd")
         tc.conv3x3_wgrad_persistent(self.da2, self.a1, self.conv2_g[g0:g1], 26, n)
-        tc.conv3x3_dgrad_persistent(self.da2, self.w2p, self.da1, 26, relu_mask=self.a1)
-        self._check(lib.nfb_mnist_conv1_wgrad(self.da1.data_ptr(), x.data_ptr(), xs, c, b,
-                                              grads.data_ptr(), n, off["conv1.weight"],
-                                              off["conv1.bias"], st), "conv1_wgrad")
+        if self.fuse_conv1_wgrad:
+            # the masked conv1 output gradient goes from the dgrad epilogue straight into a second
+            # MMA against the input windows: da1 (88 MB per step) is never written or re-read
+            tc.conv3x3_dgrad_wgrad1(self.da2, self.w2p, self.a1, x, grads, off["conv1.weight"],
+                                    off["conv1.bias"], 26)
+        else:
+            tc.conv3x3_dgrad_persistent(self.da2, self.w2p, self.da1, 26, relu_mask=self.a1)
+            self._check(lib.nfb_mnist_conv1_wgrad(self.da1.data_ptr(), x.data_ptr(), xs, c, b,
+                                                  grads.data_ptr(), n, off["conv1.weight"],
+                                                  off["conv1.bias"], st), "conv1_wgrad")
 
     def _all_steps(self) -> None:
         for s in range(self.cfg.local_steps):

@@ -142,6 +142,40 @@ def _conv_persistent(mode: int, a: torch.Tensor, w: torch.Tensor, out: torch.Ten
     native._count()
 
 
+def conv3x3_dgrad_wgrad1(dy: torch.Tensor, w: torch.Tensor, relu_mask: torch.Tensor,
+                         x1: torch.Tensor, grads: torch.Tensor, w1_off: int, b1_off: int,
+                         width: int) -> None:
+    """Data gradient of the 32→64 conv fused with the weight/bias gradient of the 1→32 conv in
+    front of it (``tc_conv.cu`` MODE 3): ``da1`` is masked, rounded to bf16 and fed straight to a
+    second tcgen05 MMA against the 3×3 input windows — it is never written to memory.
+
+    dy ``[C, B·W², 64]`` bf16, w ``[C, 64, 288]`` bf16, relu_mask ``[C, B·W², 32]`` bf16 (conv1
+    output), x1 ``[C, B, ...]`` fp32 layer-1 images of ``(W+2)²`` pixels (client stride free),
+    grads ``[C, n]`` fp32 rows: ``grads[c, w1_off + ch·9 + t]`` and ``grads[c, b1_off + ch]`` are
+    accumulated with atomics (caller zeroes them).
+    """
+    lib = _lib()
+    if not getattr(lib, "_dgw1_declared", False):
+        ll = C.c_longlong
+        lib.nfb_tc_conv3x3_dgrad_wgrad1.restype = C.c_int
+        lib.nfb_tc_conv3x3_dgrad_wgrad1.argtypes = [C.c_void_p, ll, ll, C.c_void_p, ll, C.c_int,
+                                                    C.c_int, C.c_void_p, ll, C.c_void_p, ll,
+                                                    C.c_void_p, ll, ll, ll, C.c_void_p, C.c_void_p]
+        lib._dgw1_declared = True
+    for t in (dy, w, relu_mask):
+        assert t.dtype == torch.bfloat16 and t.dim() == 3 and t.is_contiguous()
+    assert x1.dtype == torch.float32 and grads.dtype == torch.float32 and grads.stride(1) == 1
+    assert x1[0].is_contiguous() and x1[0].numel() * width * width == dy.shape[1] * (width + 2) ** 2
+    st = status_word(dy.device)
+    code = lib.nfb_tc_conv3x3_dgrad_wgrad1(
+        dy.data_ptr(), dy.shape[1], dy.stride(0), w.data_ptr(), w.stride(0), dy.shape[0], width,
+        relu_mask.data_ptr(), relu_mask.stride(0), x1.data_ptr(), x1.stride(0), grads.data_ptr(),
+        grads.stride(0), int(w1_off), int(b1_off), st.data_ptr(),
+        torch.cuda.current_stream(dy.device).cuda_stream)
+    native._check(code, "tc_conv3x3_dgrad_wgrad1")
+    native._count()
+
+
 def conv3x3_fwd_persistent(x, w, bias, out, width: int) -> None:
     """Same contract as ``conv3x3_fwd`` (bias + ReLU), persistent slab kernel (``tc_conv.cu``)."""
     _conv_persistent(0, x, w, out, width, bias, None)

@@ -200,7 +200,40 @@ def check_fc_wgrad_sgd():
     return wv.clone(), want
 
 
-CHECKS = {"fc_wgrad_sgd": check_fc_wgrad_sgd, "conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
+def check_conv_dgrad_wgrad1():
+    """dgrad of conv2 fused with the weight/bias gradient of conv1 (da1 never stored)."""
+    from nanofed_b200.ops import tc
+    c, b, cin, cout = 3, 5, 32, 64
+    r = b * W * W
+    dy, w = _bf(c, r, cout, scale=0.2), _bf(c, cout, 9 * cin, scale=0.05)
+    a1 = _bf(c, r, cin)
+    x1 = torch.randn(c, b + 2, 28 * 28, device="cuda")[:, 1:b + 1]     # strided client dimension
+    n = 1024
+    grads = torch.zeros(c, n, device="cuda")
+    w_off, b_off = 64, 512
+    tc.conv3x3_dgrad_wgrad1(dy, w, a1, x1, grads, w_off, b_off, W)
+    da1 = torch.zeros(c, r, cin, device="cuda")
+    for t, s in enumerate(tc._shifts(W)):
+        da1 += torch.einsum("cro,cok->crk", _shift_rows(dy, -s).float(),
+                            w[:, :, t * cin:(t + 1) * cin].float())
+    da1 = (da1 * (a1.float() > 0)).view(c, b, W, W, cin)
+    img = x1.reshape(c, b, 28, 28)
+    want = torch.zeros(c, cin, 10, device="cuda")
+    for kh in range(3):
+        for kw in range(3):
+            win = img[:, :, kh:kh + W, kw:kw + W]                       # [c, b, 26, 26]
+            want[:, :, kh * 3 + kw] = torch.einsum("cbhwk,cbhw->ck", da1, win)
+    want[:, :, 9] = da1.sum(dim=(1, 2, 3))
+    got = torch.cat([grads[:, w_off:w_off + cin * 9].view(c, cin, 9),
+                     grads[:, b_off:b_off + cin].view(c, cin, 1)], dim=2)
+    untouched = grads.clone()
+    untouched[:, w_off:w_off + cin * 9] = 0
+    untouched[:, b_off:b_off + cin] = 0
+    assert float(untouched.abs().sum()) == 0.0, "wrote outside the conv1 gradient entries"
+    return got, want
+
+
+CHECKS = {"conv_dgrad_wgrad1": check_conv_dgrad_wgrad1, "fc_wgrad_sgd": check_fc_wgrad_sgd, "conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
           "conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
           "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad,
           "fc_wgrad": check_fc_wgrad}
