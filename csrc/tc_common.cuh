@@ -152,5 +152,19 @@ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n, uint32_t a_mn_major,
          ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
+// ---- host side: cached tensor maps (defined in tc_gemm.cu) ------------------------------
+struct Operand {  // mirrors nfb_tc_operand: bf16 [groups][rows][inner], unit inner stride
+  const void* ptr;
+  long long inner, rows, groups, row_stride, group_stride;  // elements
+};
+// operand map with box [box_inner, box_rows, 1] and the given swizzle span
+int get_map(const Operand& op, int box_inner, int box_rows, int swz_bytes, CUtensorMap* out);
+// row-major [groups][m][n] output map, box [128 bytes, 32 rows], 128-byte swizzle
+int get_out_map(void* ptr, long long n, long long m, long long groups, long long ms, long long gs,
+                bool bf16, CUtensorMap* out);
+// bf16 [groups][m][n] map, box [32 cols, 32 rows], 64-byte swizzle
+int get_lowp_map(void* ptr, long long n, long long m, long long groups, long long ms, long long gs,
+                 CUtensorMap* out);
+
 }  // namespace tc
 }  // namespace nfb

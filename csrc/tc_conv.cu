@@ -239,37 +239,57 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     uint8_t* my_stage = staging + (warp - 4) * 4096;
     bool ok = true;
     [[maybe_unused]] int my_tiles = 0;              // MODE 3: tiles this warp has fed to its own MMA
+    // Software pipeline (dgrad): the ReLU-mask row (and MODE 3's input window) of a tile only
+    // depend on the tile index, so they are requested one iteration (two tiles) ahead; fetching
+    // them at the top of their own iteration left ~0.6 us of DRAM latency exposed per tile.
+    [[maybe_unused]] uint4 mk_nx[C::BN / 8];
+    [[maybe_unused]] float xw_nx[9];
+    auto fetch_mask = [&](int row, uint4* dst) {
+      if (mask && row < args.rows) {
+#pragma unroll
+        for (int j = 0; j < C::BN / 8; ++j)
+          dst[j] = ld_stream(mask + static_cast<long long>(row) * C::BN + 8 * j);
+      }
+    };
+    auto fetch_window = [&](int row, float* dst) {
+      if (row < args.rows) {
+        const int gsz = args.grid_w * args.grid_w, iw = args.grid_w + 2;
+        const int b = row / gsz, rem = row - b * gsz;
+        const int oh = rem / args.grid_w, ow = rem - oh * args.grid_w;
+        const float* px = args.x1 + static_cast<long long>(g) * args.x1_gs +
+                          static_cast<long long>(b) * (iw * iw) + oh * iw + ow;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) dst[kh * 3 + kw] = __ldg(px + kh * iw + kw);
+      }
+    };
+    if (kDgrad<MODE> && grp < n_tiles) {
+      const int first = (tile_lo + grp) * 128 + sub * 32 + lane;
+      fetch_mask(first, mk_nx);
+      if (MODE == 3) fetch_window(first, xw_nx);
+    }
     for (int i = grp; i < n_tiles && ok; i += 2) {
       const int acc = grp;
       const uint32_t aph = (i >> 1) & 1;
       const int row0 = (tile_lo + i) * 128 + sub * 32;   // (MODE 0/1 tiling; MODE 2 indexes by image)
       const int m = row0 + lane;
       const bool row_ok = m < args.rows;
-      // the ReLU mask of this row depends only on the tile index: fetch it BEFORE waiting for
-      // the accumulator so its DRAM latency hides behind this tile's MMAs
       uint4 mk[C::BN / 8];
-      if (kDgrad<MODE> && mask && row_ok) {
-#pragma unroll
-        for (int j = 0; j < C::BN / 8; ++j)
-          mk[j] = ld_stream(mask + static_cast<long long>(m) * C::BN + 8 * j);
-      }
       // MODE 3: this position's 3x3 window of the layer-1 input (+ a 1 for the bias column) is
-      // the B row of the conv1 weight-gradient MMA; it too only depends on the tile index
+      // the B row of the conv1 weight-gradient MMA
       [[maybe_unused]] float xv[16];
-      if (MODE == 3) {
+      if (kDgrad<MODE>) {
 #pragma unroll
-        for (int t = 0; t < 16; ++t) xv[t] = 0.f;
-        if (row_ok) {
-          const int gsz = args.grid_w * args.grid_w, iw = args.grid_w + 2;
-          const int b = m / gsz, rem = m - b * gsz;
-          const int oh = rem / args.grid_w, ow = rem - oh * args.grid_w;
-          const float* px = args.x1 + static_cast<long long>(g) * args.x1_gs +
-                            static_cast<long long>(b) * (iw * iw) + oh * iw + ow;
+        for (int j = 0; j < C::BN / 8; ++j) mk[j] = mk_nx[j];
+        if (MODE == 3) {
 #pragma unroll
-          for (int kh = 0; kh < 3; ++kh)
-#pragma unroll
-            for (int kw = 0; kw < 3; ++kw) xv[kh * 3 + kw] = __ldg(px + kh * iw + kw);
-          xv[9] = 1.f;
+          for (int t = 0; t < 16; ++t) xv[t] = (t < 9 && row_ok) ? xw_nx[t] : 0.f;
+          if (row_ok) xv[9] = 1.f;
+        }
+        if (i + 2 < n_tiles) {                       // this group's next tile
+          fetch_mask(m + 256, mk_nx);
+          if (MODE == 3) fetch_window(m + 256, xw_nx);
         }
       }
       if (!mbar_wait(&acc_full[acc], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }

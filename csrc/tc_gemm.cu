@@ -447,17 +447,13 @@ static EncodeFn encode_fn() {
   return fn;
 }
 
-struct Operand {  // mirrors nfb_tc_operand
-  const void* ptr;
-  long long inner, rows, groups, row_stride, group_stride;  // elements (bf16)
-};
 
 using MapKey = std::tuple<const void*, long long, long long, long long, long long, long long,
                           int, int, int>;
 static std::map<MapKey, CUtensorMap> g_maps;
 static std::mutex g_maps_mu;
 
-static int get_map(const Operand& op, int box_inner, int box_rows, int swz_bytes,
+int get_map(const Operand& op, int box_inner, int box_rows, int swz_bytes,
                    CUtensorMap* out) {
   MapKey key{op.ptr, op.inner, op.rows, op.groups, op.row_stride, op.group_stride,
              box_inner, box_rows, swz_bytes};
@@ -491,7 +487,7 @@ static int get_map(const Operand& op, int box_inner, int box_rows, int swz_bytes
 }
 
 // Output map for the TMA-store epilogue: [groups][m rows][n cols], n contiguous.
-static int get_out_map(void* ptr, long long n, long long m, long long groups, long long ms,
+int get_out_map(void* ptr, long long n, long long m, long long groups, long long ms,
                        long long gs, bool bf16, CUtensorMap* out) {
   const int esz = bf16 ? 2 : 4;
   MapKey key{ptr, n, m, groups, ms, gs, bf16 ? -64 : -32, 32, 128};
@@ -520,7 +516,7 @@ static int get_out_map(void* ptr, long long n, long long m, long long groups, lo
 
 // bf16 [groups][m rows][n cols] map with box [32 cols, 32 rows] and 64-byte swizzle: the working
 // copy of the weights written by the SGD epilogue.
-static int get_lowp_map(void* ptr, long long n, long long m, long long groups, long long ms,
+int get_lowp_map(void* ptr, long long n, long long m, long long groups, long long ms,
                         long long gs, CUtensorMap* out) {
   MapKey key{ptr, n, m, groups, ms, gs, -16, 32, 64};
   std::lock_guard<std::mutex> lock(g_maps_mu);

@@ -15,6 +15,7 @@ of ``nanofed/models/mnist.py:9-14,17-27`` as executed by ``trainer/base.py:145-1
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -323,6 +324,24 @@ def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp:
 def linear_dgrad(w: torch.Tensor, dy: torch.Tensor, out: torch.Tensor) -> None:
     """``out[c, b, i] = Σ_j dy[c, b, j]·w[c, j, i]`` (bf16)."""
     j, i = w.shape[1], w.shape[2]
+    if (j == 128 and dy.shape[1] <= 128 and i % 64 == 0 and out.stride(2) == 1
+            and os.environ.get("NFB_NO_PERSISTENT_FC") is None):
+        # persistent form (tc_fc.cu): dy resident, weight tiles streamed, double-buffered TMEM
+        lib = _lib()
+        if not getattr(lib, "_fc_dgrad_declared", False):
+            lib.nfb_tc_fc_dgrad.restype = C.c_int
+            lib.nfb_tc_fc_dgrad.argtypes = [C.POINTER(_Operand), C.POINTER(_Operand), C.c_void_p,
+                                            C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p]
+            lib._fc_dgrad_declared = True
+        assert out.dtype == torch.bfloat16 and out.shape == (w.shape[0], dy.shape[1], i)
+        oa, ob = _operand(dy), _operand(w)
+        st = status_word(dy.device)
+        code = lib.nfb_tc_fc_dgrad(C.byref(oa), C.byref(ob), out.data_ptr(), out.stride(1),
+                                   out.stride(0), st.data_ptr(),
+                                   torch.cuda.current_stream(dy.device).cuda_stream)
+        native._check(code, "tc_fc_dgrad")
+        native._count()
+        return
     if dy.shape[1] <= 128 and out.is_contiguous():
         # M = batch rows (zero-padded to 128 by TMA), N = i: row-major output, TMA-store epilogue
         gemm(FC_DGRAD_ROWS, dy, w, out, m=dy.shape[1], n=i,

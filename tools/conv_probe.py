@@ -23,6 +23,14 @@ def t(fn):
 print("debug", os.environ.get("NFB_CONV_DEBUG", "0"),
       "fwd %.1f us" % t(lambda: tc.conv3x3_fwd_persistent(x, w, bias, o64, 26)),
       "dgrad %.1f us" % t(lambda: tc.conv3x3_dgrad_persistent(dy, w, o32, 26, relu_mask=x)))
+p = torch.zeros(c, b, 9216, device="cuda", dtype=torch.bfloat16)
+idx = torch.zeros(c, b, 144, 64, device="cuda", dtype=torch.uint8)
+rng = torch.zeros(1, dtype=torch.int64, device="cuda")
+x1 = torch.randn(c, b, 784, device="cuda")
+g1 = torch.zeros(c, 1024, device="cuda")
+print("debug", os.environ.get("NFB_CONV_DEBUG", "0"),
+      "fwd+pool %.1f us" % t(lambda: tc.conv3x3_pool_fwd(x, w, bias, p, idx, b, 26, 0.25, rng, 1)),
+      "dgrad+wgrad1 %.1f us" % t(lambda: tc.conv3x3_dgrad_wgrad1(dy, w, x, x1, g1, 64, 512, 26)))
 n_total = 64 * 32 * 9 + 64
 grad = torch.zeros(c, n_total, device="cuda")
 print("debug", os.environ.get("NFB_CONV_DEBUG", "0"),

@@ -165,6 +165,18 @@ def check_fc_dgrad():
     return out.float(), torch.einsum("cbj,cji->cbi", dy.float(), w.float())
 
 
+def check_fc_dgrad_ragged():
+    """Persistent fc dgrad with a batch that is not a multiple of 32 and strided weights."""
+    from nanofed_b200.ops import tc
+    c, b, j, i = 5, 100, 128, 1152
+    wbuf = _bf(c, j * i + 512, scale=0.02)
+    w = wbuf[:, 256:256 + j * i].unflatten(1, (j, i))
+    dy = _bf(c, b, j)
+    out = torch.zeros(c, b, i, device="cuda", dtype=torch.bfloat16)
+    tc.linear_dgrad(w, dy, out)
+    return out.float(), torch.einsum("cbj,cji->cbi", dy.float(), w.float())
+
+
 def check_fc_wgrad():
     from nanofed_b200.ops import tc
     c, b, j, i = 2, 64, 128, 9216
@@ -235,7 +247,7 @@ def check_conv_dgrad_wgrad1():
 
 CHECKS = {"conv_dgrad_wgrad1": check_conv_dgrad_wgrad1, "fc_wgrad_sgd": check_fc_wgrad_sgd, "conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
           "conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
-          "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad,
+          "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad, "fc_dgrad_ragged": check_fc_dgrad_ragged,
           "fc_wgrad": check_fc_wgrad}
 
 
