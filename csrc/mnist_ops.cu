@@ -171,7 +171,11 @@ __global__ void __launch_bounds__(256)
     pool_bwd_kernel(const __nv_bfloat16* __restrict__ dp, const uint8_t* __restrict__ pidx, int B,
                     float drop_p, __nv_bfloat16* __restrict__ da2, float* __restrict__ grads,
                     int64_t row_stride, int64_t b2_off) {
-  __shared__ __nv_bfloat16 sd[144 * 66];  // [pos][ch] (padded rows) gradient w.r.t. pooled pre-dropout value
+  // [pos][ch] gradient w.r.t. the pooled pre-dropout value.  Rows are 72 bf16 (36 words): the
+  // transposing writes below put 32 channel pairs of one position in 32 different banks, and the
+  // readers' 16-byte loads stay aligned.  (History: [pos][66] with lanes along positions was an
+  // 8-way bank conflict on 9216 two-byte stores per image.)
+  __shared__ __align__(16) __nv_bfloat16 sd[144 * 72];
   __shared__ float sbias[64];
   const int b = blockIdx.x, c = blockIdx.y;
   const int64_t img = static_cast<int64_t>(c) * B + b;
@@ -179,13 +183,20 @@ __global__ void __launch_bounds__(256)
   const uint8_t* idx = pidx + img * 144 * 64;
   const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   if (threadIdx.x < 64) sbias[threadIdx.x] = 0.f;
-  for (int i8 = threadIdx.x; i8 < 9216 / 8; i8 += blockDim.x) {   // 16-byte loads, 144 % 8 == 0
-    const int i = i8 * 8;
-    const int ch = i / 144, pos = i % 144;
-    const uint4 raw = ld_stream(src + i);
-    const __nv_bfloat16* v = reinterpret_cast<const __nv_bfloat16*>(&raw);
+  {
+    // item = (position octet, channel pair): lanes run over the 32 channel pairs
+    uint32_t* sd32 = reinterpret_cast<uint32_t*>(sd);
+    for (int it = threadIdx.x; it < 18 * 32; it += blockDim.x) {
+      const int cp = it & 31, oc = it >> 5;
+      const uint4 ra = ld_stream(src + (2 * cp) * 144 + oc * 8);
+      const uint4 rb = ld_stream(src + (2 * cp + 1) * 144 + oc * 8);
+      const uint32_t a[4] = {ra.x, ra.y, ra.z, ra.w}, bb[4] = {rb.x, rb.y, rb.z, rb.w};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) sd[(pos + j) * 66 + ch] = v[j];
+      for (int j = 0; j < 4; ++j) {                 // two positions per 32-bit source word
+        sd32[(oc * 8 + 2 * j) * 36 + cp] = (a[j] & 0xffffu) | (bb[j] << 16);
+        sd32[(oc * 8 + 2 * j + 1) * 36 + cp] = (a[j] >> 16) | (bb[j] & 0xffff0000u);
+      }
+    }
   }
   __syncthreads();
   __nv_bfloat16* dst = da2 + img * kGrid * 64;
@@ -202,11 +213,12 @@ __global__ void __launch_bounds__(256)
       const int me = (oh & 1) * 2 + (ow & 1);
       const uint2 codes = *reinterpret_cast<const uint2*>(idx + pos * 64 + oct * 8);
       const uint8_t* code = reinterpret_cast<const uint8_t*>(&codes);
+      float gv[8];
+      unpack<__nv_bfloat16>(*reinterpret_cast<const uint4*>(sd + pos * 72 + oct * 8), gv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const uint8_t cd = code[j];
-        if ((cd & 3) == me && (cd & 4) && (cd & 8))
-          out[j] = __bfloat162float(sd[pos * 66 + oct * 8 + j]) * keep_scale;
+        if ((cd & 3) == me && (cd & 4) && (cd & 8)) out[j] = gv[j] * keep_scale;
       }
     }
     st_vec(dst + q * 64 + oct * 8, pack<__nv_bfloat16>(out));

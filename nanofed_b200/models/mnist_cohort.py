@@ -112,6 +112,7 @@ class MnistCohortNet:
         self.fc1_master = arena.slots[:, o : o + 128 * 9216].unflatten(1, (128, 9216))
         self._fc1_range = (o, o + 128 * 9216)
         self.fuse_conv1_wgrad = os.environ.get("NFB_NO_FUSED_WGRAD1") is None
+        self.tc_conv1 = os.environ.get("NFB_NO_TC_CONV1") is None
         # momentum needs the gradient history in a buffer: only plain SGD is fused
         self.fuse_fc1_sgd = (cfg.momentum == 0.0 and os.environ.get("NFB_NO_FUSED_SGD") is None)
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
@@ -168,9 +169,12 @@ class MnistCohortNet:
         # ---- forward ----
         self._check(lib.nfb_mnist_prep_conv2(slots.data_ptr(), n, off["conv2.weight"], c,
                                              self.w2p.data_ptr(), st), "prep_conv2")
-        self._check(lib.nfb_mnist_conv1_fwd(x.data_ptr(), xs, slots.data_ptr(), n,
-                                            off["conv1.weight"], off["conv1.bias"], c, b,
-                                            self.a1.data_ptr(), st), "conv1_fwd")
+        if self.tc_conv1:
+            tc.conv1_fwd(x, slots, off["conv1.weight"], off["conv1.bias"], self.a1, 26)
+        else:
+            self._check(lib.nfb_mnist_conv1_fwd(x.data_ptr(), xs, slots.data_ptr(), n,
+                                                off["conv1.weight"], off["conv1.bias"], c, b,
+                                                self.a1.data_ptr(), st), "conv1_fwd")
         # conv2 + bias + ReLU + max-pool + dropout in one kernel: the 24x24x64 conv output
         # (177 MB per step for 32 clients) never exists in memory
         tc.conv3x3_pool_fwd(self.a1, self.w2p, self._conv2_bias[g0:g1], self.p, self.pidx, b, 26,

@@ -143,6 +143,34 @@ def _conv_persistent(mode: int, a: torch.Tensor, w: torch.Tensor, out: torch.Ten
     native._count()
 
 
+def conv1_fwd(x1: torch.Tensor, slots: torch.Tensor, w_off: int, b_off: int, a1: torch.Tensor,
+              width: int) -> None:
+    """conv (1→32, 3×3) + bias + ReLU as ONE tcgen05 MMA per 128 positions (``tc_conv1.cu``).
+
+    x1 ``[C, B, ...]`` fp32 images of ``(W+2)²`` pixels (free client stride), slots ``[C, n]`` fp32
+    parameter rows holding ``conv1.weight [32, 9]`` at ``w_off`` and ``conv1.bias`` at ``b_off``,
+    a1 ``[C, B·W², 32]`` bf16 (NHWC, row-flattened).
+    """
+    lib = _lib()
+    if not getattr(lib, "_conv1_declared", False):
+        ll = C.c_longlong
+        lib.nfb_tc_conv1_fwd.restype = C.c_int
+        lib.nfb_tc_conv1_fwd.argtypes = [C.c_void_p, ll, C.c_void_p, ll, ll, ll, C.c_int, C.c_int,
+                                         C.c_int, C.c_void_p, ll, C.c_void_p, C.c_void_p]
+        lib._conv1_declared = True
+    assert x1.dtype == torch.float32 and x1[0].is_contiguous() and slots.dtype == torch.float32
+    assert a1.dtype == torch.bfloat16 and a1.is_contiguous() and a1.shape[2] == 32
+    images = x1.shape[1]
+    assert x1[0].numel() == images * (width + 2) ** 2 and a1.shape[1] == images * width * width
+    st = status_word(a1.device)
+    code = lib.nfb_tc_conv1_fwd(x1.data_ptr(), x1.stride(0), slots.data_ptr(), slots.stride(0),
+                                int(w_off), int(b_off), a1.shape[0], images, width, a1.data_ptr(),
+                                a1.stride(0), st.data_ptr(),
+                                torch.cuda.current_stream(a1.device).cuda_stream)
+    native._check(code, "tc_conv1_fwd")
+    native._count()
+
+
 def conv3x3_dgrad_wgrad1(dy: torch.Tensor, w: torch.Tensor, relu_mask: torch.Tensor,
                          x1: torch.Tensor, grads: torch.Tensor, w1_off: int, b1_off: int,
                          width: int) -> None:

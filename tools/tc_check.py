@@ -212,6 +212,25 @@ def check_fc_wgrad_sgd():
     return wv.clone(), want
 
 
+def check_conv1_fwd():
+    """conv1 + bias + ReLU on the tensor core vs F.conv2d (fp32)."""
+    import torch.nn.functional as F
+    from nanofed_b200.ops import tc
+    c, b = 3, 7
+    x1 = torch.randn(c, b + 1, 28 * 28, device="cuda")[:, 1:]
+    n = 1024
+    slots = torch.randn(c, n, device="cuda") * 0.3
+    w_off, b_off = 64, 512
+    a1 = torch.zeros(c, b * W * W, 32, device="cuda", dtype=torch.bfloat16)
+    tc.conv1_fwd(x1, slots, w_off, b_off, a1, W)
+    outs = []
+    for k in range(c):
+        wk = slots[k, w_off:w_off + 288].view(32, 1, 3, 3)
+        y = F.relu(F.conv2d(x1[k].reshape(b, 1, 28, 28), wk, slots[k, b_off:b_off + 32]))
+        outs.append(y.permute(0, 2, 3, 1).reshape(b * W * W, 32))
+    return a1.float(), torch.stack(outs)
+
+
 def check_conv_dgrad_wgrad1():
     """dgrad of conv2 fused with the weight/bias gradient of conv1 (da1 never stored)."""
     from nanofed_b200.ops import tc
@@ -245,7 +264,7 @@ def check_conv_dgrad_wgrad1():
     return got, want
 
 
-CHECKS = {"conv_dgrad_wgrad1": check_conv_dgrad_wgrad1, "fc_wgrad_sgd": check_fc_wgrad_sgd, "conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
+CHECKS = {"conv1_fwd": check_conv1_fwd, "conv_dgrad_wgrad1": check_conv_dgrad_wgrad1, "fc_wgrad_sgd": check_fc_wgrad_sgd, "conv_pool": check_conv_pool, "conv_wgrad_p": check_conv_wgrad_p, "conv_fwd_p": check_conv_fwd_p, "conv_dgrad_p": check_conv_dgrad_p,
           "conv_fwd": check_conv_fwd, "conv_dgrad": check_conv_dgrad,
           "conv_wgrad": check_conv_wgrad, "fc_fwd": check_fc_fwd, "fc_dgrad": check_fc_dgrad, "fc_dgrad_ragged": check_fc_dgrad_ragged,
           "fc_wgrad": check_fc_wgrad}
