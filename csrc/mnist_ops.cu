@@ -171,11 +171,7 @@ __global__ void __launch_bounds__(256)
     pool_bwd_kernel(const __nv_bfloat16* __restrict__ dp, const uint8_t* __restrict__ pidx, int B,
                     float drop_p, __nv_bfloat16* __restrict__ da2, float* __restrict__ grads,
                     int64_t row_stride, int64_t b2_off) {
-  // [pos][ch] gradient w.r.t. the pooled pre-dropout value.  Rows are 72 bf16 (36 words): the
-  // transposing writes below put 32 channel pairs of one position in 32 different banks, and the
-  // readers' 16-byte loads stay aligned.  (History: [pos][66] with lanes along positions was an
-  // 8-way bank conflict on 9216 two-byte stores per image.)
-  __shared__ __align__(16) __nv_bfloat16 sd[144 * 72];
+  __shared__ __nv_bfloat16 sd[144 * 66];  // [pos][ch] (padded rows) gradient w.r.t. pooled pre-dropout value
   __shared__ float sbias[64];
   const int b = blockIdx.x, c = blockIdx.y;
   const int64_t img = static_cast<int64_t>(c) * B + b;
@@ -183,20 +179,13 @@ __global__ void __launch_bounds__(256)
   const uint8_t* idx = pidx + img * 144 * 64;
   const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   if (threadIdx.x < 64) sbias[threadIdx.x] = 0.f;
-  {
-    // item = (position octet, channel pair): lanes run over the 32 channel pairs
-    uint32_t* sd32 = reinterpret_cast<uint32_t*>(sd);
-    for (int it = threadIdx.x; it < 18 * 32; it += blockDim.x) {
-      const int cp = it & 31, oc = it >> 5;
-      const uint4 ra = ld_stream(src + (2 * cp) * 144 + oc * 8);
-      const uint4 rb = ld_stream(src + (2 * cp + 1) * 144 + oc * 8);
-      const uint32_t a[4] = {ra.x, ra.y, ra.z, ra.w}, bb[4] = {rb.x, rb.y, rb.z, rb.w};
+  for (int i8 = threadIdx.x; i8 < 9216 / 8; i8 += blockDim.x) {   // 16-byte loads, 144 % 8 == 0
+    const int i = i8 * 8;
+    const int ch = i / 144, pos = i % 144;
+    const uint4 raw = ld_stream(src + i);
+    const __nv_bfloat16* v = reinterpret_cast<const __nv_bfloat16*>(&raw);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {                 // two positions per 32-bit source word
-        sd32[(oc * 8 + 2 * j) * 36 + cp] = (a[j] & 0xffffu) | (bb[j] << 16);
-        sd32[(oc * 8 + 2 * j + 1) * 36 + cp] = (a[j] >> 16) | (bb[j] & 0xffff0000u);
-      }
-    }
+    for (int j = 0; j < 8; ++j) sd[(pos + j) * 66 + ch] = v[j];
   }
   __syncthreads();
   __nv_bfloat16* dst = da2 + img * kGrid * 64;
@@ -204,27 +193,44 @@ __global__ void __launch_bounds__(256)
   // blockDim.x % 8 == 0, so a thread keeps the same channel octet for all its items and can
   // accumulate the bias gradient in registers.
   float bsum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (int it = threadIdx.x; it < kGrid * 8; it += blockDim.x) {
-    const int oct = it & 7, q = it >> 3;
-    const int oh = q / kG, ow = q % kG;
-    float out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (oh < 24 && ow < 24) {
-      const int pos = (oh >> 1) * kPool + (ow >> 1);
-      const int me = (oh & 1) * 2 + (ow & 1);
-      const uint2 codes = *reinterpret_cast<const uint2*>(idx + pos * 64 + oct * 8);
-      const uint8_t* code = reinterpret_cast<const uint8_t*>(&codes);
-      float gv[8];
-      unpack<__nv_bfloat16>(*reinterpret_cast<const uint4*>(sd + pos * 72 + oct * 8), gv);
+  // four items per trip, their argmax-code loads issued together (the loop used to expose one
+  // L2 round trip per item)
+  for (int it0 = threadIdx.x; it0 < kGrid * 8; it0 += 4 * blockDim.x) {
+    uint2 codes[4];
+    int pos[4], me[4];
+    bool live[4], inside[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const uint8_t cd = code[j];
-        if ((cd & 3) == me && (cd & 4) && (cd & 8)) out[j] = gv[j] * keep_scale;
-      }
+    for (int u = 0; u < 4; ++u) {
+      const int it = it0 + u * blockDim.x;
+      live[u] = it < kGrid * 8;
+      const int q = it >> 3, oh = q / kG, ow = q % kG;
+      inside[u] = live[u] && oh < 24 && ow < 24;
+      pos[u] = (oh >> 1) * kPool + (ow >> 1);
+      me[u] = (oh & 1) * 2 + (ow & 1);
+      codes[u] = make_uint2(0u, 0u);
+      if (inside[u])
+        codes[u] = *reinterpret_cast<const uint2*>(idx + pos[u] * 64 + (it & 7) * 8);
     }
-    st_vec(dst + q * 64 + oct * 8, pack<__nv_bfloat16>(out));
-    // bias gradient: sum over positions (values bf16-rounded exactly as conv wgrad sees them)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) bsum[j] += __bfloat162float(__float2bfloat16_rn(out[j]));
+    for (int u = 0; u < 4; ++u) {
+      if (!live[u]) continue;
+      const int it = it0 + u * blockDim.x;
+      const int oct = it & 7, q = it >> 3;
+      float out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (inside[u]) {
+        const uint8_t* code = reinterpret_cast<const uint8_t*>(&codes[u]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint8_t cd = code[j];
+          if ((cd & 3) == me[u] && (cd & 4) && (cd & 8))
+            out[j] = __bfloat162float(sd[pos[u] * 66 + oct * 8 + j]) * keep_scale;
+        }
+      }
+      st_vec(dst + q * 64 + oct * 8, pack<__nv_bfloat16>(out));
+      // bias gradient: sum over positions (values bf16-rounded exactly as conv wgrad sees them)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bsum[j] += __bfloat162float(__float2bfloat16_rn(out[j]));
+    }
   }
   {
     const int oct = threadIdx.x & 7;
@@ -250,27 +256,35 @@ __global__ void __launch_bounds__(256)
 // counters that replace the reference's two .item() syncs per batch — and bumps the
 // per-step dropout counter.
 // -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(256)
     fc_head_kernel(float* __restrict__ hpre, const int64_t* __restrict__ labels,
                    int64_t label_stride, int B, const float* __restrict__ slots,
                    float* __restrict__ grads, int64_t row_stride, int64_t b1_off, int64_t w2_off,
                    int64_t b2_off, float drop_p, unsigned long long* __restrict__ rng_state,
                    int advance_rng, uint64_t seed, __nv_bfloat16* __restrict__ dh,
                    float* __restrict__ stats) {
+  // grid (clients, splits): block (c, s) owns batch rows [r0, r1) of client c.  With one block
+  // per client (the first version) 32 of 148 SMs worked for 34 us; parameter-gradient partial
+  // sums of the row blocks meet in fp32 atomics (targets are zeroed by K-OPT after use).
   extern __shared__ float smem[];
-  float* h = smem;                 // [B][128]   (later reused for dh in fp32)
-  float* w2 = h + B * 128;         // [10][128]
-  float* lg = w2 + 1280;           // [B][10] logits -> dlogits
-  float* red = lg + B * 10;        // [64]
+  const int splits = gridDim.y;
+  const int rows_per = (B + splits - 1) / splits;
+  const int r0 = blockIdx.y * rows_per;
+  const int nb = max(min(B, r0 + rows_per) - r0, 0);
+  float* h = smem;                 // [rows_per][128]   (later reused for dh in fp32)
+  float* w2 = h + rows_per * 128;  // [10][128]
+  float* lg = w2 + 1280;           // [rows_per][10] logits -> dlogits
+  float* red = lg + rows_per * 10; // [64]
   const int c = blockIdx.x;
   const float* row = slots + c * row_stride;
   float* grow = grads + c * row_stride;
-  const uint64_t step = rng_state ? *rng_state : 0ull;
+  const uint64_t step = rng_state ? rng_state[0] : 0ull;
   const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const bool shared_targets = splits > 1;
 
   for (int i = threadIdx.x; i < 1280; i += blockDim.x) w2[i] = row[w2_off + i];
-  float* hp = hpre + static_cast<int64_t>(c) * B * 128;
-  for (int i4 = threadIdx.x; i4 < B * 32; i4 += blockDim.x) {   // 4 elements per Philox draw
+  float* hp = hpre + (static_cast<int64_t>(c) * B + r0) * 128;
+  for (int i4 = threadIdx.x; i4 < nb * 32; i4 += blockDim.x) {   // 4 elements per Philox draw
     const int i = i4 * 4;
     const float4 hv = *reinterpret_cast<const float4*>(hp + i);
     // hpre is a split-K atomic accumulator: leave it zeroed for the next step's fc1 forward
@@ -279,7 +293,7 @@ __global__ void __launch_bounds__(1024)
     float v[4] = {fmaxf(hv.x + bv.x, 0.f), fmaxf(hv.y + bv.y, 0.f), fmaxf(hv.z + bv.z, 0.f),
                   fmaxf(hv.w + bv.w, 0.f)};
     if (drop_p > 0.f) {
-      const uint64_t grp = static_cast<uint64_t>(c) * B * 32 + i4;
+      const uint64_t grp = (static_cast<uint64_t>(c) * B + r0) * 32 + i4;
       const float4 u = Philox::uniform4((step << 34) + (1ull << 33) + grp, seed);
       v[0] = u.x >= drop_p ? v[0] * keep_scale : 0.f;
       v[1] = u.y >= drop_p ? v[1] * keep_scale : 0.f;
@@ -290,7 +304,7 @@ __global__ void __launch_bounds__(1024)
   }
   __syncthreads();
   // logits
-  for (int i = threadIdx.x; i < B * 10; i += blockDim.x) {
+  for (int i = threadIdx.x; i < nb * 10; i += blockDim.x) {
     const int b = i / 10, k = i % 10;
     float acc = row[b2_off + k];
     const float* hb = h + b * 128;
@@ -302,9 +316,9 @@ __global__ void __launch_bounds__(1024)
   __syncthreads();
   // softmax / loss / accuracy / dlogits : one thread per sample
   float my_loss = 0.f, my_hit = 0.f;
-  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
     float* l = lg + b * 10;
-    const int t = static_cast<int>(labels[c * label_stride + b]);
+    const int t = static_cast<int>(labels[c * label_stride + r0 + b]);
     float mx = l[0];
     int arg = 0;
     for (int k = 1; k < 10; ++k)
@@ -319,27 +333,35 @@ __global__ void __launch_bounds__(1024)
   }
   my_loss = block_sum(my_loss, red);
   my_hit = block_sum(my_hit, red);
-  if (threadIdx.x == 0) {
-    stats[3 * c + 0] += my_loss;
-    stats[3 * c + 1] += my_hit;
-    stats[3 * c + 2] += static_cast<float>(B);
+  if (threadIdx.x == 0 && nb > 0) {
+    if (shared_targets) {
+      atomicAdd(&stats[3 * c + 0], my_loss);
+      atomicAdd(&stats[3 * c + 1], my_hit);
+      atomicAdd(&stats[3 * c + 2], static_cast<float>(nb));
+    } else {
+      stats[3 * c + 0] += my_loss;
+      stats[3 * c + 1] += my_hit;
+      stats[3 * c + 2] += static_cast<float>(nb);
+    }
   }
-  // fc2 gradients (plain stores: this block owns client c's rows)
+  // fc2 gradients over this block's rows
   for (int i = threadIdx.x; i < 1280; i += blockDim.x) {
     const int k = i >> 7, j = i & 127;
     float acc = 0.f;
-    for (int b = 0; b < B; ++b) acc = fmaf(lg[b * 10 + k], h[b * 128 + j], acc);
-    grow[w2_off + i] = acc;
+    for (int b = 0; b < nb; ++b) acc = fmaf(lg[b * 10 + k], h[b * 128 + j], acc);
+    if (shared_targets) atomicAdd(&grow[w2_off + i], acc);
+    else grow[w2_off + i] = acc;
   }
   if (threadIdx.x < 10) {
     float acc = 0.f;
-    for (int b = 0; b < B; ++b) acc += lg[b * 10 + threadIdx.x];
-    grow[b2_off + threadIdx.x] = acc;
+    for (int b = 0; b < nb; ++b) acc += lg[b * 10 + threadIdx.x];
+    if (shared_targets) atomicAdd(&grow[b2_off + threadIdx.x], acc);
+    else grow[b2_off + threadIdx.x] = acc;
   }
   __syncthreads();
   // dh (gradient w.r.t. hpre), written in place over h
-  __nv_bfloat16* dhc = dh + static_cast<int64_t>(c) * B * 128;
-  for (int i = threadIdx.x; i < B * 128; i += blockDim.x) {
+  __nv_bfloat16* dhc = dh + (static_cast<int64_t>(c) * B + r0) * 128;
+  for (int i = threadIdx.x; i < nb * 128; i += blockDim.x) {
     const int b = i >> 7, j = i & 127;
     float acc = 0.f;
 #pragma unroll
@@ -352,10 +374,20 @@ __global__ void __launch_bounds__(1024)
   __syncthreads();
   if (threadIdx.x < 128) {
     float acc = 0.f;
-    for (int b = 0; b < B; ++b) acc += h[b * 128 + threadIdx.x];
-    grow[b1_off + threadIdx.x] = acc;
+    for (int b = 0; b < nb; ++b) acc += h[b * 128 + threadIdx.x];
+    if (shared_targets) atomicAdd(&grow[b1_off + threadIdx.x], acc);
+    else grow[b1_off + threadIdx.x] = acc;
   }
-  if (advance_rng && c == 0 && threadIdx.x == 0 && rng_state) *rng_state = step + 1;
+  // dropout step counter: bumped by whichever block finishes LAST (rng_state[1] counts arrivals
+  // and is left at zero), so no block can read the new value as its own step
+  if (advance_rng && rng_state && threadIdx.x == 0) {
+    __threadfence();
+    const unsigned long long total = static_cast<unsigned long long>(gridDim.x) * gridDim.y;
+    if (atomicAdd(&rng_state[1], 1ull) == total - 1) {
+      rng_state[1] = 0ull;
+      rng_state[0] = step + 1;
+    }
+  }
 }
 
 // -------------------------------------------------------------------------------------
@@ -475,14 +507,16 @@ int nfb_mnist_fc_head(float* hpre, const int64_t* labels, int64_t label_stride, 
   NFB_REQUIRE(hpre && labels && slots && grads && dh && stats, NFB_EINVAL,
               "mnist_fc_head: null pointer");
   NFB_REQUIRE(B >= 1 && B <= 256, NFB_ERANGE, "mnist_fc_head: batch %d outside [1, 256]", B);
-  const size_t smem = (static_cast<size_t>(B) * 128 + 1280 + static_cast<size_t>(B) * 10 + 64) *
-                      sizeof(float);
+  const int splits = B >= 32 ? 4 : 1;
+  const int rows_per = (B + splits - 1) / splits;
+  const size_t smem = (static_cast<size_t>(rows_per) * 128 + 1280 +
+                       static_cast<size_t>(rows_per) * 10 + 64) * sizeof(float);
   static bool attr = false;
   if (!attr) {
     cudaFuncSetAttribute(fc_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     attr = true;
   }
-  fc_head_kernel<<<C, 1024, smem, as_stream(stream)>>>(
+  fc_head_kernel<<<dim3(C, splits), 256, smem, as_stream(stream)>>>(
       hpre, labels, label_stride, B, slots, grads, row_stride, b1_off, w2_off, b2_off, drop_p,
       static_cast<unsigned long long*>(rng_state), advance_rng, seed,
       static_cast<__nv_bfloat16*>(dh), stats);

@@ -14,6 +14,7 @@ struct SgdArgs {
   int64_t row_len;      // > 0: the flat buffer is [rows][row_len] ...
   int64_t zero_prefix;  // ... and g[row][0 : zero_prefix) is zeroed after use (atomic accumulators)
   int64_t skip_lo, skip_len;  // columns [skip_lo, skip_lo + skip_len) of every row are left alone
+  int64_t zero_from;          // > 0: g[row][zero_from : row_len) is zeroed after use as well
 };
 
 template <typename G>
@@ -42,10 +43,16 @@ __global__ void __launch_bounds__(256)
     }
 #pragma unroll
     for (int e = 0; e < 4; ++e) gv[e] = e < cnt ? to_f32(g[base + e]) * gs : 0.f;
-    if (a.zero_prefix > 0 && (base % a.row_len) < a.zero_prefix) {
+    if (a.zero_prefix > 0 || a.zero_from > 0) {
       // gradient entries that the next step accumulates into with atomics: hand them back zeroed
-      for (int e = 0; e < cnt; ++e)
-        if ((base + e) % a.row_len < a.zero_prefix) g[base + e] = from_f32<G>(0.f);
+      const int64_t col = base % a.row_len;
+      if (col < a.zero_prefix || (a.zero_from > 0 && col + 3 >= a.zero_from)) {
+        for (int e = 0; e < cnt; ++e) {
+          const int64_t ce = (base + e) % a.row_len;
+          if (ce < a.zero_prefix || (a.zero_from > 0 && ce >= a.zero_from))
+            g[base + e] = from_f32<G>(0.f);
+        }
+      }
     }
     if (a.noise_std > 0.f) {
       const float4 z = Philox::normal4(a.group0 + (base >> 2), a.seed);
@@ -125,7 +132,7 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
                           float weight_decay, int nesterov, int first_step,
                           const float* grad_scale, float noise_std, uint64_t seed,
                           uint64_t offset, int64_t row_len, int64_t zero_prefix, int64_t skip_lo,
-                          int64_t skip_hi, void* stream) {
+                          int64_t skip_hi, int64_t zero_from, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
   NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
@@ -133,6 +140,9 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
   if (n <= 0) return 0;
   NFB_REQUIRE(zero_prefix == 0 || (row_len > 0 && zero_prefix <= row_len && n % row_len == 0),
               NFB_EINVAL, "fused_sgd: bad row_len/zero_prefix");
+  NFB_REQUIRE(zero_from == 0 || (row_len > 0 && zero_from > 0 && zero_from <= row_len &&
+                                 n % row_len == 0),
+              NFB_EINVAL, "fused_sgd: bad zero_from");
   const int64_t skip_len = skip_hi - skip_lo;
   NFB_REQUIRE(skip_len == 0 ||
                   (row_len > 0 && n % row_len == 0 && skip_lo >= 0 && skip_len > 0 &&
@@ -140,7 +150,7 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
               NFB_EINVAL, "fused_sgd: skipped range must lie in a row, multiples of 4");
   SgdArgs a{lr, momentum, dampening, weight_decay, noise_std, nesterov, first_step,
             grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix, skip_lo,
-            skip_len};
+            skip_len, zero_from};
   float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
   cudaStream_t st = as_stream(stream);
   const int64_t work = skip_len > 0 ? (n / row_len) * (row_len - skip_len) : n;
@@ -160,22 +170,23 @@ extern "C" int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf
                              uint64_t offset, int64_t row_len, int64_t zero_prefix, void* stream) {
   return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
                         weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
-                        row_len, zero_prefix, 0, 0, stream);
+                        row_len, zero_prefix, 0, 0, 0, stream);
 }
 
 // Same update, except that columns [skip_lo, skip_hi) of every row are not touched (neither
 // read nor written): they belong to a parameter whose update was already applied by the kernel
-// that produced its gradient (nfb_tc_linear_wgrad_sgd).
+// that produced its gradient (nfb_tc_linear_wgrad_sgd).  zero_from > 0 additionally zeroes
+// g[row][zero_from : row_len) after use (a second block of atomically accumulated entries).
 extern "C" int nfb_fused_sgd_skip(float* p, void* g, int g_dtype, float* momentum_buf,
                                   void* lowp_out, int64_t n, float lr, float momentum,
                                   float dampening, float weight_decay, int nesterov,
                                   int first_step, const float* grad_scale, float noise_std,
                                   uint64_t seed, uint64_t offset, int64_t row_len,
                                   int64_t zero_prefix, int64_t skip_lo, int64_t skip_hi,
-                                  void* stream) {
+                                  int64_t zero_from, void* stream) {
   return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
                         weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
-                        row_len, zero_prefix, skip_lo, skip_hi, stream);
+                        row_len, zero_prefix, skip_lo, skip_hi, zero_from, stream);
 }
 
 extern "C" int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg,

@@ -3,10 +3,13 @@
 // K = 9 looks too thin for UMMA, and the first version of this layer ran on CUDA cores (45 us per
 // step for 32 clients x 64 images, LSU-bound: 18 LDS.128 per 144 FMA).  As a GEMM it is
 //     a1[q, ch] = relu( sum_t X[q, t] * W[ch, t] ),   X[q, t] = x[pixel(q) + tap t],  t = 0..8
-// with K padded to 16: ONE tcgen05.mma (128 x 32 x 16) per 128 output positions; the fp32 bias is
-// added in the epilogue.  The im2col rows are built in shared
-// memory by the threads that later read the result (9 cached loads + two 16-byte stores each), so
-// the kernel is bound by its 88 MB of output.
+// and the fp32 bias added in the epilogue.  bf16 operands alone would cost this layer its fp32
+// accuracy (the ReLU pattern of a1 is the mask of the backward pass; conv1.bias' gradient moved
+// from 8 % to 11 % off the fp32 reference), so both operands are split into bf16 high and low
+// parts and K carries three products:  x_hi*w_hi + x_lo*w_hi + x_hi*w_lo  (27 of K = 32, two
+// tcgen05.mma of 128 x 32 x 16 per 128 output positions; the dropped x_lo*w_lo term is 2^-16
+// relative).  The im2col rows are built in shared memory by the threads that later read the
+// result (9 cached loads + four 16-byte stores each); the kernel is bound by its 88 MB of output.
 //
 // 256 threads = two independent groups of 4 warps (warp % 4 = TMEM lane quarter).  Per tile a
 // group: writes its 128 window rows -> group barrier -> one thread issues the MMA and commits to
@@ -32,10 +35,18 @@ struct Conv1Args {
   int* status;
 };
 
-constexpr int kC1ATile = 2 * 128 * 16;   // two 8-tap chunks x 128 rows x 16 B
-constexpr int kC1BTile = 2 * 32 * 16;    // two chunks x 32 channels x 16 B
+constexpr int kC1Chunks = 4;                     // K = 32 = four 8-element chunks
+constexpr int kC1ATile = kC1Chunks * 128 * 16;   // chunks x 128 rows x 16 B
+constexpr int kC1BTile = kC1Chunks * 32 * 16;    // chunks x 32 channels x 16 B
 
-__global__ void __launch_bounds__(256, 2)
+// K slot k of an A row / B row:  k in [0,9): x_hi[t] / w_hi[t];  [9,18): x_lo[t] / w_hi[t];
+// [18,27): x_hi[t] / w_lo[t];  [27,32): zero.
+__device__ __forceinline__ void split_bf16(float v, float& hi, float& lo) {
+  hi = __bfloat162float(__float2bfloat16_rn(v));
+  lo = v - hi;
+}
+
+__global__ void __launch_bounds__(256, 3)
     tc_conv1_fwd_kernel(const __grid_constant__ CUtensorMap map_o,   // a1 [C][rows][32] bf16, box [32, 32]
                         const Conv1Args args) {
   __shared__ __align__(1024) uint8_t a_tiles[2][kC1ATile];
@@ -60,18 +71,20 @@ __global__ void __launch_bounds__(256, 2)
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc<64>(&tmem_slot);
-  if (threadIdx.x >= 64 && threadIdx.x < 96)
-    s_bias[threadIdx.x - 64] =
-        args.slots[static_cast<long long>(g) * args.slot_gs + args.b_off + threadIdx.x - 64];
-  // weights: W[ch][t] (t < 9), zeros above; chunk c holds taps 8c .. 8c+7
-  if (threadIdx.x < 64) {
+  if (threadIdx.x >= 128 && threadIdx.x < 160)
+    s_bias[threadIdx.x - 128] =
+        args.slots[static_cast<long long>(g) * args.slot_gs + args.b_off + threadIdx.x - 128];
+  // weights: one (channel, chunk) per thread
+  if (threadIdx.x < 32 * kC1Chunks) {
     const int ch = threadIdx.x & 31, chunk = threadIdx.x >> 5;
-    const float* w = args.slots + static_cast<long long>(g) * args.slot_gs;
+    const float* w = args.slots + static_cast<long long>(g) * args.slot_gs + args.w_off + ch * 9;
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int t = chunk * 8 + e;
-      v[e] = t < 9 ? w[args.w_off + ch * 9 + t] : 0.f;
+      const int k = chunk * 8 + e;
+      float hi = 0.f, lo = 0.f;
+      if (k < 27) split_bf16(w[k % 9], hi, lo);
+      v[e] = k < 18 ? hi : lo;                      // (k >= 27: both zero)
     }
     st_vec(b_tile + chunk * 512 + ch * 16, pack<__nv_bfloat16>(v));
   }
@@ -89,12 +102,10 @@ __global__ void __launch_bounds__(256, 2)
   constexpr uint32_t idesc = make_idesc_bf16(128, 32, 0u, 0u);
   const int trow = sub * 32 + lane;                // row of the group's tile this thread owns
 
-  int n_done = 0;
-  for (int tile = tile_lo + grp; tile < tile_hi; tile += 2, ++n_done) {
-    const int m = tile * 128 + trow;
-    float xv[16];
+  // this thread's 3x3 input window for a tile row (zeros past the last position)
+  auto fetch_window = [&](int m, float* dst) {
 #pragma unroll
-    for (int t = 0; t < 16; ++t) xv[t] = 0.f;
+    for (int t = 0; t < 9; ++t) dst[t] = 0.f;
     if (m < args.rows) {
       const int b = m / gsz, rem = m - b * gsz;
       const int oh = rem / args.grid_w, ow = rem - oh * args.grid_w;
@@ -102,21 +113,41 @@ __global__ void __launch_bounds__(256, 2)
 #pragma unroll
       for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
-        for (int kw = 0; kw < 3; ++kw) xv[kh * 3 + kw] = __ldg(px + kh * iw + kw);
+        for (int kw = 0; kw < 3; ++kw) dst[kh * 3 + kw] = __ldg(px + kh * iw + kw);
     }
+  };
+  float win[9];
+  if (tile_lo + grp < tile_hi) fetch_window((tile_lo + grp) * 128 + trow, win);
+  int n_done = 0;
+  for (int tile = tile_lo + grp; tile < tile_hi; tile += 2, ++n_done) {
+    float row[32];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      float hi, lo;
+      split_bf16(win[t], hi, lo);
+      row[t] = hi; row[9 + t] = lo; row[18 + t] = hi;
+    }
+#pragma unroll
+    for (int k = 27; k < 32; ++k) row[k] = 0.f;
     // (the previous MMA of this group has completed: everyone waited on its barrier below)
-    st_vec(a_tile + trow * 16, pack<__nv_bfloat16>(xv));
-    st_vec(a_tile + 2048 + trow * 16, pack<__nv_bfloat16>(xv + 8));
+#pragma unroll
+    for (int c = 0; c < kC1Chunks; ++c)
+      st_vec(a_tile + c * 2048 + trow * 16, pack<__nv_bfloat16>(row + 8 * c));
     fence_proxy_async();
     tc_fence_before();                              // orders last tile's tcgen05.ld before the MMA
     asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
     if (sub == 0 && lane == 0) {
       tc_fence_after();
-      const uint64_t da = make_smem_desc(smem_u32(a_tile), 2048, 128, 0);
-      const uint64_t db = make_smem_desc(smem_u32(b_tile), 512, 128, 0);
-      umma_f16(d_tmem, da, db, idesc, 0u);
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {              // 16 K slots = two chunks per MMA
+        const uint64_t da = make_smem_desc(smem_u32(a_tile) + kk * 4096, 2048, 128, 0);
+        const uint64_t db = make_smem_desc(smem_u32(b_tile) + kk * 1024, 512, 128, 0);
+        umma_f16(d_tmem, da, db, idesc, kk);
+      }
       umma_commit(&mma_bar[grp]);
     }
+    // the next tile's window loads fly while the tensor core works
+    if (tile + 2 < tile_hi) fetch_window((tile + 2) * 128 + trow, win);
     if (!mbar_wait(&mma_bar[grp], n_done & 1)) {
       if (lane == 0) *args.status = 1;
       break;
@@ -179,7 +210,7 @@ extern "C" int nfb_tc_conv1_fwd(const float* x, long long x_group_stride, const 
   args.rows = static_cast<int>(rows);
   args.grid_w = width;
   args.tiles_per_client = static_cast<int>((rows + 127) / 128);
-  int per_client = (2 * sm_count()) / clients;          // two resident CTAs per SM
+  int per_client = (3 * sm_count()) / clients;          // three resident CTAs per SM
   if (per_client < 1) per_client = 1;
   if (per_client > (args.tiles_per_client + 1) / 2) per_client = (args.tiles_per_client + 1) / 2;
   args.ctas_per_client = per_client;

@@ -136,12 +136,13 @@ int nfb_fused_sgd(float* p, void* g, int g_dtype, float* momentum_buf, void* low
                   void* stream);
 /* Same update, but columns [skip_lo, skip_hi) of every row_len row are neither read nor written:
  * they belong to a parameter whose gradient was applied by the kernel that produced it
- * (nfb_tc_linear_wgrad_sgd in csrc/tc_gemm.cu).  All three bounds must be multiples of 4.   */
+ * (nfb_tc_linear_wgrad_sgd in csrc/tc_gemm.cu); pass skip_lo == skip_hi for none.  The bounds
+ * must be multiples of 4.  zero_from > 0: g[r][zero_from:row_len) is zeroed after use too.  */
 int nfb_fused_sgd_skip(float* p, void* g, int g_dtype, float* momentum_buf, void* lowp_out,
                        int64_t n, float lr, float momentum, float dampening, float weight_decay,
                        int nesterov, int first_step, const float* grad_scale, float noise_std,
                        uint64_t seed, uint64_t offset, int64_t row_len, int64_t zero_prefix,
-                       int64_t skip_lo, int64_t skip_hi, void* stream);
+                       int64_t skip_lo, int64_t skip_hi, int64_t zero_from, void* stream);
 int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg, float* exp_avg_sq,
                    void* lowp_out, int64_t n, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float bias_corr1, float bias_corr2, int decoupled,

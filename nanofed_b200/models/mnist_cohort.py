@@ -101,7 +101,8 @@ class MnistCohortNet:
         self.da2 = torch.zeros(c, self.rows, 64, **bf)
         self.da1 = torch.zeros(c, self.rows, 32, **bf)
         self.grads = torch.zeros(c_all, self.n_total, dtype=torch.float32, device=dev)
-        self.rng_state = torch.zeros(1, dtype=torch.int64, device=dev)
+        # [0] dropout step counter, [1] fc_head's block-arrival counter (always back at zero)
+        self.rng_state = torch.zeros(2, dtype=torch.int64, device=dev)
         self.p1 = 0.25 if dropout else 0.0
         self.p2 = 0.5 if dropout else 0.0
         self.seed = int(cfg.seed) * 7919 + 13
@@ -152,7 +153,8 @@ class MnistCohortNet:
                        momentum=cfg.momentum, weight_decay=cfg.weight_decay,
                        first_step=(step == 0), lowp_out=a.slots_lowp.view(-1),
                        row_len=self.n_total, zero_grad_prefix=self._atomic_prefix,
-                       skip_range=self._fc1_range if self.fuse_fc1_sgd else None)
+                       skip_range=self._fc1_range if self.fuse_fc1_sgd else None,
+                       zero_grad_from=self._fc1_range[1])   # fc1.bias / fc2.*: fc_head's atomics
 
     def _step_group(self, step: int, g0: int) -> None:
         cfg, a, lib = self.cfg, self.arena, self.lib

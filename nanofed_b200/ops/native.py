@@ -119,7 +119,7 @@ def _declare(L: C.CDLL) -> None:
         "nfb_fused_sgd": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
                           _vp, _f32, _u64, _u64, _i64, _i64, _vp],
         "nfb_fused_sgd_skip": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
-                          _vp, _f32, _u64, _u64, _i64, _i64, _i64, _i64, _vp],
+                          _vp, _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp],
         "nfb_fused_adam": [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32,
                            _f32, _f32, _i32, _vp, _vp],
         "nfb_xent_fused": [_vp, _i32, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _f32, _vp, _vp,
@@ -337,6 +337,7 @@ def fused_sgd_(
     row_len: int = 0,
     zero_grad_prefix: int = 0,
     skip_range: tuple[int, int] | None = None,
+    zero_grad_from: int = 0,
 ) -> torch.Tensor:
     assert p.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous()
     assert p.numel() == g.numel()
@@ -348,10 +349,11 @@ def fused_sgd_(
               float(lr), float(momentum), float(dampening), float(weight_decay),
               1 if nesterov else 0, 1 if first_step else 0, _ptr(grad_scale), float(noise_std),
               seed & (2**64 - 1), offset, int(row_len), int(zero_grad_prefix))
-    if skip_range is None:
+    if skip_range is None and not zero_grad_from:
         _check(lib().nfb_fused_sgd(*common, _stream(p)), "fused_sgd")
     else:  # columns [lo, hi) of every row were already updated by the kernel that made their gradient
-        _check(lib().nfb_fused_sgd_skip(*common, int(skip_range[0]), int(skip_range[1]), _stream(p)),
+        lo, hi = skip_range if skip_range is not None else (0, 0)
+        _check(lib().nfb_fused_sgd_skip(*common, int(lo), int(hi), int(zero_grad_from), _stream(p)),
                "fused_sgd_skip")
     _count()
     return p

@@ -179,6 +179,7 @@ def fused_sgd_(
     row_len: int = 0,
     zero_grad_prefix: int = 0,
     skip_range: tuple[int, int] | None = None,
+    zero_grad_from: int = 0,
 ) -> torch.Tensor:
     """torch.optim.SGD semantics on flat buffers, with optional DP-SGD pre-processing.
 
@@ -211,6 +212,8 @@ def fused_sgd_(
         lowp_out.copy_(p.to(lowp_out.dtype))
     if zero_grad_prefix > 0:
         g.view(-1, row_len)[:, :zero_grad_prefix] = 0
+    if zero_grad_from > 0:
+        g.view(-1, row_len)[:, zero_grad_from:] = 0
     if keep is not None:
         for t, saved in keep:
             t.view(-1, row_len)[:, skip_range[0]:skip_range[1]] = saved

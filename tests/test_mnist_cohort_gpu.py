@@ -114,7 +114,7 @@ def test_graph_replay_trains_and_dropout_masks_advance():
         losses.append(s[0] / s[2])
     assert all(torch.isfinite(torch.tensor(losses)))
     assert losses[-1] < losses[0], losses          # it learns the synthetic labels
-    assert int(eng.rng_state.item()) == 6 * cfg.local_steps  # one dropout stream step per local step
+    assert int(eng.rng_state[0].item()) == 6 * cfg.local_steps  # one dropout stream step per local step
 
 
 def test_full_round_through_fedsimulation():

@@ -172,7 +172,7 @@ def test_fused_sgd_skips_a_column_range_and_zeroes_the_atomic_prefix():
     lowp = torch.full((rows * row_len,), 7.0, device=DEV, dtype=torch.bfloat16)
     pr, gr, lr_ = p.cpu().clone(), g.cpu().clone(), lowp.cpu().clone()
     kw = dict(weight_decay=0.01, row_len=row_len, zero_grad_prefix=prefix, skip_range=(lo, hi),
-              noise_std=0.3, seed=11, offset=8)
+              zero_grad_from=960, noise_std=0.3, seed=11, offset=8)
     ops.fused_sgd_(p, g, 0.1, lowp_out=lowp, **kw)
     ref.fused_sgd_(pr, gr, 0.1, lowp_out=lr_, **kw)
     torch.testing.assert_close(p.cpu(), pr, rtol=1e-5, atol=1e-6)
