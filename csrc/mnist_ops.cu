@@ -171,65 +171,90 @@ __global__ void __launch_bounds__(256)
     pool_bwd_kernel(const __nv_bfloat16* __restrict__ dp, const uint8_t* __restrict__ pidx, int B,
                     float drop_p, __nv_bfloat16* __restrict__ da2, float* __restrict__ grads,
                     int64_t row_stride, int64_t b2_off) {
-  __shared__ __nv_bfloat16 sd[144 * 66];  // [pos][ch] (padded rows) gradient w.r.t. pooled pre-dropout value
+  // The first version was issue-bound (ncu: 74 % issue slots, 57.6 M warp instructions): per
+  // output vector it tested 8 code bytes one by one, read 8 two-byte values and re-rounded 8
+  // values for the bias sum.  Now the 8 codes are compared with two byte-SIMD instructions, the
+  // values come as one 16-byte shared load and are masked as bf16 pairs, and the bias gradient is
+  // summed over the 144 pooled positions (each contributes once) instead of the 676 grid ones.
+  //
+  // sd = [pos][ch] gradient w.r.t. the pooled pre-dropout value, rows of 72 bf16 (16-byte
+  // aligned); the channel octet is XOR-swizzled with the position octet so that the transposing
+  // two-byte stores of phase 1 spread over banks.
+  __shared__ __align__(16) __nv_bfloat16 sd[144 * 72];
   __shared__ float sbias[64];
   const int b = blockIdx.x, c = blockIdx.y;
   const int64_t img = static_cast<int64_t>(c) * B + b;
   const __nv_bfloat16* src = dp + img * 9216;
   const uint8_t* idx = pidx + img * 144 * 64;
   const float keep_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const bool scale = keep_scale != 1.f;   // false when the producer of dp already applied it
   if (threadIdx.x < 64) sbias[threadIdx.x] = 0.f;
   for (int i8 = threadIdx.x; i8 < 9216 / 8; i8 += blockDim.x) {   // 16-byte loads, 144 % 8 == 0
     const int i = i8 * 8;
     const int ch = i / 144, pos = i % 144;
     const uint4 raw = ld_stream(src + i);
     const __nv_bfloat16* v = reinterpret_cast<const __nv_bfloat16*>(&raw);
+    const int col = (((ch >> 3) ^ ((pos >> 3) & 7)) << 3) + (ch & 7);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) sd[(pos + j) * 66 + ch] = v[j];
+    for (int j = 0; j < 8; ++j) sd[(pos + j) * 72 + col] = v[j];
   }
   __syncthreads();
-  __nv_bfloat16* dst = da2 + img * kGrid * 64;
-  // item = (grid position, channel octet): 676 * 8 items, every position is written.
-  // blockDim.x % 8 == 0, so a thread keeps the same channel octet for all its items and can
-  // accumulate the bias gradient in registers.
+  // 8 channels of pooled position `pos`, masked by an 8-byte compare result (0xff = keep)
+  auto masked = [&](int pos, int oct, uint32_t m0, uint32_t m1) {
+    uint4 v = *reinterpret_cast<const uint4*>(sd + pos * 72 + ((oct ^ ((pos >> 3) & 7)) << 3));
+    if (scale) {
+      float f[8];
+      unpack<__nv_bfloat16>(v, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] *= keep_scale;
+      v = pack<__nv_bfloat16>(f);
+    }
+    v.x &= __byte_perm(m0, 0, 0x1100);
+    v.y &= __byte_perm(m0, 0, 0x3322);
+    v.z &= __byte_perm(m1, 0, 0x1100);
+    v.w &= __byte_perm(m1, 0, 0x3322);
+    return v;
+  };
+  // conv2 bias gradient: every pooled element with ReLU and keep bits set reaches exactly one
+  // grid position.  blockDim.x % 8 == 0, so a thread keeps its channel octet.
   float bsum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  // four items per trip, their argmax-code loads issued together (the loop used to expose one
-  // L2 round trip per item)
+  for (int it = threadIdx.x; it < 144 * 8; it += blockDim.x) {
+    const int oct = it & 7, pos = it >> 3;
+    const uint2 codes = *reinterpret_cast<const uint2*>(idx + pos * 64 + oct * 8);
+    const uint4 v = masked(pos, oct, __vcmpeq4(codes.x & 0x0c0c0c0cu, 0x0c0c0c0cu),
+                           __vcmpeq4(codes.y & 0x0c0c0c0cu, 0x0c0c0c0cu));
+    float f[8];
+    unpack<__nv_bfloat16>(v, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bsum[j] += f[j];
+  }
+  __nv_bfloat16* dst = da2 + img * kGrid * 64;
+  // item = (grid position, channel octet): 676 * 8 items, every position is written; four items
+  // per trip with their code loads issued together
   for (int it0 = threadIdx.x; it0 < kGrid * 8; it0 += 4 * blockDim.x) {
     uint2 codes[4];
-    int pos[4], me[4];
-    bool live[4], inside[4];
+    int pos[4];
+    uint32_t want[4];
+    bool live[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int it = it0 + u * blockDim.x;
       live[u] = it < kGrid * 8;
       const int q = it >> 3, oh = q / kG, ow = q % kG;
-      inside[u] = live[u] && oh < 24 && ow < 24;
-      pos[u] = (oh >> 1) * kPool + (ow >> 1);
-      me[u] = (oh & 1) * 2 + (ow & 1);
-      codes[u] = make_uint2(0u, 0u);
-      if (inside[u])
-        codes[u] = *reinterpret_cast<const uint2*>(idx + pos[u] * 64 + (it & 7) * 8);
+      const bool inside = live[u] && oh < 24 && ow < 24;
+      pos[u] = inside ? (oh >> 1) * kPool + (ow >> 1) : 0;
+      // code byte: bits 0-1 argmax slot, bit 2 ReLU passed, bit 3 kept by dropout
+      want[u] = 0x0c0c0c0cu | (static_cast<uint32_t>((oh & 1) * 2 + (ow & 1)) * 0x01010101u);
+      codes[u] = make_uint2(0u, 0u);                 // never equals `want`: zeros outside
+      if (inside) codes[u] = *reinterpret_cast<const uint2*>(idx + pos[u] * 64 + (it & 7) * 8);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       if (!live[u]) continue;
       const int it = it0 + u * blockDim.x;
-      const int oct = it & 7, q = it >> 3;
-      float out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      if (inside[u]) {
-        const uint8_t* code = reinterpret_cast<const uint8_t*>(&codes[u]);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint8_t cd = code[j];
-          if ((cd & 3) == me[u] && (cd & 4) && (cd & 8))
-            out[j] = __bfloat162float(sd[pos[u] * 66 + oct * 8 + j]) * keep_scale;
-        }
-      }
-      st_vec(dst + q * 64 + oct * 8, pack<__nv_bfloat16>(out));
-      // bias gradient: sum over positions (values bf16-rounded exactly as conv wgrad sees them)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) bsum[j] += __bfloat162float(__float2bfloat16_rn(out[j]));
+      const uint4 v = masked(pos[u], it & 7, __vcmpeq4(codes[u].x & 0x0f0f0f0fu, want[u]),
+                             __vcmpeq4(codes[u].y & 0x0f0f0f0fu, want[u]));
+      st_vec(dst + (it >> 3) * 64 + (it & 7) * 8, v);
     }
   }
   {

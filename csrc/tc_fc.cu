@@ -35,6 +35,7 @@ struct FcDgradArgs {
   int ctas_per_client;
   int m_valid;          // batch rows (<= 128)
   int n_valid;          // columns
+  float scale;          // applied to the fp32 accumulators before the bf16 rounding
   int* status;
 };
 
@@ -165,7 +166,7 @@ __global__ void __launch_bounds__(128 + 32 * kFcEpiWarps, 1)
           for (int p = 0; p < 8; ++p) {
             float v[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * p + e]);
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * p + e]) * args.scale;
             st_vec(my_stage + lane * 128 + ((p ^ (lane & 7)) * 16), pack<__nv_bfloat16>(v));
           }
           fence_proxy_async();
@@ -203,11 +204,11 @@ typedef struct {
   long long inner, rows, groups, row_stride, group_stride;
 } nfb_tc_operand_fc;
 
-// out[g][b, i] = sum_j dy[g][b, j] * w[g][j, i]; dy bf16 [G][B <= 128][128], w bf16 [G][128][I]
+// out[g][b, i] = scale * sum_j dy[g][b, j] * w[g][j, i]; dy bf16 [G][B <= 128][128], w bf16 [G][128][I]
 // (row stride I, free group stride), out bf16 [G][B][I] with row stride `out_rs` and group stride
 // `out_gs` (elements).  I must be a multiple of 64.
 int nfb_tc_fc_dgrad(const nfb_tc_operand_fc* dy, const nfb_tc_operand_fc* w, void* out,
-                    long long out_rs, long long out_gs, int* status, void* stream) {
+                    long long out_rs, long long out_gs, float scale, int* status, void* stream) {
   using namespace nfb;
   using namespace nfb::tc;
   NFB_REQUIRE(dy && w && out && status, NFB_EINVAL, "tc_fc_dgrad: null pointer");
@@ -235,6 +236,7 @@ int nfb_tc_fc_dgrad(const nfb_tc_operand_fc* dy, const nfb_tc_operand_fc* w, voi
   args.ctas_per_client = per_client;
   args.m_valid = static_cast<int>(dy->rows);
   args.n_valid = static_cast<int>(w->inner);
+  args.scale = scale;
   args.status = status;
   static bool attr_set = false;
   if (!attr_set) {

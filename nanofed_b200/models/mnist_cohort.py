@@ -191,7 +191,11 @@ class MnistCohortNet:
                                           self.seed + 7 * g0 + 3, self.dh.data_ptr(),
                                           stats.data_ptr(), st), "fc_head")
         # ---- backward ----
-        tc.linear_dgrad(self.fc1_w[g0:g1], self.dh, self.dp)
+        # the dropout scale 1/(1-p1) of the pooled activations is applied to dp in the dgrad
+        # epilogue (fp32, before the bf16 rounding); pool_bwd then only masks
+        pre = self.p1 > 0.0 and tc.fc_dgrad_is_persistent(128, b, 9216)
+        tc.linear_dgrad(self.fc1_w[g0:g1], self.dh, self.dp,
+                        scale=1.0 / (1.0 - self.p1) if pre else 1.0)
         if self.fuse_fc1_sgd:
             # 96% of the parameters are fc1.weight: its gradient is applied inside the GEMM
             # epilogue (after the data gradient above has read the old weights) and never
@@ -201,7 +205,8 @@ class MnistCohortNet:
         else:
             tc.linear_wgrad(self.dh, self.p, self.fc1_g[g0:g1], n)
         self._check(lib.nfb_mnist_pool_bwd(self.dp.data_ptr(), self.pidx.data_ptr(), c, b,
-                                           self.p1, self.da2.data_ptr(), grads.data_ptr(), n,
+                                           0.0 if pre else self.p1, self.da2.data_ptr(),
+                                           grads.data_ptr(), n,
                                            off["conv2.bias"], st), "pool_bwd")
         tc.conv3x3_wgrad_persistent(self.da2, self.a1, self.conv2_g[g0:g1], 26, n)
         if self.fuse_conv1_wgrad:

@@ -349,27 +349,35 @@ def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp:
     native._count()
 
 
-def linear_dgrad(w: torch.Tensor, dy: torch.Tensor, out: torch.Tensor) -> None:
-    """``out[c, b, i] = Σ_j dy[c, b, j]·w[c, j, i]`` (bf16)."""
+def fc_dgrad_is_persistent(j: int, batch: int, i: int) -> bool:
+    """True when ``linear_dgrad`` runs the persistent kernel (which can also scale its output)."""
+    return (j == 128 and batch <= 128 and i % 64 == 0
+            and os.environ.get("NFB_NO_PERSISTENT_FC") is None)
+
+
+def linear_dgrad(w: torch.Tensor, dy: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -> None:
+    """``out[c, b, i] = scale·Σ_j dy[c, b, j]·w[c, j, i]`` (bf16; ``scale`` only on the
+    persistent path, see ``fc_dgrad_is_persistent``)."""
     j, i = w.shape[1], w.shape[2]
-    if (j == 128 and dy.shape[1] <= 128 and i % 64 == 0 and out.stride(2) == 1
-            and os.environ.get("NFB_NO_PERSISTENT_FC") is None):
+    if fc_dgrad_is_persistent(j, dy.shape[1], i) and out.stride(2) == 1:
         # persistent form (tc_fc.cu): dy resident, weight tiles streamed, double-buffered TMEM
         lib = _lib()
         if not getattr(lib, "_fc_dgrad_declared", False):
             lib.nfb_tc_fc_dgrad.restype = C.c_int
             lib.nfb_tc_fc_dgrad.argtypes = [C.POINTER(_Operand), C.POINTER(_Operand), C.c_void_p,
-                                            C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p]
+                                            C.c_longlong, C.c_longlong, C.c_float, C.c_void_p,
+                                            C.c_void_p]
             lib._fc_dgrad_declared = True
         assert out.dtype == torch.bfloat16 and out.shape == (w.shape[0], dy.shape[1], i)
         oa, ob = _operand(dy), _operand(w)
         st = status_word(dy.device)
         code = lib.nfb_tc_fc_dgrad(C.byref(oa), C.byref(ob), out.data_ptr(), out.stride(1),
-                                   out.stride(0), st.data_ptr(),
+                                   out.stride(0), float(scale), st.data_ptr(),
                                    torch.cuda.current_stream(dy.device).cuda_stream)
         native._check(code, "tc_fc_dgrad")
         native._count()
         return
+    assert scale == 1.0, "output scaling needs the persistent fc dgrad kernel"
     if dy.shape[1] <= 128 and out.is_contiguous():
         # M = batch rows (zero-padded to 128 by TMA), N = i: row-major output, TMA-store epilogue
         gemm(FC_DGRAD_ROWS, dy, w, out, m=dy.shape[1], n=i,
