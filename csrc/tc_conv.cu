@@ -25,6 +25,10 @@
 #include "philox.cuh"
 #include "tc_common.cuh"
 
+#ifndef NFB_CONV_POOL_GROUPS
+#define NFB_CONV_POOL_GROUPS 4
+#endif
+
 namespace nfb {
 namespace tc {
 
@@ -85,7 +89,11 @@ __device__ __forceinline__ void bulk_wait_read0() {
 // Measured alternatives (B200, 32 clients x 64 images): 1 CTA/SM with 8 epilogue warps:
 // fwd 77 us / dgrad 109 us; 2 CTAs/SM with 4 epilogue warps each: 84 / 120 us.  Both kernels
 // move ~300-430 MB per launch (3.9 TB/s): they are DRAM-bound, not latency-bound.
-constexpr int kEpiWarps = 8;   // two epilogue warpgroups, alternating tiles / accumulators
+// Epilogue warpgroups (4 warps each = the four TMEM lane quarters); group j takes tiles
+// i = j (mod GROUPS) and owns accumulator j.  MODE 2's pooling epilogue is a latency chain
+// (two group barriers per tile): probes with loads / MMAs / stores disabled left its 118 us
+// unchanged, so it gets four groups; the other modes measured best with two.
+constexpr int kMaxEpiWarps = 16;
 
 // MODE 3 = MODE 1 (dgrad) whose epilogue also accumulates the conv1 weight/bias gradient
 template <int MODE>
@@ -93,6 +101,8 @@ constexpr bool kDgrad = (MODE == 1 || MODE == 3);
 
 template <int MODE>
 struct ConvCfg {
+  static constexpr int GROUPS = MODE == 2 ? NFB_CONV_POOL_GROUPS : 2;
+  static constexpr int EPI_WARPS = 4 * GROUPS;
   static constexpr int CH = !kDgrad<MODE> ? 32 : 64;   // A channels (K per tap)
   static constexpr int BN = !kDgrad<MODE> ? 64 : 32;   // output channels
   static constexpr int CHUNKS = CH / 8;
@@ -102,18 +112,21 @@ struct ConvCfg {
   static constexpr int W_BYTES = kTaps * W_TILE;
   // 128 or 64 (both powers of two); MODE 3 adds one [128 x 32] fp32 accumulator per epilogue
   // warp behind the two tile accumulators (64 + 8 * 32 = 320 -> 512)
-  static constexpr int TMEM_COLS = MODE == 3 ? 512 : 2 * BN;
-  static constexpr int STAGES = !kDgrad<MODE> ? 10 : 6;  // slab loads in flight per CTA
+  static constexpr int TMEM_COLS = MODE == 3 ? 512 : GROUPS * BN;
+  // slab loads in flight per CTA
+  static constexpr int STAGES = kDgrad<MODE> ? 6 : (GROUPS > 2 ? 8 : 10);
   static constexpr int OUT_ROW = BN * 2;               // bytes per output row (128 / 64)
   static constexpr int STAGING = 32 * OUT_ROW;         // per epilogue warp (4 KB / 2 KB)
   // MODE 2: per epilogue group a [128 x 64] bf16 tile (16 KB = the 4 warps' 4 KB areas) plus a
   // pooled [64 ch x 24] bf16 tile (3 KB)
-  static constexpr int POOL_STAGE = MODE == 2 ? 2 * 3072 : 0;
-  static constexpr size_t SMEM = W_BYTES + STAGES * SLAB_PAD + kEpiWarps * 4096 + POOL_STAGE + 1024 + 256;
+  static constexpr int POOL_STAGE = MODE == 2 ? GROUPS * 3072 : 0;
+  static constexpr size_t SMEM = W_BYTES + STAGES * SLAB_PAD + EPI_WARPS * 4096 + POOL_STAGE + 1024 + 256;
+  static_assert(SMEM <= 227 * 1024, "shared memory budget");
+  static_assert(TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "TMEM columns");
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
+__global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
     tc_conv_kernel(const __grid_constant__ CUtensorMap map_a,   // 4-D slab map
                    const __grid_constant__ CUtensorMap map_w,   // 3-D weight map (SW64)
                    const __grid_constant__ CUtensorMap map_o,   // 3-D output map, box [BN,32,1]
@@ -124,19 +137,19 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* w_smem = smem;                              // 9 x 4 KB, 1024-aligned
   uint8_t* slabs = smem + C::W_BYTES;
-  uint8_t* staging = slabs + C::STAGES * C::SLAB_PAD;   // kEpiWarps x 4 KB, 1024-aligned
-  uint8_t* pool_stage = staging + kEpiWarps * 4096;    // MODE 2: 2 x 3 KB
+  uint8_t* staging = slabs + C::STAGES * C::SLAB_PAD;   // EPI_WARPS x 4 KB, 1024-aligned
+  uint8_t* pool_stage = staging + C::EPI_WARPS * 4096;  // MODE 2: GROUPS x 3 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(pool_stage + C::POOL_STAGE);
   uint64_t* full_bar = bars;                           // [stages]
   uint64_t* empty_bar = bars + C::STAGES;            // [stages]
-  uint64_t* acc_full = bars + 2 * C::STAGES;         // [2]
-  uint64_t* acc_empty = acc_full + 2;                  // [2]
-  uint64_t* w_bar = acc_empty + 2;
+  uint64_t* acc_full = bars + 2 * C::STAGES;         // [GROUPS]
+  uint64_t* acc_empty = acc_full + C::GROUPS;          // [GROUPS]
+  uint64_t* w_bar = acc_empty + C::GROUPS;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
-  uint64_t* wg_bar = w_bar + 2;                        // MODE 3: [kEpiWarps]
+  uint64_t* wg_bar = w_bar + 2;                        // MODE 3: [EPI_WARPS]
 
   __shared__ float s_bias[64];
-  __shared__ int s_wg_valid[kEpiWarps];
+  __shared__ int s_wg_valid[kMaxEpiWarps];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = blockIdx.x / args.ctas_per_client;
   const int part = blockIdx.x % args.ctas_per_client;
@@ -153,10 +166,10 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
     prefetch_tmap(&map_w);
     prefetch_tmap(&map_o);
     for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+    for (int a = 0; a < C::GROUPS; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
     mbar_init(w_bar, 1);
     if (MODE == 3)
-      for (int w = 0; w < kEpiWarps; ++w) mbar_init(&wg_bar[w], 1);
+      for (int w = 0; w < C::EPI_WARPS; ++w) mbar_init(&wg_bar[w], 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
@@ -199,9 +212,9 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
       const uint32_t w_addr = smem_u32(w_smem);
       for (int i = 0; i < n_tiles && ok; ++i) {
         const int s = i % C::STAGES;
-        const int acc = i & 1;
+        const int acc = i % C::GROUPS;
         const uint32_t ph = (i / C::STAGES) & 1;
-        const uint32_t aph = (i >> 1) & 1;
+        const uint32_t aph = (i / C::GROUPS) & 1;
         if (!mbar_wait(&acc_empty[acc], aph ^ 1)) { *args.status = 1; ok = false; break; }
         if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
         tc_fence_after();
@@ -269,9 +282,9 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
       fetch_mask(first, mk_nx);
       if (MODE == 3) fetch_window(first, xw_nx);
     }
-    for (int i = grp; i < n_tiles && ok; i += 2) {
+    for (int i = grp; i < n_tiles && ok; i += C::GROUPS) {
       const int acc = grp;
-      const uint32_t aph = (i >> 1) & 1;
+      const uint32_t aph = (i / C::GROUPS) & 1;
       const int row0 = (tile_lo + i) * 128 + sub * 32;   // (MODE 0/1 tiling; MODE 2 indexes by image)
       const int m = row0 + lane;
       const bool row_ok = m < args.rows;
@@ -287,9 +300,9 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
           for (int t = 0; t < 16; ++t) xv[t] = (t < 9 && row_ok) ? xw_nx[t] : 0.f;
           if (row_ok) xv[9] = 1.f;
         }
-        if (i + 2 < n_tiles) {                       // this group's next tile
-          fetch_mask(m + 256, mk_nx);
-          if (MODE == 3) fetch_window(m + 256, xw_nx);
+        if (i + C::GROUPS < n_tiles) {               // this group's next tile
+          fetch_mask(m + 128 * C::GROUPS, mk_nx);
+          if (MODE == 3) fetch_window(m + 128 * C::GROUPS, xw_nx);
         }
       }
       if (!mbar_wait(&acc_full[acc], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }
@@ -338,7 +351,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
         uint4 rnd = make_uint4(~0u, ~0u, ~0u, ~0u);
         if (args.drop_p > 0.f)
           rnd = Philox::draw((step << 40) + (static_cast<unsigned long long>(blockIdx.x) << 20) +
-                                 static_cast<unsigned long long>(i) * 256 + (threadIdx.x - 128),
+                                 static_cast<unsigned long long>(i) * 128 + gt,
                              args.seed);
         const uint32_t thresh = static_cast<uint32_t>(args.drop_p * 256.f + 0.5f);
         const uint32_t rwords[3] = {rnd.x, rnd.y, rnd.z};
@@ -467,7 +480,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1)
       }
       if (lane == 0) s_wg_valid[warp - 4] = (ok && my_tiles > 0) ? 1 : 0;
       tc_fence_before();
-      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * C::EPI_WARPS) : "memory");
       tc_fence_after();
       if (sub == 0) {
         float sum[10];
@@ -770,7 +783,7 @@ static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, const CUten
       return fail(static_cast<int>(e), "tc_conv: smem attribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<ctas, 128 + 32 * kEpiWarps, C::SMEM, st>>>(ma, mw, mo, a);
+  kern<<<ctas, 128 + 32 * C::EPI_WARPS, C::SMEM, st>>>(ma, mw, mo, a);
   return launch_status("tc_conv");
 }
 
