@@ -1,4 +1,4 @@
-.PHONY: build test test-gpu bench sass clean
+.PHONY: build test test-gpu bench sass clean docs release lint
 build:
 	python -m nanofed_b200.build
 test:
@@ -11,3 +11,10 @@ sass:
 	python tools/dump_sass.py
 clean:
 	rm -rf build nanofed_b200/_native/*.so
+docs:
+	python -m sphinx -b html docs/source docs/_build/html
+lint:
+	python -m compileall -q nanofed_b200 tools tests bench.py
+release:
+	@test -n "$(VERSION)" || (echo "usage: make release VERSION=X.Y.Z"; exit 1)
+	scripts/release.sh $(VERSION)
