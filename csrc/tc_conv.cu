@@ -510,24 +510,24 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
 // -------------------------------------------------------------------------------------
 // Weight gradient, persistent form: one CTA per (client, contiguous range of 64-row
 // k-blocks).  For kernel row kh:   D_kh[(kw,ci), co] += sum_q x[q + kh*W + kw, ci] * dy[q, co]
-//   A (M = 96 -> 128): x, MN-major, 64-byte swizzle.  The three kw taps are three N... M atoms of
-//     32 channels: the SAME 116 rows loaded three times, shifted by kw rows (three TMA boxes of
-//     64-byte rows), so one descriptor covers kw = 0..2 and the kernel row is a start-address
-//     offset of kh*W rows.  (Shifting a swizzled tile by whole rows is legal because the
-//     hardware swizzle is a function of the absolute shared-memory address — verified on B200:
-//     a 128-B-swizzled slab read at start + s*128 B gives exact results with base_offset = 0.)
+//   A (M = 96 -> 128): x, MN-major, 64-byte swizzle, ONE tile of 120 rows per k-block.  The three
+//     kw taps are three 32-channel M atoms of the same tile whose start addresses differ by one
+//     row (descriptor LBO = 64 B), the kernel row is a start-address offset of kh*W rows.
+//     (Reading a swizzled tile at whole-row offsets is legal because the hardware swizzle is a
+//     function of the absolute shared-memory address — verified on B200: a 128-B-swizzled slab
+//     read at start + s*128 B gives exact results with base_offset = 0.)  The first version
+//     loaded the tile three times, shifted by kw (30 KB instead of 15.5 KB per k-block).
 //   B (N = 64): dy, MN-major, 128-byte swizzle, one atom.
 // 3 accumulators x 64 TMEM columns live for the CTA's whole k-range; 12 MMAs of 128x64x16 per
 // k-block.  History (B200, 32 clients x 64 images): generic kernel 256 us -> x as 16-byte-piece
 // interleaved slabs 166 us (TMA piece rate ~1.4/ns was the limit) -> this form.
 // Epilogue: fp32 atomics into the OIHW gradient inside the flat slab.
 // -------------------------------------------------------------------------------------
-constexpr int kWgRows = 64 + 52;                     // k-block rows + 2 kernel rows of halo
-constexpr int kWgStages = 4;
-constexpr int kWgGroup = 7680;                       // one kw group: 116 rows x 64 B, padded to 512
-constexpr int kWgA = 4 * kWgGroup;                   // 3 groups + 1 pad group (M 96 -> 128)
-constexpr int kWgB = 64 * 128;                       // dy tile [64 rows x 128 B]
-constexpr int kWgStage = kWgA + kWgB;                // 38912
+constexpr int kWgRows = 120;                         // 64 k-block rows + 52 (two kernel rows) + 3, to 8
+constexpr int kWgStages = 8;
+constexpr int kWgB = 64 * 128;                       // dy tile [64 rows x 128 B], first in a stage
+constexpr int kWgX = kWgRows * 64;                   // ONE x tile [120 rows x 64 B]
+constexpr int kWgStage = kWgB + 8192;                // 16 KB (x tile padded to keep 1 KB alignment)
 constexpr size_t kWgSmem = static_cast<size_t>(kWgStages) * kWgStage + 1024 + 256;
 
 struct WgradArgs {
@@ -560,13 +560,6 @@ __global__ void __launch_bounds__(256, 1)
   const int kb_hi = min(kb_lo + per, args.kblocks_per_client);
   const int n_kb = max(kb_hi - kb_lo, 0);
 
-  // the pad group (M rows 96..127) is never written by TMA: zero it once so the unused
-  // accumulator rows stay finite
-  for (int s = 0; s < kWgStages; ++s) {
-    uint4* z = reinterpret_cast<uint4*>(smem + s * kWgStage + 3 * kWgGroup);
-    for (int i = threadIdx.x; i < kWgGroup / 16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
-  }
-  fence_proxy_async();
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_dy);
     prefetch_tmap(&map_x);
@@ -589,11 +582,9 @@ __global__ void __launch_bounds__(256, 1)
         uint8_t* stage = smem + s * kWgStage;
         if ((args.debug & 1) && i >= kWgStages) { mbar_arrive(&full_bar[s]); continue; }
         const int q0 = (kb_lo + i) * 64;
-        mbar_expect_tx(&full_bar[s], kWgB + 3 * kWgRows * 64);
-        tma_load_3d(stage + kWgA, &map_dy, &full_bar[s], 0, q0, g);          // dy [64 co x 64 rows]
-#pragma unroll
-        for (int kw = 0; kw < 3; ++kw)                                       // x rows shifted by kw
-          tma_load_3d(stage + kw * kWgGroup, &map_x, &full_bar[s], 0, q0 + kw, g);
+        mbar_expect_tx(&full_bar[s], kWgB + kWgX);
+        tma_load_3d(stage, &map_dy, &full_bar[s], 0, q0, g);                 // dy [64 co x 64 rows]
+        tma_load_3d(stage + kWgB, &map_x, &full_bar[s], 0, q0, g);           // x  [32 ci x 120 rows]
       }
     }
   } else if (warp == 1) {
@@ -605,17 +596,19 @@ __global__ void __launch_bounds__(256, 1)
         const uint32_t ph = (i / kWgStages) & 1;
         if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + s * kWgStage);
-        const uint32_t b_addr = a_addr + kWgA;
+        const uint32_t b_addr = smem_u32(smem + s * kWgStage);
+        const uint32_t a_addr = b_addr + kWgB;
 #pragma unroll
         for (int kh = 0; kh < 3; ++kh) {
           if ((args.debug & 2) && kh > 0) break;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             if ((args.debug & 2) && kk > 0) break;
-            // A: MN-major SW64; M atoms (kw groups) kWgGroup apart, 8-k-row groups 512 B apart;
-            // kernel row kh and the K step are row offsets of 64 B
-            const uint64_t da = make_smem_desc(a_addr + (args.shift[kh] + kk * 16) * 64, kWgGroup,
+            // A: MN-major SW64, 8-k-row groups 512 B apart.  The four 32-channel M atoms are the
+            // SAME tile one row (64 B) apart: atom kw reads x shifted by kw positions, so one
+            // copy of x serves kw = 0..2 (atom 3 pads M to 128; its rows are never read back).
+            // Kernel row kh and the K step are row offsets as well.
+            const uint64_t da = make_smem_desc(a_addr + (args.shift[kh] + kk * 16) * 64, 64,
                                                8 * 64, 4);
             // B: MN-major SW128, single 64-wide atom; K step = 16 rows of 128 B
             const uint64_t db = make_smem_desc(b_addr + kk * (16 * 128), 64 * 128, 8 * 128, 2);
