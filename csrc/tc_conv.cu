@@ -61,7 +61,7 @@ struct ConvArgs {
   long long grad1_gs;
   long long w1_off, b1_off; // conv1.weight [32][9] / conv1.bias [32] inside a row
   int* status;
-  int debug;  // bottleneck probes (env NFB_CONV_DEBUG): 1 = reuse first slabs, 2 = no MMA, 4 = no stores
+  int debug;  // bottleneck probes (env NFB_CONV_DEBUG): 1 = reuse first slabs, 2 = one tap, 4 = no stores
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar,
@@ -509,18 +509,23 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
 
 // -------------------------------------------------------------------------------------
 // Weight gradient, persistent form: one CTA per (client, contiguous range of 64-row
-// k-blocks).  For kernel row kh:   D_kh[(kw,ci), co] += sum_q x[q + kh*W + kw, ci] * dy[q, co]
-//   A (M = 96 -> 128): x, MN-major, 64-byte swizzle, ONE tile of 120 rows per k-block.  The three
-//     kw taps are three 32-channel M atoms of the same tile whose start addresses differ by one
-//     row (descriptor LBO = 64 B), the kernel row is a start-address offset of kh*W rows.
-//     (Reading a swizzled tile at whole-row offsets is legal because the hardware swizzle is a
-//     function of the absolute shared-memory address — verified on B200: a 128-B-swizzled slab
-//     read at start + s*128 B gives exact results with base_offset = 0.)  The first version
-//     loaded the tile three times, shifted by kw (30 KB instead of 15.5 KB per k-block).
-//   B (N = 64): dy, MN-major, 128-byte swizzle, one atom.
-// 3 accumulators x 64 TMEM columns live for the CTA's whole k-range; 12 MMAs of 128x64x16 per
+// k-blocks).  For kernel row kh:   D_kh[co, (kw,ci)] += sum_q dy[q, co] * x[q + kh*W + kw, ci]
+//   A (M = 64 output channels): dy, MN-major, 128-byte swizzle, one 64-wide atom.
+//   B (N = 96 = kw x 32 input channels): x, MN-major, 64-byte swizzle, ONE tile of 120 rows per
+//     k-block.  The three kw taps are three 32-channel N atoms of the same tile whose start
+//     addresses differ by one row (descriptor LBO = 64 B); the kernel row is a start-address offset
+//     of kh*W rows.  (Reading a swizzled tile at whole-row offsets is legal because the hardware
+//     swizzle is a function of the absolute shared-memory address — verified on B200: a
+//     128-B-swizzled slab read at start + s*128 B gives exact results with base_offset = 0.)
+//   UMMA M = 64 puts accumulator row m in TMEM lane (m % 16) + 32 * (m / 16) (verified).
+// 3 accumulators x 96 TMEM columns live for the CTA's whole k-range; 12 MMAs of 64x96x16 per
 // k-block.  History (B200, 32 clients x 64 images): generic kernel 256 us -> x as 16-byte-piece
-// interleaved slabs 166 us (TMA piece rate ~1.4/ns was the limit) -> this form.
+// interleaved slabs 166 us (TMA piece rate ~1.4/ns was the limit) -> x loaded three times
+// (kw-shifted) as the M operand, M = 96 -> 128 with a zeroed pad atom: 91 us -> one x tile, atoms
+// one row apart: 91 us (loads were not the limit) -> roles swapped (M = 64): 87 us.
+// Probes (NFB_CONV_DEBUG): without loads 87 us, with 1 of 12 MMAs 57 us: the kernel is paced by the
+// MMAs at ~85 cycles each, for both operand arrangements — about (A bytes + B bytes) / 64 B per
+// cycle, i.e. the shared-memory operand fetch of small-N MMAs, not the tensor pipe (48 cycles).
 // Epilogue: fp32 atomics into the OIHW gradient inside the flat slab.
 // -------------------------------------------------------------------------------------
 constexpr int kWgRows = 120;                         // 64 k-block rows + 52 (two kernel rows) + 3, to 8
@@ -538,6 +543,7 @@ struct WgradArgs {
   long long grad_gs;
   int* status;
   int debug;               // probes (env NFB_CONV_DEBUG): 1 = reuse first stages, 2 = 1/12 MMAs
+  unsigned int x_off[12];  // descriptor address field of x for (kh, kk), 16-byte units (host)
 };
 
 __global__ void __launch_bounds__(256, 1)
@@ -567,7 +573,7 @@ __global__ void __launch_bounds__(256, 1)
     mbar_init(acc_bar, 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<256>(tmem_slot);
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -589,30 +595,34 @@ __global__ void __launch_bounds__(256, 1)
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1u, 1u);
+      constexpr uint32_t idesc = make_idesc_bf16(64, 96, 1u, 1u);
+      // Descriptor prototypes with a zero address field; per MMA only the address is added (the
+      // issuing thread is the critical path: 12 MMAs per 64 positions).
+      //   A (M = 64 output channels): dy, MN-major SW128, one 64-wide atom, 16 rows per K step.
+      //   B (N = 96 = kw x 32 input channels): x, MN-major SW64, 8-k-row groups 512 B apart.  The
+      //     three 32-channel N atoms are the SAME tile one row (64 B) apart (LBO = 64): atom kw
+      //     reads x shifted by kw positions, so one copy of x serves kw = 0..2.  Kernel row kh and
+      //     the K step are row offsets as well (x_off, computed on the host).
+      const uint64_t a_proto = make_smem_desc(0, 64 * 128, 8 * 128, 2);
+      const uint64_t b_proto = make_smem_desc(0, 64, 8 * 64, 4);
       bool ok = true;
       for (int i = 0; i < n_kb && ok; ++i) {
         const int s = i % kWgStages;
         const uint32_t ph = (i / kWgStages) & 1;
         if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
         tc_fence_after();
-        const uint32_t b_addr = smem_u32(smem + s * kWgStage);
-        const uint32_t a_addr = b_addr + kWgB;
+        const uint32_t st_lo = (smem_u32(smem + s * kWgStage) & 0x3FFFFu) >> 4;
+        if (args.debug & 2) {                          // probe: 1 of the 12 MMAs
+          umma_f16(tmem_base, a_proto | st_lo, b_proto | (st_lo + (kWgB >> 4) + args.x_off[0]),
+                   idesc, i > 0 ? 1u : 0u);
+        } else {
 #pragma unroll
-        for (int kh = 0; kh < 3; ++kh) {
-          if ((args.debug & 2) && kh > 0) break;
+          for (int kh = 0; kh < 3; ++kh) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            if ((args.debug & 2) && kk > 0) break;
-            // A: MN-major SW64, 8-k-row groups 512 B apart.  The four 32-channel M atoms are the
-            // SAME tile one row (64 B) apart: atom kw reads x shifted by kw positions, so one
-            // copy of x serves kw = 0..2 (atom 3 pads M to 128; its rows are never read back).
-            // Kernel row kh and the K step are row offsets as well.
-            const uint64_t da = make_smem_desc(a_addr + (args.shift[kh] + kk * 16) * 64, 64,
-                                               8 * 64, 4);
-            // B: MN-major SW128, single 64-wide atom; K step = 16 rows of 128 B
-            const uint64_t db = make_smem_desc(b_addr + kk * (16 * 128), 64 * 128, 8 * 128, 2);
-            umma_f16(tmem_base + kh * 64, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < 4; ++kk)
+              umma_f16(tmem_base + kh * 96, a_proto | (st_lo + kk * (16 * 128 / 16)),
+                       b_proto | (st_lo + (kWgB >> 4) + args.x_off[kh * 4 + kk]), idesc,
+                       (i > 0 || kk > 0) ? 1u : 0u);
           }
         }
         umma_commit(&empty_bar[s]);
@@ -625,31 +635,30 @@ __global__ void __launch_bounds__(256, 1)
     if (n_kb > 0) ok = mbar_wait(acc_bar, 0);
     if (!ok && lane == 0) *args.status = 1;
     tc_fence_after();
-    const int row = sub * 32 + lane;            // (kw, ci) = (row / 32, row % 32)
+    // UMMA M = 64 puts accumulator row m in TMEM lane (m % 16) + 32 * (m / 16): every warp owns
+    // 16 output channels in its lanes 0..15 (lanes 16..31 of each quarter are unused)
+    const int co = sub * 16 + (lane & 15);
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
-    float* gout = args.grad + static_cast<long long>(g) * args.grad_gs;
-    if (sub < 3) {  // rows 96..127 are padding
-      const int kw = sub, ci = lane;
+    float* gout = args.grad + static_cast<long long>(g) * args.grad_gs + co * 288;
 #pragma unroll 1
-      for (int kh = 0; kh < 3; ++kh) {
+    for (int kh = 0; kh < 3; ++kh) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < 96; c0 += 16) {          // column n = kw * 32 + ci
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(lane_addr + kh * 96 + c0, r);
+        tmem_ld_wait();
+        if (ok && n_kb > 0 && lane < 16) {
+          const int kw = c0 >> 5, ci0 = c0 & 31;
 #pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 16) {
-          uint32_t r[16];
-          tmem_ld_32x32b_x16(lane_addr + kh * 64 + c0, r);
-          tmem_ld_wait();
-          if (ok && n_kb > 0) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              atomicAdd(gout + (c0 + j) * 288 + ci * 9 + kh * 3 + kw, __uint_as_float(r[j]));
-          }
+          for (int j = 0; j < 16; ++j)
+            atomicAdd(gout + (ci0 + j) * 9 + kh * 3 + kw, __uint_as_float(r[j]));
         }
       }
     }
-    (void)row;
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<256>(tmem_base);
+  if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
 }  // namespace tc
@@ -956,6 +965,9 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
   if (per_client > a.kblocks_per_client) per_client = a.kblocks_per_client;
   a.ctas_per_client = per_client;
   for (int kh = 0; kh < 3; ++kh) a.shift[kh] = kh * width;
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kk = 0; kk < 4; ++kk)       // rows of 64 B = 4 descriptor units each
+      a.x_off[kh * 4 + kk] = static_cast<unsigned>((kh * width + kk * 16) * 4);
   a.grad = grad;
   a.grad_gs = grad_group_stride;
   a.status = status;
