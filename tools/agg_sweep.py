@@ -21,6 +21,7 @@ ap.add_argument("--params", type=int, nargs="+", default=[1_199_936, 350_000_000
 ap.add_argument("--clients-per-gpu", type=int, default=8)
 ap.add_argument("--iters", type=int, default=5)
 ap.add_argument("--nvls", action="store_true")
+ap.add_argument("--both", action="store_true", help="time the P2P and the NVLS path in one run")
 args = ap.parse_args()
 info = rdist.init()
 dev = info.device
@@ -64,21 +65,25 @@ for n in args.params:
     nccl = NcclReducer(arena, info)
     t_nccl = timed(lambda: nccl.reduce(arena), args.iters)
     ref = arena.master.clone()
-    peer = PeerReducer(arena, info, use_multicast=args.nvls)
-    t_peer = timed(lambda: peer.reduce(arena), args.iters)
-    peer.check()
-    err = (arena.master - ref).abs().max().item()
     t_hbm = k * n * 4 / hbm
     t_link = 2 * 4 * n * (G - 1) / G / link
     roof = max(t_hbm, t_link)
-    if info.is_main:
-        print(json.dumps({"n_gpus": G, "params": n, "clients_per_gpu": k, "clients": k * G,
-                          "fused_ms": round(t_peer, 4), "nccl_baseline_ms": round(t_nccl, 4),
-                          "speedup_vs_nccl": round(t_nccl / t_peer, 3), "path": peer.path,
-                          "roofline_ms": round(roof * 1e3, 4),
-                          "bound": "hbm" if t_hbm >= t_link else "nvlink",
-                          "fraction_of_roofline": round(roof * 1e3 / t_peer, 3),
-                          "max_abs_diff_vs_nccl": err}), flush=True)
-    del arena, nccl, peer, ref
+    for nvls in ([False, True] if args.both else [args.nvls]):
+        peer = PeerReducer(arena, info, use_multicast=nvls)
+        t_peer = timed(lambda: peer.reduce(arena), args.iters)
+        peer.check()
+        err = (arena.master - ref).abs().max().item()
+        if info.is_main:
+            print(json.dumps({"n_gpus": G, "params": n, "clients_per_gpu": k, "clients": k * G,
+                              "fused_ms": round(t_peer, 4), "nccl_baseline_ms": round(t_nccl, 4),
+                              "speedup_vs_nccl": round(t_nccl / t_peer, 3), "path": peer.path,
+                              "roofline_ms": round(roof * 1e3, 4),
+                              "bound": "hbm" if t_hbm >= t_link else "nvlink",
+                              "fraction_of_roofline": round(roof * 1e3 / t_peer, 3),
+                              "nccl_fraction_of_roofline": round(roof * 1e3 / t_nccl, 3),
+                              "max_abs_diff_vs_nccl": err}), flush=True)
+        del peer
+        torch.cuda.empty_cache()
+    del arena, nccl, ref
     torch.cuda.empty_cache()
 rdist.shutdown()
