@@ -199,15 +199,10 @@ __global__ void __launch_bounds__(128 + 32 * kFcEpiWarps, 1)
 
 extern "C" {
 
-typedef struct {
-  const void* ptr;
-  long long inner, rows, groups, row_stride, group_stride;
-} nfb_tc_operand_fc;
-
 // out[g][b, i] = scale * sum_j dy[g][b, j] * w[g][j, i]; dy bf16 [G][B <= 128][128], w bf16 [G][128][I]
 // (row stride I, free group stride), out bf16 [G][B][I] with row stride `out_rs` and group stride
 // `out_gs` (elements).  I must be a multiple of 64.
-int nfb_tc_fc_dgrad(const nfb_tc_operand_fc* dy, const nfb_tc_operand_fc* w, void* out,
+int nfb_tc_fc_dgrad(const nfb_tc_operand* dy, const nfb_tc_operand* w, void* out,
                     long long out_rs, long long out_gs, float scale, int* status, void* stream) {
   using namespace nfb;
   using namespace nfb::tc;

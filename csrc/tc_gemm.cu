@@ -590,21 +590,7 @@ static int launch(const Operand& a, const Operand& b, int m_tiles, int n_tiles, 
 
 extern "C" {
 
-typedef struct {
-  const void* ptr;
-  long long inner, rows, groups, row_stride, group_stride;
-} nfb_tc_operand;
-
-typedef struct {
-  void* out;
-  int out_bf16, atomic;
-  long long out_gs, out_ms, out_ns, out_ts;
-  const float* bias;
-  long long bias_gs;
-  int bias_on_m, relu;
-  const void* mask_src;
-  int m_valid, n_valid;
-} nfb_tc_epilogue;
+// nfb_tc_operand / nfb_tc_epilogue: include/nanofed_b200.h
 
 // variant: 0 conv_fwd, 1 conv_dgrad, 2 conv_wgrad, 3 fc_fwd, 4 fc_dgrad, 5 fc_wgrad,
 //          6 fc_dgrad with M = batch (row-major bf16 output, TMA-store epilogue)

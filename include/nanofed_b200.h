@@ -165,6 +165,125 @@ int nfb_linear_psgn(const void* act, int act_dtype, const void* dout, int dout_d
                     int64_t B, int64_t in_features, int64_t out_features, int bias,
                     float* out, void* stream);
 
+/* ---- K-AGG + K-BCAST across GPUs (csrc/fedavg_allreduce.cu) -------------------------------
+ * ONE cooperative kernel per rank: local weighted reduce of this GPU's K client rows, chunk by
+ * chunk; reduce-scatter of each chunk over peer memory (P2P loads, or multimem.ld_reduce when the
+ * mc_* pointers are given); FedAvg epilogue (1/sum n, DP clip factors, folded Philox noise, bf16
+ * cast); all-gather by stores into every rank's model buffers (P2P or multimem.st).
+ * views_dev: device array of G rows of 10 int64 pointers
+ *   {slots, counts, mask, sumsq, partial, scal, flags, master, lowp, counters}
+ * (entries of other ranks are peer-mapped addresses of their symmetric buffers; slots / counts /
+ * mask / sumsq / counters only for my_rank).  ranks_in_grid = G runs all ranks in one launch on
+ * one GPU (test emulation, blockIdx.y = rank).  epoch must increase by one per call; producers =
+ * CTAs that reduce local clients (the rest consume), chunk_elems = pipeline granule (multiple of
+ * 4), grid_blocks <= nfb_allreduce_max_blocks().  Waits are bounded by spin_limit_ns and set
+ * *status instead of hanging.  Replaces nanofed/server/aggregator/fedavg.py:53-63 +
+ * communication/http upload/download (client.py:174-195, server.py:191-208).              */
+int nfb_allreduce_max_blocks(int x_dtype, int64_t K);
+int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, int ranks_in_grid,
+                         int x_dtype, int64_t K, int64_t N, int64_t row_stride, float clip_norm,
+                         float noise_std, const uint8_t* noise_mask, uint64_t seed,
+                         uint64_t offset, uint32_t epoch, int producers, int64_t chunk_elems,
+                         int grid_blocks, const float* mc_partial, float* mc_master,
+                         void* mc_lowp, int* status, uint64_t spin_limit_ns, void* stream);
+
+/* ---- K-GEMM / K-CONV: tcgen05 kernels (csrc/tc_gemm.cu, tc_fc.cu, tc_conv.cu, tc_conv1.cu) ---
+ * Operands are bf16 [groups][rows][inner] views with unit inner stride (group = client); every
+ * function launches ONE kernel for all groups.  `status` is a device int set to 1 if a bounded
+ * pipeline wait expires.  Together they replace nn.Conv2d / nn.Linear forward and autograd
+ * backward of nanofed/models/mnist.py:9-14,17-27 as run by trainer/base.py:145-150.        */
+typedef struct {
+  const void* ptr;
+  long long inner, rows, groups, row_stride, group_stride; /* elements */
+} nfb_tc_operand;
+typedef struct {
+  void* out;
+  int out_bf16, atomic;
+  long long out_gs, out_ms, out_ns, out_ts; /* element strides: group, m, n, tap */
+  const float* bias;
+  long long bias_gs;
+  int bias_on_m, relu;
+  const void* mask_src; /* bf16, same indexing as out: out = 0 where mask <= 0 */
+  int m_valid, n_valid;
+} nfb_tc_epilogue;
+/* D_t[g][m,n] = sum_k A[g][m + a_mn(t), k + a_k(t)] * B[g][n + b_mn(t), k + b_k(t)].
+ * variant: 0 conv_fwd, 1 conv_dgrad, 2 conv_wgrad (9 accumulators), 3 fc_fwd, 4 fc_dgrad,
+ * 5 fc_wgrad, 6 fc_dgrad with M = batch.  tap_table: taps x {a_k, a_mn, b_k, b_mn}.          */
+int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, int m_tiles,
+                int n_tiles, int groups, int taps, int inner, int k_split, const int* tap_table,
+                const nfb_tc_epilogue* epi, int* status, void* stream);
+/* w[g][j][i] -= lr * (sum_b dy[g][b][j] * x[g][b][i] + wd * w), w_lowp = bf16(w): the weight
+ * gradient is applied in the GEMM epilogue and never written.                              */
+int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* dy, const nfb_tc_operand* x, int groups, int j,
+                            int i, int inner, float* w, long long w_gs, void* w_lowp,
+                            long long lowp_gs, float lr, float weight_decay, int* status,
+                            void* stream);
+/* out[g][b,i] = scale * sum_j dy[g][b,j] * w[g][j,i]  (persistent; j = 128, b <= 128).      */
+int nfb_tc_fc_dgrad(const nfb_tc_operand* dy, const nfb_tc_operand* w, void* out, long long out_rs,
+                    long long out_gs, float scale, int* status, void* stream);
+/* 3x3 convolutions on the row-flattened NHWC grid (activation = [clients][B*W*W rows][ch], tap
+ * (kh,kw) = row shift kh*W + kw); persistent kernels of csrc/tc_conv.cu.  w = bf16 [C][64][288]
+ * (tap-major, channel-minor; see nfb_mnist_prep_conv2).
+ * mode 0: out[q,co] = relu(sum x[q+s_t, ci] w[co, t*32+ci] + bias[co])          (32 -> 64 ch)
+ * mode 1: out[q,ci] = (sum dy[q-s_t, co] w[co, t*32+ci]) * (mask[q,ci] > 0)     (64 -> 32 ch) */
+int nfb_tc_conv3x3(int mode, const void* a, long long rows, long long a_group_stride,
+                   const void* w, long long w_group_stride, int clients, int width, void* out,
+                   long long out_group_stride, const float* bias, long long bias_group_stride,
+                   const void* mask, int* status, void* stream);
+/* mode 0's convolution with bias + ReLU + 2x2 max-pool + dropout in the epilogue: writes only
+ * pool_out [C][B][64*12*12] (PyTorch flatten order) and one code byte per pooled element
+ * (bits 0-1 argmax slot, bit 2 ReLU passed, bit 3 kept by dropout); width must be 26.        */
+int nfb_tc_conv3x3_pool_fwd(const void* x, long long rows, long long x_group_stride, const void* w,
+                            long long w_group_stride, int clients, int images, int width,
+                            const float* bias, long long bias_group_stride, void* pool_out,
+                            uint8_t* pool_idx, float drop_p, const void* rng_state,
+                            unsigned long long seed, int* status, void* stream);
+/* grad[c][co][ci][kh][kw] += sum_q dy[c,q,co] * x[c, q + kh*W + kw, ci]   (fp32 atomics).     */
+int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long rows, long long dy_group_stride,
+                         long long x_group_stride, int clients, int width, float* grad,
+                         long long grad_group_stride, int* status, void* stream);
+/* mode 1 fused with the weight/bias gradient of the 1 -> 32 convolution in front of it: the
+ * masked data gradient feeds a second MMA against the 3x3 windows of the layer-1 input x1
+ * (fp32 [C][B][(W+2)^2]) and is never stored.  grad1[c][w1_off + ci*9 + t], grad1[c][b1_off + ci]
+ * are accumulated with atomics.                                                             */
+int nfb_tc_conv3x3_dgrad_wgrad1(const void* dy, long long rows, long long dy_group_stride,
+                                const void* w, long long w_group_stride, int clients, int width,
+                                const void* mask, long long mask_group_stride, const float* x1,
+                                long long x1_group_stride, float* grad1,
+                                long long grad1_group_stride, long long w1_off, long long b1_off,
+                                int* status, void* stream);
+/* a1[c][q][ch] = relu(conv1(x)[q][ch] + bias[ch]), 1 -> 32 channels, one tcgen05.mma pair per
+ * 128 positions with bf16 hi/lo split operands; weights/bias read from the fp32 parameter rows. */
+int nfb_tc_conv1_fwd(const float* x, long long x_group_stride, const float* slots,
+                     long long slot_group_stride, long long w_off, long long b_off, int clients,
+                     int images, int width, void* a1, long long a1_group_stride, int* status,
+                     void* stream);
+
+/* ---- K-ELT / K-XENT pieces of the MNIST CNN cohort engine (csrc/mnist_ops.cu) ----------------
+ * slots / grads are the [C][row_stride] fp32 parameter and gradient rows of the arena; *_off are
+ * element offsets of a state_dict entry inside a row (runtime/flat.py).                     */
+int nfb_mnist_prep_conv2(const float* slots, int64_t row_stride, int64_t w_off, int C, void* w2p,
+                         void* stream);  /* OIHW fp32 -> [C][64][tap*32+ci] bf16 */
+int nfb_mnist_conv1_fwd(const float* x, int64_t x_cstride, const float* slots, int64_t row_stride,
+                        int64_t w_off, int64_t b_off, int C, int B, void* a1, void* stream);
+int nfb_mnist_pool_fwd(const void* a2, int C, int B, float drop_p, const void* rng_state,
+                       uint64_t seed, void* p, uint8_t* pidx, void* stream);
+/* dp [C][B][9216] + code bytes -> da2 [C][B*676][64] (zero outside the 24x24 window) and the
+ * conv2 bias gradient; drop_p = 0 when the producer of dp already applied 1/(1-p).           */
+int nfb_mnist_pool_bwd(const void* dp, const uint8_t* pidx, int C, int B, float drop_p, void* da2,
+                       float* grads, int64_t row_stride, int64_t b2_off, void* stream);
+/* fc1 bias + ReLU + dropout, fc2, log-softmax/NLL/accuracy into stats[c][0..2], dlogits, fc2 and
+ * fc1-bias gradients (fp32 atomics when the batch is split over row blocks: targets must be
+ * zero), dh = gradient w.r.t. the fc1 pre-activation (bf16).  hpre is consumed and left zeroed.
+ * rng_state: 2 x uint64 {dropout step, block arrival counter}.                              */
+int nfb_mnist_fc_head(float* hpre, const int64_t* labels, int64_t label_stride, int C, int B,
+                      const float* slots, float* grads, int64_t row_stride, int64_t b1_off,
+                      int64_t w2_off, int64_t b2_off, float drop_p, void* rng_state,
+                      int advance_rng, uint64_t seed, void* dh, float* stats, void* stream);
+int nfb_mnist_conv1_wgrad(const void* da1, const float* x, int64_t x_cstride, int C, int B,
+                          float* grads, int64_t row_stride, int64_t w_off, int64_t b_off,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif
