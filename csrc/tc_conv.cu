@@ -118,8 +118,9 @@ struct ConvCfg {
   static constexpr int OUT_ROW = BN * 2;               // bytes per output row (128 / 64)
   static constexpr int STAGING = 32 * OUT_ROW;         // per epilogue warp (4 KB / 2 KB)
   // MODE 2: per epilogue group a [128 x 64] bf16 tile (16 KB = the 4 warps' 4 KB areas) plus a
-  // pooled [64 ch x 24] bf16 tile (3 KB)
-  static constexpr int POOL_STAGE = MODE == 2 ? GROUPS * 3072 : 0;
+  // pooled [24 positions x 64 ch] bf16 tile (rows of 136 B)
+  static constexpr int POOL_TILE = 3328;               // 24 pooled positions x 136 B, padded
+  static constexpr int POOL_STAGE = MODE == 2 ? GROUPS * POOL_TILE : 0;
   static constexpr size_t SMEM = W_BYTES + STAGES * SLAB_PAD + EPI_WARPS * 4096 + POOL_STAGE + 1024 + 256;
   static_assert(SMEM <= 227 * 1024, "shared memory budget");
   static_assert(TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "TMEM columns");
@@ -326,7 +327,10 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
         //     No barrier is needed before overwriting it: its last readers (phase 2 of this
         //     group's previous tile) are ordered before that tile's second barrier.
         uint8_t* tile_s = staging + grp * (4 * 4096);
-        __nv_bfloat16* pooled = reinterpret_cast<__nv_bfloat16*>(pool_stage + grp * 3072);
+        // pooled tile: [24 positions][64 ch] bf16, rows of 68 elements.  (The first layout,
+        // [ch][24] with one two-byte store per element, made every store an 8-way bank conflict:
+        // 4.1 M of the kernel's 4.7 M excess shared-memory wavefronts in ncu.)
+        __nv_bfloat16* pooled = reinterpret_cast<__nv_bfloat16*>(pool_stage + grp * C::POOL_TILE);
         const int gt = threadIdx.x - 128 - grp * 128;           // 0..127 within the group
         const int trow = sub * 32 + lane;
 #pragma unroll
@@ -372,6 +376,7 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
           }
           const int pos = (prow0 + prow) * 12 + pcol;
           uint32_t codes = 0;
+          float pv[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             float m = v[0][j];
@@ -382,7 +387,16 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
             m = fmaxf(m + s_bias[quad * 4 + j], 0.f);
             const bool keep = ((rwords[rep] >> (8 * j)) & 0xffu) >= thresh;
             codes |= (a | (m > 0.f ? 4u : 0u) | (keep ? 8u : 0u)) << (8 * j);
-            pooled[(quad * 4 + j) * 24 + pp] = __float2bfloat16_rn(keep ? m * keep_scale : 0.f);
+            pv[j] = keep ? m * keep_scale : 0.f;
+          }
+          {
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(pv[0], pv[1]);
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(pv[2], pv[3]);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(smem_u32(pooled + pp * 68 + quad * 4)),
+                         "r"(pk.x), "r"(pk.y) : "memory");
           }
           *reinterpret_cast<uint32_t*>(args.pool_idx + (img * 144 + pos) * 64 + quad * 4) = codes;
         }
@@ -390,10 +404,17 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
         // (3) write the pooled tile: per channel 24 consecutive bf16 (48 B) in flatten order
         {
           const int ch = gt >> 1, half = gt & 1;               // 64 channels x 2 halves of 12
-          const uint2* src = reinterpret_cast<const uint2*>(pooled + ch * 24 + half * 12);
+          const uint32_t src = smem_u32(pooled + half * 12 * 68 + ch);
+          uint32_t w[6];
+#pragma unroll
+          for (int k = 0; k < 6; ++k) {                        // two positions per 32-bit word
+            uint16_t a, b;
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(a) : "r"(src + (2 * k) * 136));
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(b) : "r"(src + (2 * k + 1) * 136));
+            w[k] = static_cast<uint32_t>(a) | (static_cast<uint32_t>(b) << 16);
+          }
           uint2* dst = reinterpret_cast<uint2*>(args.pool_out + img * 9216 + ch * 144 + prow0 * 12 + half * 12);
-          const uint2 a0 = src[0], a1 = src[1], a2 = src[2];
-          dst[0] = a0; dst[1] = a1; dst[2] = a2;
+          dst[0] = make_uint2(w[0], w[1]); dst[1] = make_uint2(w[2], w[3]); dst[2] = make_uint2(w[4], w[5]);
         }
         // `pooled` is rewritten only after the next tile's first barrier, i.e. after every
         // thread of the group has finished the reads above.
