@@ -262,7 +262,10 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
       if (mask && row < args.rows) {
 #pragma unroll
         for (int j = 0; j < C::BN / 8; ++j)
-          dst[j] = ld_stream(mask + static_cast<long long>(row) * C::BN + 8 * j);
+          // L1-allocating loads: a thread reads its own 64-byte row in four 16-byte pieces, so each
+          // 32-byte sector is touched by two instructions; with L1::no_allocate ncu counted twice
+          // the ideal number of L2 sectors for the mask
+          dst[j] = __ldg(reinterpret_cast<const uint4*>(mask + static_cast<long long>(row) * C::BN + 8 * j));
       }
     };
     auto fetch_window = [&](int row, float* dst) {
@@ -459,8 +462,9 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
           //   dW1[ch, t] += sum_q da1[q, ch] * x[q + s_t],   t = 9 is the bias column (x = 1)
           // The staged rows ARE an MN-major 64-byte-swizzled operand (K = 32 positions, M = 32
           // channels); the windows are written next to them in the same layout (N = 32, columns
-          // 0..9 used).  UMMA M is 128: the three extra 32-channel atoms alias bytes inside this
-          // warp's 4 KB area (LBO 512) and only produce accumulator lanes 32..127, never read.
+          // 0..9 used).  UMMA M is 64 (half the operand fetch of M = 128): the second 32-channel
+          // atom aliases bytes inside this warp's 4 KB area (LBO 512) and only produces accumulator
+          // rows 32..63, never read.  M = 64 puts row m in TMEM lane (m % 16) + 32 * (m / 16).
           uint8_t* xs = my_stage + 2048;
           st_vec(xs + lane * 64 + ((0 ^ ((lane >> 1) & 3)) * 16), pack<__nv_bfloat16>(xv));
           st_vec(xs + lane * 64 + ((1 ^ ((lane >> 1) & 3)) * 16), pack<__nv_bfloat16>(xv + 8));
@@ -468,7 +472,7 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
           __syncwarp();
           if (lane == 0) {
             tc_fence_after();
-            constexpr uint32_t idesc_w = make_idesc_bf16(128, 32, 1u, 1u);
+            constexpr uint32_t idesc_w = make_idesc_bf16(64, 32, 1u, 1u);
             const uint32_t a0 = smem_u32(my_stage), b0 = smem_u32(xs);
             const uint32_t d_w = tmem_base + 2 * C::BN + (warp - 4) * 32;
 #pragma unroll
@@ -493,8 +497,8 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
     }
     if (lane == 0) bulk_wait_read0();
     if (MODE == 3) {
-      // every warp's accumulator is complete; warps 4 and 8 (TMEM lanes 0..31 = channels) add up
-      // their group's four accumulators and flush 32 x 10 values with atomics
+      // every warp's accumulator is complete; in each group the warps of TMEM quarters 0 and 1 add
+      // up the group's four accumulators (16 channels each) and flush 32 x 10 values with atomics
       if (my_tiles > 0 && ok && !mbar_wait(&wg_bar[warp - 4], (my_tiles - 1) & 1)) {
         if (lane == 0) *args.status = 1;
         ok = false;
@@ -503,22 +507,25 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
       tc_fence_before();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * C::EPI_WARPS) : "memory");
       tc_fence_after();
-      if (sub == 0) {
+      if (sub < 2) {                                   // channels 16*sub + lane, lanes 0..15
         float sum[10];
 #pragma unroll
         for (int t = 0; t < 10; ++t) sum[t] = 0.f;
         for (int w = grp * 4; w < grp * 4 + 4; ++w) {
           if (!s_wg_valid[w]) continue;                 // warp-uniform
           uint32_t rr[16];
-          tmem_ld_32x32b_x16(tmem_base + 2 * C::BN + w * 32, rr);
+          tmem_ld_32x32b_x16(lane_addr + 2 * C::BN + w * 32, rr);
           tmem_ld_wait();
 #pragma unroll
           for (int t = 0; t < 10; ++t) sum[t] += __uint_as_float(rr[t]);
         }
         float* gd = args.grad1 + static_cast<long long>(g) * args.grad1_gs;
+        if (lane < 16) {
+          const int ch = sub * 16 + lane;
 #pragma unroll
-        for (int t = 0; t < 9; ++t) atomicAdd(gd + args.w1_off + lane * 9 + t, sum[t]);
-        atomicAdd(gd + args.b1_off + lane, sum[9]);
+          for (int t = 0; t < 9; ++t) atomicAdd(gd + args.w1_off + ch * 9 + t, sum[t]);
+          atomicAdd(gd + args.b1_off + ch, sum[9]);
+        }
       }
     }
   }
