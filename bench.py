@@ -154,13 +154,15 @@ def run_ours(args: argparse.Namespace) -> None:
     warmup = max(args.warmup, 3)
     steps = max(args.steps, 1)
 
-    def timed(fn, n: int) -> float:
+    def timed(fn, n: int, finish=None) -> float:
         rdist.barrier()
         torch.cuda.synchronize(dev)
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for _ in range(n):
             fn()
+        if finish is not None:
+            finish()
         b.record()
         torch.cuda.synchronize(dev)
         rdist.barrier()
@@ -198,14 +200,28 @@ def run_ours(args: argparse.Namespace) -> None:
         # Every round inside the timed region (a) issues the H2D copy of one round's inputs from
         # pinned host memory (it is the NEXT round's data, so PCIe overlaps this round's
         # training), (b) adopts the previously staged inputs, (c) trains + aggregates, and
-        # (d) reads the round's metrics back to the host (stream sync).
+        # (d) copies the round's metrics to pinned host memory and reads them (event sync).
+        # The metrics of round r are read after round r+1 has been submitted (two pinned metric
+        # buffers), so the GPU does not idle while the host turns counters into Python floats;
+        # the last round is collected inside the timed region too: K submits, K D2H reads.
+        pending = {"h": None}
+
         def e2e_round():
-            last["o"] = sim.run_round(use_staged=True, prefetch_next=(host_images, host_labels))
+            h = sim.submit_round(use_staged=True, prefetch_next=(host_images, host_labels))
+            if pending["h"] is not None:
+                last["o"] = sim.collect(pending["h"])
+            pending["h"] = h
+
+        def drain():
+            if pending["h"] is not None:
+                last["o"] = sim.collect(pending["h"])
+                pending["h"] = None
 
         sim.prefetch_inputs(host_images, host_labels)
         for _ in range(warmup):
             e2e_round()
-        e2e_ms = timed(e2e_round, steps) / steps
+        drain()
+        e2e_ms = timed(e2e_round, steps, finish=drain) / steps
         e2e = {"value": samples_per_round / (e2e_ms / 1e3), "unit": "client_samples/s",
                "ms_per_step": e2e_ms, "rounds_per_sec": 1e3 / e2e_ms,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -91,6 +91,15 @@ class RoundOutcome:
     phase_ms: dict[str, float] = field(default_factory=dict)
 
 
+@dataclass
+class PendingRound:
+    """Handle of a round whose metrics are still on their way to the host (``submit_round``)."""
+
+    round_id: int
+    slot: int
+    event: Any
+
+
 def build_model(name: str) -> nn.Module:
     from nanofed_b200.models import MNISTModel, ResNet18
 
@@ -378,7 +387,11 @@ class FedSimulation:
         self.accountant = GaussianAccountant(cfg.privacy) if cfg.privacy else None
         self._noise_offset = 0
         self._round = 0
-        self._stats_host = torch.zeros(c, 3, pin_memory=self.device.type == "cuda")
+        # two pinned metric buffers: round r+1 may be submitted before round r is collected
+        self._stats_ring = [torch.zeros(c, 3, pin_memory=self.device.type == "cuda")
+                            for _ in range(2)]
+        self._stats_host = self._stats_ring[0]
+        self._pending: list[PendingRound | None] = [None, None]
         self.coordinator = None
 
     # -- properties ------------------------------------------------------------
@@ -489,18 +502,50 @@ class FedSimulation:
         ``prefetch_next``: start the H2D copy of the following round's inputs, overlapped
         with this round's training.
         """
+        return self.collect(self.submit_round(host_inputs, use_staged, prefetch_next))
+
+    def submit_round(
+        self,
+        host_inputs: tuple[torch.Tensor, torch.Tensor] | None = None,
+        use_staged: bool = False,
+        prefetch_next: tuple[torch.Tensor, torch.Tensor] | None = None,
+    ) -> "PendingRound":
+        """Enqueue one round and the device→host copy of its metrics, without waiting.
+
+        ``collect(handle)`` waits for that copy and returns the ``RoundOutcome``.  Submitting
+        round r+1 before collecting round r keeps the GPU busy while the host digests metrics
+        (two pinned metric buffers alternate, so at most two rounds may be outstanding).
+        """
         if host_inputs is not None:
             self.stage_inputs(*host_inputs)
         elif use_staged and getattr(self, "_has_staged", False):
             self._adopt_staged()
         if prefetch_next is not None:
             self.prefetch_inputs(*prefetch_next)
+        slot = self._round % 2
+        if self._pending[slot] is not None:
+            raise RuntimeError("collect() the round submitted two rounds ago before submitting "
+                               "another one (two metric buffers)")
         self.enqueue_round()
         # the round's only device→host transfer: per-client (loss_sum, correct, samples)
-        self._stats_host.copy_(self.arena.stats, non_blocking=True)
+        self._stats_ring[slot].copy_(self.arena.stats, non_blocking=True)
+        event = None
         if self.device.type == "cuda":
-            torch.cuda.current_stream(self.device).synchronize()
-        outcome = self._summarise(self._round)
+            event = torch.cuda.Event()
+            event.record(torch.cuda.current_stream(self.device))
+        handle = PendingRound(self._round, slot, event)
+        self._pending[slot] = handle
+        self._round += 1
+        return handle
+
+    def collect(self, handle: "PendingRound") -> RoundOutcome:
+        """Wait for a submitted round's metrics and return them as Python floats."""
+        if self._pending[handle.slot] is not handle:
+            raise RuntimeError("round was already collected")
+        if handle.event is not None:
+            handle.event.synchronize()
+        self._pending[handle.slot] = None
+        outcome = self._summarise(handle.round_id, self._stats_ring[handle.slot])
         if self.accountant is not None:
             for _ in range(self.num_clients):
                 self.accountant.add_noise_event(self.cfg.privacy.noise_multiplier,
@@ -508,11 +553,10 @@ class FedSimulation:
             spent = self.accountant.get_privacy_spent()
             outcome.agg_metrics["privacy_epsilon"] = spent.epsilon_spent
             outcome.agg_metrics["privacy_delta"] = spent.delta_spent
-        self._round += 1
         return outcome
 
-    def _summarise(self, round_id: int) -> RoundOutcome:
-        stats = self._stats_host
+    def _summarise(self, round_id: int, stats: torch.Tensor | None = None) -> RoundOutcome:
+        stats = self._stats_host if stats is None else stats
         counts = self._counts_host
         total = sum(counts)
         base = self.rank.rank * self.cfg.clients_per_gpu

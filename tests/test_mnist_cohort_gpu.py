@@ -153,3 +153,29 @@ def test_prefetched_inputs_match_direct_staging():
 
     a, b = run(False), run(True)
     torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-4)
+
+
+def test_rounds_submitted_ahead_of_their_metrics_match_sequential_rounds():
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    def make():
+        return FedSimulation(CohortConfig(clients_per_gpu=2, samples_per_client=64, batch_size=32,
+                                          engine="grouped", seed=5))
+
+    gen = torch.Generator().manual_seed(9)
+    rounds = [(torch.randn(2, 64, 1, 28, 28, generator=gen).pin_memory(),
+               torch.randint(0, 10, (2, 64), generator=gen).pin_memory()) for _ in range(4)]
+    seq = make()
+    want = [seq.run_round(host_inputs=r).agg_metrics["loss"] for r in rounds]
+    sim = make()
+    sim.prefetch_inputs(*rounds[0])
+    got, pending = [], None
+    for r in range(4):
+        nxt = rounds[r + 1] if r + 1 < 4 else None
+        h = sim.submit_round(use_staged=True, prefetch_next=nxt)   # round r runs ...
+        if pending is not None:
+            got.append(sim.collect(pending).agg_metrics["loss"])   # ... while r-1 is read
+        pending = h
+    got.append(sim.collect(pending).agg_metrics["loss"])
+    assert got == pytest.approx(want, rel=2e-3, abs=2e-3)
+    torch.testing.assert_close(sim.arena.master, seq.arena.master, rtol=1e-3, atol=1e-4)

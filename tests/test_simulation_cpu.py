@@ -83,3 +83,22 @@ def test_resume_from_checkpoint(tmp_path):
     again = FedSimulation(_cfg(seed=3))
     again.load_global_state(torch.load(tmp_path / "g.pt", weights_only=True))
     torch.testing.assert_close(again.arena.master, sim.arena.master)
+
+
+def test_submit_collect_pipeline_matches_run_round():
+    import pytest
+
+    seq = FedSimulation(_cfg(seed=3))
+    want = [seq.run_round().agg_metrics["loss"] for _ in range(3)]
+    sim = FedSimulation(_cfg(seed=3))
+    h0 = sim.submit_round()
+    h1 = sim.submit_round()                       # round 1 enqueued before round 0 is read
+    with pytest.raises(RuntimeError):
+        sim.submit_round()                        # only two metric buffers
+    got = [sim.collect(h0).agg_metrics["loss"]]
+    h2 = sim.submit_round()
+    got += [sim.collect(h1).agg_metrics["loss"], sim.collect(h2).agg_metrics["loss"]]
+    assert got == pytest.approx(want, rel=1e-6)
+    with pytest.raises(RuntimeError):
+        sim.collect(h2)                           # already collected
+    torch.testing.assert_close(sim.arena.master, seq.arena.master)
