@@ -2,6 +2,7 @@
 
     python tools/tc_check.py            # each variant in its own subprocess (60 s timeout)
     python tools/tc_check.py conv_fwd   # one variant in-process
+    python tools/tc_check.py --inproc conv_pool fc_dgrad   # several in one process (sanitizer runs)
 
 Used while bringing the kernels up (a bad descriptor can fault the context, so variants
 are isolated); ``tests/test_tc_gpu.py`` runs the same functions under pytest.
@@ -292,6 +293,10 @@ def run_one(name: str) -> bool:
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 2 and sys.argv[1] == "--inproc":
+        # several variants in ONE process (for compute-sanitizer runs)
+        results = [run_one(name) for name in sys.argv[2:]]
+        sys.exit(0 if all(results) else 1)
     if len(sys.argv) > 1:
         sys.exit(0 if run_one(sys.argv[1]) else 1)
     failed = []
