@@ -23,6 +23,7 @@ def test_variant_matches_fp32_reference(name):
     got, ref = tc_check.CHECKS[name]()
     torch.cuda.synchronize()
     tc.check_status(got.device)
+    tc_check._check_guards()          # nothing written outside the guarded outputs
     assert torch.isfinite(got).all()
     scale = ref.abs().max().item()
     # bf16 operands, fp32 accumulation: 2% of the output range, elementwise

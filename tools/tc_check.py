@@ -22,6 +22,32 @@ def _bf(*shape, scale=1.0):
     return (torch.randn(*shape, device="cuda") * scale).bfloat16()
 
 
+_GUARDS = []
+
+
+def _guarded(*shape, dtype=torch.bfloat16, pad=4096):
+    """Zeroed tensor of ``shape`` inside a larger canary-filled buffer; ``_check_guards()``
+    verifies afterwards that nothing outside the tensor was written (compute-sanitizer is not
+    available on the GPU pool, so out-of-bounds stores are caught this way)."""
+    n = 1
+    for d in shape:
+        n *= d
+    canary = 77 if dtype == torch.uint8 else 1234.0
+    buf = torch.full((n + 2 * pad,), canary, dtype=dtype, device="cuda")
+    view = buf[pad:pad + n].view(*shape)
+    view.zero_()
+    _GUARDS.append((buf, pad, n, canary))
+    return view
+
+
+def _check_guards():
+    torch.cuda.synchronize()
+    for buf, pad, n, canary in _GUARDS:
+        assert bool((buf[:pad] == canary).all()) and bool((buf[pad + n:] == canary).all()), \
+            "a kernel wrote outside its output tensor"
+    _GUARDS.clear()
+
+
 def _shift_rows(x, s):
     """y[:, q] = x[:, q + s] with zero fill outside (per client)."""
     c, r, ch = x.shape
@@ -71,7 +97,7 @@ def check_conv_fwd_p():
     r = b * W * W
     x, w = _bf(c, r, cin), _bf(c, cout, 9 * cin, scale=0.05)
     bias = torch.randn(c, cout, device="cuda")
-    out = torch.zeros(c, r, cout, device="cuda", dtype=torch.bfloat16)
+    out = _guarded(c, r, cout)
     tc.conv3x3_fwd_persistent(x, w, bias, out, W)
     ref = torch.zeros(c, r, cout, device="cuda")
     for t, s in enumerate(tc._shifts(W)):
@@ -89,8 +115,8 @@ def check_conv_pool():
     x = _bf(c, r, 32)
     w = _bf(c, 64, 288, scale=0.05)
     bias = torch.randn(c, 64, device="cuda")
-    p = torch.zeros(c, b, 9216, device="cuda", dtype=torch.bfloat16)
-    idx = torch.zeros(c, b, 144, 64, device="cuda", dtype=torch.uint8)
+    p = _guarded(c, b, 9216)
+    idx = _guarded(c, b, 144, 64, dtype=torch.uint8)
     tc.conv3x3_pool_fwd(x, w, bias, p, idx, b, W, 0.0, None, 0)
     outs = []
     for k in range(c):
@@ -111,7 +137,7 @@ def check_conv_dgrad_p():
     r = b * W * W
     dy, w = _bf(c, r, cout), _bf(c, cout, 9 * cin, scale=0.05)
     a1 = _bf(c, r, cin)
-    out = torch.zeros(c, r, cin, device="cuda", dtype=torch.bfloat16)
+    out = _guarded(c, r, cin)
     tc.conv3x3_dgrad_persistent(dy, w, out, W, relu_mask=a1)
     ref = torch.zeros(c, r, cin, device="cuda")
     for t, s in enumerate(tc._shifts(W)):
@@ -161,7 +187,7 @@ def check_fc_dgrad():
     from nanofed_b200.ops import tc
     c, b, j, i = 2, 64, 128, 9216
     w, dy = _bf(c, j, i, scale=0.02), _bf(c, b, j)
-    out = torch.zeros(c, b, i, device="cuda", dtype=torch.bfloat16)
+    out = _guarded(c, b, i)
     tc.linear_dgrad(w, dy, out)
     return out.float(), torch.einsum("cbj,cji->cbi", dy.float(), w.float())
 
@@ -173,7 +199,7 @@ def check_fc_dgrad_ragged():
     wbuf = _bf(c, j * i + 512, scale=0.02)
     w = wbuf[:, 256:256 + j * i].unflatten(1, (j, i))
     dy = _bf(c, b, j)
-    out = torch.zeros(c, b, i, device="cuda", dtype=torch.bfloat16)
+    out = _guarded(c, b, i)
     tc.linear_dgrad(w, dy, out)
     return out.float(), torch.einsum("cbj,cji->cbi", dy.float(), w.float())
 
@@ -222,7 +248,7 @@ def check_conv1_fwd():
     n = 1024
     slots = torch.randn(c, n, device="cuda") * 0.3
     w_off, b_off = 64, 512
-    a1 = torch.zeros(c, b * W * W, 32, device="cuda", dtype=torch.bfloat16)
+    a1 = _guarded(c, b * W * W, 32)
     tc.conv1_fwd(x1, slots, w_off, b_off, a1, W)
     outs = []
     for k in range(c):
@@ -277,6 +303,7 @@ def run_one(name: str) -> bool:
     got, ref = CHECKS[name]()
     torch.cuda.synchronize()
     tc.check_status(got.device)
+    _check_guards()
     err = (got - ref).abs().max().item()
     scale = ref.abs().max().item()
     rel = err / max(scale, 1e-6)
