@@ -25,7 +25,7 @@ def _simulate(args: argparse.Namespace) -> int:
         model=args.model, clients_per_gpu=args.clients_per_gpu,
         samples_per_client=args.samples_per_client, batch_size=args.batch_size,
         local_epochs=args.local_epochs, learning_rate=args.lr, engine=args.engine,
-        compute_dtype=args.dtype, device=args.device,
+        compute_dtype=args.dtype, device=args.device, round_deadline_ms=args.round_deadline_ms,
         privacy=PrivacyConfig(noise_multiplier=args.noise_multiplier,
                               max_gradient_norm=args.clip_norm) if args.dp else None,
     )
@@ -68,7 +68,8 @@ def main(argv: list[str] | None = None) -> int:
                                  formatter_class=argparse.RawDescriptionHelpFormatter)
     sub = ap.add_subparsers(dest="cmd", required=True)
 
-    s = sub.add_parser("simulate", help="in-box federated simulation on the local GPUs")
+    s = sub.add_parser("simulate", aliases=["train"],
+                       help="in-box federated simulation on the local GPUs")
     s.add_argument("--model", default="mnist_cnn")
     s.add_argument("--clients-per-gpu", type=int, default=32)
     s.add_argument("--samples-per-client", type=int, default=512)
@@ -82,6 +83,8 @@ def main(argv: list[str] | None = None) -> int:
     s.add_argument("--dp", action="store_true")
     s.add_argument("--noise-multiplier", type=float, default=1.1)
     s.add_argument("--clip-norm", type=float, default=1.0)
+    s.add_argument("--round-deadline-ms", type=float, default=None,
+                   help="leave a GPU's cohort out of a round when its local training takes longer")
     s.add_argument("--save", default=None, help="write the final global state_dict here")
     s.set_defaults(fn=_simulate)
 

@@ -68,6 +68,11 @@ class CohortConfig:
     max_steps_per_epoch: int | None = None
     sample_counts: list[int] | None = None  # per-client n_k on this rank (≤ samples_per_client)
     screen_nonfinite: bool = False  # K-STATS every round; clients with NaN/Inf weights are masked out
+    # Straggler deadline: local training of a cohort is timed with CUDA events; a
+    # GPU whose cohort needs longer than this is left out of the round's average (its clients run
+    # in lock-step, so the GPU is the unit of straggling).  Costs one host sync per round and, with
+    # several ranks, one tiny all-reduce so that a round in which EVERY cohort is late is kept.
+    round_deadline_ms: float | None = None
 
     @property
     def steps_per_epoch(self) -> int:
@@ -454,8 +459,7 @@ class FedSimulation:
         with self.timer.phase("bcast"):
             ops.bcast_global(arena.master, arena.slots, arena.slots_lowp, arena.momentum)
             self.engine.after_broadcast()
-        with self.timer.phase("local_train"):
-            self.engine.local_steps()
+        late = self._train_with_deadline()
         with self.timer.phase("aggregate"):
             self.engine.before_aggregate()
             for k in getattr(self, "_poison", []):
@@ -478,16 +482,70 @@ class FedSimulation:
                           noise_mask=arena.noise_mask, seed=cfg.seed + 7919,
                           offset=self._noise_offset)
                 self._noise_offset += arena.layout.total
-            mask = getattr(self, "_round_mask", None)
-            if mask is not None and cfg.screen_nonfinite:
-                saved, arena.mask = arena.mask, mask
+            mask = getattr(self, "_round_mask", None) if cfg.screen_nonfinite else None
+            if late:                     # this cohort missed the deadline: none of its clients count
+                mask = torch.zeros_like(arena.mask)
+            if mask is not None:
+                # in place: the fused multi-GPU kernel holds the address of arena.mask
+                saved = arena.mask.clone()
+                arena.mask.copy_(mask)
             if self.reducer is None:
                 ops.fedavg_reduce(arena.slots, arena.counts, out=arena.master,
                                   out_lowp=arena.master_lowp, mask=arena.mask, **kw)
             else:
                 self.reducer.reduce(arena, **kw)
-            if mask is not None and cfg.screen_nonfinite:
-                arena.mask = saved
+            if mask is not None:
+                arena.mask.copy_(saved)
+
+    def _train_with_deadline(self) -> bool:
+        """Local training of this rank's cohort; returns True if the cohort is a straggler that
+        must be left out of this round (``CohortConfig.round_deadline_ms``)."""
+        import time
+
+        cfg = self.cfg
+        delay_ms, self._delay_ms = getattr(self, "_delay_ms", 0.0), 0.0
+        deadline = cfg.round_deadline_ms
+        cuda = self.device.type == "cuda"
+        if deadline is not None:
+            if cuda:
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+            else:
+                start = time.perf_counter()
+        with self.timer.phase("local_train"):
+            if delay_ms > 0:                     # injected fault: a slow cohort
+                if cuda:
+                    torch.cuda._sleep(int(delay_ms * 1.9e6))   # ~cycles at 1.9 GHz
+                else:
+                    time.sleep(delay_ms / 1e3)
+            self.engine.local_steps()
+        self.last_train_ms = None
+        self.stragglers_last_round: list[str] = []
+        if deadline is None:
+            return False
+        if cuda:
+            t1.record()
+            t1.synchronize()
+            elapsed = t0.elapsed_time(t1)
+        else:
+            elapsed = (time.perf_counter() - start) * 1e3
+        self.last_train_ms = elapsed
+        late = elapsed > deadline
+        on_time = torch.tensor([0.0 if late else 1.0], device=self.device)
+        if self.rank.distributed:
+            import torch.distributed as dist
+
+            dist.all_reduce(on_time)
+        if late and float(on_time.item()) == 0.0:
+            self.logger.warning(f"round {self._round}: every cohort missed the {deadline} ms "
+                                "deadline; keeping all of them")
+            return False
+        if late:
+            base = self.rank.rank * cfg.clients_per_gpu
+            self.stragglers_last_round = [f"client_{base + k}" for k in range(cfg.clients_per_gpu)]
+            self.logger.warning(f"round {self._round}: cohort of rank {self.rank.rank} took "
+                                f"{elapsed:.1f} ms > {deadline} ms; its clients are left out")
+        return late
 
     def run_round(
         self,
@@ -586,13 +644,18 @@ class FedSimulation:
     def drop_clients(self, indices: list[int]) -> None:
         self.arena.mask[torch.as_tensor(indices, device=self.device)] = 0.0
 
-    def inject_fault(self, kind: str, client: int) -> None:
+    def inject_fault(self, kind: str, client: int, delay_ms: float = 50.0) -> None:
         """Test hook: ``"drop"`` masks the client out, ``"nan"`` poisons its weights AFTER the
-        next local training (use with ``screen_nonfinite=True`` to see it rejected)."""
+        next local training (use with ``screen_nonfinite=True`` to see it rejected), ``"delay"``
+        slows the client's cohort down by ``delay_ms`` (use with ``round_deadline_ms``)."""
         if kind == "drop":
             self.drop_clients([client])
         elif kind == "nan":
             self._poison = getattr(self, "_poison", []) + [client]
+        elif kind == "delay":
+            # a straggler: the client's cohort (its GPU) is held back by ``delay_ms`` in the next
+            # round (clients of one GPU train in lock-step)
+            self._delay_ms = float(delay_ms)
         else:
             raise ValueError(f"unknown fault kind {kind!r}")
 

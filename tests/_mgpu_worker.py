@@ -83,6 +83,31 @@ for transport in ("peer", "nccl"):
 d = (states["peer"] - states["nccl"]).abs().max().item()
 if d > 2e-4:
     fail(f"peer vs nccl transports diverge after 2 rounds: {d:.3e}")
+# 3. straggler deadline with the fused peer kernel: rank 1's cohort is delayed past the deadline,
+#    so the global model must be the average of rank 0's clients only (the kernel reads the
+#    participation mask through the address it was given at construction)
+cfg = CohortConfig(model="mnist_cnn", clients_per_gpu=2, samples_per_client=64, batch_size=32,
+                   local_epochs=1, learning_rate=0.05, seed=11, transport="peer",
+                   round_deadline_ms=150.0, use_cuda_graph=False)
+sim = FedSimulation(cfg)
+sim.run_round()                                   # warm-up round (lazy initialisation is slow)
+if info.rank == 1:
+    sim.inject_fault("delay", 0, delay_ms=400.0)
+sim.run_round()
+late = sim.stragglers_last_round
+if (info.rank == 1) != bool(late):
+    fail(f"straggler detection wrong on rank {info.rank}: {late} (train {sim.last_train_ms} ms)")
+slots = [torch.zeros_like(sim.arena.slots) for _ in range(info.world_size)]
+counts = [torch.zeros_like(sim.arena.counts) for _ in range(info.world_size)]
+dist.all_gather(slots, sim.arena.slots.contiguous())
+dist.all_gather(counts, sim.arena.counts.contiguous())
+want = (counts[0] / counts[0].sum()).view(-1, 1).mul(slots[0]).sum(0)
+err = (sim.arena.master - want).abs().max().item()
+if err > 1e-5:
+    fail(f"straggler round: global model is not the average of rank 0's clients ({err:.3e})")
+if not bool((sim.arena.mask == 1).all()):
+    fail("participation mask was not restored after the straggler round")
 if info.is_main:
-    print(f"MULTI_GPU_OK world={info.world_size} transport_diff={d:.2e}", flush=True)
+    print(f"MULTI_GPU_OK world={info.world_size} transport_diff={d:.2e} straggler_err={err:.1e}",
+          flush=True)
 rdist.shutdown()

@@ -52,3 +52,40 @@ def test_two_rank_round_equals_global_fedavg(tmp_path):
     counts = torch.cat([a["counts"], b["counts"]])
     want = (counts / counts.sum()).view(-1, 1).mul(slots).sum(0)
     torch.testing.assert_close(a["master"], want, rtol=1e-5, atol=1e-6)
+
+
+def _straggler_worker(rank: int, world: int, port: int, out_dir: str) -> None:
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import logging
+
+    logging.getLogger("nanofed").setLevel(logging.ERROR)
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    cfg = CohortConfig(model="mnist_cnn", clients_per_gpu=2, samples_per_client=16, batch_size=8,
+                       compute_dtype="fp32", engine="autograd", device="cpu", transport="nccl",
+                       round_deadline_ms=2000.0)
+    sim = FedSimulation(cfg)
+    if rank == 1:
+        sim.inject_fault("delay", 0, delay_ms=4000.0)       # rank 1's cohort misses the deadline
+    sim.run_round()
+    torch.save({"master": sim.arena.master.clone(), "slots": sim.arena.slots.clone(),
+                "counts": sim.arena.counts.clone(), "late": sim.stragglers_last_round,
+                "mask": sim.arena.mask.clone()}, f"{out_dir}/s{rank}.pt")
+    from nanofed_b200.runtime import dist as rdist
+
+    rdist.shutdown()
+
+
+def test_cohort_that_misses_the_deadline_is_left_out_of_the_round(tmp_path):
+    port = _free_port()
+    mp.spawn(_straggler_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    a = torch.load(tmp_path / "s0.pt")
+    b = torch.load(tmp_path / "s1.pt")
+    assert a["late"] == [] and b["late"] == ["client_2", "client_3"]
+    assert torch.equal(a["master"], b["master"])
+    # the global model is the average of rank 0's clients only
+    want = (a["counts"] / a["counts"].sum()).view(-1, 1).mul(a["slots"]).sum(0)
+    torch.testing.assert_close(a["master"], want, rtol=1e-5, atol=1e-6)
+    assert bool((b["mask"] == 1).all())          # the participation mask itself is restored

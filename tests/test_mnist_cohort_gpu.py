@@ -179,3 +179,20 @@ def test_rounds_submitted_ahead_of_their_metrics_match_sequential_rounds():
     got.append(sim.collect(pending).agg_metrics["loss"])
     assert got == pytest.approx(want, rel=2e-3, abs=2e-3)
     torch.testing.assert_close(sim.arena.master, seq.arena.master, rtol=1e-3, atol=1e-4)
+
+
+def test_deadline_times_local_training_with_cuda_events():
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    sim = FedSimulation(CohortConfig(clients_per_gpu=2, samples_per_client=64, batch_size=32,
+                                     engine="grouped", round_deadline_ms=1e9))
+    sim.run_round()
+    fast = sim.last_train_ms
+    sim.inject_fault("delay", 0, delay_ms=30.0)
+    sim.run_round()
+    assert sim.last_train_ms > fast + 15.0          # the injected delay is seen by the event timer
+    assert sim.stragglers_last_round == []          # deadline not exceeded
+    sim.cfg.round_deadline_ms = 1e-3                # impossible deadline, single cohort: kept
+    before = sim.arena.master.clone()
+    sim.run_round()
+    assert not torch.equal(before, sim.arena.master) and torch.isfinite(sim.arena.master).all()

@@ -102,3 +102,11 @@ def test_submit_collect_pipeline_matches_run_round():
     with pytest.raises(RuntimeError):
         sim.collect(h2)                           # already collected
     torch.testing.assert_close(sim.arena.master, seq.arena.master)
+
+
+def test_single_cohort_missing_its_deadline_is_kept():
+    sim = FedSimulation(_cfg(round_deadline_ms=1e-6))      # impossible deadline, one cohort
+    before = sim.arena.master.clone()
+    sim.run_round()
+    assert sim.last_train_ms > 1e-6 and sim.stragglers_last_round == []
+    assert torch.isfinite(sim.arena.master).all() and not torch.equal(before, sim.arena.master)
