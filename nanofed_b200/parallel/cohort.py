@@ -185,12 +185,24 @@ class AutogradCohort:
             n for n, b in self.workers[0].named_buffers()
             if not b.is_floating_point() and n in layout
         ]
-        # integer state (e.g. BatchNorm counters) lives outside the fp32 arena
+        # Integer state (e.g. BatchNorm counters) lives outside the fp32 arena: ONE [C, total]
+        # tensor whose slices are the modules' buffers, so the per-round exchange with the arena
+        # is one gather and one scatter (ResNet-18 has 20 counters per client; one copy per
+        # counter and client cost 2.3 ms of every 73 ms round).
+        sizes = [int(layout[n].numel) for n in self._int_buffers]
+        offsets = [sum(sizes[:i]) for i in range(len(sizes))]
+        self._int_all = torch.zeros(arena.num_clients, max(sum(sizes), 1), dtype=torch.int64,
+                                    device=self.device)
+        self._int_idx = torch.tensor(
+            [layout[n].offset + e for n, sz in zip(self._int_buffers, sizes) for e in range(sz)],
+            dtype=torch.long, device=self.device)
         self._int_state = [
-            {n: torch.zeros(layout[n].shape, dtype=layout[n].dtype, device=self.device)
-             for n in self._int_buffers}
-            for _ in range(arena.num_clients)
+            {n: self._int_all[k, o : o + sz].view(layout[n].shape).to(layout[n].dtype)
+             if layout[n].dtype != torch.int64 else self._int_all[k, o : o + sz].view(layout[n].shape)
+             for n, o, sz in zip(self._int_buffers, offsets, sizes)}
+            for k in range(arena.num_clients)
         ]
+        self._int_fast = all(layout[n].dtype == torch.int64 for n in self._int_buffers)
         self._slot_views = [arena.client_views(k) for k in range(arena.num_clients)]
         self._grad_views = [arena.grad_views(k) for k in range(arena.num_clients)]
         self._graph: "torch.cuda.CUDAGraph | None" = None
@@ -216,6 +228,10 @@ class AutogradCohort:
         """Integer entries: arena (fp32) → per-client integer tensors."""
         if not self._int_buffers:
             return
+        if self._int_fast:
+            vals = self.arena.master[self._int_idx].round().to(torch.int64)
+            self._int_all[:, : vals.numel()] = vals.unsqueeze(0)
+            return
         master = self.arena.layout.views(self.arena.master)
         for state in self._int_state:
             for name, t in state.items():
@@ -224,6 +240,10 @@ class AutogradCohort:
     def before_aggregate(self) -> None:
         """Integer entries: per-client integer tensors → arena rows (as fp32)."""
         if not self._int_buffers:
+            return
+        if self._int_fast:
+            n = self._int_idx.numel()
+            self.arena.slots[:, self._int_idx] = self._int_all[:, :n].to(torch.float32)
             return
         for k, state in enumerate(self._int_state):
             for name, t in state.items():

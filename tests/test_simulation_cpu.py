@@ -110,3 +110,20 @@ def test_single_cohort_missing_its_deadline_is_kept():
     sim.run_round()
     assert sim.last_train_ms > 1e-6 and sim.stragglers_last_round == []
     assert torch.isfinite(sim.arena.master).all() and not torch.equal(before, sim.arena.master)
+
+
+def test_batchnorm_counters_travel_through_the_arena_in_one_gather_scatter():
+    cfg = CohortConfig(model="resnet18", clients_per_gpu=2, samples_per_client=4, batch_size=2,
+                       compute_dtype="fp32", engine="autograd", device="cpu")
+    sim = FedSimulation(cfg)
+    eng = sim.engine
+    assert eng._int_fast and eng._int_idx.numel() == 20          # ResNet-18: 20 BN counters
+    sim.run_round()
+    state = sim.global_state()
+    counters = [v for k, v in state.items() if k.endswith("num_batches_tracked")]
+    assert len(counters) == 20 and all(v.dtype == torch.int64 for v in counters)
+    assert all(int(v) == cfg.local_steps for v in counters)      # mean of identical counters
+    sim.run_round()                                              # counters restart from the global value
+    assert all(int(v) == 2 * cfg.local_steps
+               for k, v in sim.global_state().items() if k.endswith("num_batches_tracked"))
+    assert all(torch.isfinite(v).all() for v in sim.global_state().values() if v.is_floating_point())
