@@ -58,6 +58,10 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--dp", action="store_true", help="central DP fused into aggregation")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--streams-per-gpu", type=int, default=8,
+                    help="client streams of the generic autograd engine (ResNet configs)")
+    ap.add_argument("--no-channels-last", action="store_true",
+                    help="generic autograd engine: keep NCHW inputs (NHWC is the default)")
     return ap.parse_args()
 
 
@@ -143,9 +147,11 @@ def run_ours(args: argparse.Namespace) -> None:
         model=args.model, clients_per_gpu=args.clients_per_gpu,
         samples_per_client=args.samples_per_client, batch_size=BATCH, local_epochs=LOCAL_EPOCHS,
         learning_rate=LR, compute_dtype=args.dtype, engine=args.engine,
-        transport=args.transport,
+        transport=args.transport, streams_per_gpu=args.streams_per_gpu,
         privacy=PrivacyConfig(epsilon=10.0, noise_multiplier=1.1) if args.dp else None,
     )
+    if args.no_channels_last:
+        os.environ["NFB_CHANNELS_LAST"] = "0"
     sim = FedSimulation(cfg)
     rank, dev = sim.rank, sim.device
     if rank.world_size != args.gpus:
