@@ -87,8 +87,9 @@ __device__ __forceinline__ void bulk_wait_read0() {
 }
 
 // Measured alternatives (B200, 32 clients x 64 images): 1 CTA/SM with 8 epilogue warps:
-// fwd 77 us / dgrad 109 us; 2 CTAs/SM with 4 epilogue warps each: 84 / 120 us.  Both kernels
-// move ~300-430 MB per launch (3.9 TB/s): they are DRAM-bound, not latency-bound.
+// fwd 77 us / dgrad 109 us; 2 CTAs/SM with 4 epilogue warps each: 84 / 120 us.  (Later probes:
+// these kernels are paced by the shared-memory operand fetch of their small-N MMAs and by the
+// 16-byte-piece slab loads, not by DRAM)
 // Epilogue warpgroups (4 warps each = the four TMEM lane quarters); group j takes tiles
 // i = j (mod GROUPS) and owns accumulator j.  MODE 2's pooling epilogue is a latency chain
 // (two group barriers per tile): probes with loads / MMAs / stores disabled left its 118 us
