@@ -83,7 +83,7 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(prefix="nfb_clocks_", suffix=".csv")
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                 "-lms", "100", "-i", str(self.gpu)],
+                 "-lms", "20", "-i", str(self.gpu)],
                 stdout=fd, stderr=subprocess.DEVNULL)
             os.close(fd)
         except Exception:
@@ -93,7 +93,7 @@ class ClockSampler:
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.proc is None:
             return out
-        time.sleep(0.12)
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
