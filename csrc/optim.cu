@@ -15,6 +15,12 @@ struct SgdArgs {
   int64_t zero_prefix;  // ... and g[row][0 : zero_prefix) is zeroed after use (atomic accumulators)
   int64_t skip_lo, skip_len;  // columns [skip_lo, skip_lo + skip_len) of every row are left alone
   int64_t zero_from;          // > 0: g[row][zero_from : row_len) is zeroed after use as well
+  // Optional permuted bf16 side output for ONE parameter stored [rows][inner][taps] at columns
+  // [perm_lo, perm_lo + perm_len): written as [rows][taps][inner] into perm_out + row * perm_gs
+  // (the tap-major conv weights the implicit-GEMM kernels read; saves a permutation kernel per step).
+  __nv_bfloat16* perm_out;
+  int64_t perm_gs, perm_lo, perm_len;
+  int perm_inner, perm_taps;
 };
 
 template <typename G>
@@ -84,6 +90,21 @@ __global__ void __launch_bounds__(256)
     if (lowp) {
       for (int e = 0; e < cnt; ++e) lowp[base + e] = __float2bfloat16_rn(pv[e]);
     }
+    if (a.perm_out) {
+      const int64_t row = base / a.row_len;
+      const int64_t col0 = base - row * a.row_len;
+      if (col0 + 3 >= a.perm_lo && col0 < a.perm_lo + a.perm_len) {
+        const int block = a.perm_inner * a.perm_taps;
+        for (int e = 0; e < cnt; ++e) {
+          const int64_t idx = col0 + e - a.perm_lo;
+          if (idx < 0 || idx >= a.perm_len) continue;
+          const int r = static_cast<int>(idx / block), rem = static_cast<int>(idx % block);
+          const int ci = rem / a.perm_taps, t = rem % a.perm_taps;
+          a.perm_out[row * a.perm_gs + static_cast<int64_t>(r) * block + t * a.perm_inner + ci] =
+              __float2bfloat16_rn(pv[e]);
+        }
+      }
+    }
   }
 }
 
@@ -132,7 +153,9 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
                           float weight_decay, int nesterov, int first_step,
                           const float* grad_scale, float noise_std, uint64_t seed,
                           uint64_t offset, int64_t row_len, int64_t zero_prefix, int64_t skip_lo,
-                          int64_t skip_hi, int64_t zero_from, void* stream) {
+                          int64_t skip_hi, int64_t zero_from, void* stream,
+                          void* perm_out = nullptr, int64_t perm_gs = 0, int64_t perm_lo = 0,
+                          int64_t perm_rows = 0, int perm_inner = 0, int perm_taps = 0) {
   using namespace nfb;
   NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
   NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
@@ -148,9 +171,15 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
                   (row_len > 0 && n % row_len == 0 && skip_lo >= 0 && skip_len > 0 &&
                    skip_hi <= row_len && ((row_len | skip_lo | skip_len) & 3) == 0),
               NFB_EINVAL, "fused_sgd: skipped range must lie in a row, multiples of 4");
+  const int64_t perm_len = perm_rows * perm_inner * perm_taps;
+  NFB_REQUIRE(!perm_out || (row_len > 0 && n % row_len == 0 && perm_len > 0 && perm_lo >= 0 &&
+                            perm_lo + perm_len <= row_len && perm_gs >= perm_len &&
+                            (skip_len == 0 || perm_lo + perm_len <= skip_lo || perm_lo >= skip_hi)),
+              NFB_EINVAL, "fused_sgd: bad permuted-output range");
   SgdArgs a{lr, momentum, dampening, weight_decay, noise_std, nesterov, first_step,
             grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix, skip_lo,
-            skip_len, zero_from};
+            skip_len, zero_from, static_cast<__nv_bfloat16*>(perm_out), perm_gs, perm_lo,
+            perm_out ? perm_len : 0, perm_inner, perm_taps};
   float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
   cudaStream_t st = as_stream(stream);
   const int64_t work = skip_len > 0 ? (n / row_len) * (row_len - skip_len) : n;
@@ -187,6 +216,25 @@ extern "C" int nfb_fused_sgd_skip(float* p, void* g, int g_dtype, float* momentu
   return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
                         weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
                         row_len, zero_prefix, skip_lo, skip_hi, zero_from, stream);
+}
+
+// nfb_fused_sgd_skip plus a permuted bf16 side output: the parameter stored as
+// [perm_rows][perm_inner][perm_taps] at columns perm_lo.. of every row is also written as
+// [perm_rows][perm_taps][perm_inner] (bf16) to perm_out + row * perm_group_stride.
+extern "C" int nfb_fused_sgd_perm(float* p, void* g, int g_dtype, float* momentum_buf,
+                                  void* lowp_out, int64_t n, float lr, float momentum,
+                                  float dampening, float weight_decay, int nesterov,
+                                  int first_step, const float* grad_scale, float noise_std,
+                                  uint64_t seed, uint64_t offset, int64_t row_len,
+                                  int64_t zero_prefix, int64_t skip_lo, int64_t skip_hi,
+                                  int64_t zero_from, void* perm_out, int64_t perm_group_stride,
+                                  int64_t perm_lo, int64_t perm_rows, int perm_inner,
+                                  int perm_taps, void* stream) {
+  NFB_REQUIRE(perm_out, NFB_EINVAL, "fused_sgd_perm: null permuted output");
+  return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
+                        weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
+                        row_len, zero_prefix, skip_lo, skip_hi, zero_from, stream, perm_out,
+                        perm_group_stride, perm_lo, perm_rows, perm_inner, perm_taps);
 }
 
 extern "C" int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg,

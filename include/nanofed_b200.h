@@ -143,6 +143,17 @@ int nfb_fused_sgd_skip(float* p, void* g, int g_dtype, float* momentum_buf, void
                        int nesterov, int first_step, const float* grad_scale, float noise_std,
                        uint64_t seed, uint64_t offset, int64_t row_len, int64_t zero_prefix,
                        int64_t skip_lo, int64_t skip_hi, int64_t zero_from, void* stream);
+/* nfb_fused_sgd_skip plus a permuted bf16 side output: the parameter stored as
+ * [perm_rows][perm_inner][perm_taps] at columns perm_lo.. of every row is also written as
+ * [perm_rows][perm_taps][perm_inner] to perm_out + row * perm_group_stride (tap-major conv weights
+ * for the implicit-GEMM kernels; replaces nfb_mnist_prep_conv2 after the first step).      */
+int nfb_fused_sgd_perm(float* p, void* g, int g_dtype, float* momentum_buf, void* lowp_out,
+                       int64_t n, float lr, float momentum, float dampening, float weight_decay,
+                       int nesterov, int first_step, const float* grad_scale, float noise_std,
+                       uint64_t seed, uint64_t offset, int64_t row_len, int64_t zero_prefix,
+                       int64_t skip_lo, int64_t skip_hi, int64_t zero_from, void* perm_out,
+                       int64_t perm_group_stride, int64_t perm_lo, int64_t perm_rows,
+                       int perm_inner, int perm_taps, void* stream);
 int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg, float* exp_avg_sq,
                    void* lowp_out, int64_t n, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float bias_corr1, float bias_corr2, int decoupled,

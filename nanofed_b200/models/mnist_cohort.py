@@ -114,6 +114,8 @@ class MnistCohortNet:
         self._fc1_range = (o, o + 128 * 9216)
         self.fuse_conv1_wgrad = os.environ.get("NFB_NO_FUSED_WGRAD1") is None
         self.tc_conv1 = os.environ.get("NFB_NO_TC_CONV1") is None
+        # K-OPT also writes the permuted bf16 conv2 weights (needs one w2p buffer for all clients)
+        self.opt_writes_w2p = (self.group == c_all and os.environ.get("NFB_NO_OPT_W2P") is None)
         # momentum needs the gradient history in a buffer: only plain SGD is fused
         self.fuse_fc1_sgd = (cfg.momentum == 0.0 and os.environ.get("NFB_NO_FUSED_SGD") is None)
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
@@ -154,7 +156,10 @@ class MnistCohortNet:
                        first_step=(step == 0), lowp_out=a.slots_lowp.view(-1),
                        row_len=self.n_total, zero_grad_prefix=self._atomic_prefix,
                        skip_range=self._fc1_range if self.fuse_fc1_sgd else None,
-                       zero_grad_from=self._fc1_range[1])   # fc1.bias / fc2.*: fc_head's atomics
+                       zero_grad_from=self._fc1_range[1],   # fc1.bias / fc2.*: fc_head's atomics
+                       # the tap-major bf16 conv2 weights of the NEXT step come out of this pass
+                       perm_out=(self.w2p.view(self.c_all, -1), self.off["conv2.weight"], 64, 32, 9)
+                       if self.opt_writes_w2p else None)
 
     def _step_group(self, step: int, g0: int) -> None:
         cfg, a, lib = self.cfg, self.arena, self.lib
@@ -169,8 +174,10 @@ class MnistCohortNet:
         off = self.off
         xs = x.stride(0)   # x / y are [c, b, ...] slices of [C, S, ...]: client stride stays S*784
         # ---- forward ----
-        self._check(lib.nfb_mnist_prep_conv2(slots.data_ptr(), n, off["conv2.weight"], c,
-                                             self.w2p.data_ptr(), st), "prep_conv2")
+        if step == 0 or not self.opt_writes_w2p:
+            # first step after a broadcast; later steps get w2p from K-OPT's permuted side output
+            self._check(lib.nfb_mnist_prep_conv2(slots.data_ptr(), n, off["conv2.weight"], c,
+                                                 self.w2p.data_ptr(), st), "prep_conv2")
         if self.tc_conv1:
             tc.conv1_fwd(x, slots, off["conv1.weight"], off["conv1.bias"], self.a1, 26)
         else:

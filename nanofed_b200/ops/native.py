@@ -120,6 +120,9 @@ def _declare(L: C.CDLL) -> None:
                           _vp, _f32, _u64, _u64, _i64, _i64, _vp],
         "nfb_fused_sgd_skip": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
                           _vp, _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp],
+        "nfb_fused_sgd_perm": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
+                               _vp, _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp, _i64,
+                               _i64, _i64, _i32, _i32, _vp],
         "nfb_fused_adam": [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32,
                            _f32, _f32, _i32, _vp, _vp],
         "nfb_xent_fused": [_vp, _i32, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _f32, _vp, _vp,
@@ -338,6 +341,7 @@ def fused_sgd_(
     zero_grad_prefix: int = 0,
     skip_range: tuple[int, int] | None = None,
     zero_grad_from: int = 0,
+    perm_out: tuple[torch.Tensor, int, int, int, int] | None = None,
 ) -> torch.Tensor:
     assert p.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous()
     assert p.numel() == g.numel()
@@ -349,7 +353,15 @@ def fused_sgd_(
               float(lr), float(momentum), float(dampening), float(weight_decay),
               1 if nesterov else 0, 1 if first_step else 0, _ptr(grad_scale), float(noise_std),
               seed & (2**64 - 1), offset, int(row_len), int(zero_grad_prefix))
-    if skip_range is None and not zero_grad_from:
+    if perm_out is not None:
+        # (out [rows_of_p, >= n_perm] bf16, lo, rows, inner, taps): permuted copy of one parameter
+        out_t, plo, prows, pinner, ptaps = perm_out
+        assert out_t.dtype == torch.bfloat16 and out_t.is_contiguous()
+        lo, hi = skip_range if skip_range is not None else (0, 0)
+        _check(lib().nfb_fused_sgd_perm(*common, int(lo), int(hi), int(zero_grad_from),
+                                        out_t.data_ptr(), out_t.stride(0), int(plo), int(prows),
+                                        int(pinner), int(ptaps), _stream(p)), "fused_sgd_perm")
+    elif skip_range is None and not zero_grad_from:
         _check(lib().nfb_fused_sgd(*common, _stream(p)), "fused_sgd")
     else:  # columns [lo, hi) of every row were already updated by the kernel that made their gradient
         lo, hi = skip_range if skip_range is not None else (0, 0)

@@ -180,6 +180,7 @@ def fused_sgd_(
     zero_grad_prefix: int = 0,
     skip_range: tuple[int, int] | None = None,
     zero_grad_from: int = 0,
+    perm_out: tuple[torch.Tensor, int, int, int, int] | None = None,
 ) -> torch.Tensor:
     """torch.optim.SGD semantics on flat buffers, with optional DP-SGD pre-processing.
 
@@ -217,6 +218,12 @@ def fused_sgd_(
     if keep is not None:
         for t, saved in keep:
             t.view(-1, row_len)[:, skip_range[0]:skip_range[1]] = saved
+    if perm_out is not None:
+        # the parameter stored [rows][inner][taps] at columns lo.. is also written [rows][taps][inner]
+        out_t, lo, rows, inner, taps = perm_out
+        block = p.view(-1, row_len)[:, lo:lo + rows * inner * taps].view(-1, rows, inner, taps)
+        flat = block.permute(0, 1, 3, 2).reshape(block.shape[0], -1)
+        out_t.view(block.shape[0], -1)[:, :flat.shape[1]] = flat.to(out_t.dtype)
     return p
 
 

@@ -181,6 +181,23 @@ def test_fused_sgd_skips_a_column_range_and_zeroes_the_atomic_prefix():
     assert float((lowp.view(rows, row_len)[:, lo:hi] - 7.0).abs().max()) == 0.0   # untouched
 
 
+def test_fused_sgd_permuted_side_output_matches_oracle():
+    rows, row_len = 3, 64 * 32 * 9 + 256
+    lo = 128
+    p = torch.randn(rows * row_len, device=DEV)
+    g = torch.randn(rows * row_len, device=DEV)
+    out = torch.zeros(rows, 64 * 288, device=DEV, dtype=torch.bfloat16)
+    pr, gr, outr = p.cpu().clone(), g.cpu().clone(), out.cpu().clone()
+    kw = dict(row_len=row_len, zero_grad_prefix=lo + 64 * 288, skip_range=(lo + 64 * 288, row_len - 64))
+    ops.fused_sgd_(p, g, 0.1, perm_out=(out, lo, 64, 32, 9), **kw)
+    ref.fused_sgd_(pr, gr, 0.1, perm_out=(outr, lo, 64, 32, 9), **kw)
+    torch.testing.assert_close(p.cpu(), pr, rtol=1e-5, atol=1e-6)
+    assert torch.equal(out.cpu(), outr)
+    # and it is exactly what the stand-alone permutation kernel produces from the new weights
+    w = p.view(rows, row_len)[:, lo:lo + 64 * 288].view(rows, 64, 32, 9)
+    assert torch.equal(out.view(rows, 64, 9, 32), w.permute(0, 1, 3, 2).bfloat16())
+
+
 def test_fused_adam_matches_torch():
     n = 5000
     p0 = torch.randn(n, device=DEV)

@@ -101,3 +101,16 @@ def test_fused_sgd_skip_range_leaves_columns_alone():
     assert torch.equal(pv[:, :8], p0v[:, :8] - 0.5) and torch.equal(pv[:, 24:], p0v[:, 24:] - 0.5)
     assert float(lowp.view(rows, row_len)[:, 8:24].abs().sum()) == 0.0
     assert float(g.view(rows, row_len)[:, :4].abs().sum()) == 0.0
+
+
+def test_fused_sgd_permuted_side_output():
+    from nanofed_b200.ops import reference as ref
+
+    rows, row_len, lo, r, inner, taps = 2, 64, 8, 2, 3, 4      # parameter [2][3][4] at column 8
+    p = torch.arange(rows * row_len, dtype=torch.float32)
+    g = torch.zeros(rows * row_len)
+    out = torch.zeros(rows, r * inner * taps, dtype=torch.bfloat16)
+    ref.fused_sgd_(p, g, 0.1, row_len=row_len, perm_out=(out, lo, r, inner, taps))
+    src = p.view(rows, row_len)[:, lo:lo + r * inner * taps].view(rows, r, inner, taps)
+    want = src.permute(0, 1, 3, 2).reshape(rows, -1)
+    assert torch.equal(out.float(), want)
