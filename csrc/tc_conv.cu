@@ -370,28 +370,42 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
           const int prow = pp / 12, pcol = pp % 12;
           const int r0 = (2 * prow) * args.grid_w + 2 * pcol;
           const int rows4[4] = {r0, r0 + 1, r0 + args.grid_w, r0 + args.grid_w + 1};
-          float v[4][4];
+          // 2x2 window, four channels: max and argmax on packed bf16 pairs (the staged values
+          // ARE bf16, so this is exact), only the winners are widened for bias + ReLU + dropout.
+          // First maximum wins, as in a scalar `>` scan.
+          uint2 raw[4];
 #pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            const uint2 raw = *reinterpret_cast<const uint2*>(
+          for (int w = 0; w < 4; ++w)
+            raw[w] = *reinterpret_cast<const uint2*>(
                 tile_s + rows4[w] * 128 + (((quad >> 1) ^ (rows4[w] & 7)) * 16) + (quad & 1) * 8);
-            v[w][0] = __uint_as_float(raw.x << 16); v[w][1] = __uint_as_float(raw.x & 0xffff0000u);
-            v[w][2] = __uint_as_float(raw.y << 16); v[w][3] = __uint_as_float(raw.y & 0xffff0000u);
-          }
           const int pos = (prow0 + prow) * 12 + pcol;
           uint32_t codes = 0;
           float pv[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float m = v[0][j];
-            uint32_t a = 0;
+          for (int h = 0; h < 2; ++h) {                        // channel pairs (0,1) and (2,3)
+            __nv_bfloat162 c[4];
 #pragma unroll
-            for (int w = 1; w < 4; ++w)
-              if (v[w][j] > m) { m = v[w][j]; a = w; }
-            m = fmaxf(m + s_bias[quad * 4 + j], 0.f);
-            const bool keep = ((rwords[rep] >> (8 * j)) & 0xffu) >= thresh;
-            codes |= (a | (m > 0.f ? 4u : 0u) | (keep ? 8u : 0u)) << (8 * j);
-            pv[j] = keep ? m * keep_scale : 0.f;
+            for (int w = 0; w < 4; ++w) {
+              const uint32_t bits = h == 0 ? raw[w].x : raw[w].y;
+              c[w] = *reinterpret_cast<const __nv_bfloat162*>(&bits);
+            }
+            const __nv_bfloat162 mx = __hmax2(__hmax2(c[0], c[1]), __hmax2(c[2], c[3]));
+            const uint32_t e0 = __heq2_mask(c[0], mx), e1 = __heq2_mask(c[1], mx),
+                           e2 = __heq2_mask(c[2], mx);
+            // per 16-bit half: 0 if c0 is the max, else 1 if c1, else 2 if c2, else 3
+            const uint32_t arg2 = ~e0 & ((e1 & 0x00010001u) |
+                                         (~e1 & ((e2 & 0x00020002u) | (~e2 & 0x00030003u))));
+            const uint32_t mbits = *reinterpret_cast<const uint32_t*>(&mx);
+            const float mf[2] = {__uint_as_float(mbits << 16), __uint_as_float(mbits & 0xffff0000u)};
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const int j = 2 * h + k;
+              const float m = fmaxf(mf[k] + s_bias[quad * 4 + j], 0.f);
+              const uint32_t a = (arg2 >> (16 * k)) & 3u;
+              const bool keep = ((rwords[rep] >> (8 * j)) & 0xffu) >= thresh;
+              codes |= (a | (m > 0.f ? 4u : 0u) | (keep ? 8u : 0u)) << (8 * j);
+              pv[j] = keep ? m * keep_scale : 0.f;
+            }
           }
           {
             const __nv_bfloat162 lo = __floats2bfloat162_rn(pv[0], pv[1]);
