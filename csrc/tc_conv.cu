@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
         for (int rep = 0; rep < 3; ++rep) {
           const int it = gt + rep * 128;
           const int quad = it & 15, pp = it >> 4;             // pp = prow*12 + pcol
-          const int prow = pp / 12, pcol = pp % 12;
+          const int prow = pp >= 12 ? 1 : 0, pcol = pp - 12 * prow;   // pp < 24: no division
           const int r0 = (2 * prow) * args.grid_w + 2 * pcol;
           const int rows4[4] = {r0, r0 + 1, r0 + args.grid_w, r0 + args.grid_w + 1};
           // 2x2 window, four channels: max and argmax on packed bf16 pairs (the staged values
@@ -378,7 +378,7 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
           for (int w = 0; w < 4; ++w)
             raw[w] = *reinterpret_cast<const uint2*>(
                 tile_s + rows4[w] * 128 + (((quad >> 1) ^ (rows4[w] & 7)) * 16) + (quad & 1) * 8);
-          const int pos = (prow0 + prow) * 12 + pcol;
+          const int pos = prow0 * 12 + pp;                     // (prow0 + prow) * 12 + pcol
           uint32_t codes = 0;
           float pv[4];
 #pragma unroll

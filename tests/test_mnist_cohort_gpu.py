@@ -152,7 +152,8 @@ def test_prefetched_inputs_match_direct_staging():
         return sim.arena.master.clone()
 
     a, b = run(False), run(True)
-    torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-4)
+    diff = (a - b).norm() / a.norm()            # atomics reorder sums between runs
+    assert float(diff) < 2e-3, float(diff)
 
 
 def test_rounds_submitted_ahead_of_their_metrics_match_sequential_rounds():
@@ -177,8 +178,11 @@ def test_rounds_submitted_ahead_of_their_metrics_match_sequential_rounds():
             got.append(sim.collect(pending).agg_metrics["loss"])   # ... while r-1 is read
         pending = h
     got.append(sim.collect(pending).agg_metrics["loss"])
-    assert got == pytest.approx(want, rel=2e-3, abs=2e-3)
-    torch.testing.assert_close(sim.arena.master, seq.arena.master, rtol=1e-3, atol=1e-4)
+    # same data, same seeds; the two runs differ only in the summation order of the atomically
+    # accumulated gradients (and in bf16 roundings that tip over because of it)
+    assert got == pytest.approx(want, rel=1e-2, abs=1e-2)
+    diff = (sim.arena.master - seq.arena.master).norm() / seq.arena.master.norm()
+    assert float(diff) < 2e-3, float(diff)
 
 
 def test_deadline_times_local_training_with_cuda_events():
@@ -186,11 +190,12 @@ def test_deadline_times_local_training_with_cuda_events():
 
     sim = FedSimulation(CohortConfig(clients_per_gpu=2, samples_per_client=64, batch_size=32,
                                      engine="grouped", round_deadline_ms=1e9))
+    sim.run_round()                                 # includes graph capture: not representative
     sim.run_round()
     fast = sim.last_train_ms
-    sim.inject_fault("delay", 0, delay_ms=30.0)
+    sim.inject_fault("delay", 0, delay_ms=60.0)
     sim.run_round()
-    assert sim.last_train_ms > fast + 15.0          # the injected delay is seen by the event timer
+    assert sim.last_train_ms > fast + 25.0          # the injected delay is seen by the event timer
     assert sim.stragglers_last_round == []          # deadline not exceeded
     sim.cfg.round_deadline_ms = 1e-3                # impossible deadline, single cohort: kept
     before = sim.arena.master.clone()
