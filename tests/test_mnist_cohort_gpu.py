@@ -98,7 +98,9 @@ def test_fc1_update_fused_into_the_wgrad_epilogue_matches_separate_optimizer():
         results.append(arena.slots.clone())
     # same fp32 accumulators, same update formula; the atomically accumulated conv gradients
     # differ in summation order between runs
-    torch.testing.assert_close(results[0], results[1], rtol=1e-4, atol=2e-6)
+    diff = (results[0] - results[1]).norm() / results[1].norm()
+    assert float(diff) < 1e-4, float(diff)
+    torch.testing.assert_close(results[0], results[1], rtol=1e-3, atol=5e-5)
     moved = (results[0] - arena.master[None]).abs().max().item()
     assert moved > 1e-4                    # and the step did move the weights
 
