@@ -9,6 +9,11 @@ tensor's device, so ops compose with torch work, CUDA graphs capture them, and
 
 All wrappers count launches in ``LAUNCHES`` (read by ``bench.py`` for its
 ``gpu_launches`` field).
+
+Reference spans each kernel replaces are listed per entry point in the header; in short:
+FedAvg reduce ``nanofed/server/aggregator/fedavg.py:53-63``, DP clip + noise
+``privacy/mechanisms.py:85-129``, optimizer step / DP-SGD ``trainer/private.py:54-86``,
+loss + accuracy + ``.item()`` syncs ``trainer/torch.py:14-22`` / ``trainer/base.py:153-159``.
 """
 
 from __future__ import annotations

@@ -10,6 +10,10 @@ split over the first two 32-bit words; words 2,3 are zero), key
 ``(seed & 0xffffffff, seed >> 32)`` and lane ``(offset+i) % 4``.  Uniforms are
 ``((x >> 8) + 0.5) · 2⁻²⁴ ∈ (0,1)``.  Normals: lanes (0,1) and (2,3) are the
 (cos, sin) pair of a Box–Muller transform of uniforms (0,1) and (2,3).
+
+Replaces the CPU ``torch.Generator`` of the reference's noise generators
+(``nanofed/privacy/noise/base.py:16-31``, ``generators.py:49-67``): seeded, reproducible, and
+available on the device that holds the gradients.
 """
 
 from __future__ import annotations
