@@ -33,6 +33,8 @@ from nanofed_b200.trainer.base import TrainingMetrics
 from nanofed_b200.utils import Logger, get_current_time, log_exec
 
 from . import codec
+from .types import (ClientModelUpdateRequest, GlobalModelResponse,  # noqa: F401  (re-exported
+                    ServerModelUpdateRequest)                       # as in the reference module)
 
 
 @dataclass(slots=True, frozen=True)

@@ -4,6 +4,8 @@ from __future__ import annotations
 
 from typing import Any, Literal, TypedDict
 
+from nanofed_b200.privacy.accountant.base import PrivacySpent  # noqa: F401  (reference re-export)
+
 
 class BaseResponse(TypedDict):
     status: Literal["success", "error"]

@@ -16,6 +16,8 @@ from typing import Any, NotRequired, TypedDict
 
 import torch
 
+from nanofed_b200.privacy.accountant.base import PrivacySpent  # noqa: F401  (reference re-export)
+
 
 class ModelUpdate(TypedDict):
     """One client's contribution to a round."""

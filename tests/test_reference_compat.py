@@ -32,3 +32,19 @@ def test_alias_maps_modules_to_the_same_objects():
     out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True,
                          timeout=120)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-1000:]
+
+
+def test_public_api_surface_matches_the_reference():
+    """Every public name / parameter of every ``nanofed.*`` module exists in ``nanofed_b200.*``."""
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    if not (root / "baseline" / "_ref" / "nanofed").exists():
+        import pytest
+
+        pytest.skip("reference not installed under baseline/_ref")
+    p = subprocess.run([sys.executable, str(root / "tools" / "api_diff.py")], capture_output=True,
+                       text=True, timeout=300)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
