@@ -1,0 +1,117 @@
+"""Worker for tests/test_wire_interop.py: the UNMODIFIED reference (baseline/_ref, imported as
+``nanofed``) and this package (``nanofed_b200``) in one process, talking over localhost HTTP.
+
+  mode "ref_client":  reference HTTPClient / TorchTrainer  <->  our HTTPServer + Coordinator
+                      (one full FedAvg round, two clients)
+  mode "ref_server":  our HTTPClient  <->  reference HTTPServer (+ its ModelManager): fetch the
+                      global model, submit an update, read /status
+
+Prints INTEROP_OK on success, exits non-zero otherwise.
+"""
+import asyncio
+import logging
+import socket
+import sys
+import tempfile
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT / "baseline" / "_ref"))
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+from torch.utils.data import DataLoader, TensorDataset  # noqa: E402
+
+import nanofed as ref  # noqa: E402  (the reference)
+import nanofed_b200 as ours  # noqa: E402
+from nanofed.models import MNISTModel as RefModel  # noqa: E402
+from nanofed_b200.models import MNISTModel as OurModel  # noqa: E402
+
+logging.getLogger("nanofed").setLevel(logging.ERROR)
+assert "baseline/_ref" in ref.__file__, ref.__file__
+
+
+def free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def loader(seed: int, n: int = 32) -> DataLoader:
+    g = torch.Generator().manual_seed(seed)
+    return DataLoader(TensorDataset(torch.randn(n, 1, 28, 28, generator=g),
+                                    torch.randint(0, 10, (n,), generator=g)), batch_size=16)
+
+
+async def ref_client_vs_our_server() -> None:
+    server = ours.HTTPServer("127.0.0.1", free_port(), max_request_size=1 << 30)
+    await server.start()
+    base = Path(tempfile.mkdtemp(prefix="nfb_interop_"))
+    coord = ours.Coordinator(ours.ModelManager(OurModel()), ours.FedAvgAggregator(), server,
+                             ours.CoordinatorConfig(1, 2, 1.0, 120, base))
+    before = {k: v.clone() for k, v in coord.model_manager.model.state_dict().items()}
+    sent = []
+
+    async def client(cid: int) -> None:
+        trainer = ref.TorchTrainer(ref.TrainingConfig(epochs=1, batch_size=16, learning_rate=0.1))
+        async with ref.HTTPClient(server.url, f"client_{cid}") as http:   # reference client, JSON wire
+            state, rnd = await http.fetch_global_model()
+            assert rnd == 0 and set(state) == set(before)
+            model = RefModel()
+            model.load_state_dict(state)
+            opt = torch.optim.SGD(model.parameters(), lr=0.1)
+            metrics = trainer.train_epoch(model, loader(cid), opt, 0)
+            ok = await http.submit_update(model, metrics)
+            assert ok, "our server rejected the reference client's update"
+            sent.append({k: v.detach().clone() for k, v in model.state_dict().items()})
+
+    async def drive() -> list:
+        return [m async for m in coord.start_training()]
+
+    rounds, *_ = await asyncio.gather(drive(), client(0), client(1))
+    await server.stop()
+    assert len(rounds) == 1 and rounds[0].num_clients == 2
+    after = coord.model_manager.model.state_dict()
+    # equal sample counts -> plain mean of the two submitted models
+    for k in after:
+        want = (sent[0][k].float() + sent[1][k].float()) / 2
+        torch.testing.assert_close(after[k].float(), want, rtol=1e-5, atol=1e-6)
+    assert (base / "metrics" / "metrics_round_0.json").exists()
+
+
+async def our_client_vs_ref_server() -> None:
+    server = ref.HTTPServer("127.0.0.1", free_port())
+    base = Path(tempfile.mkdtemp(prefix="nfb_interop_ref_"))
+    manager = ref.ModelManager(RefModel())
+    # the reference Coordinator constructor wires manager dirs + server.set_coordinator
+    ref.Coordinator(manager, ref.FedAvgAggregator(), server,
+                    ref.CoordinatorConfig(num_rounds=1, min_clients=1, min_completion_rate=1.0,
+                                          round_timeout=60, base_dir=base))
+    await server.start()
+    try:
+        async with ours.HTTPClient(server.url, "client_ours") as http:    # JSON wire (default)
+            state, rnd = await http.fetch_global_model()
+            assert rnd == 0
+            want = manager.model.state_dict()
+            assert set(state) == set(want)
+            for k in want:
+                torch.testing.assert_close(state[k].float(), want[k].float())
+            model = OurModel()
+            model.load_state_dict(state)
+            trainer = ours.TorchTrainer(ours.TrainingConfig(epochs=1, batch_size=16,
+                                                            learning_rate=0.1))
+            opt = torch.optim.SGD(model.parameters(), lr=0.1)
+            metrics = trainer.train_epoch(model, loader(7), opt, 0)
+            assert await http.submit_update(model, metrics), "reference server rejected our update"
+            assert await http.check_server_status() is False          # training not finished
+        stored = server._updates["client_ours"]
+        assert stored["round_number"] == 0 and set(stored["model_state"]) == set(want)
+        assert stored["metrics"]["samples_processed"] == metrics.samples_processed
+    finally:
+        await server.stop()
+
+
+if __name__ == "__main__":
+    mode = sys.argv[1]
+    asyncio.run(ref_client_vs_our_server() if mode == "ref_client" else our_client_vs_ref_server())
+    print("INTEROP_OK", mode, flush=True)
