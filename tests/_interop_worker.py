@@ -5,6 +5,7 @@
                       (one full FedAvg round, two clients)
   mode "ref_server":  our HTTPClient  <->  reference HTTPServer (+ its ModelManager): fetch the
                       global model, submit an update, read /status
+  mode "checkpoint":  a model version written by either ModelManager is loaded by the other
 
 Prints INTEROP_OK on success, exits non-zero otherwise.
 """
@@ -111,7 +112,36 @@ async def our_client_vs_ref_server() -> None:
         await server.stop()
 
 
+def checkpoints_both_ways() -> None:
+    """A version written by one ModelManager is loaded by the other (layout of SURVEY 5.4)."""
+    for writer, reader, w_model, r_model in ((ours, ref, OurModel, RefModel),
+                                             (ref, ours, RefModel, OurModel)):
+        base = Path(tempfile.mkdtemp(prefix="nfb_ckpt_"))
+        models, configs = base / "models", base / "configs"
+        models.mkdir(), configs.mkdir()
+        torch.manual_seed(3)
+        src = w_model()
+        wm = writer.ModelManager(src)
+        wm.set_dirs(models, configs)                       # seeds version 001
+        with torch.no_grad():
+            for p_ in src.parameters():
+                p_.add_(0.25)
+        version = wm.save_model({"round_id": 7, "note": "interop"})
+        rm = reader.ModelManager(r_model())
+        rm.set_dirs(models, configs)                       # finds existing versions, saves nothing
+        loaded = rm.load_model()                           # latest = the version saved above
+        assert loaded.version_id == version.version_id, (loaded.version_id, version.version_id)
+        assert loaded.config.get("round_id") == 7
+        for (k, a), (_, b) in zip(src.state_dict().items(), rm.model.state_dict().items()):
+            assert torch.equal(a, b), k
+        assert len(rm.list_versions()) == len(wm.list_versions()) == 2
+
+
 if __name__ == "__main__":
     mode = sys.argv[1]
-    asyncio.run(ref_client_vs_our_server() if mode == "ref_client" else our_client_vs_ref_server())
+    if mode == "checkpoint":
+        checkpoints_both_ways()
+    else:
+        asyncio.run(ref_client_vs_our_server() if mode == "ref_client"
+                    else our_client_vs_ref_server())
     print("INTEROP_OK", mode, flush=True)

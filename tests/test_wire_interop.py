@@ -1,5 +1,6 @@
-"""Wire compatibility with the UNMODIFIED reference: its HTTPClient completes a
-FedAvg round against our server, and our HTTPClient works against its server."""
+"""Wire and checkpoint compatibility with the UNMODIFIED reference: its
+HTTPClient completes a FedAvg round against our server, our HTTPClient works against its server,
+and model versions written by either ModelManager are loaded by the other."""
 
 import subprocess
 import sys
@@ -12,7 +13,7 @@ pytestmark = pytest.mark.skipif(not (ROOT / "baseline" / "_ref" / "nanofed").exi
                                 reason="reference not installed under baseline/_ref")
 
 
-@pytest.mark.parametrize("mode", ["ref_client", "ref_server"])
+@pytest.mark.parametrize("mode", ["ref_client", "ref_server", "checkpoint"])
 def test_reference_and_this_package_interoperate_over_http(mode):
     p = subprocess.run([sys.executable, str(ROOT / "tests" / "_interop_worker.py"), mode],
                        capture_output=True, text=True, timeout=600)
