@@ -136,6 +136,31 @@ def checkpoints_both_ways() -> None:
             assert torch.equal(a, b), k
         assert len(rm.list_versions()) == len(wm.list_versions()) == 2
 
+    # fault-tolerance store: <dir>/checkpoints/round_N/{metadata.json,state.pt}
+    from datetime import datetime, timezone
+
+    import nanofed.server.fault_tolerance as ref_ft
+    import nanofed_b200.server.fault_tolerance as our_ft
+
+    for w_ft, r_ft in ((our_ft, ref_ft), (ref_ft, our_ft)):
+        base = Path(tempfile.mkdtemp(prefix="nfb_ft_"))
+        update = {"model_state": {"w": [[1.0, 2.0], [3.0, 4.0]]}, "client_id": "c0",
+                  "round_number": 3, "metrics": {"loss": 0.5, "samples_processed": 8},
+                  "timestamp": datetime.now(timezone.utc).isoformat()}
+        meta = w_ft.CheckpointMetadata(round_id=3, timestamp=datetime.now(timezone.utc),
+                                       num_clients=1, client_updates={"c0": update},
+                                       global_model_version="model_v_x_001",
+                                       state=w_ft.RoundState.COMPLETED)
+        w_ft.FileStateStore(base).save_checkpoint(meta, {"w": torch.ones(2, 2)})
+        got = r_ft.FileStateStore(base).load_checkpoint(3)
+        assert got is not None
+        rmeta, rstate = got
+        assert rmeta.round_id == 3 and rmeta.state.name == "COMPLETED" and rmeta.num_clients == 1
+        assert torch.equal(rstate["w"], torch.ones(2, 2))
+        assert torch.equal(torch.as_tensor(rmeta.client_updates["c0"]["model_state"]["w"]),
+                           torch.tensor([[1.0, 2.0], [3.0, 4.0]]))
+        assert [m.round_id for m in r_ft.FileStateStore(base).list_checkpoints()] == [3]
+
 
 if __name__ == "__main__":
     mode = sys.argv[1]
