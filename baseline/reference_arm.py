@@ -33,6 +33,9 @@ from pathlib import Path
 REF_DIR = Path(__file__).resolve().parent / "_ref"
 
 
+_REF_INFO: dict = {}
+
+
 def _unavailable(why: str) -> None:
     print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
 
@@ -49,9 +52,16 @@ class _ShimUpdates(dict):
 
 
 def run_reference(args) -> None:
-    if not (REF_DIR / "nanofed" / "__init__.py").exists():
-        _unavailable("baseline/_ref/nanofed missing (offline pip install did not run)")
+    global _REF_INFO
+    try:
+        from baseline.install_ref import install
+
+        manifest = install()          # verifies an existing install, installs when it can
+    except Exception as exc:
+        _unavailable(f"baseline/_ref unavailable: {exc}"[:300])
         return
+    _REF_INFO = {"ref_source": manifest["how"], "ref_sha": manifest["tree_sha256"],
+                 "ref_identical_to_source": manifest["identical_to_source"]}
     sys.path.insert(0, str(REF_DIR))
     # make sure `nanofed` is the reference, not this repo's compat alias
     for name in [m for m in sys.modules if m == "nanofed" or m.startswith("nanofed.")]:
@@ -192,7 +202,7 @@ async def _run(args, torch) -> None:
         "metric": "client_samples_per_sec", "value": samples_per_round / sec,
         "unit": "client_samples/s", "n_gpus": args.gpus, "steps": len(timed), "warmup": warm,
         "ms_per_step": sec * 1e3, "rounds_per_sec": 1.0 / sec, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": (samples_per_round / sec) / 898.0,
+        "scaling": "weak", "vs_baseline": None, **_REF_INFO,
         "dtype": "fp32", "data": "synthetic", "impl": "reference",
         "config": {"model": "mnist_cnn (1199882 params, random init)",
                    "global_batch": total_clients * 64, "seq_len": None,

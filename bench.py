@@ -34,9 +34,6 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-BASELINE_SAMPLES_PER_SEC = 898.0   # 48 000 client-samples / 53.48 s (CPU, HTTP)
-BASELINE_ROUNDS_PER_SEC = 0.0187
-
 CLIENTS_PER_GPU = 32
 SAMPLES_PER_CLIENT = 512
 BATCH = 64
@@ -247,8 +244,7 @@ def run_ours(args: argparse.Namespace) -> None:
             "metric": "client_samples_per_sec", "value": value, "unit": "client_samples/s",
             "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step,
             "rounds_per_sec": 1e3 / ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": value / BASELINE_SAMPLES_PER_SEC,
-            "vs_baseline_rounds": (1e3 / ms_per_step) / BASELINE_ROUNDS_PER_SEC,
+            "vs_baseline": None,   # BASELINE.json publishes no number for this config
             "dtype": args.dtype, "data": "synthetic", "impl": "ours",
             "config": {
                 "model": f"{args.model} ({sim.layout.num_values} state elements, random init)",

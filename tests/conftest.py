@@ -16,6 +16,16 @@ if str(ROOT) not in sys.path:
 
 os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
 
+# The interoperability tests need the unmodified reference under baseline/_ref.  Where its source
+# tree is mounted (the build box) install it before collection so their skipif sees it; on a GPU
+# box it arrives with the snapshot.
+try:
+    from baseline.install_ref import install as _install_reference
+
+    _install_reference()
+except Exception:
+    pass
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200, sm_100a)")
