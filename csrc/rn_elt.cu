@@ -1,0 +1,570 @@
+// K-ELT for the ResNet cohort engine: everything around the tcgen05 convolutions of
+// csrc/rn_conv.cu, each as ONE launch for all clients of the GPU (client = blockIdx.y):
+//
+//   im2col3      stem input [3, 32, 32] fp32 -> [32*32, 64] bf16 patch rows (27 taps + zero pad)
+//   bn_apply     y = relu(gamma * (x - mean) * rstd + beta [+ residual | + bn2(residual)]) from the
+//                batch sums the conv epilogue accumulated; also the running-statistics update
+//                (momentum 0.1, unbiased variance, num_batches_tracked += 1) in the client's row
+//   bn_bwd_red   dbeta = sum g, dgamma = sum g * xhat with g = dout * (out > 0)  (ReLU mask), for
+//                the main branch and optionally the projection shortcut's BatchNorm at once
+//   bn_bwd_apply dx = gamma * rstd * (g - dbeta / n - xhat * dgamma / n)
+//   head         global average pool -> fc -> log-softmax / NLL / accuracy -> dlogits -> fc
+//                gradients -> gradient of the pooled features broadcast back over the 4x4 grid
+//   conv_sgd     SGD (momentum, weight decay) on the fp32 master conv weights [co][ci][kh][kw] from
+//                the tap-major gradient dWt[tap][co][ci] the wgrad kernel produced; emits the bf16
+//                tap-major working copy for the next forward pass and zeroes the gradient
+//   small_sgd    the same for BatchNorm weight/bias and the classifier
+//
+// No reference counterpart: these are the torch library calls (BatchNorm2d, ReLU, AdaptiveAvgPool2d,
+// Linear, CrossEntropyLoss, SGD.step) that a ResNet runs inside nanofed/trainer/base.py:134-160.
+#include "common.cuh"
+
+namespace nfb {
+namespace rn {
+
+struct BnRef {               // one BatchNorm layer of one launch (offsets into a client's fp32 row)
+  const float* stats;        // [clients][2][C]: sum, sum of squares of the conv output
+  long long gamma, beta, rmean, rvar, nbt;
+};
+
+__device__ __forceinline__ void bn_coeffs(const BnRef& bn, const float* row, int g, int C, int c,
+                                          float inv_n, float eps, float& mean, float& rstd) {
+  const float s = bn.stats[(static_cast<long long>(g) * 2) * C + c];
+  const float q = bn.stats[(static_cast<long long>(g) * 2 + 1) * C + c];
+  mean = s * inv_n;
+  const float var = fmaxf(q * inv_n - mean * mean, 0.f);
+  rstd = rsqrtf(var + eps);
+}
+
+// ---- stem im2col ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    im2col3_kernel(const float* __restrict__ x, long long x_gs, int B, __nv_bfloat16* __restrict__ out) {
+  // one thread = one position x 8 patch entries; entry k = (kh*3 + kw)*3 + ci
+  const int g = blockIdx.y;
+  const long long total = static_cast<long long>(B) * 1024 * 8;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
+    const int oct = static_cast<int>(i & 7);
+    const long long pos = i >> 3;
+    const int b = static_cast<int>(pos >> 10), h = static_cast<int>((pos >> 5) & 31),
+              w = static_cast<int>(pos & 31);
+    const float* img = x + g * x_gs + static_cast<long long>(b) * 3072;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = oct * 8 + e;
+      float val = 0.f;
+      if (k < 27) {
+        const int ci = k % 3, tap = k / 3, hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+        if (hh >= 0 && hh < 32 && ww >= 0 && ww < 32) val = __ldg(img + ci * 1024 + hh * 32 + ww);
+      }
+      v[e] = val;
+    }
+    st_vec(out + ((static_cast<long long>(g) * B * 1024 + pos) * 64 + oct * 8), pack<__nv_bfloat16>(v));
+  }
+}
+
+// ---- BatchNorm forward --------------------------------------------------------------------------
+struct BnApplyArgs {
+  const __nv_bfloat16* x;     // raw conv output [clients][P][C]
+  const __nv_bfloat16* res;   // optional residual (already activated input, or a raw shortcut conv)
+  __nv_bfloat16* y;
+  float* slots;               // client rows (parameters + running statistics)
+  long long row_stride;
+  BnRef bn, bn_res;           // bn_res.stats == null: residual is added as is
+  int P, C, relu;
+  float eps, momentum;
+};
+
+__global__ void __launch_bounds__(256) bn_apply_kernel(const BnApplyArgs a) {
+  extern __shared__ float sm[];   // scale, shift, scale2, shift2 : [4][C]
+  const int g = blockIdx.y, C = a.C;
+  float* row = a.slots + g * a.row_stride;
+  const float inv_n = 1.f / static_cast<float>(a.P);
+  const bool res_bn = a.res != nullptr && a.bn_res.stats != nullptr;
+  for (int c = threadIdx.x; c < C; c += 256) {
+    float mean, rstd;
+    bn_coeffs(a.bn, row, g, C, c, inv_n, a.eps, mean, rstd);
+    const float sc = row[a.bn.gamma + c] * rstd;
+    sm[c] = sc;
+    sm[C + c] = row[a.bn.beta + c] - mean * sc;
+    float mean2 = 0.f, rstd2 = 0.f;
+    if (res_bn) {
+      bn_coeffs(a.bn_res, row, g, C, c, inv_n, a.eps, mean2, rstd2);
+      const float sc2 = row[a.bn_res.gamma + c] * rstd2;
+      sm[2 * C + c] = sc2;
+      sm[3 * C + c] = row[a.bn_res.beta + c] - mean2 * sc2;
+    }
+    if (blockIdx.x == 0) {
+      // torch.nn.BatchNorm2d in training mode: running = (1 - m) * running + m * batch, with the
+      // unbiased batch variance
+      const float unb = static_cast<float>(a.P) / static_cast<float>(a.P - 1);
+      const float var = 1.f / (rstd * rstd) - a.eps;
+      row[a.bn.rmean + c] = (1.f - a.momentum) * row[a.bn.rmean + c] + a.momentum * mean;
+      row[a.bn.rvar + c] = (1.f - a.momentum) * row[a.bn.rvar + c] + a.momentum * var * unb;
+      if (c == 0) row[a.bn.nbt] += 1.f;
+      if (res_bn) {
+        const float var2 = 1.f / (rstd2 * rstd2) - a.eps;
+        row[a.bn_res.rmean + c] = (1.f - a.momentum) * row[a.bn_res.rmean + c] + a.momentum * mean2;
+        row[a.bn_res.rvar + c] = (1.f - a.momentum) * row[a.bn_res.rvar + c] + a.momentum * var2 * unb;
+        if (c == 0) row[a.bn_res.nbt] += 1.f;
+      }
+    }
+  }
+  __syncthreads();
+  const int octs = C >> 3;
+  const long long total = static_cast<long long>(a.P) * octs;
+  const long long base = static_cast<long long>(g) * a.P * C;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
+    const int c0 = static_cast<int>(i % octs) * 8;
+    const long long off = base + i * 8;
+    float v[8], r[8];
+    unpack<__nv_bfloat16>(ld_stream(a.x + off), v);
+    if (a.res) unpack<__nv_bfloat16>(ld_stream(a.res + off), r);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float o = fmaf(v[e], sm[c0 + e], sm[C + c0 + e]);
+      if (a.res) o += res_bn ? fmaf(r[e], sm[2 * C + c0 + e], sm[3 * C + c0 + e]) : r[e];
+      v[e] = a.relu ? fmaxf(o, 0.f) : o;
+    }
+    st_vec(a.y + off, pack<__nv_bfloat16>(v));
+  }
+}
+
+// ---- BatchNorm backward -------------------------------------------------------------------------
+struct BnBwdArgs {
+  const __nv_bfloat16* dout;   // gradient w.r.t. the activated output [clients][P][C]
+  const __nv_bfloat16* out;    // activated output (ReLU mask), or null
+  const __nv_bfloat16* x;      // raw conv output of the main branch
+  const __nv_bfloat16* x2;     // raw conv output of the projection shortcut, or null
+  __nv_bfloat16* dx;           // gradient w.r.t. x   (apply pass)
+  __nv_bfloat16* dx2;          // gradient w.r.t. x2  (apply pass)
+  const float* slots;
+  long long row_stride;
+  float* sgrad;                // compact gradient rows [clients][sgrad_stride]
+  long long sgrad_stride;
+  long long dgamma, dbeta, dgamma2, dbeta2;   // offsets into a sgrad row
+  BnRef bn, bn2;
+  int P, C;
+  float eps;
+};
+
+// shared: mean[C], rstd[C], (mean2, rstd2)
+__device__ __forceinline__ void bn_bwd_prologue(const BnBwdArgs& a, float* sm, int g) {
+  const float inv_n = 1.f / static_cast<float>(a.P);
+  const float* row = a.slots + g * a.row_stride;
+  for (int c = threadIdx.x; c < a.C; c += 256) {
+    float mean, rstd;
+    bn_coeffs(a.bn, row, g, a.C, c, inv_n, a.eps, mean, rstd);
+    sm[c] = mean;
+    sm[a.C + c] = rstd;
+    if (a.x2) {
+      bn_coeffs(a.bn2, row, g, a.C, c, inv_n, a.eps, mean, rstd);
+      sm[2 * a.C + c] = mean;
+      sm[3 * a.C + c] = rstd;
+    }
+  }
+  __syncthreads();
+}
+
+template <bool TWO>
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdArgs a) {
+  extern __shared__ float sm[];   // [4][C] coefficients, then [256][8] reduction scratch
+  const int g = blockIdx.y, C = a.C, octs = C >> 3;
+  bn_bwd_prologue(a, sm, g);
+  const int oct = threadIdx.x % octs, lane_row = threadIdx.x / octs, rows = 256 / octs;
+  const int c0 = oct * 8;
+  float sg[8], sgx[8], sgx2[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) sg[e] = sgx[e] = sgx2[e] = 0.f;
+  const long long base = static_cast<long long>(g) * a.P * C;
+  if (lane_row < rows) {
+    for (int p = blockIdx.x * rows + lane_row; p < a.P; p += gridDim.x * rows) {
+      const long long off = base + static_cast<long long>(p) * C + c0;
+      float d[8], xv[8];
+      unpack<__nv_bfloat16>(ld_stream(a.dout + off), d);
+      if (a.out) {
+        float o[8];
+        unpack<__nv_bfloat16>(ld_stream(a.out + off), o);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) d[e] = o[e] > 0.f ? d[e] : 0.f;
+      }
+      unpack<__nv_bfloat16>(ld_stream(a.x + off), xv);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        sg[e] += d[e];
+        sgx[e] = fmaf(d[e], (xv[e] - sm[c0 + e]) * sm[C + c0 + e], sgx[e]);
+      }
+      if constexpr (TWO) {
+        unpack<__nv_bfloat16>(ld_stream(a.x2 + off), xv);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          sgx2[e] = fmaf(d[e], (xv[e] - sm[2 * C + c0 + e]) * sm[3 * C + c0 + e], sgx2[e]);
+      }
+    }
+  }
+  // reduce over the `rows` threads that share a channel octet
+  float* scratch = sm + 4 * C;
+  float* grow = a.sgrad + g * a.sgrad_stride;
+  for (int pass = 0; pass < (TWO ? 3 : 2); ++pass) {
+    const float* src = pass == 0 ? sg : pass == 1 ? sgx : sgx2;
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 8; ++e) scratch[threadIdx.x * 8 + e] = src[e];
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += 256) {
+      float t = 0.f;
+      for (int r = 0; r < rows; ++r) t += scratch[(r * octs + (c >> 3)) * 8 + (c & 7)];
+      if (pass == 0) {
+        atomicAdd(grow + a.dbeta + c, t);
+        if (TWO) atomicAdd(grow + a.dbeta2 + c, t);
+      } else if (pass == 1) {
+        atomicAdd(grow + a.dgamma + c, t);
+      } else {
+        atomicAdd(grow + a.dgamma2 + c, t);
+      }
+    }
+  }
+}
+
+template <bool TWO>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
+  extern __shared__ float sm[];   // mean, rstd, mean2, rstd2 [4][C]; then k1,k2,k3 per branch [6][C]
+  const int g = blockIdx.y, C = a.C, octs = C >> 3;
+  bn_bwd_prologue(a, sm, g);
+  float* k = sm + 4 * C;
+  const float inv_n = 1.f / static_cast<float>(a.P);
+  const float* row = a.slots + g * a.row_stride;
+  const float* grow = a.sgrad + g * a.sgrad_stride;
+  // dx = s * g - s * dbeta / n - s * xhat * dgamma / n  with s = gamma * rstd
+  for (int c = threadIdx.x; c < C; c += 256) {
+    const float s = row[a.bn.gamma + c] * sm[C + c];
+    k[c] = s;
+    k[C + c] = s * grow[a.dbeta + c] * inv_n;
+    k[2 * C + c] = s * grow[a.dgamma + c] * inv_n;
+    if (TWO) {
+      const float s2 = row[a.bn2.gamma + c] * sm[3 * C + c];
+      k[3 * C + c] = s2;
+      k[4 * C + c] = s2 * grow[a.dbeta2 + c] * inv_n;
+      k[5 * C + c] = s2 * grow[a.dgamma2 + c] * inv_n;
+    }
+  }
+  __syncthreads();
+  const long long total = static_cast<long long>(a.P) * octs;
+  const long long base = static_cast<long long>(g) * a.P * C;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
+    const int c0 = static_cast<int>(i % octs) * 8;
+    const long long off = base + i * 8;
+    float d[8], xv[8], o[8];
+    unpack<__nv_bfloat16>(ld_stream(a.dout + off), d);
+    if (a.out) {
+      float m[8];
+      unpack<__nv_bfloat16>(ld_stream(a.out + off), m);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) d[e] = m[e] > 0.f ? d[e] : 0.f;
+    }
+    unpack<__nv_bfloat16>(ld_stream(a.x + off), xv);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float xh = (xv[e] - sm[c0 + e]) * sm[C + c0 + e];
+      o[e] = k[c0 + e] * d[e] - k[C + c0 + e] - xh * k[2 * C + c0 + e];
+    }
+    st_vec(a.dx + off, pack<__nv_bfloat16>(o));
+    if constexpr (TWO) {
+      unpack<__nv_bfloat16>(ld_stream(a.x2 + off), xv);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float xh = (xv[e] - sm[2 * C + c0 + e]) * sm[3 * C + c0 + e];
+        o[e] = k[3 * C + c0 + e] * d[e] - k[4 * C + c0 + e] - xh * k[5 * C + c0 + e];
+      }
+      st_vec(a.dx2 + off, pack<__nv_bfloat16>(o));
+    }
+  }
+}
+
+// ---- classifier head ------------------------------------------------------------------------------
+// feat [clients][B][pp positions][F] bf16 -> average pool -> logits = W [NC][F] pooled + b.
+// grid (B / 8, clients), 512 threads (one per feature; F == 512), 8 samples per block.
+constexpr int HEAD_NC = 10;
+__global__ void __launch_bounds__(512)
+    head_kernel(const __nv_bfloat16* __restrict__ feat, int B, int pp, const int64_t* __restrict__ labels,
+                long long label_gs, const float* __restrict__ slots, long long row_stride,
+                long long w_off, long long b_off, float* __restrict__ sgrad, long long sgrad_stride,
+                long long dw_off, long long db_off, __nv_bfloat16* __restrict__ dfeat,
+                float* __restrict__ stats) {
+  constexpr int F = 512, SB = 8, NC = HEAD_NC;
+  __shared__ float part[16][SB * NC];     // per-warp partial logits
+  __shared__ float logit[SB * NC];
+  __shared__ float dl[SB * NC];
+  const int g = blockIdx.y, b0 = blockIdx.x * SB, f = threadIdx.x;
+  const int warp = f >> 5, lane = f & 31;
+  const float* row = slots + g * row_stride;
+  float w[NC];
+#pragma unroll
+  for (int j = 0; j < NC; ++j) w[j] = row[w_off + j * F + f];
+  float pooled[SB];
+  const float inv_pp = 1.f / static_cast<float>(pp);
+#pragma unroll
+  for (int s = 0; s < SB; ++s) {
+    const __nv_bfloat16* src = feat + ((static_cast<long long>(g) * B + b0 + s) * pp) * F + f;
+    float t = 0.f;
+    for (int p = 0; p < pp; ++p) t += __bfloat162float(src[static_cast<long long>(p) * F]);
+    pooled[s] = t * inv_pp;
+  }
+#pragma unroll
+  for (int s = 0; s < SB; ++s)
+#pragma unroll
+    for (int j = 0; j < NC; ++j) {
+      const float t = warp_sum(pooled[s] * w[j]);
+      if (lane == 0) part[warp][s * NC + j] = t;
+    }
+  __syncthreads();
+  if (f < SB * NC) {
+    float t = row[b_off + f % NC];
+    for (int wq = 0; wq < 16; ++wq) t += part[wq][f];
+    logit[f] = t;
+  }
+  __syncthreads();
+  if (f < SB) {
+    const int s = f;
+    const int y = static_cast<int>(labels[g * label_gs + b0 + s]);
+    float mx = -3.4e38f;
+    int arg = 0;
+    for (int j = 0; j < NC; ++j)
+      if (logit[s * NC + j] > mx) { mx = logit[s * NC + j]; arg = j; }
+    float z = 0.f;
+    for (int j = 0; j < NC; ++j) z += __expf(logit[s * NC + j] - mx);
+    const float lse = mx + __logf(z);
+    const float invb = 1.f / static_cast<float>(B);
+    for (int j = 0; j < NC; ++j)
+      dl[s * NC + j] = (__expf(logit[s * NC + j] - lse) - (j == y ? 1.f : 0.f)) * invb;
+    atomicAdd(stats + g * 3 + 0, lse - logit[s * NC + y]);
+    atomicAdd(stats + g * 3 + 1, arg == y ? 1.f : 0.f);
+    atomicAdd(stats + g * 3 + 2, 1.f);
+  }
+  __syncthreads();
+  float* grow = sgrad + g * sgrad_stride;
+  float dwj[NC];
+#pragma unroll
+  for (int j = 0; j < NC; ++j) dwj[j] = 0.f;
+#pragma unroll
+  for (int s = 0; s < SB; ++s) {
+    float df = 0.f;
+#pragma unroll
+    for (int j = 0; j < NC; ++j) {
+      df = fmaf(dl[s * NC + j], w[j], df);
+      dwj[j] = fmaf(dl[s * NC + j], pooled[s], dwj[j]);
+    }
+    const __nv_bfloat16 o = __float2bfloat16_rn(df * inv_pp);
+    __nv_bfloat16* dst = dfeat + ((static_cast<long long>(g) * B + b0 + s) * pp) * F + f;
+    for (int p = 0; p < pp; ++p) dst[static_cast<long long>(p) * F] = o;
+  }
+#pragma unroll
+  for (int j = 0; j < NC; ++j) atomicAdd(grow + dw_off + j * F + f, dwj[j]);
+  if (f < NC) {
+    float t = 0.f;
+    for (int s = 0; s < SB; ++s) t += dl[s * NC + f];
+    atomicAdd(grow + db_off + f, t);
+  }
+}
+
+// ---- optimizer ----------------------------------------------------------------------------------
+struct ConvEntry {            // one convolution in the conv_sgd table (device memory)
+  long long w_off;            // fp32 master [co][ci][taps] inside a client row
+  long long t_off;            // tap-major [taps][co][ci] inside a client's dwt / wt row
+  long long col_start;        // first (co, ci) column of this layer in the flattened index space
+  int cout, cin, taps, stem;  // stem: cin == 64 patch entries, only 27 real (k = tap*3 + ci)
+};
+
+__global__ void __launch_bounds__(256)
+    conv_sgd_kernel(const ConvEntry* __restrict__ table, int n_layers, long long total_cols,
+                    float* __restrict__ slots, long long row_stride, float* __restrict__ momentum,
+                    float* __restrict__ dwt, __nv_bfloat16* __restrict__ wt, long long t_stride,
+                    float lr, float mu, float wd, int use_grad) {
+  const int g = blockIdx.y;
+  float* row = slots + g * row_stride;
+  float* mrow = momentum ? momentum + g * row_stride : nullptr;
+  float* grow = dwt + g * t_stride;
+  __nv_bfloat16* trow = wt + g * t_stride;
+  for (long long col = blockIdx.x * 256ll + threadIdx.x; col < total_cols; col += gridDim.x * 256ll) {
+    int l = 0;
+    while (l + 1 < n_layers && col >= table[l + 1].col_start) ++l;
+    const ConvEntry e = table[l];
+    const long long local = col - e.col_start;
+    const int co = static_cast<int>(local / e.cin), ci = static_cast<int>(local % e.cin);
+    if (e.stem) {
+      const long long ti = e.t_off + static_cast<long long>(co) * e.cin + ci;
+      if (ci >= 27) { trow[ti] = __float2bfloat16_rn(0.f); grow[ti] = 0.f; continue; }
+      const long long wi = e.w_off + (static_cast<long long>(co) * 3 + ci % 3) * 9 + ci / 3;
+      float w = row[wi];
+      if (use_grad) {
+        float gr = fmaf(wd, w, grow[ti]);
+        if (mrow) { gr = fmaf(mu, mrow[wi], gr); mrow[wi] = gr; }
+        w = fmaf(-lr, gr, w);
+        row[wi] = w;
+        grow[ti] = 0.f;
+      }
+      trow[ti] = __float2bfloat16_rn(w);
+      continue;
+    }
+    const long long wi0 = e.w_off + local * e.taps;
+    for (int t = 0; t < e.taps; ++t) {
+      const long long ti = e.t_off + (static_cast<long long>(t) * e.cout + co) * e.cin + ci;
+      float w = row[wi0 + t];
+      if (use_grad) {
+        float gr = fmaf(wd, w, grow[ti]);
+        if (mrow) { gr = fmaf(mu, mrow[wi0 + t], gr); mrow[wi0 + t] = gr; }
+        w = fmaf(-lr, gr, w);
+        row[wi0 + t] = w;
+        grow[ti] = 0.f;
+      }
+      trow[ti] = __float2bfloat16_rn(w);
+    }
+  }
+}
+
+struct SmallEntry { long long p_off, g_off, len; };
+
+__global__ void __launch_bounds__(256)
+    small_sgd_kernel(const SmallEntry* __restrict__ table, float* __restrict__ slots,
+                     long long row_stride, float* __restrict__ momentum, float* __restrict__ sgrad,
+                     long long sgrad_stride, float lr, float mu, float wd) {
+  const SmallEntry e = table[blockIdx.x];
+  const int g = blockIdx.y;
+  float* p = slots + g * row_stride + e.p_off;
+  float* m = momentum ? momentum + g * row_stride + e.p_off : nullptr;
+  float* gr = sgrad + g * sgrad_stride + e.g_off;
+  for (long long i = threadIdx.x; i < e.len; i += 256) {
+    float w = p[i];
+    float d = fmaf(wd, w, gr[i]);
+    if (m) { d = fmaf(mu, m[i], d); m[i] = d; }
+    p[i] = fmaf(-lr, d, w);
+    gr[i] = 0.f;
+  }
+}
+
+static int blocks_for(long long work_items, int clients) {
+  long long want = (work_items + 255) / 256;
+  const long long cap = (8ll * sm_count() + clients - 1) / clients;
+  if (want > cap) want = cap;
+  return static_cast<int>(want < 1 ? 1 : want);
+}
+
+}  // namespace rn
+}  // namespace nfb
+
+extern "C" {
+
+int nfb_rn_im2col3(const float* x, long long x_gs, int clients, int batch, void* out, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(x && out && clients >= 1 && batch >= 1, NFB_EINVAL, "rn_im2col3: bad argument");
+  dim3 grid(rn::blocks_for(static_cast<long long>(batch) * 8192, clients), clients);
+  rn::im2col3_kernel<<<grid, 256, 0, as_stream(stream)>>>(x, x_gs, batch,
+                                                          static_cast<__nv_bfloat16*>(out));
+  return launch_status("rn_im2col3");
+}
+
+static nfb::rn::BnRef bn_ref(const float* stats, const long long* offs) {
+  return nfb::rn::BnRef{stats, offs[0], offs[1], offs[2], offs[3], offs[4]};
+}
+
+int nfb_rn_bn_apply(const void* x, const void* res, void* y, float* slots, long long row_stride,
+                    const float* stats, const long long* bn_offs, const float* res_stats,
+                    const long long* res_offs, int clients, int P, int C, int relu, float eps,
+                    float momentum, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(x && y && slots && stats && bn_offs, NFB_EINVAL, "rn_bn_apply: null pointer");
+  NFB_REQUIRE(C % 8 == 0 && C <= 512 && P > 1, NFB_EINVAL, "rn_bn_apply: bad shape");
+  rn::BnApplyArgs a{};
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.res = static_cast<const __nv_bfloat16*>(res);
+  a.y = static_cast<__nv_bfloat16*>(y);
+  a.slots = slots; a.row_stride = row_stride;
+  a.bn = bn_ref(stats, bn_offs);
+  if (res_stats) {
+    NFB_REQUIRE(res && res_offs, NFB_EINVAL, "rn_bn_apply: shortcut BatchNorm without a residual");
+    a.bn_res = bn_ref(res_stats, res_offs);
+  }
+  a.P = P; a.C = C; a.relu = relu; a.eps = eps; a.momentum = momentum;
+  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8, clients), clients);
+  rn::bn_apply_kernel<<<grid, 256, 4 * C * sizeof(float), as_stream(stream)>>>(a);
+  return launch_status("rn_bn_apply");
+}
+
+int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, const void* x2,
+                  void* dx, void* dx2, const float* slots, long long row_stride, float* sgrad,
+                  long long sgrad_stride, const long long* grad_offs /* dgamma dbeta dgamma2 dbeta2 */,
+                  const float* stats, const long long* bn_offs, const float* stats2,
+                  const long long* bn2_offs, int clients, int P, int C, float eps, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(dout && x && slots && sgrad && grad_offs && stats && bn_offs, NFB_EINVAL,
+              "rn_bn_bwd: null pointer");
+  NFB_REQUIRE(C % 8 == 0 && C <= 512 && 256 % (C / 8) == 0, NFB_EINVAL, "rn_bn_bwd: bad channels");
+  NFB_REQUIRE(!x2 || (stats2 && bn2_offs), NFB_EINVAL, "rn_bn_bwd: second branch incomplete");
+  NFB_REQUIRE(!apply || (dx && (!x2 || dx2)), NFB_EINVAL, "rn_bn_bwd: apply needs outputs");
+  rn::BnBwdArgs a{};
+  a.dout = static_cast<const __nv_bfloat16*>(dout);
+  a.out = static_cast<const __nv_bfloat16*>(out);
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.x2 = static_cast<const __nv_bfloat16*>(x2);
+  a.dx = static_cast<__nv_bfloat16*>(dx);
+  a.dx2 = static_cast<__nv_bfloat16*>(dx2);
+  a.slots = slots; a.row_stride = row_stride; a.sgrad = sgrad; a.sgrad_stride = sgrad_stride;
+  a.dgamma = grad_offs[0]; a.dbeta = grad_offs[1]; a.dgamma2 = grad_offs[2]; a.dbeta2 = grad_offs[3];
+  a.bn = bn_ref(stats, bn_offs);
+  if (x2) a.bn2 = bn_ref(stats2, bn2_offs);
+  a.P = P; a.C = C; a.eps = eps;
+  cudaStream_t st = as_stream(stream);
+  if (!apply) {
+    const int rows = 256 / (C / 8);
+    dim3 grid(rn::blocks_for(static_cast<long long>(P) * 256 / rows / 4, clients), clients);
+    const size_t sm = (4 * C + 256 * 8) * sizeof(float);
+    if (x2) rn::bn_bwd_reduce_kernel<true><<<grid, 256, sm, st>>>(a);
+    else rn::bn_bwd_reduce_kernel<false><<<grid, 256, sm, st>>>(a);
+    return launch_status("rn_bn_bwd_reduce");
+  }
+  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8, clients), clients);
+  const size_t sm = 10 * C * sizeof(float);
+  if (x2) rn::bn_bwd_apply_kernel<true><<<grid, 256, sm, st>>>(a);
+  else rn::bn_bwd_apply_kernel<false><<<grid, 256, sm, st>>>(a);
+  return launch_status("rn_bn_bwd_apply");
+}
+
+int nfb_rn_head(const void* feat, int clients, int batch, int positions, const int64_t* labels,
+                long long label_gs, const float* slots, long long row_stride, long long w_off,
+                long long b_off, float* sgrad, long long sgrad_stride, long long dw_off,
+                long long db_off, void* dfeat, float* stats, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(feat && labels && slots && sgrad && dfeat && stats, NFB_EINVAL, "rn_head: null pointer");
+  NFB_REQUIRE(batch % 8 == 0 && positions >= 1, NFB_EINVAL, "rn_head: batch must be a multiple of 8");
+  dim3 grid(batch / 8, clients);
+  rn::head_kernel<<<grid, 512, 0, as_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(feat), batch, positions, labels, label_gs, slots, row_stride,
+      w_off, b_off, sgrad, sgrad_stride, dw_off, db_off, static_cast<__nv_bfloat16*>(dfeat), stats);
+  return launch_status("rn_head");
+}
+
+int nfb_rn_conv_sgd(const void* table, int n_layers, long long total_cols, float* slots,
+                    long long row_stride, float* momentum, float* dwt, void* wt, long long t_stride,
+                    int clients, float lr, float mu, float wd, int use_grad, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(table && slots && dwt && wt && n_layers >= 1, NFB_EINVAL, "rn_conv_sgd: null pointer");
+  dim3 grid(rn::blocks_for(total_cols, clients), clients);
+  rn::conv_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      static_cast<const rn::ConvEntry*>(table), n_layers, total_cols, slots, row_stride, momentum,
+      dwt, static_cast<__nv_bfloat16*>(wt), t_stride, lr, mu, wd, use_grad);
+  return launch_status("rn_conv_sgd");
+}
+
+int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long row_stride,
+                     float* momentum, float* sgrad, long long sgrad_stride, int clients, float lr,
+                     float mu, float wd, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(table && slots && sgrad && n_entries >= 1, NFB_EINVAL, "rn_small_sgd: null pointer");
+  dim3 grid(n_entries, clients);
+  rn::small_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      static_cast<const rn::SmallEntry*>(table), slots, row_stride, momentum, sgrad, sgrad_stride,
+      lr, mu, wd);
+  return launch_status("rn_small_sgd");
+}
+
+}  // extern "C"

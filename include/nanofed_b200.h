@@ -295,6 +295,56 @@ int nfb_mnist_conv1_wgrad(const void* da1, const float* x, int64_t x_cstride, in
                           float* grads, int64_t row_stride, int64_t w_off, int64_t b_off,
                           void* stream);
 
+/* ---- ResNet cohort engine: generic K-CONV (csrc/rn_conv.cu) and K-ELT (csrc/rn_elt.cu) ---------
+ * No counterpart in the reference: these replace the torch library calls (Conv2d, BatchNorm2d,
+ * ReLU, AdaptiveAvgPool2d, Linear, CrossEntropyLoss, SGD.step) that a ResNet-18 executes inside
+ * nanofed/trainer/base.py:134-160, for all clients of a GPU per launch.
+ * An activation is bf16 NHWC [imgs][H][W][C] with imgs = clients * batch, C a multiple of 64 and a
+ * 128-byte aligned base; `parity` != 0 addresses it through the stride-2 view [2C, W/2, 2, H/2].  */
+typedef struct {
+  const void* ptr;
+  int imgs, H, W, C, parity;
+} nfb_rn_act;
+/* taps: n_taps x {dh, dw, ph, pw, wrow, src}: row/column shift of the A box, parity of the A view,
+ * first weight row of the tap, operand pair (0 | 1).  dgrad = 0: out[pos, n] = sum A[pos+tap, k] *
+ * W[wrow + n][k] (weights K-major); dgrad = 1: ... * W[wrow + k][n].  w_dims = {inner, rows, client
+ * stride} per pair.  H x W is the position grid of the output; stats (optional) receives per
+ * client the per-channel sum and sum of squares of the stored bf16 values ([clients][2][n_out],
+ * fp32 atomics); residual (+ optional ReLU mask) is added before the store.                   */
+int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, const void* w0,
+                     const void* w1, const int* w_dims, int clients, int imgs_per_client, int H,
+                     int W, int n_out, int n_taps, const int* taps, const nfb_rn_act* out,
+                     int out_ph, int out_pw, float* stats, const void* residual,
+                     const void* res_mask, int bn_tile, int halves, int* status, void* stream);
+/* out[client][tap][co][ci] (+)= sum_pos x[pos + tap][ci] * dy[pos][co]; k_split > 1 adds with fp32
+ * atomics (the target must then be zero).                                                     */
+int nfb_rn_conv_wgrad(const nfb_rn_act* x, const nfb_rn_act* dy, int clients, int imgs_per_client,
+                      int n_taps, const int* taps, float* out, long long out_gs, int k_split,
+                      int bn_tile, int posk, int* status, void* stream);
+int nfb_rn_im2col3(const float* x, long long x_gs, int clients, int batch, void* out, void* stream);
+/* bn_offs / res_offs: {weight, bias, running_mean, running_var, num_batches_tracked} offsets in a
+ * client's fp32 row; stats as written by nfb_rn_conv_gemm.                                    */
+int nfb_rn_bn_apply(const void* x, const void* res, void* y, float* slots, long long row_stride,
+                    const float* stats, const long long* bn_offs, const float* res_stats,
+                    const long long* res_offs, int clients, int P, int C, int relu, float eps,
+                    float momentum, void* stream);
+/* apply = 0: accumulate dgamma / dbeta (fp32 atomics into sgrad rows); apply = 1: write dx (dx2). */
+int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, const void* x2,
+                  void* dx, void* dx2, const float* slots, long long row_stride, float* sgrad,
+                  long long sgrad_stride, const long long* grad_offs, const float* stats,
+                  const long long* bn_offs, const float* stats2, const long long* bn2_offs,
+                  int clients, int P, int C, float eps, void* stream);
+int nfb_rn_head(const void* feat, int clients, int batch, int positions, const int64_t* labels,
+                long long label_gs, const float* slots, long long row_stride, long long w_off,
+                long long b_off, float* sgrad, long long sgrad_stride, long long dw_off,
+                long long db_off, void* dfeat, float* stats, void* stream);
+int nfb_rn_conv_sgd(const void* table, int n_layers, long long total_cols, float* slots,
+                    long long row_stride, float* momentum, float* dwt, void* wt, long long t_stride,
+                    int clients, float lr, float mu, float wd, int use_grad, void* stream);
+int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long row_stride,
+                     float* momentum, float* sgrad, long long sgrad_stride, int clients, float lr,
+                     float mu, float wd, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
