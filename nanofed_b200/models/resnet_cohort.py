@@ -1,0 +1,353 @@
+"""ResNet-18 (CIFAR shape, BatchNorm) for a whole cohort of clients on hand-written kernels.
+
+Same math as ``models.resnet.ResNet18(norm="batch")`` trained by the reference's client loop
+(``nanofed/trainer/base.py:134-160`` with ``torch.optim.SGD``), expressed for all C clients of a
+GPU at once: the client is the group dimension of every launch, a local step is ~125 launches
+whatever the client count, and a local epoch is one CUDA graph.  No autograd, no cuDNN, no cuBLAS.
+
+    forward   im2col(3x3x3 stem) → [conv (tcgen05, BN batch sums in the epilogue) → BN+ReLU
+              (+ residual | + BN(projection))]* → avg-pool + fc + cross-entropy (one kernel)
+    backward  per BatchNorm: reduce (dγ, dβ with the ReLU mask applied on the fly) + apply;
+              per conv: wgrad (tcgen05, both operands MN-major, tap-major fp32 result) and dgrad
+              (tcgen05; stride 2 = four parity-class launches, the 1×1 projection's gradient rides
+              in the k-loop of class (0,0); identity shortcuts are added in the dgrad epilogue)
+    update    SGD on the fp32 master weights from the tap-major gradients, which also writes the
+              bf16 tap-major working copy of the next step
+
+Activations are bf16 NHWC, accumulation / BatchNorm statistics / master weights fp32.  BatchNorm
+running statistics and ``num_batches_tracked`` are updated in the client's arena row, so FedAvg
+averages them exactly like the reference does for every ``state_dict`` entry
+(``nanofed/server/aggregator/fedavg.py:53-66``).
+"""
+
+from __future__ import annotations
+
+import os
+import struct
+from dataclasses import dataclass, field
+from typing import Any
+
+import torch
+
+from nanofed_b200.ops import native, rn, tc
+
+AVAILABLE = True
+_WIDTHS, _STRIDES = (64, 128, 256, 512), (1, 2, 2, 2)
+
+
+@dataclass
+class _Conv:
+    name: str          # state_dict key of the weight
+    cin: int           # channels of the A tensor (64 patch entries for the stem)
+    cout: int
+    k: int
+    stride: int
+    hin: int
+    w_off: int = 0     # fp32 master inside a client row
+    t_off: int = 0     # tap-major copy / gradient inside a wt / dwt row
+    stem: bool = False
+
+    @property
+    def taps(self) -> int:
+        return self.k * self.k
+
+    @property
+    def hout(self) -> int:
+        return self.hin // self.stride
+
+
+@dataclass
+class _Bn:
+    prefix: str
+    c: int
+    offs: tuple[int, ...] = ()       # weight, bias, running_mean, running_var, num_batches_tracked
+    s_off: int = 0                   # batch sums [clients][2][c] inside the stats buffer
+    g_off: tuple[int, int] = (0, 0)  # dgamma, dbeta inside a sgrad row
+
+
+@dataclass
+class _Block:
+    conv1: _Conv
+    bn1: _Bn
+    conv2: _Conv
+    bn2: _Bn
+    conv_sc: _Conv | None = None
+    bn_sc: _Bn | None = None
+    bufs: dict[str, torch.Tensor] = field(default_factory=dict)
+
+
+class ResNetCohortNet:
+    """Lock-step local training of ``arena.num_clients`` ResNet-18s on one GPU."""
+
+    def __init__(self, cfg: Any, arena: Any, shards: Any) -> None:
+        assert arena.device.type == "cuda", "ResNetCohortNet needs a CUDA device"
+        self.cfg, self.arena, self.shards = cfg, arena, shards
+        self.device = dev = arena.device
+        g, b = arena.num_clients, cfg.batch_size
+        if b % 8:
+            raise ValueError("ResNetCohortNet: batch_size must be a multiple of 8")
+        self.g, self.b = g, b
+        lay = arena.layout
+        self.n_total = lay.total
+        off = {name: lay[name].offset for name in lay.names}
+
+        def bn(prefix: str, c: int) -> _Bn:
+            return _Bn(prefix, c, tuple(off[f"{prefix}.{n}"] for n in
+                                        ("weight", "bias", "running_mean", "running_var",
+                                         "num_batches_tracked")))
+
+        # ---- layer table ------------------------------------------------------------------
+        self.stem = _Conv("conv1.weight", 64, 64, 1, 1, 32, stem=True)
+        self.stem_bn = bn("bn1", 64)
+        self.blocks: list[_Block] = []
+        cin, h = 64, 32
+        for li, (width, stride) in enumerate(zip(_WIDTHS, _STRIDES)):
+            for bi in range(2):
+                p = f"layer{li + 1}.{bi}"
+                s = stride if bi == 0 else 1
+                blk = _Block(_Conv(f"{p}.conv1.weight", cin, width, 3, s, h), bn(f"{p}.bn1", width),
+                             _Conv(f"{p}.conv2.weight", width, width, 3, 1, h // s),
+                             bn(f"{p}.bn2", width))
+                if s != 1 or cin != width:
+                    blk.conv_sc = _Conv(f"{p}.shortcut.0.weight", cin, width, 1, s, h)
+                    blk.bn_sc = bn(f"{p}.shortcut.1", width)
+                self.blocks.append(blk)
+                cin, h = width, h // s
+        self.convs = [self.stem] + [c for blk in self.blocks
+                                    for c in (blk.conv1, blk.conv2, blk.conv_sc) if c is not None]
+        self.bns = [self.stem_bn] + [n for blk in self.blocks
+                                     for n in (blk.bn1, blk.bn2, blk.bn_sc) if n is not None]
+        t = 0
+        for c in self.convs:
+            c.w_off, c.t_off = off[c.name], t
+            t += c.taps * c.cout * c.cin
+        self.t_stride = t
+        s_cursor = g_cursor = 0
+        small: list[tuple[int, int, int]] = []           # (p_off, g_off, len)
+        for n in self.bns:
+            n.s_off = s_cursor
+            s_cursor += g * 2 * n.c
+            n.g_off = (g_cursor, g_cursor + n.c)
+            small += [(n.offs[0], g_cursor, n.c), (n.offs[1], g_cursor + n.c, n.c)]
+            g_cursor += 2 * n.c
+        self.fc_w, self.fc_b = off["fc.weight"], off["fc.bias"]
+        self.fc_gw, self.fc_gb = g_cursor, g_cursor + 10 * 512
+        small += [(self.fc_w, self.fc_gw, 10 * 512), (self.fc_b, self.fc_gb, 10)]
+        g_cursor += 10 * 512 + 64
+        self.n_small = len(small)
+
+        # ---- device state -----------------------------------------------------------------
+        f32 = dict(dtype=torch.float32, device=dev)
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        self.wt = torch.zeros(g, self.t_stride, **bf)       # tap-major bf16 weights
+        self.dwt = torch.zeros(g, self.t_stride, **f32)     # tap-major fp32 gradients
+        self.sgrad = torch.zeros(g, g_cursor, **f32)        # BatchNorm / classifier gradients
+        self.stats = torch.zeros(s_cursor, **f32)           # BatchNorm batch sums
+        cols, rows = 0, []
+        for c in self.convs:
+            rows.append(struct.pack("<qqqiiii", c.w_off, c.t_off, cols, c.cout, c.cin, c.taps,
+                                    1 if c.stem else 0))
+            cols += c.cout * c.cin
+        self.total_cols = cols
+        self.conv_table = torch.frombuffer(bytearray(b"".join(rows)), dtype=torch.uint8).to(dev)
+        self.small_table = torch.tensor(small, dtype=torch.int64, device=dev)
+
+        def act(h: int, c: int) -> torch.Tensor:
+            return torch.zeros(g * b, h, h, c, **bf)
+
+        self.xcol, self.raw0, self.a0 = act(32, 64), act(32, 64), act(32, 64)
+        for blk in self.blocks:
+            ho, w = blk.conv1.hout, blk.conv1.cout
+            blk.bufs = {"raw1": act(ho, w), "a": act(ho, w), "raw2": act(ho, w), "out": act(ho, w)}
+            if blk.conv_sc is not None:
+                blk.bufs["rawsc"] = act(ho, w)
+        big = g * b * 32 * 32 * 64
+        self._scratch = [torch.zeros(big, **bf) for _ in range(5)]   # D0, D1, S1, S2, S3
+        self._graph: "torch.cuda.CUDAGraph | None" = None
+        self.launches_per_round = 0
+        self.sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        self._tile_override = os.environ.get("NFB_RN_TILE")   # "bn,halves" for experiments
+
+    # ---- helpers ---------------------------------------------------------------------------
+    def _view(self, i: int, h: int, c: int) -> torch.Tensor:
+        n = self.g * self.b * h * h * c
+        return self._scratch[i][:n].view(self.g * self.b, h, h, c)
+
+    def _wref(self, c: _Conv) -> rn.WeightRef:
+        return rn.WeightRef(self.wt, c.t_off, c.taps * c.cout, c.cin)
+
+    def _bn_stats(self, n: _Bn) -> torch.Tensor:
+        return self.stats[n.s_off : n.s_off + self.g * 2 * n.c].view(self.g, 2, n.c)
+
+    def _tile(self, positions: int, n_out: int) -> tuple[int, int]:
+        if self._tile_override:
+            bn, halves = (int(v) for v in self._tile_override.split(","))
+            if n_out % bn == 0 and positions % (128 * halves) == 0:
+                return bn, halves
+        return rn.pick_tile(positions, n_out, self.g, self.sms)
+
+    def _fwd_conv(self, c: _Conv, x: torch.Tensor, raw: torch.Tensor, n: _Bn) -> None:
+        rn.conv_gemm(False, x, self._wref(c), raw, clients=self.g, grid_hw=(c.hout, c.hout),
+                     taps=rn.fwd_taps(c.k, c.stride, c.cout), a_parity=c.stride == 2,
+                     stats=self._bn_stats(n), n_out=c.cout,
+                     tile=self._tile(self.b * c.hout * c.hout, c.cout))
+
+    def _wgrad(self, c: _Conv, x: torch.Tensor, dy: torch.Tensor) -> None:
+        bn = min(c.cout, 256)
+        kb_total = self.b * c.hout * c.hout // 128
+        tiles = (c.taps * (c.cin // 64) + 1) // 2 * (c.cout // bn) * self.g
+        k_split = max(1, min(kb_total // 4 if kb_total >= 4 else 1, -(-self.sms // tiles)))
+        rn.conv_wgrad(x, dy, self.dwt, c.t_off, clients=self.g,
+                      taps=rn.fwd_taps(c.k, c.stride, c.cout), x_parity=c.stride == 2,
+                      k_split=k_split, tile=(bn, 128))
+
+    def _dgrad(self, c: _Conv, dy: torch.Tensor, dx: torch.Tensor, *, residual=None, res_mask=None,
+               sc: _Conv | None = None, dy_sc: torch.Tensor | None = None) -> None:
+        if c.stride == 1:
+            rn.conv_gemm(True, dy, self._wref(c), dx, clients=self.g, grid_hw=(c.hin, c.hin),
+                         taps=rn.dgrad_taps(c.k, 1, c.cout), residual=residual, res_mask=res_mask,
+                         n_out=c.cin, tile=self._tile(self.b * c.hin * c.hin, c.cin))
+            return
+        assert residual is None
+        for cls in ((0, 0), (0, 1), (1, 0), (1, 1)):
+            taps = rn.dgrad_taps(c.k, 2, c.cout, cls)
+            extra = rn.dgrad_taps(1, 2, sc.cout, cls, src=1) if sc is not None else []
+            rn.conv_gemm(True, dy, self._wref(c), dx, clients=self.g, grid_hw=(c.hout, c.hout),
+                         taps=taps + extra, out_parity=cls, a1=dy_sc if extra else None,
+                         w1=self._wref(sc) if extra else None, n_out=c.cin,
+                         tile=self._tile(self.b * c.hout * c.hout, c.cin))
+
+    # ---- hooks used by FedSimulation ---------------------------------------------------------
+    def after_broadcast(self) -> None:
+        """Fresh global weights arrived in the client rows: rebuild the bf16 tap-major copies."""
+        a = self.arena
+        rn.conv_sgd(self.conv_table, len(self.convs), self.total_cols, a.slots, None, self.dwt,
+                    self.wt, lr=0.0, mu=0.0, wd=0.0, use_grad=False)
+
+    def before_aggregate(self) -> None:
+        pass
+
+    # ---- one local step for every client -------------------------------------------------------
+    def step(self, step: int) -> None:
+        cfg, a, g, b = self.cfg, self.arena, self.g, self.b
+        lo = (step % cfg.steps_per_epoch) * b
+        x = self.shards.images[:, lo : lo + b]
+        y = self.shards.labels[:, lo : lo + b]
+        slots = a.slots
+        # ---------------- forward ----------------
+        rn.im2col3(x, self.xcol)
+        self._fwd_conv(self.stem, self.xcol, self.raw0, self.stem_bn)
+        rn.bn_apply(self.raw0, self.a0, slots, self._bn_stats(self.stem_bn), self.stem_bn.offs,
+                    clients=g, relu=True)
+        cur = self.a0
+        for blk in self.blocks:
+            u = blk.bufs
+            self._fwd_conv(blk.conv1, cur, u["raw1"], blk.bn1)
+            rn.bn_apply(u["raw1"], u["a"], slots, self._bn_stats(blk.bn1), blk.bn1.offs, clients=g,
+                        relu=True)
+            self._fwd_conv(blk.conv2, u["a"], u["raw2"], blk.bn2)
+            if blk.conv_sc is not None:
+                self._fwd_conv(blk.conv_sc, cur, u["rawsc"], blk.bn_sc)
+                rn.bn_apply(u["raw2"], u["out"], slots, self._bn_stats(blk.bn2), blk.bn2.offs,
+                            clients=g, relu=True, res=u["rawsc"],
+                            res_stats=self._bn_stats(blk.bn_sc), res_offs=blk.bn_sc.offs)
+            else:
+                rn.bn_apply(u["raw2"], u["out"], slots, self._bn_stats(blk.bn2), blk.bn2.offs,
+                            clients=g, relu=True, res=cur)
+            u["in"] = cur
+            cur = u["out"]
+        # ---------------- head: loss, metrics, gradient of the last feature map ----------------
+        d0, d1 = 0, 1
+        dout = self._view(d0, 4, 512)
+        rn.head(cur, y, slots, self.fc_w, self.fc_b, self.sgrad, self.fc_gw, self.fc_gb, dout,
+                a.stats, clients=g)
+        # ---------------- backward ----------------
+        for blk in reversed(self.blocks):
+            u = blk.bufs
+            ho, w, hin, cin = blk.conv1.hout, blk.conv1.cout, blk.conv1.hin, blk.conv1.cin
+            dout = self._view(d0, ho, w)
+            dc2 = self._view(2, ho, w)
+            proj = blk.conv_sc is not None
+            dcs = self._view(3, ho, w) if proj else None
+            offs = (blk.bn2.g_off[0], blk.bn2.g_off[1]) + (
+                (blk.bn_sc.g_off[0], blk.bn_sc.g_off[1]) if proj else (0, 0))
+            kw = dict(clients=g, x2=u["rawsc"] if proj else None,
+                      stats2=self._bn_stats(blk.bn_sc) if proj else None,
+                      bn2_offs=blk.bn_sc.offs if proj else None)
+            rn.bn_bwd(False, dout, u["out"], u["raw2"], slots, self.sgrad, offs,
+                      self._bn_stats(blk.bn2), blk.bn2.offs, **kw)
+            rn.bn_bwd(True, dout, u["out"], u["raw2"], slots, self.sgrad, offs,
+                      self._bn_stats(blk.bn2), blk.bn2.offs, dx=dc2, dx2=dcs, **kw)
+            self._wgrad(blk.conv2, u["a"], dc2)
+            da = self._view(4, ho, w)
+            self._dgrad(blk.conv2, dc2, da)
+            dc1 = dc2                                     # dc2 is dead after the two launches above
+            offs1 = (blk.bn1.g_off[0], blk.bn1.g_off[1], 0, 0)
+            rn.bn_bwd(False, da, u["a"], u["raw1"], slots, self.sgrad, offs1,
+                      self._bn_stats(blk.bn1), blk.bn1.offs, clients=g)
+            rn.bn_bwd(True, da, u["a"], u["raw1"], slots, self.sgrad, offs1,
+                      self._bn_stats(blk.bn1), blk.bn1.offs, clients=g, dx=dc1)
+            self._wgrad(blk.conv1, u["in"], dc1)
+            dx = self._view(d1, hin, cin)
+            if proj:
+                self._wgrad(blk.conv_sc, u["in"], dcs)
+                self._dgrad(blk.conv1, dc1, dx, sc=blk.conv_sc, dy_sc=dcs)
+            else:
+                self._dgrad(blk.conv1, dc1, dx, residual=dout, res_mask=u["out"])
+            d0, d1 = d1, d0
+        dout = self._view(d0, 32, 64)
+        dc0 = self._view(2, 32, 64)
+        offs0 = (self.stem_bn.g_off[0], self.stem_bn.g_off[1], 0, 0)
+        rn.bn_bwd(False, dout, self.a0, self.raw0, slots, self.sgrad, offs0,
+                  self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g)
+        rn.bn_bwd(True, dout, self.a0, self.raw0, slots, self.sgrad, offs0,
+                  self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g, dx=dc0)
+        self._wgrad(self.stem, self.xcol, dc0)
+        # ---------------- update ----------------
+        rn.conv_sgd(self.conv_table, len(self.convs), self.total_cols, slots, a.momentum, self.dwt,
+                    self.wt, lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay,
+                    use_grad=True)
+        rn.small_sgd(self.small_table, self.n_small, slots, a.momentum, self.sgrad,
+                     lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay)
+        self.stats.zero_()
+
+    def _all_steps(self) -> None:
+        for s in range(self.cfg.local_steps):
+            self.step(s)
+
+    def local_steps(self) -> None:
+        if not self.cfg.use_cuda_graph:
+            self._all_steps()
+            return
+        if self._graph is None:
+            self._capture()
+        self._graph.replay()
+
+    def _capture(self) -> None:
+        a = self.arena
+        keep = (a.slots.clone(), a.stats.clone(), self.wt.clone(),
+                None if a.momentum is None else a.momentum.clone())
+
+        def restore() -> None:
+            a.slots.copy_(keep[0])
+            a.stats.copy_(keep[1])
+            self.wt.copy_(keep[2])
+            if keep[3] is not None:
+                a.momentum.copy_(keep[3])
+
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            self.step(0)      # eager warm-up: tensor maps, function attributes
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        tc.check_status(self.device)
+        restore()
+        before = native.LAUNCHES
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            self._all_steps()
+        self.launches_per_round = native.LAUNCHES - before
+        restore()
+        torch.cuda.synchronize(self.device)
+        self._graph = graph

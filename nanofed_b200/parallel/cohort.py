@@ -380,14 +380,18 @@ class FedSimulation:
 
         engine = cfg.engine
         if engine == "auto":
-            engine = "grouped" if (cfg.model == "mnist_cnn" and self.device.type == "cuda"
+            engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18")
+                                   and self.device.type == "cuda"
                                    and _grouped_available()) else "autograd"
+        if engine == "grouped" and cfg.model not in ("mnist_cnn", "resnet18"):
+            raise ValueError(f"engine='grouped' has no hand-written network for {cfg.model!r} "
+                             "(available: mnist_cnn, resnet18); use engine='autograd'")
         self.engine_name = engine
 
         self.arena = Arena(
             self.layout, c, self.device,
             with_momentum=cfg.momentum != 0.0,
-            with_lowp=(engine == "grouped"),
+            with_lowp=(engine == "grouped" and cfg.model == "mnist_cnn"),
             with_grads=(engine == "autograd"),
         )
         self.arena.load_global(template.state_dict())
@@ -403,10 +407,14 @@ class FedSimulation:
         self.arena.counts.copy_(self.shards.sample_counts.to(torch.float32))
         self._counts_host = [float(v) for v in shards.sample_counts.tolist()]
 
-        if engine == "grouped":
+        if engine == "grouped" and cfg.model == "resnet18":
+            from nanofed_b200.models.resnet_cohort import ResNetCohortNet
+
+            self.engine: Any = ResNetCohortNet(cfg, self.arena, self.shards)
+        elif engine == "grouped":
             from nanofed_b200.models.mnist_cohort import MnistCohortNet
 
-            self.engine: Any = MnistCohortNet(cfg, self.arena, self.shards)
+            self.engine = MnistCohortNet(cfg, self.arena, self.shards)
         else:
             self.engine = AutogradCohort(cfg, self.arena, self.shards)
 

@@ -1,0 +1,109 @@
+"""One local step of the hand-written ResNet-18 cohort engine against PyTorch autograd in fp32
+(TF32 off): loss, every parameter's update, BatchNorm running statistics.  The yardstick for a
+bf16-activation engine is PyTorch's own bf16 autocast run of the same step, printed alongside.
+
+    python tools/rn_step_check.py [--clients 2] [--batch 16] [--steps 1]
+"""
+
+from __future__ import annotations
+
+import argparse
+import sys
+from pathlib import Path
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
+
+def reference_step(state, x, y, lr, steps, autocast):
+    from nanofed_b200.models import ResNet18
+
+    model = ResNet18(norm="batch").cuda().train()
+    model.load_state_dict(state)
+    opt = torch.optim.SGD(model.parameters(), lr=lr)
+    b = x.shape[0] // steps
+    losses = []
+    for s in range(steps):
+        xb, yb = x[s * b : (s + 1) * b], y[s * b : (s + 1) * b]
+        opt.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            logits = model(xb)
+        loss = F.cross_entropy(logits.float(), yb)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    return {k: v.detach().float().clone() for k, v in model.state_dict().items()}, losses
+
+
+def run(clients: int, batch: int, steps: int, verbose: bool = True) -> dict:
+    from nanofed_b200 import ops
+    from nanofed_b200.ops import tc
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    lr = 0.05
+    cfg = CohortConfig(model="resnet18", clients_per_gpu=clients, samples_per_client=batch * steps,
+                       batch_size=batch, learning_rate=lr, use_cuda_graph=False, device="cuda",
+                       engine="grouped")
+    sim = FedSimulation(cfg)
+    a = sim.arena
+    ops.bcast_global(a.master, a.slots, a.slots_lowp, a.momentum)
+    sim.engine.after_broadcast()
+    a.stats.zero_()
+    before = sim.layout.unflatten(a.slots[0].clone())
+    for s in range(steps):
+        sim.engine.step(s)
+    torch.cuda.synchronize()
+    tc.check_status(sim.device)
+    worst = {"cos_min": 1.0, "rel_max": 0.0, "ref_rel_max": 0.0, "loss_err": 0.0, "stat_rel": 0.0}
+    for g in range(clients):
+        got = {k: v.float() for k, v in sim.layout.unflatten(a.slots[g].clone()).items()}
+        x, y = sim.shards.images[g], sim.shards.labels[g]
+        want, losses = reference_step(before, x, y, lr, steps, autocast=False)
+        auto, _ = reference_step(before, x, y, lr, steps, autocast=True)
+        loss_got = float(a.stats[g, 0] / a.stats[g, 2])
+        loss_want = sum(losses) / len(losses)
+        worst["loss_err"] = max(worst["loss_err"], abs(loss_got - loss_want) / abs(loss_want))
+        if verbose:
+            print(f"client {g}: loss {loss_got:.5f} (fp32 autograd {loss_want:.5f})")
+        for k in want:
+            b0 = before[k].float().cuda()
+            if "num_batches" in k:
+                assert float(got[k]) == float(want[k]), (k, got[k], want[k])
+                continue
+            if "running" in k:
+                r = float((got[k] - want[k]).norm() / (want[k].norm() + 1e-12))
+                worst["stat_rel"] = max(worst["stat_rel"], r)
+                continue
+            dg, dw, da = got[k] - b0, want[k] - b0, auto[k] - b0
+            cos = float(F.cosine_similarity(dg.flatten(), dw.flatten(), dim=0))
+            r = float((dg - dw).norm() / (dw.norm() + 1e-20))
+            ra = float((da - dw).norm() / (dw.norm() + 1e-20))
+            worst["cos_min"] = min(worst["cos_min"], cos)
+            worst["rel_max"] = max(worst["rel_max"], r)
+            worst["ref_rel_max"] = max(worst["ref_rel_max"], ra)
+            if verbose and g == 0:
+                print(f"  {k:32s} cos {cos:.5f}  rel {r:.3e}  (torch bf16 autocast: {ra:.3e})")
+    if verbose:
+        print({k: round(v, 5) for k, v in worst.items()})
+    return worst
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--clients", type=int, default=2)
+    ap.add_argument("--batch", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=1)
+    args = ap.parse_args()
+    w = run(args.clients, args.batch, args.steps)
+    ok = w["cos_min"] > 0.98 and w["loss_err"] < 2e-2 and w["stat_rel"] < 2e-2
+    print("STEP OK" if ok else "STEP MISMATCH")
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
