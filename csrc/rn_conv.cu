@@ -333,6 +333,9 @@ struct WgradArgs {
   float* out;
   long long out_gs;
   int atomic;
+  float* sgd_w;            // fused SGD: tap-major fp32 master (null = write the gradient)
+  __nv_bfloat16* sgd_wt;   // ... and its bf16 working copy
+  float lr, wd;
   int* status;
 };
 
@@ -443,14 +446,31 @@ __global__ void __launch_bounds__(256, 1)
     const int t = min(q, n_atoms - 1) / args.ci_chunks;
     const int ci = (min(q, n_atoms - 1) % args.ci_chunks) * 64 + (sub & 1) * 32 + lane;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
-    float* base = args.out + static_cast<long long>(g) * args.out_gs +
-                  (static_cast<long long>(t) * args.c_out + ntile * BN) * args.c_in + ci;
+    const long long off0 = static_cast<long long>(g) * args.out_gs +
+                           (static_cast<long long>(t) * args.c_out + ntile * BN) * args.c_in + ci;
+    float* base = args.out + off0;
+    const bool fused = args.sgd_w != nullptr;
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 16) {
       uint32_t r[16];
       tmem_ld_32x32b_x16(lane_addr + c0, r);
       tmem_ld_wait();
       if (!live) continue;
+      if (fused) {
+        // the gradient of these weights is complete in TMEM: apply it to the fp32 master and
+        // refresh the bf16 copy; 32 lanes = 32 consecutive ci, so every access is one full line
+        float w[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[j] = args.sgd_w[off0 + static_cast<long long>(c0 + j) * args.c_in];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const long long o = off0 + static_cast<long long>(c0 + j) * args.c_in;
+          const float nw = fmaf(-args.lr, fmaf(args.wd, w[j], __uint_as_float(r[j])), w[j]);
+          args.sgd_w[o] = nw;
+          args.sgd_wt[o] = __float2bfloat16_rn(nw);
+        }
+        continue;
+      }
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         float* p = base + static_cast<long long>(c0 + j) * args.c_in;
@@ -643,7 +663,8 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
 
 int nfb_rn_conv_wgrad(const nfb_rn_act* x, const nfb_rn_act* dy, int clients, int imgs_per_client,
                       int n_taps, const int* taps, float* out, long long out_gs, int k_split,
-                      int bn_tile, int posk, int* status, void* stream) {
+                      int bn_tile, int posk, float* sgd_w, void* sgd_wt, float lr, float wd,
+                      int* status, void* stream) {
   using namespace nfb;
   using namespace nfb::rn;
   NFB_REQUIRE(x && dy && taps && out && status, NFB_EINVAL, "rn_conv_wgrad: null pointer");
@@ -656,6 +677,9 @@ int nfb_rn_conv_wgrad(const nfb_rn_act* x, const nfb_rn_act* dy, int clients, in
   g.H = dy->H; g.W = dy->W; g.P = P; g.k_split = k_split; g.n_taps = n_taps;
   g.ci_chunks = x->C / 64; g.cpar = x->C; g.c_out = dy->C; g.c_in = x->C;
   g.out = out; g.out_gs = out_gs; g.atomic = k_split > 1 ? 1 : 0; g.status = status;
+  NFB_REQUIRE(!sgd_w || (k_split == 1 && sgd_wt), NFB_EINVAL,
+              "rn_conv_wgrad: the fused update needs the complete gradient (k_split == 1)");
+  g.sgd_w = sgd_w; g.sgd_wt = static_cast<__nv_bfloat16*>(sgd_wt); g.lr = lr; g.wd = wd;
   for (int t = 0; t < n_taps; ++t)
     g.tap[t] = Tap{taps[6 * t], taps[6 * t + 1], taps[6 * t + 2], taps[6 * t + 3], taps[6 * t + 4],
                    taps[6 * t + 5]};

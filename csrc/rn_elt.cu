@@ -10,10 +10,11 @@
 //   bn_bwd_apply dx = gamma * rstd * (g - dbeta / n - xhat * dgamma / n)
 //   head         global average pool -> fc -> log-softmax / NLL / accuracy -> dlogits -> fc
 //                gradients -> gradient of the pooled features broadcast back over the 4x4 grid
-//   conv_sgd     SGD (momentum, weight decay) on the fp32 master conv weights [co][ci][kh][kw] from
-//                the tap-major gradient dWt[tap][co][ci] the wgrad kernel produced; emits the bf16
-//                tap-major working copy for the next forward pass and zeroes the gradient
-//   small_sgd    the same for BatchNorm weight/bias and the classifier
+//   wm_convert   conv weights between the arena's torch layout [co][ci][kh][kw] and the engine's
+//                tap-major fp32 master + bf16 working copy [tap][co][ci] (once per round each way)
+//   tap_sgd      SGD (momentum, weight decay) on tap-major ranges whose gradient the wgrad kernel
+//                accumulated with atomics; the other convolutions are updated in the wgrad epilogue
+//   small_sgd    SGD for BatchNorm weight/bias and the classifier; also re-zeroes the batch sums
 //
 // No reference counterpart: these are the torch library calls (BatchNorm2d, ReLU, AdaptiveAvgPool2d,
 // Linear, CrossEntropyLoss, SGD.step) that a ResNet runs inside nanofed/trainer/base.py:134-160.
@@ -63,7 +64,14 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// ---- BatchNorm forward --------------------------------------------------------------------------
+// ---- BatchNorm forward / backward ------------------------------------------------------------
+// Thread layout shared by the three kernels: a thread owns ONE channel octet (16 bytes) for the
+// whole launch, threads of a block cover 256 / (C / 8) consecutive positions; every per-channel
+// coefficient therefore lives in registers, the loop body is loads -> FMAs -> store with no index
+// arithmetic beyond one pointer increment, and U positions are in flight per thread (the kernels
+// are latency-bound otherwise: 3 loads per 64 bytes of traffic).
+constexpr int BN_U = 4;
+
 struct BnApplyArgs {
   const __nv_bfloat16* x;     // raw conv output [clients][P][C]
   const __nv_bfloat16* res;   // optional residual (already activated input, or a raw shortcut conv)
@@ -75,26 +83,29 @@ struct BnApplyArgs {
   float eps, momentum;
 };
 
+template <bool RES, bool RES_BN>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const BnApplyArgs a) {
-  extern __shared__ float sm[];   // scale, shift, scale2, shift2 : [4][C]
-  const int g = blockIdx.y, C = a.C;
+  const int g = blockIdx.y, C = a.C, octs = C >> 3;
+  const int oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs, c0 = oct * 8;
   float* row = a.slots + g * a.row_stride;
   const float inv_n = 1.f / static_cast<float>(a.P);
-  const bool res_bn = a.res != nullptr && a.bn_res.stats != nullptr;
-  for (int c = threadIdx.x; c < C; c += 256) {
+  float sc[8], sh[8], sc2[8], sh2[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int c = c0 + e;
     float mean, rstd;
     bn_coeffs(a.bn, row, g, C, c, inv_n, a.eps, mean, rstd);
-    const float sc = row[a.bn.gamma + c] * rstd;
-    sm[c] = sc;
-    sm[C + c] = row[a.bn.beta + c] - mean * sc;
-    float mean2 = 0.f, rstd2 = 0.f;
-    if (res_bn) {
+    sc[e] = row[a.bn.gamma + c] * rstd;
+    sh[e] = row[a.bn.beta + c] - mean * sc[e];
+    float mean2 = 0.f, rstd2 = 1.f;
+    sc2[e] = 1.f;
+    sh2[e] = 0.f;
+    if constexpr (RES_BN) {
       bn_coeffs(a.bn_res, row, g, C, c, inv_n, a.eps, mean2, rstd2);
-      const float sc2 = row[a.bn_res.gamma + c] * rstd2;
-      sm[2 * C + c] = sc2;
-      sm[3 * C + c] = row[a.bn_res.beta + c] - mean2 * sc2;
+      sc2[e] = row[a.bn_res.gamma + c] * rstd2;
+      sh2[e] = row[a.bn_res.beta + c] - mean2 * sc2[e];
     }
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == 0 && r == 0) {
       // torch.nn.BatchNorm2d in training mode: running = (1 - m) * running + m * batch, with the
       // unbiased batch variance
       const float unb = static_cast<float>(a.P) / static_cast<float>(a.P - 1);
@@ -102,7 +113,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnApplyArgs a) {
       row[a.bn.rmean + c] = (1.f - a.momentum) * row[a.bn.rmean + c] + a.momentum * mean;
       row[a.bn.rvar + c] = (1.f - a.momentum) * row[a.bn.rvar + c] + a.momentum * var * unb;
       if (c == 0) row[a.bn.nbt] += 1.f;
-      if (res_bn) {
+      if constexpr (RES_BN) {
         const float var2 = 1.f / (rstd2 * rstd2) - a.eps;
         row[a.bn_res.rmean + c] = (1.f - a.momentum) * row[a.bn_res.rmean + c] + a.momentum * mean2;
         row[a.bn_res.rvar + c] = (1.f - a.momentum) * row[a.bn_res.rvar + c] + a.momentum * var2 * unb;
@@ -110,27 +121,35 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnApplyArgs a) {
       }
     }
   }
-  __syncthreads();
-  const int octs = C >> 3;
-  const long long total = static_cast<long long>(a.P) * octs;
-  const long long base = static_cast<long long>(g) * a.P * C;
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
-    const int c0 = static_cast<int>(i % octs) * 8;
-    const long long off = base + i * 8;
-    float v[8], r[8];
-    unpack<__nv_bfloat16>(ld_stream(a.x + off), v);
-    if (a.res) unpack<__nv_bfloat16>(ld_stream(a.res + off), r);
+  const long long base = static_cast<long long>(g) * a.P * C + c0;
+  for (int p0 = blockIdx.x * R * BN_U; p0 < a.P; p0 += gridDim.x * R * BN_U) {
+    uint4 xv[BN_U], rv[BN_U];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      float o = fmaf(v[e], sm[c0 + e], sm[C + c0 + e]);
-      if (a.res) o += res_bn ? fmaf(r[e], sm[2 * C + c0 + e], sm[3 * C + c0 + e]) : r[e];
-      v[e] = a.relu ? fmaxf(o, 0.f) : o;
+    for (int u = 0; u < BN_U; ++u) {
+      const int p = p0 + u * R + r;
+      if (p < a.P) {
+        xv[u] = ld_stream(a.x + base + static_cast<long long>(p) * C);
+        if constexpr (RES) rv[u] = ld_stream(a.res + base + static_cast<long long>(p) * C);
+      }
     }
-    st_vec(a.y + off, pack<__nv_bfloat16>(v));
+#pragma unroll
+    for (int u = 0; u < BN_U; ++u) {
+      const int p = p0 + u * R + r;
+      if (p >= a.P) continue;
+      float v[8], rr[8];
+      unpack<__nv_bfloat16>(xv[u], v);
+      if constexpr (RES) unpack<__nv_bfloat16>(rv[u], rr);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        float o = fmaf(v[e], sc[e], sh[e]);
+        if constexpr (RES) o += RES_BN ? fmaf(rr[e], sc2[e], sh2[e]) : rr[e];
+        v[e] = a.relu ? fmaxf(o, 0.f) : o;
+      }
+      st_vec(a.y + base + static_cast<long long>(p) * C, pack<__nv_bfloat16>(v));
+    }
   }
 }
 
-// ---- BatchNorm backward -------------------------------------------------------------------------
 struct BnBwdArgs {
   const __nv_bfloat16* dout;   // gradient w.r.t. the activated output [clients][P][C]
   const __nv_bfloat16* out;    // activated output (ReLU mask), or null
@@ -148,62 +167,71 @@ struct BnBwdArgs {
   float eps;
 };
 
-// shared: mean[C], rstd[C], (mean2, rstd2)
-__device__ __forceinline__ void bn_bwd_prologue(const BnBwdArgs& a, float* sm, int g) {
-  const float inv_n = 1.f / static_cast<float>(a.P);
-  const float* row = a.slots + g * a.row_stride;
-  for (int c = threadIdx.x; c < a.C; c += 256) {
-    float mean, rstd;
-    bn_coeffs(a.bn, row, g, a.C, c, inv_n, a.eps, mean, rstd);
-    sm[c] = mean;
-    sm[a.C + c] = rstd;
-    if (a.x2) {
-      bn_coeffs(a.bn2, row, g, a.C, c, inv_n, a.eps, mean, rstd);
-      sm[2 * a.C + c] = mean;
-      sm[3 * a.C + c] = rstd;
-    }
-  }
-  __syncthreads();
+// g = dout where the activated output is positive (bf16 > 0  <=>  sign clear and magnitude != 0)
+__device__ __forceinline__ void relu_mask(uint4& d, const uint4& o) {
+  auto m = [](uint32_t dv, uint32_t ov) {
+    const uint32_t lo = ((ov & 0x8000u) == 0u && (ov & 0x7fffu) != 0u) ? 0x0000ffffu : 0u;
+    const uint32_t hi = ((ov & 0x80000000u) == 0u && (ov & 0x7fff0000u) != 0u) ? 0xffff0000u : 0u;
+    return dv & (lo | hi);
+  };
+  d.x = m(d.x, o.x); d.y = m(d.y, o.y); d.z = m(d.z, o.z); d.w = m(d.w, o.w);
 }
 
 template <bool TWO>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdArgs a) {
-  extern __shared__ float sm[];   // [4][C] coefficients, then [256][8] reduction scratch
+  __shared__ float scratch[256 * 8];
   const int g = blockIdx.y, C = a.C, octs = C >> 3;
-  bn_bwd_prologue(a, sm, g);
-  const int oct = threadIdx.x % octs, lane_row = threadIdx.x / octs, rows = 256 / octs;
-  const int c0 = oct * 8;
+  const int oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs, c0 = oct * 8;
+  const float* row = a.slots + g * a.row_stride;
+  const float inv_n = 1.f / static_cast<float>(a.P);
+  float rs[8], mrs[8], rs2[8], mrs2[8];        // xhat = x * rs - mrs
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    float mean, rstd;
+    bn_coeffs(a.bn, row, g, C, c0 + e, inv_n, a.eps, mean, rstd);
+    rs[e] = rstd; mrs[e] = mean * rstd;
+    rs2[e] = mrs2[e] = 0.f;
+    if constexpr (TWO) {
+      bn_coeffs(a.bn2, row, g, C, c0 + e, inv_n, a.eps, mean, rstd);
+      rs2[e] = rstd; mrs2[e] = mean * rstd;
+    }
+  }
   float sg[8], sgx[8], sgx2[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) sg[e] = sgx[e] = sgx2[e] = 0.f;
-  const long long base = static_cast<long long>(g) * a.P * C;
-  if (lane_row < rows) {
-    for (int p = blockIdx.x * rows + lane_row; p < a.P; p += gridDim.x * rows) {
-      const long long off = base + static_cast<long long>(p) * C + c0;
-      float d[8], xv[8];
-      unpack<__nv_bfloat16>(ld_stream(a.dout + off), d);
-      if (a.out) {
-        float o[8];
-        unpack<__nv_bfloat16>(ld_stream(a.out + off), o);
+  const long long base = static_cast<long long>(g) * a.P * C + c0;
+  for (int p0 = blockIdx.x * R * BN_U; p0 < a.P; p0 += gridDim.x * R * BN_U) {
+    uint4 dv[BN_U], xv[BN_U], x2v[BN_U];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) d[e] = o[e] > 0.f ? d[e] : 0.f;
+    for (int u = 0; u < BN_U; ++u) {
+      const int p = p0 + u * R + r;
+      dv[u] = xv[u] = x2v[u] = make_uint4(0, 0, 0, 0);
+      if (p < a.P) {
+        const long long off = base + static_cast<long long>(p) * C;
+        dv[u] = ld_stream(a.dout + off);
+        if (a.out) relu_mask(dv[u], ld_stream(a.out + off));
+        xv[u] = ld_stream(a.x + off);
+        if constexpr (TWO) x2v[u] = ld_stream(a.x2 + off);
       }
-      unpack<__nv_bfloat16>(ld_stream(a.x + off), xv);
+    }
+#pragma unroll
+    for (int u = 0; u < BN_U; ++u) {
+      float d[8], xx[8];
+      unpack<__nv_bfloat16>(dv[u], d);      // rows past the end hold zeros: they add nothing
+      unpack<__nv_bfloat16>(xv[u], xx);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         sg[e] += d[e];
-        sgx[e] = fmaf(d[e], (xv[e] - sm[c0 + e]) * sm[C + c0 + e], sgx[e]);
+        sgx[e] = fmaf(d[e], fmaf(xx[e], rs[e], -mrs[e]), sgx[e]);
       }
       if constexpr (TWO) {
-        unpack<__nv_bfloat16>(ld_stream(a.x2 + off), xv);
+        unpack<__nv_bfloat16>(x2v[u], xx);
 #pragma unroll
-        for (int e = 0; e < 8; ++e)
-          sgx2[e] = fmaf(d[e], (xv[e] - sm[2 * C + c0 + e]) * sm[3 * C + c0 + e], sgx2[e]);
+        for (int e = 0; e < 8; ++e) sgx2[e] = fmaf(d[e], fmaf(xx[e], rs2[e], -mrs2[e]), sgx2[e]);
       }
     }
   }
-  // reduce over the `rows` threads that share a channel octet
-  float* scratch = sm + 4 * C;
+  // reduce over the R threads that share a channel octet, one fp32 atomic per channel and block
   float* grow = a.sgrad + g * a.sgrad_stride;
   for (int pass = 0; pass < (TWO ? 3 : 2); ++pass) {
     const float* src = pass == 0 ? sg : pass == 1 ? sgx : sgx2;
@@ -213,7 +241,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdArgs a) {
     __syncthreads();
     for (int c = threadIdx.x; c < C; c += 256) {
       float t = 0.f;
-      for (int r = 0; r < rows; ++r) t += scratch[(r * octs + (c >> 3)) * 8 + (c & 7)];
+      for (int rr = 0; rr < R; ++rr) t += scratch[(rr * octs + (c >> 3)) * 8 + (c & 7)];
       if (pass == 0) {
         atomicAdd(grow + a.dbeta + c, t);
         if (TWO) atomicAdd(grow + a.dbeta2 + c, t);
@@ -228,55 +256,60 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdArgs a) {
 
 template <bool TWO>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
-  extern __shared__ float sm[];   // mean, rstd, mean2, rstd2 [4][C]; then k1,k2,k3 per branch [6][C]
   const int g = blockIdx.y, C = a.C, octs = C >> 3;
-  bn_bwd_prologue(a, sm, g);
-  float* k = sm + 4 * C;
-  const float inv_n = 1.f / static_cast<float>(a.P);
+  const int oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs, c0 = oct * 8;
   const float* row = a.slots + g * a.row_stride;
   const float* grow = a.sgrad + g * a.sgrad_stride;
-  // dx = s * g - s * dbeta / n - s * xhat * dgamma / n  with s = gamma * rstd
-  for (int c = threadIdx.x; c < C; c += 256) {
-    const float s = row[a.bn.gamma + c] * sm[C + c];
-    k[c] = s;
-    k[C + c] = s * grow[a.dbeta + c] * inv_n;
-    k[2 * C + c] = s * grow[a.dgamma + c] * inv_n;
-    if (TWO) {
-      const float s2 = row[a.bn2.gamma + c] * sm[3 * C + c];
-      k[3 * C + c] = s2;
-      k[4 * C + c] = s2 * grow[a.dbeta2 + c] * inv_n;
-      k[5 * C + c] = s2 * grow[a.dgamma2 + c] * inv_n;
+  const float inv_n = 1.f / static_cast<float>(a.P);
+  // dx = s * (g - dbeta / n - xhat * dgamma / n) = ka * g + kb * x + kc,  s = gamma * rstd
+  float ka[8], kb[8], kc[8], ka2[8], kb2[8], kc2[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int c = c0 + e;
+    float mean, rstd;
+    bn_coeffs(a.bn, row, g, C, c, inv_n, a.eps, mean, rstd);
+    const float s = row[a.bn.gamma + c] * rstd;
+    const float t = s * grow[a.dgamma + c] * inv_n * rstd;
+    ka[e] = s; kb[e] = -t; kc[e] = t * mean - s * grow[a.dbeta + c] * inv_n;
+    ka2[e] = kb2[e] = kc2[e] = 0.f;
+    if constexpr (TWO) {
+      bn_coeffs(a.bn2, row, g, C, c, inv_n, a.eps, mean, rstd);
+      const float s2 = row[a.bn2.gamma + c] * rstd;
+      const float t2 = s2 * grow[a.dgamma2 + c] * inv_n * rstd;
+      ka2[e] = s2; kb2[e] = -t2; kc2[e] = t2 * mean - s2 * grow[a.dbeta2 + c] * inv_n;
     }
   }
-  __syncthreads();
-  const long long total = static_cast<long long>(a.P) * octs;
-  const long long base = static_cast<long long>(g) * a.P * C;
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
-    const int c0 = static_cast<int>(i % octs) * 8;
-    const long long off = base + i * 8;
-    float d[8], xv[8], o[8];
-    unpack<__nv_bfloat16>(ld_stream(a.dout + off), d);
-    if (a.out) {
-      float m[8];
-      unpack<__nv_bfloat16>(ld_stream(a.out + off), m);
+  const long long base = static_cast<long long>(g) * a.P * C + c0;
+  for (int p0 = blockIdx.x * R * BN_U; p0 < a.P; p0 += gridDim.x * R * BN_U) {
+    uint4 dv[BN_U], xv[BN_U], x2v[BN_U];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) d[e] = m[e] > 0.f ? d[e] : 0.f;
-    }
-    unpack<__nv_bfloat16>(ld_stream(a.x + off), xv);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const float xh = (xv[e] - sm[c0 + e]) * sm[C + c0 + e];
-      o[e] = k[c0 + e] * d[e] - k[C + c0 + e] - xh * k[2 * C + c0 + e];
-    }
-    st_vec(a.dx + off, pack<__nv_bfloat16>(o));
-    if constexpr (TWO) {
-      unpack<__nv_bfloat16>(ld_stream(a.x2 + off), xv);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float xh = (xv[e] - sm[2 * C + c0 + e]) * sm[3 * C + c0 + e];
-        o[e] = k[3 * C + c0 + e] * d[e] - k[4 * C + c0 + e] - xh * k[5 * C + c0 + e];
+    for (int u = 0; u < BN_U; ++u) {
+      const int p = p0 + u * R + r;
+      if (p < a.P) {
+        const long long off = base + static_cast<long long>(p) * C;
+        dv[u] = ld_stream(a.dout + off);
+        if (a.out) relu_mask(dv[u], ld_stream(a.out + off));
+        xv[u] = ld_stream(a.x + off);
+        if constexpr (TWO) x2v[u] = ld_stream(a.x2 + off);
       }
-      st_vec(a.dx2 + off, pack<__nv_bfloat16>(o));
+    }
+#pragma unroll
+    for (int u = 0; u < BN_U; ++u) {
+      const int p = p0 + u * R + r;
+      if (p >= a.P) continue;
+      const long long off = base + static_cast<long long>(p) * C;
+      float d[8], xx[8], o[8];
+      unpack<__nv_bfloat16>(dv[u], d);
+      unpack<__nv_bfloat16>(xv[u], xx);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = fmaf(ka[e], d[e], fmaf(kb[e], xx[e], kc[e]));
+      st_vec(a.dx + off, pack<__nv_bfloat16>(o));
+      if constexpr (TWO) {
+        unpack<__nv_bfloat16>(x2v[u], xx);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = fmaf(ka2[e], d[e], fmaf(kb2[e], xx[e], kc2[e]));
+        st_vec(a.dx2 + off, pack<__nv_bfloat16>(o));
+      }
     }
   }
 }
@@ -375,15 +408,15 @@ struct ConvEntry {            // one convolution in the conv_sgd table (device m
   int cout, cin, taps, stem;  // stem: cin == 64 patch entries, only 27 real (k = tap*3 + ci)
 };
 
+// dir 0: client rows (torch layout [co][ci][kh][kw]) -> fp32 tap-major master wm + bf16 copy wt
+// dir 1: wm -> client rows.  Once per round each; local steps work on the tap-major copies only.
 __global__ void __launch_bounds__(256)
-    conv_sgd_kernel(const ConvEntry* __restrict__ table, int n_layers, long long total_cols,
-                    float* __restrict__ slots, long long row_stride, float* __restrict__ momentum,
-                    float* __restrict__ dwt, __nv_bfloat16* __restrict__ wt, long long t_stride,
-                    float lr, float mu, float wd, int use_grad) {
+    wm_convert_kernel(const ConvEntry* __restrict__ table, int n_layers, long long total_cols,
+                      float* __restrict__ slots, long long row_stride, float* __restrict__ wm,
+                      __nv_bfloat16* __restrict__ wt, long long t_stride, int dir) {
   const int g = blockIdx.y;
   float* row = slots + g * row_stride;
-  float* mrow = momentum ? momentum + g * row_stride : nullptr;
-  float* grow = dwt + g * t_stride;
+  float* mrow = wm + g * t_stride;
   __nv_bfloat16* trow = wt + g * t_stride;
   for (long long col = blockIdx.x * 256ll + threadIdx.x; col < total_cols; col += gridDim.x * 256ll) {
     int l = 0;
@@ -393,32 +426,54 @@ __global__ void __launch_bounds__(256)
     const int co = static_cast<int>(local / e.cin), ci = static_cast<int>(local % e.cin);
     if (e.stem) {
       const long long ti = e.t_off + static_cast<long long>(co) * e.cin + ci;
-      if (ci >= 27) { trow[ti] = __float2bfloat16_rn(0.f); grow[ti] = 0.f; continue; }
-      const long long wi = e.w_off + (static_cast<long long>(co) * 3 + ci % 3) * 9 + ci / 3;
-      float w = row[wi];
-      if (use_grad) {
-        float gr = fmaf(wd, w, grow[ti]);
-        if (mrow) { gr = fmaf(mu, mrow[wi], gr); mrow[wi] = gr; }
-        w = fmaf(-lr, gr, w);
-        row[wi] = w;
-        grow[ti] = 0.f;
+      if (ci >= 27) {
+        if (dir == 0) { mrow[ti] = 0.f; trow[ti] = __float2bfloat16_rn(0.f); }
+        continue;
       }
-      trow[ti] = __float2bfloat16_rn(w);
+      const long long wi = e.w_off + (static_cast<long long>(co) * 3 + ci % 3) * 9 + ci / 3;
+      if (dir == 0) { const float w = row[wi]; mrow[ti] = w; trow[ti] = __float2bfloat16_rn(w); }
+      else row[wi] = mrow[ti];
       continue;
     }
     const long long wi0 = e.w_off + local * e.taps;
     for (int t = 0; t < e.taps; ++t) {
       const long long ti = e.t_off + (static_cast<long long>(t) * e.cout + co) * e.cin + ci;
-      float w = row[wi0 + t];
-      if (use_grad) {
-        float gr = fmaf(wd, w, grow[ti]);
-        if (mrow) { gr = fmaf(mu, mrow[wi0 + t], gr); mrow[wi0 + t] = gr; }
-        w = fmaf(-lr, gr, w);
-        row[wi0 + t] = w;
-        grow[ti] = 0.f;
-      }
-      trow[ti] = __float2bfloat16_rn(w);
+      if (dir == 0) { const float w = row[wi0 + t]; mrow[ti] = w; trow[ti] = __float2bfloat16_rn(w); }
+      else row[wi0 + t] = mrow[ti];
     }
+  }
+}
+
+// SGD on tap-major ranges: w -= lr * (mu * v + g + wd * w), wt = bf16(w), g = 0.  Used for the
+// convolutions whose weight gradient was accumulated with atomics (split-K) or when momentum is on;
+// the others are updated inside the wgrad epilogue (csrc/rn_conv.cu).
+struct TapRange { long long t_off, len; };
+
+__global__ void __launch_bounds__(256)
+    tap_sgd_kernel(const TapRange* __restrict__ ranges, float* __restrict__ wm,
+                   float* __restrict__ dwt, float* __restrict__ mom, __nv_bfloat16* __restrict__ wt,
+                   long long t_stride, float lr, float mu, float wd) {
+  const TapRange rg = ranges[blockIdx.y];
+  const long long base = blockIdx.z * t_stride + rg.t_off;
+  for (long long i = (blockIdx.x * 256ll + threadIdx.x) * 4; i < rg.len; i += gridDim.x * 1024ll) {
+    float4 w = *reinterpret_cast<float4*>(wm + base + i);
+    const float4 gr = *reinterpret_cast<const float4*>(dwt + base + i);
+    float d[4] = {fmaf(wd, w.x, gr.x), fmaf(wd, w.y, gr.y), fmaf(wd, w.z, gr.z), fmaf(wd, w.w, gr.w)};
+    if (mom) {
+      float4 v = *reinterpret_cast<float4*>(mom + base + i);
+      d[0] = fmaf(mu, v.x, d[0]); d[1] = fmaf(mu, v.y, d[1]);
+      d[2] = fmaf(mu, v.z, d[2]); d[3] = fmaf(mu, v.w, d[3]);
+      *reinterpret_cast<float4*>(mom + base + i) = make_float4(d[0], d[1], d[2], d[3]);
+    }
+    w.x = fmaf(-lr, d[0], w.x); w.y = fmaf(-lr, d[1], w.y);
+    w.z = fmaf(-lr, d[2], w.z); w.w = fmaf(-lr, d[3], w.w);
+    *reinterpret_cast<float4*>(wm + base + i) = w;
+    *reinterpret_cast<float4*>(dwt + base + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(w.x, w.y), hi = __floats2bfloat162_rn(w.z, w.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(wt + base + i) = pk;
   }
 }
 
@@ -427,9 +482,14 @@ struct SmallEntry { long long p_off, g_off, len; };
 __global__ void __launch_bounds__(256)
     small_sgd_kernel(const SmallEntry* __restrict__ table, float* __restrict__ slots,
                      long long row_stride, float* __restrict__ momentum, float* __restrict__ sgrad,
-                     long long sgrad_stride, float lr, float mu, float wd) {
+                     long long sgrad_stride, float lr, float mu, float wd,
+                     float* __restrict__ zero_ptr, long long zero_len) {
   const SmallEntry e = table[blockIdx.x];
   const int g = blockIdx.y;
+  // the BatchNorm batch sums of this step have been consumed: hand them back zeroed
+  for (long long i = (static_cast<long long>(g) * gridDim.x + blockIdx.x) * 256 + threadIdx.x;
+       i < zero_len; i += 256ll * gridDim.x * gridDim.y)
+    zero_ptr[i] = 0.f;
   float* p = slots + g * row_stride + e.p_off;
   float* m = momentum ? momentum + g * row_stride + e.p_off : nullptr;
   float* gr = sgrad + g * sgrad_stride + e.g_off;
@@ -485,8 +545,12 @@ int nfb_rn_bn_apply(const void* x, const void* res, void* y, float* slots, long 
     a.bn_res = bn_ref(res_stats, res_offs);
   }
   a.P = P; a.C = C; a.relu = relu; a.eps = eps; a.momentum = momentum;
-  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8, clients), clients);
-  rn::bn_apply_kernel<<<grid, 256, 4 * C * sizeof(float), as_stream(stream)>>>(a);
+  NFB_REQUIRE(256 % (C / 8) == 0, NFB_EINVAL, "rn_bn_apply: C / 8 must divide 256");
+  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / rn::BN_U, clients), clients);
+  cudaStream_t st = as_stream(stream);
+  if (!res) rn::bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(a);
+  else if (!res_stats) rn::bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(a);
+  else rn::bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(a);
   return launch_status("rn_bn_apply");
 }
 
@@ -515,17 +579,15 @@ int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, c
   a.P = P; a.C = C; a.eps = eps;
   cudaStream_t st = as_stream(stream);
   if (!apply) {
-    const int rows = 256 / (C / 8);
-    dim3 grid(rn::blocks_for(static_cast<long long>(P) * 256 / rows / 4, clients), clients);
-    const size_t sm = (4 * C + 256 * 8) * sizeof(float);
-    if (x2) rn::bn_bwd_reduce_kernel<true><<<grid, 256, sm, st>>>(a);
-    else rn::bn_bwd_reduce_kernel<false><<<grid, 256, sm, st>>>(a);
+    // fewer, longer blocks: every block ends with C atomics per sum
+    dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / (4 * rn::BN_U), clients), clients);
+    if (x2) rn::bn_bwd_reduce_kernel<true><<<grid, 256, 0, st>>>(a);
+    else rn::bn_bwd_reduce_kernel<false><<<grid, 256, 0, st>>>(a);
     return launch_status("rn_bn_bwd_reduce");
   }
-  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8, clients), clients);
-  const size_t sm = 10 * C * sizeof(float);
-  if (x2) rn::bn_bwd_apply_kernel<true><<<grid, 256, sm, st>>>(a);
-  else rn::bn_bwd_apply_kernel<false><<<grid, 256, sm, st>>>(a);
+  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / rn::BN_U, clients), clients);
+  if (x2) rn::bn_bwd_apply_kernel<true><<<grid, 256, 0, st>>>(a);
+  else rn::bn_bwd_apply_kernel<false><<<grid, 256, 0, st>>>(a);
   return launch_status("rn_bn_bwd_apply");
 }
 
@@ -543,27 +605,42 @@ int nfb_rn_head(const void* feat, int clients, int batch, int positions, const i
   return launch_status("rn_head");
 }
 
-int nfb_rn_conv_sgd(const void* table, int n_layers, long long total_cols, float* slots,
-                    long long row_stride, float* momentum, float* dwt, void* wt, long long t_stride,
-                    int clients, float lr, float mu, float wd, int use_grad, void* stream) {
+int nfb_rn_wm_convert(const void* table, int n_layers, long long total_cols, float* slots,
+                      long long row_stride, float* wm, void* wt, long long t_stride, int clients,
+                      int to_slots, void* stream) {
   using namespace nfb;
-  NFB_REQUIRE(table && slots && dwt && wt && n_layers >= 1, NFB_EINVAL, "rn_conv_sgd: null pointer");
+  NFB_REQUIRE(table && slots && wm && wt && n_layers >= 1, NFB_EINVAL, "rn_wm_convert: null pointer");
   dim3 grid(rn::blocks_for(total_cols, clients), clients);
-  rn::conv_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
-      static_cast<const rn::ConvEntry*>(table), n_layers, total_cols, slots, row_stride, momentum,
-      dwt, static_cast<__nv_bfloat16*>(wt), t_stride, lr, mu, wd, use_grad);
-  return launch_status("rn_conv_sgd");
+  rn::wm_convert_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      static_cast<const rn::ConvEntry*>(table), n_layers, total_cols, slots, row_stride, wm,
+      static_cast<__nv_bfloat16*>(wt), t_stride, to_slots);
+  return launch_status("rn_wm_convert");
+}
+
+int nfb_rn_tap_sgd(const void* ranges, int n_ranges, long long max_len, float* wm, float* dwt,
+                   float* momentum, void* wt, long long t_stride, int clients, float lr, float mu,
+                   float wd, void* stream) {
+  using namespace nfb;
+  NFB_REQUIRE(ranges && wm && dwt && wt && n_ranges >= 1, NFB_EINVAL, "rn_tap_sgd: null pointer");
+  const int per = (4 * sm_count() + n_ranges * clients - 1) / (n_ranges * clients);
+  long long want = (max_len / 4 + 255) / 256;
+  if (want > per) want = per;
+  dim3 grid(static_cast<unsigned>(want < 1 ? 1 : want), n_ranges, clients);
+  rn::tap_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      static_cast<const rn::TapRange*>(ranges), wm, dwt, momentum, static_cast<__nv_bfloat16*>(wt),
+      t_stride, lr, mu, wd);
+  return launch_status("rn_tap_sgd");
 }
 
 int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long row_stride,
                      float* momentum, float* sgrad, long long sgrad_stride, int clients, float lr,
-                     float mu, float wd, void* stream) {
+                     float mu, float wd, float* zero_ptr, long long zero_len, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(table && slots && sgrad && n_entries >= 1, NFB_EINVAL, "rn_small_sgd: null pointer");
   dim3 grid(n_entries, clients);
   rn::small_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
       static_cast<const rn::SmallEntry*>(table), slots, row_stride, momentum, sgrad, sgrad_stride,
-      lr, mu, wd);
+      lr, mu, wd, zero_ptr, zero_ptr ? zero_len : 0);
   return launch_status("rn_small_sgd");
 }
 

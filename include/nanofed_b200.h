@@ -317,10 +317,13 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
                      int out_ph, int out_pw, float* stats, const void* residual,
                      const void* res_mask, int bn_tile, int halves, int* status, void* stream);
 /* out[client][tap][co][ci] (+)= sum_pos x[pos + tap][ci] * dy[pos][co]; k_split > 1 adds with fp32
- * atomics (the target must then be zero).                                                     */
+ * atomics (the target must then be zero).  With k_split == 1 and sgd_w != NULL the gradient is not
+ * written at all: the epilogue applies w -= lr * (dW + wd * w) to the tap-major fp32 master sgd_w
+ * (same layout and client stride as out) and refreshes the bf16 copy sgd_wt.                  */
 int nfb_rn_conv_wgrad(const nfb_rn_act* x, const nfb_rn_act* dy, int clients, int imgs_per_client,
                       int n_taps, const int* taps, float* out, long long out_gs, int k_split,
-                      int bn_tile, int posk, int* status, void* stream);
+                      int bn_tile, int posk, float* sgd_w, void* sgd_wt, float lr, float wd,
+                      int* status, void* stream);
 int nfb_rn_im2col3(const float* x, long long x_gs, int clients, int batch, void* out, void* stream);
 /* bn_offs / res_offs: {weight, bias, running_mean, running_var, num_batches_tracked} offsets in a
  * client's fp32 row; stats as written by nfb_rn_conv_gemm.                                    */
@@ -338,12 +341,17 @@ int nfb_rn_head(const void* feat, int clients, int batch, int positions, const i
                 long long label_gs, const float* slots, long long row_stride, long long w_off,
                 long long b_off, float* sgrad, long long sgrad_stride, long long dw_off,
                 long long db_off, void* dfeat, float* stats, void* stream);
-int nfb_rn_conv_sgd(const void* table, int n_layers, long long total_cols, float* slots,
-                    long long row_stride, float* momentum, float* dwt, void* wt, long long t_stride,
-                    int clients, float lr, float mu, float wd, int use_grad, void* stream);
+/* conv weights: arena rows (torch layout) <-> tap-major fp32 master wm + bf16 copy wt.       */
+int nfb_rn_wm_convert(const void* table, int n_layers, long long total_cols, float* slots,
+                      long long row_stride, float* wm, void* wt, long long t_stride, int clients,
+                      int to_slots, void* stream);
+/* ranges: n_ranges x {t_off, len} (int64, device, len % 4 == 0).                              */
+int nfb_rn_tap_sgd(const void* ranges, int n_ranges, long long max_len, float* wm, float* dwt,
+                   float* momentum, void* wt, long long t_stride, int clients, float lr, float mu,
+                   float wd, void* stream);
 int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long row_stride,
                      float* momentum, float* sgrad, long long sgrad_stride, int clients, float lr,
-                     float mu, float wd, void* stream);
+                     float mu, float wd, float* zero_ptr, long long zero_len, void* stream);
 
 #ifdef __cplusplus
 }

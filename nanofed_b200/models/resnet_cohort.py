@@ -11,8 +11,11 @@ whatever the client count, and a local epoch is one CUDA graph.  No autograd, no
               per conv: wgrad (tcgen05, both operands MN-major, tap-major fp32 result) and dgrad
               (tcgen05; stride 2 = four parity-class launches, the 1×1 projection's gradient rides
               in the k-loop of class (0,0); identity shortcuts are added in the dgrad epilogue)
-    update    SGD on the fp32 master weights from the tap-major gradients, which also writes the
-              bf16 tap-major working copy of the next step
+    update    conv weights live in a tap-major fp32 master + bf16 working copy during local
+              training (converted from / to the arena's torch layout once per round); where the
+              weight gradient is complete in one CTA (94 % of the parameters) SGD is applied in the
+              wgrad epilogue and the gradient is never written; split-K layers, BatchNorm and the
+              classifier take two small elementwise launches
 
 Activations are bf16 NHWC, accumulation / BatchNorm statistics / master weights fp32.  BatchNorm
 running statistics and ``num_batches_tracked`` are updated in the client's arena row, so FedAvg
@@ -140,7 +143,9 @@ class ResNetCohortNet:
         f32 = dict(dtype=torch.float32, device=dev)
         bf = dict(dtype=torch.bfloat16, device=dev)
         self.wt = torch.zeros(g, self.t_stride, **bf)       # tap-major bf16 weights
-        self.dwt = torch.zeros(g, self.t_stride, **f32)     # tap-major fp32 gradients
+        self.wm = torch.zeros(g, self.t_stride, **f32)      # tap-major fp32 master weights
+        self.dwt = torch.zeros(g, self.t_stride, **f32)     # tap-major fp32 gradients (split-K layers)
+        self.mom = torch.zeros(g, self.t_stride, **f32) if cfg.momentum != 0.0 else None
         self.sgrad = torch.zeros(g, g_cursor, **f32)        # BatchNorm / classifier gradients
         self.stats = torch.zeros(s_cursor, **f32)           # BatchNorm batch sums
         cols, rows = 0, []
@@ -166,6 +171,14 @@ class ResNetCohortNet:
         self._graph: "torch.cuda.CUDAGraph | None" = None
         self.launches_per_round = 0
         self.sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        # which convolutions get their SGD step inside the wgrad epilogue (complete gradient in one
+        # CTA, momentum-free); the others go through dwt + tap_sgd
+        self.fuse_sgd = cfg.momentum == 0.0 and os.environ.get("NFB_RN_NO_FUSED_SGD") is None
+        self._ksplit = {c.name: self._pick_ksplit(c) for c in self.convs}
+        ranges = [(c.t_off, c.taps * c.cout * c.cin) for c in self.convs
+                  if not (self.fuse_sgd and self._ksplit[c.name] == 1)]
+        self.tap_ranges = torch.tensor(ranges or [(0, 0)], dtype=torch.int64, device=dev)
+        self.tap_max = max((r[1] for r in ranges), default=0)
         self._tile_override = os.environ.get("NFB_RN_TILE")   # "bn,halves" for experiments
 
     # ---- helpers ---------------------------------------------------------------------------
@@ -192,14 +205,23 @@ class ResNetCohortNet:
                      stats=self._bn_stats(n), n_out=c.cout,
                      tile=self._tile(self.b * c.hout * c.hout, c.cout))
 
-    def _wgrad(self, c: _Conv, x: torch.Tensor, dy: torch.Tensor) -> None:
+    def _pick_ksplit(self, c: _Conv) -> int:
         bn = min(c.cout, 256)
         kb_total = self.b * c.hout * c.hout // 128
         tiles = (c.taps * (c.cin // 64) + 1) // 2 * (c.cout // bn) * self.g
-        k_split = max(1, min(kb_total // 4 if kb_total >= 4 else 1, -(-self.sms // tiles)))
+        if tiles * 2 > self.sms:          # at least half a wave without splitting: keep K whole
+            return 1
+        return max(1, min(kb_total // 4 if kb_total >= 4 else 1, self.sms // tiles))
+
+    def _wgrad(self, c: _Conv, x: torch.Tensor, dy: torch.Tensor) -> None:
+        """Weight gradient of ``c`` — call AFTER the data gradient that reads the old weights."""
+        k_split = self._ksplit[c.name]
+        cfg = self.cfg
+        sgd = ((self.wm, self.wt, cfg.learning_rate, cfg.weight_decay)
+               if self.fuse_sgd and k_split == 1 else None)
         rn.conv_wgrad(x, dy, self.dwt, c.t_off, clients=self.g,
                       taps=rn.fwd_taps(c.k, c.stride, c.cout), x_parity=c.stride == 2,
-                      k_split=k_split, tile=(bn, 128))
+                      k_split=k_split, tile=(min(c.cout, 256), 128), sgd=sgd)
 
     def _dgrad(self, c: _Conv, dy: torch.Tensor, dx: torch.Tensor, *, residual=None, res_mask=None,
                sc: _Conv | None = None, dy_sc: torch.Tensor | None = None) -> None:
@@ -220,12 +242,15 @@ class ResNetCohortNet:
     # ---- hooks used by FedSimulation ---------------------------------------------------------
     def after_broadcast(self) -> None:
         """Fresh global weights arrived in the client rows: rebuild the bf16 tap-major copies."""
-        a = self.arena
-        rn.conv_sgd(self.conv_table, len(self.convs), self.total_cols, a.slots, None, self.dwt,
-                    self.wt, lr=0.0, mu=0.0, wd=0.0, use_grad=False)
+        rn.wm_convert(self.conv_table, len(self.convs), self.total_cols, self.arena.slots, self.wm,
+                      self.wt, to_slots=False)
+        if self.mom is not None:
+            self.mom.zero_()             # fresh optimizer per round, like K-BCAST does for the arena
 
     def before_aggregate(self) -> None:
-        pass
+        """Trained conv weights back into the client rows (torch layout) that K-AGG reads."""
+        rn.wm_convert(self.conv_table, len(self.convs), self.total_cols, self.arena.slots, self.wm,
+                      self.wt, to_slots=True)
 
     # ---- one local step for every client -------------------------------------------------------
     def step(self, step: int) -> None:
@@ -278,22 +303,22 @@ class ResNetCohortNet:
                       self._bn_stats(blk.bn2), blk.bn2.offs, **kw)
             rn.bn_bwd(True, dout, u["out"], u["raw2"], slots, self.sgrad, offs,
                       self._bn_stats(blk.bn2), blk.bn2.offs, dx=dc2, dx2=dcs, **kw)
-            self._wgrad(blk.conv2, u["a"], dc2)
             da = self._view(4, ho, w)
-            self._dgrad(blk.conv2, dc2, da)
+            self._dgrad(blk.conv2, dc2, da)               # reads the old weights: before the wgrad
+            self._wgrad(blk.conv2, u["a"], dc2)
             dc1 = dc2                                     # dc2 is dead after the two launches above
             offs1 = (blk.bn1.g_off[0], blk.bn1.g_off[1], 0, 0)
             rn.bn_bwd(False, da, u["a"], u["raw1"], slots, self.sgrad, offs1,
                       self._bn_stats(blk.bn1), blk.bn1.offs, clients=g)
             rn.bn_bwd(True, da, u["a"], u["raw1"], slots, self.sgrad, offs1,
                       self._bn_stats(blk.bn1), blk.bn1.offs, clients=g, dx=dc1)
-            self._wgrad(blk.conv1, u["in"], dc1)
             dx = self._view(d1, hin, cin)
             if proj:
-                self._wgrad(blk.conv_sc, u["in"], dcs)
                 self._dgrad(blk.conv1, dc1, dx, sc=blk.conv_sc, dy_sc=dcs)
+                self._wgrad(blk.conv_sc, u["in"], dcs)
             else:
                 self._dgrad(blk.conv1, dc1, dx, residual=dout, res_mask=u["out"])
+            self._wgrad(blk.conv1, u["in"], dc1)
             d0, d1 = d1, d0
         dout = self._view(d0, 32, 64)
         dc0 = self._view(2, 32, 64)
@@ -304,12 +329,11 @@ class ResNetCohortNet:
                   self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g, dx=dc0)
         self._wgrad(self.stem, self.xcol, dc0)
         # ---------------- update ----------------
-        rn.conv_sgd(self.conv_table, len(self.convs), self.total_cols, slots, a.momentum, self.dwt,
-                    self.wt, lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay,
-                    use_grad=True)
+        if self.tap_max:
+            rn.tap_sgd(self.tap_ranges, self.tap_max, self.wm, self.dwt, self.mom, self.wt,
+                       lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay)
         rn.small_sgd(self.small_table, self.n_small, slots, a.momentum, self.sgrad,
-                     lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay)
-        self.stats.zero_()
+                     lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay, zero=self.stats)
 
     def _all_steps(self) -> None:
         for s in range(self.cfg.local_steps):
@@ -325,15 +349,19 @@ class ResNetCohortNet:
 
     def _capture(self) -> None:
         a = self.arena
-        keep = (a.slots.clone(), a.stats.clone(), self.wt.clone(),
-                None if a.momentum is None else a.momentum.clone())
+        keep = (a.slots.clone(), a.stats.clone(), self.wt.clone(), self.wm.clone(),
+                None if a.momentum is None else a.momentum.clone(),
+                None if self.mom is None else self.mom.clone())
 
         def restore() -> None:
             a.slots.copy_(keep[0])
             a.stats.copy_(keep[1])
             self.wt.copy_(keep[2])
-            if keep[3] is not None:
-                a.momentum.copy_(keep[3])
+            self.wm.copy_(keep[3])
+            if keep[4] is not None:
+                a.momentum.copy_(keep[4])
+            if keep[5] is not None:
+                self.mom.copy_(keep[5])
 
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))

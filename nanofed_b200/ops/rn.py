@@ -3,7 +3,7 @@ kernels of the ResNet cohort engine (``csrc/rn_conv.cu``, ``csrc/rn_elt.cu``).
 
 Conventions: activations are bf16 NHWC ``[clients·batch, H, W, C]`` (C a multiple of 64);
 convolution weights live per client in tap-major bf16 rows ``wt[client][t_off + (tap·Cout + co)·Cin
-+ ci]`` (written by ``conv_sgd``), weight gradients in the same layout in fp32.
++ ci]`` (written by ``wm_convert`` / the SGD kernels), weight gradients in the same layout in fp32.
 
 Replaces (reference): the torch library calls a ResNet-18 makes inside
 ``nanofed/trainer/base.py:134-160`` (``model(data)``, ``loss.backward()``, ``optimizer.step()``).
@@ -37,14 +37,16 @@ def _lib() -> C.CDLL:
         sigs = {
             "nfb_rn_conv_gemm": [i32, pa, pa, vp, vp, pi, i32, i32, i32, i32, i32, i32, pi, pa, i32,
                                  i32, vp, vp, vp, i32, i32, vp, vp],
-            "nfb_rn_conv_wgrad": [pa, pa, i32, i32, i32, pi, vp, ll, i32, i32, i32, vp, vp],
+            "nfb_rn_conv_wgrad": [pa, pa, i32, i32, i32, pi, vp, ll, i32, i32, i32, vp, vp, f32, f32,
+                                  vp, vp],
             "nfb_rn_im2col3": [vp, ll, i32, i32, vp, vp],
             "nfb_rn_bn_apply": [vp, vp, vp, vp, ll, vp, pll, vp, pll, i32, i32, i32, i32, f32, f32, vp],
             "nfb_rn_bn_bwd": [i32, vp, vp, vp, vp, vp, vp, vp, ll, vp, ll, pll, vp, pll, vp, pll,
                               i32, i32, i32, f32, vp],
             "nfb_rn_head": [vp, i32, i32, i32, vp, ll, vp, ll, ll, ll, vp, ll, ll, ll, vp, vp, vp],
-            "nfb_rn_conv_sgd": [vp, i32, ll, vp, ll, vp, vp, vp, ll, i32, f32, f32, f32, i32, vp],
-            "nfb_rn_small_sgd": [vp, i32, vp, ll, vp, vp, ll, i32, f32, f32, f32, vp],
+            "nfb_rn_wm_convert": [vp, i32, ll, vp, ll, vp, vp, ll, i32, i32, vp],
+            "nfb_rn_tap_sgd": [vp, i32, ll, vp, vp, vp, vp, ll, i32, f32, f32, f32, vp],
+            "nfb_rn_small_sgd": [vp, i32, vp, ll, vp, vp, ll, i32, f32, f32, f32, vp, ll, vp],
         }
         for name, args in sigs.items():
             fn = getattr(lib, name)
@@ -186,17 +188,28 @@ def conv_gemm(
 
 def conv_wgrad(x: torch.Tensor, dy: torch.Tensor, dwt: torch.Tensor, t_off: int, *, clients: int,
                taps: list[tuple[int, ...]], x_parity: bool = False, k_split: int = 1,
-               tile: tuple[int, int] | None = None) -> None:
-    """``dwt[client][t_off + (tap·Cout + co)·Cin + ci] (+)= Σ_pos x[pos + tap, ci] · dy[pos, co]``."""
+               tile: tuple[int, int] | None = None,
+               sgd: tuple[torch.Tensor, torch.Tensor, float, float] | None = None) -> None:
+    """``dwt[client][t_off + (tap·Cout + co)·Cin + ci] (+)= Σ_pos x[pos + tap, ci] · dy[pos, co]``.
+
+    ``sgd=(wm, wt, lr, wd)`` (needs ``k_split == 1``): the gradient is applied to the tap-major
+    fp32 master ``wm`` / bf16 copy ``wt`` inside the epilogue instead of being written."""
     lib = _lib()
     imgs = dy.shape[0] // clients
     cout = dy.shape[3]
     bn, posk = tile or (min(cout, 256), 128)
     st = status_word(x.device)
     xa, dya = _act(x, x_parity), _act(dy)
+    wm_ptr = wt_ptr = None
+    lr = wd = 0.0
+    if sgd is not None:
+        wm, wt, lr, wd = sgd
+        assert wm.stride(0) == dwt.stride(0) == wt.stride(0)
+        wm_ptr, wt_ptr = wm.data_ptr() + 4 * t_off, wt.data_ptr() + 2 * t_off
     code = lib.nfb_rn_conv_wgrad(C.byref(xa), C.byref(dya), clients, imgs, len(taps),
                                  _tap_array(taps), dwt.data_ptr() + 4 * t_off, dwt.stride(0),
-                                 k_split, bn, posk, st.data_ptr(), _stream(x))
+                                 k_split, bn, posk, wm_ptr, wt_ptr, lr, wd, st.data_ptr(),
+                                 _stream(x))
     _check(code, "rn_conv_wgrad")
 
 
@@ -243,17 +256,25 @@ def head(feat, labels, slots, w_off, b_off, sgrad, dw_off, db_off, dfeat, stats,
         "rn_head")
 
 
-def conv_sgd(table: torch.Tensor, n_layers: int, total_cols: int, slots, momentum, dwt, wt, *,
-             lr: float, mu: float, wd: float, use_grad: bool) -> None:
-    _check(_lib().nfb_rn_conv_sgd(
-        table.data_ptr(), n_layers, total_cols, slots.data_ptr(), slots.stride(0), _ptr(momentum),
-        dwt.data_ptr(), wt.data_ptr(), wt.stride(0), slots.shape[0], lr, mu, wd,
-        1 if use_grad else 0, _stream(slots)), "rn_conv_sgd")
+def wm_convert(table: torch.Tensor, n_layers: int, total_cols: int, slots, wm, wt, *,
+               to_slots: bool) -> None:
+    """Conv weights: arena rows (torch layout) → tap-major ``wm`` / ``wt``, or ``wm`` → arena rows."""
+    _check(_lib().nfb_rn_wm_convert(
+        table.data_ptr(), n_layers, total_cols, slots.data_ptr(), slots.stride(0), wm.data_ptr(),
+        wt.data_ptr(), wt.stride(0), slots.shape[0], 1 if to_slots else 0, _stream(slots)),
+        "rn_wm_convert")
+
+
+def tap_sgd(ranges: torch.Tensor, max_len: int, wm, dwt, momentum, wt, *, lr: float, mu: float,
+            wd: float) -> None:
+    _check(_lib().nfb_rn_tap_sgd(
+        ranges.data_ptr(), ranges.shape[0], max_len, wm.data_ptr(), dwt.data_ptr(), _ptr(momentum),
+        wt.data_ptr(), wt.stride(0), wm.shape[0], lr, mu, wd, _stream(wm)), "rn_tap_sgd")
 
 
 def small_sgd(table: torch.Tensor, n_entries: int, slots, momentum, sgrad, *, lr: float, mu: float,
-              wd: float) -> None:
+              wd: float, zero: torch.Tensor | None = None) -> None:
     _check(_lib().nfb_rn_small_sgd(
         table.data_ptr(), n_entries, slots.data_ptr(), slots.stride(0), _ptr(momentum),
-        sgrad.data_ptr(), sgrad.stride(0), slots.shape[0], lr, mu, wd, _stream(slots)),
-        "rn_small_sgd")
+        sgrad.data_ptr(), sgrad.stride(0), slots.shape[0], lr, mu, wd, _ptr(zero),
+        0 if zero is None else zero.numel(), _stream(slots)), "rn_small_sgd")

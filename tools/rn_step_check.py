@@ -57,6 +57,7 @@ def run(clients: int, batch: int, steps: int, verbose: bool = True) -> dict:
     before = sim.layout.unflatten(a.slots[0].clone())
     for s in range(steps):
         sim.engine.step(s)
+    sim.engine.before_aggregate()
     torch.cuda.synchronize()
     tc.check_status(sim.device)
     worst = {"cos_min": 1.0, "rel_max": 0.0, "ref_rel_max": 0.0, "loss_err": 0.0, "stat_rel": 0.0}
@@ -100,7 +101,10 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=1)
     args = ap.parse_args()
     w = run(args.clients, args.batch, args.steps)
-    ok = w["cos_min"] > 0.98 and w["loss_err"] < 2e-2 and w["stat_rel"] < 2e-2
+    # a bf16-activation engine cannot be closer to fp32 than bf16 allows: the bar for the parameter
+    # updates is PyTorch's own bf16 autocast run of the same step (+30 % head room)
+    ok = (w["loss_err"] < 5e-3 and w["stat_rel"] < 1e-2
+          and w["rel_max"] <= 1.3 * w["ref_rel_max"] + 1e-3)
     print("STEP OK" if ok else "STEP MISMATCH")
     return 0 if ok else 1
 
