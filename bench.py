@@ -49,7 +49,8 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--engine", default="auto", help="auto | grouped | autograd")
     ap.add_argument("--transport", default="peer", help="peer | nccl (baseline)")
-    ap.add_argument("--clients-per-gpu", type=int, default=CLIENTS_PER_GPU)
+    ap.add_argument("--clients-per-gpu", type=int, default=None,
+                    help="default: 32 (mnist_cnn), 8 (resnet18: 64 clients on 8 GPUs)")
     ap.add_argument("--samples-per-client", type=int, default=SAMPLES_PER_CLIENT)
     ap.add_argument("--model", default="mnist_cnn")
     ap.add_argument("--dtype", default="bf16")
@@ -59,7 +60,10 @@ def parse() -> argparse.Namespace:
                     help="client streams of the generic autograd engine (ResNet configs)")
     ap.add_argument("--no-channels-last", action="store_true",
                     help="generic autograd engine: keep NCHW inputs (NHWC is the default)")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.clients_per_gpu is None:
+        args.clients_per_gpu = CLIENTS_PER_GPU if args.model == "mnist_cnn" else 8
+    return args
 
 
 # ---------------------------------------------------------------------------
