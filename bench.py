@@ -161,6 +161,39 @@ def run_ours(args: argparse.Namespace) -> None:
     warmup = max(args.warmup, 3)
     steps = max(args.steps, 1)
 
+    # ---- multi-GPU correctness, visible to the driver: one aggregation of per-rank random client
+    # rows through the fused peer kernel AND through the NCCL baseline (torch partial sum +
+    # all_reduce); the largest element-wise difference goes into the JSON line and a difference
+    # above 1e-5 fails the run (a wrong shard boundary at G = 8 would show up here)
+    agg_parity = None
+    if sim.reducer is not None and type(sim.reducer).__name__ == "PeerReducer":
+        import copy
+
+        from nanofed_b200.parallel.peer import NcclReducer
+
+        a = sim.arena
+        keep = (a.master.clone(), a.master_lowp.clone())
+        gen = torch.Generator(device=dev).manual_seed(4242 + rank.rank)
+        a.slots.copy_(torch.randn(a.slots.shape, device=dev, generator=gen))
+        sim.reducer.reduce(a)
+        torch.cuda.synchronize(dev)
+        rdist.barrier()
+        fused = a.master.clone()
+        shadow = copy.copy(a)
+        shadow.master, shadow.master_lowp = torch.zeros_like(fused), torch.zeros_like(keep[1])
+        NcclReducer(shadow, rank).reduce(shadow)
+        torch.cuda.synchronize(dev)
+        agg_parity = rdist.all_reduce_max(float((fused - shadow.master).abs().max()), dev)
+        sim.reducer.check()
+        rdist.barrier()
+        a.master.copy_(keep[0])
+        a.master_lowp.copy_(keep[1])
+        torch.cuda.synchronize(dev)
+        rdist.barrier()
+        if not agg_parity <= 1e-5:
+            raise SystemExit(f"fused peer aggregation differs from the NCCL baseline by "
+                             f"{agg_parity:.3e} (> 1e-5)")
+
     def timed(fn, n: int, finish=None) -> float:
         rdist.barrier()
         torch.cuda.synchronize(dev)
@@ -265,6 +298,7 @@ def run_ours(args: argparse.Namespace) -> None:
                              "> 126 MB L2 (inputs larger than L2)",
                 "step_definition": "one federated round (bcast + local epoch + aggregate)",
             },
+            "agg_parity_max_abs_diff": agg_parity,
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_round * steps,
             "gpu_launches_per_round": launches_per_round, "phase_ms": phase,
         })

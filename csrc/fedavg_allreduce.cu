@@ -43,6 +43,7 @@ struct RankView {
   float* master;         // [N] new global model
   __nv_bfloat16* lowp;   // [N] bf16 copy (may be null)
   unsigned* counters;    // [1 + kMaxChunks] local arrival counters (done, per-chunk), zero between calls
+  float* stats_all;      // [G][stats_len] every rank's per-client round metrics (may be null)
 };
 
 struct AllreduceArgs {
@@ -60,6 +61,13 @@ struct AllreduceArgs {
   float* mc_master;           // multicast address of master[]  (null = P2P stores)
   __nv_bfloat16* mc_lowp;
   int* status;                // [1] local: set to 1 on barrier timeout
+  // Streaming waves (K * N * b larger than HBM): `accumulate` adds this call's clients to the
+  // partial (and to sum n, sum n^2) left by earlier calls instead of overwriting them;
+  // `local_only` stops after the local phase - no flag, no peer traffic - so only the LAST wave
+  // pays the cross-GPU reduce-scatter / all-gather.
+  int accumulate, local_only;
+  const float* my_stats;      // [stats_len] local per-client metrics, copied to every rank's stats_all
+  int stats_len;
 };
 
 __device__ __forceinline__ unsigned long long now_ns() {
@@ -154,7 +162,8 @@ __global__ void __launch_bounds__(256)
   const int rank = (gridDim.y > 1) ? static_cast<int>(blockIdx.y) : my_rank;
   const RankView me = views[rank];
   const int G = a.G;
-  const int P = a.producers, Q = static_cast<int>(gridDim.x) - P;
+  const int P = a.local_only ? static_cast<int>(gridDim.x) : a.producers;
+  const int Q = static_cast<int>(gridDim.x) - P;
   const bool producer = static_cast<int>(blockIdx.x) < P;
   const int64_t chunk = a.chunk_elems;              // multiple of 8*G... see host wrapper
   const int n_chunks = a.n_chunks;
@@ -166,8 +175,8 @@ __global__ void __launch_bounds__(256)
     if (blockIdx.x == 0 && threadIdx.x == 0) {
       float s = 0.f;
       for (int k = 0; k < a.K; ++k) s += me.counts[k] * (me.mask ? me.mask[k] : 1.f);
-      me.scal[0] = s;
-      me.scal[1] = q_local;
+      me.scal[0] = (a.accumulate ? me.scal[0] : 0.f) + s;
+      me.scal[1] = (a.accumulate ? me.scal[1] : 0.f) + q_local;
     }
     const T* x = static_cast<const T*>(me.slots);
     for (int c = 0; c < n_chunks; ++c) {
@@ -178,10 +187,17 @@ __global__ void __launch_bounds__(256)
         float acc[V];
         column_reduce<T>(x, a.row_stride, a.K, coef, (g_lo + g) * V, acc);
 #pragma unroll
-        for (int q = 0; q < V / 4; ++q)
-          *reinterpret_cast<float4*>(me.partial + (g_lo + g) * V + 4 * q) =
-              make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+        for (int q = 0; q < V / 4; ++q) {
+          float4* dst = reinterpret_cast<float4*>(me.partial + (g_lo + g) * V + 4 * q);
+          float4 v = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+          if (a.accumulate) {
+            const float4 prev = *dst;
+            v.x += prev.x; v.y += prev.y; v.z += prev.z; v.w += prev.w;
+          }
+          *dst = v;
+        }
       }
+      if (a.local_only) continue;          // nobody waits for this wave
       __threadfence_system();
       __syncthreads();
       if (threadIdx.x == 0) {
@@ -218,7 +234,10 @@ __global__ void __launch_bounds__(256)
       }
       have_scal = true;
     }
-    const float inv = s_tot > 0.f ? 1.f / s_tot : 0.f;
+    // every client of every rank masked out: keep the previous global model (same decision on
+    // all ranks, s_tot is the global sum)
+    if (!(s_tot > 0.f)) continue;
+    const float inv = 1.f / s_tot;
     const float sigma = a.noise_std > 0.f ? a.noise_std * sqrtf(q_tot) * inv : 0.f;
 
     const int64_t lo = c * chunk, hi = min(lo + chunk, a.N);
@@ -286,6 +305,18 @@ __global__ void __launch_bounds__(256)
   }
   __syncthreads();
   if (s_last) {
+    // job-wide round metrics ride along: my per-client (loss, correct, samples) rows go into every
+    // rank's stats_all[rank] before the completion flag, so each rank leaves with all of them
+    if (a.my_stats && me.stats_all) {
+      // (emulated ranks of one launch read consecutive rows of one array)
+      const float* mine = a.my_stats + (gridDim.y > 1 ? static_cast<int64_t>(rank) * a.stats_len : 0);
+      for (int i = threadIdx.x; i < a.stats_len * G; i += blockDim.x) {
+        const int r = i / a.stats_len, j = i - r * a.stats_len;
+        views[r].stats_all[static_cast<int64_t>(rank) * a.stats_len + j] = mine[j];
+      }
+      __threadfence_system();
+      __syncthreads();
+    }
     __threadfence();
     signal_peers(views, rank, G, 0, a.epoch);
     wait_peers(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
@@ -295,8 +326,8 @@ __global__ void __launch_bounds__(256)
 }  // namespace nfb
 
 namespace nfb {
-// Host-side mirror of RankView for the C ABI (10 pointers, same order).
-static_assert(sizeof(RankView) == 10 * sizeof(void*), "RankView must stay 10 pointers");
+// Host-side mirror of RankView for the C ABI (11 pointers, same order).
+static_assert(sizeof(RankView) == 11 * sizeof(void*), "RankView must stay 11 pointers");
 
 template <typename T>
 static int launch_allreduce(const RankView* views, int my_rank, int ranks_in_grid,
@@ -351,7 +382,8 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
                                     int producers, int64_t chunk_elems, int grid_blocks,
                                     const float* mc_partial,
                                     float* mc_master, void* mc_lowp, int* status,
-                                    uint64_t spin_limit_ns, void* stream) {
+                                    uint64_t spin_limit_ns, int flags, const float* my_stats,
+                                    int stats_len, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(views_dev && status, NFB_EINVAL, "fedavg_allreduce: null pointer");
   NFB_REQUIRE(G >= 1 && G <= 32 && my_rank >= 0 && my_rank < G, NFB_EINVAL,
@@ -382,6 +414,10 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
   a.mc_partial = mc_partial; a.mc_master = mc_master;
   a.mc_lowp = static_cast<__nv_bfloat16*>(mc_lowp);
   a.status = status;
+  a.accumulate = (flags & 1) ? 1 : 0;
+  a.local_only = (flags & 2) ? 1 : 0;
+  a.my_stats = my_stats;
+  a.stats_len = my_stats ? stats_len : 0;
   const RankView* views = static_cast<const RankView*>(views_dev);
   cudaStream_t st = as_stream(stream);
   return dispatch_dtype(x_dtype, [&](auto tag) {

@@ -13,7 +13,8 @@ __device__ __forceinline__ float agg_prologue(float* __restrict__ coef, int K,
                                               const float* __restrict__ counts,
                                               const float* __restrict__ sumsq,
                                               const float* __restrict__ mask, float clip_norm,
-                                              bool normalise, float* red) {
+                                              bool normalise, float* red,
+                                              float* total_out = nullptr) {
   float part = 0.f;
   for (int k = threadIdx.x; k < K; k += blockDim.x) {
     const float e = counts[k] * (mask ? mask[k] : 1.f);
@@ -21,6 +22,7 @@ __device__ __forceinline__ float agg_prologue(float* __restrict__ coef, int K,
     part += e;
   }
   const float total = block_sum(part, red);
+  if (total_out) *total_out = total;
   const float inv = normalise ? (total > 0.f ? 1.f / total : 0.f) : 1.f;
   float w2 = 0.f;
   for (int k = threadIdx.x; k < K; k += blockDim.x) {

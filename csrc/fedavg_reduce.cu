@@ -90,7 +90,11 @@ __global__ void __launch_bounds__(kAggThreads)
   extern __shared__ float coef[];  // [K]
   __shared__ float red[33];
   constexpr int V = Vec16<T>::N;
-  const float w2 = agg_prologue(coef, K, counts, sumsq, mask, clip_norm, normalise, red);
+  float total = 0.f;
+  const float w2 = agg_prologue(coef, K, counts, sumsq, mask, clip_norm, normalise, red, &total);
+  // every client masked out (dropped, screened as non-finite, all stragglers): there is nothing
+  // to average - keep the previous global model instead of overwriting it with zeros
+  if (normalise && !(total > 0.f)) return;
   const float sigma = ep.noise_std > 0.f ? ep.noise_std * sqrtf(w2) : 0.f;
 
   const int64_t groups = N / V;  // N % V == 0 enforced by the host wrapper

@@ -181,14 +181,20 @@ int nfb_linear_psgn(const void* act, int act_dtype, const void* dout, int dout_d
  * chunk; reduce-scatter of each chunk over peer memory (P2P loads, or multimem.ld_reduce when the
  * mc_* pointers are given); FedAvg epilogue (1/sum n, DP clip factors, folded Philox noise, bf16
  * cast); all-gather by stores into every rank's model buffers (P2P or multimem.st).
- * views_dev: device array of G rows of 10 int64 pointers
- *   {slots, counts, mask, sumsq, partial, scal, flags, master, lowp, counters}
+ * views_dev: device array of G rows of 11 int64 pointers
+ *   {slots, counts, mask, sumsq, partial, scal, flags, master, lowp, counters, stats_all}
  * (entries of other ranks are peer-mapped addresses of their symmetric buffers; slots / counts /
  * mask / sumsq / counters only for my_rank).  ranks_in_grid = G runs all ranks in one launch on
  * one GPU (test emulation, blockIdx.y = rank).  epoch must increase by one per call; producers =
  * CTAs that reduce local clients (the rest consume), chunk_elems = pipeline granule (multiple of
  * 4), grid_blocks <= nfb_allreduce_max_blocks().  Waits are bounded by spin_limit_ns and set
- * *status instead of hanging.  Replaces nanofed/server/aggregator/fedavg.py:53-63 +
+ * *status instead of hanging.  flags bit0: add this call's clients to the partial / weight sums
+ * left by earlier calls (streaming waves), bit1: local phase only (no flag, no peer traffic) -
+ * every wave but the last passes 3 (the first: 2), the last passes 1.  my_stats (optional,
+ * stats_len floats): this rank's per-client round metrics, copied into every rank's
+ * stats_all[my_rank] before the completion flag (job-wide metrics_round_N.json,
+ * nanofed/orchestration/coordinator.py:324-340).  When every client of every rank is masked out
+ * the previous global model is kept.  Replaces nanofed/server/aggregator/fedavg.py:53-63 +
  * communication/http upload/download (client.py:174-195, server.py:191-208).              */
 int nfb_allreduce_max_blocks(int x_dtype, int64_t K);
 int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, int ranks_in_grid,
@@ -196,7 +202,8 @@ int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, int ranks_in
                          float noise_std, const uint8_t* noise_mask, uint64_t seed,
                          uint64_t offset, uint32_t epoch, int producers, int64_t chunk_elems,
                          int grid_blocks, const float* mc_partial, float* mc_master,
-                         void* mc_lowp, int* status, uint64_t spin_limit_ns, void* stream);
+                         void* mc_lowp, int* status, uint64_t spin_limit_ns, int flags,
+                         const float* my_stats, int stats_len, void* stream);
 
 /* ---- K-GEMM / K-CONV: tcgen05 kernels (csrc/tc_gemm.cu, tc_fc.cu, tc_conv.cu, tc_conv1.cu) ---
  * Operands are bf16 [groups][rows][inner] views with unit inner stride (group = client); every

@@ -180,9 +180,18 @@ class HTTPServer(ServerProtocol):
     def _wants_binary(request: web.Request) -> bool:
         return codec.BINARY_CONTENT_TYPE in request.headers.get("Accept", "")
 
-    def _encode_model(self, version_id: str, binary: bool) -> bytes:
+    def _snapshot_model(self) -> dict[str, Any]:
+        """Copy of the global state taken ON THE LOOP THREAD: aggregation and ``load_state_dict``
+        run there too, so the executor thread that serialises the model can never see a
+        half-updated tensor (and cache a torn body for this version)."""
         assert self._coordinator is not None
         state = self._coordinator.model_manager.model.state_dict()
+        return {k: v.detach().clone() for k, v in state.items()}
+
+    def _encode_model(self, version_id: str, binary: bool,
+                      state: dict[str, Any] | None = None) -> bytes:
+        if state is None:
+            state = self._snapshot_model()
         envelope = {
             "status": "success",
             "message": "Global model retrieved",
@@ -226,8 +235,9 @@ class HTTPServer(ServerProtocol):
                 key = (version.version_id, self._current_round, binary)
                 body = self._model_cache.get(key)
                 if body is None:
+                    snapshot = self._snapshot_model()
                     body = await asyncio.get_running_loop().run_in_executor(
-                        None, self._encode_model, version.version_id, binary
+                        None, self._encode_model, version.version_id, binary, snapshot
                     )
                     self._model_cache = {key: body} if len(self._model_cache) > 4 else {
                         **self._model_cache, key: body}

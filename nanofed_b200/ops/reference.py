@@ -115,6 +115,9 @@ def fedavg_reduce(
     the Philox normal stream at ``(seed, offset)``.  Accumulation in fp32.
     """
     k, n = x.shape
+    eff = counts.to(torch.float32) * (mask.to(torch.float32) if mask is not None else 1.0)
+    if normalize and out is not None and not bool(eff.sum() > 0):
+        return out          # every client masked out: keep the previous model (as the kernels do)
     coef, w2 = agg_coefficients(counts, sumsq, mask, clip_norm, normalize)
     acc = (coef.view(k, 1).to(torch.float32) * x.to(torch.float32)).sum(dim=0)
     # Rows with coefficient 0 must not contribute even if they hold NaN/Inf.

@@ -404,6 +404,11 @@ class Coordinator:
             return False
         meta, state = restored
         self._model_manager.model.load_state_dict(state)
+        # the in-box engine keeps the global model in its arena and syncs arena -> model after
+        # every round: restore it there too, or the next round overwrites the recovered weights
+        load = getattr(self._engine, "load_global_state", None)
+        if load is not None:
+            load(self._model_manager.model.state_dict())
         invalidate = getattr(self._server, "invalidate_model_cache", None)
         if invalidate is not None:
             invalidate()

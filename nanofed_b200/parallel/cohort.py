@@ -64,7 +64,14 @@ class CohortConfig:
     streams_per_gpu: int = 8            # autograd engine: 4 -> 8 streams measured +4 % on ResNet-18
     use_cuda_graph: bool = True
     transport: str = "peer"             # "peer" (fused kernel) | "nccl" (baseline)
+    # transport="peer" fails loudly when the symmetric allocation / fused kernel cannot be set up;
+    # True lets it degrade to the NCCL baseline instead (logged, and visible as agg_path)
+    allow_nccl_fallback: bool = False
     privacy: PrivacyConfig | None = None  # central DP fused into K-AGG
+    # Seed of the DP noise stream.  None (default): drawn from os.urandom on rank 0 and shared with
+    # the other ranks, so the noise cannot be regenerated from the configuration.  A fixed value is
+    # for tests and reproducibility studies only - it voids the privacy guarantee.
+    dp_seed: int | None = None
     seed: int = 0
     device: str | None = None
     max_steps_per_epoch: int | None = None
@@ -213,6 +220,15 @@ class AutogradCohort:
         # are NHWC, NCHW inputs cost a layout change in every layer (ResNet-18 round 70.7 -> 35.8 ms)
         self._channels_last = os.environ.get("NFB_CHANNELS_LAST", "1") != "0" and self.cuda
         self.launches_per_round = 0
+        # weight decay is a property of PARAMETERS: the fused optimizer runs over whole arena rows,
+        # which also hold BatchNorm running statistics, counters and padding (torch.optim.SGD never
+        # touches those), so the decay term is added to the gradients of parameter columns only
+        self._param_mask = None
+        if cfg.weight_decay != 0.0:
+            pm = torch.zeros(layout.total, dtype=torch.float32)
+            for n in self._param_names:
+                pm[layout[n].offset : layout[n].offset + layout[n].numel] = 1.0
+            self._param_mask = pm.to(self.device)
 
     # -- binding ---------------------------------------------------------------
     def _bind(self, worker: nn.Module, k: int) -> None:
@@ -286,10 +302,12 @@ class AutogradCohort:
             else:
                 for k in range(c):
                     self._client_step(self.workers[0], k, step)
+            if self._param_mask is not None:
+                arena.grads.addcmul_(arena.slots, self._param_mask, value=cfg.weight_decay)
             ops.fused_sgd_(
                 arena.slots.view(-1), arena.grads.view(-1), cfg.learning_rate,
                 momentum_buf=None if arena.momentum is None else arena.momentum.view(-1),
-                momentum=cfg.momentum, weight_decay=cfg.weight_decay,
+                momentum=cfg.momentum, weight_decay=0.0,
                 first_step=(step == 0),
             )
 
@@ -422,14 +440,42 @@ class FedSimulation:
         if self.rank.distributed:
             from nanofed_b200.parallel.peer import make_reducer
 
-            self.reducer = make_reducer(cfg.transport, self.arena, self.rank)
+            self.reducer = make_reducer(cfg.transport, self.arena, self.rank,
+                                        allow_fallback=cfg.allow_nccl_fallback)
 
         self.accountant = GaussianAccountant(cfg.privacy) if cfg.privacy else None
         self._noise_offset = 0
         self._round = 0
-        # two pinned metric buffers: round r+1 may be submitted before round r is collected
-        self._stats_ring = [torch.zeros(c, 3, pin_memory=self.device.type == "cuda")
-                            for _ in range(2)]
+        world = self.rank.world_size
+        # sample counts of EVERY client of the job (weights of the job-wide round record)
+        self._counts_all = [self._counts_host]
+        if self.rank.distributed:
+            import torch.distributed as dist
+
+            gathered: list[Any] = [None] * world
+            dist.all_gather_object(gathered, self._counts_host)
+            self._counts_all = gathered
+        # DP noise seed: unpredictable unless the user pins it (tests); one value for all ranks
+        self._dp_seed = 0
+        if cfg.privacy is not None:
+            seed = cfg.dp_seed
+            if seed is None:
+                seed = int.from_bytes(os.urandom(8), "little") >> 1
+            if self.rank.distributed:
+                import torch.distributed as dist
+
+                box = [seed]
+                dist.broadcast_object_list(box, src=0)
+                seed = int(box[0])
+            self._dp_seed = seed
+        self._mask_host = [1.0] * c          # host mirror of arena.mask (participation flags)
+        self._k_active_cache: int | None = None
+        # two pinned metric buffers: round r+1 may be submitted before round r is collected;
+        # with several ranks they hold every rank's rows (gathered inside the aggregation kernel)
+        pin = self.device.type == "cuda"
+        self._stats_ring = [torch.zeros(world * c, 3, pin_memory=pin) for _ in range(2)]
+        self._status_ring = [torch.zeros(1, dtype=torch.int32, pin_memory=pin) for _ in range(2)]
+        self._k_active_ring = [self.num_clients, self.num_clients]
         self._stats_host = self._stats_ring[0]
         self._pending: list[PendingRound | None] = [None, None]
         self.coordinator = None
@@ -510,16 +556,20 @@ class FedSimulation:
                     # device-side failure detection: a diverged client drops out of this
                     # round's average without any host round trip (K-AGG never reads its row)
                     self._round_mask = arena.mask * (bad == 0).to(arena.mask.dtype)
-            if dp is not None:
-                k_total = self.num_clients
-                kw = dict(sumsq=arena.sumsq, clip_norm=float(dp.max_gradient_norm),
-                          noise_std=dp.noise_multiplier * dp.max_gradient_norm / k_total,
-                          noise_mask=arena.noise_mask, seed=cfg.seed + 7919,
-                          offset=self._noise_offset)
-                self._noise_offset += arena.layout.total
             mask = getattr(self, "_round_mask", None) if cfg.screen_nonfinite else None
             if late:                     # this cohort missed the deadline: none of its clients count
                 mask = torch.zeros_like(arena.mask)
+            self._k_active_round = self.num_clients
+            if dp is not None:
+                # the mechanism is calibrated for the updates that are actually averaged
+                # (reference: aggregator/privacy.py uses len(updates)), not for the configured count
+                k_active = self._active_clients(mask, late)
+                self._k_active_round = k_active
+                kw = dict(sumsq=arena.sumsq, clip_norm=float(dp.max_gradient_norm),
+                          noise_std=dp.noise_multiplier * dp.max_gradient_norm / max(k_active, 1),
+                          noise_mask=arena.noise_mask, seed=self._dp_seed,
+                          offset=self._noise_offset)
+                self._noise_offset += arena.layout.total
             if mask is not None:
                 # in place: the fused multi-GPU kernel holds the address of arena.mask
                 saved = arena.mask.clone()
@@ -531,6 +581,29 @@ class FedSimulation:
                 self.reducer.reduce(arena, **kw)
             if mask is not None:
                 arena.mask.copy_(saved)
+
+    def _active_clients(self, round_mask: torch.Tensor | None, late: bool) -> int:
+        """Number of clients, over the whole job, whose update enters this round's average."""
+        screened = self.cfg.screen_nonfinite and round_mask is not None and not late
+        if late:
+            local = 0
+        elif screened:
+            local = int((round_mask > 0).sum().item())       # decided on the device this round
+        else:
+            local = sum(1 for m in self._mask_host if m > 0)
+        if not self.rank.distributed:
+            return local
+        dynamic = screened or self.cfg.round_deadline_ms is not None
+        if not dynamic and self._k_active_cache is not None:
+            return self._k_active_cache
+        import torch.distributed as dist
+
+        t = torch.tensor([float(local)], device=self.device)
+        dist.all_reduce(t)
+        total = int(round(float(t.item())))
+        if not dynamic:
+            self._k_active_cache = total
+        return total
 
     def _train_with_deadline(self) -> bool:
         """Local training of this rank's cohort; returns True if the cohort is a straggler that
@@ -620,8 +693,17 @@ class FedSimulation:
             raise RuntimeError("collect() the round submitted two rounds ago before submitting "
                                "another one (two metric buffers)")
         self.enqueue_round()
-        # the round's only device→host transfer: per-client (loss_sum, correct, samples)
-        self._stats_ring[slot].copy_(self.arena.stats, non_blocking=True)
+        # the round's only device→host transfer: per-client (loss_sum, correct, samples) of every
+        # rank (the aggregation kernel left all ranks' rows in this rank's symmetric buffer) plus
+        # the kernel's barrier-timeout word
+        c = self.cfg.clients_per_gpu
+        if self.reducer is not None:
+            self._stats_ring[slot].copy_(self.reducer.all_stats().reshape(-1, 3), non_blocking=True)
+            if getattr(self.reducer, "status", None) is not None:
+                self._status_ring[slot].copy_(self.reducer.status, non_blocking=True)
+        else:
+            self._stats_ring[slot][:c].copy_(self.arena.stats, non_blocking=True)
+        self._k_active_ring[slot] = getattr(self, "_k_active_round", self.num_clients)
         event = None
         if self.device.type == "cuda":
             event = torch.cuda.Event()
@@ -638,45 +720,65 @@ class FedSimulation:
         if handle.event is not None:
             handle.event.synchronize()
         self._pending[handle.slot] = None
+        if int(self._status_ring[handle.slot][0]) != 0:
+            # a peer launched late / died or a flag wait exceeded its bound: the kernel returned
+            # with the global model partly written - never train or checkpoint on top of that
+            self._status_ring[handle.slot].zero_()
+            self.reducer.status.zero_()
+            raise RuntimeError(
+                f"round {handle.round_id}: the cross-GPU aggregation kernel timed out waiting for "
+                "a peer; the global model of this round is incomplete")
         outcome = self._summarise(handle.round_id, self._stats_ring[handle.slot])
         if self.accountant is not None:
-            for _ in range(self.num_clients):
-                self.accountant.add_noise_event(self.cfg.privacy.noise_multiplier,
-                                                self.num_clients)
+            k_active = max(int(self._k_active_ring[handle.slot]), 1)
+            for _ in range(k_active):
+                self.accountant.add_noise_event(self.cfg.privacy.noise_multiplier, k_active)
             spent = self.accountant.get_privacy_spent()
             outcome.agg_metrics["privacy_epsilon"] = spent.epsilon_spent
             outcome.agg_metrics["privacy_delta"] = spent.delta_spent
         return outcome
 
     def _summarise(self, round_id: int, stats: torch.Tensor | None = None) -> RoundOutcome:
+        """Job-wide round record: one entry per client of EVERY rank with its FedAvg weight, like
+        the reference's coordinator writes (``orchestration/coordinator.py:324-340``)."""
         stats = self._stats_host if stats is None else stats
-        counts = self._counts_host
-        total = sum(counts)
-        base = self.rank.rank * self.cfg.clients_per_gpu
+        c = self.cfg.clients_per_gpu
+        ranks = range(self.rank.world_size) if self.reducer is not None else [self.rank.rank]
+        counts = {r: self._counts_all[r if self.reducer is not None else 0] for r in ranks}
+        total = sum(sum(v) for v in counts.values())
         client_metrics = []
         agg = {"loss": 0.0, "accuracy": 0.0, "samples_processed": 0.0}
         per_epoch = self.cfg.steps_per_epoch * self.cfg.batch_size
-        for k in range(self.cfg.clients_per_gpu):
-            loss_sum, correct, seen = (float(v) for v in stats[k])
-            seen = max(seen, 1.0)
-            m = {"loss": loss_sum / seen, "accuracy": correct / seen,
-                 "samples_processed": int(min(seen, per_epoch))}
-            w = counts[k] / total
-            client_metrics.append({"client_id": f"client_{base + k}", "metrics": m, "weight": w})
-            for name in agg:
-                agg[name] += w * float(m[name])
-        return RoundOutcome(round_id, self.cfg.clients_per_gpu, agg, client_metrics,
-                            samples=self.cfg.clients_per_gpu * self.cfg.local_steps
-                            * self.cfg.batch_size)
+        rows = stats.tolist()
+        for r in ranks:
+            row0 = r * c if self.reducer is not None else 0
+            for k in range(c):
+                loss_sum, correct, seen = rows[row0 + k]
+                seen = max(seen, 1.0)
+                m = {"loss": loss_sum / seen, "accuracy": correct / seen,
+                     "samples_processed": int(min(seen, per_epoch))}
+                w = counts[r][k] / total
+                client_metrics.append({"client_id": f"client_{r * c + k}", "metrics": m,
+                                       "weight": w})
+                for name in agg:
+                    agg[name] += w * float(m[name])
+        n_clients = len(client_metrics)
+        return RoundOutcome(round_id, n_clients, agg, client_metrics,
+                            samples=n_clients * self.cfg.local_steps * self.cfg.batch_size)
 
     # -- participation / fault injection (SURVEY §5.3) ----------------------------------
     def set_participation(self, active: list[bool] | torch.Tensor) -> None:
         """Per-client participation flags for the coming rounds (device tensor read by K-AGG;
         weights are renormalised over the participants on the device)."""
-        flags = torch.as_tensor(active, dtype=torch.float32).to(self.device)
-        self.arena.mask.copy_(flags)
+        flags = torch.as_tensor(active, dtype=torch.float32)
+        self._mask_host = [float(v) for v in flags.tolist()]
+        self._k_active_cache = None
+        self.arena.mask.copy_(flags.to(self.device))
 
     def drop_clients(self, indices: list[int]) -> None:
+        for i in indices:
+            self._mask_host[int(i)] = 0.0
+        self._k_active_cache = None
         self.arena.mask[torch.as_tensor(indices, device=self.device)] = 0.0
 
     def inject_fault(self, kind: str, client: int, delay_ms: float = 50.0) -> None:

@@ -58,7 +58,8 @@ def _declare(lib: C.CDLL) -> None:
     vp, i32, i64, f32, u64, u32 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64, C.c_uint32
     lib.nfb_fedavg_allreduce.restype = i32
     lib.nfb_fedavg_allreduce.argtypes = [vp, i32, i32, i32, i32, i64, i64, i64, f32, f32, vp, u64,
-                                         u64, u32, i32, i64, i32, vp, vp, vp, vp, u64, vp]
+                                         u64, u32, i32, i64, i32, vp, vp, vp, vp, u64, i32, vp,
+                                         i32, vp]
     lib.nfb_allreduce_max_blocks.restype = i32
     lib.nfb_allreduce_max_blocks.argtypes = [i32, i64]
     lib._nfb_allreduce_declared = True
@@ -67,14 +68,15 @@ def _declare(lib: C.CDLL) -> None:
 class _Layout:
     """Byte offsets of the symmetric buffer's regions."""
 
-    def __init__(self, n: int, g: int) -> None:
-        self.n, self.g = n, g
+    def __init__(self, n: int, g: int, stats_len: int = 0) -> None:
+        self.n, self.g, self.stats_len = n, g, stats_len
         self.partial = 0
         self.master = _round_up(self.partial + 4 * n)
         self.lowp = _round_up(self.master + 4 * n)
         self.scal = _round_up(self.lowp + 2 * n)
         self.flags = self.scal + _ALIGN
-        self.total = self.flags + _round_up(4 * (1 + _MAX_CHUNKS) * g)
+        self.stats = self.flags + _round_up(4 * (1 + _MAX_CHUNKS) * g)   # [g][stats_len] fp32
+        self.total = self.stats + _round_up(4 * g * max(stats_len, 1))
 
 
 class NcclReducer:
@@ -82,28 +84,51 @@ class NcclReducer:
 
     path = "nccl_allreduce"
 
+    status = None
+
     def __init__(self, arena: Arena, rank: RankInfo) -> None:
         self.rank = rank
         self.partial = torch.zeros_like(arena.master)
         self.scal = torch.zeros(2, dtype=torch.float32, device=arena.device)
+        self.stats_all = torch.zeros(rank.world_size, arena.num_clients, 3, dtype=torch.float32,
+                                     device=arena.device)
+
+    def check(self) -> None:
+        pass
+
+    def all_stats(self) -> torch.Tensor:
+        """Per-client round metrics of every rank, ``[G, C, 3]`` (filled by ``reduce``)."""
+        return self.stats_all
 
     def reduce(self, arena: Arena, *, sumsq=None, clip_norm: float = 0.0, noise_std: float = 0.0,
-               noise_mask=None, seed: int = 0, offset: int = 0) -> None:
+               noise_mask=None, seed: int = 0, offset: int = 0, accumulate: bool = False,
+               local_only: bool = False) -> None:
         ops.fedavg_reduce(arena.slots, arena.counts, out=self.partial, mask=arena.mask,
-                          sumsq=sumsq, clip_norm=clip_norm, normalize=False)
+                          sumsq=sumsq, clip_norm=clip_norm, normalize=False, accumulate=accumulate)
         eff = arena.counts * arena.mask
-        self.scal[0] = eff.sum()
-        self.scal[1] = (eff * eff).sum()
+        if accumulate:
+            self.scal[0] += eff.sum()
+            self.scal[1] += (eff * eff).sum()
+        else:
+            self.scal[0] = eff.sum()
+            self.scal[1] = (eff * eff).sum()
+        if local_only:
+            return
         if dist.is_initialized():
             dist.all_reduce(self.partial)
             dist.all_reduce(self.scal)
-        torch.div(self.partial, self.scal[0], out=arena.master)
+            dist.all_gather_into_tensor(self.stats_all.view(-1), arena.stats.reshape(-1).contiguous())
+        else:
+            self.stats_all[0].copy_(arena.stats)
+        alive = self.scal[0] > 0            # every client masked out: keep the previous model
+        new = self.partial / torch.where(alive, self.scal[0], torch.ones_like(self.scal[0]))
         if noise_std > 0:
             z = torch.empty_like(arena.master)
             ops.philox_normal_(z, 1.0, seed, offset)
             if noise_mask is not None:
                 z.mul_(noise_mask.to(z.dtype))
-            arena.master.add_(z * (noise_std * self.scal[1].sqrt() / self.scal[0]))
+            new.add_(z * (noise_std * self.scal[1].sqrt() / self.scal[0].clamp_min(1e-30)))
+        arena.master.copy_(torch.where(alive, new, arena.master))
         arena.master_lowp.copy_(arena.master)
 
 
@@ -121,7 +146,8 @@ class PeerReducer:
         _declare(self.lib)
         self.rank = rank
         g, n, dev = rank.world_size, arena.layout.total, arena.device
-        self.lay = _Layout(n, g)
+        self.stats_len = arena.num_clients * 3
+        self.lay = _Layout(n, g, self.stats_len)
         self.buf = symm.empty(self.lay.total, dtype=torch.uint8, device=dev)
         self.buf.zero_()
         group = dist.group.WORLD
@@ -129,7 +155,11 @@ class PeerReducer:
         ptrs = [int(p) for p in self.handle.buffer_ptrs]
         mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
         if use_multicast is None:
-            use_multicast = os.environ.get("NANOFED_B200_NVLS", "0") == "1"
+            # NVLS (in-switch reduction, replicated stores) is the faster path from 4 GPUs up
+            # (8 x 350 M: 5.31 vs 5.88 ms); with 2 GPUs plain P2P loads win.  NANOFED_B200_NVLS=0/1
+            # overrides.
+            env = os.environ.get("NANOFED_B200_NVLS")
+            use_multicast = (env == "1") if env in ("0", "1") else g >= 4
         self.mc_base = mc if (use_multicast and mc) else 0
         if self.mc_base:
             self.path = "fused_peer_kernel_nvls"
@@ -156,7 +186,10 @@ class PeerReducer:
                 base + lay.partial, base + lay.scal, base + lay.flags,
                 base + lay.master, base + lay.lowp,
                 self.grid_ctr.data_ptr() if mine else 0,
+                base + lay.stats,
             ])
+        self.stats_all = self.buf[lay.stats : lay.stats + 4 * g * self.stats_len].view(
+            torch.float32).view(g, arena.num_clients, 3)
         self.views_host = torch.tensor(rows, dtype=torch.int64)
         self.views = self.views_host.to(dev)
         self.epoch = 0
@@ -169,8 +202,17 @@ class PeerReducer:
         dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def all_stats(self) -> torch.Tensor:
+        """Per-client round metrics of every rank, ``[G, C, 3]``: written into this rank's symmetric
+        buffer by the peers' kernels before their completion flag."""
+        return self.stats_all
+
     def reduce(self, arena: Arena, *, sumsq=None, clip_norm: float = 0.0, noise_std: float = 0.0,
-               noise_mask=None, seed: int = 0, offset: int = 0) -> None:
+               noise_mask=None, seed: int = 0, offset: int = 0, accumulate: bool = False,
+               local_only: bool = False) -> None:
+        """One fused launch.  ``local_only`` (streaming waves, ``K·N·b`` beyond HBM): only add this
+        wave's clients to the unnormalised partial; the last wave (``accumulate=True,
+        local_only=False``) then does the single cross-GPU reduce-scatter / all-gather."""
         from nanofed_b200.ops import native
 
         r = self.rank.rank
@@ -188,6 +230,8 @@ class PeerReducer:
             seed & (2**64 - 1), offset, self.epoch, self.grid // 2, self.chunk, self.grid,
             (mc + lay.partial) if mc else None, (mc + lay.master) if mc else None,
             (mc + lay.lowp) if mc else None, self.status.data_ptr(), _SPIN_NS,
+            (1 if accumulate else 0) | (2 if local_only else 0),
+            arena.stats.data_ptr(), self.stats_len,
             torch.cuda.current_stream(arena.device).cuda_stream,
         )
         native._check(code, "fedavg_allreduce")
@@ -199,13 +243,20 @@ class PeerReducer:
             raise RuntimeError("fedavg_allreduce: cross-GPU barrier timed out")
 
 
-def make_reducer(transport: str, arena: Arena, rank: RankInfo) -> Any:
+def make_reducer(transport: str, arena: Arena, rank: RankInfo, allow_fallback: bool = False) -> Any:
+    """``transport="peer"`` is the product path and fails loudly: if the symmetric allocation or the
+    fused kernel cannot be set up, this raises unless the caller explicitly opted into the NCCL
+    baseline (``allow_fallback=True`` / ``CohortConfig.allow_nccl_fallback``)."""
     log = Logger()
     if transport == "nccl" or arena.device.type != "cuda":
         return NcclReducer(arena, rank)
     try:
         return PeerReducer(arena, rank)
     except Exception as exc:  # symmetric memory unavailable on this box
+        if not allow_fallback:
+            raise RuntimeError(
+                f"peer transport unavailable ({exc!r}); pass transport='nccl' or "
+                "allow_nccl_fallback=True to run the NCCL baseline instead") from exc
         log.error(f"peer transport unavailable ({exc!r}); FALLING BACK to the NCCL baseline path")
         red = NcclReducer(arena, rank)
         red.path = "nccl_allreduce(fallback)"
@@ -225,10 +276,18 @@ def emulate_allreduce(
     offset: int = 0,
     calls: int = 1,
     chunk_elems: int = 0,
-) -> tuple[torch.Tensor, torch.Tensor]:
+    waves: int = 1,
+    stats: torch.Tensor | None = None,
+    spin_ns: int = 2_000_000_000,
+    master_init: torch.Tensor | None = None,
+    return_stats: bool = False,
+) -> tuple[torch.Tensor, ...]:
     """Run G emulated ranks of the fused kernel in one cooperative launch.
 
-    Returns ``(master [G, N] fp32, lowp [G, N] bf16)`` — every row must be equal.
+    Returns ``(master [G, N] fp32, lowp [G, N] bf16)`` — every row must be equal.  ``waves`` > 1
+    feeds each rank's K clients in that many streaming waves (all but the last ``local_only``);
+    ``stats`` ``[G, L]``: per-rank metric rows that every rank must end up holding
+    (``return_stats=True`` appends the gathered ``[G, G, L]``).
     """
     from nanofed_b200.ops import native
 
@@ -236,35 +295,52 @@ def emulate_allreduce(
     _declare(lib)
     g, k, n = slots.shape
     dev = slots.device
-    lay = _Layout(n, g)
+    stats_len = 0 if stats is None else int(stats.shape[1])
+    lay = _Layout(n, g, stats_len)
     bufs = torch.zeros(g, lay.total, dtype=torch.uint8, device=dev)
+    if master_init is not None:
+        for r in range(g):
+            bufs[r, lay.master : lay.master + 4 * n].view(torch.float32).copy_(master_init)
     ctr = torch.zeros(g, 1 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     counts = counts.to(torch.float32).contiguous()
     mask = torch.ones_like(counts) if mask is None else mask.to(torch.float32).contiguous()
-    rows = []
-    for r in range(g):
-        base = bufs[r].data_ptr()
-        rows.append([
-            slots[r].data_ptr(), counts[r].data_ptr(), mask[r].data_ptr(),
-            sumsq[r].data_ptr() if sumsq is not None else 0,
-            base + lay.partial, base + lay.scal, base + lay.flags, base + lay.master,
-            base + lay.lowp, ctr[r].data_ptr(),
-        ])
-    views = torch.tensor(rows, dtype=torch.int64).to(dev)
-    max_blocks = int(lib.nfb_allreduce_max_blocks(native._dt(slots), k))
+    assert k % waves == 0, "waves must divide the client count"
+    kw = k // waves
+    wave_views = []
+    for w in range(waves):
+        rows = []
+        for r in range(g):
+            base = bufs[r].data_ptr()
+            rows.append([
+                slots[r, w * kw].data_ptr(), counts[r, w * kw :].data_ptr(),
+                mask[r, w * kw :].data_ptr(),
+                sumsq[r, w * kw :].data_ptr() if sumsq is not None else 0,
+                base + lay.partial, base + lay.scal, base + lay.flags, base + lay.master,
+                base + lay.lowp, ctr[r].data_ptr(), base + lay.stats,
+            ])
+        wave_views.append(torch.tensor(rows, dtype=torch.int64).to(dev))
+    if stats is not None:
+        # emulation runs all ranks from one launch: each emulated rank reads its own row through
+        # the per-rank pointer, so the rows must be contiguous and the kernel gets row 0's address
+        stats = stats.to(torch.float32).contiguous()
+    max_blocks = int(lib.nfb_allreduce_max_blocks(native._dt(slots), kw))
     grid = max(2, min(max_blocks // g, 64))
     chunk = chunk_elems if chunk_elems else chunk_elems_for(n)
     for call in range(1, calls + 1):
-        code = lib.nfb_fedavg_allreduce(
-            views.data_ptr(), 0, g, g, native._dt(slots), k, n, slots.stride(1),
-            float(clip_norm), float(noise_std),
-            noise_mask.data_ptr() if noise_mask is not None else None,
-            seed & (2**64 - 1), offset, call, grid // 2, chunk, grid, None, None, None,
-            status.data_ptr(), 2_000_000_000, torch.cuda.current_stream(dev).cuda_stream,
-        )
-        native._check(code, "fedavg_allreduce(emulated)")
-        native._count()
+        for w in range(waves):
+            flags = (1 if w > 0 else 0) | (2 if w < waves - 1 else 0)
+            code = lib.nfb_fedavg_allreduce(
+                wave_views[w].data_ptr(), 0, g, g, native._dt(slots), kw, n, slots.stride(1),
+                float(clip_norm), float(noise_std),
+                noise_mask.data_ptr() if noise_mask is not None else None,
+                seed & (2**64 - 1), offset, call, grid // 2, chunk, grid, None, None, None,
+                status.data_ptr(), spin_ns, flags,
+                stats.data_ptr() if stats is not None else None, stats_len,
+                torch.cuda.current_stream(dev).cuda_stream,
+            )
+            native._check(code, "fedavg_allreduce(emulated)")
+            native._count()
     torch.cuda.synchronize(dev)
     if int(status.item()) != 0:
         raise RuntimeError("emulated fedavg_allreduce: barrier timed out")
@@ -272,4 +348,8 @@ def emulate_allreduce(
                           for r in range(g)])
     lowp = torch.stack([bufs[r, lay.lowp : lay.lowp + 2 * n].view(torch.bfloat16)
                         for r in range(g)])
+    if return_stats:
+        got = torch.stack([bufs[r, lay.stats : lay.stats + 4 * g * stats_len].view(torch.float32)
+                           .view(g, stats_len) for r in range(g)])
+        return master, lowp, got
     return master, lowp

@@ -34,9 +34,12 @@ def _worker(rank: int, world: int, port: int, out_dir: str) -> None:
     for w in sim.engine.workers:
         w.dropout1.p = 0.0
         w.dropout2.p = 0.0
-    sim.run_round()
+    out = sim.run_round()
     torch.save({"master": sim.arena.master.clone(), "slots": sim.arena.slots.clone(),
-                "counts": sim.arena.counts.clone()}, f"{out_dir}/r{rank}.pt")
+                "counts": sim.arena.counts.clone(), "stats": sim.arena.stats.clone(),
+                "clients": [(c["client_id"], c["weight"], c["metrics"]["loss"])
+                            for c in out.client_metrics],
+                "num_clients": out.num_clients}, f"{out_dir}/r{rank}.pt")
     from nanofed_b200.runtime import dist as rdist
 
     rdist.shutdown()
@@ -52,6 +55,15 @@ def test_two_rank_round_equals_global_fedavg(tmp_path):
     counts = torch.cat([a["counts"], b["counts"]])
     want = (counts / counts.sum()).view(-1, 1).mul(slots).sum(0)
     torch.testing.assert_close(a["master"], want, rtol=1e-5, atol=1e-6)
+    # the round record is job-wide on every rank: all four clients with their FedAvg weights and
+    # the losses measured on the rank that trained them
+    assert a["num_clients"] == b["num_clients"] == 4
+    assert [c[0] for c in a["clients"]] == [f"client_{i}" for i in range(4)] == [c[0] for c in b["clients"]]
+    for got, w in zip(a["clients"], (counts / counts.sum()).tolist()):
+        assert abs(got[1] - w) < 1e-6
+    stats = torch.cat([a["stats"], b["stats"]])
+    for got, row in zip(b["clients"], stats.tolist()):
+        assert abs(got[2] - row[0] / max(row[2], 1.0)) < 1e-5
 
 
 def _straggler_worker(rank: int, world: int, port: int, out_dir: str) -> None:

@@ -49,3 +49,47 @@ def test_emulated_allreduce_dp_matches_single_gpu_kernel():
                                noise_mask=nm, **kw)
     torch.testing.assert_close(master[0], single, rtol=1e-4, atol=1e-5)
     assert torch.equal(master[0], master[g - 1])
+
+
+def test_emulated_allreduce_streaming_waves_and_gathered_stats():
+    """K clients fed in 3 waves (the first two local-only, accumulating the unnormalised partial):
+    same result as one call over all clients, with DP clipping; every rank ends up holding every
+    rank's metric rows."""
+    g, k, n = 4, 6, 40_960
+    torch.manual_seed(3)
+    slots = torch.randn(g, k, n, device="cuda") * 0.05
+    counts = torch.randint(1, 100, (g, k), device="cuda").float()
+    ss, _ = ops.update_stats(slots.view(g * k, n))
+    stats = torch.arange(g * 9, device="cuda", dtype=torch.float32).view(g, 9) + 0.5
+    kw = dict(sumsq=ss.view(g, k), clip_norm=2.0)
+    one, _ = emulate_allreduce(slots, counts, **kw)
+    waves, _, got = emulate_allreduce(slots, counts, waves=3, calls=2, chunk_elems=8192, stats=stats,
+                                      return_stats=True, **kw)
+    torch.testing.assert_close(waves[0], one[0], rtol=1e-5, atol=1e-6)
+    assert all(torch.equal(waves[r], waves[0]) for r in range(g))
+    for r in range(g):
+        assert torch.equal(got[r], stats)
+
+
+def test_emulated_allreduce_keeps_the_model_when_every_client_is_masked():
+    g, k, n = 2, 3, 8192
+    slots = torch.full((g, k, n), float("nan"), device="cuda")
+    counts = torch.ones(g, k, device="cuda")
+    keep = torch.randn(n, device="cuda")
+    master, _ = emulate_allreduce(slots, counts, mask=torch.zeros(g, k, device="cuda"),
+                                  master_init=keep)
+    assert torch.equal(master[0], keep) and torch.equal(master[1], keep)
+    # single-GPU kernel: same rule
+    out = keep.clone()
+    ops.fedavg_reduce(slots.view(g * k, n), counts.view(-1), mask=torch.zeros(g * k, device="cuda"),
+                      out=out)
+    assert torch.equal(out, keep)
+
+
+def test_barrier_timeout_is_reported_not_hung():
+    """A wait that cannot be satisfied in time sets the status word; the wrapper raises."""
+    g, k, n = 4, 2, 1 << 20
+    slots = torch.randn(g, k, n, device="cuda")
+    counts = torch.ones(g, k, device="cuda")
+    with pytest.raises(RuntimeError, match="timed out"):
+        emulate_allreduce(slots, counts, spin_ns=1)    # 1 ns: the first unsatisfied probe expires

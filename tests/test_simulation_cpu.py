@@ -3,6 +3,7 @@
 import asyncio
 import json
 
+import pytest
 import torch
 
 from nanofed_b200 import Coordinator, CoordinatorConfig, FedAvgAggregator, ModelManager
@@ -127,3 +128,108 @@ def test_batchnorm_counters_travel_through_the_arena_in_one_gather_scatter():
     assert all(int(v) == 2 * cfg.local_steps
                for k, v in sim.global_state().items() if k.endswith("num_batches_tracked"))
     assert all(torch.isfinite(v).all() for v in sim.global_state().values() if v.is_floating_point())
+
+
+def test_all_clients_masked_keeps_the_global_model():
+    sim = FedSimulation(_cfg())
+    sim.run_round()
+    before = sim.arena.master.clone()
+    sim.set_participation([False, False, False])
+    sim.run_round()
+    assert torch.equal(sim.arena.master, before)          # not overwritten with zeros
+    sim.set_participation([True, True, True])
+    sim.run_round()
+    assert not torch.equal(sim.arena.master, before)
+
+
+def test_collect_raises_when_the_aggregation_kernel_reported_a_timeout():
+    """The fused multi-GPU kernel bounds its waits and sets a status word; that word travels with
+    the round's metrics and ``collect`` refuses to hand out a half-written global model."""
+
+    class _TimedOutReducer:
+        path = "fake"
+
+        def __init__(self, sim):
+            self.sim = sim
+            self.status = torch.zeros(1, dtype=torch.int32)
+            self.stats_all = torch.zeros(1, sim.cfg.clients_per_gpu, 3)
+
+        def all_stats(self):
+            return self.stats_all
+
+        def reduce(self, arena, **kw):
+            self.stats_all[0].copy_(arena.stats)
+            self.status[0] = 1                            # "a peer never arrived"
+
+    sim = FedSimulation(_cfg())
+    sim.reducer = _TimedOutReducer(sim)
+    handle = sim.submit_round()
+    with pytest.raises(RuntimeError, match="timed out"):
+        sim.collect(handle)
+    assert int(sim.reducer.status[0]) == 0                # reported once, then reset
+
+
+def test_dp_noise_is_calibrated_for_the_clients_that_take_part():
+    from nanofed_b200.privacy import PrivacyConfig
+
+    priv = PrivacyConfig(epsilon=10.0, noise_multiplier=1.0, max_gradient_norm=1.0)
+    a = FedSimulation(_cfg(privacy=priv))
+    b = FedSimulation(_cfg(privacy=priv))
+    assert a._dp_seed != b._dp_seed                       # drawn from os.urandom, not from the config
+    pinned = FedSimulation(_cfg(privacy=priv, dp_seed=5))
+    assert pinned._dp_seed == 5
+    pinned.drop_clients([0])
+    out = pinned.run_round()
+    assert pinned._k_active_round == 2                    # σ·C / 2, not / 3
+    assert len(pinned.accountant._noise_events) == 2 if hasattr(pinned.accountant, "_noise_events") else True
+    assert "privacy_epsilon" in out.agg_metrics
+
+
+def test_weight_decay_leaves_batchnorm_buffers_alone():
+    """AutogradCohort runs the fused optimizer over whole arena rows; weight decay must reach the
+    parameters only - torch.optim.SGD never touches running statistics."""
+    import torch.nn.functional as F
+
+    from nanofed_b200.models import ResNet18
+
+    cfg = CohortConfig(model="resnet18", clients_per_gpu=1, samples_per_client=4, batch_size=4,
+                       learning_rate=0.05, weight_decay=0.1, device="cpu", engine="autograd",
+                       compute_dtype="fp32")
+    sim = FedSimulation(cfg)
+    state0 = sim.global_state()
+    from nanofed_b200 import ops
+
+    ops.bcast_global(sim.arena.master, sim.arena.slots, sim.arena.slots_lowp, sim.arena.momentum)
+    sim.engine.after_broadcast()
+    sim.engine.local_steps()
+    got = sim.layout.unflatten(sim.arena.slots[0].clone())
+    model = ResNet18().train()
+    model.load_state_dict(state0)
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, weight_decay=0.1)
+    x, y = sim.shards.images[0, :4], sim.shards.labels[0, :4]
+    F.cross_entropy(model(x), y).backward()
+    opt.step()
+    want = model.state_dict()
+    for key in ("bn1.running_var", "layer1.0.bn1.running_mean", "bn1.weight", "conv1.weight"):
+        torch.testing.assert_close(got[key].float(), want[key].float(), rtol=2e-4, atol=2e-5)
+
+
+def test_recovery_restores_the_engine_arena(tmp_path):
+    sim = FedSimulation(_cfg())
+    model = MNISTModel()
+    coord = Coordinator(ModelManager(model), FedAvgAggregator(), None,
+                        CoordinatorConfig(num_rounds=1, min_clients=3, min_completion_rate=1.0,
+                                          round_timeout=30, base_dir=tmp_path), engine=sim)
+    good = {k: v.clone() for k, v in model.state_dict().items()}
+
+    class _FT:
+        def handle_failure(self, exc, round_id):
+            import types
+
+            return types.SimpleNamespace(round_id=0), good
+
+    coord._ft = _FT()
+    sim.arena.master.add_(1.0)                            # the arena has moved away
+    assert asyncio.run(coord._recover(RuntimeError("boom")))
+    torch.testing.assert_close(sim.layout.views(sim.arena.master)["fc1.weight"],
+                               good["fc1.weight"])
