@@ -401,6 +401,16 @@ class FedSimulation:
             engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18")
                                    and self.device.type == "cuda"
                                    and _grouped_available()) else "autograd"
+        if cfg.compute_dtype not in ("bf16", "fp32"):
+            raise ValueError(f"compute_dtype must be 'bf16' or 'fp32', got {cfg.compute_dtype!r}")
+        if cfg.compute_dtype == "fp32":
+            # the hand-written engines feed bf16 operands to the tensor cores (fp32 accumulation,
+            # fp32 master weights); a user who asks for fp32 compute gets the fp32 autograd engine,
+            # never a silent bf16 run
+            if cfg.engine == "grouped":
+                raise ValueError("engine='grouped' computes in bf16 (fp32 accumulate/master); use "
+                                 "compute_dtype='bf16', or engine='autograd' for fp32 compute")
+            engine = "autograd"
         if engine == "grouped" and cfg.model not in ("mnist_cnn", "resnet18"):
             raise ValueError(f"engine='grouped' has no hand-written network for {cfg.model!r} "
                              "(available: mnist_cnn, resnet18); use engine='autograd'")

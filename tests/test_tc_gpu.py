@@ -26,7 +26,8 @@ def test_variant_matches_fp32_reference(name):
     tc_check._check_guards()          # nothing written outside the guarded outputs
     assert torch.isfinite(got).all()
     scale = ref.abs().max().item()
-    # bf16 operands, fp32 accumulation: 2% of the output range, elementwise
-    bad = int(((got - ref).abs() > 0.02 * scale + 0.02).sum())
+    # fp32 oracle (TF32 off).  fp32 outputs: 1e-3 of the output range, bf16 outputs: 1e-2
+    tol = tc_check.tolerance(name)
+    bad = int(((got - ref).abs() > tol * scale).sum())
     assert bad == 0, f"{name}: {bad}/{got.numel()} elements off (range {scale:.3g})"
     assert native.LAUNCHES > before, "no native kernel was launched"

@@ -15,7 +15,19 @@ import torch
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 
+# the oracles are fp32: no TF32 in the library convolutions / matmuls they call
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 W = 26  # grid width
+
+# kernels whose OUTPUT is fp32 (fp32 accumulation of exact bf16 products: only the summation order
+# differs from the oracle) are held to 1e-3 of the output range, bf16 outputs to 1e-2
+FP32_OUT = {"fc_fwd", "conv_wgrad", "conv_wgrad_p", "fc_wgrad", "fc_wgrad_sgd"}
+
+
+def tolerance(name: str) -> float:
+    return 1e-3 if name in FP32_OUT else 1e-2
 
 
 def _bf(*shape, scale=1.0):
@@ -307,13 +319,14 @@ def run_one(name: str) -> bool:
     err = (got - ref).abs().max().item()
     scale = ref.abs().max().item()
     rel = err / max(scale, 1e-6)
-    bad = int(((got - ref).abs() > 0.02 * scale + 0.02).sum())
-    ok = rel < 0.02 and bad == 0 and torch.isfinite(got).all().item()
+    tol = tolerance(name)
+    bad = int(((got - ref).abs() > tol * scale).sum())
+    ok = rel < tol and bad == 0 and torch.isfinite(got).all().item()
     print(f"{name:12s} max_abs_err={err:.4e} ref_max={scale:.3e} rel={rel:.3e} "
           f"mismatches={bad}/{got.numel()} {'OK' if ok else 'FAIL'}", flush=True)
     if not ok:
         d = (got - ref).abs()
-        idx = torch.nonzero(d > 0.02 * scale + 0.02)[:5].tolist()
+        idx = torch.nonzero(d > tol * scale)[:5].tolist()
         for ix in idx:
             print("   at", ix, "got", got[tuple(ix)].item(), "want", ref[tuple(ix)].item())
     return ok
