@@ -57,7 +57,8 @@ struct GemmArgs {
 };
 
 // EPI: 0 = store / accumulate the product, 1 = the product is a weight gradient that is applied
-// to the fp32 master weights in the epilogue (SGD) and never written to memory.
+// to the fp32 master weights in the epilogue (SGD) and never written to memory, 2 = the product is
+// one sample's weight gradient and only the sum of its squares is accumulated into out[group].
 template <bool A_MN, int A_SWZ, bool B_MN, int B_SWZ, int BK, int BN, int TPS, int STAGES,
           int EPI = 0>
 struct Cfg {
@@ -237,7 +238,22 @@ __global__ void __launch_bounds__(256, MINB)
     tc_fence_after();
     const bool row_ok = ok && n_iters > 0 && m < args.m_valid;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
-    if constexpr (EPI == 1) {
+    if constexpr (EPI == 2) {
+      // ---- K-PSGN: the product is ONE SAMPLE's weight gradient; only its squared Frobenius norm
+      // leaves the kernel (rows / columns beyond the operands were zero-filled by TMA, so they add
+      // nothing and need no masking) ----
+      float acc = 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(lane_addr + c0, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc = fmaf(__uint_as_float(r[j]), __uint_as_float(r[j]), acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0 && ok && n_iters > 0) atomicAdd(static_cast<float*>(args.out) + g, acc);
+    } else if constexpr (EPI == 1) {
       // ---- weight gradient applied in place: w <- w - lr * (dW + wd * w) ----
       // Per 32-column chunk: the fp32 weights arrive by TMA in a 128-byte-swizzled [32 x 128 B]
       // buffer, each thread updates its own row in place, and the same buffer is the source of
@@ -678,6 +694,30 @@ int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* A, const nfb_tc_operand* B, in
   return launch<true, 128, true, 128, 64, 128, 1, 2, 2, 1>(a, b, (j + BM - 1) / BM, (i + 127) / 128,
                                                          groups, g, as_stream(stream), w_lowp,
                                                          lowp_gs);
+}
+
+// K-PSGN for convolutions (and any layer whose per-sample weight gradient is delta_i^T U_i):
+//   out[i] += || sum_p dy[i][p][:]^T u[i][p][:] ||_F^2     for every sample i (= GEMM group),
+// on tensor cores, both operands MN-major ([P rows][channels contiguous], bf16); the per-sample
+// gradient lives only in TMEM.  out must be zero on entry (CTAs of one sample add atomically).
+// Replaces the clip_grad_norm_ of nanofed/trainer/private.py:62-63 for TRUE per-sample clipping.
+int nfb_tc_psgn(const nfb_tc_operand* dy, const nfb_tc_operand* u, int samples, int cout, int kdim,
+                int inner, float* out, int* status, void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(dy && u && out && status, NFB_EINVAL, "tc_psgn: null pointer");
+  NFB_REQUIRE(samples >= 1 && samples <= 65535 && cout >= 1 && kdim >= 1 && inner >= 1, NFB_EINVAL,
+              "tc_psgn: bad shape");
+  GemmArgs g{};
+  g.taps = 1; g.inner = inner; g.k_split = 1;
+  g.tap[0] = Tap{0, 0, 0, 0};
+  g.out = out; g.m_valid = cout; g.n_valid = kdim;
+  g.status = status;
+  Operand a{dy->ptr, dy->inner, dy->rows, dy->groups, dy->row_stride, dy->group_stride};
+  Operand b{u->ptr, u->inner, u->rows, u->groups, u->row_stride, u->group_stride};
+  return launch<true, 128, true, 128, 64, 128, 1, 2, 2, 2>(a, b, (cout + BM - 1) / BM,
+                                                          (kdim + 127) / 128, samples, g,
+                                                          as_stream(stream));
 }
 
 }  // extern "C"

@@ -237,6 +237,12 @@ int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* dy, const nfb_tc_operand* x, i
                             long long lowp_gs, float lr, float weight_decay, int* status,
                             void* stream);
 /* out[g][b,i] = scale * sum_j dy[g][b,j] * w[g][j,i]  (persistent; j = 128, b <= 128).      */
+/* K-PSGN on tensor cores: out[i] += ||sum_p dy[i][p][:]^T u[i][p][:]||_F^2 per sample (group) i;
+ * dy [samples][P][cout], u [samples][P][kdim] bf16 (unfolded patches, optionally with a ones
+ * column for the bias term); inner = ceil(P / 64); out zero on entry.  Replaces the whole-batch
+ * clip_grad_norm_ of nanofed/trainer/private.py:62-63 with true per-sample norms.           */
+int nfb_tc_psgn(const nfb_tc_operand* dy, const nfb_tc_operand* u, int samples, int cout, int kdim,
+                int inner, float* out, int* status, void* stream);
 int nfb_tc_fc_dgrad(const nfb_tc_operand* dy, const nfb_tc_operand* w, void* out, long long out_rs,
                     long long out_gs, float scale, int* status, void* stream);
 /* 3x3 convolutions on the row-flattened NHWC grid (activation = [clients][B*W*W rows][ch], tap

@@ -11,7 +11,12 @@ from .http import (
     ServerModelUpdateRequest,
 )
 
+from .peer import ClientSpec, PeerClient, PeerHub
+
 __all__ = [
+    "PeerClient",
+    "PeerHub",
+    "ClientSpec",
     "HTTPClient",
     "HTTPServer",
     "ClientEndpoints",

@@ -122,8 +122,13 @@ def linear_per_sample_grad_sqnorms(activations, grad_outputs, bias: bool = True)
 
 
 def conv_per_sample_grad_sqnorms(unfolded, grad_outputs, bias: bool = True) -> torch.Tensor:
-    # Gram products are library GEMMs on either device; the linear (ghost-norm)
-    # case above is the hand-written kernel.
+    """``[B]`` squared per-sample weight-gradient norms of a convolution (or a Linear applied to
+    sequences).  CUDA: grouped tcgen05 GEMM with a sum-of-squares epilogue (``ops.tc.conv_psgn``,
+    one group per sample, gradients never leave TMEM); CPU: the Gram-matrix oracle."""
+    if unfolded.is_cuda and unfolded.shape[0] <= 65535:
+        from . import tc
+
+        return tc.conv_psgn(unfolded, grad_outputs, bias)
     return reference.conv_per_sample_grad_sqnorms(unfolded, grad_outputs, bias)
 
 

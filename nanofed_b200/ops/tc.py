@@ -395,3 +395,43 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, grad: torch.Tensor,
     # The swapped orientation (lanes along i, scalar stores) measured 1.7x slower.
     gemm(FC_WGRAD, dy, x, grad, m=j, n=i, strides=(grad_group_stride, i, 1, 0),
          inner=(dy.shape[1] + 63) // 64)
+
+
+def conv_psgn(unfolded: torch.Tensor, grad_outputs: torch.Tensor, bias: bool = True) -> torch.Tensor:
+    """K-PSGN for convolutions on tensor cores: ``out[i] = ‖δ_iᵀ U_i‖_F² (+ ‖Σ_p δ_i[p]‖²)``.
+
+    ``unfolded`` ``[B, P, K]`` (im2col patches, ``K = Cin·kh·kw``), ``grad_outputs`` ``[B, P, Cout]``.
+    Each sample is one group of the grouped tcgen05 GEMM (both operands MN-major); the epilogue
+    sums the squares of the per-sample gradient straight out of TMEM, so the ``B × Cout × K``
+    per-sample gradients never exist in memory.  The bias term rides along as a column of ones
+    appended to the patches.  Operands are rounded to bf16 (fp32 accumulation): relative error of
+    the norms ≈ 3e-3.  Reference span: ``nanofed/trainer/private.py:54-86``.
+    """
+    lib = _lib()
+    if not getattr(lib, "_nfb_psgn_declared", False):
+        lib.nfb_tc_psgn.restype = C.c_int
+        lib.nfb_tc_psgn.argtypes = [C.POINTER(_Operand), C.POINTER(_Operand), C.c_int, C.c_int,
+                                    C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib._nfb_psgn_declared = True
+    b, p, k = unfolded.shape
+    cout = grad_outputs.shape[2]
+    assert grad_outputs.shape[:2] == (b, p)
+    kp = -(-(k + (1 if bias else 0)) // 8) * 8          # 16-byte rows for the TMA descriptors
+    cp = -(-cout // 8) * 8
+    u = torch.zeros(b, p, kp, dtype=torch.bfloat16, device=unfolded.device)
+    u[:, :, :k] = unfolded
+    if bias:
+        u[:, :, k] = 1.0
+    d = grad_outputs
+    if cp != cout or d.dtype != torch.bfloat16 or not d.is_contiguous():
+        dd = torch.zeros(b, p, cp, dtype=torch.bfloat16, device=d.device)
+        dd[:, :, :cout] = d
+        d = dd
+    out = torch.zeros(b, dtype=torch.float32, device=u.device)
+    st = status_word(u.device)
+    od, ou = _operand(d), _operand(u)
+    code = lib.nfb_tc_psgn(C.byref(od), C.byref(ou), b, cp, kp, (p + 63) // 64, out.data_ptr(),
+                           st.data_ptr(), torch.cuda.current_stream(u.device).cuda_stream)
+    native._check(code, "tc_psgn")
+    native._count()
+    return out

@@ -194,7 +194,8 @@ class PeerReducer:
         self.views = self.views_host.to(dev)
         self.epoch = 0
         self.chunk = chunk_elems_for(n)
-        max_blocks = int(self.lib.nfb_allreduce_max_blocks(0, arena.num_clients))
+        max_blocks = int(self.lib.nfb_allreduce_max_blocks(native._dt(arena.slots),
+                                                           arena.num_clients))
         if max_blocks <= 0:
             raise RuntimeError("fedavg_allreduce: occupancy query failed")
         # one wave, at most 4 CTAs per SM: enough loads in flight to saturate HBM/NVLink
@@ -223,8 +224,8 @@ class PeerReducer:
         self.epoch += 1
         lay, mc = self.lay, self.mc_base
         code = self.lib.nfb_fedavg_allreduce(
-            self.views.data_ptr(), r, self.rank.world_size, 1, 0,
-            arena.num_clients, arena.layout.total, arena.slots.stride(0),
+            self.views.data_ptr(), r, self.rank.world_size, 1, native._dt(arena.slots),
+            arena.slots.shape[0], arena.layout.total, arena.slots.stride(0),
             float(clip_norm), float(noise_std),
             noise_mask.data_ptr() if noise_mask is not None else None,
             seed & (2**64 - 1), offset, self.epoch, self.grid // 2, self.chunk, self.grid,

@@ -34,7 +34,44 @@ def test_per_sample_norms_on_cuda_use_the_native_kernel():
         model.zero_grad()
         nn.functional.cross_entropy(model(x[i:i + 1]), y[i:i + 1]).backward()
         explicit.append(torch.sqrt(sum(p.grad.pow(2).sum() for p in model.parameters())))
-    torch.testing.assert_close(norms, torch.stack(explicit), rtol=2e-3, atol=1e-4)
+    # conv norms come from bf16 tensor-core operands (fp32 accumulation): 1e-2
+    torch.testing.assert_close(norms, torch.stack(explicit), rtol=1e-2, atol=1e-4)
+
+
+def test_conv_psgn_kernel_matches_per_sample_gradients():
+    """K-PSGN for convolutions (grouped tcgen05 GEMM, sum-of-squares epilogue) at the MNIST CNN's
+    conv2 shape against explicit per-sample weight + bias gradients in fp32."""
+    import torch.nn.functional as F
+
+    from nanofed_b200 import ops
+    from nanofed_b200.ops import native, tc
+
+    torch.manual_seed(2)
+    b, cin, cout, hw = 16, 32, 64, 26
+    x = torch.randn(b, cin, hw, hw, device=DEV)
+    dy = torch.randn(b, cout, hw - 2, hw - 2, device=DEV)
+    unf = F.unfold(x, 3).transpose(1, 2)
+    before = native.LAUNCHES
+    got = ops.conv_per_sample_grad_sqnorms(unf, dy.flatten(2).transpose(1, 2), bias=True)
+    torch.cuda.synchronize()
+    tc.check_status(x.device)
+    assert native.LAUNCHES > before
+    w = torch.zeros(cout, cin, 3, 3, device=DEV, requires_grad=True)
+    bias = torch.zeros(cout, device=DEV, requires_grad=True)
+    want = []
+    for i in range(b):
+        gw, gb = torch.autograd.grad((F.conv2d(x[i:i + 1], w, bias) * dy[i:i + 1]).sum(), (w, bias))
+        want.append(gw.pow(2).sum() + gb.pow(2).sum())
+    torch.testing.assert_close(got, torch.stack(want), rtol=1e-2, atol=0)
+    # odd sizes: K = 9 (one input channel), Cout = 4, P = 36: padding to 16-byte rows is internal
+    x1, d1 = torch.randn(5, 1, 8, 8, device=DEV), torch.randn(5, 4, 6, 6, device=DEV)
+    got1 = ops.conv_per_sample_grad_sqnorms(F.unfold(x1, 3).transpose(1, 2),
+                                            d1.flatten(2).transpose(1, 2), bias=False)
+    from nanofed_b200.ops import reference
+
+    want1 = reference.conv_per_sample_grad_sqnorms(F.unfold(x1, 3).transpose(1, 2),
+                                                   d1.flatten(2).transpose(1, 2), bias=False)
+    torch.testing.assert_close(got1, want1, rtol=1e-2, atol=0)
 
 
 def test_per_sample_step_applies_clipped_mean():
@@ -58,7 +95,7 @@ def test_per_sample_step_applies_clipped_mean():
     model.zero_grad()
     t.train_batch(model, (x, y), opt)
     for p, b0, g in zip(model.parameters(), before, want):
-        torch.testing.assert_close(b0 - p.detach(), g / 6, rtol=5e-3, atol=1e-4)
+        torch.testing.assert_close(b0 - p.detach(), g / 6, rtol=1.5e-2, atol=1e-4)
 
 
 def test_torch_trainer_epoch_on_cuda_learns_and_reports_device_metrics():
