@@ -48,6 +48,7 @@ constexpr int UMMA_K = 16;
 
 struct Tap {
   int dh, dw, ph, pw, wrow, src;
+  int cls;   // output parity class this tap belongs to (-1: every class); see GemmArgs::n_cls
 };
 
 __device__ __forceinline__ void tma_load_5d(void* smem_dst, const CUtensorMap* map, uint64_t* bar,
@@ -93,9 +94,15 @@ struct GemmArgs {
   Tap tap[kMaxTaps];
   int n_out;             // output channels
   int out_ph, out_pw, out_c;  // output parity class (parity view) and channel count of the output
+  int clients, n_cls;         // n_cls = 4: grid.z also runs over the parity classes (taps carry cls)
   float* stats;          // [clients][2][n_out] or null
   const __nv_bfloat16* residual;  // [clients * P][n_out] added to the result (dgrad) or null
   const __nv_bfloat16* res_mask;  // residual counts only where res_mask > 0 (or null)
+  // ReLU backward of the layer this gradient flows INTO, fused: the stored value is zeroed where
+  // out_mask (dense tensor of the output's shape, e.g. the activation whose gradient this is) is
+  // not positive, so the BatchNorm backward kernels downstream need no mask operand
+  const __nv_bfloat16* out_mask;
+  int out_is_parity;
   int* status;
 };
 
@@ -135,14 +142,15 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int mtile = blockIdx.x, ntile = blockIdx.y, g = blockIdx.z;
-  const int it0 = [&] {   // iterations that read source 0
-    int n = 0;
-    for (int t = 0; t < args.n_taps; ++t) n += args.tap[t].src == 0 ? args.kc[0] : 0;
-    return n;
-  }();
-  int n_iters = it0;
-  for (int t = 0; t < args.n_taps; ++t) n_iters += args.tap[t].src == 1 ? args.kc[1] : 0;
+  // grid.z = class * clients + client: the four output parity classes of a stride-2 data gradient
+  // are one launch (each class has its own taps and its own quarter of the output pixels)
+  const int mtile = blockIdx.x, ntile = blockIdx.y;
+  const int g = blockIdx.z % args.clients, cls = blockIdx.z / args.clients;
+  const int out_ph = args.n_cls > 1 ? (cls >> 1) : args.out_ph;
+  const int out_pw = args.n_cls > 1 ? (cls & 1) : args.out_pw;
+  int n_iters = 0;
+  for (int t = 0; t < args.n_taps; ++t)
+    if (args.tap[t].cls < 0 || args.tap[t].cls == cls) n_iters += args.kc[args.tap[t].src];
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_a0);
@@ -175,6 +183,7 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
       bool ok = true;
       for (int t = 0; t < args.n_taps && ok; ++t) {
         const Tap tp = args.tap[t];
+        if (tp.cls >= 0 && tp.cls != cls) continue;
         const CUtensorMap* ma = tp.src ? &map_a1 : &map_a0;
         const CUtensorMap* mb = tp.src ? &map_b1 : &map_b0;
         const int kcn = args.kc[tp.src];
@@ -267,6 +276,26 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
             for (int e = 0; e < 8; ++e) v[p * 8 + e] += rf[e];
           }
         }
+        if (args.out_mask) {
+          long long moff;
+          if (!args.out_is_parity) {
+            moff = row * args.n_out;
+          } else {   // this row is pixel (2*hh + ph, 2*wh + pw) of the full-resolution output
+            const int hw = args.H * args.W;
+            const int n = static_cast<int>(row / hw), rem = static_cast<int>(row - static_cast<long long>(n) * hw);
+            const int hh = rem / args.W, wh = rem - hh * args.W;
+            moff = ((static_cast<long long>(n) * 2 * args.H + 2 * hh + out_ph) * (2 * args.W) +
+                    2 * wh + out_pw) * args.out_c;
+          }
+          moff += ntile * BN + c * 64;
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            float mf[8];
+            unpack<__nv_bfloat16>(ld_plain(args.out_mask + moff + p * 8), mf);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[p * 8 + e] = mf[e] > 0.f ? v[p * 8 + e] : 0.f;
+          }
+        }
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
 #pragma unroll
@@ -275,8 +304,8 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
         fence_proxy_async();
         __syncwarp();
         if (lane == 0 && ok) {
-          tma_store_5d(&map_o, my_stage, ntile * BN + c * 64 + args.out_pw * args.out_c, 0,
-                       args.out_ph, h0, n0);
+          tma_store_5d(&map_o, my_stage, ntile * BN + c * 64 + out_pw * args.out_c, 0, out_ph, h0,
+                       n0);
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
         if (args.stats) {
@@ -343,7 +372,10 @@ template <int BN, int POSK>
 struct WgradCfg {
   static constexpr int ATOM = POSK * 128;             // POSK positions x 64 channels
   static constexpr int STAGE = (2 + BN / 64) * ATOM;
-  static constexpr int STAGES = (200 * 1024 / STAGE) > 6 ? 6 : (200 * 1024 / STAGE);
+  // POSK = 64: at most ~100 KB so that two CTAs share an SM (the epilogue of one - TMEM reads,
+  // fp32 atomics or the fused SGD update - overlaps the k-loop of the other)
+  static constexpr int BUDGET = POSK == 64 ? 100 * 1024 : 200 * 1024;
+  static constexpr int STAGES = (BUDGET / STAGE) > 6 ? 6 : (BUDGET / STAGE);
   static constexpr int TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
   static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + 1024 + 256;
   static_assert(STAGES >= 2, "pipeline needs two stages");
@@ -600,8 +632,8 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
                      const void* w1, const int* w_dims /* [2][3]: inner, rows, group stride */,
                      int clients, int imgs_per_client, int H, int W, int n_out, int n_taps,
                      const int* taps, const nfb_rn_act* out, int out_ph, int out_pw, float* stats,
-                     const void* residual, const void* res_mask, int bn_tile, int halves,
-                     int* status, void* stream) {
+                     const void* residual, const void* res_mask, const void* out_mask, int bn_tile,
+                     int halves, int n_cls, int* status, void* stream) {
   using namespace nfb;
   using namespace nfb::rn;
   NFB_REQUIRE(a0 && w0 && w_dims && taps && out && status, NFB_EINVAL, "rn_conv_gemm: null pointer");
@@ -622,11 +654,18 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
   g.stats = stats;
   g.residual = static_cast<const __nv_bfloat16*>(residual);
   g.res_mask = static_cast<const __nv_bfloat16*>(res_mask);
+  g.out_mask = static_cast<const __nv_bfloat16*>(out_mask);
+  g.out_is_parity = out->parity ? 1 : 0;
+  NFB_REQUIRE(!out_mask || out->C == n_out, NFB_EINVAL, "rn_conv_gemm: output mask needs a full-width output");
   g.status = status;
   bool use1 = false;
+  NFB_REQUIRE(n_cls == 1 || (n_cls == 4 && out->parity), NFB_EINVAL,
+              "rn_conv_gemm: classes are the 4 parities of a parity-view output");
+  NFB_REQUIRE(static_cast<long long>(clients) * n_cls <= 65535, NFB_ERANGE, "rn_conv_gemm: grid");
+  g.clients = clients; g.n_cls = n_cls;
   for (int t = 0; t < n_taps; ++t) {
-    g.tap[t] = Tap{taps[6 * t], taps[6 * t + 1], taps[6 * t + 2], taps[6 * t + 3], taps[6 * t + 4],
-                   taps[6 * t + 5]};
+    g.tap[t] = Tap{taps[7 * t], taps[7 * t + 1], taps[7 * t + 2], taps[7 * t + 3], taps[7 * t + 4],
+                   taps[7 * t + 5], n_cls > 1 ? taps[7 * t + 6] : -1};
     NFB_REQUIRE(g.tap[t].src == 0 || g.tap[t].src == 1, NFB_EINVAL, "rn_conv_gemm: tap source");
     use1 |= g.tap[t].src == 1;
   }
@@ -648,7 +687,7 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
   // k-chunks: forward K = input channels = weight inner; dgrad K = output channels of the conv
   g.cpar[0] = a0->C; g.cpar[1] = use1 ? a1->C : 0;
   g.kc[0] = a0->C / 64; g.kc[1] = use1 ? a1->C / 64 : 0;
-  dim3 grid(P / (128 * halves), n_out / bn_tile, clients);
+  dim3 grid(P / (128 * halves), n_out / bn_tile, clients * n_cls);
   cudaStream_t st = as_stream(stream);
 #define NFB_RN_CASE(MN, BNV, HV)                                                     \
   if ((dgrad != 0) == MN && bn_tile == BNV && halves == HV)                          \
@@ -681,8 +720,8 @@ int nfb_rn_conv_wgrad(const nfb_rn_act* x, const nfb_rn_act* dy, int clients, in
               "rn_conv_wgrad: the fused update needs the complete gradient (k_split == 1)");
   g.sgd_w = sgd_w; g.sgd_wt = static_cast<__nv_bfloat16*>(sgd_wt); g.lr = lr; g.wd = wd;
   for (int t = 0; t < n_taps; ++t)
-    g.tap[t] = Tap{taps[6 * t], taps[6 * t + 1], taps[6 * t + 2], taps[6 * t + 3], taps[6 * t + 4],
-                   taps[6 * t + 5]};
+    g.tap[t] = Tap{taps[7 * t], taps[7 * t + 1], taps[7 * t + 2], taps[7 * t + 3], taps[7 * t + 4],
+                   taps[7 * t + 5], -1};
   CUtensorMap mx, mdy;
   int rc = act_map(x, posk, &mx);
   if (rc) return rc;

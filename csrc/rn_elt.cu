@@ -9,7 +9,8 @@
 //                the main branch and optionally the projection shortcut's BatchNorm at once
 //   bn_bwd_apply dx = gamma * rstd * (g - dbeta / n - xhat * dgamma / n)
 //   head         global average pool -> fc -> log-softmax / NLL / accuracy -> dlogits -> fc
-//                gradients -> gradient of the pooled features broadcast back over the 4x4 grid
+//                gradients -> gradient of the pooled features broadcast back over the 4x4 grid and
+//                masked by the ReLU of the feature map (gradient w.r.t. the pre-ReLU block output)
 //   wm_convert   conv weights between the arena's torch layout [co][ci][kh][kw] and the engine's
 //                tap-major fp32 master + bf16 working copy [tap][co][ci] (once per round each way)
 //   tap_sgd      SGD (momentum, weight decay) on tap-major ranges whose gradient the wgrad kernel
@@ -387,9 +388,12 @@ __global__ void __launch_bounds__(512)
       df = fmaf(dl[s * NC + j], w[j], df);
       dwj[j] = fmaf(dl[s * NC + j], pooled[s], dwj[j]);
     }
-    const __nv_bfloat16 o = __float2bfloat16_rn(df * inv_pp);
-    __nv_bfloat16* dst = dfeat + ((static_cast<long long>(g) * B + b0 + s) * pp) * F + f;
-    for (int p = 0; p < pp; ++p) dst[static_cast<long long>(p) * F] = o;
+    // gradient w.r.t. the PRE-ReLU block output: zero where the feature was clipped by the ReLU
+    const __nv_bfloat16 o = __float2bfloat16_rn(df * inv_pp), zero = __float2bfloat16_rn(0.f);
+    const long long base = ((static_cast<long long>(g) * B + b0 + s) * pp) * F + f;
+    for (int p = 0; p < pp; ++p)
+      dfeat[base + static_cast<long long>(p) * F] =
+          __bfloat162float(feat[base + static_cast<long long>(p) * F]) > 0.f ? o : zero;
   }
 #pragma unroll
   for (int j = 0; j < NC; ++j) atomicAdd(grow + dw_off + j * F + f, dwj[j]);

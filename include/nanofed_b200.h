@@ -318,17 +318,22 @@ typedef struct {
   const void* ptr;
   int imgs, H, W, C, parity;
 } nfb_rn_act;
-/* taps: n_taps x {dh, dw, ph, pw, wrow, src}: row/column shift of the A box, parity of the A view,
- * first weight row of the tap, operand pair (0 | 1).  dgrad = 0: out[pos, n] = sum A[pos+tap, k] *
+/* taps: n_taps x {dh, dw, ph, pw, wrow, src, cls}: row/column shift of the A box, parity of the A
+ * view, first weight row of the tap, operand pair (0 | 1), output parity class 2*ph_out + pw_out the
+ * tap contributes to (used with n_cls = 4: the four classes of a stride-2 data gradient in one
+ * launch; -1 / n_cls = 1: every tap counts and out_ph / out_pw select the class).  dgrad = 0: out[pos, n] = sum A[pos+tap, k] *
  * W[wrow + n][k] (weights K-major); dgrad = 1: ... * W[wrow + k][n].  w_dims = {inner, rows, client
  * stride} per pair.  H x W is the position grid of the output; stats (optional) receives per
  * client the per-channel sum and sum of squares of the stored bf16 values ([clients][2][n_out],
- * fp32 atomics); residual (+ optional ReLU mask) is added before the store.                   */
+ * fp32 atomics); residual (+ optional ReLU mask) is added before the store; out_mask (dense
+ * tensor of the output's shape) zeroes the stored value where it is not positive (the ReLU
+ * backward of the layer the gradient flows into).                                             */
 int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, const void* w0,
                      const void* w1, const int* w_dims, int clients, int imgs_per_client, int H,
                      int W, int n_out, int n_taps, const int* taps, const nfb_rn_act* out,
                      int out_ph, int out_pw, float* stats, const void* residual,
-                     const void* res_mask, int bn_tile, int halves, int* status, void* stream);
+                     const void* res_mask, const void* out_mask, int bn_tile, int halves,
+                     int n_cls, int* status, void* stream);
 /* out[client][tap][co][ci] (+)= sum_pos x[pos + tap][ci] * dy[pos][co]; k_split > 1 adds with fp32
  * atomics (the target must then be zero).  With k_split == 1 and sgd_w != NULL the gradient is not
  * written at all: the epilogue applies w -= lr * (dW + wd * w) to the tap-major fp32 master sgd_w

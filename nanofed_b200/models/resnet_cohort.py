@@ -7,7 +7,8 @@ whatever the client count, and a local epoch is one CUDA graph.  No autograd, no
 
     forward   im2col(3x3x3 stem) → [conv (tcgen05, BN batch sums in the epilogue) → BN+ReLU
               (+ residual | + BN(projection))]* → avg-pool + fc + cross-entropy (one kernel)
-    backward  per BatchNorm: reduce (dγ, dβ with the ReLU mask applied on the fly) + apply;
+    backward  per BatchNorm: reduce (dγ, dβ) + apply; every ReLU backward is a mask in the epilogue
+              of the kernel that PRODUCES the gradient (head, dgrad), never a separate operand;
               per conv: wgrad (tcgen05, both operands MN-major, tap-major fp32 result) and dgrad
               (tcgen05; stride 2 = four parity-class launches, the 1×1 projection's gradient rides
               in the k-loop of class (0,0); identity shortcuts are added in the dgrad epilogue)
@@ -180,6 +181,7 @@ class ResNetCohortNet:
         self.tap_ranges = torch.tensor(ranges or [(0, 0)], dtype=torch.int64, device=dev)
         self.tap_max = max((r[1] for r in ranges), default=0)
         self._tile_override = os.environ.get("NFB_RN_TILE")   # "bn,halves" for experiments
+        self._wgrad_posk = int(os.environ.get("NFB_RN_WGRAD_K", "0"))   # 0 = per-layer choice
 
     # ---- helpers ---------------------------------------------------------------------------
     def _view(self, i: int, h: int, c: int) -> torch.Tensor:
@@ -213,6 +215,14 @@ class ResNetCohortNet:
             return 1
         return max(1, min(kb_total // 4 if kb_total >= 4 else 1, self.sms // tiles))
 
+    def _posk(self, c: _Conv) -> int:
+        """Positions per k-block of the wgrad kernel.  64 keeps two CTAs on an SM, which pays where
+        the k-loop is short and the epilogue (fused SGD over 128 x 256 weights) is not: the
+        512-channel layers (246 vs 339 us for the three 512->512 convs); elsewhere 128 wins."""
+        if self._wgrad_posk:
+            return self._wgrad_posk
+        return 64 if c.cout >= 512 else 128
+
     def _wgrad(self, c: _Conv, x: torch.Tensor, dy: torch.Tensor) -> None:
         """Weight gradient of ``c`` — call AFTER the data gradient that reads the old weights."""
         k_split = self._ksplit[c.name]
@@ -221,23 +231,26 @@ class ResNetCohortNet:
                if self.fuse_sgd and k_split == 1 else None)
         rn.conv_wgrad(x, dy, self.dwt, c.t_off, clients=self.g,
                       taps=rn.fwd_taps(c.k, c.stride, c.cout), x_parity=c.stride == 2,
-                      k_split=k_split, tile=(min(c.cout, 256), 128), sgd=sgd)
+                      k_split=k_split, tile=(min(c.cout, 256), self._posk(c)), sgd=sgd)
 
-    def _dgrad(self, c: _Conv, dy: torch.Tensor, dx: torch.Tensor, *, residual=None, res_mask=None,
-               sc: _Conv | None = None, dy_sc: torch.Tensor | None = None) -> None:
+    def _dgrad(self, c: _Conv, dy: torch.Tensor, dx: torch.Tensor, *, relu_of: torch.Tensor,
+               residual=None, sc: _Conv | None = None, dy_sc: torch.Tensor | None = None) -> None:
+        """Gradient w.r.t. the PRE-ReLU value of the conv's input: ``relu_of`` is that (activated)
+        input, its ReLU mask is applied in the epilogue; ``residual`` (an already masked gradient
+        arriving over an identity shortcut) is added before the mask."""
         if c.stride == 1:
             rn.conv_gemm(True, dy, self._wref(c), dx, clients=self.g, grid_hw=(c.hin, c.hin),
-                         taps=rn.dgrad_taps(c.k, 1, c.cout), residual=residual, res_mask=res_mask,
+                         taps=rn.dgrad_taps(c.k, 1, c.cout), residual=residual, out_mask=relu_of,
                          n_out=c.cin, tile=self._tile(self.b * c.hin * c.hin, c.cin))
             return
         assert residual is None
-        for cls in ((0, 0), (0, 1), (1, 0), (1, 1)):
-            taps = rn.dgrad_taps(c.k, 2, c.cout, cls)
-            extra = rn.dgrad_taps(1, 2, sc.cout, cls, src=1) if sc is not None else []
-            rn.conv_gemm(True, dy, self._wref(c), dx, clients=self.g, grid_hw=(c.hout, c.hout),
-                         taps=taps + extra, out_parity=cls, a1=dy_sc if extra else None,
-                         w1=self._wref(sc) if extra else None, n_out=c.cin,
-                         tile=self._tile(self.b * c.hout * c.hout, c.cin))
+        # the four output parity classes in ONE launch (grid.z = class x client); the 1x1 projection
+        # shortcut's gradient rides in the k-loop of class (0, 0)
+        rn.conv_gemm(True, dy, self._wref(c), dx, clients=self.g, grid_hw=(c.hout, c.hout),
+                     taps=rn.dgrad_taps_all_classes(c.k, c.cout, sc.cout if sc is not None else None),
+                     out_parity=(0, 0), all_classes=True, a1=dy_sc, w1=self._wref(sc) if sc else None,
+                     out_mask=relu_of, n_out=c.cin,
+                     tile=self._tile(self.b * c.hout * c.hout, c.cin))
 
     # ---- hooks used by FedSimulation ---------------------------------------------------------
     def after_broadcast(self) -> None:
@@ -299,33 +312,35 @@ class ResNetCohortNet:
             kw = dict(clients=g, x2=u["rawsc"] if proj else None,
                       stats2=self._bn_stats(blk.bn_sc) if proj else None,
                       bn2_offs=blk.bn_sc.offs if proj else None)
-            rn.bn_bwd(False, dout, u["out"], u["raw2"], slots, self.sgrad, offs,
+            # dout is already the gradient w.r.t. the pre-ReLU block output (its producer - the
+            # head or the next block's dgrad epilogue - applied the mask): no mask operand here
+            rn.bn_bwd(False, dout, None, u["raw2"], slots, self.sgrad, offs,
                       self._bn_stats(blk.bn2), blk.bn2.offs, **kw)
-            rn.bn_bwd(True, dout, u["out"], u["raw2"], slots, self.sgrad, offs,
+            rn.bn_bwd(True, dout, None, u["raw2"], slots, self.sgrad, offs,
                       self._bn_stats(blk.bn2), blk.bn2.offs, dx=dc2, dx2=dcs, **kw)
             da = self._view(4, ho, w)
-            self._dgrad(blk.conv2, dc2, da)               # reads the old weights: before the wgrad
+            self._dgrad(blk.conv2, dc2, da, relu_of=u["a"])   # reads the old weights: before the wgrad
             self._wgrad(blk.conv2, u["a"], dc2)
             dc1 = dc2                                     # dc2 is dead after the two launches above
             offs1 = (blk.bn1.g_off[0], blk.bn1.g_off[1], 0, 0)
-            rn.bn_bwd(False, da, u["a"], u["raw1"], slots, self.sgrad, offs1,
+            rn.bn_bwd(False, da, None, u["raw1"], slots, self.sgrad, offs1,
                       self._bn_stats(blk.bn1), blk.bn1.offs, clients=g)
-            rn.bn_bwd(True, da, u["a"], u["raw1"], slots, self.sgrad, offs1,
+            rn.bn_bwd(True, da, None, u["raw1"], slots, self.sgrad, offs1,
                       self._bn_stats(blk.bn1), blk.bn1.offs, clients=g, dx=dc1)
             dx = self._view(d1, hin, cin)
             if proj:
-                self._dgrad(blk.conv1, dc1, dx, sc=blk.conv_sc, dy_sc=dcs)
+                self._dgrad(blk.conv1, dc1, dx, relu_of=u["in"], sc=blk.conv_sc, dy_sc=dcs)
                 self._wgrad(blk.conv_sc, u["in"], dcs)
             else:
-                self._dgrad(blk.conv1, dc1, dx, residual=dout, res_mask=u["out"])
+                self._dgrad(blk.conv1, dc1, dx, relu_of=u["in"], residual=dout)
             self._wgrad(blk.conv1, u["in"], dc1)
             d0, d1 = d1, d0
         dout = self._view(d0, 32, 64)
         dc0 = self._view(2, 32, 64)
         offs0 = (self.stem_bn.g_off[0], self.stem_bn.g_off[1], 0, 0)
-        rn.bn_bwd(False, dout, self.a0, self.raw0, slots, self.sgrad, offs0,
+        rn.bn_bwd(False, dout, None, self.raw0, slots, self.sgrad, offs0,
                   self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g)
-        rn.bn_bwd(True, dout, self.a0, self.raw0, slots, self.sgrad, offs0,
+        rn.bn_bwd(True, dout, None, self.raw0, slots, self.sgrad, offs0,
                   self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g, dx=dc0)
         self._wgrad(self.stem, self.xcol, dc0)
         # ---------------- update ----------------

@@ -36,7 +36,7 @@ def _lib() -> C.CDLL:
         pa, pi, pll = C.POINTER(_Act), C.POINTER(C.c_int), C.POINTER(C.c_longlong)
         sigs = {
             "nfb_rn_conv_gemm": [i32, pa, pa, vp, vp, pi, i32, i32, i32, i32, i32, i32, pi, pa, i32,
-                                 i32, vp, vp, vp, i32, i32, vp, vp],
+                                 i32, vp, vp, vp, vp, i32, i32, i32, vp, vp],
             "nfb_rn_conv_wgrad": [pa, pa, i32, i32, i32, pi, vp, ll, i32, i32, i32, vp, vp, f32, f32,
                                   vp, vp],
             "nfb_rn_im2col3": [vp, ll, i32, i32, vp, vp],
@@ -117,8 +117,21 @@ def dgrad_taps(ksize: int, stride: int, cout: int, cls: tuple[int, int] = (0, 0)
 
 
 def _tap_array(taps: list[tuple[int, ...]]):
-    flat = [v for t in taps for v in t]
+    """7 ints per tap for the C side: the 6 documented above + the output parity class (-1 = all)."""
+    flat = [v for t in taps for v in (tuple(t) + (-1,))[:7]]
     return (C.c_int * len(flat))(*flat)
+
+
+def dgrad_taps_all_classes(ksize: int, cout: int, sc_cout: int | None = None) -> list[tuple[int, ...]]:
+    """Taps of a stride-2 data gradient for ALL four output parity classes (7th entry = class
+    2·row_parity + col_parity), plus the 1x1 projection shortcut's tap (operand pair 1) in class 0."""
+    taps: list[tuple[int, ...]] = []
+    for cls in ((0, 0), (0, 1), (1, 0), (1, 1)):
+        idx = 2 * cls[0] + cls[1]
+        taps += [t + (idx,) for t in dgrad_taps(ksize, 2, cout, cls)]
+        if sc_cout is not None:
+            taps += [t + (idx,) for t in dgrad_taps(1, 2, sc_cout, cls, src=1)]
+    return taps
 
 
 @dataclass
@@ -169,7 +182,8 @@ def conv_gemm(
     a_parity: bool = False, out_parity: tuple[int, int] | None = None,
     a1: torch.Tensor | None = None, w1: WeightRef | None = None,
     stats: torch.Tensor | None = None, residual: torch.Tensor | None = None,
-    res_mask: torch.Tensor | None = None, n_out: int, tile: tuple[int, int] | None = None,
+    res_mask: torch.Tensor | None = None, out_mask: torch.Tensor | None = None, n_out: int,
+    tile: tuple[int, int] | None = None, all_classes: bool = False,
 ) -> None:
     """``out[pos, n] = Σ_taps A[pos + tap, :] · W`` on tensor cores (see ``csrc/rn_conv.cu``)."""
     lib = _lib()
@@ -182,14 +196,15 @@ def conv_gemm(
     wd0 = list(w.dims) + (list(w1.dims) if w1 is not None else [0, 0, 0])
     dims = (C.c_int * 6)(*wd0)
     oph, opw = out_parity if out_parity is not None else (0, 0)
+    assert not all_classes or out_parity is not None, "all_classes needs a parity-view output"
     if stats is not None:
         assert stats.dtype == torch.float32 and stats.shape == (clients, 2, n_out)
     st = status_word(a.device)
     code = lib.nfb_rn_conv_gemm(
         1 if dgrad else 0, C.byref(a0), C.byref(a1s) if a1s is not None else None, w.ptr,
         w1.ptr if w1 is not None else None, dims, clients, imgs, h, wd, n_out, len(taps),
-        _tap_array(taps), C.byref(o), oph, opw, _ptr(stats), _ptr(residual), _ptr(res_mask), bn,
-        halves, st.data_ptr(), _stream(a))
+        _tap_array(taps), C.byref(o), oph, opw, _ptr(stats), _ptr(residual), _ptr(res_mask),
+        _ptr(out_mask), bn, halves, 4 if all_classes else 1, st.data_ptr(), _stream(a))
     _check(code, "rn_conv_gemm")
 
 

@@ -96,37 +96,40 @@ def check_layer(cin, cout, h, stride, k, clients=2, batch=16, tol=1.2e-2):
     if stride == 1:
         res = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
         msk = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
+        om = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
         rn.conv_gemm(True, dy, wref, dx, clients=clients, grid_hw=(h, h),
-                     taps=rn.dgrad_taps(k, 1, cout), residual=res, res_mask=msk, n_out=cin)
-        want = ref_dx + res.float() * (msk.float() > 0)
+                     taps=rn.dgrad_taps(k, 1, cout), residual=res, res_mask=msk, out_mask=om,
+                     n_out=cin)
+        want = (ref_dx + res.float() * (msk.float() > 0)) * (om.float() > 0)
     else:
         dx.zero_()
+        om = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
         for cls in ((0, 0), (0, 1), (1, 0), (1, 1)):
             taps = rn.dgrad_taps(k, 2, cout, cls)
             if not taps:
                 continue     # 1x1 stride 2: only the even/even pixels receive a gradient
             rn.conv_gemm(True, dy, wref, dx, clients=clients, grid_hw=(ho, ho), taps=taps,
-                         out_parity=cls, n_out=cin)
-        want = ref_dx
+                         out_parity=cls, out_mask=om, n_out=cin)
+        want = ref_dx * (om.float() > 0)
     torch.cuda.synchronize()
     e = rel(dx, want)
     good = e < tol and canaries_ok(raw, dx.numel())
     ok &= good
     print(f"  dgrad {name}: rel {e:.2e}  {'ok' if good else 'FAIL'}")
     # ---------------- wgrad ----------------
-    for k_split in (1, 3):
+    for k_split, posk in ((1, 128), (3, 128), (1, 64)):
         n = k * k * cout * cin
         raw, dwt = guarded((clients, n + 128), torch.float32)
         dwt.zero_()
         rn.conv_wgrad(x, dy, dwt, 64, clients=clients, taps=rn.fwd_taps(k, stride, cout),
-                      x_parity=stride == 2, k_split=k_split)
+                      x_parity=stride == 2, k_split=k_split, tile=(min(cout, 256), posk))
         torch.cuda.synchronize()
         got = dwt[:, 64 : 64 + n].view(clients, k, k, cout, cin).permute(0, 3, 4, 1, 2)
         e = rel(got, ref_dw)
         untouched = bool((dwt[:, :64] == 0).all() and (dwt[:, 64 + n :] == 0).all())
         good = e < tol and canaries_ok(raw, dwt.numel()) and untouched
         ok &= good
-        print(f"  wgrad {name} split {k_split}: rel {e:.2e}  {'ok' if good else 'FAIL'}")
+        print(f"  wgrad {name} split {k_split} k-block {posk}: rel {e:.2e}  {'ok' if good else 'FAIL'}")
     tc.check_status(DEV)
     return ok
 
@@ -145,11 +148,11 @@ def check_fused_shortcut(cin=64, cout=128, h=32, clients=2, batch=16, tol=1.2e-2
     buf[:, n3:] = tap_major(w1).reshape(clients, -1)
     r3, r1 = rn.WeightRef(buf, 0, 9 * cout, cin), rn.WeightRef(buf, n3, cout, cin)
     raw, dx = guarded((clients * batch, h, h, cin), torch.bfloat16)
-    for cls in ((0, 0), (0, 1), (1, 0), (1, 1)):
-        taps = rn.dgrad_taps(3, 2, cout, cls)
-        extra = rn.dgrad_taps(1, 2, cout, cls, src=1)
-        rn.conv_gemm(True, dy3, r3, dx, clients=clients, grid_hw=(ho, ho), taps=taps + extra,
-                     out_parity=cls, a1=dy1 if extra else None, w1=r1 if extra else None, n_out=cin)
+    # all four output parity classes in one launch (grid.z = class x client), with an output mask
+    om = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
+    rn.conv_gemm(True, dy3, r3, dx, clients=clients, grid_hw=(ho, ho),
+                 taps=rn.dgrad_taps_all_classes(3, cout, cout), out_parity=(0, 0), all_classes=True,
+                 a1=dy1, w1=r1, out_mask=om, n_out=cin)
     torch.cuda.synchronize()
     want = []
     for g in range(clients):
@@ -160,7 +163,7 @@ def check_fused_shortcut(cin=64, cout=128, h=32, clients=2, batch=16, tol=1.2e-2
         d1 = dy1.float().view(clients, batch, ho, ho, cout)[g].permute(0, 3, 1, 2)
         (y3 * d3).sum().add((y1 * d1).sum()).backward()
         want.append(xi.grad.permute(0, 2, 3, 1))
-    e = rel(dx, torch.cat(want))
+    e = rel(dx, torch.cat(want) * (om.float() > 0))
     good = e < tol and canaries_ok(raw, dx.numel())
     print(f"  dgrad 3x3 s2 + 1x1 s2 shortcut {cin}->{cout}: rel {e:.2e}  {'ok' if good else 'FAIL'}")
     tc.check_status(DEV)
