@@ -34,7 +34,9 @@ for name, lines in kernels.items():
     rows.append((short, len(lines), dict(ops)))
     if any(s in name for s in ("tc_conv", "tc_fc_dgrad", "tc_gemm_kernel<false, 128, false, 128",
                                "tc_gemm_kernel<true, 128, true, 128, 64, 128, 1, 2, 2, 1>",
-                               "fedavg_allreduce_kernel<float>", "fedavg_reduce_kernel<float>", "fc_head")):
+                               "fedavg_allreduce_kernel<float>", "fedavg_reduce_kernel<float>", "fc_head",
+                               "rn_conv_gemm_kernel<false, 128, 2>", "rn_conv_gemm_kernel<true, 64, 2>",
+                               "rn_conv_wgrad_kernel<256, 128>", "tc_gemm_kernel<true, 128, true, 128, 64, 128, 1, 2, 2, 2>")):
         fn = re.sub(r"[^A-Za-z0-9_]+", "_", short)[:80]
         (OUT / f"{fn}.sass").write_text("\n".join(lines))
 with open(OUT / "SUMMARY.md", "w") as f:
