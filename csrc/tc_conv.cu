@@ -39,6 +39,7 @@ constexpr int kSlabRows = 128 + kHalo;
 struct ConvArgs {
   int tiles_per_client;   // ceil(R / 128)
   int ctas_per_client;
+  int client0;            // first client of this launch (a cohort may be covered by several launches)
   int rows;               // R
   int shift[kTaps];       // slab-relative row shift per tap
   void* out;              // bf16 [C, R, N]
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
   __shared__ float s_bias[64];
   __shared__ int s_wg_valid[kMaxEpiWarps];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = blockIdx.x / args.ctas_per_client;
+  const int g = args.client0 + blockIdx.x / args.ctas_per_client;
   const int part = blockIdx.x % args.ctas_per_client;
   if (threadIdx.x < 64)
     s_bias[threadIdx.x] = (!kDgrad<MODE> && args.bias)
@@ -358,7 +359,7 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
         // in the code byte, so the backward pass never regenerates the stream.
         uint4 rnd = make_uint4(~0u, ~0u, ~0u, ~0u);
         if (args.drop_p > 0.f)
-          rnd = Philox::draw((step << 40) + (static_cast<unsigned long long>(blockIdx.x) << 20) +
+          rnd = Philox::draw((step << 40) + (static_cast<unsigned long long>(args.client0 * args.ctas_per_client + blockIdx.x) << 20) +
                                  static_cast<unsigned long long>(i) * 128 + gt,
                              args.seed);
         const uint32_t thresh = static_cast<uint32_t>(args.drop_p * 256.f + 0.5f);
@@ -581,6 +582,7 @@ constexpr size_t kWgSmem = static_cast<size_t>(kWgStages) * kWgStage + 1024 + 25
 struct WgradArgs {
   int kblocks_per_client;  // ceil(R / 64)
   int ctas_per_client;
+  int client0;             // first client of this launch
   int shift[kTaps];        // [kh] = kh * width (entries 0..2 used)
   float* grad;             // first client's [64][32][3][3] block inside the gradient slab
   long long grad_gs;
@@ -602,7 +604,7 @@ __global__ void __launch_bounds__(256, 1)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = blockIdx.x / args.ctas_per_client;
+  const int g = args.client0 + blockIdx.x / args.ctas_per_client;
   const int part = blockIdx.x % args.ctas_per_client;
   const int per = (args.kblocks_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
   const int kb_lo = part * per;
@@ -815,9 +817,35 @@ static int out_map(const void* ptr, long long rows, long long groups, long long 
   return 0;
 }
 
+// With one CTA range per client, 32 clients use 4 x 32 = 128 of 148 SMs (85 tiles per CTA).  Covering
+// the cohort with `n` back-to-back launches of clients / n clients each lets every launch spread
+// its clients over (nearly) all SMs: 2 launches x 16 clients x 9 CTAs = 144 SMs, 2 x 38 tiles.
+// A launch boundary costs about `gap` work units; the plan minimises n * ceil(units / per) + gaps.
+// MEASURED (B200, 32 clients x 64): two launches per kernel make the local step SLOWER, 0.547 vs
+// 0.527 ms (four: 0.641 ms) - a persistent kernel's drain + the next one's prologue (weights by TMA,
+// TMEM allocation, pipeline fill) cost more than the 13 % of idle SMs.  The gaps below encode
+// that (one launch wins for every shape used so far); NFB_CONV_SPLIT=n forces n for A/B runs.
+// Using the idle SMs needs CTA ranges that cross a client boundary inside ONE launch.
+static void plan_split(int clients, int units, int gap, int* n_split, int* per_client) {
+  static const int forced = [] { const char* e = getenv("NFB_CONV_SPLIT"); return e ? atoi(e) : 0; }();
+  int best_n = 1, best_pc = 1;
+  long long best_cost = -1;
+  for (int n = 1; n <= 8; n *= 2) {
+    if (clients % n) break;
+    if (forced && n != forced) continue;
+    int pc = sm_count() / (clients / n);
+    if (pc < 1) pc = 1;
+    if (pc > units) pc = units;
+    const long long cost = static_cast<long long>(n) * ((units + pc - 1) / pc) + static_cast<long long>(gap) * (n - 1);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_n = n; best_pc = pc; }
+  }
+  *n_split = best_n;
+  *per_client = best_pc;
+}
+
 template <int MODE>
 static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mo,
-                       int ctas, const ConvArgs& a, cudaStream_t st) {
+                       int ctas, const ConvArgs& a_in, cudaStream_t st) {
   using C = ConvCfg<MODE>;
   auto kern = tc_conv_kernel<MODE>;
   static bool attr_set = false;
@@ -828,8 +856,19 @@ static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, const CUten
       return fail(static_cast<int>(e), "tc_conv: smem attribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<ctas, 128 + 32 * C::EPI_WARPS, C::SMEM, st>>>(ma, mw, mo, a);
-  return launch_status("tc_conv");
+  const int clients = ctas / a_in.ctas_per_client;
+  int n_split = 1, per_client = a_in.ctas_per_client;
+  plan_split(clients, a_in.tiles_per_client, 16, &n_split, &per_client);
+  ConvArgs a = a_in;
+  a.ctas_per_client = per_client;
+  const int group = clients / n_split;
+  for (int h = 0; h < n_split; ++h) {
+    a.client0 = h * group;
+    kern<<<group * per_client, 128 + 32 * C::EPI_WARPS, C::SMEM, st>>>(ma, mw, mo, a);
+    const int rc = launch_status("tc_conv");
+    if (rc) return rc;
+  }
+  return 0;
 }
 
 }  // namespace tc
@@ -1027,8 +1066,17 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
       return fail(static_cast<int>(e), "tc_conv3x3_wgrad: smem attribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  tc_conv_wgrad_kernel<<<clients * per_client, 256, kWgSmem, as_stream(stream)>>>(mdy, mx, a);
-  return launch_status("tc_conv3x3_wgrad");
+  int n_split = 1;
+  plan_split(clients, a.kblocks_per_client, 32, &n_split, &per_client);
+  a.ctas_per_client = per_client;
+  const int group = clients / n_split;
+  for (int h = 0; h < n_split; ++h) {
+    a.client0 = h * group;
+    tc_conv_wgrad_kernel<<<group * per_client, 256, kWgSmem, as_stream(stream)>>>(mdy, mx, a);
+    const int rc = launch_status("tc_conv3x3_wgrad");
+    if (rc) return rc;
+  }
+  return 0;
 }
 
 // Forward 3x3 conv (32 -> 64 ch) + bias + ReLU + 2x2 max-pool + dropout in ONE kernel; the conv
