@@ -36,8 +36,10 @@ __device__ __forceinline__ float agg_prologue(float* __restrict__ coef, int K,
 }
 
 // acc[0..V) = sum_k coef[k] * x[k, col .. col+V)   (col = 16-byte column group)
-template <typename T>
-__device__ __forceinline__ void column_reduce(const T* __restrict__ x, int64_t row_stride,
+// NC = false: plain loads instead of the non-coherent path, for launches that write the rows they
+// read (K-AGG fused with K-BCAST replicates the result into the client rows in place).
+template <typename T, bool NC = true>
+__device__ __forceinline__ void column_reduce(const T* x, int64_t row_stride,
                                               int K, const float* __restrict__ coef,
                                               int64_t col, float* acc) {
   constexpr int V = Vec16<T>::N;
@@ -50,7 +52,9 @@ __device__ __forceinline__ void column_reduce(const T* __restrict__ x, int64_t r
 #pragma unroll
     for (int u = 0; u < kAggUnroll; ++u) {
       // A zero coefficient means "client absent": do not touch its row at all.
-      r[u] = (coef[k + u] != 0.f) ? ld_stream(p + (k + u) * row_stride) : make_uint4(0, 0, 0, 0);
+      r[u] = (coef[k + u] != 0.f) ? (NC ? ld_stream(p + (k + u) * row_stride)
+                                        : ld_plain(p + (k + u) * row_stride))
+                                  : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
     for (int u = 0; u < kAggUnroll; ++u) {
@@ -65,7 +69,7 @@ __device__ __forceinline__ void column_reduce(const T* __restrict__ x, int64_t r
     const float c = coef[k];
     if (c == 0.f) continue;
     float f[V];
-    unpack<T>(ld_stream(p + k * row_stride), f);
+    unpack<T>(NC ? ld_stream(p + k * row_stride) : ld_plain(p + k * row_stride), f);
 #pragma unroll
     for (int e = 0; e < V; ++e) acc[e] = fmaf(c, f[e], acc[e]);
   }

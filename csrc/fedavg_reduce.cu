@@ -29,6 +29,7 @@ struct AggEpilogue {
   void* out_lowp;
   int lowp_dtype;
   bool accumulate;
+  nfb_bcast_target bc;        // rows > 0: K-BCAST fused - replicate the result into the client rows
 };
 
 // Noise + accumulate + store for V consecutive outputs starting at col (col % 4 == 0).
@@ -66,6 +67,28 @@ __device__ __forceinline__ void agg_store(const AggEpilogue& ep, float sigma, in
     }
     *o = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
   }
+  if (ep.bc.rows > 0) {
+    // K-BCAST in the same pass: the finished columns go straight into every client's fp32 row and
+    // bf16 working copy, and the optimiser state of the next round starts at zero.  The rows may
+    // be the very rows this thread has just reduced (same column, same thread: no hazard).
+#pragma unroll
+    for (int q = 0; q < V / 4; ++q) {
+      const float4 v = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+      uint2 pk;
+      pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+      pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+      const int64_t c4 = col + 4 * q;
+      for (int64_t k = 0; k < ep.bc.rows; ++k) {
+        if (ep.bc.slots) *reinterpret_cast<float4*>(ep.bc.slots + k * ep.bc.slots_stride + c4) = v;
+        if (ep.bc.lowp)
+          *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(ep.bc.lowp) + k * ep.bc.lowp_stride + c4) = pk;
+        if (ep.bc.momentum)
+          *reinterpret_cast<float4*>(ep.bc.momentum + k * ep.bc.momentum_stride + c4) =
+              make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
   if (ep.out_lowp) {
     if (ep.lowp_dtype == NFB_DT_BF16) {
       __nv_bfloat16* o = static_cast<__nv_bfloat16*>(ep.out_lowp) + col;
@@ -81,9 +104,9 @@ __device__ __forceinline__ void agg_store(const AggEpilogue& ep, float sigma, in
   }
 }
 
-template <typename T>
+template <typename T, bool BCAST>
 __global__ void __launch_bounds__(kAggThreads)
-    fedavg_reduce_kernel(const T* __restrict__ x, int K, int64_t N, int64_t row_stride,
+    fedavg_reduce_kernel(const T* x, int K, int64_t N, int64_t row_stride,
                          const float* __restrict__ counts, const float* __restrict__ sumsq,
                          const float* __restrict__ mask, float clip_norm, bool normalise,
                          AggEpilogue ep) {
@@ -93,15 +116,22 @@ __global__ void __launch_bounds__(kAggThreads)
   float total = 0.f;
   const float w2 = agg_prologue(coef, K, counts, sumsq, mask, clip_norm, normalise, red, &total);
   // every client masked out (dropped, screened as non-finite, all stragglers): there is nothing
-  // to average - keep the previous global model instead of overwriting it with zeros
-  if (normalise && !(total > 0.f)) return;
-  const float sigma = ep.noise_std > 0.f ? ep.noise_std * sqrtf(w2) : 0.f;
+  // to average - keep the previous global model instead of overwriting it with zeros (with the
+  // fused broadcast the unchanged model still has to reach the client rows)
+  const bool keep = normalise && !(total > 0.f);
+  if (keep && !BCAST) return;
+  const float sigma = (ep.noise_std > 0.f && !keep) ? ep.noise_std * sqrtf(w2) : 0.f;
 
   const int64_t groups = N / V;  // N % V == 0 enforced by the host wrapper
   for (int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; g < groups;
        g += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     float acc[V];
-    column_reduce<T>(x, row_stride, K, coef, g * V, acc);
+    if (BCAST && keep) {
+#pragma unroll
+      for (int e = 0; e < V; ++e) acc[e] = ep.out[g * V + e];
+    } else {
+      column_reduce<T, !BCAST>(x, row_stride, K, coef, g * V, acc);
+    }
     agg_store<V>(ep, sigma, g * V, acc);
   }
 }
@@ -115,7 +145,7 @@ extern "C" int nfb_fedavg_reduce(const void* x, int x_dtype, int64_t K, int64_t 
                                  uint64_t seed, uint64_t offset, float* out, void* out_lowp,
                                  int lowp_dtype, int flags, void* reserved, void* stream) {
   using namespace nfb;
-  (void)reserved;
+  const nfb_bcast_target* bc = static_cast<const nfb_bcast_target*>(reserved);
   NFB_REQUIRE(x && counts && out, NFB_EINVAL, "fedavg_reduce: null pointer");
   NFB_REQUIRE(K >= 1 && K <= 12000, NFB_ERANGE, "fedavg_reduce: K=%lld outside [1, 12000]",
               static_cast<long long>(K));
@@ -142,6 +172,17 @@ extern "C" int nfb_fedavg_reduce(const void* x, int x_dtype, int64_t K, int64_t 
   ep.out_lowp = out_lowp;
   ep.lowp_dtype = lowp_dtype;
   ep.accumulate = (flags & 2) != 0;
+  ep.bc = nfb_bcast_target{};
+  if (bc && bc->rows > 0) {
+    NFB_REQUIRE(!ep.accumulate, NFB_EINVAL, "fedavg_reduce: a partial sum cannot be broadcast");
+    NFB_REQUIRE((!bc->slots || aligned16(bc->slots)) && (!bc->momentum || aligned16(bc->momentum)) &&
+                    (!bc->lowp || (reinterpret_cast<uintptr_t>(bc->lowp) & 7u) == 0) &&
+                    (bc->slots_stride & 7) == 0 && (bc->lowp_stride & 7) == 0 &&
+                    (bc->momentum_stride & 7) == 0,
+                NFB_EINVAL, "fedavg_reduce: misaligned broadcast target");
+    ep.bc = *bc;
+  }
+  const bool do_bcast = ep.bc.rows > 0;
   const bool normalise = (flags & 1) != 0;
   cudaStream_t st = as_stream(stream);
   const size_t smem = static_cast<size_t>(K) * sizeof(float);
@@ -153,9 +194,14 @@ extern "C" int nfb_fedavg_reduce(const void* x, int x_dtype, int64_t K, int64_t 
     int64_t blocks = (groups + kAggThreads - 1) / kAggThreads;
     const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
     if (blocks > cap) blocks = cap;
-    fedavg_reduce_kernel<T><<<static_cast<int>(blocks), kAggThreads, smem, st>>>(
-        static_cast<const T*>(x), static_cast<int>(K), N, row_stride, counts, sumsq, mask,
-        clip_norm, normalise, ep);
+    if (do_bcast)
+      fedavg_reduce_kernel<T, true><<<static_cast<int>(blocks), kAggThreads, smem, st>>>(
+          static_cast<const T*>(x), static_cast<int>(K), N, row_stride, counts, sumsq, mask,
+          clip_norm, normalise, ep);
+    else
+      fedavg_reduce_kernel<T, false><<<static_cast<int>(blocks), kAggThreads, smem, st>>>(
+          static_cast<const T*>(x), static_cast<int>(K), N, row_stride, counts, sumsq, mask,
+          clip_norm, normalise, ep);
     return launch_status("fedavg_reduce");
   });
 }

@@ -106,11 +106,24 @@ int nfb_segment_sumsq(const void* x, int x_dtype, int64_t K, int64_t row_stride,
  * orchestration/coordinator.py:307-322, server/aggregator/fedavg.py:53-63,
  * privacy/mechanisms.py:85-129 (via aggregator/privacy.py:179-194,322-335,88-92).
  */
+/* Optional K-BCAST target of nfb_fedavg_reduce (host struct passed as `bcast`): the finished
+ * columns are also written into `rows` client rows (fp32 and/or bf16) and `rows` momentum rows are
+ * zeroed, in the same pass - the next round's broadcast + optimizer reset
+ * (examples/mnist/run_experiment.py:65-73) without a second kernel.  The rows may be x itself.  */
+typedef struct {
+  float* slots;
+  int64_t slots_stride;
+  void* lowp;               /* bf16 rows */
+  int64_t lowp_stride;
+  float* momentum;
+  int64_t momentum_stride;
+  int64_t rows;
+} nfb_bcast_target;
 int nfb_fedavg_reduce(const void* x, int x_dtype, int64_t K, int64_t N, int64_t row_stride,
                       const float* counts, const float* sumsq, const float* mask,
                       float clip_norm, float noise_std, const uint8_t* noise_mask,
                       const float* unit_noise, uint64_t seed, uint64_t offset, float* out,
-                      void* out_lowp, int lowp_dtype, int flags, void* reserved, void* stream);
+                      void* out_lowp, int lowp_dtype, int flags, void* bcast, void* stream);
 
 /* ---- K-BCAST ---------------------------------------------------------------
  * Replicate the fp32 global vector into K client slots (fp32 and/or bf16 working

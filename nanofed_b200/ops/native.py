@@ -243,6 +243,12 @@ def segment_sumsq(x: torch.Tensor, segments: torch.Tensor) -> torch.Tensor:
 # ---------------------------------------------------------------------------
 # K-AGG
 # ---------------------------------------------------------------------------
+class _BcastTarget(C.Structure):
+    _fields_ = [("slots", C.c_void_p), ("slots_stride", C.c_int64), ("lowp", C.c_void_p),
+                ("lowp_stride", C.c_int64), ("momentum", C.c_void_p),
+                ("momentum_stride", C.c_int64), ("rows", C.c_int64)]
+
+
 def fedavg_reduce(
     x: torch.Tensor,
     counts: torch.Tensor,
@@ -259,7 +265,10 @@ def fedavg_reduce(
     unit_noise: torch.Tensor | None = None,
     normalize: bool = True,
     accumulate: bool = False,
+    bcast: tuple | None = None,
 ) -> torch.Tensor:
+    """``bcast=(slots, slots_lowp, momentum)`` (each optional): K-BCAST fused into the same launch —
+    the result is replicated into the client rows / bf16 copies and the momentum rows are zeroed."""
     assert x.dim() == 2 and x.stride(1) == 1, "x must be [K, N] with unit inner stride"
     k, n = x.shape
     dev = x.device
@@ -277,6 +286,14 @@ def fedavg_reduce(
     if unit_noise is not None:
         unit_noise = unit_noise.to(device=dev, dtype=torch.float32).contiguous()
     lowp_dt = _dt(out_lowp) if out_lowp is not None else 1
+    target = None
+    if bcast is not None:
+        b_slots, b_lowp, b_mom = bcast
+        rows = next(t.shape[0] for t in (b_slots, b_lowp, b_mom) if t is not None)
+        target = _BcastTarget(
+            _ptr(b_slots), b_slots.stride(0) if b_slots is not None else 0,
+            _ptr(b_lowp), b_lowp.stride(0) if b_lowp is not None else 0,
+            _ptr(b_mom), b_mom.stride(0) if b_mom is not None else 0, rows)
     _check(
         lib().nfb_fedavg_reduce(
             x.data_ptr(), _dt(x), k, n, x.stride(0),
@@ -285,7 +302,7 @@ def fedavg_reduce(
             seed & (2**64 - 1), offset,
             out.data_ptr(), _ptr(out_lowp), lowp_dt,
             (1 if normalize else 0) | (2 if accumulate else 0),
-            None, _stream(x),
+            C.byref(target) if target is not None else None, _stream(x),
         ),
         "fedavg_reduce",
     )

@@ -107,6 +107,7 @@ def fedavg_reduce(
     unit_noise: torch.Tensor | None = None,
     normalize: bool = True,
     accumulate: bool = False,
+    bcast: tuple | None = None,
 ) -> torch.Tensor:
     """``out[j] (+)= Σ_k w_k c_k x[k,j] + noise_std·sqrt(Σ w_k²)·z[j]·noise_mask[j]``.
 
@@ -117,6 +118,8 @@ def fedavg_reduce(
     k, n = x.shape
     eff = counts.to(torch.float32) * (mask.to(torch.float32) if mask is not None else 1.0)
     if normalize and out is not None and not bool(eff.sum() > 0):
+        if bcast is not None:
+            bcast_global(out, *bcast)
         return out          # every client masked out: keep the previous model (as the kernels do)
     coef, w2 = agg_coefficients(counts, sumsq, mask, clip_norm, normalize)
     acc = (coef.view(k, 1).to(torch.float32) * x.to(torch.float32)).sum(dim=0)
@@ -139,6 +142,8 @@ def fedavg_reduce(
         out.copy_(acc)
     if out_lowp is not None:
         out_lowp.copy_(out.to(out_lowp.dtype))
+    if bcast is not None:        # K-BCAST fused into the aggregation (native: same launch)
+        bcast_global(out, *bcast)
     return out
 
 

@@ -67,6 +67,10 @@ class CohortConfig:
     # transport="peer" fails loudly when the symmetric allocation / fused kernel cannot be set up;
     # True lets it degrade to the NCCL baseline instead (logged, and visible as agg_path)
     allow_nccl_fallback: bool = False
+    # Single-GPU rounds: K-BCAST (replication of the new global model into the client rows + the
+    # optimizer-state reset) runs inside the aggregation kernel, so a steady-state round has no
+    # broadcast launch at all.  False keeps the client rows as trained after a round (debugging).
+    fuse_bcast: bool = True
     privacy: PrivacyConfig | None = None  # central DP fused into K-AGG
     # Seed of the DP noise stream.  None (default): drawn from os.urandom on rank 0 and shared with
     # the other ranks, so the noise cannot be regenerated from the configuration.  A fixed value is
@@ -548,7 +552,9 @@ class FedSimulation:
         arena, cfg = self.arena, self.cfg
         arena.stats.zero_()
         with self.timer.phase("bcast"):
-            ops.bcast_global(arena.master, arena.slots, arena.slots_lowp, arena.momentum)
+            if not getattr(self, "_slots_fresh", False):
+                ops.bcast_global(arena.master, arena.slots, arena.slots_lowp, arena.momentum)
+            self._slots_fresh = False
             self.engine.after_broadcast()
         late = self._train_with_deadline()
         with self.timer.phase("aggregate"):
@@ -585,8 +591,12 @@ class FedSimulation:
                 saved = arena.mask.clone()
                 arena.mask.copy_(mask)
             if self.reducer is None:
+                fuse = cfg.fuse_bcast and self.device.type == "cuda" and not cfg.screen_nonfinite
+                if fuse:     # the client rows leave this launch holding the NEW global model
+                    kw["bcast"] = (arena.slots, arena.slots_lowp, arena.momentum)
                 ops.fedavg_reduce(arena.slots, arena.counts, out=arena.master,
                                   out_lowp=arena.master_lowp, mask=arena.mask, **kw)
+                self._slots_fresh = fuse
             else:
                 self.reducer.reduce(arena, **kw)
             if mask is not None:
@@ -812,6 +822,7 @@ class FedSimulation:
         host = self.layout.flatten(state, device="cpu")
         self.arena.master.copy_(host.to(self.device))
         self.arena.master_lowp.copy_(self.arena.master)
+        self._slots_fresh = False        # the client rows no longer hold this model
 
     def global_state(self) -> dict[str, torch.Tensor]:
         return self.arena.global_state()

@@ -20,7 +20,9 @@ def test_grouped_bf16_engine_converges_like_the_fp32_reference_recipe():
     assert last["reference_fp32"]["accuracy"] > first["reference_fp32"]["accuracy"] + 0.15, s
     assert last["reference_fp32"]["loss"] < first["reference_fp32"]["loss"] - 0.1, s
     assert s["final_loss_rel_diff"] < 0.02, s
-    assert s["final_accuracy_diff"] < 0.01, s
+    # measured 0.0002-0.005; the accuracy curve climbs ~3 points per round here, so 2 points is
+    # less than one round of head start
+    assert s["final_accuracy_diff"] < 0.02, s
 
 
 def test_fp32_compute_is_never_silently_bf16():

@@ -254,3 +254,57 @@ def test_cuda_tensor_without_library_is_loud(monkeypatch):
     monkeypatch.setenv("NANOFED_B200_LIB", "/nonexistent/lib.so")
     with pytest.raises(native.NativeLibraryError):
         ops.update_stats(torch.zeros(1, 64, device=DEV))
+
+
+def test_fedavg_reduce_with_fused_broadcast_equals_two_kernels():
+    """K-AGG + K-BCAST in one launch: the client rows it reads are overwritten in place with the
+    new global model (fp32 + bf16), momentum rows are zeroed; DP noise and masks included; with
+    every client masked out the OLD model is what gets broadcast."""
+    from nanofed_b200 import ops
+
+    torch.manual_seed(4)
+    k, n = 6, 70_016
+    slots = torch.randn(k, n, device="cuda")
+    counts = torch.randint(1, 90, (k,), device="cuda").float()
+    mask = torch.ones(k, device="cuda")
+    mask[2] = 0
+    slots[2] = float("nan")                      # masked rows are never read
+    kw = dict(mask=mask, noise_std=0.1, seed=9, offset=128)
+    want = ops.fedavg_reduce(slots.clone(), counts, **kw)
+    lowp = torch.zeros(k, n, dtype=torch.bfloat16, device="cuda")
+    mom = torch.ones(k, n, device="cuda")
+    master = torch.zeros(n, device="cuda")
+    mlow = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    ops.fedavg_reduce(slots, counts, out=master, out_lowp=mlow, bcast=(slots, lowp, mom), **kw)
+    torch.cuda.synchronize()
+    assert torch.equal(master, want)
+    assert all(torch.equal(slots[i], want) for i in range(k))
+    assert all(torch.equal(lowp[i], want.bfloat16()) for i in range(k))
+    assert float(mom.abs().sum()) == 0.0
+    # all masked: the previous model is kept AND still reaches the rows
+    slots.normal_()
+    ops.fedavg_reduce(slots, counts, out=master, out_lowp=mlow, mask=torch.zeros(k, device="cuda"),
+                      bcast=(slots, lowp, None))
+    assert torch.equal(master, want) and torch.equal(slots[k - 1], want)
+
+
+def test_simulation_round_has_no_broadcast_launch_after_the_first():
+    from nanofed_b200.ops import native
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    def run(fuse):
+        sim = FedSimulation(CohortConfig(model="mnist_cnn", clients_per_gpu=4, samples_per_client=128,
+                                         batch_size=64, device="cuda", fuse_bcast=fuse))
+        if hasattr(sim.engine, "p1"):
+            sim.engine.p1 = sim.engine.p2 = 0.0
+        sim.run_round()
+        native.reset_launch_count()
+        sim.run_round()
+        eager = native.LAUNCHES
+        torch.cuda.synchronize()
+        return eager, sim.arena.master.clone()
+
+    fused_launches, fused = run(True)
+    plain_launches, plain = run(False)
+    assert fused_launches == plain_launches - 1          # K-BCAST is gone from the round
+    assert float((fused - plain).norm() / plain.norm()) < 1e-3
