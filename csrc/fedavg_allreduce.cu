@@ -68,6 +68,10 @@ struct AllreduceArgs {
   int accumulate, local_only;
   const float* my_stats;      // [stats_len] local per-client metrics, copied to every rank's stats_all
   int stats_len;
+  // K-BCAST as the tail of the same kernel: once this rank owns the complete new model (second
+  // flag barrier), EVERY CTA replicates it into the local client rows (fp32 + bf16) and zeroes the
+  // momentum rows.  Emulated ranks (one launch) use consecutive targets of `bc_rank_stride` rows.
+  nfb_bcast_target bc;
 };
 
 __device__ __forceinline__ unsigned long long now_ns() {
@@ -116,6 +120,49 @@ __device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
 }
 
 constexpr int kMaxChunks = 64;
+constexpr int kGoSlot = 1 + kMaxChunks;   // counters[kGoSlot]: epoch of the last completed call
+
+// Tail phase: replicate master[] into the client rows.  Called by every CTA of the rank after the
+// completion barrier; `part` / `parts` = this CTA's index / the rank's CTA count.
+__device__ __forceinline__ void bcast_tail(const float* master, int64_t N, const nfb_bcast_target& bc,
+                                           int part, int parts) {
+  const int64_t groups = N >> 2;
+  for (int64_t g = part * static_cast<int64_t>(blockDim.x) + threadIdx.x; g < groups;
+       g += static_cast<int64_t>(parts) * blockDim.x) {
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(master + 4 * g));   // L2: peers wrote it
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+    for (int64_t k = 0; k < bc.rows; ++k) {
+      if (bc.slots) *reinterpret_cast<float4*>(bc.slots + k * bc.slots_stride + 4 * g) = v;
+      if (bc.lowp)
+        *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(bc.lowp) + k * bc.lowp_stride + 4 * g) = pk;
+      if (bc.momentum)
+        *reinterpret_cast<float4*>(bc.momentum + k * bc.momentum_stride + 4 * g) =
+            make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+// Every CTA of the rank waits (bounded) until the last consumer CTA has seen all peers' completion
+// flags and published this call's epoch in counters[kGoSlot].
+__device__ __forceinline__ bool wait_go(const unsigned* go, unsigned epoch, unsigned long long limit,
+                                        int* status) {
+  __shared__ int s_go;
+  if (threadIdx.x == 0) {
+    s_go = 1;
+    const unsigned long long t0 = now_ns();
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(go) : "memory");
+      if (v >= epoch) break;
+      if (now_ns() - t0 > limit) { *status = 1; s_go = 0; break; }
+    } while (true);
+  }
+  __syncthreads();
+  return s_go != 0;
+}
 
 // One thread per peer: publish `value` into slot `slot` of every peer's flag array.
 __device__ __forceinline__ void signal_peers(const RankView* views, int rank, int G, int slot,
@@ -211,6 +258,16 @@ __global__ void __launch_bounds__(256)
         signal_peers(views, rank, G, 1 + c, a.epoch);
       }
       __syncthreads();
+    }
+    if (a.bc.rows > 0 && !a.local_only &&
+        wait_go(me.counters + kGoSlot, a.epoch, a.spin_limit_ns, a.status)) {
+      nfb_bcast_target bc = a.bc;
+      if (gridDim.y > 1) {   // emulation: rank r's rows follow rank r-1's
+        if (bc.slots) bc.slots += static_cast<int64_t>(rank) * bc.rows * bc.slots_stride;
+        if (bc.lowp) bc.lowp = static_cast<__nv_bfloat16*>(bc.lowp) + static_cast<int64_t>(rank) * bc.rows * bc.lowp_stride;
+        if (bc.momentum) bc.momentum += static_cast<int64_t>(rank) * bc.rows * bc.momentum_stride;
+      }
+      bcast_tail(me.master, a.N, bc, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
     }
     return;
   }
@@ -319,7 +376,21 @@ __global__ void __launch_bounds__(256)
     }
     __threadfence();
     signal_peers(views, rank, G, 0, a.epoch);
-    wait_peers(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
+    const bool done = wait_peers(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
+    if (a.bc.rows > 0 && done && threadIdx.x == 0) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(me.counters + kGoSlot), "r"(a.epoch)
+                   : "memory");
+    }
+  }
+  if (a.bc.rows > 0 && ok && wait_go(me.counters + kGoSlot, a.epoch, a.spin_limit_ns, a.status)) {
+    nfb_bcast_target bc = a.bc;
+    if (gridDim.y > 1) {
+      if (bc.slots) bc.slots += static_cast<int64_t>(rank) * bc.rows * bc.slots_stride;
+      if (bc.lowp) bc.lowp = static_cast<__nv_bfloat16*>(bc.lowp) + static_cast<int64_t>(rank) * bc.rows * bc.lowp_stride;
+      if (bc.momentum) bc.momentum += static_cast<int64_t>(rank) * bc.rows * bc.momentum_stride;
+    }
+    bcast_tail(me.master, a.N, bc, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
   }
 }
 
@@ -383,7 +454,7 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
                                     const float* mc_partial,
                                     float* mc_master, void* mc_lowp, int* status,
                                     uint64_t spin_limit_ns, int flags, const float* my_stats,
-                                    int stats_len, void* stream) {
+                                    int stats_len, const void* bcast, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(views_dev && status, NFB_EINVAL, "fedavg_allreduce: null pointer");
   NFB_REQUIRE(G >= 1 && G <= 32 && my_rank >= 0 && my_rank < G, NFB_EINVAL,
@@ -418,6 +489,8 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
   a.local_only = (flags & 2) ? 1 : 0;
   a.my_stats = my_stats;
   a.stats_len = my_stats ? stats_len : 0;
+  a.bc = nfb_bcast_target{};
+  if (bcast && !a.local_only) a.bc = *static_cast<const nfb_bcast_target*>(bcast);
   const RankView* views = static_cast<const RankView*>(views_dev);
   cudaStream_t st = as_stream(stream);
   return dispatch_dtype(x_dtype, [&](auto tag) {

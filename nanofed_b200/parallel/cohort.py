@@ -598,7 +598,11 @@ class FedSimulation:
                                   out_lowp=arena.master_lowp, mask=arena.mask, **kw)
                 self._slots_fresh = fuse
             else:
+                fuse = (cfg.fuse_bcast and self.device.type == "cuda" and not cfg.screen_nonfinite)
+                if fuse:     # K-BCAST rides in the tail of the aggregation kernel
+                    kw["bcast"] = (arena.slots, arena.slots_lowp, arena.momentum)
                 self.reducer.reduce(arena, **kw)
+                self._slots_fresh = fuse
             if mask is not None:
                 arena.mask.copy_(saved)
 

@@ -59,7 +59,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.nfb_fedavg_allreduce.restype = i32
     lib.nfb_fedavg_allreduce.argtypes = [vp, i32, i32, i32, i32, i64, i64, i64, f32, f32, vp, u64,
                                          u64, u32, i32, i64, i32, vp, vp, vp, vp, u64, i32, vp,
-                                         i32, vp]
+                                         i32, vp, vp]
     lib.nfb_allreduce_max_blocks.restype = i32
     lib.nfb_allreduce_max_blocks.argtypes = [i32, i64]
     lib._nfb_allreduce_declared = True
@@ -102,7 +102,7 @@ class NcclReducer:
 
     def reduce(self, arena: Arena, *, sumsq=None, clip_norm: float = 0.0, noise_std: float = 0.0,
                noise_mask=None, seed: int = 0, offset: int = 0, accumulate: bool = False,
-               local_only: bool = False) -> None:
+               local_only: bool = False, bcast: tuple | None = None) -> None:
         ops.fedavg_reduce(arena.slots, arena.counts, out=self.partial, mask=arena.mask,
                           sumsq=sumsq, clip_norm=clip_norm, normalize=False, accumulate=accumulate)
         eff = arena.counts * arena.mask
@@ -130,6 +130,8 @@ class NcclReducer:
             new.add_(z * (noise_std * self.scal[1].sqrt() / self.scal[0].clamp_min(1e-30)))
         arena.master.copy_(torch.where(alive, new, arena.master))
         arena.master_lowp.copy_(arena.master)
+        if bcast is not None:
+            ops.bcast_global(arena.master, *bcast)
 
 
 class PeerReducer:
@@ -171,7 +173,7 @@ class PeerReducer:
         self.lowp.copy_(arena.master_lowp)
         arena.master, arena.master_lowp = self.master, self.lowp
 
-        self.grid_ctr = torch.zeros(1 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
+        self.grid_ctr = torch.zeros(2 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
         self.sumsq_dummy = None
         rows = []
@@ -210,11 +212,22 @@ class PeerReducer:
 
     def reduce(self, arena: Arena, *, sumsq=None, clip_norm: float = 0.0, noise_std: float = 0.0,
                noise_mask=None, seed: int = 0, offset: int = 0, accumulate: bool = False,
-               local_only: bool = False) -> None:
+               local_only: bool = False, bcast: tuple | None = None) -> None:
         """One fused launch.  ``local_only`` (streaming waves, ``K·N·b`` beyond HBM): only add this
         wave's clients to the unnormalised partial; the last wave (``accumulate=True,
-        local_only=False``) then does the single cross-GPU reduce-scatter / all-gather."""
+        local_only=False``) then does the single cross-GPU reduce-scatter / all-gather.
+        ``bcast=(slots, slots_lowp, momentum)``: K-BCAST as the tail of the same kernel — once this
+        rank owns the complete new model, all CTAs replicate it into the client rows."""
         from nanofed_b200.ops import native
+
+        target = None
+        if bcast is not None and not local_only:
+            b_slots, b_lowp, b_mom = bcast
+            rows = next(t.shape[0] for t in (b_slots, b_lowp, b_mom) if t is not None)
+            target = native._BcastTarget(
+                native._ptr(b_slots), b_slots.stride(0) if b_slots is not None else 0,
+                native._ptr(b_lowp), b_lowp.stride(0) if b_lowp is not None else 0,
+                native._ptr(b_mom), b_mom.stride(0) if b_mom is not None else 0, rows)
 
         r = self.rank.rank
         want = sumsq.data_ptr() if sumsq is not None else 0
@@ -233,6 +246,7 @@ class PeerReducer:
             (mc + lay.lowp) if mc else None, self.status.data_ptr(), _SPIN_NS,
             (1 if accumulate else 0) | (2 if local_only else 0),
             arena.stats.data_ptr(), self.stats_len,
+            C.byref(target) if target is not None else None,
             torch.cuda.current_stream(arena.device).cuda_stream,
         )
         native._check(code, "fedavg_allreduce")
@@ -282,6 +296,7 @@ def emulate_allreduce(
     spin_ns: int = 2_000_000_000,
     master_init: torch.Tensor | None = None,
     return_stats: bool = False,
+    bcast: tuple | None = None,
 ) -> tuple[torch.Tensor, ...]:
     """Run G emulated ranks of the fused kernel in one cooperative launch.
 
@@ -302,8 +317,16 @@ def emulate_allreduce(
     if master_init is not None:
         for r in range(g):
             bufs[r, lay.master : lay.master + 4 * n].view(torch.float32).copy_(master_init)
-    ctr = torch.zeros(g, 1 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
+    ctr = torch.zeros(g, 2 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
+    target = None
+    if bcast is not None:        # (slots [G, R, N], lowp [G, R, N] | None, momentum [G, R, N] | None)
+        b_slots, b_lowp, b_mom = bcast
+        rows = next(t.shape[1] for t in (b_slots, b_lowp, b_mom) if t is not None)
+        target = native._BcastTarget(
+            native._ptr(b_slots), b_slots.stride(1) if b_slots is not None else 0,
+            native._ptr(b_lowp), b_lowp.stride(1) if b_lowp is not None else 0,
+            native._ptr(b_mom), b_mom.stride(1) if b_mom is not None else 0, rows)
     counts = counts.to(torch.float32).contiguous()
     mask = torch.ones_like(counts) if mask is None else mask.to(torch.float32).contiguous()
     assert k % waves == 0, "waves must divide the client count"
@@ -338,6 +361,7 @@ def emulate_allreduce(
                 seed & (2**64 - 1), offset, call, grid // 2, chunk, grid, None, None, None,
                 status.data_ptr(), spin_ns, flags,
                 stats.data_ptr() if stats is not None else None, stats_len,
+                C.byref(target) if (target is not None and w == waves - 1) else None,
                 torch.cuda.current_stream(dev).cuda_stream,
             )
             native._check(code, "fedavg_allreduce(emulated)")

@@ -89,7 +89,8 @@ if d > 2e-3:
 #    participation mask through the address it was given at construction)
 cfg = CohortConfig(model="mnist_cnn", clients_per_gpu=2, samples_per_client=64, batch_size=32,
                    local_epochs=1, learning_rate=0.05, seed=11, transport="peer",
-                   round_deadline_ms=150.0, use_cuda_graph=False)
+                   round_deadline_ms=150.0, use_cuda_graph=False,
+                   fuse_bcast=False)       # this check reads the trained client rows after the round
 sim = FedSimulation(cfg)
 sim.run_round()                                   # warm-up round (lazy initialisation is slow)
 if info.rank == 1:

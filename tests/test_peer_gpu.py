@@ -93,3 +93,24 @@ def test_barrier_timeout_is_reported_not_hung():
     counts = torch.ones(g, k, device="cuda")
     with pytest.raises(RuntimeError, match="timed out"):
         emulate_allreduce(slots, counts, spin_ns=1)    # 1 ns: the first unsatisfied probe expires
+
+
+def test_emulated_allreduce_with_broadcast_tail():
+    """K-BCAST as the tail of the fused kernel: after the completion barrier every CTA of a rank
+    replicates the new model into that rank's client rows (fp32 + bf16) and zeroes momentum."""
+    g, k, n, rows = 4, 3, 70_016, 5
+    torch.manual_seed(5)
+    slots = torch.randn(g, k, n, device="cuda")
+    counts = torch.randint(1, 50, (g, k), device="cuda").float()
+    b_slots = torch.full((g, rows, n), -7.0, device="cuda")
+    b_lowp = torch.zeros(g, rows, n, dtype=torch.bfloat16, device="cuda")
+    b_mom = torch.ones(g, rows, n, device="cuda")
+    master, _ = emulate_allreduce(slots, counts, calls=2, chunk_elems=8192,
+                                  bcast=(b_slots, b_lowp, b_mom))
+    want = ref.fedavg_reduce(slots.view(g * k, n).cpu(), counts.view(-1).cpu()).cuda()
+    torch.testing.assert_close(master[0], want, rtol=1e-5, atol=1e-5)
+    for r in range(g):
+        for j in range(rows):
+            assert torch.equal(b_slots[r, j], master[r])
+            assert torch.equal(b_lowp[r, j], master[r].bfloat16())
+    assert float(b_mom.abs().sum()) == 0.0
