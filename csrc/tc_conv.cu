@@ -38,8 +38,9 @@ constexpr int kSlabRows = 128 + kHalo;
 
 struct ConvArgs {
   int tiles_per_client;   // ceil(R / 128)
-  int ctas_per_client;
-  int client0;            // first client of this launch (a cohort may be covered by several launches)
+  int n_clients;          // clients covered by this launch
+  int client0;            // first client of this launch
+  int cta0;               // global index of this launch's first CTA (dropout counter)
   int rows;               // R
   int shift[kTaps];       // slab-relative row shift per tap
   void* out;              // bf16 [C, R, N]
@@ -154,20 +155,38 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
   __shared__ float s_bias[64];
   __shared__ int s_wg_valid[kMaxEpiWarps];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = args.client0 + blockIdx.x / args.ctas_per_client;
-  const int part = blockIdx.x % args.ctas_per_client;
-  if (threadIdx.x < 64)
-    s_bias[threadIdx.x] = (!kDgrad<MODE> && args.bias)
-                              ? args.bias[static_cast<long long>(g) * args.bias_gs + threadIdx.x] : 0.f;
-  const int per = (args.tiles_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
-  const int tile_lo = part * per;
-  const int tile_hi = min(tile_lo + per, args.tiles_per_client);
-  const int n_tiles = max(tile_hi - tile_lo, 0);
+  // Work distribution: the tiles of ALL clients form one sequence (client-major) that is cut into
+  // gridDim.x equal ranges, so every SM has a CTA even when the client count does not divide the
+  // SM count (32 clients: 148 CTAs x 73 tiles instead of 128 x 85).  A range that crosses a client
+  // boundary is processed as consecutive SEGMENTS; a segment = (client, tile range) runs the
+  // whole pipeline below with that client's resident weights, then the barriers are re-initialised.
+  const long long t_total = static_cast<long long>(args.n_clients) * args.tiles_per_client;
+  const long long cta_lo = t_total * blockIdx.x / gridDim.x;
+  const long long cta_hi = t_total * (blockIdx.x + 1) / gridDim.x;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_a);
     prefetch_tmap(&map_w);
     prefetch_tmap(&map_o);
+  }
+  if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  int tiles_done = 0;                                  // tiles of earlier segments (RNG counter)
+  for (long long cur = cta_lo; cur < cta_hi;) {
+  const int g_rel = static_cast<int>(cur / args.tiles_per_client);
+  const int g = args.client0 + g_rel;
+  const int tile_lo = static_cast<int>(cur - static_cast<long long>(g_rel) * args.tiles_per_client);
+  const long long seg_end = min(cta_hi, static_cast<long long>(g_rel + 1) * args.tiles_per_client);
+  const int n_tiles = static_cast<int>(seg_end - cur);
+  cur = seg_end;
+  if (threadIdx.x < 64)
+    s_bias[threadIdx.x] = (!kDgrad<MODE> && args.bias)
+                              ? args.bias[static_cast<long long>(g) * args.bias_gs + threadIdx.x] : 0.f;
+  if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < C::GROUPS; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
     mbar_init(w_bar, 1);
@@ -175,11 +194,9 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
       for (int w = 0; w < C::EPI_WARPS; ++w) mbar_init(&wg_bar[w], 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     // ===================== producer =====================
@@ -203,6 +220,12 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
                                  : tile * 128;
         const int row0 = !kDgrad<MODE> ? m0 : m0 - kHalo;
         tma_load_4d(slabs + s * C::SLAB_PAD, &map_a, &full_bar[s], 0, row0, 0, g);
+      }
+      // drain: every stage's last "slot free" arrival (tcgen05.commit) must have landed before the
+      // barriers are re-initialised for the next segment
+      for (int i = n_tiles; i < n_tiles + C::STAGES; ++i) {
+        if (i < C::STAGES) continue;                     // this stage was never filled
+        if (!mbar_wait(&empty_bar[i % C::STAGES], ((i / C::STAGES) & 1) ^ 1)) { *args.status = 1; break; }
       }
     }
   } else if (warp == 1) {
@@ -359,8 +382,8 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
         // in the code byte, so the backward pass never regenerates the stream.
         uint4 rnd = make_uint4(~0u, ~0u, ~0u, ~0u);
         if (args.drop_p > 0.f)
-          rnd = Philox::draw((step << 40) + (static_cast<unsigned long long>(args.client0 * args.ctas_per_client + blockIdx.x) << 20) +
-                                 static_cast<unsigned long long>(i) * 128 + gt,
+          rnd = Philox::draw((step << 40) + (static_cast<unsigned long long>(args.cta0 + blockIdx.x) << 20) +
+                                 static_cast<unsigned long long>(tiles_done + i) * 128 + gt,
                              args.seed);
         const uint32_t thresh = static_cast<uint32_t>(args.drop_p * 256.f + 0.5f);
         const uint32_t rwords[3] = {rnd.x, rnd.y, rnd.z};
@@ -548,6 +571,9 @@ __global__ void __launch_bounds__(128 + 32 * ConvCfg<MODE>::EPI_WARPS, 1)
 
   tc_fence_before();
   __syncthreads();
+  tiles_done += n_tiles;
+  }  // segments
+
   if (warp == 2) tmem_dealloc<C::TMEM_COLS>(tmem_base);
 }
 
@@ -581,7 +607,7 @@ constexpr size_t kWgSmem = static_cast<size_t>(kWgStages) * kWgStage + 1024 + 25
 
 struct WgradArgs {
   int kblocks_per_client;  // ceil(R / 64)
-  int ctas_per_client;
+  int n_clients;           // clients covered by this launch
   int client0;             // first client of this launch
   int shift[kTaps];        // [kh] = kh * width (entries 0..2 used)
   float* grad;             // first client's [64][32][3][3] block inside the gradient slab
@@ -604,25 +630,37 @@ __global__ void __launch_bounds__(256, 1)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = args.client0 + blockIdx.x / args.ctas_per_client;
-  const int part = blockIdx.x % args.ctas_per_client;
-  const int per = (args.kblocks_per_client + args.ctas_per_client - 1) / args.ctas_per_client;
-  const int kb_lo = part * per;
-  const int kb_hi = min(kb_lo + per, args.kblocks_per_client);
-  const int n_kb = max(kb_hi - kb_lo, 0);
+  // one sequence of k-blocks over all clients, cut into gridDim.x equal ranges; a range crossing a
+  // client boundary runs as consecutive segments (see tc_conv_kernel)
+  const long long t_total = static_cast<long long>(args.n_clients) * args.kblocks_per_client;
+  const long long cta_lo = t_total * blockIdx.x / gridDim.x;
+  const long long cta_hi = t_total * (blockIdx.x + 1) / gridDim.x;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_dy);
     prefetch_tmap(&map_x);
-    for (int s = 0; s < kWgStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    mbar_init(acc_bar, 1);
-    fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+
+  for (long long cur = cta_lo; cur < cta_hi;) {
+  const int g_rel = static_cast<int>(cur / args.kblocks_per_client);
+  const int g = args.client0 + g_rel;
+  const int kb_lo = static_cast<int>(cur - static_cast<long long>(g_rel) * args.kblocks_per_client);
+  const long long seg_end = min(cta_hi, static_cast<long long>(g_rel + 1) * args.kblocks_per_client);
+  const int n_kb = static_cast<int>(seg_end - cur);
+  cur = seg_end;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kWgStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -636,6 +674,10 @@ __global__ void __launch_bounds__(256, 1)
         mbar_expect_tx(&full_bar[s], kWgB + kWgX);
         tma_load_3d(stage, &map_dy, &full_bar[s], 0, q0, g);                 // dy [64 co x 64 rows]
         tma_load_3d(stage + kWgB, &map_x, &full_bar[s], 0, q0, g);           // x  [32 ci x 120 rows]
+      }
+      for (int i = n_kb; i < n_kb + kWgStages; ++i) {   // drain the "slot free" arrivals
+        if (i < kWgStages) continue;
+        if (!mbar_wait(&empty_bar[i % kWgStages], ((i / kWgStages) & 1) ^ 1)) { *args.status = 1; break; }
       }
     }
   } else if (warp == 1) {
@@ -703,6 +745,7 @@ __global__ void __launch_bounds__(256, 1)
   }
   tc_fence_before();
   __syncthreads();
+  }  // segments
   if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
@@ -817,30 +860,15 @@ static int out_map(const void* ptr, long long rows, long long groups, long long 
   return 0;
 }
 
-// With one CTA range per client, 32 clients use 4 x 32 = 128 of 148 SMs (85 tiles per CTA).  Covering
-// the cohort with `n` back-to-back launches of clients / n clients each lets every launch spread
-// its clients over (nearly) all SMs: 2 launches x 16 clients x 9 CTAs = 144 SMs, 2 x 38 tiles.
-// A launch boundary costs about `gap` work units; the plan minimises n * ceil(units / per) + gaps.
-// MEASURED (B200, 32 clients x 64): two launches per kernel make the local step SLOWER, 0.547 vs
-// 0.527 ms (four: 0.641 ms) - a persistent kernel's drain + the next one's prologue (weights by TMA,
-// TMEM allocation, pipeline fill) cost more than the 13 % of idle SMs.  The gaps below encode
-// that (one launch wins for every shape used so far); NFB_CONV_SPLIT=n forces n for A/B runs.
-// Using the idle SMs needs CTA ranges that cross a client boundary inside ONE launch.
-static void plan_split(int clients, int units, int gap, int* n_split, int* per_client) {
-  static const int forced = [] { const char* e = getenv("NFB_CONV_SPLIT"); return e ? atoi(e) : 0; }();
-  int best_n = 1, best_pc = 1;
-  long long best_cost = -1;
-  for (int n = 1; n <= 8; n *= 2) {
-    if (clients % n) break;
-    if (forced && n != forced) continue;
-    int pc = sm_count() / (clients / n);
-    if (pc < 1) pc = 1;
-    if (pc > units) pc = units;
-    const long long cost = static_cast<long long>(n) * ((units + pc - 1) / pc) + static_cast<long long>(gap) * (n - 1);
-    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_n = n; best_pc = pc; }
-  }
-  *n_split = best_n;
-  *per_client = best_pc;
+// Grid of the persistent conv kernels: one CTA per SM (or per work unit if there are fewer).
+// History: one CTA range per client left 20 of 148 SMs idle with 32 clients; covering the cohort
+// with 2 / 4 back-to-back launches of 16 / 8 clients was SLOWER (0.547 / 0.641 vs 0.527 ms per
+// local step: a persistent kernel's drain + the next prologue cost more than the idle SMs);
+// ranges that cross client boundaries inside ONE launch (segments) are what is used now.
+static int conv_grid(int clients, int units_per_client) {
+  const long long total = static_cast<long long>(clients) * units_per_client;
+  const long long sms = sm_count();
+  return static_cast<int>(total < sms ? total : sms);
 }
 
 template <int MODE>
@@ -856,19 +884,12 @@ static int launch_conv(const CUtensorMap& ma, const CUtensorMap& mw, const CUten
       return fail(static_cast<int>(e), "tc_conv: smem attribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  const int clients = ctas / a_in.ctas_per_client;
-  int n_split = 1, per_client = a_in.ctas_per_client;
-  plan_split(clients, a_in.tiles_per_client, 16, &n_split, &per_client);
+  (void)ctas;
   ConvArgs a = a_in;
-  a.ctas_per_client = per_client;
-  const int group = clients / n_split;
-  for (int h = 0; h < n_split; ++h) {
-    a.client0 = h * group;
-    kern<<<group * per_client, 128 + 32 * C::EPI_WARPS, C::SMEM, st>>>(ma, mw, mo, a);
-    const int rc = launch_status("tc_conv");
-    if (rc) return rc;
-  }
-  return 0;
+  a.client0 = 0;
+  a.cta0 = 0;
+  kern<<<conv_grid(a.n_clients, a.tiles_per_client), 128 + 32 * C::EPI_WARPS, C::SMEM, st>>>(ma, mw, mo, a);
+  return launch_status("tc_conv");
 }
 
 }  // namespace tc
@@ -900,10 +921,8 @@ extern "C" int nfb_tc_conv3x3(int mode, const void* a, long long rows, long long
   if (rc) return rc;
   ConvArgs args{};
   args.tiles_per_client = static_cast<int>((rows + 127) / 128);
-  int per_client = sm_count() / clients;
-  if (per_client < 1) per_client = 1;
-  if (per_client > args.tiles_per_client) per_client = args.tiles_per_client;
-  args.ctas_per_client = per_client;
+  args.n_clients = clients;
+  const int per_client = 1;   // (grid is chosen in launch_conv)
   args.rows = static_cast<int>(rows);
   for (int kh = 0; kh < 3; ++kh)
     for (int kw = 0; kw < 3; ++kw) {
@@ -957,10 +976,8 @@ extern "C" int nfb_tc_conv3x3_dgrad_wgrad1(const void* dy, long long rows,
   if (rc) return rc;
   ConvArgs args{};
   args.tiles_per_client = static_cast<int>((rows + 127) / 128);
-  int per_client = sm_count() / clients;
-  if (per_client < 1) per_client = 1;
-  if (per_client > args.tiles_per_client) per_client = args.tiles_per_client;
-  args.ctas_per_client = per_client;
+  args.n_clients = clients;
+  const int per_client = 1;   // (grid is chosen in launch_conv)
   args.rows = static_cast<int>(rows);
   for (int kh = 0; kh < 3; ++kh)
     for (int kw = 0; kw < 3; ++kw) args.shift[kh * 3 + kw] = kHalo - (kh * width + kw);
@@ -1042,10 +1059,8 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
   }
   WgradArgs a{};
   a.kblocks_per_client = static_cast<int>((rows + 63) / 64);
-  int per_client = sm_count() / clients;
-  if (per_client < 1) per_client = 1;
-  if (per_client > a.kblocks_per_client) per_client = a.kblocks_per_client;
-  a.ctas_per_client = per_client;
+  a.n_clients = clients;
+  a.client0 = 0;
   for (int kh = 0; kh < 3; ++kh) a.shift[kh] = kh * width;
   for (int kh = 0; kh < 3; ++kh)
     for (int kk = 0; kk < 4; ++kk)       // rows of 64 B = 4 descriptor units each
@@ -1066,17 +1081,9 @@ extern "C" int nfb_tc_conv3x3_wgrad(const void* dy, const void* x, long long row
       return fail(static_cast<int>(e), "tc_conv3x3_wgrad: smem attribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  int n_split = 1;
-  plan_split(clients, a.kblocks_per_client, 32, &n_split, &per_client);
-  a.ctas_per_client = per_client;
-  const int group = clients / n_split;
-  for (int h = 0; h < n_split; ++h) {
-    a.client0 = h * group;
-    tc_conv_wgrad_kernel<<<group * per_client, 256, kWgSmem, as_stream(stream)>>>(mdy, mx, a);
-    const int rc = launch_status("tc_conv3x3_wgrad");
-    if (rc) return rc;
-  }
-  return 0;
+  tc_conv_wgrad_kernel<<<conv_grid(clients, a.kblocks_per_client), 256, kWgSmem, as_stream(stream)>>>(
+      mdy, mx, a);
+  return launch_status("tc_conv3x3_wgrad");
 }
 
 // Forward 3x3 conv (32 -> 64 ch) + bias + ReLU + 2x2 max-pool + dropout in ONE kernel; the conv
@@ -1103,10 +1110,8 @@ extern "C" int nfb_tc_conv3x3_pool_fwd(const void* x, long long rows, long long 
   if (rc) return rc;
   ConvArgs args{};
   args.tiles_per_client = images * 6;
-  int per_client = sm_count() / clients;
-  if (per_client < 1) per_client = 1;
-  if (per_client > args.tiles_per_client) per_client = args.tiles_per_client;
-  args.ctas_per_client = per_client;
+  args.n_clients = clients;
+  const int per_client = 1;   // (grid is chosen in launch_conv)
   args.rows = static_cast<int>(rows);
   for (int kh = 0; kh < 3; ++kh)
     for (int kw = 0; kw < 3; ++kw) args.shift[kh * 3 + kw] = kh * width + kw;
