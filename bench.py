@@ -55,6 +55,8 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--model", default="mnist_cnn")
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--dp", action="store_true", help="central DP fused into aggregation")
+    ap.add_argument("--local-dp", action="store_true",
+                    help="client-side DP-SGD (clip + noise inside K-OPT) in every local step")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--streams-per-gpu", type=int, default=8,
                     help="client streams of the generic autograd engine (ResNet configs)")
@@ -150,6 +152,7 @@ def run_ours(args: argparse.Namespace) -> None:
         learning_rate=LR, compute_dtype=args.dtype, engine=args.engine,
         transport=args.transport, streams_per_gpu=args.streams_per_gpu,
         privacy=PrivacyConfig(epsilon=10.0, noise_multiplier=1.1) if args.dp else None,
+        local_privacy=PrivacyConfig(epsilon=10.0, noise_multiplier=1.1) if args.local_dp else None,
     )
     if args.no_channels_last:
         os.environ["NFB_CHANNELS_LAST"] = "0"
@@ -291,7 +294,8 @@ def run_ours(args: argparse.Namespace) -> None:
                 "samples_per_client": args.samples_per_client, "local_epochs": LOCAL_EPOCHS,
                 "local_batch": BATCH, "local_steps_per_round": cfg.local_steps,
                 "optimizer": f"SGD(lr={LR})", "aggregation": "FedAvg (sample-weighted)"
-                + (" + central DP clip/noise" if args.dp else ""),
+                + (" + central DP clip/noise" if args.dp else "")
+                + (" + client-side DP-SGD" if args.local_dp else ""),
                 "parallelism": f"clients-dp{args.gpus}", "engine": sim.engine_name,
                 "agg_path": getattr(sim.reducer, "path", "single_gpu_fused_kernel"),
                 "l2_policy": f"working set per round {arena_mb:.0f} MB arena + activations "

@@ -21,13 +21,22 @@ struct SgdArgs {
   __nv_bfloat16* perm_out;
   int64_t perm_gs, perm_lo, perm_len;
   int perm_inner, perm_taps;
+  // DP-SGD per row (= per client): g' = g * min(1, clip_norm / ||g_row||) + noise_std * z, with the
+  // row's squared gradient norm from K-STATS (reference: clip_grad_norm_ + per-parameter noise of
+  // nanofed/trainer/private.py:54-86).  noise_mask limits the noise to real parameter entries;
+  // step_ctr (device) advances the noise stream from step to step inside a replayed CUDA graph.
+  const float* row_sumsq;
+  float clip_norm;
+  const uint8_t* noise_mask;
+  const unsigned long long* step_ctr;
 };
 
 template <typename G>
 __global__ void __launch_bounds__(256)
     sgd_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ mom,
                __nv_bfloat16* __restrict__ lowp, int64_t n, SgdArgs a) {
-  const float gs = a.grad_scale ? *a.grad_scale : 1.f;
+  const float gs0 = a.grad_scale ? *a.grad_scale : 1.f;
+  const uint64_t group0 = a.group0 + (a.step_ctr ? *a.step_ctr * static_cast<uint64_t>((n + 3) >> 2) : 0ull);
   // with a skipped column range the thread index runs over the remaining columns only
   const int64_t eff_row = a.row_len - a.skip_len;
   const int64_t groups = a.skip_len > 0 ? (n / a.row_len) * (eff_row >> 2) : (n + 3) >> 2;
@@ -40,6 +49,22 @@ __global__ void __launch_bounds__(256)
       base = row * a.row_len + (col < a.skip_lo ? col : col + a.skip_len);
     }
     const int cnt = (n - base) >= 4 ? 4 : static_cast<int>(n - base);
+    float gs = gs0;
+    // row / column of this group for the per-row clip factor and the noise mask: 32-bit division
+    // where the buffer allows it (a 64-bit divide per group cost 10 us of a 124 us pass)
+    int64_t dp_row = 0, dp_col = 0;
+    if (a.row_sumsq || a.noise_mask) {
+      if (n < (1ll << 31)) {
+        const uint32_t b32 = static_cast<uint32_t>(base), rl = static_cast<uint32_t>(a.row_len);
+        const uint32_t r32 = b32 / rl;
+        dp_row = r32;
+        dp_col = b32 - r32 * rl;
+      } else {
+        dp_row = base / a.row_len;
+        dp_col = base - dp_row * a.row_len;
+      }
+    }
+    if (a.row_sumsq) gs *= fminf(a.clip_norm / (sqrtf(a.row_sumsq[dp_row]) + 1e-6f), 1.f);
     float pv[4], gv[4], mv[4] = {0, 0, 0, 0};
     if (cnt == 4) {
       const float4 t = *reinterpret_cast<const float4*>(p + base);
@@ -61,9 +86,23 @@ __global__ void __launch_bounds__(256)
       }
     }
     if (a.noise_std > 0.f) {
-      const float4 z = Philox::normal4(a.group0 + (base >> 2), a.seed);
-      gv[0] = fmaf(a.noise_std, z.x, gv[0]); gv[1] = fmaf(a.noise_std, z.y, gv[1]);
-      gv[2] = fmaf(a.noise_std, z.z, gv[2]); gv[3] = fmaf(a.noise_std, z.w, gv[3]);
+      const float4 z = Philox::normal4(group0 + (base >> 2), a.seed);
+      float zz[4] = {z.x, z.y, z.z, z.w};
+      if (a.noise_mask) {
+        if (cnt == 4 && (dp_col & 3) == 0) {          // one 4-byte load per group
+          const uchar4 m = *reinterpret_cast<const uchar4*>(a.noise_mask + dp_col);
+          if (!m.x) zz[0] = 0.f;
+          if (!m.y) zz[1] = 0.f;
+          if (!m.z) zz[2] = 0.f;
+          if (!m.w) zz[3] = 0.f;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (e >= cnt || !a.noise_mask[dp_col + e]) zz[e] = 0.f;
+        }
+      }
+      gv[0] = fmaf(a.noise_std, zz[0], gv[0]); gv[1] = fmaf(a.noise_std, zz[1], gv[1]);
+      gv[2] = fmaf(a.noise_std, zz[2], gv[2]); gv[3] = fmaf(a.noise_std, zz[3], gv[3]);
     }
     if (a.weight_decay != 0.f) {
 #pragma unroll
@@ -155,7 +194,10 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
                           uint64_t offset, int64_t row_len, int64_t zero_prefix, int64_t skip_lo,
                           int64_t skip_hi, int64_t zero_from, void* stream,
                           void* perm_out = nullptr, int64_t perm_gs = 0, int64_t perm_lo = 0,
-                          int64_t perm_rows = 0, int perm_inner = 0, int perm_taps = 0) {
+                          int64_t perm_rows = 0, int perm_inner = 0, int perm_taps = 0,
+                          const float* row_sumsq = nullptr, float clip_norm = 0.f,
+                          const uint8_t* noise_mask = nullptr,
+                          const unsigned long long* step_ctr = nullptr) {
   using namespace nfb;
   NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
   NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
@@ -179,7 +221,10 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
   SgdArgs a{lr, momentum, dampening, weight_decay, noise_std, nesterov, first_step,
             grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix, skip_lo,
             skip_len, zero_from, static_cast<__nv_bfloat16*>(perm_out), perm_gs, perm_lo,
-            perm_out ? perm_len : 0, perm_inner, perm_taps};
+            perm_out ? perm_len : 0, perm_inner, perm_taps, row_sumsq, clip_norm, noise_mask,
+            step_ctr};
+  NFB_REQUIRE(!(row_sumsq || noise_mask) || (row_len > 0 && n % row_len == 0), NFB_EINVAL,
+              "fused_sgd: per-row clipping / noise mask need row_len");
   float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
   cudaStream_t st = as_stream(stream);
   const int64_t work = skip_len > 0 ? (n / row_len) * (row_len - skip_len) : n;
@@ -235,6 +280,26 @@ extern "C" int nfb_fused_sgd_perm(float* p, void* g, int g_dtype, float* momentu
                         weight_decay, nesterov, first_step, grad_scale, noise_std, seed, offset,
                         row_len, zero_prefix, skip_lo, skip_hi, zero_from, stream, perm_out,
                         perm_group_stride, perm_lo, perm_rows, perm_inner, perm_taps);
+}
+
+// DP-SGD for a cohort in one launch: every row (client) is clipped to clip_norm by its own gradient
+// norm (row_sumsq from K-STATS) and gets Gaussian noise of std noise_std on the entries noise_mask
+// marks; step_ctr (device counter, may be null) makes the noise stream advance inside a replayed
+// graph.  perm_out may be null.  Other arguments as nfb_fused_sgd_perm.
+extern "C" int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_buf,
+                                void* lowp_out, int64_t n, float lr, float momentum,
+                                float dampening, float weight_decay, int nesterov, int first_step,
+                                float noise_std, uint64_t seed, uint64_t offset, int64_t row_len,
+                                int64_t zero_prefix, int64_t zero_from, const float* row_sumsq,
+                                float clip_norm, const uint8_t* noise_mask,
+                                const unsigned long long* step_ctr, void* perm_out,
+                                int64_t perm_group_stride, int64_t perm_lo, int64_t perm_rows,
+                                int perm_inner, int perm_taps, void* stream) {
+  return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
+                        weight_decay, nesterov, first_step, nullptr, noise_std, seed, offset,
+                        row_len, zero_prefix, 0, 0, zero_from, stream, perm_out, perm_group_stride,
+                        perm_lo, perm_rows, perm_inner, perm_taps, row_sumsq, clip_norm, noise_mask,
+                        step_ctr);
 }
 
 extern "C" int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg,

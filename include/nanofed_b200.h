@@ -167,6 +167,18 @@ int nfb_fused_sgd_perm(float* p, void* g, int g_dtype, float* momentum_buf, void
                        int64_t skip_lo, int64_t skip_hi, int64_t zero_from, void* perm_out,
                        int64_t perm_group_stride, int64_t perm_lo, int64_t perm_rows,
                        int perm_inner, int perm_taps, void* stream);
+/* DP-SGD for a whole cohort: row r (client) is clipped by min(1, clip_norm / sqrt(row_sumsq[r]))
+ * and gets N(0, noise_std^2) on the entries noise_mask marks (nanofed/trainer/private.py:54-86:
+ * clip_grad_norm_ + per-parameter Gaussian noise); step_ctr (device, optional) advances the noise
+ * stream between the steps of a replayed CUDA graph; perm_out optional.                        */
+int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_buf, void* lowp_out, int64_t n,
+                     float lr, float momentum, float dampening, float weight_decay, int nesterov,
+                     int first_step, float noise_std, uint64_t seed, uint64_t offset,
+                     int64_t row_len, int64_t zero_prefix, int64_t zero_from,
+                     const float* row_sumsq, float clip_norm, const uint8_t* noise_mask,
+                     const unsigned long long* step_ctr, void* perm_out, int64_t perm_group_stride,
+                     int64_t perm_lo, int64_t perm_rows, int perm_inner, int perm_taps,
+                     void* stream);
 int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg, float* exp_avg_sq,
                    void* lowp_out, int64_t n, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float bias_corr1, float bias_corr2, int decoupled,

@@ -116,8 +116,16 @@ class MnistCohortNet:
         self.tc_conv1 = os.environ.get("NFB_NO_TC_CONV1") is None
         # K-OPT also writes the permuted bf16 conv2 weights (needs one w2p buffer for all clients)
         self.opt_writes_w2p = (self.group == c_all and os.environ.get("NFB_NO_OPT_W2P") is None)
-        # momentum needs the gradient history in a buffer: only plain SGD is fused
-        self.fuse_fc1_sgd = (cfg.momentum == 0.0 and os.environ.get("NFB_NO_FUSED_SGD") is None)
+        # DP-SGD on the client (reference PrivateTrainer semantics: clip the batch gradient to C, add
+        # N(0, (sigma C)^2) per parameter): every client's gradient norm comes from K-STATS over the
+        # gradient slab, the clip factor and the Philox noise are applied inside K-OPT
+        self.local_dp = getattr(cfg, "local_privacy", None)
+        self.dp_seed = int(getattr(cfg, "dp_seed", None) if getattr(cfg, "dp_seed", None) is not None
+                           else int.from_bytes(os.urandom(8), "little") >> 1)
+        # momentum needs the gradient history in a buffer: only plain SGD is fused; DP needs the
+        # complete gradient (its norm) before any of it is applied
+        self.fuse_fc1_sgd = (cfg.momentum == 0.0 and self.local_dp is None
+                             and os.environ.get("NFB_NO_FUSED_SGD") is None)
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
         # atomic-accumulated gradient entries (conv1.*, conv2.*) sit in front of fc1.weight
         self._atomic_prefix = self.off["fc1.weight"]
@@ -150,12 +158,20 @@ class MnistCohortNet:
         """One fused K-OPT launch over all clients; also hands the atomically accumulated
         gradient entries (conv1.*, conv2.*) back zeroed for the next step."""
         cfg, a = self.cfg, self.arena
+        dp_kw: dict[str, Any] = {}
+        if self.local_dp is not None:
+            ss, _ = ops.update_stats(self.grads)          # per-client squared gradient norm
+            dp_kw = dict(row_sumsq=ss, clip_norm=float(self.local_dp.max_gradient_norm),
+                         noise_std=float(self.local_dp.noise_multiplier
+                                         * self.local_dp.max_gradient_norm),
+                         noise_mask=a.noise_mask, seed=self.dp_seed,
+                         step_counter=self.rng_state[0:1])   # bumped by fc_head once per step
         ops.fused_sgd_(a.slots.view(-1), self.grads.view(-1), cfg.learning_rate,
                        momentum_buf=None if a.momentum is None else a.momentum.view(-1),
                        momentum=cfg.momentum, weight_decay=cfg.weight_decay,
                        first_step=(step == 0), lowp_out=a.slots_lowp.view(-1),
                        row_len=self.n_total, zero_grad_prefix=self._atomic_prefix,
-                       skip_range=self._fc1_range if self.fuse_fc1_sgd else None,
+                       skip_range=self._fc1_range if self.fuse_fc1_sgd else None, **dp_kw,
                        zero_grad_from=self._fc1_range[1],   # fc1.bias / fc2.*: fc_head's atomics
                        # the tap-major bf16 conv2 weights of the NEXT step come out of this pass
                        perm_out=(self.w2p.view(self.c_all, -1), self.off["conv2.weight"], 64, 32, 9)

@@ -128,6 +128,9 @@ def _declare(L: C.CDLL) -> None:
         "nfb_fused_sgd_perm": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
                                _vp, _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp, _i64,
                                _i64, _i64, _i32, _i32, _vp],
+        "nfb_fused_sgd_dp": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
+                             _f32, _u64, _u64, _i64, _i64, _i64, _vp, _f32, _vp, _vp, _vp, _i64,
+                             _i64, _i64, _i32, _i32, _vp],
         "nfb_fused_adam": [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32,
                            _f32, _f32, _i32, _vp, _vp],
         "nfb_xent_fused": [_vp, _i32, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _f32, _vp, _vp,
@@ -364,11 +367,36 @@ def fused_sgd_(
     skip_range: tuple[int, int] | None = None,
     zero_grad_from: int = 0,
     perm_out: tuple[torch.Tensor, int, int, int, int] | None = None,
+    row_sumsq: torch.Tensor | None = None,
+    clip_norm: float = 0.0,
+    noise_mask: torch.Tensor | None = None,
+    step_counter: torch.Tensor | None = None,
 ) -> torch.Tensor:
+    """``row_sumsq`` / ``clip_norm`` / ``noise_mask`` / ``step_counter``: DP-SGD for a cohort — row
+    ``r`` of the ``[rows, row_len]`` buffers is clipped by ``min(1, clip_norm / sqrt(row_sumsq[r]))``
+    and gets ``N(0, noise_std²)`` on the masked entries; ``step_counter`` (device int64) advances
+    the noise stream inside a replayed CUDA graph."""
     assert p.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous()
     assert p.numel() == g.numel()
     if momentum == 0.0:
         momentum_buf = None
+    if row_sumsq is not None or noise_mask is not None or step_counter is not None:
+        assert grad_scale is None and skip_range is None and row_len > 0
+        if noise_mask is not None:
+            noise_mask = noise_mask.to(device=p.device, dtype=torch.uint8).contiguous()
+        pout = (None, 0, 0, 0, 0, 0)
+        if perm_out is not None:
+            out_t, plo, prows, pinner, ptaps = perm_out
+            pout = (out_t.data_ptr(), out_t.stride(0), int(plo), int(prows), int(pinner), int(ptaps))
+        _check(lib().nfb_fused_sgd_dp(
+            p.data_ptr(), g.data_ptr(), _dt(g), _ptr(momentum_buf), _ptr(lowp_out), p.numel(),
+            float(lr), float(momentum), float(dampening), float(weight_decay),
+            1 if nesterov else 0, 1 if first_step else 0, float(noise_std), seed & (2**64 - 1),
+            offset, int(row_len), int(zero_grad_prefix), int(zero_grad_from), _ptr(row_sumsq),
+            float(clip_norm), _ptr(noise_mask), _ptr(step_counter), *pout, _stream(p)),
+            "fused_sgd_dp")
+        _count()
+        return p
     if grad_scale is not None:
         grad_scale = grad_scale.to(device=p.device, dtype=torch.float32).reshape(1)
     common = (p.data_ptr(), g.data_ptr(), _dt(g), _ptr(momentum_buf), _ptr(lowp_out), p.numel(),

@@ -189,8 +189,16 @@ def fused_sgd_(
     skip_range: tuple[int, int] | None = None,
     zero_grad_from: int = 0,
     perm_out: tuple[torch.Tensor, int, int, int, int] | None = None,
+    row_sumsq: torch.Tensor | None = None,
+    clip_norm: float = 0.0,
+    noise_mask: torch.Tensor | None = None,
+    step_counter: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """torch.optim.SGD semantics on flat buffers, with optional DP-SGD pre-processing.
+
+    Cohort form: ``row_sumsq`` ``[rows]`` clips row ``r`` by ``min(1, clip_norm / (sqrt(ss_r) +
+    1e-6))``, ``noise_mask`` ``[row_len]`` limits the noise to real parameter entries and
+    ``step_counter`` shifts the noise stream by ``step·ceil(n/4)`` Philox groups.
 
     ``g' = g·grad_scale + noise_std·z`` (clip factor and Gaussian noise, both optional),
     then ``g' += wd·p``; momentum buffer ``b = g'`` on the first step else
@@ -206,8 +214,17 @@ def fused_sgd_(
     gf = g.to(torch.float32)
     if grad_scale is not None:
         gf = gf * grad_scale.to(torch.float32)
+    if row_sumsq is not None:
+        c = torch.clamp(clip_norm / (row_sumsq.to(torch.float32).sqrt() + 1e-6), max=1.0)
+        gf = (gf.view(-1, row_len) * c.view(-1, 1).to(gf.device)).reshape(g.shape)
     if noise_std > 0:
-        gf = gf + noise_std * philox.normal(g.numel(), seed, offset).reshape(g.shape).to(g.device)
+        shift = 0
+        if step_counter is not None:
+            shift = int(step_counter.reshape(-1)[0]) * ((g.numel() + 3) // 4) * 4
+        z = philox.normal(g.numel(), seed, offset + shift).reshape(g.shape).to(g.device)
+        if noise_mask is not None:
+            z = (z.view(-1, row_len) * noise_mask.to(z.dtype).view(1, -1).to(z.device)).reshape(g.shape)
+        gf = gf + noise_std * z
     if weight_decay != 0:
         gf = gf + weight_decay * p.to(torch.float32)
     if momentum != 0 and momentum_buf is not None:

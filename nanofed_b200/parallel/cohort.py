@@ -72,6 +72,9 @@ class CohortConfig:
     # broadcast launch at all.  False keeps the client rows as trained after a round (debugging).
     fuse_bcast: bool = True
     privacy: PrivacyConfig | None = None  # central DP fused into K-AGG
+    # DP-SGD on the clients (reference PrivateTrainer: batch gradient clipped to max_gradient_norm,
+    # N(0, (noise_multiplier * max_gradient_norm)^2) added per parameter), inside K-OPT
+    local_privacy: PrivacyConfig | None = None
     # Seed of the DP noise stream.  None (default): drawn from os.urandom on rank 0 and shared with
     # the other ranks, so the noise cannot be regenerated from the configuration.  A fixed value is
     # for tests and reproducibility studies only - it voids the privacy guarantee.
@@ -227,6 +230,15 @@ class AutogradCohort:
         # weight decay is a property of PARAMETERS: the fused optimizer runs over whole arena rows,
         # which also hold BatchNorm running statistics, counters and padding (torch.optim.SGD never
         # touches those), so the decay term is added to the gradients of parameter columns only
+        self._dp_step = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self._dp_seed = int(cfg.dp_seed if getattr(cfg, "dp_seed", None) is not None
+                            else int.from_bytes(os.urandom(8), "little") >> 1)
+        self._dp_noise_mask = None
+        if getattr(cfg, "local_privacy", None) is not None:
+            pm = torch.zeros(layout.total, dtype=torch.uint8)      # noise on PARAMETERS only
+            for n in self._param_names:
+                pm[layout[n].offset : layout[n].offset + layout[n].numel] = 1
+            self._dp_noise_mask = pm.to(self.device)
         self._param_mask = None
         if cfg.weight_decay != 0.0:
             pm = torch.zeros(layout.total, dtype=torch.float32)
@@ -306,13 +318,22 @@ class AutogradCohort:
             else:
                 for k in range(c):
                     self._client_step(self.workers[0], k, step)
+            dp_kw: dict[str, Any] = {}
+            dp = getattr(cfg, "local_privacy", None)
+            if dp is not None:       # client-side DP-SGD: clip each client's batch gradient, add noise
+                ss, _ = ops.update_stats(arena.grads)
+                self._dp_step.add_(1)
+                dp_kw = dict(row_sumsq=ss, clip_norm=float(dp.max_gradient_norm),
+                             noise_std=float(dp.noise_multiplier * dp.max_gradient_norm),
+                             noise_mask=self._dp_noise_mask, seed=self._dp_seed,
+                             step_counter=self._dp_step, row_len=arena.layout.total)
             if self._param_mask is not None:
                 arena.grads.addcmul_(arena.slots, self._param_mask, value=cfg.weight_decay)
             ops.fused_sgd_(
                 arena.slots.view(-1), arena.grads.view(-1), cfg.learning_rate,
                 momentum_buf=None if arena.momentum is None else arena.momentum.view(-1),
                 momentum=cfg.momentum, weight_decay=0.0,
-                first_step=(step == 0),
+                first_step=(step == 0), **dp_kw,
             )
 
     def local_steps(self) -> None:
@@ -405,6 +426,8 @@ class FedSimulation:
             engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18")
                                    and self.device.type == "cuda"
                                    and _grouped_available()) else "autograd"
+            if cfg.local_privacy is not None and cfg.model == "resnet18":
+                engine = "autograd"      # client-side DP-SGD: MNIST grouped engine and autograd
         if cfg.compute_dtype not in ("bf16", "fp32"):
             raise ValueError(f"compute_dtype must be 'bf16' or 'fp32', got {cfg.compute_dtype!r}")
         if cfg.compute_dtype == "fp32":
@@ -415,6 +438,9 @@ class FedSimulation:
                 raise ValueError("engine='grouped' computes in bf16 (fp32 accumulate/master); use "
                                  "compute_dtype='bf16', or engine='autograd' for fp32 compute")
             engine = "autograd"
+        if engine == "grouped" and cfg.model == "resnet18" and cfg.local_privacy is not None:
+            raise ValueError("client-side DP-SGD (local_privacy) is implemented in the MNIST grouped "
+                             "engine and the autograd engine, not in the ResNet grouped engine")
         if engine == "grouped" and cfg.model not in ("mnist_cnn", "resnet18"):
             raise ValueError(f"engine='grouped' has no hand-written network for {cfg.model!r} "
                              "(available: mnist_cnn, resnet18); use engine='autograd'")
@@ -458,6 +484,7 @@ class FedSimulation:
                                         allow_fallback=cfg.allow_nccl_fallback)
 
         self.accountant = GaussianAccountant(cfg.privacy) if cfg.privacy else None
+        self.local_accountant = GaussianAccountant(cfg.local_privacy) if cfg.local_privacy else None
         self._noise_offset = 0
         self._round = 0
         world = self.rank.world_size
@@ -760,6 +787,15 @@ class FedSimulation:
             spent = self.accountant.get_privacy_spent()
             outcome.agg_metrics["privacy_epsilon"] = spent.epsilon_spent
             outcome.agg_metrics["privacy_delta"] = spent.delta_spent
+        if self.local_accountant is not None:
+            # every client ran local_steps noisy steps on batches of batch_size (one budget per
+            # client, identical for all of them: reference PrivateTrainer._add_noise)
+            for _ in range(self.cfg.local_steps):
+                self.local_accountant.add_noise_event(self.cfg.local_privacy.noise_multiplier,
+                                                      self.cfg.batch_size)
+            spent = self.local_accountant.get_privacy_spent()
+            outcome.agg_metrics["local_privacy_epsilon"] = spent.epsilon_spent
+            outcome.agg_metrics["local_privacy_delta"] = spent.delta_spent
         return outcome
 
     def _summarise(self, round_id: int, stats: torch.Tensor | None = None) -> RoundOutcome:

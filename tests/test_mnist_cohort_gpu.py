@@ -203,3 +203,52 @@ def test_deadline_times_local_training_with_cuda_events():
     before = sim.arena.master.clone()
     sim.run_round()
     assert not torch.equal(before, sim.arena.master) and torch.isfinite(sim.arena.master).all()
+
+
+def test_dp_sgd_mode_of_the_grouped_engine_matches_the_oracle_update():
+    """`local_privacy`: per-client clip factor from K-STATS over the gradient slab, clip + Philox
+    noise inside K-OPT.  The gradients themselves are checked elsewhere; here the UPDATE rule:
+    new = old - lr * (g * min(1, C / |g|) + sigma * C * z) with z from the same Philox stream, and
+    the overhead of the mode (one K-STATS pass, no fused fc1 update) stays small."""
+    from nanofed_b200 import ops
+    from nanofed_b200.data.synthetic import make_client_shards
+    from nanofed_b200.models import MNISTModel
+    from nanofed_b200.models.mnist_cohort import MnistCohortNet
+    from nanofed_b200.ops import philox, tc
+    from nanofed_b200.parallel.cohort import CohortConfig
+    from nanofed_b200.privacy import PrivacyConfig
+    from nanofed_b200.runtime.arena import Arena
+    from nanofed_b200.runtime.flat import FlatLayout
+
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    c, b = 3, 16
+    priv = PrivacyConfig(epsilon=10.0, noise_multiplier=0.2, max_gradient_norm=0.05)
+    cfg = CohortConfig(clients_per_gpu=c, samples_per_client=b, batch_size=b, learning_rate=0.1,
+                       use_cuda_graph=False, local_privacy=priv, dp_seed=77)
+    model = MNISTModel()
+    layout = FlatLayout.from_module(model)
+    arena = Arena(layout, c, dev, with_lowp=True, with_grads=False)
+    arena.load_global(model.state_dict())
+    shards = make_client_shards(c, b, seed=3).to(dev)
+    eng = MnistCohortNet(cfg, arena, shards, dropout=False)
+    assert eng.local_dp is not None and not eng.fuse_fc1_sgd
+    ops.bcast_global(arena.master, arena.slots, arena.slots_lowp, None)
+    before = arena.slots.clone()
+    eng._step_group(0, 0)
+    torch.cuda.synchronize()
+    tc.check_status(dev)
+    g = eng.grads.clone()
+    step_ctr = int(eng.rng_state[0])
+    eng._apply_optimizer(0)
+    torch.cuda.synchronize()
+    n = layout.total
+    shift = step_ctr * ((c * n + 3) // 4) * 4
+    z = philox.normal(c * n, 77, shift).view(c, n).to(dev)
+    mask = arena.noise_mask.float()
+    norms = g.norm(dim=1)
+    assert float(norms.min()) > 0.05                       # the clip is active for every client
+    clip = torch.clamp(0.05 / (norms + 1e-6), max=1.0).view(-1, 1)
+    want = before - 0.1 * (g * clip + 0.2 * 0.05 * z * mask)
+    torch.testing.assert_close(arena.slots, want, rtol=1e-4, atol=1e-6)
+    assert torch.equal(arena.slots_lowp, arena.slots.bfloat16())
