@@ -290,14 +290,16 @@ extern "C" int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_
                                 void* lowp_out, int64_t n, float lr, float momentum,
                                 float dampening, float weight_decay, int nesterov, int first_step,
                                 float noise_std, uint64_t seed, uint64_t offset, int64_t row_len,
-                                int64_t zero_prefix, int64_t zero_from, const float* row_sumsq,
+                                int64_t zero_prefix, int64_t skip_lo, int64_t skip_hi,
+                                int64_t zero_from, const float* row_sumsq,
                                 float clip_norm, const uint8_t* noise_mask,
                                 const unsigned long long* step_ctr, void* perm_out,
                                 int64_t perm_group_stride, int64_t perm_lo, int64_t perm_rows,
                                 int perm_inner, int perm_taps, void* stream) {
   return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
                         weight_decay, nesterov, first_step, nullptr, noise_std, seed, offset,
-                        row_len, zero_prefix, 0, 0, zero_from, stream, perm_out, perm_group_stride,
+                        row_len, zero_prefix, skip_lo, skip_hi, zero_from, stream, perm_out,
+                        perm_group_stride,
                         perm_lo, perm_rows, perm_inner, perm_taps, row_sumsq, clip_norm, noise_mask,
                         step_ctr);
 }

@@ -21,6 +21,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "philox.cuh"
 #include "tc_common.cuh"
 
 namespace nfb {
@@ -53,6 +54,14 @@ struct GemmArgs {
   int vec_store;     // n contiguous (out_ns == 1), non-atomic, 16-byte aligned rows
   int tma_store;     // stage 32-row x 128-byte chunks in smem and write them with TMA (map_o)
   float sgd_lr, sgd_wd;  // EPI == 1: w <- w - lr * (acc + wd * w), w addressed by map_o
+  // EPI == 1 with DP-SGD: g' = acc * min(1, clip / sqrt(dp_ss[group])) + dp_noise * z, where z is
+  // the SAME Philox stream K-OPT uses for the other parameters of the row (element index inside
+  // the [groups][dp_row_len] slab = group * dp_row_len + dp_w_off + m * n_valid + n)
+  const float* dp_ss;
+  float dp_clip, dp_noise;
+  unsigned long long dp_seed, dp_group0, dp_groups_total;
+  const unsigned long long* dp_step;
+  long long dp_row_len, dp_w_off;
   int* status;       // set to 1 if a pipeline wait timed out
 };
 
@@ -262,6 +271,11 @@ __global__ void __launch_bounds__(256, MINB)
       uint8_t* lstage = staging + 4 * 8192 + sub * 2048;
       const float lr = args.sgd_lr, wd = args.sgd_wd;
       const bool live = ok && n_iters > 0;
+      const float cs = args.dp_ss ? fminf(args.dp_clip / (sqrtf(args.dp_ss[g]) + 1e-6f), 1.f) : 1.f;
+      const unsigned long long dp_g0 =
+          args.dp_group0 + (args.dp_step ? *args.dp_step * args.dp_groups_total : 0ull);
+      const long long dp_row0 = static_cast<long long>(g) * args.dp_row_len + args.dp_w_off +
+                                static_cast<long long>(m) * args.n_valid + n0;
 #pragma unroll 1
       for (int c = 0; c < sgd_chunks; ++c) {
         const int buf = c & 1;
@@ -281,9 +295,15 @@ __global__ void __launch_bounds__(256, MINB)
           uint8_t* addr = wbuf + lane * 128 + ((p ^ (lane & 7)) * 16);
           float w4[4];
           unpack<float>(*reinterpret_cast<const uint4*>(addr), w4);
+          float zn[4] = {0.f, 0.f, 0.f, 0.f};
+          if (args.dp_noise > 0.f) {
+            const float4 z = Philox::normal4(dp_g0 + ((dp_row0 + c * 32 + 4 * p) >> 2), args.dp_seed);
+            zn[0] = args.dp_noise * z.x; zn[1] = args.dp_noise * z.y;
+            zn[2] = args.dp_noise * z.z; zn[3] = args.dp_noise * z.w;
+          }
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float gr = fmaf(wd, w4[e], __uint_as_float(r[4 * p + e]));
+            const float gr = fmaf(wd, w4[e], fmaf(cs, __uint_as_float(r[4 * p + e]), zn[e]));
             nw[4 * p + e] = fmaf(-lr, gr, w4[e]);
           }
           st_vec(addr, pack<float>(nw + 4 * p));
@@ -688,6 +708,45 @@ int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* A, const nfb_tc_operand* B, in
   g.m_valid = j; g.n_valid = i;
   g.vec_store = 1;
   g.sgd_lr = lr; g.sgd_wd = weight_decay;
+  g.status = status;
+  Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
+  Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};
+  return launch<true, 128, true, 128, 64, 128, 1, 2, 2, 1>(a, b, (j + BM - 1) / BM, (i + 127) / 128,
+                                                         groups, g, as_stream(stream), w_lowp,
+                                                         lowp_gs);
+}
+
+// nfb_tc_linear_wgrad_sgd with the DP-SGD front end in the epilogue: the gradient tile in TMEM is
+// scaled by the client's clip factor min(1, clip / sqrt(row_sumsq[client])) and gets Gaussian noise
+// from the Philox stream at the weight's position inside the [groups][row_len] parameter slab
+// (w_off = offset of this weight in a row), i.e. the same stream nfb_fused_sgd_dp uses for the
+// rest of the row.  row_sumsq must hold the COMPLETE squared gradient norm of each client (this
+// weight's part is obtained without materialising it: ghost norm, nfb_mnist_dp_norm).
+int nfb_tc_linear_wgrad_sgd_dp(const nfb_tc_operand* A, const nfb_tc_operand* B, int groups, int j,
+                               int i, int inner, float* w, long long w_gs, void* w_lowp,
+                               long long lowp_gs, float lr, float weight_decay,
+                               const float* row_sumsq, float clip_norm, float noise_std,
+                               uint64_t seed, uint64_t offset, const unsigned long long* step_ctr,
+                               long long row_len, long long w_off, int* status, void* stream) {
+  using namespace nfb;
+  using namespace nfb::tc;
+  NFB_REQUIRE(A && B && w && w_lowp && status && row_sumsq, NFB_EINVAL, "linear_wgrad_sgd_dp: null pointer");
+  NFB_REQUIRE(groups >= 1 && groups <= 65535 && j >= 1 && i >= 32 && i % 32 == 0 && inner >= 1,
+              NFB_EINVAL, "linear_wgrad_sgd_dp: bad shape");
+  NFB_REQUIRE((row_len & 3) == 0 && (w_off & 3) == 0 && (offset & 3u) == 0, NFB_EINVAL,
+              "linear_wgrad_sgd_dp: row length / offsets must be multiples of 4");
+  GemmArgs g{};
+  g.taps = 1; g.inner = inner; g.k_split = 1;
+  g.tap[0] = Tap{0, 0, 0, 0};
+  g.out = w; g.out_bf16 = 0; g.atomic = 0;
+  g.out_gs = w_gs; g.out_ms = i; g.out_ns = 1; g.out_ts = 0;
+  g.m_valid = j; g.n_valid = i;
+  g.vec_store = 1;
+  g.sgd_lr = lr; g.sgd_wd = weight_decay;
+  g.dp_ss = row_sumsq; g.dp_clip = clip_norm; g.dp_noise = noise_std; g.dp_seed = seed;
+  g.dp_group0 = offset >> 2;
+  g.dp_groups_total = static_cast<unsigned long long>((static_cast<long long>(groups) * row_len + 3) >> 2);
+  g.dp_step = step_ctr; g.dp_row_len = row_len; g.dp_w_off = w_off;
   g.status = status;
   Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
   Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};

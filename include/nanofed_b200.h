@@ -174,8 +174,8 @@ int nfb_fused_sgd_perm(float* p, void* g, int g_dtype, float* momentum_buf, void
 int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_buf, void* lowp_out, int64_t n,
                      float lr, float momentum, float dampening, float weight_decay, int nesterov,
                      int first_step, float noise_std, uint64_t seed, uint64_t offset,
-                     int64_t row_len, int64_t zero_prefix, int64_t zero_from,
-                     const float* row_sumsq, float clip_norm, const uint8_t* noise_mask,
+                     int64_t row_len, int64_t zero_prefix, int64_t skip_lo, int64_t skip_hi,
+                     int64_t zero_from, const float* row_sumsq, float clip_norm, const uint8_t* noise_mask,
                      const unsigned long long* step_ctr, void* perm_out, int64_t perm_group_stride,
                      int64_t perm_lo, int64_t perm_rows, int perm_inner, int perm_taps,
                      void* stream);
@@ -269,6 +269,20 @@ int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* dy, const nfb_tc_operand* x, i
  * dy [samples][P][cout], u [samples][P][kdim] bf16 (unfolded patches, optionally with a ones
  * column for the bias term); inner = ceil(P / 64); out zero on entry.  Replaces the whole-batch
  * clip_grad_norm_ of nanofed/trainer/private.py:62-63 with true per-sample norms.           */
+/* Batch ghost norm: out[c] = |sum_b d[c][b] (x) x[c][b]|_F^2 + add_a[c] + add_b[c] from gram_x[c] =
+ * x x^T ([B][B] fp32, consumed and zeroed) and d [C][B][J] bf16 - the squared norm of a linear
+ * layer's batch weight gradient without materialising it (DP-SGD clip of the grouped engine;
+ * reference nanofed/trainer/private.py:62-63 computes it from the materialised gradient).    */
+int nfb_batch_ghost_norm(float* gram_x, const void* d, int clients, int batch, int J,
+                         const float* add_a, const float* add_b, float* out, void* stream);
+/* nfb_tc_linear_wgrad_sgd + DP-SGD front end in the epilogue (clip factor from row_sumsq, Philox
+ * noise at the weight's position in the [groups][row_len] slab: same stream as nfb_fused_sgd_dp). */
+int nfb_tc_linear_wgrad_sgd_dp(const nfb_tc_operand* dy, const nfb_tc_operand* x, int groups, int j,
+                               int i, int inner, float* w, long long w_gs, void* w_lowp,
+                               long long lowp_gs, float lr, float weight_decay,
+                               const float* row_sumsq, float clip_norm, float noise_std,
+                               uint64_t seed, uint64_t offset, const unsigned long long* step_ctr,
+                               long long row_len, long long w_off, int* status, void* stream);
 int nfb_tc_psgn(const nfb_tc_operand* dy, const nfb_tc_operand* u, int samples, int cout, int kdim,
                 int inner, float* out, int* status, void* stream);
 int nfb_tc_fc_dgrad(const nfb_tc_operand* dy, const nfb_tc_operand* w, void* out, long long out_rs,

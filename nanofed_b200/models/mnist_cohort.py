@@ -126,6 +126,16 @@ class MnistCohortNet:
         # complete gradient (its norm) before any of it is applied
         self.fuse_fc1_sgd = (cfg.momentum == 0.0 and self.local_dp is None
                              and os.environ.get("NFB_NO_FUSED_SGD") is None)
+        # DP with the fc1 update still inside its GEMM: the norm of the (never written) fc1 weight
+        # gradient comes from a ghost norm - |sum_b dh_b (x) p_b|^2 = <dh dh^T, p p^T> - so the clip
+        # factor is known before the wgrad kernel runs and is applied, with the noise, in its epilogue
+        # MEASURED: slower than the materialised path (round 6.52 vs 5.83 ms; 3.98 ms without DP) -
+        # 38 M Box-Muller normals per step generated by the GEMM's four epilogue warps per CTA take
+        # longer than the K-OPT pass they replace (which spreads them over the whole GPU: +37 us).
+        # Kept behind NFB_FUSED_DP=1 with its test; the default is the materialised path.
+        self.fuse_fc1_dp = (self.local_dp is not None and cfg.momentum == 0.0 and self.group == c_all
+                            and os.environ.get("NFB_FUSED_DP") == "1")
+        self.gram = torch.zeros(c_all, b, b, dtype=torch.float32, device=dev) if self.fuse_fc1_dp else None
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
         # atomic-accumulated gradient entries (conv1.*, conv2.*) sit in front of fc1.weight
         self._atomic_prefix = self.off["fc1.weight"]
@@ -159,8 +169,24 @@ class MnistCohortNet:
         gradient entries (conv1.*, conv2.*) back zeroed for the next step."""
         cfg, a = self.cfg, self.arena
         dp_kw: dict[str, Any] = {}
+        skip = self._fc1_range if self.fuse_fc1_sgd else None
         if self.local_dp is not None:
-            ss, _ = ops.update_stats(self.grads)          # per-client squared gradient norm
+            if self.fuse_fc1_dp:
+                lo, hi = self._fc1_range
+                ss_a, _ = ops.update_stats(self.grads[:, :lo])       # conv1.*, conv2.*
+                ss_b, _ = ops.update_stats(self.grads[:, hi:])       # fc1.bias, fc2.*
+                tc.linear_fwd(self.p, self.p, self.gram, k_split=self.k_split_fc)   # p p^T per client
+                ss = native.batch_ghost_norm(self.gram, self.dh, ss_a, ss_b)
+                tc.linear_wgrad_sgd(self.dh, self.p, self.fc1_master, self.fc1_w, cfg.learning_rate,
+                                    cfg.weight_decay,
+                                    dp=dict(row_sumsq=ss, clip_norm=self.local_dp.max_gradient_norm,
+                                            noise_std=self.local_dp.noise_multiplier
+                                            * self.local_dp.max_gradient_norm, seed=self.dp_seed,
+                                            step_counter=self.rng_state[0:1], row_len=self.n_total,
+                                            w_off=lo))
+                skip = self._fc1_range
+            else:
+                ss, _ = ops.update_stats(self.grads)      # per-client squared gradient norm
             dp_kw = dict(row_sumsq=ss, clip_norm=float(self.local_dp.max_gradient_norm),
                          noise_std=float(self.local_dp.noise_multiplier
                                          * self.local_dp.max_gradient_norm),
@@ -171,7 +197,7 @@ class MnistCohortNet:
                        momentum=cfg.momentum, weight_decay=cfg.weight_decay,
                        first_step=(step == 0), lowp_out=a.slots_lowp.view(-1),
                        row_len=self.n_total, zero_grad_prefix=self._atomic_prefix,
-                       skip_range=self._fc1_range if self.fuse_fc1_sgd else None, **dp_kw,
+                       skip_range=skip, **dp_kw,
                        zero_grad_from=self._fc1_range[1],   # fc1.bias / fc2.*: fc_head's atomics
                        # the tap-major bf16 conv2 weights of the NEXT step come out of this pass
                        perm_out=(self.w2p.view(self.c_all, -1), self.off["conv2.weight"], 64, 32, 9)
@@ -219,7 +245,9 @@ class MnistCohortNet:
         pre = self.p1 > 0.0 and tc.fc_dgrad_is_persistent(128, b, 9216)
         tc.linear_dgrad(self.fc1_w[g0:g1], self.dh, self.dp,
                         scale=1.0 / (1.0 - self.p1) if pre else 1.0)
-        if self.fuse_fc1_sgd:
+        if self.fuse_fc1_dp:
+            pass       # DP: the fc1 update needs the client's total gradient norm: _apply_optimizer
+        elif self.fuse_fc1_sgd:
             # 96% of the parameters are fc1.weight: its gradient is applied inside the GEMM
             # epilogue (after the data gradient above has read the old weights) and never
             # written; K-OPT then skips that range

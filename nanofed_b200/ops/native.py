@@ -129,8 +129,9 @@ def _declare(L: C.CDLL) -> None:
                                _vp, _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp, _i64,
                                _i64, _i64, _i32, _i32, _vp],
         "nfb_fused_sgd_dp": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
-                             _f32, _u64, _u64, _i64, _i64, _i64, _vp, _f32, _vp, _vp, _vp, _i64,
-                             _i64, _i64, _i32, _i32, _vp],
+                             _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp, _f32, _vp, _vp,
+                             _vp, _i64, _i64, _i64, _i32, _i32, _vp],
+        "nfb_batch_ghost_norm": [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
         "nfb_fused_adam": [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32,
                            _f32, _f32, _i32, _vp, _vp],
         "nfb_xent_fused": [_vp, _i32, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _f32, _vp, _vp,
@@ -381,7 +382,8 @@ def fused_sgd_(
     if momentum == 0.0:
         momentum_buf = None
     if row_sumsq is not None or noise_mask is not None or step_counter is not None:
-        assert grad_scale is None and skip_range is None and row_len > 0
+        assert grad_scale is None and row_len > 0
+        lo, hi = skip_range if skip_range is not None else (0, 0)
         if noise_mask is not None:
             noise_mask = noise_mask.to(device=p.device, dtype=torch.uint8).contiguous()
         pout = (None, 0, 0, 0, 0, 0)
@@ -392,7 +394,8 @@ def fused_sgd_(
             p.data_ptr(), g.data_ptr(), _dt(g), _ptr(momentum_buf), _ptr(lowp_out), p.numel(),
             float(lr), float(momentum), float(dampening), float(weight_decay),
             1 if nesterov else 0, 1 if first_step else 0, float(noise_std), seed & (2**64 - 1),
-            offset, int(row_len), int(zero_grad_prefix), int(zero_grad_from), _ptr(row_sumsq),
+            offset, int(row_len), int(zero_grad_prefix), int(lo), int(hi), int(zero_grad_from),
+            _ptr(row_sumsq),
             float(clip_norm), _ptr(noise_mask), _ptr(step_counter), *pout, _stream(p)),
             "fused_sgd_dp")
         _count()
@@ -419,6 +422,19 @@ def fused_sgd_(
                "fused_sgd_skip")
     _count()
     return p
+
+
+def batch_ghost_norm(gram_x: torch.Tensor, d: torch.Tensor, add_a=None, add_b=None) -> torch.Tensor:
+    """``out[c] = ‖Σ_b d[c,b] ⊗ x[c,b]‖_F² + add_a[c] + add_b[c]`` from ``gram_x[c] = x xᵀ`` (fp32
+    ``[C, B, B]``, consumed and zeroed) and ``d`` (bf16 ``[C, B, J]``)."""
+    c, b, j = d.shape
+    assert gram_x.shape == (c, b, b) and gram_x.dtype == torch.float32 and gram_x.is_contiguous()
+    assert d.dtype == torch.bfloat16 and d.is_contiguous()
+    out = torch.empty(c, dtype=torch.float32, device=d.device)
+    _check(lib().nfb_batch_ghost_norm(gram_x.data_ptr(), d.data_ptr(), c, b, j, _ptr(add_a),
+                                      _ptr(add_b), out.data_ptr(), _stream(d)), "batch_ghost_norm")
+    _count()
+    return out
 
 
 def fused_adam_(

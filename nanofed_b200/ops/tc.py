@@ -320,7 +320,7 @@ def linear_fwd(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, k_split: int
 
 
 def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp: torch.Tensor,
-                     lr: float, weight_decay: float = 0.0) -> None:
+                     lr: float, weight_decay: float = 0.0, dp: dict | None = None) -> None:
     """``w[c, j, i] -= lr·(Σ_b dy[c, b, j]·x[c, b, i] + wd·w)`` and ``w_lowp = bf16(w)`` in ONE
     kernel: the weight gradient is consumed in the tcgen05 epilogue and never written.  ``w`` (fp32)
     and ``w_lowp`` (bf16) are ``[C, j, i]`` views with contiguous ``[j, i]`` blocks and arbitrary
@@ -340,6 +340,28 @@ def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp:
     assert dy.shape[0] == c and x.shape[0] == c and dy.shape[2] == j and x.shape[2] == i
     oa, ob = _operand(dy), _operand(x)
     st = status_word(dy.device)
+    if dp is not None:
+        # DP-SGD front end in the epilogue: dp = {row_sumsq, clip_norm, noise_std, seed, offset,
+        # step_counter, row_len, w_off} (see nfb_tc_linear_wgrad_sgd_dp)
+        if not getattr(lib, "_wgrad_sgd_dp_declared", False):
+            ll = C.c_longlong
+            lib.nfb_tc_linear_wgrad_sgd_dp.restype = C.c_int
+            lib.nfb_tc_linear_wgrad_sgd_dp.argtypes = [
+                C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, ll,
+                C.c_void_p, ll, C.c_float, C.c_float, C.c_void_p, C.c_float, C.c_float,
+                C.c_uint64, C.c_uint64, C.c_void_p, ll, ll, C.c_void_p, C.c_void_p]
+            lib._wgrad_sgd_dp_declared = True
+        ctr = dp.get("step_counter")
+        code = lib.nfb_tc_linear_wgrad_sgd_dp(
+            C.byref(oa), C.byref(ob), c, j, i, (dy.shape[1] + 63) // 64, w.data_ptr(), w.stride(0),
+            w_lowp.data_ptr(), w_lowp.stride(0), float(lr), float(weight_decay),
+            dp["row_sumsq"].data_ptr(), float(dp["clip_norm"]), float(dp["noise_std"]),
+            int(dp["seed"]) & (2**64 - 1), int(dp.get("offset", 0)),
+            ctr.data_ptr() if ctr is not None else None, int(dp["row_len"]), int(dp["w_off"]),
+            st.data_ptr(), torch.cuda.current_stream(dy.device).cuda_stream)
+        native._check(code, "tc_linear_wgrad_sgd_dp")
+        native._count()
+        return
     code = lib.nfb_tc_linear_wgrad_sgd(C.byref(oa), C.byref(ob), c, j, i, (dy.shape[1] + 63) // 64,
                                        w.data_ptr(), w.stride(0), w_lowp.data_ptr(),
                                        w_lowp.stride(0), float(lr), float(weight_decay),

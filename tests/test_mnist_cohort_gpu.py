@@ -205,16 +205,11 @@ def test_deadline_times_local_training_with_cuda_events():
     assert not torch.equal(before, sim.arena.master) and torch.isfinite(sim.arena.master).all()
 
 
-def test_dp_sgd_mode_of_the_grouped_engine_matches_the_oracle_update():
-    """`local_privacy`: per-client clip factor from K-STATS over the gradient slab, clip + Philox
-    noise inside K-OPT.  The gradients themselves are checked elsewhere; here the UPDATE rule:
-    new = old - lr * (g * min(1, C / |g|) + sigma * C * z) with z from the same Philox stream, and
-    the overhead of the mode (one K-STATS pass, no fused fc1 update) stays small."""
+def _dp_engine(fused: bool):
     from nanofed_b200 import ops
     from nanofed_b200.data.synthetic import make_client_shards
     from nanofed_b200.models import MNISTModel
     from nanofed_b200.models.mnist_cohort import MnistCohortNet
-    from nanofed_b200.ops import philox, tc
     from nanofed_b200.parallel.cohort import CohortConfig
     from nanofed_b200.privacy import PrivacyConfig
     from nanofed_b200.runtime.arena import Arena
@@ -231,9 +226,29 @@ def test_dp_sgd_mode_of_the_grouped_engine_matches_the_oracle_update():
     arena = Arena(layout, c, dev, with_lowp=True, with_grads=False)
     arena.load_global(model.state_dict())
     shards = make_client_shards(c, b, seed=3).to(dev)
-    eng = MnistCohortNet(cfg, arena, shards, dropout=False)
-    assert eng.local_dp is not None and not eng.fuse_fc1_sgd
+    import os
+
+    os.environ["NFB_FUSED_DP"] = "1" if fused else "0"
+    try:
+        eng = MnistCohortNet(cfg, arena, shards, dropout=False)
+    finally:
+        os.environ.pop("NFB_FUSED_DP", None)
+    assert eng.local_dp is not None and not eng.fuse_fc1_sgd and eng.fuse_fc1_dp == fused
     ops.bcast_global(arena.master, arena.slots, arena.slots_lowp, None)
+    return eng, arena, layout
+
+
+def test_dp_sgd_mode_of_the_grouped_engine_matches_the_oracle_update():
+    """`local_privacy`: per-client clip factor from the client's complete gradient norm, clip +
+    Philox noise inside the optimizer kernels.  (a) materialised path: new = old - lr * (g * min(1,
+    C / |g|) + sigma * C * z) with z from the same Philox stream; (b) fused path - the fc1 weight
+    gradient never written, its norm from the ghost norm <dh dh^T, p p^T>, clip + noise in the
+    wgrad epilogue - gives the same parameters."""
+    from nanofed_b200.ops import philox, tc
+
+    eng, arena, layout = _dp_engine(fused=False)
+    dev = arena.device
+    c = arena.num_clients
     before = arena.slots.clone()
     eng._step_group(0, 0)
     torch.cuda.synchronize()
@@ -252,3 +267,14 @@ def test_dp_sgd_mode_of_the_grouped_engine_matches_the_oracle_update():
     want = before - 0.1 * (g * clip + 0.2 * 0.05 * z * mask)
     torch.testing.assert_close(arena.slots, want, rtol=1e-4, atol=1e-6)
     assert torch.equal(arena.slots_lowp, arena.slots.bfloat16())
+    # (b) the fused path on the same state
+    eng2, arena2, _ = _dp_engine(fused=True)
+    eng2.step(0)
+    torch.cuda.synchronize()
+    tc.check_status(dev)
+    assert float(eng2.gram.abs().sum()) == 0.0             # Gram scratch handed back zeroed
+    lo, hi = eng2._fc1_range
+    assert float(eng2.grads[:, lo:hi].abs().sum()) == 0.0  # the fc1 gradient was never written
+    # same noise stream, clip factors equal up to the summation order of the norm
+    assert float((arena2.slots - arena.slots).abs().max()) < 2e-6
+    assert torch.equal(arena2.slots_lowp, arena2.slots.bfloat16())
