@@ -27,6 +27,7 @@ exchange models through the peer-memory arena (``parallel.peer``).
 from __future__ import annotations
 
 import asyncio
+import copy
 import json
 from dataclasses import dataclass
 from typing import TYPE_CHECKING, Any
@@ -186,7 +187,8 @@ class HTTPServer(ServerProtocol):
         half-updated tensor (and cache a torn body for this version)."""
         assert self._coordinator is not None
         state = self._coordinator.model_manager.model.state_dict()
-        return {k: v.detach().clone() for k, v in state.items()}
+        return {k: (v.detach().clone() if isinstance(v, torch.Tensor) else copy.deepcopy(v))
+                for k, v in state.items()}
 
     def _encode_model(self, version_id: str, binary: bool,
                       state: dict[str, Any] | None = None) -> bytes:
