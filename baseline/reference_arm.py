@@ -182,7 +182,14 @@ async def _run(args, torch) -> None:
         tasks.append(serve())
     else:
         await asyncio.sleep(3.0)  # server start-up on rank 0
-    await asyncio.gather(*tasks, return_exceptions=True)
+    # hard stop: a reference round cannot be interrupted from outside its own API, so a run whose
+    # rounds do not finish at all (very large client counts) is cut off after 4x the budget and
+    # reports whatever rounds completed (or "unavailable" if none did)
+    hard_cap = float(os.environ.get("NANOFED_REF_HARD_CAP_S", str(4 * budget)))
+    try:
+        await asyncio.wait_for(asyncio.gather(*tasks, return_exceptions=True), timeout=hard_cap)
+    except asyncio.TimeoutError:
+        state["stop"] = True
 
     if rank != 0:
         return

@@ -72,6 +72,11 @@ struct AllreduceArgs {
   // flag barrier), EVERY CTA replicates it into the local client rows (fp32 + bf16) and zeroes the
   // momentum rows.  Emulated ranks (one launch) use consecutive targets of `bc_rank_stride` rows.
   nfb_bcast_target bc;
+  // optional phase timestamps (%globaltimer, ns) for latency studies: [0] kernel start (CTA 0),
+  // [1] last producer CTA done (flag published), [2] consumer CTA 0 saw every peer's chunk-0 flag,
+  // [3] consumer CTA 0 has read the peers' scalars, [4] last consumer CTA done (before its signal),
+  // [5] completion flags of all peers seen, [6] broadcast tail finished (CTA 0).  Null = off.
+  unsigned long long* dbg;
 };
 
 __device__ __forceinline__ unsigned long long now_ns() {
@@ -215,6 +220,7 @@ __global__ void __launch_bounds__(256)
   const int64_t chunk = a.chunk_elems;              // multiple of 8*G... see host wrapper
   const int n_chunks = a.n_chunks;
 
+  if (a.dbg && blockIdx.x == 0 && threadIdx.x == 0) a.dbg[0] = now_ns();
   if (producer) {
     // ---- A. local unnormalised partial, chunk by chunk -----------------------------------
     const float q_local = agg_prologue(coef, a.K, me.counts, me.sumsq, me.mask, a.clip_norm,
@@ -256,6 +262,7 @@ __global__ void __launch_bounds__(256)
       if (s_last) {
         __threadfence();
         signal_peers(views, rank, G, 1 + c, a.epoch);
+        if (a.dbg && threadIdx.x == 0 && c == n_chunks - 1) a.dbg[1] = now_ns();
       }
       __syncthreads();
     }
@@ -280,16 +287,27 @@ __global__ void __launch_bounds__(256)
   for (int c = 0; c < n_chunks && ok; ++c) {
     ok = wait_peers(views, rank, G, 1 + c, a.epoch, a.spin_limit_ns, a.status);
     if (!ok) break;
+    if (a.dbg && cb == 0 && threadIdx.x == 0 && c == 0) a.dbg[2] = now_ns();
     if (!have_scal) {
-      for (int r = 0; r < G; ++r) {
-        const float* sc = views[r].scal;
-        float s_r, q_r;
-        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r) : "l"(sc) : "memory");
-        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r) : "l"(sc + 1) : "memory");
-        s_tot += s_r;
-        q_tot += q_r;
+      // all G pairs of peer loads go out before the first result is used: one NVLink round trip
+      // instead of G dependent ones (the loop used to add each value as it arrived)
+      float s_r[32], q_r[32];
+#pragma unroll 1
+      for (int r0 = 0; r0 < G; r0 += 8) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (r0 + i < G) {
+            const float* sc = views[r0 + i].scal;
+            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r[i]) : "l"(sc) : "memory");
+            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r[i]) : "l"(sc + 1) : "memory");
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (r0 + i < G) { s_tot += s_r[i]; q_tot += q_r[i]; }
       }
       have_scal = true;
+      if (a.dbg && cb == 0 && threadIdx.x == 0) a.dbg[3] = now_ns();
     }
     // every client of every rank masked out: keep the previous global model (same decision on
     // all ranks, s_tot is the global sum)
@@ -362,6 +380,7 @@ __global__ void __launch_bounds__(256)
   }
   __syncthreads();
   if (s_last) {
+    if (a.dbg && threadIdx.x == 0) a.dbg[4] = now_ns();
     // job-wide round metrics ride along: my per-client (loss, correct, samples) rows go into every
     // rank's stats_all[rank] before the completion flag, so each rank leaves with all of them
     if (a.my_stats && me.stats_all) {
@@ -377,6 +396,7 @@ __global__ void __launch_bounds__(256)
     __threadfence();
     signal_peers(views, rank, G, 0, a.epoch);
     const bool done = wait_peers(views, rank, G, 0, a.epoch, a.spin_limit_ns, a.status);
+    if (a.dbg && threadIdx.x == 0) a.dbg[5] = now_ns();
     if (a.bc.rows > 0 && done && threadIdx.x == 0) {
       __threadfence();
       asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(me.counters + kGoSlot), "r"(a.epoch)
@@ -391,6 +411,7 @@ __global__ void __launch_bounds__(256)
       if (bc.momentum) bc.momentum += static_cast<int64_t>(rank) * bc.rows * bc.momentum_stride;
     }
     bcast_tail(me.master, a.N, bc, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
+    if (a.dbg && cb == 0 && threadIdx.x == 0) a.dbg[6] = now_ns();
   }
 }
 
@@ -454,7 +475,8 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
                                     const float* mc_partial,
                                     float* mc_master, void* mc_lowp, int* status,
                                     uint64_t spin_limit_ns, int flags, const float* my_stats,
-                                    int stats_len, const void* bcast, void* stream) {
+                                    int stats_len, const void* bcast, unsigned long long* dbg,
+                                    void* stream) {
   using namespace nfb;
   NFB_REQUIRE(views_dev && status, NFB_EINVAL, "fedavg_allreduce: null pointer");
   NFB_REQUIRE(G >= 1 && G <= 32 && my_rank >= 0 && my_rank < G, NFB_EINVAL,
@@ -489,6 +511,7 @@ extern "C" int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, i
   a.local_only = (flags & 2) ? 1 : 0;
   a.my_stats = my_stats;
   a.stats_len = my_stats ? stats_len : 0;
+  a.dbg = dbg;
   a.bc = nfb_bcast_target{};
   if (bcast && !a.local_only) a.bc = *static_cast<const nfb_bcast_target*>(bcast);
   const RankView* views = static_cast<const RankView*>(views_dev);

@@ -221,7 +221,8 @@ int nfb_linear_psgn(const void* act, int act_dtype, const void* dout, int dout_d
  * nanofed/orchestration/coordinator.py:324-340).  When every client of every rank is masked out
  * the previous global model is kept.  bcast (optional, host nfb_bcast_target): K-BCAST as the tail
  * of the same kernel - after the completion barrier every CTA replicates the new model into the
- * local client rows and zeroes the momentum rows (counters needs 2 + 64 words then).  Replaces
+ * local client rows and zeroes the momentum rows (counters needs 2 + 64 words then).
+ * dbg_timestamps (optional, 8 words): %globaltimer at the kernel's phase boundaries.  Replaces
  * nanofed/server/aggregator/fedavg.py:53-63 +
  * communication/http upload/download (client.py:174-195, server.py:191-208).              */
 int nfb_allreduce_max_blocks(int x_dtype, int64_t K);
@@ -231,7 +232,8 @@ int nfb_fedavg_allreduce(const void* views_dev, int my_rank, int G, int ranks_in
                          uint64_t offset, uint32_t epoch, int producers, int64_t chunk_elems,
                          int grid_blocks, const float* mc_partial, float* mc_master,
                          void* mc_lowp, int* status, uint64_t spin_limit_ns, int flags,
-                         const float* my_stats, int stats_len, const void* bcast, void* stream);
+                         const float* my_stats, int stats_len, const void* bcast,
+                         unsigned long long* dbg_timestamps, void* stream);
 
 /* ---- K-GEMM / K-CONV: tcgen05 kernels (csrc/tc_gemm.cu, tc_fc.cu, tc_conv.cu, tc_conv1.cu) ---
  * Operands are bf16 [groups][rows][inner] views with unit inner stride (group = client); every

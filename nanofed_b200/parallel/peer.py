@@ -59,7 +59,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.nfb_fedavg_allreduce.restype = i32
     lib.nfb_fedavg_allreduce.argtypes = [vp, i32, i32, i32, i32, i64, i64, i64, f32, f32, vp, u64,
                                          u64, u32, i32, i64, i32, vp, vp, vp, vp, u64, i32, vp,
-                                         i32, vp, vp]
+                                         i32, vp, vp, vp]
     lib.nfb_allreduce_max_blocks.restype = i32
     lib.nfb_allreduce_max_blocks.argtypes = [i32, i64]
     lib._nfb_allreduce_declared = True
@@ -175,6 +175,9 @@ class PeerReducer:
 
         self.grid_ctr = torch.zeros(2 + _MAX_CHUNKS, dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        # NANOFED_B200_AGG_TRACE=1: the kernel records %globaltimer at its phase boundaries
+        self.dbg = (torch.zeros(8, dtype=torch.int64, device=dev)
+                    if os.environ.get("NANOFED_B200_AGG_TRACE") == "1" else None)
         self.sumsq_dummy = None
         rows = []
         for r in range(g):
@@ -247,6 +250,7 @@ class PeerReducer:
             (1 if accumulate else 0) | (2 if local_only else 0),
             arena.stats.data_ptr(), self.stats_len,
             C.byref(target) if target is not None else None,
+            self.dbg.data_ptr() if self.dbg is not None else None,
             torch.cuda.current_stream(arena.device).cuda_stream,
         )
         native._check(code, "fedavg_allreduce")
@@ -361,7 +365,7 @@ def emulate_allreduce(
                 seed & (2**64 - 1), offset, call, grid // 2, chunk, grid, None, None, None,
                 status.data_ptr(), spin_ns, flags,
                 stats.data_ptr() if stats is not None else None, stats_len,
-                C.byref(target) if (target is not None and w == waves - 1) else None,
+                C.byref(target) if (target is not None and w == waves - 1) else None, None,
                 torch.cuda.current_stream(dev).cuda_stream,
             )
             native._check(code, "fedavg_allreduce(emulated)")

@@ -111,6 +111,20 @@ for n in args.params:
         t_peer_b2b = timed_b2b(waves_of(peer), args.b2b)
         peer.check()
         err = (arena.master - ref).abs().max().item()
+        if peer.dbg is not None:       # NANOFED_B200_AGG_TRACE=1: phase timestamps of one call
+            torch.cuda.synchronize(); dist.barrier()
+            for _ in range(3):
+                peer.reduce(arena)
+            torch.cuda.synchronize()
+            t = peer.dbg.cpu().tolist()
+            rel = [round((v - t[0]) / 1e3, 1) if v else None for v in t[:7]]
+            gathered = [None] * G
+            dist.all_gather_object(gathered, rel)
+            if info.is_main:
+                print(json.dumps({"trace_us_since_kernel_start": {
+                    "fields": ["start", "local_done+flag", "peer_flags_seen", "scalars_read",
+                               "shard_done", "completion_seen", "bcast_tail_done"],
+                    "per_rank": gathered, "params": n, "path": peer.path}}), flush=True)
         is_nvls = peer.path.endswith("nvls")
         link_bytes = (4 + 6 * (G - 1)) * n / G if is_nvls else 10 * n * (G - 1) / G
         t_link = link_bytes / link
