@@ -38,7 +38,7 @@ struct RankView {
   const float* sumsq;
   // peer-visible buffers (dereferenced by every rank)
   float* partial;        // [N]
-  float* scal;           // [4]: sum n, sum n^2
+  float* scal;           // [4 + 2G]: own sum n, sum n^2; then every rank's pair (pushed with flag 1)
   unsigned* flags;       // [(1 + kMaxChunks) * G]: epoch words written by peers (slot 0 = done)
   float* master;         // [N] new global model
   __nv_bfloat16* lowp;   // [N] bf16 copy (may be null)
@@ -214,11 +214,15 @@ __global__ void __launch_bounds__(256)
   const int rank = (gridDim.y > 1) ? static_cast<int>(blockIdx.y) : my_rank;
   const RankView me = views[rank];
   const int G = a.G;
-  const int P = a.local_only ? static_cast<int>(gridDim.x) : a.producers;
-  const int Q = static_cast<int>(gridDim.x) - P;
-  const bool producer = static_cast<int>(blockIdx.x) < P;
   const int64_t chunk = a.chunk_elems;              // multiple of 8*G... see host wrapper
   const int n_chunks = a.n_chunks;
+  // Latency regime (one chunk): there is nothing to pipeline, so EVERY CTA first reduces its share
+  // of the local clients and then turns consumer - the local phase runs on the whole grid instead
+  // of the producer half (2 GPUs x 32 clients x 1.2 M: 42 -> 25 us of a 79 us kernel).
+  const bool single = n_chunks == 1 && !a.local_only;
+  const int P = (a.local_only || single) ? static_cast<int>(gridDim.x) : a.producers;
+  const int Q = single ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x) - P;
+  const bool producer = static_cast<int>(blockIdx.x) < P;
 
   if (a.dbg && blockIdx.x == 0 && threadIdx.x == 0) a.dbg[0] = now_ns();
   if (producer) {
@@ -261,12 +265,20 @@ __global__ void __launch_bounds__(256)
       __syncthreads();
       if (s_last) {
         __threadfence();
+        // the weight sums travel WITH the first flag: written into every peer's scal[4 + 2 * rank]
+        // before the release store, so consumers read them from local memory (one NVLink round
+        // trip less on the critical path)
+        if (c == 0 && threadIdx.x < G) {
+          float* dst = views[threadIdx.x].scal + 4 + 2 * rank;
+          dst[0] = me.scal[0];
+          dst[1] = me.scal[1];
+        }
         signal_peers(views, rank, G, 1 + c, a.epoch);
         if (a.dbg && threadIdx.x == 0 && c == n_chunks - 1) a.dbg[1] = now_ns();
       }
       __syncthreads();
     }
-    if (a.bc.rows > 0 && !a.local_only &&
+    if (!single && a.bc.rows > 0 && !a.local_only &&
         wait_go(me.counters + kGoSlot, a.epoch, a.spin_limit_ns, a.status)) {
       nfb_bcast_target bc = a.bc;
       if (gridDim.y > 1) {   // emulation: rank r's rows follow rank r-1's
@@ -276,11 +288,11 @@ __global__ void __launch_bounds__(256)
       }
       bcast_tail(me.master, a.N, bc, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
     }
-    return;
+    if (!single) return;
   }
 
   // ---- consumers -----------------------------------------------------------------------------
-  const int cb = static_cast<int>(blockIdx.x) - P;
+  const int cb = single ? static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x) - P;
   float s_tot = 0.f, q_tot = 0.f;
   bool have_scal = false;
   bool ok = true;
@@ -289,22 +301,13 @@ __global__ void __launch_bounds__(256)
     if (!ok) break;
     if (a.dbg && cb == 0 && threadIdx.x == 0 && c == 0) a.dbg[2] = now_ns();
     if (!have_scal) {
-      // all G pairs of peer loads go out before the first result is used: one NVLink round trip
-      // instead of G dependent ones (the loop used to add each value as it arrived)
-      float s_r[32], q_r[32];
-#pragma unroll 1
-      for (int r0 = 0; r0 < G; r0 += 8) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (r0 + i < G) {
-            const float* sc = views[r0 + i].scal;
-            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r[i]) : "l"(sc) : "memory");
-            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r[i]) : "l"(sc + 1) : "memory");
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          if (r0 + i < G) { s_tot += s_r[i]; q_tot += q_r[i]; }
+      // every rank pushed its (sum n, sum n^2) into my scal[4 + 2r] before its flag: local reads
+      for (int r = 0; r < G; ++r) {
+        float s_r, q_r;
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(s_r) : "l"(me.scal + 4 + 2 * r) : "memory");
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(q_r) : "l"(me.scal + 5 + 2 * r) : "memory");
+        s_tot += s_r;
+        q_tot += q_r;
       }
       have_scal = true;
       if (a.dbg && cb == 0 && threadIdx.x == 0) a.dbg[3] = now_ns();

@@ -74,7 +74,7 @@ class _Layout:
         self.master = _round_up(self.partial + 4 * n)
         self.lowp = _round_up(self.master + 4 * n)
         self.scal = _round_up(self.lowp + 2 * n)
-        self.flags = self.scal + _ALIGN
+        self.flags = self.scal + 2 * _ALIGN          # scal: 4 + 2g floats (g <= 32)
         self.stats = self.flags + _round_up(4 * (1 + _MAX_CHUNKS) * g)   # [g][stats_len] fp32
         self.total = self.stats + _round_up(4 * g * max(stats_len, 1))
 
