@@ -111,19 +111,50 @@ struct GemmCfg {
   static constexpr int A_TILE = 128 * 128;            // 128 positions x 64 channels bf16
   static constexpr int B_TILE = BN * 128;             // BN rows x 64 (K-major) == BN/64 atoms of 64 x 64
   static constexpr int STAGE = HALVES * A_TILE + B_TILE;
-  static constexpr int BUDGET = (HALVES * BN <= 256) ? 100 * 1024 : 200 * 1024;
-  static constexpr int STAGES = (BUDGET / STAGE) > 6 ? 6 : (BUDGET / STAGE);
-  static constexpr int STAGING = 4 * 4096;
-  static constexpr int TMEM_COLS = HALVES * BN <= 32 ? 32 : HALVES * BN <= 64 ? 64
-                                   : HALVES * BN <= 128 ? 128 : HALVES * BN <= 256 ? 256 : 512;
-  static constexpr int MINB = (HALVES * BN <= 256) ? 2 : 1;
+  // PERSISTENT kernel, one CTA per SM: the whole shared memory is pipeline.  Measured on the first
+  // (one tile per CTA, two CTAs per SM, 2 stages each) version: tensor pipe 30 %, L2 21 %, issue
+  // 12 % - a latency chain: ~180 KB must be in flight per SM to cover ~1 us of TMA latency at the
+  // MMA's consumption rate, and prologue + epilogue were 60 % of a CTA's life.
+  // one epilogue warpgroup (4 warps = the four TMEM lane quarters) per 128-row half: with a single
+  // group the epilogue of a 256 x 64 tile (2 TMEM reads, stores, statistics) took longer than its
+  // MMAs and the persistent kernel was epilogue-bound on the 64-channel layers
+  static constexpr int EPI_WARPS = 4 * HALVES;
+  static constexpr int THREADS = 128 + 32 * EPI_WARPS;
+  static constexpr int STAGING = EPI_WARPS * 4096;
+  // every byte of the 227 KB counts: the kernel is latency-bound, a fourth 48 KB stage is worth
+  // more than slack (budget = 227 KB - alignment - barriers - BatchNorm sums - staging)
+  static constexpr int BUDGET = 227 * 1024 - 1024 - 512 - 2 * BN * 4 - STAGING;
+  static constexpr int STAGES = (BUDGET / STAGE) > 8 ? 8 : (BUDGET / STAGE);
+  // two accumulator sets when they fit: the epilogue of tile i overlaps the MMAs of tile i + 1
+  static constexpr int ACC_STAGES = (2 * HALVES * BN <= 512) ? 2 : 1;
+  static constexpr int ACC_COLS = HALVES * BN;
+  static constexpr int TMEM_NEED = ACC_STAGES * ACC_COLS;
+  static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64
+                                   : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
   static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + STAGING + 2 * BN * 4 +
-                                 1024 /*align*/ + 256 /*barriers*/;
+                                 1024 /*align*/ + 512 /*barriers*/;
   static_assert(STAGES >= 2, "pipeline needs two stages");
+  static_assert(SMEM <= 227 * 1024, "shared memory budget");
 };
 
+// Tile t of a launch: t = ((cls * clients + g) * n_tiles + ntile) * m_tiles + mtile (mtile fastest, so
+// the CTAs that run concurrently share a client's weight tile in L2).
+struct TileCoord {
+  int mtile, ntile, g, cls;
+};
+__device__ __forceinline__ TileCoord tile_coord(int t, int m_tiles, int n_tiles, int clients) {
+  TileCoord c;
+  c.mtile = t % m_tiles;
+  const int r = t / m_tiles;
+  c.ntile = r % n_tiles;
+  const int z = r / n_tiles;
+  c.g = z % clients;
+  c.cls = z / clients;
+  return c;
+}
+
 template <bool B_MN, int BN, int HALVES>
-__global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
+__global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
     rn_conv_gemm_kernel(const __grid_constant__ CUtensorMap map_a0,
                         const __grid_constant__ CUtensorMap map_a1,
                         const __grid_constant__ CUtensorMap map_b0,
@@ -134,23 +165,21 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
   uint8_t* smem = reinterpret_cast<uint8_t*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* staging = smem + C::STAGES * C::STAGE;
-  float* red = reinterpret_cast<float*>(staging + C::STAGING);          // [2][BN]
+  float* red = reinterpret_cast<float*>(staging + C::STAGING);          // [2][BN] BatchNorm sums
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(red + 2 * BN);
   uint64_t* empty_bar = full_bar + C::STAGES;
-  uint64_t* acc_bar = empty_bar + C::STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+  uint64_t* acc_full = empty_bar + C::STAGES;          // [ACC_STAGES]
+  uint64_t* acc_empty = acc_full + C::ACC_STAGES;      // [ACC_STAGES]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + C::ACC_STAGES);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  // grid.z = class * clients + client: the four output parity classes of a stride-2 data gradient
-  // are one launch (each class has its own taps and its own quarter of the output pixels)
-  const int mtile = blockIdx.x, ntile = blockIdx.y;
-  const int g = blockIdx.z % args.clients, cls = blockIdx.z / args.clients;
-  const int out_ph = args.n_cls > 1 ? (cls >> 1) : args.out_ph;
-  const int out_pw = args.n_cls > 1 ? (cls & 1) : args.out_pw;
-  int n_iters = 0;
-  for (int t = 0; t < args.n_taps; ++t)
-    if (args.tap[t].cls < 0 || args.tap[t].cls == cls) n_iters += args.kc[args.tap[t].src];
+  const int m_tiles = args.P / (HALVES * 128), n_tiles = args.n_out / BN;
+  const int total_tiles = m_tiles * n_tiles * args.clients * args.n_cls;
+  // Tiles are dealt round-robin (CTA b takes b, b + grid, ...): concurrent CTAs share a client's
+  // weight tile in L2 and the parity classes of a stride-2 dgrad (1 to 5 taps per tile) interleave.
+  // Contiguous ranges were tried for the sake of register-resident BatchNorm sums: faster on the
+  // 64-channel layers, 25-55 % slower on the deep ones (class imbalance, weight locality).
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_a0);
@@ -160,51 +189,63 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(acc_bar, 1);
+    for (int s = 0; s < C::ACC_STAGES; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], C::EPI_WARPS);          // one arrival per epilogue warp
+    }
     fence_barrier_init();
   }
-  for (int i = threadIdx.x; i < 2 * BN; i += 256) red[i] = 0.f;
+  for (int i = threadIdx.x; i < 2 * BN; i += C::THREADS) red[i] = 0.f;
   if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // first 128-position box of this tile, counted over all clients
-  const int pb0 = (g * args.P + mtile * HALVES * 128) >> 7;
+  // k-iterations of one tile of class `cls`
+  auto iters_of = [&](int cls) {
+    int n = 0;
+    for (int t = 0; t < args.n_taps; ++t)
+      if (args.tap[t].cls < 0 || args.tap[t].cls == cls) n += args.kc[args.tap[t].src];
+    return n;
+  };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
-      int n0[HALVES], h0[HALVES];
-#pragma unroll
-      for (int h = 0; h < HALVES; ++h) box_origin(pb0 + h, 128, args.H, args.W, n0[h], h0[h]);
-      int i = 0;
+      int i = 0;                                       // stage counter, runs across tiles
       bool ok = true;
-      for (int t = 0; t < args.n_taps && ok; ++t) {
-        const Tap tp = args.tap[t];
-        if (tp.cls >= 0 && tp.cls != cls) continue;
-        const CUtensorMap* ma = tp.src ? &map_a1 : &map_a0;
-        const CUtensorMap* mb = tp.src ? &map_b1 : &map_b0;
-        const int kcn = args.kc[tp.src];
-        for (int kc = 0; kc < kcn; ++kc, ++i) {
-          const int s = i % C::STAGES;
-          const uint32_t ph = (i / C::STAGES) & 1;
-          if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; ok = false; break; }
-          uint8_t* stage = smem + s * C::STAGE;
-          mbar_expect_tx(&full_bar[s], C::STAGE);
+      for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x) {
+        const TileCoord tc_ = tile_coord(tile, m_tiles, n_tiles, args.clients);
+        const int pb0 = (tc_.g * args.P + tc_.mtile * HALVES * 128) >> 7;
+        int n0[HALVES], h0[HALVES];
 #pragma unroll
-          for (int h = 0; h < HALVES; ++h)
-            tma_load_5d(stage + h * C::A_TILE, ma, &full_bar[s],
-                        kc * 64 + tp.pw * args.cpar[tp.src], tp.dw, tp.ph, h0[h] + tp.dh, n0[h]);
-          uint8_t* bdst = stage + HALVES * C::A_TILE;
-          if constexpr (!B_MN) {
-            tma_load_3d(bdst, mb, &full_bar[s], kc * 64, tp.wrow + ntile * BN, g);
-          } else {
+        for (int h = 0; h < HALVES; ++h) box_origin(pb0 + h, 128, args.H, args.W, n0[h], h0[h]);
+        for (int t = 0; t < args.n_taps && ok; ++t) {
+          const Tap tp = args.tap[t];
+          if (tp.cls >= 0 && tp.cls != tc_.cls) continue;
+          const CUtensorMap* ma = tp.src ? &map_a1 : &map_a0;
+          const CUtensorMap* mb = tp.src ? &map_b1 : &map_b0;
+          const int kcn = args.kc[tp.src];
+          for (int kc = 0; kc < kcn; ++kc, ++i) {
+            const int s = i % C::STAGES;
+            const uint32_t ph = (i / C::STAGES) & 1;
+            if (!mbar_wait(&empty_bar[s], ph ^ 1)) { *args.status = 1; ok = false; break; }
+            uint8_t* stage = smem + s * C::STAGE;
+            mbar_expect_tx(&full_bar[s], C::STAGE);
 #pragma unroll
-            for (int a = 0; a < BN / 64; ++a)
-              tma_load_3d(bdst + a * 8192, mb, &full_bar[s], ntile * BN + a * 64,
-                          tp.wrow + kc * 64, g);
+            for (int h = 0; h < HALVES; ++h)
+              tma_load_5d(stage + h * C::A_TILE, ma, &full_bar[s],
+                          kc * 64 + tp.pw * args.cpar[tp.src], tp.dw, tp.ph, h0[h] + tp.dh, n0[h]);
+            uint8_t* bdst = stage + HALVES * C::A_TILE;
+            if constexpr (!B_MN) {
+              tma_load_3d(bdst, mb, &full_bar[s], kc * 64, tp.wrow + tc_.ntile * BN, tc_.g);
+            } else {
+#pragma unroll
+              for (int a = 0; a < BN / 64; ++a)
+                tma_load_3d(bdst + a * 8192, mb, &full_bar[s], tc_.ntile * BN + a * 64,
+                            tp.wrow + kc * 64, tc_.g);
+            }
           }
         }
       }
@@ -213,134 +254,168 @@ __global__ void __launch_bounds__(256, GemmCfg<B_MN, BN, HALVES>::MINB)
     // ===================== MMA issuer =====================
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0u, B_MN ? 1u : 0u);
-      for (int i = 0; i < n_iters; ++i) {
-        const int s = i % C::STAGES;
-        const uint32_t ph = (i / C::STAGES) & 1;
-        if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; break; }
+      int i = 0, local = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x, ++local) {
+        const TileCoord tc_ = tile_coord(tile, m_tiles, n_tiles, args.clients);
+        const int n_iters = iters_of(tc_.cls);
+        const int as = local % C::ACC_STAGES;
+        const uint32_t aph = (local / C::ACC_STAGES) & 1;
+        if (!mbar_wait(&acc_empty[as], aph ^ 1)) { *args.status = 1; ok = false; break; }
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + s * C::STAGE);
-        const uint32_t b_addr = a_addr + HALVES * C::A_TILE;
+        const uint32_t d_tmem = tmem_base + as * C::ACC_COLS;
+        for (int it = 0; it < n_iters; ++it, ++i) {
+          const int s = i % C::STAGES;
+          const uint32_t ph = (i / C::STAGES) & 1;
+          if (!mbar_wait(&full_bar[s], ph)) { *args.status = 1; ok = false; break; }
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + s * C::STAGE);
+          const uint32_t b_addr = a_addr + HALVES * C::A_TILE;
 #pragma unroll
-        for (int h = 0; h < HALVES; ++h) {
+          for (int h = 0; h < HALVES; ++h) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const uint64_t da = make_smem_desc(a_addr + h * C::A_TILE + kk * 32, 0, 1024, 2u);
-            const uint64_t db = B_MN ? make_smem_desc(b_addr + kk * 2048, 8192, 1024, 2u)
-                                     : make_smem_desc(b_addr + kk * 32, 0, 1024, 2u);
-            umma_f16(tmem_base + h * BN, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t da = make_smem_desc(a_addr + h * C::A_TILE + kk * 32, 0, 1024, 2u);
+              const uint64_t db = B_MN ? make_smem_desc(b_addr + kk * 2048, 8192, 1024, 2u)
+                                       : make_smem_desc(b_addr + kk * 32, 0, 1024, 2u);
+              umma_f16(d_tmem + h * BN, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+            }
           }
+          umma_commit(&empty_bar[s]);
         }
-        umma_commit(&empty_bar[s]);
+        umma_commit(&acc_full[as]);
       }
-      umma_commit(acc_bar);
     }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
-    const int sub = warp - 4;
-    bool ok = mbar_wait(acc_bar, 0);
-    if (!ok && lane == 0) *args.status = 1;
-    tc_fence_after();
-    uint8_t* my_stage = staging + sub * 4096;
-    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(sub * 32) << 16);
-    float csum[BN / 32], csq[BN / 32];   // this lane's two columns of every 64-column chunk
+    const int sub = warp & 3;                          // TMEM lane quarter of this warp
+    const int grp = (warp - 4) >> 2;                   // = the 128-row half this warpgroup owns
+    uint8_t* my_stage = staging + (warp - 4) * 4096;
+    int local = 0;
+    bool ok = true;
+    for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x, ++local) {
+      const TileCoord tc_ = tile_coord(tile, m_tiles, n_tiles, args.clients);
+      const int mtile = tc_.mtile, ntile = tc_.ntile, g = tc_.g;
+      const int out_ph = args.n_cls > 1 ? (tc_.cls >> 1) : args.out_ph;
+      const int out_pw = args.n_cls > 1 ? (tc_.cls & 1) : args.out_pw;
+      const int as = local % C::ACC_STAGES;
+      const uint32_t aph = (local / C::ACC_STAGES) & 1;
+      if (!mbar_wait(&acc_full[as], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }
+      tc_fence_after();
+      const uint32_t lane_addr =
+          tmem_base + as * C::ACC_COLS + (static_cast<uint32_t>(sub * 32) << 16);
+      float csum[BN / 32], csq[BN / 32];   // this lane's two columns of every 64-column chunk
 #pragma unroll
-    for (int j = 0; j < BN / 32; ++j) csum[j] = csq[j] = 0.f;
-#pragma unroll 1
-    for (int h = 0; h < HALVES; ++h) {
-      const int pos0 = mtile * HALVES * 128 + h * 128 + sub * 32;   // within the client
-      int n0, h0;
-      box_origin((g * args.P + pos0) >> 5, 32, args.H, args.W, n0, h0);
-      const long long row = static_cast<long long>(g) * args.P + pos0 + lane;
+      for (int j = 0; j < BN / 32; ++j) csum[j] = csq[j] = 0.f;
+      {
+        const int h = grp;
+        const int pos0 = mtile * HALVES * 128 + h * 128 + sub * 32;   // within the client
+        int n0, h0;
+        box_origin((g * args.P + pos0) >> 5, 32, args.H, args.W, n0, h0);
+        const long long row = static_cast<long long>(g) * args.P + pos0 + lane;
 #pragma unroll
-      for (int c = 0; c < BN / 64; ++c) {
-        uint32_t r[64];
+        for (int c = 0; c < BN / 64; ++c) {
+          uint32_t r[64];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) tmem_ld_32x32b_x16(lane_addr + h * BN + c * 64 + q * 16, r + q * 16);
-        tmem_ld_wait();
-        float v[64];
+          for (int q = 0; q < 4; ++q)
+            tmem_ld_32x32b_x16(lane_addr + h * BN + c * 64 + q * 16, r + q * 16);
+          tmem_ld_wait();
+          if (c == BN / 64 - 1) {
+            // the accumulator set is in registers / already consumed: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[as]);
+          }
+          float v[64];
 #pragma unroll
-        for (int j = 0; j < 64; ++j) v[j] = __uint_as_float(r[j]);
-        if (args.residual) {
-          const long long off = row * args.n_out + ntile * BN + c * 64;
+          for (int j = 0; j < 64; ++j) v[j] = __uint_as_float(r[j]);
+          if (args.residual) {
+            const long long off = row * args.n_out + ntile * BN + c * 64;
 #pragma unroll
-          for (int p = 0; p < 8; ++p) {
-            float rf[8];
-            unpack<__nv_bfloat16>(ld_plain(args.residual + off + p * 8), rf);
-            if (args.res_mask) {
-              float mf[8];
-              unpack<__nv_bfloat16>(ld_plain(args.res_mask + off + p * 8), mf);
+            for (int p = 0; p < 8; ++p) {
+              float rf[8];
+              unpack<__nv_bfloat16>(ld_plain(args.residual + off + p * 8), rf);
+              if (args.res_mask) {
+                float mf[8];
+                unpack<__nv_bfloat16>(ld_plain(args.res_mask + off + p * 8), mf);
 #pragma unroll
-              for (int e = 0; e < 8; ++e) rf[e] = mf[e] > 0.f ? rf[e] : 0.f;
+                for (int e = 0; e < 8; ++e) rf[e] = mf[e] > 0.f ? rf[e] : 0.f;
+              }
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[p * 8 + e] += rf[e];
             }
-#pragma unroll
-            for (int e = 0; e < 8; ++e) v[p * 8 + e] += rf[e];
           }
-        }
-        if (args.out_mask) {
-          long long moff;
-          if (!args.out_is_parity) {
-            moff = row * args.n_out;
-          } else {   // this row is pixel (2*hh + ph, 2*wh + pw) of the full-resolution output
-            const int hw = args.H * args.W;
-            const int n = static_cast<int>(row / hw), rem = static_cast<int>(row - static_cast<long long>(n) * hw);
-            const int hh = rem / args.W, wh = rem - hh * args.W;
-            moff = ((static_cast<long long>(n) * 2 * args.H + 2 * hh + out_ph) * (2 * args.W) +
-                    2 * wh + out_pw) * args.out_c;
+          if (args.out_mask) {
+            long long moff;
+            if (!args.out_is_parity) {
+              moff = row * args.n_out;
+            } else {   // this row is pixel (2*hh + ph, 2*wh + pw) of the full-resolution output
+              const int hw = args.H * args.W;
+              const int n = static_cast<int>(row / hw), rem = static_cast<int>(row - static_cast<long long>(n) * hw);
+              const int hh = rem / args.W, wh = rem - hh * args.W;
+              moff = ((static_cast<long long>(n) * 2 * args.H + 2 * hh + out_ph) * (2 * args.W) +
+                      2 * wh + out_pw) * args.out_c;
+            }
+            moff += ntile * BN + c * 64;
+#pragma unroll
+            for (int p = 0; p < 8; ++p) {
+              float mf[8];
+              unpack<__nv_bfloat16>(ld_plain(args.out_mask + moff + p * 8), mf);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[p * 8 + e] = mf[e] > 0.f ? v[p * 8 + e] : 0.f;
+            }
           }
-          moff += ntile * BN + c * 64;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          __syncwarp();
 #pragma unroll
-          for (int p = 0; p < 8; ++p) {
-            float mf[8];
-            unpack<__nv_bfloat16>(ld_plain(args.out_mask + moff + p * 8), mf);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) v[p * 8 + e] = mf[e] > 0.f ? v[p * 8 + e] : 0.f;
+          for (int p = 0; p < 8; ++p)
+            st_vec(my_stage + lane * 128 + ((p ^ (lane & 7)) * 16), pack<__nv_bfloat16>(v + 8 * p));
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_5d(&map_o, my_stage, ntile * BN + c * 64 + out_pw * args.out_c, 0, out_ph, h0,
+                         n0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
-        }
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-        __syncwarp();
-#pragma unroll
-        for (int p = 0; p < 8; ++p)
-          st_vec(my_stage + lane * 128 + ((p ^ (lane & 7)) * 16), pack<__nv_bfloat16>(v + 8 * p));
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0 && ok) {
-          tma_store_5d(&map_o, my_stage, ntile * BN + c * 64 + out_pw * args.out_c, 0, out_ph, h0,
-                       n0);
-          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        }
-        if (args.stats) {
-          // column sums of the ROUNDED values (what the normalisation pass will read): lane l
-          // owns columns 2l, 2l+1 of the chunk; row r's piece p sits at (p ^ (r & 7)) * 16
-          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+          if (args.stats) {
+            // column sums of the ROUNDED values (what the normalisation pass will read): lane l
+            // owns columns 2l, 2l+1 of the chunk; row r's piece p sits at (p ^ (r & 7)) * 16
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
-          for (int rr = 0; rr < 32; ++rr) {
-            const uint32_t w = *reinterpret_cast<const uint32_t*>(
-                my_stage + rr * 128 + (((lane >> 2) ^ (rr & 7)) * 16) + (lane & 3) * 4);
-            const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
-            s0 += a; s1 += b;
-            q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
+            for (int rr = 0; rr < 32; ++rr) {
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(
+                  my_stage + rr * 128 + (((lane >> 2) ^ (rr & 7)) * 16) + (lane & 3) * 4);
+              const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
+              s0 += a; s1 += b;
+              q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
+            }
+            csum[2 * c] += s0; csum[2 * c + 1] += s1;
+            csq[2 * c] += q0; csq[2 * c + 1] += q1;
           }
-          csum[2 * c] += s0; csum[2 * c + 1] += s1;
-          csq[2 * c] += q0; csq[2 * c + 1] += q1;
         }
+      }
+      if (args.stats) {
+        // the tile's sums: all epilogue warps add into shared memory, then ONE fp32 atomic per
+        // channel and sum leaves the CTA (a warp-level flush put 8x as many atomics onto the few
+        // hundred addresses of a 64-channel layer and halved its speed)
+#pragma unroll
+        for (int c = 0; c < BN / 64; ++c) {
+          atomicAdd(&red[c * 64 + 2 * lane], csum[2 * c]);
+          atomicAdd(&red[c * 64 + 2 * lane + 1], csum[2 * c + 1]);
+          atomicAdd(&red[BN + c * 64 + 2 * lane], csq[2 * c]);
+          atomicAdd(&red[BN + c * 64 + 2 * lane + 1], csq[2 * c + 1]);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * C::EPI_WARPS) : "memory");
+        float* dst = args.stats + static_cast<long long>(g) * 2 * args.n_out;
+        for (int i = threadIdx.x - 128; i < 2 * BN; i += 32 * C::EPI_WARPS) {
+          const int which = i / BN, col = i - which * BN;
+          atomicAdd(dst + which * args.n_out + ntile * BN + col, red[i]);
+          red[i] = 0.f;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * C::EPI_WARPS) : "memory");
       }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-    if (args.stats) {
-#pragma unroll
-      for (int c = 0; c < BN / 64; ++c) {
-        atomicAdd(&red[c * 64 + 2 * lane], csum[2 * c]);
-        atomicAdd(&red[c * 64 + 2 * lane + 1], csum[2 * c + 1]);
-        atomicAdd(&red[BN + c * 64 + 2 * lane], csq[2 * c]);
-        atomicAdd(&red[BN + c * 64 + 2 * lane + 1], csq[2 * c + 1]);
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      float* dst = args.stats + static_cast<long long>(g) * 2 * args.n_out;
-      for (int i = threadIdx.x - 128; i < 2 * BN; i += 128) {
-        const int which = i / BN, col = i - which * BN;
-        atomicAdd(dst + which * args.n_out + ntile * BN + col, red[i]);
-      }
-    }
   }
 
   tc_fence_before();
@@ -602,7 +677,7 @@ static int launch_gemm(const CUtensorMap* maps, const GemmArgs& args, dim3 grid,
                                       cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<grid, 256, C::SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], maps[4], args);
+  kern<<<grid, C::THREADS, C::SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], maps[4], args);
   return launch_status("rn_conv_gemm");
 }
 
@@ -687,7 +762,9 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
   // k-chunks: forward K = input channels = weight inner; dgrad K = output channels of the conv
   g.cpar[0] = a0->C; g.cpar[1] = use1 ? a1->C : 0;
   g.kc[0] = a0->C / 64; g.kc[1] = use1 ? a1->C / 64 : 0;
-  dim3 grid(P / (128 * halves), n_out / bn_tile, clients * n_cls);
+  const long long tiles = static_cast<long long>(P / (128 * halves)) * (n_out / bn_tile) * clients * n_cls;
+  const long long sms = sm_count();
+  dim3 grid(static_cast<unsigned>(tiles < sms ? tiles : sms));
   cudaStream_t st = as_stream(stream);
 #define NFB_RN_CASE(MN, BNV, HV)                                                     \
   if ((dgrad != 0) == MN && bn_tile == BNV && halves == HV)                          \

@@ -153,26 +153,16 @@ class WeightRef:
 
 
 def pick_tile(positions_per_client: int, n_out: int, clients: int, sms: int = 148) -> tuple[int, int]:
-    """(bn_tile, halves): the largest tile that still gives every SM a CTA.
+    """(bn_tile, halves) of the persistent conv kernel.
 
-    Measured on B200 (``profiles/rn_tile_sweep.log``): the 256 x 256 tile reaches 52-56 % of the
-    sustained bf16 peak where smaller tiles stay at 38-40 % (operand traffic from L2 per FLOP
-    halves), so it is taken as soon as it fills 80 % of the SMs."""
-    if (n_out % 256 == 0 and positions_per_client % 256 == 0
-            and positions_per_client // 256 * (n_out // 256) * clients >= 0.8 * sms):
-        return (256, 2)
-    best, best_key = (64, 1), None
-    for halves in (2, 1):
-        if positions_per_client % (128 * halves):
-            continue
-        for bn in (256, 128, 64):
-            if n_out % bn:
-                continue
-            ctas = positions_per_client // (128 * halves) * (n_out // bn) * clients
-            key = (min(ctas, sms), halves * bn)   # fill the GPU first, then prefer the larger tile
-            if best_key is None or key > best_key:
-                best, best_key = (bn, halves), key
-    return best
+    Measured on B200 (``profiles/rn_tile_sweep_persistent.log``): 128 output channels x 256 positions
+    is the best or within 5 % of the best tile for every ResNet-18 layer - it keeps two accumulator
+    sets in TMEM (the epilogue of a tile overlaps the MMAs of the next) and three 48 KB stages in
+    flight; the 256 x 256 tile, best for the one-tile-per-CTA kernel of the first version, has a
+    single accumulator set and two stages here and is 20-50 % slower."""
+    halves = 2 if positions_per_client % 256 == 0 else 1
+    bn = 128 if n_out % 128 == 0 else 64
+    return (bn, halves)
 
 
 def conv_gemm(
