@@ -103,6 +103,10 @@ struct GemmArgs {
   // not positive, so the BatchNorm backward kernels downstream need no mask operand
   const __nv_bfloat16* out_mask;
   int out_is_parity;
+  // BatchNorm backward sums fused into a data gradient: with bn_x (the raw conv output that the
+  // BatchNorm under the masked activation normalises; dense, shape of the output) `stats` receives
+  // per channel sum(g) and sum(g * x) of the stored gradient g instead of sum / sum of squares
+  const __nv_bfloat16* bn_x;
   int* status;
 };
 
@@ -121,9 +125,14 @@ struct GemmCfg {
   static constexpr int EPI_WARPS = 4 * HALVES;
   static constexpr int THREADS = 128 + 32 * EPI_WARPS;
   static constexpr int STAGING = EPI_WARPS * 4096;
+  // data gradients only: a second 4 KB tile per epilogue warp, TMA-loaded with the BatchNorm input
+  // x of the chunk while the accumulator is read (sum(g * x) for the BatchNorm backward).  Plain
+  // loads of x after the store exposed their latency once per chunk and cost more than the
+  // separate reduction pass they replaced.
+  static constexpr int XSTAGING = B_MN ? EPI_WARPS * 4096 : 0;
   // every byte of the 227 KB counts: the kernel is latency-bound, a fourth 48 KB stage is worth
   // more than slack (budget = 227 KB - alignment - barriers - BatchNorm sums - staging)
-  static constexpr int BUDGET = 227 * 1024 - 1024 - 512 - 2 * BN * 4 - STAGING;
+  static constexpr int BUDGET = 227 * 1024 - 1024 - 512 - 2 * BN * 4 - STAGING - XSTAGING;
   static constexpr int STAGES = (BUDGET / STAGE) > 8 ? 8 : (BUDGET / STAGE);
   // two accumulator sets when they fit: the epilogue of tile i overlaps the MMAs of tile i + 1
   static constexpr int ACC_STAGES = (2 * HALVES * BN <= 512) ? 2 : 1;
@@ -131,8 +140,8 @@ struct GemmCfg {
   static constexpr int TMEM_NEED = ACC_STAGES * ACC_COLS;
   static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64
                                    : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
-  static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + STAGING + 2 * BN * 4 +
-                                 1024 /*align*/ + 512 /*barriers*/;
+  static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + STAGING + XSTAGING +
+                                 2 * BN * 4 + 1024 /*align*/ + 512 /*barriers*/;
   static_assert(STAGES >= 2, "pipeline needs two stages");
   static_assert(SMEM <= 227 * 1024, "shared memory budget");
 };
@@ -159,18 +168,21 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
                         const __grid_constant__ CUtensorMap map_a1,
                         const __grid_constant__ CUtensorMap map_b0,
                         const __grid_constant__ CUtensorMap map_b1,
-                        const __grid_constant__ CUtensorMap map_o, const GemmArgs args) {
+                        const __grid_constant__ CUtensorMap map_o,
+                        const __grid_constant__ CUtensorMap map_x, const GemmArgs args) {
   using C = GemmCfg<B_MN, BN, HALVES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* staging = smem + C::STAGES * C::STAGE;
-  float* red = reinterpret_cast<float*>(staging + C::STAGING);          // [2][BN] BatchNorm sums
+  uint8_t* xstaging = staging + C::STAGING;
+  float* red = reinterpret_cast<float*>(xstaging + C::XSTAGING);        // [2][BN] BatchNorm sums
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(red + 2 * BN);
   uint64_t* empty_bar = full_bar + C::STAGES;
   uint64_t* acc_full = empty_bar + C::STAGES;          // [ACC_STAGES]
   uint64_t* acc_empty = acc_full + C::ACC_STAGES;      // [ACC_STAGES]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + C::ACC_STAGES);
+  uint64_t* x_bar = acc_empty + C::ACC_STAGES;         // [EPI_WARPS]: x tile of a warp has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_bar + C::EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -193,6 +205,7 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
       mbar_init(&acc_full[s], 1);
       mbar_init(&acc_empty[s], C::EPI_WARPS);          // one arrival per epilogue warp
     }
+    for (int s = 0; s < C::EPI_WARPS; ++s) mbar_init(&x_bar[s], 1);
     fence_barrier_init();
   }
   for (int i = threadIdx.x; i < 2 * BN; i += C::THREADS) red[i] = 0.f;
@@ -291,6 +304,9 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
     const int sub = warp & 3;                          // TMEM lane quarter of this warp
     const int grp = (warp - 4) >> 2;                   // = the 128-row half this warpgroup owns
     uint8_t* my_stage = staging + (warp - 4) * 4096;
+    uint8_t* my_x = xstaging + (C::XSTAGING ? (warp - 4) * 4096 : 0);
+    const bool bn_bwd = B_MN && args.stats && args.bn_x;
+    uint32_t x_phase = 0;
     int local = 0;
     bool ok = true;
     for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x, ++local) {
@@ -315,6 +331,14 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
         const long long row = static_cast<long long>(g) * args.P + pos0 + lane;
 #pragma unroll
         for (int c = 0; c < BN / 64; ++c) {
+          if (bn_bwd) {
+            __syncwarp();          // every lane is done with the previous x tile
+            if (lane == 0) {
+              mbar_expect_tx(&x_bar[warp - 4], 4096);
+              tma_load_5d(my_x, &map_x, &x_bar[warp - 4],
+                          ntile * BN + c * 64 + out_pw * args.out_c, 0, out_ph, h0, n0);
+            }
+          }
           uint32_t r[64];
 #pragma unroll
           for (int q = 0; q < 4; ++q)
@@ -378,16 +402,32 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
           if (args.stats) {
-            // column sums of the ROUNDED values (what the normalisation pass will read): lane l
-            // owns columns 2l, 2l+1 of the chunk; row r's piece p sits at (p ^ (r & 7)) * 16
+            // column sums over the ROUNDED values in the staged tile: lane l owns columns 2l, 2l+1
+            // of the chunk; row r's piece p sits at (p ^ (r & 7)) * 16.
+            //   forward:        sum(y), sum(y * y)      (what the normalisation pass will read)
+            //   with bn_x:      sum(g), sum(g * x)      (BatchNorm backward of the layer whose raw
+            //                   output x produced this gradient's mask)
+            if (bn_bwd) {
+              if (!mbar_wait(&x_bar[warp - 4], x_phase)) {
+                if (lane == 0) *args.status = 1;
+                ok = false;
+              }
+              x_phase ^= 1;
+            }
             float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
             for (int rr = 0; rr < 32; ++rr) {
               const uint32_t w = *reinterpret_cast<const uint32_t*>(
                   my_stage + rr * 128 + (((lane >> 2) ^ (rr & 7)) * 16) + (lane & 3) * 4);
               const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
+              float xa = a, xb = b;
+              if (bn_bwd) {   // the x tile has the layout of the staged tile (same box, same swizzle)
+                const uint32_t xw = *reinterpret_cast<const uint32_t*>(
+                    my_x + rr * 128 + (((lane >> 2) ^ (rr & 7)) * 16) + (lane & 3) * 4);
+                xa = __uint_as_float(xw << 16); xb = __uint_as_float(xw & 0xffff0000u);
+              }
               s0 += a; s1 += b;
-              q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
+              q0 = fmaf(a, xa, q0); q1 = fmaf(b, xb, q1);
             }
             csum[2 * c] += s0; csum[2 * c + 1] += s1;
             csq[2 * c] += q0; csq[2 * c + 1] += q1;
@@ -677,7 +717,8 @@ static int launch_gemm(const CUtensorMap* maps, const GemmArgs& args, dim3 grid,
                                       cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<grid, C::THREADS, C::SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], maps[4], args);
+  kern<<<grid, C::THREADS, C::SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], maps[4], maps[5],
+                                          args);
   return launch_status("rn_conv_gemm");
 }
 
@@ -707,8 +748,9 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
                      const void* w1, const int* w_dims /* [2][3]: inner, rows, group stride */,
                      int clients, int imgs_per_client, int H, int W, int n_out, int n_taps,
                      const int* taps, const nfb_rn_act* out, int out_ph, int out_pw, float* stats,
-                     const void* residual, const void* res_mask, const void* out_mask, int bn_tile,
-                     int halves, int n_cls, int* status, void* stream) {
+                     const void* residual, const void* res_mask, const void* out_mask,
+                     const void* bn_x, int bn_tile, int halves, int n_cls, int* status,
+                     void* stream) {
   using namespace nfb;
   using namespace nfb::rn;
   NFB_REQUIRE(a0 && w0 && w_dims && taps && out && status, NFB_EINVAL, "rn_conv_gemm: null pointer");
@@ -730,6 +772,10 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
   g.residual = static_cast<const __nv_bfloat16*>(residual);
   g.res_mask = static_cast<const __nv_bfloat16*>(res_mask);
   g.out_mask = static_cast<const __nv_bfloat16*>(out_mask);
+  g.bn_x = static_cast<const __nv_bfloat16*>(bn_x);
+  NFB_REQUIRE(!bn_x || (dgrad && stats && out->C == n_out), NFB_EINVAL,
+              "rn_conv_gemm: BatchNorm-backward sums need a data gradient, a stats buffer and a "
+              "full-width output");
   g.out_is_parity = out->parity ? 1 : 0;
   NFB_REQUIRE(!out_mask || out->C == n_out, NFB_EINVAL, "rn_conv_gemm: output mask needs a full-width output");
   g.status = status;
@@ -745,7 +791,7 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
     use1 |= g.tap[t].src == 1;
   }
   NFB_REQUIRE(!use1 || (a1 && w1), NFB_EINVAL, "rn_conv_gemm: second operand pair missing");
-  CUtensorMap maps[5];
+  CUtensorMap maps[6];
   int rc = act_map(a0, 128, &maps[0]);
   if (rc) return rc;
   maps[1] = maps[0];
@@ -759,6 +805,12 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
     return rc;
   rc = act_map(out, 32, &maps[4]);
   if (rc) return rc;
+  maps[5] = maps[4];
+  if (bn_x) {   // same geometry as the output: the epilogue loads the tile it is about to store
+    nfb_rn_act xa = *out;
+    xa.ptr = bn_x;
+    if ((rc = act_map(&xa, 32, &maps[5]))) return rc;
+  }
   // k-chunks: forward K = input channels = weight inner; dgrad K = output channels of the conv
   g.cpar[0] = a0->C; g.cpar[1] = use1 ? a1->C : 0;
   g.kc[0] = a0->C / 64; g.kc[1] = use1 ? a1->C / 64 : 0;

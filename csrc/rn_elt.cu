@@ -166,6 +166,10 @@ struct BnBwdArgs {
   BnRef bn, bn2;
   int P, C;
   float eps;
+  // apply pass without a reduce pass: the dgrad kernel that produced dout left sum(g), sum(g * x)
+  // per channel here ([clients][2][C]); dgamma = rstd * (sum gx - mean * sum g), dbeta = sum g are
+  // derived on the fly and written to the gradient row by the first block
+  const float* raw_sums;
 };
 
 // g = dout where the activated output is positive (bf16 > 0  <=>  sign clear and magnitude != 0)
@@ -270,8 +274,20 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
     float mean, rstd;
     bn_coeffs(a.bn, row, g, C, c, inv_n, a.eps, mean, rstd);
     const float s = row[a.bn.gamma + c] * rstd;
-    const float t = s * grow[a.dgamma + c] * inv_n * rstd;
-    ka[e] = s; kb[e] = -t; kc[e] = t * mean - s * grow[a.dbeta + c] * inv_n;
+    float dgamma, dbeta;
+    if (a.raw_sums) {
+      dbeta = a.raw_sums[(static_cast<long long>(g) * 2) * C + c];
+      dgamma = rstd * (a.raw_sums[(static_cast<long long>(g) * 2 + 1) * C + c] - mean * dbeta);
+      if (blockIdx.x == 0 && r == 0) {
+        a.sgrad[g * a.sgrad_stride + a.dgamma + c] = dgamma;
+        a.sgrad[g * a.sgrad_stride + a.dbeta + c] = dbeta;
+      }
+    } else {
+      dgamma = grow[a.dgamma + c];
+      dbeta = grow[a.dbeta + c];
+    }
+    const float t = s * dgamma * inv_n * rstd;
+    ka[e] = s; kb[e] = -t; kc[e] = t * mean - s * dbeta * inv_n;
     ka2[e] = kb2[e] = kc2[e] = 0.f;
     if constexpr (TWO) {
       bn_coeffs(a.bn2, row, g, C, c, inv_n, a.eps, mean, rstd);
@@ -562,7 +578,8 @@ int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, c
                   void* dx, void* dx2, const float* slots, long long row_stride, float* sgrad,
                   long long sgrad_stride, const long long* grad_offs /* dgamma dbeta dgamma2 dbeta2 */,
                   const float* stats, const long long* bn_offs, const float* stats2,
-                  const long long* bn2_offs, int clients, int P, int C, float eps, void* stream) {
+                  const long long* bn2_offs, int clients, int P, int C, float eps,
+                  const float* raw_sums, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(dout && x && slots && sgrad && grad_offs && stats && bn_offs, NFB_EINVAL,
               "rn_bn_bwd: null pointer");
@@ -581,6 +598,9 @@ int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, c
   a.bn = bn_ref(stats, bn_offs);
   if (x2) a.bn2 = bn_ref(stats2, bn2_offs);
   a.P = P; a.C = C; a.eps = eps;
+  NFB_REQUIRE(!raw_sums || (apply && !x2), NFB_EINVAL,
+              "rn_bn_bwd: raw sums replace the reduce pass of a single-branch apply");
+  a.raw_sums = raw_sums;
   cudaStream_t st = as_stream(stream);
   if (!apply) {
     // fewer, longer blocks: every block ends with C atomics per sum

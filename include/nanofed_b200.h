@@ -371,13 +371,15 @@ typedef struct {
  * client the per-channel sum and sum of squares of the stored bf16 values ([clients][2][n_out],
  * fp32 atomics); residual (+ optional ReLU mask) is added before the store; out_mask (dense
  * tensor of the output's shape) zeroes the stored value where it is not positive (the ReLU
- * backward of the layer the gradient flows into).                                             */
+ * backward of the layer the gradient flows into).  bn_x (dgrad, with stats): the raw conv output
+ * under that activation's BatchNorm - stats then receives sum(g) and sum(g * x) of the stored
+ * gradient (the reduction pass of the BatchNorm backward, folded into this epilogue).          */
 int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, const void* w0,
                      const void* w1, const int* w_dims, int clients, int imgs_per_client, int H,
                      int W, int n_out, int n_taps, const int* taps, const nfb_rn_act* out,
                      int out_ph, int out_pw, float* stats, const void* residual,
-                     const void* res_mask, const void* out_mask, int bn_tile, int halves,
-                     int n_cls, int* status, void* stream);
+                     const void* res_mask, const void* out_mask, const void* bn_x, int bn_tile,
+                     int halves, int n_cls, int* status, void* stream);
 /* out[client][tap][co][ci] (+)= sum_pos x[pos + tap][ci] * dy[pos][co]; k_split > 1 adds with fp32
  * atomics (the target must then be zero).  With k_split == 1 and sgd_w != NULL the gradient is not
  * written at all: the epilogue applies w -= lr * (dW + wd * w) to the tap-major fp32 master sgd_w
@@ -393,12 +395,14 @@ int nfb_rn_bn_apply(const void* x, const void* res, void* y, float* slots, long 
                     const float* stats, const long long* bn_offs, const float* res_stats,
                     const long long* res_offs, int clients, int P, int C, int relu, float eps,
                     float momentum, void* stream);
-/* apply = 0: accumulate dgamma / dbeta (fp32 atomics into sgrad rows); apply = 1: write dx (dx2). */
+/* apply = 0: accumulate dgamma / dbeta (fp32 atomics into sgrad rows); apply = 1: write dx (dx2).
+ * raw_sums (apply only): [clients][2][C] sum(g), sum(g * x) left by the dgrad kernel that produced
+ * dout - no reduce pass is needed then, dgamma / dbeta are derived and stored by this launch.    */
 int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, const void* x2,
                   void* dx, void* dx2, const float* slots, long long row_stride, float* sgrad,
                   long long sgrad_stride, const long long* grad_offs, const float* stats,
                   const long long* bn_offs, const float* stats2, const long long* bn2_offs,
-                  int clients, int P, int C, float eps, void* stream);
+                  int clients, int P, int C, float eps, const float* raw_sums, void* stream);
 int nfb_rn_head(const void* feat, int clients, int batch, int positions, const int64_t* labels,
                 long long label_gs, const float* slots, long long row_stride, long long w_off,
                 long long b_off, float* sgrad, long long sgrad_stride, long long dw_off,

@@ -148,7 +148,10 @@ class ResNetCohortNet:
         self.dwt = torch.zeros(g, self.t_stride, **f32)     # tap-major fp32 gradients (split-K layers)
         self.mom = torch.zeros(g, self.t_stride, **f32) if cfg.momentum != 0.0 else None
         self.sgrad = torch.zeros(g, g_cursor, **f32)        # BatchNorm / classifier gradients
-        self.stats = torch.zeros(s_cursor, **f32)           # BatchNorm batch sums
+        # BatchNorm batch sums: [0, s_cursor) forward (sum x, sum x^2), [s_cursor, 2 s_cursor)
+        # backward (sum g, sum g x) left by the dgrad epilogues; zeroed together after every step
+        self.stats = torch.zeros(2 * s_cursor, **f32)
+        self._s_half = s_cursor
         cols, rows = 0, []
         for c in self.convs:
             rows.append(struct.pack("<qqqiiii", c.w_off, c.t_off, cols, c.cout, c.cin, c.taps,
@@ -180,6 +183,8 @@ class ResNetCohortNet:
                   if not (self.fuse_sgd and self._ksplit[c.name] == 1)]
         self.tap_ranges = torch.tensor(ranges or [(0, 0)], dtype=torch.int64, device=dev)
         self.tap_max = max((r[1] for r in ranges), default=0)
+        # BatchNorm backward sums from the dgrad epilogue instead of a reduction pass
+        self.fuse_bn_sums = os.environ.get("NFB_RN_NO_FUSED_BN_SUMS") is None
         self._tile_override = os.environ.get("NFB_RN_TILE")   # "bn,halves" for experiments
         self._wgrad_posk = int(os.environ.get("NFB_RN_WGRAD_K", "0"))   # 0 = per-layer choice
 
@@ -193,6 +198,10 @@ class ResNetCohortNet:
 
     def _bn_stats(self, n: _Bn) -> torch.Tensor:
         return self.stats[n.s_off : n.s_off + self.g * 2 * n.c].view(self.g, 2, n.c)
+
+    def _bn_bsum(self, n: _Bn) -> torch.Tensor:
+        lo = self._s_half + n.s_off
+        return self.stats[lo : lo + self.g * 2 * n.c].view(self.g, 2, n.c)
 
     def _tile(self, positions: int, n_out: int) -> tuple[int, int]:
         if self._tile_override:
@@ -234,14 +243,18 @@ class ResNetCohortNet:
                       k_split=k_split, tile=(min(c.cout, 256), self._posk(c)), sgd=sgd)
 
     def _dgrad(self, c: _Conv, dy: torch.Tensor, dx: torch.Tensor, *, relu_of: torch.Tensor,
-               residual=None, sc: _Conv | None = None, dy_sc: torch.Tensor | None = None) -> None:
+               residual=None, sc: _Conv | None = None, dy_sc: torch.Tensor | None = None,
+               bn: "tuple[_Bn, torch.Tensor] | None" = None) -> None:
         """Gradient w.r.t. the PRE-ReLU value of the conv's input: ``relu_of`` is that (activated)
         input, its ReLU mask is applied in the epilogue; ``residual`` (an already masked gradient
-        arriving over an identity shortcut) is added before the mask."""
+        arriving over an identity shortcut) is added before the mask.  ``bn = (layer, raw)``: the
+        input is ``relu(bn(raw) [+ shortcut])`` - the epilogue also leaves that BatchNorm's backward
+        sums (sum g, sum g * raw) in ``_bn_bsum(layer)``, so no reduction pass over dx is needed."""
+        kw = dict(stats=self._bn_bsum(bn[0]), bn_x=bn[1]) if bn is not None else {}
         if c.stride == 1:
             rn.conv_gemm(True, dy, self._wref(c), dx, clients=self.g, grid_hw=(c.hin, c.hin),
                          taps=rn.dgrad_taps(c.k, 1, c.cout), residual=residual, out_mask=relu_of,
-                         n_out=c.cin, tile=self._tile(self.b * c.hin * c.hin, c.cin))
+                         n_out=c.cin, tile=self._tile(self.b * c.hin * c.hin, c.cin), **kw)
             return
         assert residual is None
         # the four output parity classes in ONE launch (grid.z = class x client); the 1x1 projection
@@ -250,7 +263,7 @@ class ResNetCohortNet:
                      taps=rn.dgrad_taps_all_classes(c.k, c.cout, sc.cout if sc is not None else None),
                      out_parity=(0, 0), all_classes=True, a1=dy_sc, w1=self._wref(sc) if sc else None,
                      out_mask=relu_of, n_out=c.cin,
-                     tile=self._tile(self.b * c.hout * c.hout, c.cin))
+                     tile=self._tile(self.b * c.hout * c.hout, c.cin), **kw)
 
     # ---- hooks used by FedSimulation ---------------------------------------------------------
     def after_broadcast(self) -> None:
@@ -300,7 +313,10 @@ class ResNetCohortNet:
         rn.head(cur, y, slots, self.fc_w, self.fc_b, self.sgrad, self.fc_gw, self.fc_gb, dout,
                 a.stats, clients=g)
         # ---------------- backward ----------------
-        for blk in reversed(self.blocks):
+        fuse = self.fuse_bn_sums
+        have_sums = False          # did dout's producer leave this block's bn2 backward sums?
+        for bi in range(len(self.blocks) - 1, -1, -1):
+            blk = self.blocks[bi]
             u = blk.bufs
             ho, w, hin, cin = blk.conv1.hout, blk.conv1.cout, blk.conv1.hin, blk.conv1.cin
             dout = self._view(d0, ho, w)
@@ -314,34 +330,52 @@ class ResNetCohortNet:
                       bn2_offs=blk.bn_sc.offs if proj else None)
             # dout is already the gradient w.r.t. the pre-ReLU block output (its producer - the
             # head or the next block's dgrad epilogue - applied the mask): no mask operand here
-            rn.bn_bwd(False, dout, None, u["raw2"], slots, self.sgrad, offs,
-                      self._bn_stats(blk.bn2), blk.bn2.offs, **kw)
+            if not have_sums:
+                rn.bn_bwd(False, dout, None, u["raw2"], slots, self.sgrad, offs,
+                          self._bn_stats(blk.bn2), blk.bn2.offs, **kw)
             rn.bn_bwd(True, dout, None, u["raw2"], slots, self.sgrad, offs,
-                      self._bn_stats(blk.bn2), blk.bn2.offs, dx=dc2, dx2=dcs, **kw)
+                      self._bn_stats(blk.bn2), blk.bn2.offs, dx=dc2, dx2=dcs,
+                      raw_sums=self._bn_bsum(blk.bn2) if have_sums else None, **kw)
             da = self._view(4, ho, w)
-            self._dgrad(blk.conv2, dc2, da, relu_of=u["a"])   # reads the old weights: before the wgrad
+            # reads the old weights: before the wgrad
+            self._dgrad(blk.conv2, dc2, da, relu_of=u["a"],
+                        bn=(blk.bn1, u["raw1"]) if fuse else None)
             self._wgrad(blk.conv2, u["a"], dc2)
             dc1 = dc2                                     # dc2 is dead after the two launches above
             offs1 = (blk.bn1.g_off[0], blk.bn1.g_off[1], 0, 0)
-            rn.bn_bwd(False, da, None, u["raw1"], slots, self.sgrad, offs1,
-                      self._bn_stats(blk.bn1), blk.bn1.offs, clients=g)
+            if not fuse:
+                rn.bn_bwd(False, da, None, u["raw1"], slots, self.sgrad, offs1,
+                          self._bn_stats(blk.bn1), blk.bn1.offs, clients=g)
             rn.bn_bwd(True, da, None, u["raw1"], slots, self.sgrad, offs1,
-                      self._bn_stats(blk.bn1), blk.bn1.offs, clients=g, dx=dc1)
+                      self._bn_stats(blk.bn1), blk.bn1.offs, clients=g, dx=dc1,
+                      raw_sums=self._bn_bsum(blk.bn1) if fuse else None)
             dx = self._view(d1, hin, cin)
+            # dx is the gradient at the producer of this block's input: the stem BatchNorm or the
+            # previous block's bn2 (+ shortcut).  A projection block there needs sum(g * x) for two
+            # layers - it keeps its own reduction pass.
+            prev = self.blocks[bi - 1] if bi else None
+            nxt = None
+            if fuse and prev is None:
+                nxt = (self.stem_bn, self.raw0)
+            elif fuse and prev.conv_sc is None:
+                nxt = (prev.bn2, prev.bufs["raw2"])
             if proj:
-                self._dgrad(blk.conv1, dc1, dx, relu_of=u["in"], sc=blk.conv_sc, dy_sc=dcs)
+                self._dgrad(blk.conv1, dc1, dx, relu_of=u["in"], sc=blk.conv_sc, dy_sc=dcs, bn=nxt)
                 self._wgrad(blk.conv_sc, u["in"], dcs)
             else:
-                self._dgrad(blk.conv1, dc1, dx, relu_of=u["in"], residual=dout)
+                self._dgrad(blk.conv1, dc1, dx, relu_of=u["in"], residual=dout, bn=nxt)
             self._wgrad(blk.conv1, u["in"], dc1)
+            have_sums = nxt is not None
             d0, d1 = d1, d0
         dout = self._view(d0, 32, 64)
         dc0 = self._view(2, 32, 64)
         offs0 = (self.stem_bn.g_off[0], self.stem_bn.g_off[1], 0, 0)
-        rn.bn_bwd(False, dout, None, self.raw0, slots, self.sgrad, offs0,
-                  self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g)
+        if not have_sums:
+            rn.bn_bwd(False, dout, None, self.raw0, slots, self.sgrad, offs0,
+                      self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g)
         rn.bn_bwd(True, dout, None, self.raw0, slots, self.sgrad, offs0,
-                  self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g, dx=dc0)
+                  self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g, dx=dc0,
+                  raw_sums=self._bn_bsum(self.stem_bn) if have_sums else None)
         self._wgrad(self.stem, self.xcol, dc0)
         # ---------------- update ----------------
         if self.tap_max:

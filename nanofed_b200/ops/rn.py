@@ -36,13 +36,13 @@ def _lib() -> C.CDLL:
         pa, pi, pll = C.POINTER(_Act), C.POINTER(C.c_int), C.POINTER(C.c_longlong)
         sigs = {
             "nfb_rn_conv_gemm": [i32, pa, pa, vp, vp, pi, i32, i32, i32, i32, i32, i32, pi, pa, i32,
-                                 i32, vp, vp, vp, vp, i32, i32, i32, vp, vp],
+                                 i32, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp],
             "nfb_rn_conv_wgrad": [pa, pa, i32, i32, i32, pi, vp, ll, i32, i32, i32, vp, vp, f32, f32,
                                   vp, vp],
             "nfb_rn_im2col3": [vp, ll, i32, i32, vp, vp],
             "nfb_rn_bn_apply": [vp, vp, vp, vp, ll, vp, pll, vp, pll, i32, i32, i32, i32, f32, f32, vp],
             "nfb_rn_bn_bwd": [i32, vp, vp, vp, vp, vp, vp, vp, ll, vp, ll, pll, vp, pll, vp, pll,
-                              i32, i32, i32, f32, vp],
+                              i32, i32, i32, f32, vp, vp],
             "nfb_rn_head": [vp, i32, i32, i32, vp, ll, vp, ll, ll, ll, vp, ll, ll, ll, vp, vp, vp],
             "nfb_rn_wm_convert": [vp, i32, ll, vp, ll, vp, vp, ll, i32, i32, vp],
             "nfb_rn_tap_sgd": [vp, i32, ll, vp, vp, vp, vp, ll, i32, f32, f32, f32, vp],
@@ -174,6 +174,7 @@ def conv_gemm(
     stats: torch.Tensor | None = None, residual: torch.Tensor | None = None,
     res_mask: torch.Tensor | None = None, out_mask: torch.Tensor | None = None, n_out: int,
     tile: tuple[int, int] | None = None, all_classes: bool = False,
+    bn_x: torch.Tensor | None = None,
 ) -> None:
     """``out[pos, n] = Σ_taps A[pos + tap, :] · W`` on tensor cores (see ``csrc/rn_conv.cu``)."""
     lib = _lib()
@@ -194,7 +195,7 @@ def conv_gemm(
         1 if dgrad else 0, C.byref(a0), C.byref(a1s) if a1s is not None else None, w.ptr,
         w1.ptr if w1 is not None else None, dims, clients, imgs, h, wd, n_out, len(taps),
         _tap_array(taps), C.byref(o), oph, opw, _ptr(stats), _ptr(residual), _ptr(res_mask),
-        _ptr(out_mask), bn, halves, 4 if all_classes else 1, st.data_ptr(), _stream(a))
+        _ptr(out_mask), _ptr(bn_x), bn, halves, 4 if all_classes else 1, st.data_ptr(), _stream(a))
     _check(code, "rn_conv_gemm")
 
 
@@ -247,15 +248,16 @@ def bn_apply(x, y, slots, stats, bn_offs, *, clients: int, relu: bool, res=None,
 
 
 def bn_bwd(apply: bool, dout, out, x, slots, sgrad, grad_offs, stats, bn_offs, *, clients: int,
-           dx=None, x2=None, dx2=None, stats2=None, bn2_offs=None, eps: float = 1e-5) -> None:
+           dx=None, x2=None, dx2=None, stats2=None, bn2_offs=None, eps: float = 1e-5,
+           raw_sums: torch.Tensor | None = None) -> None:
     c = x.shape[-1]
     p = x.numel() // c // clients
     _check(_lib().nfb_rn_bn_bwd(
         1 if apply else 0, dout.data_ptr(), _ptr(out), x.data_ptr(), _ptr(x2), _ptr(dx), _ptr(dx2),
         slots.data_ptr(), slots.stride(0), sgrad.data_ptr(), sgrad.stride(0), _ll(grad_offs),
         stats.data_ptr(), _ll(bn_offs), _ptr(stats2),
-        _ll(bn2_offs) if bn2_offs is not None else None, clients, p, c, eps, _stream(x)),
-        "rn_bn_bwd")
+        _ll(bn2_offs) if bn2_offs is not None else None, clients, p, c, eps, _ptr(raw_sums),
+        _stream(x)), "rn_bn_bwd")
 
 
 def head(feat, labels, slots, w_off, b_off, sgrad, dw_off, db_off, dfeat, stats, *, clients: int) -> None:

@@ -201,3 +201,49 @@ def test_momentum_and_weight_decay_match_torch_sgd():
         assert cos > 0.7 and 0.9 < ratio < 1.1, (k, cos, ratio)
     for k in ("bn1.running_var", "layer2.0.shortcut.1.running_mean"):
         torch.testing.assert_close(got[k].float(), want[k].float(), rtol=2e-2, atol=2e-3)
+
+
+def test_bn_sums_from_the_dgrad_epilogue_give_the_bn_gradients(monkeypatch):
+    """Every BatchNorm backward of one step, checked in place: the gradient rows (dgamma, dbeta)
+    the apply kernel leaves in ``sgrad`` - derived from the sums of the dgrad epilogue where the
+    engine fuses them - against fp32 torch on the very tensors the kernel read.  (Two separate runs
+    cannot be compared this tightly: fp32 atomics reorder the forward statistics and a batch-16
+    network in bf16 amplifies that to per cents within a few layers.)"""
+    import nanofed_b200.models.resnet_cohort as rc
+    from nanofed_b200 import ops
+    from nanofed_b200.ops import rn
+
+    seen = []
+    real = rn.bn_bwd
+
+    def spy(apply, dout, out, x, slots, sgrad, grad_offs, stats, bn_offs, **kw):
+        if apply:
+            torch.cuda.synchronize()
+            g, c = stats.shape[0], stats.shape[2]
+            d, xx = dout.float().reshape(g, -1, c), x.float().reshape(g, -1, c)
+            n = d.shape[1]
+            mean = stats[:, 0] / n
+            rstd = (stats[:, 1] / n - mean * mean + 1e-5).rsqrt()
+            want_g = (d * (xx - mean[:, None]) * rstd[:, None]).sum(1)
+            want_b = d.sum(1)
+        real(apply, dout, out, x, slots, sgrad, grad_offs, stats, bn_offs, **kw)
+        if apply:
+            torch.cuda.synchronize()
+            got_g = sgrad[:, grad_offs[0] : grad_offs[0] + c]
+            got_b = sgrad[:, grad_offs[1] : grad_offs[1] + c]
+            seen.append((kw.get("raw_sums") is not None,
+                         float((got_g - want_g).norm() / want_g.norm()),
+                         float((got_b - want_b).norm() / want_b.norm())))
+
+    monkeypatch.setattr(rc.rn, "bn_bwd", spy)
+    sim = _sim(use_cuda_graph=False)
+    assert sim.engine.fuse_bn_sums
+    a = sim.arena
+    ops.bcast_global(a.master, a.slots, a.slots_lowp, a.momentum)
+    sim.engine.after_broadcast()
+    sim.engine.step(0)
+    torch.cuda.synchronize()
+    assert len(seen) == 17                       # stem + 8 blocks x (bn1, bn2 [+ shortcut])
+    assert sum(fused for fused, _, _ in seen) == 13, seen   # all but the last bn2 and 3 projections
+    for fused, eg, eb in seen:
+        assert eg < 1e-5 and eb < 1e-5, seen

@@ -97,9 +97,11 @@ def check_layer(cin, cout, h, stride, k, clients=2, batch=16, tol=1.2e-2):
         res = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
         msk = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
         om = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
+        bx = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
+        bsum = torch.zeros(clients, 2, cin, device=DEV)
         rn.conv_gemm(True, dy, wref, dx, clients=clients, grid_hw=(h, h),
                      taps=rn.dgrad_taps(k, 1, cout), residual=res, res_mask=msk, out_mask=om,
-                     n_out=cin)
+                     n_out=cin, stats=bsum, bn_x=bx)
         want = (ref_dx + res.float() * (msk.float() > 0)) * (om.float() > 0)
     else:
         dx.zero_()
@@ -114,8 +116,15 @@ def check_layer(cin, cout, h, stride, k, clients=2, batch=16, tol=1.2e-2):
     torch.cuda.synchronize()
     e = rel(dx, want)
     good = e < tol and canaries_ok(raw, dx.numel())
+    extra = ""
+    if stride == 1:   # BatchNorm backward sums of the stored (rounded) gradient
+        gf = dx.float().view(clients, -1, cin)
+        e1 = rel(bsum[:, 0], gf.sum(1))
+        e2 = rel(bsum[:, 1], (gf * bx.float().view(clients, -1, cin)).sum(1))
+        good = good and e1 < 1e-3 and e2 < 1e-3
+        extra = f"  sum g {e1:.1e}  sum gx {e2:.1e}"
     ok &= good
-    print(f"  dgrad {name}: rel {e:.2e}  {'ok' if good else 'FAIL'}")
+    print(f"  dgrad {name}: rel {e:.2e}{extra}  {'ok' if good else 'FAIL'}")
     # ---------------- wgrad ----------------
     for k_split, posk in ((1, 128), (3, 128), (1, 64)):
         n = k * k * cout * cin
@@ -150,9 +159,11 @@ def check_fused_shortcut(cin=64, cout=128, h=32, clients=2, batch=16, tol=1.2e-2
     raw, dx = guarded((clients * batch, h, h, cin), torch.bfloat16)
     # all four output parity classes in one launch (grid.z = class x client), with an output mask
     om = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
+    bx = torch.randn(clients * batch, h, h, cin, generator=gen).to(DEV).bfloat16()
+    bsum = torch.zeros(clients, 2, cin, device=DEV)
     rn.conv_gemm(True, dy3, r3, dx, clients=clients, grid_hw=(ho, ho),
                  taps=rn.dgrad_taps_all_classes(3, cout, cout), out_parity=(0, 0), all_classes=True,
-                 a1=dy1, w1=r1, out_mask=om, n_out=cin)
+                 a1=dy1, w1=r1, out_mask=om, n_out=cin, stats=bsum, bn_x=bx)
     torch.cuda.synchronize()
     want = []
     for g in range(clients):
@@ -164,8 +175,12 @@ def check_fused_shortcut(cin=64, cout=128, h=32, clients=2, batch=16, tol=1.2e-2
         (y3 * d3).sum().add((y1 * d1).sum()).backward()
         want.append(xi.grad.permute(0, 2, 3, 1))
     e = rel(dx, torch.cat(want) * (om.float() > 0))
-    good = e < tol and canaries_ok(raw, dx.numel())
-    print(f"  dgrad 3x3 s2 + 1x1 s2 shortcut {cin}->{cout}: rel {e:.2e}  {'ok' if good else 'FAIL'}")
+    gf = dx.float().view(clients, -1, cin)
+    e1 = rel(bsum[:, 0], gf.sum(1))
+    e2 = rel(bsum[:, 1], (gf * bx.float().view(clients, -1, cin)).sum(1))
+    good = e < tol and e1 < 1e-3 and e2 < 1e-3 and canaries_ok(raw, dx.numel())
+    print(f"  dgrad 3x3 s2 + 1x1 s2 shortcut {cin}->{cout}: rel {e:.2e}  sum g {e1:.1e}  "
+          f"sum gx {e2:.1e}  {'ok' if good else 'FAIL'}")
     tc.check_status(DEV)
     return good
 
