@@ -80,8 +80,22 @@ class _Block:
     bufs: dict[str, torch.Tensor] = field(default_factory=dict)
 
 
-class ResNetCohortNet:
-    """Lock-step local training of ``arena.num_clients`` ResNet-18s on one GPU."""
+class _Rows:
+    """Clients ``[lo, hi)`` of an arena (or of the resident shards): row views, nothing copied."""
+
+    def __init__(self, arena: Any, lo: int, hi: int) -> None:
+        self.device, self.layout, self.num_clients = arena.device, arena.layout, hi - lo
+        self.slots, self.stats = arena.slots[lo:hi], arena.stats[lo:hi]
+        self.momentum = None if arena.momentum is None else arena.momentum[lo:hi]
+
+
+class _ShardRows:
+    def __init__(self, shards: Any, lo: int, hi: int) -> None:
+        self.images, self.labels = shards.images[lo:hi], shards.labels[lo:hi]
+
+
+class _Lane:
+    """Lock-step local training of ``arena.num_clients`` ResNet-18s on the current stream."""
 
     def __init__(self, cfg: Any, arena: Any, shards: Any) -> None:
         assert arena.device.type == "cuda", "ResNetCohortNet needs a CUDA device"
@@ -172,8 +186,6 @@ class ResNetCohortNet:
                 blk.bufs["rawsc"] = act(ho, w)
         big = g * b * 32 * 32 * 64
         self._scratch = [torch.zeros(big, **bf) for _ in range(5)]   # D0, D1, S1, S2, S3
-        self._graph: "torch.cuda.CUDAGraph | None" = None
-        self.launches_per_round = 0
         self.sms = torch.cuda.get_device_properties(dev).multi_processor_count
         # which convolutions get their SGD step inside the wgrad epilogue (complete gradient in one
         # CTA, momentum-free); the others go through dwt + tap_sgd
@@ -384,9 +396,72 @@ class ResNetCohortNet:
         rn.small_sgd(self.small_table, self.n_small, slots, a.momentum, self.sgrad,
                      lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay, zero=self.stats)
 
+
+
+class ResNetCohortNet:
+    """Local training of ``arena.num_clients`` ResNet-18s on one GPU: the clients are dealt to
+    ``NFB_RN_STREAMS`` lanes, each a lock-step sub-cohort on its own CUDA stream; the whole local
+    epoch of all lanes is one CUDA graph with one fork and one join.
+
+    Default: ONE lane.  Within a lane every kernel depends on the one before it, so the HBM-bound
+    BatchNorm passes and the tails of the persistent convolution kernels (512 tiles on 148 SMs =
+    3.46 waves) leave the tensor pipe idle, and two independent lanes should fill those holes with
+    each other's work.  Measured (8 clients x batch 64, one B200): 1 lane 142.6 k samples/s,
+    2 lanes 140.3 k, 4 lanes 129.2 k.  The persistent convolution CTA owns its SM outright (384
+    threads x 168 registers = the whole register file, 225 KB of shared memory), so no BatchNorm
+    block can run next to it: the lanes only alternate, and every half-size launch pays its own
+    prologue and its own last wave."""
+
+    def __init__(self, cfg: Any, arena: Any, shards: Any) -> None:
+        self.cfg, self.arena, self.shards = cfg, arena, shards
+        self.device = arena.device
+        g = arena.num_clients
+        n = max(1, int(os.environ.get("NFB_RN_STREAMS", "1")))
+        while g % n:
+            n -= 1
+        per = g // n
+        self.lanes = [_Lane(cfg, _Rows(arena, k * per, (k + 1) * per),
+                            _ShardRows(shards, k * per, (k + 1) * per)) for k in range(n)]
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in self.lanes[1:]]
+        self._graph: "torch.cuda.CUDAGraph | None" = None
+        self.launches_per_round = 0
+        self.fuse_bn_sums = self.lanes[0].fuse_bn_sums
+
+    def after_broadcast(self) -> None:
+        for lane in self.lanes:
+            lane.after_broadcast()
+
+    def before_aggregate(self) -> None:
+        for lane in self.lanes:
+            lane.before_aggregate()
+
+    def _run(self, steps: "range | list[int]") -> None:
+        """``steps`` of every lane: lane 0 on the current stream, the others forked from it and
+        joined back (also what stream capture records)."""
+        main = torch.cuda.current_stream(self.device)
+        if not self.streams:
+            for s in steps:
+                self.lanes[0].step(s)
+            return
+        fork = torch.cuda.Event()
+        fork.record(main)
+        for st in self.streams:
+            st.wait_event(fork)
+        for s in steps:      # interleaved issue order: eager launches of the lanes overlap too
+            self.lanes[0].step(s)
+            for lane, st in zip(self.lanes[1:], self.streams):
+                with torch.cuda.stream(st):
+                    lane.step(s)
+        for st in self.streams:
+            done = torch.cuda.Event()
+            done.record(st)
+            main.wait_event(done)
+
+    def step(self, step: int) -> None:
+        self._run([step])
+
     def _all_steps(self) -> None:
-        for s in range(self.cfg.local_steps):
-            self.step(s)
+        self._run(range(self.cfg.local_steps))
 
     def local_steps(self) -> None:
         if not self.cfg.use_cuda_graph:
@@ -398,19 +473,14 @@ class ResNetCohortNet:
 
     def _capture(self) -> None:
         a = self.arena
-        keep = (a.slots.clone(), a.stats.clone(), self.wt.clone(), self.wm.clone(),
-                None if a.momentum is None else a.momentum.clone(),
-                None if self.mom is None else self.mom.clone())
+        state = [a.slots, a.stats] + ([a.momentum] if a.momentum is not None else [])
+        for lane in self.lanes:
+            state += [lane.wt, lane.wm] + ([lane.mom] if lane.mom is not None else [])
+        keep = [t.clone() for t in state]
 
         def restore() -> None:
-            a.slots.copy_(keep[0])
-            a.stats.copy_(keep[1])
-            self.wt.copy_(keep[2])
-            self.wm.copy_(keep[3])
-            if keep[4] is not None:
-                a.momentum.copy_(keep[4])
-            if keep[5] is not None:
-                self.mom.copy_(keep[5])
+            for t, k in zip(state, keep):
+                t.copy_(k)
 
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
@@ -420,6 +490,7 @@ class ResNetCohortNet:
         torch.cuda.synchronize(self.device)
         tc.check_status(self.device)
         restore()
+        torch.cuda.synchronize(self.device)
         before = native.LAUNCHES
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=side):

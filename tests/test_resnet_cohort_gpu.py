@@ -243,7 +243,8 @@ def test_bn_sums_from_the_dgrad_epilogue_give_the_bn_gradients(monkeypatch):
     sim.engine.after_broadcast()
     sim.engine.step(0)
     torch.cuda.synchronize()
-    assert len(seen) == 17                       # stem + 8 blocks x (bn1, bn2 [+ shortcut])
-    assert sum(fused for fused, _, _ in seen) == 13, seen   # all but the last bn2 and 3 projections
+    lanes = len(sim.engine.lanes)
+    assert len(seen) == 17 * lanes               # stem + 8 blocks x (bn1, bn2 [+ shortcut])
+    assert sum(fused for fused, _, _ in seen) == 13 * lanes, seen   # all but the last bn2 and 3 projections
     for fused, eg, eb in seen:
         assert eg < 1e-5 and eb < 1e-5, seen

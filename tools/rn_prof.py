@@ -13,6 +13,8 @@ import sys
 from collections import defaultdict
 from pathlib import Path
 
+import os
+os.environ.setdefault("NFB_RN_STREAMS", "1")   # one lane: per-launch event times stay meaningful
 import torch
 
 ROOT = Path(__file__).resolve().parent.parent

@@ -4,6 +4,8 @@ weight conversion; the third step starts at launch 247)."""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import os
+os.environ.setdefault("NFB_RN_STREAMS", "1")   # one lane: per-launch event times stay meaningful
 import torch
 from nanofed_b200 import ops
 from nanofed_b200.ops import native, tc
