@@ -403,6 +403,20 @@ int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, c
                   long long sgrad_stride, const long long* grad_offs, const float* stats,
                   const long long* bn_offs, const float* stats2, const long long* bn2_offs,
                   int clients, int P, int C, float eps, const float* raw_sums, void* stream);
+/* GroupNorm(8) of the ResNet engine (csrc/rn_gn.cu).  Activations [imgs][HW][C] bf16; stats and
+ * bsums are [imgs][8][2] fp32 and must be zero before the launch that accumulates into them
+ * (gn_stats / the reduce pass of gn_bwd).  gn_offs = {weight, bias} offsets in a client's row;
+ * image i belongs to client i / imgs_per_client.                                               */
+int nfb_rn_gn_stats(const void* x, int imgs, int HW, int C, float* stats, void* stream);
+int nfb_rn_gn_apply(const void* x, const void* res, void* y, const float* slots,
+                    long long row_stride, const float* stats, const long long* gn_offs,
+                    const float* res_stats, const long long* res_offs, int imgs,
+                    int imgs_per_client, int HW, int C, int relu, float eps, void* stream);
+int nfb_rn_gn_bwd(int apply, const void* dout, const void* x, const void* x2, void* dx, void* dx2,
+                  const float* slots, long long row_stride, float* sgrad, long long sgrad_stride,
+                  const long long* grad_offs, const float* stats, const long long* gn_offs,
+                  const float* stats2, const long long* gn2_offs, float* bsums, float* bsums2,
+                  int imgs, int imgs_per_client, int HW, int C, float eps, void* stream);
 int nfb_rn_head(const void* feat, int clients, int batch, int positions, const int64_t* labels,
                 long long label_gs, const float* slots, long long row_stride, long long w_off,
                 long long b_off, float* sgrad, long long sgrad_stride, long long dw_off,

@@ -108,9 +108,12 @@ class _Lane:
         lay = arena.layout
         self.n_total = lay.total
         off = {name: lay[name].offset for name in lay.names}
+        # "batch": BatchNorm2d (statistics per client and channel, from the conv epilogue);
+        # "group": GroupNorm(8) (statistics per image and group, csrc/rn_gn.cu) - model resnet18_gn
+        self.norm = "batch" if "bn1.running_mean" in off else "group"
 
         def bn(prefix: str, c: int) -> _Bn:
-            return _Bn(prefix, c, tuple(off[f"{prefix}.{n}"] for n in
+            return _Bn(prefix, c, tuple(off.get(f"{prefix}.{n}", -1) for n in
                                         ("weight", "bias", "running_mean", "running_var",
                                          "num_batches_tracked")))
 
@@ -144,7 +147,7 @@ class _Lane:
         small: list[tuple[int, int, int]] = []           # (p_off, g_off, len)
         for n in self.bns:
             n.s_off = s_cursor
-            s_cursor += g * 2 * n.c
+            s_cursor += g * 2 * n.c if self.norm == "batch" else g * b * 16
             n.g_off = (g_cursor, g_cursor + n.c)
             small += [(n.offs[0], g_cursor, n.c), (n.offs[1], g_cursor + n.c, n.c)]
             g_cursor += 2 * n.c
@@ -196,7 +199,8 @@ class _Lane:
         self.tap_ranges = torch.tensor(ranges or [(0, 0)], dtype=torch.int64, device=dev)
         self.tap_max = max((r[1] for r in ranges), default=0)
         # BatchNorm backward sums from the dgrad epilogue instead of a reduction pass
-        self.fuse_bn_sums = os.environ.get("NFB_RN_NO_FUSED_BN_SUMS") is None
+        self.fuse_bn_sums = (self.norm == "batch"
+                             and os.environ.get("NFB_RN_NO_FUSED_BN_SUMS") is None)
         self._tile_override = os.environ.get("NFB_RN_TILE")   # "bn,halves" for experiments
         self._wgrad_posk = int(os.environ.get("NFB_RN_WGRAD_K", "0"))   # 0 = per-layer choice
 
@@ -209,10 +213,14 @@ class _Lane:
         return rn.WeightRef(self.wt, c.t_off, c.taps * c.cout, c.cin)
 
     def _bn_stats(self, n: _Bn) -> torch.Tensor:
+        if self.norm == "group":      # [images][8 groups][sum, sum of squares]
+            return self.stats[n.s_off : n.s_off + self.g * self.b * 16].view(self.g * self.b, 8, 2)
         return self.stats[n.s_off : n.s_off + self.g * 2 * n.c].view(self.g, 2, n.c)
 
     def _bn_bsum(self, n: _Bn) -> torch.Tensor:
         lo = self._s_half + n.s_off
+        if self.norm == "group":      # [images][8 groups][sum gamma g, sum gamma g xhat]
+            return self.stats[lo : lo + self.g * self.b * 16].view(self.g * self.b, 8, 2)
         return self.stats[lo : lo + self.g * 2 * n.c].view(self.g, 2, n.c)
 
     def _tile(self, positions: int, n_out: int) -> tuple[int, int]:
@@ -223,10 +231,43 @@ class _Lane:
         return rn.pick_tile(positions, n_out, self.g, self.sms)
 
     def _fwd_conv(self, c: _Conv, x: torch.Tensor, raw: torch.Tensor, n: _Bn) -> None:
+        batch = self.norm == "batch"
         rn.conv_gemm(False, x, self._wref(c), raw, clients=self.g, grid_hw=(c.hout, c.hout),
                      taps=rn.fwd_taps(c.k, c.stride, c.cout), a_parity=c.stride == 2,
-                     stats=self._bn_stats(n), n_out=c.cout,
+                     stats=self._bn_stats(n) if batch else None, n_out=c.cout,
                      tile=self._tile(self.b * c.hout * c.hout, c.cout))
+        if not batch:
+            rn.gn_stats(raw, self._bn_stats(n))
+
+    def _norm_apply(self, n: _Bn, raw: torch.Tensor, y: torch.Tensor, *, res=None,
+                    res_n: "_Bn | None" = None) -> None:
+        """y = relu(norm(raw) [+ res | + norm_sc(res)])."""
+        fn = rn.bn_apply if self.norm == "batch" else rn.gn_apply
+        fn(raw, y, self.arena.slots, self._bn_stats(n), n.offs, clients=self.g, relu=True, res=res,
+           res_stats=self._bn_stats(res_n) if res_n is not None else None,
+           res_offs=res_n.offs if res_n is not None else None)
+
+    def _norm_bwd(self, n: _Bn, dout: torch.Tensor, x: torch.Tensor, dx: torch.Tensor, *,
+                  n2: "_Bn | None" = None, x2=None, dx2=None, have_sums: bool = False) -> None:
+        """Normalisation backward: parameter gradients into ``sgrad``, dx (and dx2 for the
+        projection shortcut's layer, which receives the same ``dout``).  ``have_sums``: the dgrad
+        that produced ``dout`` already left the BatchNorm sums in ``_bn_bsum(n)``."""
+        slots = self.arena.slots
+        offs = n.g_off + (n2.g_off if n2 is not None else (0, 0))
+        if self.norm == "group":
+            kw = dict(clients=self.g, x2=x2, stats2=self._bn_stats(n2) if n2 is not None else None,
+                      gn2_offs=n2.offs if n2 is not None else None,
+                      bsums2=self._bn_bsum(n2) if n2 is not None else None)
+            args = (dout, x, slots, self.sgrad, offs, self._bn_stats(n), n.offs, self._bn_bsum(n))
+            rn.gn_bwd(False, *args, **kw)
+            rn.gn_bwd(True, *args, dx=dx, dx2=dx2, **kw)
+            return
+        kw = dict(clients=self.g, x2=x2, stats2=self._bn_stats(n2) if n2 is not None else None,
+                  bn2_offs=n2.offs if n2 is not None else None)
+        if not have_sums:
+            rn.bn_bwd(False, dout, None, x, slots, self.sgrad, offs, self._bn_stats(n), n.offs, **kw)
+        rn.bn_bwd(True, dout, None, x, slots, self.sgrad, offs, self._bn_stats(n), n.offs, dx=dx,
+                  dx2=dx2, raw_sums=self._bn_bsum(n) if have_sums else None, **kw)
 
     def _pick_ksplit(self, c: _Conv) -> int:
         bn = min(c.cout, 256)
@@ -300,23 +341,18 @@ class _Lane:
         # ---------------- forward ----------------
         rn.im2col3(x, self.xcol)
         self._fwd_conv(self.stem, self.xcol, self.raw0, self.stem_bn)
-        rn.bn_apply(self.raw0, self.a0, slots, self._bn_stats(self.stem_bn), self.stem_bn.offs,
-                    clients=g, relu=True)
+        self._norm_apply(self.stem_bn, self.raw0, self.a0)
         cur = self.a0
         for blk in self.blocks:
             u = blk.bufs
             self._fwd_conv(blk.conv1, cur, u["raw1"], blk.bn1)
-            rn.bn_apply(u["raw1"], u["a"], slots, self._bn_stats(blk.bn1), blk.bn1.offs, clients=g,
-                        relu=True)
+            self._norm_apply(blk.bn1, u["raw1"], u["a"])
             self._fwd_conv(blk.conv2, u["a"], u["raw2"], blk.bn2)
             if blk.conv_sc is not None:
                 self._fwd_conv(blk.conv_sc, cur, u["rawsc"], blk.bn_sc)
-                rn.bn_apply(u["raw2"], u["out"], slots, self._bn_stats(blk.bn2), blk.bn2.offs,
-                            clients=g, relu=True, res=u["rawsc"],
-                            res_stats=self._bn_stats(blk.bn_sc), res_offs=blk.bn_sc.offs)
+                self._norm_apply(blk.bn2, u["raw2"], u["out"], res=u["rawsc"], res_n=blk.bn_sc)
             else:
-                rn.bn_apply(u["raw2"], u["out"], slots, self._bn_stats(blk.bn2), blk.bn2.offs,
-                            clients=g, relu=True, res=cur)
+                self._norm_apply(blk.bn2, u["raw2"], u["out"], res=cur)
             u["in"] = cur
             cur = u["out"]
         # ---------------- head: loss, metrics, gradient of the last feature map ----------------
@@ -335,32 +371,17 @@ class _Lane:
             dc2 = self._view(2, ho, w)
             proj = blk.conv_sc is not None
             dcs = self._view(3, ho, w) if proj else None
-            offs = (blk.bn2.g_off[0], blk.bn2.g_off[1]) + (
-                (blk.bn_sc.g_off[0], blk.bn_sc.g_off[1]) if proj else (0, 0))
-            kw = dict(clients=g, x2=u["rawsc"] if proj else None,
-                      stats2=self._bn_stats(blk.bn_sc) if proj else None,
-                      bn2_offs=blk.bn_sc.offs if proj else None)
             # dout is already the gradient w.r.t. the pre-ReLU block output (its producer - the
             # head or the next block's dgrad epilogue - applied the mask): no mask operand here
-            if not have_sums:
-                rn.bn_bwd(False, dout, None, u["raw2"], slots, self.sgrad, offs,
-                          self._bn_stats(blk.bn2), blk.bn2.offs, **kw)
-            rn.bn_bwd(True, dout, None, u["raw2"], slots, self.sgrad, offs,
-                      self._bn_stats(blk.bn2), blk.bn2.offs, dx=dc2, dx2=dcs,
-                      raw_sums=self._bn_bsum(blk.bn2) if have_sums else None, **kw)
+            self._norm_bwd(blk.bn2, dout, u["raw2"], dc2, n2=blk.bn_sc if proj else None,
+                           x2=u["rawsc"] if proj else None, dx2=dcs, have_sums=have_sums)
             da = self._view(4, ho, w)
             # reads the old weights: before the wgrad
             self._dgrad(blk.conv2, dc2, da, relu_of=u["a"],
                         bn=(blk.bn1, u["raw1"]) if fuse else None)
             self._wgrad(blk.conv2, u["a"], dc2)
             dc1 = dc2                                     # dc2 is dead after the two launches above
-            offs1 = (blk.bn1.g_off[0], blk.bn1.g_off[1], 0, 0)
-            if not fuse:
-                rn.bn_bwd(False, da, None, u["raw1"], slots, self.sgrad, offs1,
-                          self._bn_stats(blk.bn1), blk.bn1.offs, clients=g)
-            rn.bn_bwd(True, da, None, u["raw1"], slots, self.sgrad, offs1,
-                      self._bn_stats(blk.bn1), blk.bn1.offs, clients=g, dx=dc1,
-                      raw_sums=self._bn_bsum(blk.bn1) if fuse else None)
+            self._norm_bwd(blk.bn1, da, u["raw1"], dc1, have_sums=fuse)
             dx = self._view(d1, hin, cin)
             # dx is the gradient at the producer of this block's input: the stem BatchNorm or the
             # previous block's bn2 (+ shortcut).  A projection block there needs sum(g * x) for two
@@ -381,13 +402,7 @@ class _Lane:
             d0, d1 = d1, d0
         dout = self._view(d0, 32, 64)
         dc0 = self._view(2, 32, 64)
-        offs0 = (self.stem_bn.g_off[0], self.stem_bn.g_off[1], 0, 0)
-        if not have_sums:
-            rn.bn_bwd(False, dout, None, self.raw0, slots, self.sgrad, offs0,
-                      self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g)
-        rn.bn_bwd(True, dout, None, self.raw0, slots, self.sgrad, offs0,
-                  self._bn_stats(self.stem_bn), self.stem_bn.offs, clients=g, dx=dc0,
-                  raw_sums=self._bn_bsum(self.stem_bn) if have_sums else None)
+        self._norm_bwd(self.stem_bn, dout, self.raw0, dc0, have_sums=have_sums)
         self._wgrad(self.stem, self.xcol, dc0)
         # ---------------- update ----------------
         if self.tap_max:

@@ -43,6 +43,10 @@ def _lib() -> C.CDLL:
             "nfb_rn_bn_apply": [vp, vp, vp, vp, ll, vp, pll, vp, pll, i32, i32, i32, i32, f32, f32, vp],
             "nfb_rn_bn_bwd": [i32, vp, vp, vp, vp, vp, vp, vp, ll, vp, ll, pll, vp, pll, vp, pll,
                               i32, i32, i32, f32, vp, vp],
+            "nfb_rn_gn_stats": [vp, i32, i32, i32, vp, vp],
+            "nfb_rn_gn_apply": [vp, vp, vp, vp, ll, vp, pll, vp, pll, i32, i32, i32, i32, i32, f32, vp],
+            "nfb_rn_gn_bwd": [i32, vp, vp, vp, vp, vp, vp, ll, vp, ll, pll, vp, pll, vp, pll, vp, vp,
+                              i32, i32, i32, i32, f32, vp],
             "nfb_rn_head": [vp, i32, i32, i32, vp, ll, vp, ll, ll, ll, vp, ll, ll, ll, vp, vp, vp],
             "nfb_rn_wm_convert": [vp, i32, ll, vp, ll, vp, vp, ll, i32, i32, vp],
             "nfb_rn_tap_sgd": [vp, i32, ll, vp, vp, vp, vp, ll, i32, f32, f32, f32, vp],
@@ -258,6 +262,38 @@ def bn_bwd(apply: bool, dout, out, x, slots, sgrad, grad_offs, stats, bn_offs, *
         stats.data_ptr(), _ll(bn_offs), _ptr(stats2),
         _ll(bn2_offs) if bn2_offs is not None else None, clients, p, c, eps, _ptr(raw_sums),
         _stream(x)), "rn_bn_bwd")
+
+
+def gn_stats(x: torch.Tensor, stats: torch.Tensor) -> None:
+    """GroupNorm(8) sums of ``x`` bf16 ``[imgs, h, w, c]`` into ``stats`` fp32 ``[imgs, 8, 2]``
+    (accumulated: the buffer must be zero)."""
+    imgs, h, w, c = x.shape
+    assert stats.shape == (imgs, 8, 2) and stats.dtype == torch.float32
+    _check(_lib().nfb_rn_gn_stats(x.data_ptr(), imgs, h * w, c, stats.data_ptr(), _stream(x)),
+           "rn_gn_stats")
+
+
+def gn_apply(x, y, slots, stats, gn_offs, *, clients: int, relu: bool, res=None, res_stats=None,
+             res_offs=None, eps: float = 1e-5) -> None:
+    imgs, h, w, c = x.shape
+    _check(_lib().nfb_rn_gn_apply(
+        x.data_ptr(), _ptr(res), y.data_ptr(), slots.data_ptr(), slots.stride(0), stats.data_ptr(),
+        _ll(gn_offs[:2]), _ptr(res_stats), _ll(res_offs[:2]) if res_offs is not None else None,
+        imgs, imgs // clients, h * w, c, 1 if relu else 0, eps, _stream(x)), "rn_gn_apply")
+
+
+def gn_bwd(apply: bool, dout, x, slots, sgrad, grad_offs, stats, gn_offs, bsums, *, clients: int,
+           dx=None, x2=None, dx2=None, stats2=None, gn2_offs=None, bsums2=None,
+           eps: float = 1e-5) -> None:
+    """``apply=False``: group sums into ``bsums`` (zero before) and dgamma / dbeta into ``sgrad``
+    (atomics); ``apply=True``: dx (dx2) from those sums."""
+    imgs, h, w, c = x.shape
+    _check(_lib().nfb_rn_gn_bwd(
+        1 if apply else 0, dout.data_ptr(), x.data_ptr(), _ptr(x2), _ptr(dx), _ptr(dx2),
+        slots.data_ptr(), slots.stride(0), sgrad.data_ptr(), sgrad.stride(0), _ll(grad_offs),
+        stats.data_ptr(), _ll(gn_offs[:2]), _ptr(stats2),
+        _ll(gn2_offs[:2]) if gn2_offs is not None else None, bsums.data_ptr(), _ptr(bsums2),
+        imgs, imgs // clients, h * w, c, eps, _stream(x)), "rn_gn_bwd")
 
 
 def head(feat, labels, slots, w_off, b_off, sgrad, dw_off, db_off, dfeat, stats, *, clients: int) -> None:

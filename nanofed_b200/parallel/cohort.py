@@ -423,10 +423,10 @@ class FedSimulation:
 
         engine = cfg.engine
         if engine == "auto":
-            engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18")
+            engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18", "resnet18_gn")
                                    and self.device.type == "cuda"
                                    and _grouped_available()) else "autograd"
-            if cfg.local_privacy is not None and cfg.model == "resnet18":
+            if cfg.local_privacy is not None and cfg.model.startswith("resnet18"):
                 engine = "autograd"      # client-side DP-SGD: MNIST grouped engine and autograd
         if cfg.compute_dtype not in ("bf16", "fp32"):
             raise ValueError(f"compute_dtype must be 'bf16' or 'fp32', got {cfg.compute_dtype!r}")
@@ -438,12 +438,12 @@ class FedSimulation:
                 raise ValueError("engine='grouped' computes in bf16 (fp32 accumulate/master); use "
                                  "compute_dtype='bf16', or engine='autograd' for fp32 compute")
             engine = "autograd"
-        if engine == "grouped" and cfg.model == "resnet18" and cfg.local_privacy is not None:
+        if engine == "grouped" and cfg.model.startswith("resnet18") and cfg.local_privacy is not None:
             raise ValueError("client-side DP-SGD (local_privacy) is implemented in the MNIST grouped "
                              "engine and the autograd engine, not in the ResNet grouped engine")
-        if engine == "grouped" and cfg.model not in ("mnist_cnn", "resnet18"):
+        if engine == "grouped" and cfg.model not in ("mnist_cnn", "resnet18", "resnet18_gn"):
             raise ValueError(f"engine='grouped' has no hand-written network for {cfg.model!r} "
-                             "(available: mnist_cnn, resnet18); use engine='autograd'")
+                             "(available: mnist_cnn, resnet18, resnet18_gn); use engine='autograd'")
         self.engine_name = engine
 
         self.arena = Arena(
@@ -465,7 +465,7 @@ class FedSimulation:
         self.arena.counts.copy_(self.shards.sample_counts.to(torch.float32))
         self._counts_host = [float(v) for v in shards.sample_counts.tolist()]
 
-        if engine == "grouped" and cfg.model == "resnet18":
+        if engine == "grouped" and cfg.model.startswith("resnet18"):
             from nanofed_b200.models.resnet_cohort import ResNetCohortNet
 
             self.engine: Any = ResNetCohortNet(cfg, self.arena, self.shards)

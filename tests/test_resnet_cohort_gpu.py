@@ -248,3 +248,100 @@ def test_bn_sums_from_the_dgrad_epilogue_give_the_bn_gradients(monkeypatch):
     assert sum(fused for fused, _, _ in seen) == 13 * lanes, seen   # all but the last bn2 and 3 projections
     for fused, eg, eb in seen:
         assert eg < 1e-5 and eb < 1e-5, seen
+
+
+@pytest.mark.parametrize("c,hw,two", [(64, 32, False), (128, 16, True), (512, 4, True)])
+def test_group_norm_kernels_match_torch(c, hw, two):
+    """csrc/rn_gn.cu against fp32 torch (F.group_norm + autograd): statistics, forward with the
+    residual variants, backward (parameter gradients, dx; with ``two`` also the projection
+    shortcut's GroupNorm fed by the same gradient)."""
+    from nanofed_b200.ops import rn
+
+    dev = torch.device("cuda")
+    gen = torch.Generator(device="cpu").manual_seed(c + hw)
+    clients, batch = 2, 8
+    imgs = clients * batch
+    x = (torch.randn(imgs, hw, hw, c, generator=gen) * 1.5 + 0.3).to(dev).bfloat16()
+    x2 = torch.randn(imgs, hw, hw, c, generator=gen).to(dev).bfloat16()
+    dout = torch.randn(imgs, hw, hw, c, generator=gen).to(dev).bfloat16()
+    row = 4 * c + 8
+    slots = torch.randn(clients, row, generator=gen).to(dev)          # gamma, beta, gamma2, beta2
+    offs, offs2 = (0, c), (2 * c, 3 * c)
+    stats = torch.zeros(imgs, 8, 2, device=dev)
+    stats2 = torch.zeros(imgs, 8, 2, device=dev)
+    rn.gn_stats(x, stats)
+    rn.gn_stats(x2, stats2)
+    xg = x.float().view(imgs, hw * hw, 8, c // 8)
+    torch.testing.assert_close(stats[:, :, 0], xg.sum((1, 3)), rtol=1e-4, atol=1e-2)
+    torch.testing.assert_close(stats[:, :, 1], (xg * xg).sum((1, 3)), rtol=1e-4, atol=1e-2)
+
+    def ref_forward(xf, x2f, gam, bet, gam2, bet2):
+        outs = []
+        for k in range(clients):
+            sl = slice(k * batch, (k + 1) * batch)
+            y = F.group_norm(xf[sl].permute(0, 3, 1, 2), 8, gam[k], bet[k], eps=1e-5)
+            if two:
+                y = y + F.group_norm(x2f[sl].permute(0, 3, 1, 2), 8, gam2[k], bet2[k], eps=1e-5)
+            else:
+                y = y + x2f[sl].permute(0, 3, 1, 2)
+            outs.append(y.permute(0, 2, 3, 1))
+        return torch.cat(outs)
+
+    leaves = [t.clone().requires_grad_(True) for t in
+              (x.float(), x2.float(), slots[:, :c], slots[:, c : 2 * c], slots[:, 2 * c : 3 * c],
+               slots[:, 3 * c : 4 * c])]
+    pre = ref_forward(*leaves)
+    y = torch.empty_like(x)
+    rn.gn_apply(x, y, slots, stats, offs, clients=clients, relu=True, res=x2,
+                res_stats=stats2 if two else None, res_offs=offs2 if two else None)
+    torch.cuda.synchronize()
+    want = torch.relu(pre)
+    assert float((y.float() - want).abs().max()) <= 2e-2 * float(want.abs().max()) + 1e-2
+    # backward: dout is the gradient w.r.t. the pre-ReLU sum
+    pre.backward(dout.float())
+    sgrad = torch.zeros(clients, 4 * c, device=dev)
+    bs, bs2 = torch.zeros(imgs, 8, 2, device=dev), torch.zeros(imgs, 8, 2, device=dev)
+    dx, dx2 = torch.empty_like(x), torch.empty_like(x)
+    kw = dict(clients=clients)
+    if two:
+        kw.update(x2=x2, stats2=stats2, gn2_offs=offs2, bsums2=bs2)
+    args = (dout, x, slots, sgrad, (0, c, 2 * c, 3 * c), stats, offs, bs)
+    rn.gn_bwd(False, *args, **kw)
+    rn.gn_bwd(True, *args, dx=dx, dx2=dx2 if two else None, **kw)
+    torch.cuda.synchronize()
+
+    def close(got, ref, tol):
+        assert float((got.float() - ref).norm()) <= tol * float(ref.norm()) + 1e-6, (
+            float((got.float() - ref).norm()), float(ref.norm()))
+
+    close(sgrad[:, :c], leaves[2].grad, 2e-3)          # dgamma
+    close(sgrad[:, c : 2 * c], leaves[3].grad, 2e-3)   # dbeta
+    close(dx, leaves[0].grad, 1e-2)                    # bf16 output
+    if two:
+        close(sgrad[:, 2 * c : 3 * c], leaves[4].grad, 2e-3)
+        close(sgrad[:, 3 * c :], leaves[5].grad, 2e-3)
+        close(dx2, leaves[1].grad, 1e-2)
+
+
+def test_group_norm_step_matches_fp32_autograd():
+    """resnet18_gn on the grouped engine: one step against fp32 autograd, judged like the
+    BatchNorm network (as close to fp32 as PyTorch's own bf16 autocast run)."""
+    import rn_step_check
+
+    w = rn_step_check.run(clients=2, batch=16, steps=1, verbose=False, model="resnet18_gn")
+    assert w["loss_err"] < 5e-3, w
+    assert rn_step_check.acceptable(w), w
+
+
+def test_group_norm_model_trains_on_the_grouped_engine():
+    from nanofed_b200.models import ResNet18
+    from nanofed_b200.ops import tc
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+
+    sim = FedSimulation(CohortConfig(model="resnet18_gn", clients_per_gpu=2, samples_per_client=32,
+                                     batch_size=16, learning_rate=0.02, device="cuda"))
+    assert sim.engine_name == "grouped" and sim.engine.lanes[0].norm == "group"
+    losses = [sim.run_round().agg_metrics["loss"] for _ in range(4)]
+    tc.check_status(sim.device)
+    assert all(l == l for l in losses) and losses[-1] < losses[0], losses
+    ResNet18(norm="group").load_state_dict(sim.global_state())

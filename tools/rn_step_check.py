@@ -2,7 +2,7 @@
 (TF32 off): loss, every parameter's update, BatchNorm running statistics.  The yardstick for a
 bf16-activation engine is PyTorch's own bf16 autocast run of the same step, printed alongside.
 
-    python tools/rn_step_check.py [--clients 2] [--batch 16] [--steps 1]
+    python tools/rn_step_check.py [--clients 2] [--batch 16] [--steps 1] [--model resnet18_gn]
 """
 
 from __future__ import annotations
@@ -20,10 +20,10 @@ torch.backends.cudnn.allow_tf32 = False
 torch.backends.cuda.matmul.allow_tf32 = False
 
 
-def reference_step(state, x, y, lr, steps, autocast):
+def reference_step(state, x, y, lr, steps, autocast, norm="batch"):
     from nanofed_b200.models import ResNet18
 
-    model = ResNet18(norm="batch").cuda().train()
+    model = ResNet18(norm=norm).cuda().train()
     model.load_state_dict(state)
     opt = torch.optim.SGD(model.parameters(), lr=lr)
     b = x.shape[0] // steps
@@ -40,13 +40,14 @@ def reference_step(state, x, y, lr, steps, autocast):
     return {k: v.detach().float().clone() for k, v in model.state_dict().items()}, losses
 
 
-def run(clients: int, batch: int, steps: int, verbose: bool = True) -> dict:
+def run(clients: int, batch: int, steps: int, verbose: bool = True, model: str = "resnet18") -> dict:
     from nanofed_b200 import ops
     from nanofed_b200.ops import tc
     from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
 
     lr = 0.05
-    cfg = CohortConfig(model="resnet18", clients_per_gpu=clients, samples_per_client=batch * steps,
+    norm = "group" if model == "resnet18_gn" else "batch"
+    cfg = CohortConfig(model=model, clients_per_gpu=clients, samples_per_client=batch * steps,
                        batch_size=batch, learning_rate=lr, use_cuda_graph=False, device="cuda",
                        engine="grouped")
     sim = FedSimulation(cfg)
@@ -66,8 +67,8 @@ def run(clients: int, batch: int, steps: int, verbose: bool = True) -> dict:
     for g in range(clients):
         got = {k: v.float() for k, v in sim.layout.unflatten(a.slots[g].clone()).items()}
         x, y = sim.shards.images[g], sim.shards.labels[g]
-        want, losses = reference_step(before, x, y, lr, steps, autocast=False)
-        auto, _ = reference_step(before, x, y, lr, steps, autocast=True)
+        want, losses = reference_step(before, x, y, lr, steps, autocast=False, norm=norm)
+        auto, _ = reference_step(before, x, y, lr, steps, autocast=True, norm=norm)
         loss_got = float(a.stats[g, 0] / a.stats[g, 2])
         loss_want = sum(losses) / len(losses)
         worst["loss_err"] = max(worst["loss_err"], abs(loss_got - loss_want) / abs(loss_want))
@@ -115,8 +116,9 @@ def main() -> int:
     ap.add_argument("--clients", type=int, default=2)
     ap.add_argument("--batch", type=int, default=16)
     ap.add_argument("--steps", type=int, default=1)
+    ap.add_argument("--model", default="resnet18", choices=["resnet18", "resnet18_gn"])
     args = ap.parse_args()
-    w = run(args.clients, args.batch, args.steps)
+    w = run(args.clients, args.batch, args.steps, model=args.model)
     ok = acceptable(w)
     print("STEP OK" if ok else "STEP MISMATCH")
     return 0 if ok else 1
