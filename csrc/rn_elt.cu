@@ -20,6 +20,7 @@
 // No reference counterpart: these are the torch library calls (BatchNorm2d, ReLU, AdaptiveAvgPool2d,
 // Linear, CrossEntropyLoss, SGD.step) that a ResNet runs inside nanofed/trainer/base.py:134-160.
 #include "common.cuh"
+#include "philox.cuh"
 
 namespace nfb {
 namespace rn {
@@ -469,15 +470,47 @@ __global__ void __launch_bounds__(256)
 // the others are updated inside the wgrad epilogue (csrc/rn_conv.cu).
 struct TapRange { long long t_off, len; };
 
+// Client-side DP-SGD (reference: nanofed/trainer/private.py:54-86 - clip the batch gradient of the
+// client to C, add N(0, (sigma C)^2) to every parameter's gradient) inside the two update kernels.
+// A client's gradient lives in two buffers, the tap-major conv gradients [0, t_stride) and the
+// compact BatchNorm / classifier row; idx_base places a kernel's buffer in that index space so the
+// two kernels draw from disjoint Philox counters.  Stream position = (steps done before this local
+// epoch (device counter) + step) x all clients of the job.
+struct RnDp {
+  const float* row_sumsq;              // [clients of this launch] squared gradient norm; null: no DP
+  float clip_norm, noise_std;
+  unsigned long long seed;
+  const unsigned long long* ctr;       // device: local steps of earlier rounds
+  int step;                            // step inside this local epoch
+  int client0, clients_total;          // global index of the launch's first client / of the job
+  long long row_groups;                // Philox groups (4 values) per client and step
+  long long idx_base;
+};
+__device__ __forceinline__ float rn_dp_scale(const RnDp& dp, int g) {
+  return fminf(dp.clip_norm / (sqrtf(dp.row_sumsq[g]) + 1e-6f), 1.f);
+}
+__device__ __forceinline__ unsigned long long rn_dp_group0(const RnDp& dp, int g) {
+  const unsigned long long t = *dp.ctr + static_cast<unsigned long long>(dp.step);
+  return (t * dp.clients_total + dp.client0 + g) * static_cast<unsigned long long>(dp.row_groups);
+}
+
 __global__ void __launch_bounds__(256)
     tap_sgd_kernel(const TapRange* __restrict__ ranges, float* __restrict__ wm,
                    float* __restrict__ dwt, float* __restrict__ mom, __nv_bfloat16* __restrict__ wt,
-                   long long t_stride, float lr, float mu, float wd) {
+                   long long t_stride, float lr, float mu, float wd, const RnDp dp) {
   const TapRange rg = ranges[blockIdx.y];
   const long long base = blockIdx.z * t_stride + rg.t_off;
+  const float gs = dp.row_sumsq ? rn_dp_scale(dp, blockIdx.z) : 1.f;
+  const unsigned long long group0 =
+      dp.row_sumsq ? rn_dp_group0(dp, blockIdx.z) + ((dp.idx_base + rg.t_off) >> 2) : 0ull;
   for (long long i = (blockIdx.x * 256ll + threadIdx.x) * 4; i < rg.len; i += gridDim.x * 1024ll) {
     float4 w = *reinterpret_cast<float4*>(wm + base + i);
-    const float4 gr = *reinterpret_cast<const float4*>(dwt + base + i);
+    float4 gr = *reinterpret_cast<const float4*>(dwt + base + i);
+    if (dp.row_sumsq) {
+      const float4 z = Philox::normal4(group0 + (i >> 2), dp.seed);
+      gr.x = fmaf(dp.noise_std, z.x, gr.x * gs); gr.y = fmaf(dp.noise_std, z.y, gr.y * gs);
+      gr.z = fmaf(dp.noise_std, z.z, gr.z * gs); gr.w = fmaf(dp.noise_std, z.w, gr.w * gs);
+    }
     float d[4] = {fmaf(wd, w.x, gr.x), fmaf(wd, w.y, gr.y), fmaf(wd, w.z, gr.z), fmaf(wd, w.w, gr.w)};
     if (mom) {
       float4 v = *reinterpret_cast<float4*>(mom + base + i);
@@ -503,9 +536,11 @@ __global__ void __launch_bounds__(256)
     small_sgd_kernel(const SmallEntry* __restrict__ table, float* __restrict__ slots,
                      long long row_stride, float* __restrict__ momentum, float* __restrict__ sgrad,
                      long long sgrad_stride, float lr, float mu, float wd,
-                     float* __restrict__ zero_ptr, long long zero_len) {
+                     float* __restrict__ zero_ptr, long long zero_len, const RnDp dp) {
   const SmallEntry e = table[blockIdx.x];
   const int g = blockIdx.y;
+  const float gs = dp.row_sumsq ? rn_dp_scale(dp, g) : 1.f;
+  const unsigned long long group0 = dp.row_sumsq ? rn_dp_group0(dp, g) : 0ull;
   // the BatchNorm batch sums of this step have been consumed: hand them back zeroed
   for (long long i = (static_cast<long long>(g) * gridDim.x + blockIdx.x) * 256 + threadIdx.x;
        i < zero_len; i += 256ll * gridDim.x * gridDim.y)
@@ -515,11 +550,28 @@ __global__ void __launch_bounds__(256)
   float* gr = sgrad + g * sgrad_stride + e.g_off;
   for (long long i = threadIdx.x; i < e.len; i += 256) {
     float w = p[i];
-    float d = fmaf(wd, w, gr[i]);
+    float gi = gr[i];
+    if (dp.row_sumsq) {
+      const long long idx = dp.idx_base + e.g_off + i;
+      const float4 z = Philox::normal4(group0 + (idx >> 2), dp.seed);
+      const int lane = static_cast<int>(idx & 3);
+      gi = fmaf(dp.noise_std, lane == 0 ? z.x : lane == 1 ? z.y : lane == 2 ? z.z : z.w, gi * gs);
+    }
+    float d = fmaf(wd, w, gi);
     if (m) { d = fmaf(mu, m[i], d); m[i] = d; }
     p[i] = fmaf(-lr, d, w);
     gr[i] = 0.f;
   }
+}
+
+static RnDp make_dp(const nfb_rn_dp* dp) {
+  RnDp d{};
+  if (dp && dp->row_sumsq) {
+    d.row_sumsq = dp->row_sumsq; d.clip_norm = dp->clip_norm; d.noise_std = dp->noise_std;
+    d.seed = dp->seed; d.ctr = dp->step_base; d.step = dp->step; d.client0 = dp->client0;
+    d.clients_total = dp->clients_total; d.row_groups = dp->row_groups; d.idx_base = dp->idx_base;
+  }
+  return d;
 }
 
 static int blocks_for(long long work_items, int clients) {
@@ -643,7 +695,7 @@ int nfb_rn_wm_convert(const void* table, int n_layers, long long total_cols, flo
 
 int nfb_rn_tap_sgd(const void* ranges, int n_ranges, long long max_len, float* wm, float* dwt,
                    float* momentum, void* wt, long long t_stride, int clients, float lr, float mu,
-                   float wd, void* stream) {
+                   float wd, const nfb_rn_dp* dp, void* stream) {
   using namespace nfb;
   NFB_REQUIRE(ranges && wm && dwt && wt && n_ranges >= 1, NFB_EINVAL, "rn_tap_sgd: null pointer");
   const int per = (4 * sm_count() + n_ranges * clients - 1) / (n_ranges * clients);
@@ -652,19 +704,22 @@ int nfb_rn_tap_sgd(const void* ranges, int n_ranges, long long max_len, float* w
   dim3 grid(static_cast<unsigned>(want < 1 ? 1 : want), n_ranges, clients);
   rn::tap_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
       static_cast<const rn::TapRange*>(ranges), wm, dwt, momentum, static_cast<__nv_bfloat16*>(wt),
-      t_stride, lr, mu, wd);
+      t_stride, lr, mu, wd, rn::make_dp(dp));
   return launch_status("rn_tap_sgd");
 }
 
 int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long row_stride,
                      float* momentum, float* sgrad, long long sgrad_stride, int clients, float lr,
-                     float mu, float wd, float* zero_ptr, long long zero_len, void* stream) {
+                     float mu, float wd, float* zero_ptr, long long zero_len, const nfb_rn_dp* dp,
+                     void* stream) {
   using namespace nfb;
   NFB_REQUIRE(table && slots && sgrad && n_entries >= 1, NFB_EINVAL, "rn_small_sgd: null pointer");
+  NFB_REQUIRE(!dp || !dp->row_sumsq || (dp->step_base && dp->clients_total >= 1), NFB_EINVAL,
+              "rn_small_sgd: DP needs the device step counter and the job's client count");
   dim3 grid(n_entries, clients);
   rn::small_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
       static_cast<const rn::SmallEntry*>(table), slots, row_stride, momentum, sgrad, sgrad_stride,
-      lr, mu, wd, zero_ptr, zero_ptr ? zero_len : 0);
+      lr, mu, wd, zero_ptr, zero_ptr ? zero_len : 0, rn::make_dp(dp));
   return launch_status("rn_small_sgd");
 }
 

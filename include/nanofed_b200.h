@@ -426,12 +426,25 @@ int nfb_rn_wm_convert(const void* table, int n_layers, long long total_cols, flo
                       long long row_stride, float* wm, void* wt, long long t_stride, int clients,
                       int to_slots, void* stream);
 /* ranges: n_ranges x {t_off, len} (int64, device, len % 4 == 0).                              */
+/* Client-side DP-SGD inside the ResNet engine's update kernels (NULL or row_sumsq == NULL: plain
+ * SGD): g' = g * min(1, clip_norm / (||g_client|| + 1e-6)) + noise_std * z.  row_sumsq [clients of
+ * the launch] is the squared norm of the client's WHOLE gradient; the Philox stream position is
+ * ((*step_base + step) * clients_total + client0 + g) * row_groups + (idx_base + index) / 4.   */
+typedef struct {
+  const float* row_sumsq;
+  float clip_norm, noise_std;
+  unsigned long long seed;
+  const unsigned long long* step_base;
+  int step, client0, clients_total;
+  long long row_groups, idx_base;
+} nfb_rn_dp;
 int nfb_rn_tap_sgd(const void* ranges, int n_ranges, long long max_len, float* wm, float* dwt,
                    float* momentum, void* wt, long long t_stride, int clients, float lr, float mu,
-                   float wd, void* stream);
+                   float wd, const nfb_rn_dp* dp, void* stream);
 int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long row_stride,
                      float* momentum, float* sgrad, long long sgrad_stride, int clients, float lr,
-                     float mu, float wd, float* zero_ptr, long long zero_len, void* stream);
+                     float mu, float wd, float* zero_ptr, long long zero_len, const nfb_rn_dp* dp,
+                     void* stream);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,7 @@ from typing import Any
 
 import torch
 
+from nanofed_b200 import ops
 from nanofed_b200.ops import native, rn, tc
 
 AVAILABLE = True
@@ -85,6 +86,7 @@ class _Rows:
 
     def __init__(self, arena: Any, lo: int, hi: int) -> None:
         self.device, self.layout, self.num_clients = arena.device, arena.layout, hi - lo
+        self.client0 = lo
         self.slots, self.stats = arena.slots[lo:hi], arena.stats[lo:hi]
         self.momentum = None if arena.momentum is None else arena.momentum[lo:hi]
 
@@ -97,7 +99,8 @@ class _ShardRows:
 class _Lane:
     """Lock-step local training of ``arena.num_clients`` ResNet-18s on the current stream."""
 
-    def __init__(self, cfg: Any, arena: Any, shards: Any) -> None:
+    def __init__(self, cfg: Any, arena: Any, shards: Any, client_base: int = 0,
+                 clients_total: int | None = None) -> None:
         assert arena.device.type == "cuda", "ResNetCohortNet needs a CUDA device"
         self.cfg, self.arena, self.shards = cfg, arena, shards
         self.device = dev = arena.device
@@ -192,7 +195,19 @@ class _Lane:
         self.sms = torch.cuda.get_device_properties(dev).multi_processor_count
         # which convolutions get their SGD step inside the wgrad epilogue (complete gradient in one
         # CTA, momentum-free); the others go through dwt + tap_sgd
-        self.fuse_sgd = cfg.momentum == 0.0 and os.environ.get("NFB_RN_NO_FUSED_SGD") is None
+        # client-side DP-SGD (CohortConfig.local_privacy; reference nanofed/trainer/private.py:54-86):
+        # the clip factor needs the norm of the COMPLETE gradient, so no update rides in a wgrad
+        # epilogue; K-STATS over the two gradient buffers, clip + Philox noise inside tap_sgd /
+        # small_sgd.  dp_steps counts the local steps of earlier rounds (advanced once per round,
+        # outside the graph) so a replayed graph keeps drawing fresh noise.
+        self.local_dp = getattr(cfg, "local_privacy", None)
+        seed = getattr(cfg, "dp_seed", None)
+        self.dp_seed = int(seed) if seed is not None else int.from_bytes(os.urandom(8), "little") >> 1
+        self.dp_steps = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.dp_client0 = int(getattr(arena, "client0", 0)) + int(client_base)
+        self.dp_clients_total = int(clients_total) if clients_total else self.dp_client0 + g
+        self.fuse_sgd = (cfg.momentum == 0.0 and self.local_dp is None
+                         and os.environ.get("NFB_RN_NO_FUSED_SGD") is None)
         self._ksplit = {c.name: self._pick_ksplit(c) for c in self.convs}
         ranges = [(c.t_off, c.taps * c.cout * c.cin) for c in self.convs
                   if not (self.fuse_sgd and self._ksplit[c.name] == 1)]
@@ -325,6 +340,8 @@ class _Lane:
                       self.wt, to_slots=False)
         if self.mom is not None:
             self.mom.zero_()             # fresh optimizer per round, like K-BCAST does for the arena
+        if self.local_dp is not None:
+            self.dp_steps += self.cfg.local_steps      # new noise for this round's replay
 
     def before_aggregate(self) -> None:
         """Trained conv weights back into the client rows (torch layout) that K-AGG reads."""
@@ -405,11 +422,21 @@ class _Lane:
         self._norm_bwd(self.stem_bn, dout, self.raw0, dc0, have_sums=have_sums)
         self._wgrad(self.stem, self.xcol, dc0)
         # ---------------- update ----------------
+        dp = None
+        if self.local_dp is not None:
+            ss = ops.update_stats(self.dwt)[0] + ops.update_stats(self.sgrad)[0]
+            c_norm = float(self.local_dp.max_gradient_norm)
+            dp = dict(sumsq=ss, clip_norm=c_norm,
+                      noise_std=float(self.local_dp.noise_multiplier) * c_norm, seed=self.dp_seed,
+                      step_base=self.dp_steps, step=step, client0=self.dp_client0,
+                      clients_total=self.dp_clients_total,
+                      row_groups=(self.t_stride + self.sgrad.shape[1] + 3) // 4)
         if self.tap_max:
             rn.tap_sgd(self.tap_ranges, self.tap_max, self.wm, self.dwt, self.mom, self.wt,
-                       lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay)
+                       lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay, dp=dp)
         rn.small_sgd(self.small_table, self.n_small, slots, a.momentum, self.sgrad,
-                     lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay, zero=self.stats)
+                     lr=cfg.learning_rate, mu=cfg.momentum, wd=cfg.weight_decay, zero=self.stats,
+                     dp=dp, dp_idx_base=self.t_stride)
 
 
 
@@ -427,16 +454,21 @@ class ResNetCohortNet:
     block can run next to it: the lanes only alternate, and every half-size launch pays its own
     prologue and its own last wave."""
 
-    def __init__(self, cfg: Any, arena: Any, shards: Any) -> None:
+    def __init__(self, cfg: Any, arena: Any, shards: Any, client_base: int = 0,
+                 clients_total: int | None = None) -> None:
+        """``client_base`` / ``clients_total``: position of this GPU's clients in the whole job
+        (distinct DP noise streams per client across ranks that share a seed)."""
         self.cfg, self.arena, self.shards = cfg, arena, shards
         self.device = arena.device
         g = arena.num_clients
+        clients_total = clients_total or client_base + g
         n = max(1, int(os.environ.get("NFB_RN_STREAMS", "1")))
         while g % n:
             n -= 1
         per = g // n
         self.lanes = [_Lane(cfg, _Rows(arena, k * per, (k + 1) * per),
-                            _ShardRows(shards, k * per, (k + 1) * per)) for k in range(n)]
+                            _ShardRows(shards, k * per, (k + 1) * per), client_base,
+                            clients_total) for k in range(n)]
         self.streams = [torch.cuda.Stream(device=self.device) for _ in self.lanes[1:]]
         self._graph: "torch.cuda.CUDAGraph | None" = None
         self.launches_per_round = 0

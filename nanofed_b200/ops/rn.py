@@ -20,6 +20,13 @@ from . import native
 from .tc import status_word
 
 
+class _Dp(C.Structure):
+    _fields_ = [("row_sumsq", C.c_void_p), ("clip_norm", C.c_float), ("noise_std", C.c_float),
+                ("seed", C.c_ulonglong), ("step_base", C.c_void_p), ("step", C.c_int),
+                ("client0", C.c_int), ("clients_total", C.c_int), ("row_groups", C.c_longlong),
+                ("idx_base", C.c_longlong)]
+
+
 class _Act(C.Structure):
     _fields_ = [("ptr", C.c_void_p), ("imgs", C.c_int), ("H", C.c_int), ("W", C.c_int),
                 ("C", C.c_int), ("parity", C.c_int)]
@@ -49,8 +56,9 @@ def _lib() -> C.CDLL:
                               i32, i32, i32, i32, f32, vp],
             "nfb_rn_head": [vp, i32, i32, i32, vp, ll, vp, ll, ll, ll, vp, ll, ll, ll, vp, vp, vp],
             "nfb_rn_wm_convert": [vp, i32, ll, vp, ll, vp, vp, ll, i32, i32, vp],
-            "nfb_rn_tap_sgd": [vp, i32, ll, vp, vp, vp, vp, ll, i32, f32, f32, f32, vp],
-            "nfb_rn_small_sgd": [vp, i32, vp, ll, vp, vp, ll, i32, f32, f32, f32, vp, ll, vp],
+            "nfb_rn_tap_sgd": [vp, i32, ll, vp, vp, vp, vp, ll, i32, f32, f32, f32, C.POINTER(_Dp), vp],
+            "nfb_rn_small_sgd": [vp, i32, vp, ll, vp, vp, ll, i32, f32, f32, f32, vp, ll,
+                                 C.POINTER(_Dp), vp],
         }
         for name, args in sigs.items():
             fn = getattr(lib, name)
@@ -315,16 +323,29 @@ def wm_convert(table: torch.Tensor, n_layers: int, total_cols: int, slots, wm, w
         "rn_wm_convert")
 
 
+def _dp(dp: dict | None, idx_base: int) -> "C.pointer | None":
+    """``dp``: sumsq [clients] fp32, clip_norm, noise_std, seed, step_base (int64 device counter),
+    step, client0, clients_total, row_groups - client-side DP-SGD inside the update kernels."""
+    if dp is None:
+        return None
+    return C.byref(_Dp(dp["sumsq"].data_ptr(), float(dp["clip_norm"]), float(dp["noise_std"]),
+                       int(dp["seed"]), dp["step_base"].data_ptr(), int(dp["step"]),
+                       int(dp["client0"]), int(dp["clients_total"]), int(dp["row_groups"]),
+                       int(idx_base)))
+
+
 def tap_sgd(ranges: torch.Tensor, max_len: int, wm, dwt, momentum, wt, *, lr: float, mu: float,
-            wd: float) -> None:
+            wd: float, dp: dict | None = None) -> None:
     _check(_lib().nfb_rn_tap_sgd(
         ranges.data_ptr(), ranges.shape[0], max_len, wm.data_ptr(), dwt.data_ptr(), _ptr(momentum),
-        wt.data_ptr(), wt.stride(0), wm.shape[0], lr, mu, wd, _stream(wm)), "rn_tap_sgd")
+        wt.data_ptr(), wt.stride(0), wm.shape[0], lr, mu, wd, _dp(dp, 0), _stream(wm)),
+        "rn_tap_sgd")
 
 
 def small_sgd(table: torch.Tensor, n_entries: int, slots, momentum, sgrad, *, lr: float, mu: float,
-              wd: float, zero: torch.Tensor | None = None) -> None:
+              wd: float, zero: torch.Tensor | None = None, dp: dict | None = None,
+              dp_idx_base: int = 0) -> None:
     _check(_lib().nfb_rn_small_sgd(
         table.data_ptr(), n_entries, slots.data_ptr(), slots.stride(0), _ptr(momentum),
         sgrad.data_ptr(), sgrad.stride(0), slots.shape[0], lr, mu, wd, _ptr(zero),
-        0 if zero is None else zero.numel(), _stream(slots)), "rn_small_sgd")
+        0 if zero is None else zero.numel(), _dp(dp, dp_idx_base), _stream(slots)), "rn_small_sgd")

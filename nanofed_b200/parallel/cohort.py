@@ -426,8 +426,6 @@ class FedSimulation:
             engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18", "resnet18_gn")
                                    and self.device.type == "cuda"
                                    and _grouped_available()) else "autograd"
-            if cfg.local_privacy is not None and cfg.model.startswith("resnet18"):
-                engine = "autograd"      # client-side DP-SGD: MNIST grouped engine and autograd
         if cfg.compute_dtype not in ("bf16", "fp32"):
             raise ValueError(f"compute_dtype must be 'bf16' or 'fp32', got {cfg.compute_dtype!r}")
         if cfg.compute_dtype == "fp32":
@@ -438,9 +436,6 @@ class FedSimulation:
                 raise ValueError("engine='grouped' computes in bf16 (fp32 accumulate/master); use "
                                  "compute_dtype='bf16', or engine='autograd' for fp32 compute")
             engine = "autograd"
-        if engine == "grouped" and cfg.model.startswith("resnet18") and cfg.local_privacy is not None:
-            raise ValueError("client-side DP-SGD (local_privacy) is implemented in the MNIST grouped "
-                             "engine and the autograd engine, not in the ResNet grouped engine")
         if engine == "grouped" and cfg.model not in ("mnist_cnn", "resnet18", "resnet18_gn"):
             raise ValueError(f"engine='grouped' has no hand-written network for {cfg.model!r} "
                              "(available: mnist_cnn, resnet18, resnet18_gn); use engine='autograd'")
@@ -468,7 +463,9 @@ class FedSimulation:
         if engine == "grouped" and cfg.model.startswith("resnet18"):
             from nanofed_b200.models.resnet_cohort import ResNetCohortNet
 
-            self.engine: Any = ResNetCohortNet(cfg, self.arena, self.shards)
+            self.engine: Any = ResNetCohortNet(
+                cfg, self.arena, self.shards, client_base=self.rank.rank * c,
+                clients_total=c * self.rank.world_size)
         elif engine == "grouped":
             from nanofed_b200.models.mnist_cohort import MnistCohortNet
 

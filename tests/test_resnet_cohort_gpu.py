@@ -345,3 +345,79 @@ def test_group_norm_model_trains_on_the_grouped_engine():
     tc.check_status(sim.device)
     assert all(l == l for l in losses) and losses[-1] < losses[0], losses
     ResNet18(norm="group").load_state_dict(sim.global_state())
+
+
+def _dp_sim(sigma, clip, **kw):
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+    from nanofed_b200.privacy import PrivacyConfig
+
+    cfg = CohortConfig(model="resnet18_gn", clients_per_gpu=2, samples_per_client=32, batch_size=16,
+                       learning_rate=0.1, device="cuda", dp_seed=1234,
+                       local_privacy=PrivacyConfig(epsilon=8.0, delta=1e-5, max_gradient_norm=clip,
+                                                   noise_multiplier=sigma), **kw)
+    return FedSimulation(cfg)
+
+
+def _param_delta(sim, before, k):
+    """Update of client k's trainable parameters, flattened (buffers excluded)."""
+    after = sim.layout.unflatten(sim.arena.slots[k].clone())
+    names = [n for n, _ in sim.template.named_parameters()]
+    return {n: after[n].float() - before[n].float().cuda() for n in names}
+
+
+def test_client_side_dp_sgd_in_the_resnet_engine_clips_and_adds_noise():
+    """``local_privacy`` on the grouped ResNet engine (reference recipe
+    ``nanofed/trainer/private.py:54-86``): with sigma ~ 0 one step moves the parameters by exactly
+    lr * C in total norm (the batch gradient is far larger than C); with sigma > 0 every parameter
+    receives N(0, (sigma C)^2) noise, different per client and per step."""
+    from nanofed_b200 import ops
+
+    lr, clip = 0.1, 0.05
+    sim = _dp_sim(1e-6, clip, use_cuda_graph=False)   # sigma must be > 0; 1e-6 adds nothing visible
+    assert sim.engine_name == "grouped" and sim.engine.lanes[0].local_dp is not None
+    a = sim.arena
+    ops.bcast_global(a.master, a.slots, a.slots_lowp, a.momentum)
+    sim.engine.after_broadcast()
+    before = sim.layout.unflatten(a.slots[0].clone())
+    sim.engine.step(0)
+    sim.engine.before_aggregate()
+    torch.cuda.synchronize()
+    for k in range(2):
+        d = _param_delta(sim, before, k)
+        total = float(torch.sqrt(sum((v * v).sum() for v in d.values())))
+        assert abs(total - lr * clip) < 2e-3 * lr * clip, (k, total, lr * clip)
+
+    sigma = 2.0
+    sim = _dp_sim(sigma, clip, use_cuda_graph=False)
+    a = sim.arena
+    ops.bcast_global(a.master, a.slots, a.slots_lowp, a.momentum)
+    sim.engine.after_broadcast()
+    before = sim.layout.unflatten(a.slots[0].clone())
+    sim.engine.step(0)
+    sim.engine.before_aggregate()
+    torch.cuda.synchronize()
+    d0, d1 = _param_delta(sim, before, 0), _param_delta(sim, before, 1)
+    for name in ("layer4.1.conv2.weight", "layer1.0.conv1.weight", "fc.weight", "bn1.weight"):
+        z0, z1 = d0[name].flatten() / (lr * sigma * clip), d1[name].flatten() / (lr * sigma * clip)
+        n = z0.numel()
+        tol = 5.0 / n ** 0.5
+        assert abs(float(z0.std()) - 1.0) < max(tol, 0.01), (name, float(z0.std()))
+        assert abs(float(z0.mean())) < tol + 0.02, (name, float(z0.mean()))
+        # different clients draw different noise
+        corr = float((z0 * z1).mean())
+        assert abs(corr) < tol + 0.02, (name, corr)
+
+
+def test_client_side_dp_sgd_noise_advances_inside_a_replayed_graph():
+    """Two rounds through the CUDA graph: the second replay must not repeat the first one's noise
+    (the step counter lives on the device and moves once per round)."""
+    sim = _dp_sim(1.0, 0.05)
+    m0 = sim.arena.master.clone()
+    sim.run_round()
+    m1 = sim.arena.master.clone()
+    sim.arena.master.copy_(m0)          # same starting model: only the noise stream differs
+    sim._slots_fresh = False
+    sim.run_round()
+    m2 = sim.arena.master.clone()
+    moved = float((m1 - m0).norm())
+    assert moved > 0 and float((m2 - m1).norm()) > 0.5 * moved, (float((m2 - m1).norm()), moved)
