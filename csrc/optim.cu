@@ -29,12 +29,23 @@ struct SgdArgs {
   float clip_norm;
   const uint8_t* noise_mask;
   const unsigned long long* step_ctr;
+  // K-STATS side output (optional, [rows]): += sum of the squares of the UPDATED parameters of each
+  // row, over the columns this launch touches - with the matching output of the fused weight-
+  // gradient kernel for the skipped range this is the per-client sum(x^2) that central DP clips by,
+  // so the last local step makes the separate pass over the client rows unnecessary.
+  float* sumsq_out;
 };
 
 template <typename G>
 __global__ void __launch_bounds__(256)
     sgd_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ mom,
                __nv_bfloat16* __restrict__ lowp, int64_t n, SgdArgs a) {
+  __shared__ float s_rowsq[256];       // per-row partial sums of this block (rows <= 256)
+  const int64_t n_rows = a.sumsq_out ? n / a.row_len : 0;
+  if (a.sumsq_out) {
+    s_rowsq[threadIdx.x] = 0.f;
+    __syncthreads();
+  }
   const float gs0 = a.grad_scale ? *a.grad_scale : 1.f;
   const uint64_t group0 = a.group0 + (a.step_ctr ? *a.step_ctr * static_cast<uint64_t>((n + 3) >> 2) : 0ull);
   // with a skipped column range the thread index runs over the remaining columns only
@@ -53,7 +64,7 @@ __global__ void __launch_bounds__(256)
     // row / column of this group for the per-row clip factor and the noise mask: 32-bit division
     // where the buffer allows it (a 64-bit divide per group cost 10 us of a 124 us pass)
     int64_t dp_row = 0, dp_col = 0;
-    if (a.row_sumsq || a.noise_mask) {
+    if (a.row_sumsq || a.noise_mask || a.sumsq_out) {
       if (n < (1ll << 31)) {
         const uint32_t b32 = static_cast<uint32_t>(base), rl = static_cast<uint32_t>(a.row_len);
         const uint32_t r32 = b32 / rl;
@@ -129,6 +140,12 @@ __global__ void __launch_bounds__(256)
     if (lowp) {
       for (int e = 0; e < cnt; ++e) lowp[base + e] = __float2bfloat16_rn(pv[e]);
     }
+    if (a.sumsq_out) {                     // row_len % 4 == 0: a group never straddles two rows
+      float t = 0.f;
+      for (int e = 0; e < cnt; ++e) t = fmaf(pv[e], pv[e], t);
+      if (n_rows <= 256) atomicAdd(&s_rowsq[dp_row], t);
+      else atomicAdd(a.sumsq_out + dp_row, t);
+    }
     if (a.perm_out) {
       const int64_t row = base / a.row_len;
       const int64_t col0 = base - row * a.row_len;
@@ -144,6 +161,11 @@ __global__ void __launch_bounds__(256)
         }
       }
     }
+  }
+  if (a.sumsq_out && n_rows <= 256) {
+    __syncthreads();
+    if (threadIdx.x < n_rows && s_rowsq[threadIdx.x] != 0.f)
+      atomicAdd(a.sumsq_out + threadIdx.x, s_rowsq[threadIdx.x]);
   }
 }
 
@@ -197,9 +219,12 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
                           int64_t perm_rows = 0, int perm_inner = 0, int perm_taps = 0,
                           const float* row_sumsq = nullptr, float clip_norm = 0.f,
                           const uint8_t* noise_mask = nullptr,
-                          const unsigned long long* step_ctr = nullptr) {
+                          const unsigned long long* step_ctr = nullptr,
+                          float* sumsq_out = nullptr) {
   using namespace nfb;
   NFB_REQUIRE(p && g, NFB_EINVAL, "fused_sgd: null pointer");
+  NFB_REQUIRE(!sumsq_out || (row_len > 0 && n % row_len == 0 && (row_len & 3) == 0), NFB_EINVAL,
+              "fused_sgd: the sum-of-squares output needs rows of a multiple of 4 elements");
   NFB_REQUIRE(aligned16(p), NFB_EINVAL, "fused_sgd: parameters must be 16-byte aligned");
   NFB_REQUIRE((offset & 3u) == 0, NFB_EINVAL, "fused_sgd: offset must be a multiple of 4");
   if (n <= 0) return 0;
@@ -222,7 +247,7 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
             grad_scale, seed, offset >> 2, row_len > 0 ? row_len : n, zero_prefix, skip_lo,
             skip_len, zero_from, static_cast<__nv_bfloat16*>(perm_out), perm_gs, perm_lo,
             perm_out ? perm_len : 0, perm_inner, perm_taps, row_sumsq, clip_norm, noise_mask,
-            step_ctr};
+            step_ctr, sumsq_out};
   NFB_REQUIRE(!(row_sumsq || noise_mask) || (row_len > 0 && n % row_len == 0), NFB_EINVAL,
               "fused_sgd: per-row clipping / noise mask need row_len");
   float* mom = (momentum != 0.f) ? momentum_buf : nullptr;
@@ -285,7 +310,9 @@ extern "C" int nfb_fused_sgd_perm(float* p, void* g, int g_dtype, float* momentu
 // DP-SGD for a cohort in one launch: every row (client) is clipped to clip_norm by its own gradient
 // norm (row_sumsq from K-STATS) and gets Gaussian noise of std noise_std on the entries noise_mask
 // marks; step_ctr (device counter, may be null) makes the noise stream advance inside a replayed
-// graph.  perm_out may be null.  Other arguments as nfb_fused_sgd_perm.
+// graph.  perm_out may be null.  sumsq_out (optional, [rows]): += sum of the squares of the updated
+// parameters per row.  With row_sumsq == NULL, noise_std == 0 this is plain SGD with that side
+// output.  Other arguments as nfb_fused_sgd_perm.
 extern "C" int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_buf,
                                 void* lowp_out, int64_t n, float lr, float momentum,
                                 float dampening, float weight_decay, int nesterov, int first_step,
@@ -295,13 +322,13 @@ extern "C" int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_
                                 float clip_norm, const uint8_t* noise_mask,
                                 const unsigned long long* step_ctr, void* perm_out,
                                 int64_t perm_group_stride, int64_t perm_lo, int64_t perm_rows,
-                                int perm_inner, int perm_taps, void* stream) {
+                                int perm_inner, int perm_taps, float* sumsq_out, void* stream) {
   return fused_sgd_impl(p, g, g_dtype, momentum_buf, lowp_out, n, lr, momentum, dampening,
                         weight_decay, nesterov, first_step, nullptr, noise_std, seed, offset,
                         row_len, zero_prefix, skip_lo, skip_hi, zero_from, stream, perm_out,
                         perm_group_stride,
                         perm_lo, perm_rows, perm_inner, perm_taps, row_sumsq, clip_norm, noise_mask,
-                        step_ctr);
+                        step_ctr, sumsq_out);
 }
 
 extern "C" int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg,

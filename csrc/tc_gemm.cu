@@ -62,6 +62,9 @@ struct GemmArgs {
   unsigned long long dp_seed, dp_group0, dp_groups_total;
   const unsigned long long* dp_step;
   long long dp_row_len, dp_w_off;
+  // EPI == 1: optional [groups] accumulator of sum(w_new^2) over this weight (K-STATS side output:
+  // central DP needs every client's squared update norm, and this weight never passes through K-OPT)
+  float* sumsq_out;
   int* status;       // set to 1 if a pipeline wait timed out
 };
 
@@ -276,6 +279,7 @@ __global__ void __launch_bounds__(256, MINB)
           args.dp_group0 + (args.dp_step ? *args.dp_step * args.dp_groups_total : 0ull);
       const long long dp_row0 = static_cast<long long>(g) * args.dp_row_len + args.dp_w_off +
                                 static_cast<long long>(m) * args.n_valid + n0;
+      float wsq = 0.f;
 #pragma unroll 1
       for (int c = 0; c < sgd_chunks; ++c) {
         const int buf = c & 1;
@@ -305,6 +309,7 @@ __global__ void __launch_bounds__(256, MINB)
           for (int e = 0; e < 4; ++e) {
             const float gr = fmaf(wd, w4[e], fmaf(cs, __uint_as_float(r[4 * p + e]), zn[e]));
             nw[4 * p + e] = fmaf(-lr, gr, w4[e]);
+            wsq = fmaf(nw[4 * p + e], nw[4 * p + e], wsq);
           }
           st_vec(addr, pack<float>(nw + 4 * p));
         }
@@ -332,6 +337,11 @@ __global__ void __launch_bounds__(256, MINB)
             tma_load_3d(wbuf, &map_o, &w_bar[sub * 2 + buf], n0 + (c + 2) * 32, m0 + sub * 32, g);
           }
         }
+      }
+      if (args.sumsq_out) {   // rows / columns past the weight's edge hold zeros (TMA fill)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wsq += __shfl_xor_sync(0xffffffffu, wsq, o);
+        if (lane == 0 && live) atomicAdd(args.sumsq_out + g, wsq);
       }
       if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     } else if (args.tma_store) {
@@ -686,13 +696,14 @@ int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, i
 
 // fc weight gradient fused with the optimizer step (momentum-free SGD):
 //   w[g][j][i] <- w - lr * (sum_b dy[g][b][j] * x[g][b][i] + wd * w),  w_lowp <- bf16(w)
+// sumsq_out (optional, [groups]): += sum of the squares of the NEW weights of each group.
 // A = dy [groups][batch][j] and B = x [groups][batch][i] (both MN-major), w fp32 rows of length i
 // `w_gs` / `lowp_gs` elements apart per group.  The gradient is never written.  The caller must
 // have finished every read of the OLD weights (e.g. the data gradient) on this stream.
 int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* A, const nfb_tc_operand* B, int groups, int j,
                             int i, int inner, float* w, long long w_gs, void* w_lowp,
-                            long long lowp_gs, float lr, float weight_decay, int* status,
-                            void* stream) {
+                            long long lowp_gs, float lr, float weight_decay, float* sumsq_out,
+                            int* status, void* stream) {
   using namespace nfb;
   using namespace nfb::tc;
   NFB_REQUIRE(A && B && w && w_lowp && status, NFB_EINVAL, "linear_wgrad_sgd: null pointer");
@@ -708,6 +719,7 @@ int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* A, const nfb_tc_operand* B, in
   g.m_valid = j; g.n_valid = i;
   g.vec_store = 1;
   g.sgd_lr = lr; g.sgd_wd = weight_decay;
+  g.sumsq_out = sumsq_out;
   g.status = status;
   Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
   Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};

@@ -178,7 +178,7 @@ int nfb_fused_sgd_dp(float* p, void* g, int g_dtype, float* momentum_buf, void* 
                      int64_t zero_from, const float* row_sumsq, float clip_norm, const uint8_t* noise_mask,
                      const unsigned long long* step_ctr, void* perm_out, int64_t perm_group_stride,
                      int64_t perm_lo, int64_t perm_rows, int perm_inner, int perm_taps,
-                     void* stream);
+                     float* sumsq_out, void* stream);
 int nfb_fused_adam(float* p, const void* g, int g_dtype, float* exp_avg, float* exp_avg_sq,
                    void* lowp_out, int64_t n, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float bias_corr1, float bias_corr2, int decoupled,
@@ -264,8 +264,8 @@ int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, i
  * gradient is applied in the GEMM epilogue and never written.                              */
 int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* dy, const nfb_tc_operand* x, int groups, int j,
                             int i, int inner, float* w, long long w_gs, void* w_lowp,
-                            long long lowp_gs, float lr, float weight_decay, int* status,
-                            void* stream);
+                            long long lowp_gs, float lr, float weight_decay, float* sumsq_out,
+                            int* status, void* stream);
 /* out[g][b,i] = scale * sum_j dy[g][b,j] * w[g][j,i]  (persistent; j = 128, b <= 128).      */
 /* K-PSGN on tensor cores: out[i] += ||sum_p dy[i][p][:]^T u[i][p][:]||_F^2 per sample (group) i;
  * dy [samples][P][cout], u [samples][P][kdim] bf16 (unfolded patches, optionally with a ones

@@ -135,6 +135,14 @@ class MnistCohortNet:
         # Kept behind NFB_FUSED_DP=1 with its test; the default is the materialised path.
         self.fuse_fc1_dp = (self.local_dp is not None and cfg.momentum == 0.0 and self.group == c_all
                             and os.environ.get("NFB_FUSED_DP") == "1")
+        # Central DP clips every client's update by its L2 norm.  The last local step's update
+        # kernels (K-OPT and the fused fc1 update) leave each client's sum of squared parameters in
+        # arena.sumsq, so the round runs no K-STATS pass over the client rows.
+        # Not with non-finite screening (needs the scan anyway) nor with NFB_FUSED_DP's epilogue.
+        self.emits_sumsq = (getattr(cfg, "privacy", None) is not None
+                            and not getattr(cfg, "screen_nonfinite", False)
+                            and not self.fuse_fc1_dp
+                            and os.environ.get("NFB_NO_SUMSQ_SIDE_OUTPUT") is None)
         self.gram = torch.zeros(c_all, b, b, dtype=torch.float32, device=dev) if self.fuse_fc1_dp else None
         self.conv2_g = self.grads[:, self.off["conv2.weight"] :]
         # atomic-accumulated gradient entries (conv1.*, conv2.*) sit in front of fc1.weight
@@ -158,17 +166,25 @@ class MnistCohortNet:
         native._check(code, what)
         native._count()
 
-    def step(self, step: int) -> None:
+    def step(self, step: int, last: bool = False) -> None:
+        """``last``: the final step of the local epoch - with central DP configured its update
+        kernels also leave every client's sum of squared parameters in ``arena.sumsq`` (K-STATS
+        folded into K-OPT and the fused fc1 update), so the round needs no extra pass over the rows."""
         cfg, a = self.cfg, self.arena
+        emit = last and self.emits_sumsq
+        if emit:
+            a.sumsq.zero_()
         for g0 in range(0, self.c_all, self.group):
-            self._step_group(step, g0)
-        self._apply_optimizer(step)
+            self._step_group(step, g0, emit)
+        self._apply_optimizer(step, emit)
 
-    def _apply_optimizer(self, step: int) -> None:
+    def _apply_optimizer(self, step: int, emit_sumsq: bool = False) -> None:
         """One fused K-OPT launch over all clients; also hands the atomically accumulated
         gradient entries (conv1.*, conv2.*) back zeroed for the next step."""
         cfg, a = self.cfg, self.arena
         dp_kw: dict[str, Any] = {}
+        if emit_sumsq:
+            dp_kw["sumsq_out"] = a.sumsq
         skip = self._fc1_range if self.fuse_fc1_sgd else None
         if self.local_dp is not None:
             if self.fuse_fc1_dp:
@@ -187,7 +203,7 @@ class MnistCohortNet:
                 skip = self._fc1_range
             else:
                 ss, _ = ops.update_stats(self.grads)      # per-client squared gradient norm
-            dp_kw = dict(row_sumsq=ss, clip_norm=float(self.local_dp.max_gradient_norm),
+            dp_kw.update(row_sumsq=ss, clip_norm=float(self.local_dp.max_gradient_norm),
                          noise_std=float(self.local_dp.noise_multiplier
                                          * self.local_dp.max_gradient_norm),
                          noise_mask=a.noise_mask, seed=self.dp_seed,
@@ -203,7 +219,7 @@ class MnistCohortNet:
                        perm_out=(self.w2p.view(self.c_all, -1), self.off["conv2.weight"], 64, 32, 9)
                        if self.opt_writes_w2p else None)
 
-    def _step_group(self, step: int, g0: int) -> None:
+    def _step_group(self, step: int, g0: int, emit_sumsq: bool = False) -> None:
         cfg, a, lib = self.cfg, self.arena, self.lib
         c, b, n = self.c, self.b, self.n_total
         g1 = g0 + c
@@ -252,7 +268,8 @@ class MnistCohortNet:
             # epilogue (after the data gradient above has read the old weights) and never
             # written; K-OPT then skips that range
             tc.linear_wgrad_sgd(self.dh, self.p, self.fc1_master[g0:g1], self.fc1_w[g0:g1],
-                                cfg.learning_rate, cfg.weight_decay)
+                                cfg.learning_rate, cfg.weight_decay,
+                                sumsq_out=a.sumsq[g0:g1] if emit_sumsq else None)
         else:
             tc.linear_wgrad(self.dh, self.p, self.fc1_g[g0:g1], n)
         self._check(lib.nfb_mnist_pool_bwd(self.dp.data_ptr(), self.pidx.data_ptr(), c, b,
@@ -272,8 +289,9 @@ class MnistCohortNet:
                                                   off["conv1.bias"], st), "conv1_wgrad")
 
     def _all_steps(self) -> None:
-        for s in range(self.cfg.local_steps):
-            self.step(s)
+        n = self.cfg.local_steps
+        for s in range(n):
+            self.step(s, last=s == n - 1)
 
     def local_steps(self) -> None:
         if not self.cfg.use_cuda_graph:

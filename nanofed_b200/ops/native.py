@@ -130,7 +130,7 @@ def _declare(L: C.CDLL) -> None:
                                _i64, _i64, _i32, _i32, _vp],
         "nfb_fused_sgd_dp": [_vp, _vp, _i32, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _i32,
                              _f32, _u64, _u64, _i64, _i64, _i64, _i64, _i64, _vp, _f32, _vp, _vp,
-                             _vp, _i64, _i64, _i64, _i32, _i32, _vp],
+                             _vp, _i64, _i64, _i64, _i32, _i32, _vp, _vp],
         "nfb_batch_ghost_norm": [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
         "nfb_fused_adam": [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32,
                            _f32, _f32, _i32, _vp, _vp],
@@ -372,8 +372,11 @@ def fused_sgd_(
     clip_norm: float = 0.0,
     noise_mask: torch.Tensor | None = None,
     step_counter: torch.Tensor | None = None,
+    sumsq_out: torch.Tensor | None = None,
 ) -> torch.Tensor:
-    """``row_sumsq`` / ``clip_norm`` / ``noise_mask`` / ``step_counter``: DP-SGD for a cohort — row
+    """``sumsq_out`` (fp32 ``[rows]``, accumulated): K-STATS side output — Σ of the squares of the
+    updated parameters per row over the columns this call touches.
+    ``row_sumsq`` / ``clip_norm`` / ``noise_mask`` / ``step_counter``: DP-SGD for a cohort — row
     ``r`` of the ``[rows, row_len]`` buffers is clipped by ``min(1, clip_norm / sqrt(row_sumsq[r]))``
     and gets ``N(0, noise_std²)`` on the masked entries; ``step_counter`` (device int64) advances
     the noise stream inside a replayed CUDA graph."""
@@ -381,8 +384,11 @@ def fused_sgd_(
     assert p.numel() == g.numel()
     if momentum == 0.0:
         momentum_buf = None
-    if row_sumsq is not None or noise_mask is not None or step_counter is not None:
+    if (row_sumsq is not None or noise_mask is not None or step_counter is not None
+            or sumsq_out is not None):
         assert grad_scale is None and row_len > 0
+        if sumsq_out is not None:
+            assert sumsq_out.dtype == torch.float32 and sumsq_out.numel() == p.numel() // row_len
         lo, hi = skip_range if skip_range is not None else (0, 0)
         if noise_mask is not None:
             noise_mask = noise_mask.to(device=p.device, dtype=torch.uint8).contiguous()
@@ -396,7 +402,8 @@ def fused_sgd_(
             1 if nesterov else 0, 1 if first_step else 0, float(noise_std), seed & (2**64 - 1),
             offset, int(row_len), int(zero_grad_prefix), int(lo), int(hi), int(zero_grad_from),
             _ptr(row_sumsq),
-            float(clip_norm), _ptr(noise_mask), _ptr(step_counter), *pout, _stream(p)),
+            float(clip_norm), _ptr(noise_mask), _ptr(step_counter), *pout, _ptr(sumsq_out),
+            _stream(p)),
             "fused_sgd_dp")
         _count()
         return p

@@ -193,8 +193,12 @@ def fused_sgd_(
     clip_norm: float = 0.0,
     noise_mask: torch.Tensor | None = None,
     step_counter: torch.Tensor | None = None,
+    sumsq_out: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """torch.optim.SGD semantics on flat buffers, with optional DP-SGD pre-processing.
+
+    ``sumsq_out`` ``[rows]`` (accumulated): Σ of the squares of the updated parameters per row,
+    over the columns outside ``skip_range`` (K-STATS side output of the last local step).
 
     Cohort form: ``row_sumsq`` ``[rows]`` clips row ``r`` by ``min(1, clip_norm / (sqrt(ss_r) +
     1e-6))``, ``noise_mask`` ``[row_len]`` limits the noise to real parameter entries and
@@ -243,6 +247,11 @@ def fused_sgd_(
     if keep is not None:
         for t, saved in keep:
             t.view(-1, row_len)[:, skip_range[0]:skip_range[1]] = saved
+    if sumsq_out is not None:
+        sq = p.to(torch.float32).view(-1, row_len) ** 2
+        if skip_range is not None:
+            sq[:, skip_range[0]:skip_range[1]] = 0
+        sumsq_out.add_(sq.sum(1).to(sumsq_out.device))
     if perm_out is not None:
         # the parameter stored [rows][inner][taps] at columns lo.. is also written [rows][taps][inner]
         out_t, lo, rows, inner, taps = perm_out

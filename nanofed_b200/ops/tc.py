@@ -320,19 +320,21 @@ def linear_fwd(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, k_split: int
 
 
 def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp: torch.Tensor,
-                     lr: float, weight_decay: float = 0.0, dp: dict | None = None) -> None:
+                     lr: float, weight_decay: float = 0.0, dp: dict | None = None,
+                     sumsq_out: torch.Tensor | None = None) -> None:
     """``w[c, j, i] -= lr·(Σ_b dy[c, b, j]·x[c, b, i] + wd·w)`` and ``w_lowp = bf16(w)`` in ONE
     kernel: the weight gradient is consumed in the tcgen05 epilogue and never written.  ``w`` (fp32)
     and ``w_lowp`` (bf16) are ``[C, j, i]`` views with contiguous ``[j, i]`` blocks and arbitrary
     client strides (rows of the parameter arena).  Everything that reads the OLD weights in this
-    step (the data gradient) must already be enqueued."""
+    step (the data gradient) must already be enqueued.  ``sumsq_out`` (fp32 ``[C]``, accumulated):
+    Σ of the squares of the new weights per client (K-STATS side output)."""
     lib = _lib()
     if not getattr(lib, "_wgrad_sgd_declared", False):
         ll = C.c_longlong
         lib.nfb_tc_linear_wgrad_sgd.restype = C.c_int
         lib.nfb_tc_linear_wgrad_sgd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                                 C.c_int, C.c_void_p, ll, C.c_void_p, ll, C.c_float,
-                                                C.c_float, C.c_void_p, C.c_void_p]
+                                                C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         lib._wgrad_sgd_declared = True
     c, j, i = w.shape
     assert w.dtype == torch.float32 and w_lowp.dtype == torch.bfloat16 and w_lowp.shape == w.shape
@@ -365,6 +367,7 @@ def linear_wgrad_sgd(dy: torch.Tensor, x: torch.Tensor, w: torch.Tensor, w_lowp:
     code = lib.nfb_tc_linear_wgrad_sgd(C.byref(oa), C.byref(ob), c, j, i, (dy.shape[1] + 63) // 64,
                                        w.data_ptr(), w.stride(0), w_lowp.data_ptr(),
                                        w_lowp.stride(0), float(lr), float(weight_decay),
+                                       sumsq_out.data_ptr() if sumsq_out is not None else None,
                                        st.data_ptr(),
                                        torch.cuda.current_stream(dy.device).cuda_stream)
     native._check(code, "tc_linear_wgrad_sgd")

@@ -583,12 +583,17 @@ class FedSimulation:
         late = self._train_with_deadline()
         with self.timer.phase("aggregate"):
             self.engine.before_aggregate()
+            poisoned = bool(getattr(self, "_poison", []))
             for k in getattr(self, "_poison", []):
                 arena.slots[k, :16] = float("nan")
             self._poison = []
             dp = cfg.privacy
             kw: dict[str, Any] = {}
-            if dp is not None or cfg.screen_nonfinite:
+            # K-STATS: every client's sum of squares (DP clipping) and non-finite count.  The MNIST
+            # engine's last local step already left the sums in arena.sumsq (emits_sumsq).
+            side_output = (getattr(self.engine, "emits_sumsq", False) and not cfg.screen_nonfinite
+                           and not poisoned)
+            if (dp is not None and not side_output) or cfg.screen_nonfinite:
                 ss, bad = ops.update_stats(arena.slots)
                 arena.sumsq.copy_(ss)
                 arena.nonfinite.copy_(bad)

@@ -278,3 +278,38 @@ def test_dp_sgd_mode_of_the_grouped_engine_matches_the_oracle_update():
     # same noise stream, clip factors equal up to the summation order of the norm
     assert float((arena2.slots - arena.slots).abs().max()) < 2e-6
     assert torch.equal(arena2.slots_lowp, arena2.slots.bfloat16())
+
+
+
+def test_central_dp_round_takes_the_update_norms_from_the_last_local_step(monkeypatch):
+    """K-STATS folded into the last K-OPT step and the fused fc1 update: ``arena.sumsq`` after the
+    local epoch equals the sum of squares of the trained client rows, no ``update_stats`` launch is
+    part of the round, and the aggregated model equals the one of a round that runs K-STATS."""
+    from nanofed_b200 import ops
+    from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
+    from nanofed_b200.privacy import PrivacyConfig
+
+    def sim_of():
+        cfg = CohortConfig(model="mnist_cnn", clients_per_gpu=4, samples_per_client=128, batch_size=64,
+                           learning_rate=0.05, device="cuda", dp_seed=5, fuse_bcast=False,
+                           privacy=PrivacyConfig(epsilon=8.0, max_gradient_norm=10.0,
+                                                 noise_multiplier=0.5))
+        return FedSimulation(cfg)
+
+    calls = []
+    real = ops.update_stats
+    monkeypatch.setattr(ops, "update_stats", lambda x: (calls.append(1), real(x))[1])
+    sim = sim_of()
+    assert sim.engine.emits_sumsq
+    sim.engine.p1 = sim.engine.p2 = 0.0          # same dropout-free training in both runs
+    sim.run_round()
+    assert not calls                              # no separate pass over the client rows
+    rows = sim.arena.slots.double()
+    torch.testing.assert_close(sim.arena.sumsq.double(), (rows * rows).sum(1), rtol=1e-5, atol=0)
+    monkeypatch.setenv("NFB_NO_SUMSQ_SIDE_OUTPUT", "1")
+    ref_sim = sim_of()
+    assert not ref_sim.engine.emits_sumsq
+    ref_sim.engine.p1 = ref_sim.engine.p2 = 0.0
+    ref_sim.run_round()
+    assert calls
+    torch.testing.assert_close(sim.arena.master, ref_sim.arena.master, rtol=1e-3, atol=2e-4)

@@ -181,6 +181,24 @@ def test_fused_sgd_skips_a_column_range_and_zeroes_the_atomic_prefix():
     assert float((lowp.view(rows, row_len)[:, lo:hi] - 7.0).abs().max()) == 0.0   # untouched
 
 
+@pytest.mark.parametrize("rows", [5, 300])
+def test_fused_sgd_sum_of_squares_side_output(rows):
+    """K-STATS folded into K-OPT: per-row sum of the squared UPDATED parameters outside the skipped
+    range, accumulated into the output (shared-memory path up to 256 rows, direct atomics above)."""
+    row_len, lo, hi = 512, 128, 384
+    p = torch.randn(rows * row_len, device=DEV)
+    g = torch.randn(rows * row_len, device=DEV)
+    out = torch.full((rows,), 2.0, device=DEV)
+    pr, gr, outr = p.cpu().clone(), g.cpu().clone(), out.cpu().clone()
+    kw = dict(weight_decay=0.01, row_len=row_len, skip_range=(lo, hi))
+    ops.fused_sgd_(p, g, 0.1, sumsq_out=out, **kw)
+    ref.fused_sgd_(pr, gr, 0.1, sumsq_out=outr, **kw)
+    torch.testing.assert_close(p.cpu(), pr, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(out.cpu(), outr, rtol=1e-5, atol=1e-5)
+    want = 2.0 + (p.view(rows, row_len).double() ** 2).sum(1) - (p.view(rows, row_len)[:, lo:hi].double() ** 2).sum(1)
+    torch.testing.assert_close(out.double(), want, rtol=1e-5, atol=1e-5)
+
+
 def test_fused_sgd_permuted_side_output_matches_oracle():
     rows, row_len = 3, 64 * 32 * 9 + 256
     lo = 128

@@ -239,8 +239,11 @@ def check_fc_wgrad_sgd():
     w0 = w.clone()
     wv = w[:, 128:128 + j * i].unflatten(1, (j, i))
     lv = lowp[:, 128:128 + j * i].unflatten(1, (j, i))
-    tc.linear_wgrad_sgd(dy, x, wv, lv, lr, wd)
+    ssq = torch.full((c,), 3.0, device="cuda")           # accumulated, not overwritten
+    tc.linear_wgrad_sgd(dy, x, wv, lv, lr, wd, sumsq_out=ssq)
     torch.cuda.synchronize()
+    want_ssq = 3.0 + (wv.double() ** 2).sum((1, 2))
+    assert float(((ssq.double() - want_ssq) / want_ssq).abs().max()) < 1e-5, "sum-of-squares side output"
     old = w0[:, 128:128 + j * i].unflatten(1, (j, i))
     grad = torch.einsum("cbj,cbi->cji", dy.float(), x.float())
     want = old - lr * (grad + wd * old)
