@@ -1,6 +1,8 @@
 // Error plumbing and device queries shared by all entry points.
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace nfb {
 
 static thread_local char g_error[512];
@@ -23,6 +25,14 @@ int launch_status(const char* what) {
     return static_cast<int>(e);
   }
   return 0;
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("NFB_PDL");   // opt-in: measured slower than plain graph edges
+    return v && v[0] == '1';
+  }();
+  return on;
 }
 
 int sm_count() {

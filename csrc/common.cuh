@@ -27,6 +27,36 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
 
 int sm_count();
 
+// ---- programmatic dependent launch ------------------------------------------------------------
+// The kernels of a local step form one dependency chain inside a CUDA graph; between two of them
+// the GPU idles for the launch latency plus the next kernel's prologue (barrier init, TMEM
+// allocation, tensor-map fetch: ~3 us, 98 times per ResNet step).  With the attribute below a
+// kernel's CTAs may become resident while the previous kernel's last wave is still running; every
+// such kernel calls pdl_trigger() first thing (lets ITS successor do the same) and pdl_wait()
+// before its first access to global memory (returns when the predecessor grid has completed and
+// its writes are visible).  Both instructions are no-ops in a launch without the attribute.
+// MEASURED on the ResNet-18 step (98 kernels in one graph): 138.3 k client-samples/s with the
+// attribute, 141.9 k without - the graph's own kernel-to-kernel gaps are already shorter than what
+// the early-resident CTAs cost the predecessor's last wave.  Off unless NFB_PDL=1.
+__device__ __forceinline__ void pdl_trigger() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+bool pdl_enabled();   // NFB_PDL=1 switches it on
+
+template <typename... Params, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(Params...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<Params>(args)...);
+}
+
 // ---- dtype tags ---------------------------------------------------------------
 template <int DT> struct DType;
 template <> struct DType<NFB_DT_F32> { using type = float; };

@@ -170,6 +170,7 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
                         const __grid_constant__ CUtensorMap map_b1,
                         const __grid_constant__ CUtensorMap map_o,
                         const __grid_constant__ CUtensorMap map_x, const GemmArgs args) {
+  pdl_trigger();   // the next kernel of the stream may start its prologue
   using C = GemmCfg<B_MN, BN, HALVES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -214,6 +215,7 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();   // barriers, TMEM and tensor maps are ready: now wait for the producer of our inputs
 
   // k-iterations of one tile of class `cls`
   auto iters_of = [&](int cls) {
@@ -500,6 +502,7 @@ template <int BN, int POSK>
 __global__ void __launch_bounds__(256, 1)
     rn_conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_x,
                          const __grid_constant__ CUtensorMap map_dy, const WgradArgs args) {
+  pdl_trigger();   // the next kernel of the stream may start its prologue
   using C = WgradCfg<BN, POSK>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -534,6 +537,7 @@ __global__ void __launch_bounds__(256, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();   // barriers, TMEM and tensor maps are ready: now wait for the producer of our inputs
 
   if (warp == 0) {
     if (elect_one()) {
@@ -717,7 +721,7 @@ static int launch_gemm(const CUtensorMap* maps, const GemmArgs& args, dim3 grid,
                                       cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<grid, C::THREADS, C::SMEM, st>>>(maps[0], maps[1], maps[2], maps[3], maps[4], maps[5],
+  launch_pdl(kern, dim3(grid), dim3(C::THREADS), C::SMEM, st, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5],
                                           args);
   return launch_status("rn_conv_gemm");
 }
@@ -735,7 +739,7 @@ static int launch_wgrad(const CUtensorMap& mx, const CUtensorMap& mdy, const Wgr
                                       cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<grid, 256, C::SMEM, st>>>(mx, mdy, args);
+  launch_pdl(kern, dim3(grid), dim3(256), C::SMEM, st, mx, mdy, args);
   return launch_status("rn_conv_wgrad");
 }
 

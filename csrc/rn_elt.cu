@@ -42,6 +42,8 @@ __device__ __forceinline__ void bn_coeffs(const BnRef& bn, const float* row, int
 // ---- stem im2col ------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
     im2col3_kernel(const float* __restrict__ x, long long x_gs, int B, __nv_bfloat16* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   // one thread = one position x 8 patch entries; entry k = (kh*3 + kw)*3 + ci
   const int g = blockIdx.y;
   const long long total = static_cast<long long>(B) * 1024 * 8;
@@ -87,6 +89,8 @@ struct BnApplyArgs {
 
 template <bool RES, bool RES_BN>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const BnApplyArgs a) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const int g = blockIdx.y, C = a.C, octs = C >> 3;
   const int oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs, c0 = oct * 8;
   float* row = a.slots + g * a.row_stride;
@@ -185,6 +189,8 @@ __device__ __forceinline__ void relu_mask(uint4& d, const uint4& o) {
 
 template <bool TWO>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdArgs a) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   __shared__ float scratch[256 * 8];
   const int g = blockIdx.y, C = a.C, octs = C >> 3;
   const int oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs, c0 = oct * 8;
@@ -262,6 +268,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnBwdArgs a) {
 
 template <bool TWO>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const int g = blockIdx.y, C = a.C, octs = C >> 3;
   const int oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs, c0 = oct * 8;
   const float* row = a.slots + g * a.row_stride;
@@ -342,6 +350,8 @@ __global__ void __launch_bounds__(512)
                 long long w_off, long long b_off, float* __restrict__ sgrad, long long sgrad_stride,
                 long long dw_off, long long db_off, __nv_bfloat16* __restrict__ dfeat,
                 float* __restrict__ stats) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   constexpr int F = 512, SB = 8, NC = HEAD_NC;
   __shared__ float part[16][SB * NC];     // per-warp partial logits
   __shared__ float logit[SB * NC];
@@ -435,6 +445,8 @@ __global__ void __launch_bounds__(256)
     wm_convert_kernel(const ConvEntry* __restrict__ table, int n_layers, long long total_cols,
                       float* __restrict__ slots, long long row_stride, float* __restrict__ wm,
                       __nv_bfloat16* __restrict__ wt, long long t_stride, int dir) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const int g = blockIdx.y;
   float* row = slots + g * row_stride;
   float* mrow = wm + g * t_stride;
@@ -498,6 +510,8 @@ __global__ void __launch_bounds__(256)
     tap_sgd_kernel(const TapRange* __restrict__ ranges, float* __restrict__ wm,
                    float* __restrict__ dwt, float* __restrict__ mom, __nv_bfloat16* __restrict__ wt,
                    long long t_stride, float lr, float mu, float wd, const RnDp dp) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const TapRange rg = ranges[blockIdx.y];
   const long long base = blockIdx.z * t_stride + rg.t_off;
   const float gs = dp.row_sumsq ? rn_dp_scale(dp, blockIdx.z) : 1.f;
@@ -537,6 +551,8 @@ __global__ void __launch_bounds__(256)
                      long long row_stride, float* __restrict__ momentum, float* __restrict__ sgrad,
                      long long sgrad_stride, float lr, float mu, float wd,
                      float* __restrict__ zero_ptr, long long zero_len, const RnDp dp) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const SmallEntry e = table[blockIdx.x];
   const int g = blockIdx.y;
   const float gs = dp.row_sumsq ? rn_dp_scale(dp, g) : 1.f;
@@ -590,7 +606,7 @@ int nfb_rn_im2col3(const float* x, long long x_gs, int clients, int batch, void*
   using namespace nfb;
   NFB_REQUIRE(x && out && clients >= 1 && batch >= 1, NFB_EINVAL, "rn_im2col3: bad argument");
   dim3 grid(rn::blocks_for(static_cast<long long>(batch) * 8192, clients), clients);
-  rn::im2col3_kernel<<<grid, 256, 0, as_stream(stream)>>>(x, x_gs, batch,
+  launch_pdl(rn::im2col3_kernel, dim3(grid), dim3(256), 0, as_stream(stream), x, x_gs, batch,
                                                           static_cast<__nv_bfloat16*>(out));
   return launch_status("rn_im2col3");
 }
@@ -620,9 +636,9 @@ int nfb_rn_bn_apply(const void* x, const void* res, void* y, float* slots, long 
   NFB_REQUIRE(256 % (C / 8) == 0, NFB_EINVAL, "rn_bn_apply: C / 8 must divide 256");
   dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / rn::BN_U, clients), clients);
   cudaStream_t st = as_stream(stream);
-  if (!res) rn::bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(a);
-  else if (!res_stats) rn::bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(a);
-  else rn::bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(a);
+  if (!res) launch_pdl(rn::bn_apply_kernel<false, false>, dim3(grid), dim3(256), 0, st, a);
+  else if (!res_stats) launch_pdl(rn::bn_apply_kernel<true, false>, dim3(grid), dim3(256), 0, st, a);
+  else launch_pdl(rn::bn_apply_kernel<true, true>, dim3(grid), dim3(256), 0, st, a);
   return launch_status("rn_bn_apply");
 }
 
@@ -657,13 +673,13 @@ int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, c
   if (!apply) {
     // fewer, longer blocks: every block ends with C atomics per sum
     dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / (4 * rn::BN_U), clients), clients);
-    if (x2) rn::bn_bwd_reduce_kernel<true><<<grid, 256, 0, st>>>(a);
-    else rn::bn_bwd_reduce_kernel<false><<<grid, 256, 0, st>>>(a);
+    if (x2) launch_pdl(rn::bn_bwd_reduce_kernel<true>, dim3(grid), dim3(256), 0, st, a);
+    else launch_pdl(rn::bn_bwd_reduce_kernel<false>, dim3(grid), dim3(256), 0, st, a);
     return launch_status("rn_bn_bwd_reduce");
   }
   dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / rn::BN_U, clients), clients);
-  if (x2) rn::bn_bwd_apply_kernel<true><<<grid, 256, 0, st>>>(a);
-  else rn::bn_bwd_apply_kernel<false><<<grid, 256, 0, st>>>(a);
+  if (x2) launch_pdl(rn::bn_bwd_apply_kernel<true>, dim3(grid), dim3(256), 0, st, a);
+  else launch_pdl(rn::bn_bwd_apply_kernel<false>, dim3(grid), dim3(256), 0, st, a);
   return launch_status("rn_bn_bwd_apply");
 }
 
@@ -675,7 +691,7 @@ int nfb_rn_head(const void* feat, int clients, int batch, int positions, const i
   NFB_REQUIRE(feat && labels && slots && sgrad && dfeat && stats, NFB_EINVAL, "rn_head: null pointer");
   NFB_REQUIRE(batch % 8 == 0 && positions >= 1, NFB_EINVAL, "rn_head: batch must be a multiple of 8");
   dim3 grid(batch / 8, clients);
-  rn::head_kernel<<<grid, 512, 0, as_stream(stream)>>>(
+  launch_pdl(rn::head_kernel, dim3(grid), dim3(512), 0, as_stream(stream), 
       static_cast<const __nv_bfloat16*>(feat), batch, positions, labels, label_gs, slots, row_stride,
       w_off, b_off, sgrad, sgrad_stride, dw_off, db_off, static_cast<__nv_bfloat16*>(dfeat), stats);
   return launch_status("rn_head");
@@ -687,7 +703,7 @@ int nfb_rn_wm_convert(const void* table, int n_layers, long long total_cols, flo
   using namespace nfb;
   NFB_REQUIRE(table && slots && wm && wt && n_layers >= 1, NFB_EINVAL, "rn_wm_convert: null pointer");
   dim3 grid(rn::blocks_for(total_cols, clients), clients);
-  rn::wm_convert_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+  launch_pdl(rn::wm_convert_kernel, dim3(grid), dim3(256), 0, as_stream(stream), 
       static_cast<const rn::ConvEntry*>(table), n_layers, total_cols, slots, row_stride, wm,
       static_cast<__nv_bfloat16*>(wt), t_stride, to_slots);
   return launch_status("rn_wm_convert");
@@ -702,7 +718,7 @@ int nfb_rn_tap_sgd(const void* ranges, int n_ranges, long long max_len, float* w
   long long want = (max_len / 4 + 255) / 256;
   if (want > per) want = per;
   dim3 grid(static_cast<unsigned>(want < 1 ? 1 : want), n_ranges, clients);
-  rn::tap_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+  launch_pdl(rn::tap_sgd_kernel, dim3(grid), dim3(256), 0, as_stream(stream), 
       static_cast<const rn::TapRange*>(ranges), wm, dwt, momentum, static_cast<__nv_bfloat16*>(wt),
       t_stride, lr, mu, wd, rn::make_dp(dp));
   return launch_status("rn_tap_sgd");
@@ -717,7 +733,7 @@ int nfb_rn_small_sgd(const void* table, int n_entries, float* slots, long long r
   NFB_REQUIRE(!dp || !dp->row_sumsq || (dp->step_base && dp->clients_total >= 1), NFB_EINVAL,
               "rn_small_sgd: DP needs the device step counter and the job's client count");
   dim3 grid(n_entries, clients);
-  rn::small_sgd_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+  launch_pdl(rn::small_sgd_kernel, dim3(grid), dim3(256), 0, as_stream(stream), 
       static_cast<const rn::SmallEntry*>(table), slots, row_stride, momentum, sgrad, sgrad_stride,
       lr, mu, wd, zero_ptr, zero_ptr ? zero_len : 0, rn::make_dp(dp));
   return launch_status("rn_small_sgd");

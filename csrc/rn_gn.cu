@@ -38,6 +38,8 @@ __device__ __forceinline__ void gn_moments(const float* stats, long long img, in
 
 __global__ void __launch_bounds__(256)
     gn_stats_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C, float* __restrict__ stats) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   __shared__ float red[GN_GROUPS * 2];
   const long long img = blockIdx.y;
   const int octs = C >> 3, oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs;
@@ -81,6 +83,8 @@ struct GnApplyArgs {
 
 template <bool RES, bool RES_GN>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const GnApplyArgs a) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const long long img = blockIdx.y;
   const int C = a.C, octs = C >> 3, oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs;
   const int grp = oct * 64 / C, c0 = oct * 8;
@@ -149,6 +153,8 @@ struct GnBwdArgs {
 
 template <bool TWO>
 __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const GnBwdArgs a) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   __shared__ float scratch[256 * 8];
   __shared__ float red[GN_GROUPS * 4];
   const long long img = blockIdx.y;
@@ -248,6 +254,8 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const GnBwdArgs a) {
 
 template <bool TWO>
 __global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const GnBwdArgs a) {
+  pdl_trigger();
+  pdl_wait();      // programmatic dependent launch: see common.cuh
   const long long img = blockIdx.y;
   const int C = a.C, octs = C >> 3, oct = threadIdx.x % octs, r = threadIdx.x / octs, R = 256 / octs;
   const int grp = oct * 64 / C, c0 = oct * 8;
@@ -322,7 +330,7 @@ int nfb_rn_gn_stats(const void* x, int imgs, int HW, int C, float* stats, void* 
   NFB_REQUIRE(x && stats && imgs >= 1 && HW >= 1, NFB_EINVAL, "rn_gn_stats: bad argument");
   NFB_REQUIRE(C % 64 == 0 && C <= 512 && 256 % (C / 8) == 0, NFB_EINVAL, "rn_gn_stats: bad channels");
   NFB_REQUIRE(imgs <= 65535, NFB_ERANGE, "rn_gn_stats: too many images for one launch");
-  rn::gn_stats_kernel<<<dim3(rn::gn_splits(HW, C), imgs), 256, 0, as_stream(stream)>>>(
+  launch_pdl(rn::gn_stats_kernel, dim3(dim3(rn::gn_splits(HW, C), imgs)), dim3(256), 0, as_stream(stream), 
       static_cast<const __nv_bfloat16*>(x), HW, C, stats);
   return launch_status("rn_gn_stats");
 }
@@ -346,9 +354,9 @@ int nfb_rn_gn_apply(const void* x, const void* res, void* y, const float* slots,
   a.HW = HW; a.C = C; a.imgs_per_client = imgs_per_client; a.relu = relu; a.eps = eps;
   const dim3 grid(rn::gn_splits(HW, C), imgs);
   cudaStream_t st = as_stream(stream);
-  if (!res) rn::gn_apply_kernel<false, false><<<grid, 256, 0, st>>>(a);
-  else if (!res_stats) rn::gn_apply_kernel<true, false><<<grid, 256, 0, st>>>(a);
-  else rn::gn_apply_kernel<true, true><<<grid, 256, 0, st>>>(a);
+  if (!res) launch_pdl(rn::gn_apply_kernel<false, false>, dim3(grid), dim3(256), 0, st, a);
+  else if (!res_stats) launch_pdl(rn::gn_apply_kernel<true, false>, dim3(grid), dim3(256), 0, st, a);
+  else launch_pdl(rn::gn_apply_kernel<true, true>, dim3(grid), dim3(256), 0, st, a);
   return launch_status("rn_gn_apply");
 }
 
@@ -379,11 +387,11 @@ int nfb_rn_gn_bwd(int apply, const void* dout, const void* x, const void* x2, vo
   const dim3 grid(rn::gn_splits(HW, C), imgs);
   cudaStream_t st = as_stream(stream);
   if (!apply) {
-    if (x2) rn::gn_bwd_reduce_kernel<true><<<grid, 256, 0, st>>>(a);
-    else rn::gn_bwd_reduce_kernel<false><<<grid, 256, 0, st>>>(a);
+    if (x2) launch_pdl(rn::gn_bwd_reduce_kernel<true>, dim3(grid), dim3(256), 0, st, a);
+    else launch_pdl(rn::gn_bwd_reduce_kernel<false>, dim3(grid), dim3(256), 0, st, a);
   } else {
-    if (x2) rn::gn_bwd_apply_kernel<true><<<grid, 256, 0, st>>>(a);
-    else rn::gn_bwd_apply_kernel<false><<<grid, 256, 0, st>>>(a);
+    if (x2) launch_pdl(rn::gn_bwd_apply_kernel<true>, dim3(grid), dim3(256), 0, st, a);
+    else launch_pdl(rn::gn_bwd_apply_kernel<false>, dim3(grid), dim3(256), 0, st, a);
   }
   return launch_status(apply ? "rn_gn_bwd_apply" : "rn_gn_bwd_reduce");
 }
