@@ -309,7 +309,6 @@ __global__ void __launch_bounds__(256, MINB)
           for (int e = 0; e < 4; ++e) {
             const float gr = fmaf(wd, w4[e], fmaf(cs, __uint_as_float(r[4 * p + e]), zn[e]));
             nw[4 * p + e] = fmaf(-lr, gr, w4[e]);
-            wsq = fmaf(nw[4 * p + e], nw[4 * p + e], wsq);
           }
           st_vec(addr, pack<float>(nw + 4 * p));
         }
@@ -336,6 +335,10 @@ __global__ void __launch_bounds__(256, MINB)
             mbar_expect_tx(&w_bar[sub * 2 + buf], 4096);
             tma_load_3d(wbuf, &map_o, &w_bar[sub * 2 + buf], n0 + (c + 2) * 32, m0 + sub * 32, g);
           }
+        }
+        if (args.sumsq_out) {   // off the store's critical path: the tile is on its way already
+#pragma unroll
+          for (int e = 0; e < 32; ++e) wsq = fmaf(nw[e], nw[e], wsq);
         }
       }
       if (args.sumsq_out) {   // rows / columns past the weight's edge hold zeros (TMA fill)
