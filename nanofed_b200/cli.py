@@ -28,6 +28,8 @@ def _simulate(args: argparse.Namespace) -> int:
         compute_dtype=args.dtype, device=args.device, round_deadline_ms=args.round_deadline_ms,
         privacy=PrivacyConfig(noise_multiplier=args.noise_multiplier,
                               max_gradient_norm=args.clip_norm) if args.dp else None,
+        local_privacy=PrivacyConfig(noise_multiplier=args.noise_multiplier,
+                                    max_gradient_norm=args.clip_norm) if args.local_dp else None,
     )
     sim = FedSimulation(cfg)
     for r in range(args.rounds):
@@ -80,7 +82,10 @@ def main(argv: list[str] | None = None) -> int:
     s.add_argument("--engine", default="auto")
     s.add_argument("--dtype", default="bf16")
     s.add_argument("--device", default=None)
-    s.add_argument("--dp", action="store_true")
+    s.add_argument("--dp", action="store_true",
+                   help="central DP: per-update clipping + Gaussian noise inside the aggregation")
+    s.add_argument("--local-dp", action="store_true",
+                   help="client-side DP-SGD: clip + noise in every local step (PrivateTrainer recipe)")
     s.add_argument("--noise-multiplier", type=float, default=1.1)
     s.add_argument("--clip-norm", type=float, default=1.0)
     s.add_argument("--round-deadline-ms", type=float, default=None,
