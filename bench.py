@@ -57,6 +57,8 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--dp", action="store_true", help="central DP fused into aggregation")
     ap.add_argument("--local-dp", action="store_true",
                     help="client-side DP-SGD (clip + noise inside K-OPT) in every local step")
+    ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"],
+                    help="local optimizer (the BASELINE configs use SGD; adam = fused Adam K-OPT)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--streams-per-gpu", type=int, default=8,
                     help="client streams of the generic autograd engine (ResNet configs)")
@@ -149,7 +151,8 @@ def run_ours(args: argparse.Namespace) -> None:
     cfg = CohortConfig(
         model=args.model, clients_per_gpu=args.clients_per_gpu,
         samples_per_client=args.samples_per_client, batch_size=BATCH, local_epochs=LOCAL_EPOCHS,
-        learning_rate=LR, compute_dtype=args.dtype, engine=args.engine,
+        learning_rate=LR if args.optimizer == "sgd" else 1e-3, optimizer=args.optimizer,
+        compute_dtype=args.dtype, engine=args.engine,
         transport=args.transport, streams_per_gpu=args.streams_per_gpu,
         privacy=PrivacyConfig(epsilon=10.0, noise_multiplier=1.1) if args.dp else None,
         local_privacy=PrivacyConfig(epsilon=10.0, noise_multiplier=1.1) if args.local_dp else None,
@@ -293,7 +296,8 @@ def run_ours(args: argparse.Namespace) -> None:
                 "clients_per_gpu": args.clients_per_gpu,
                 "samples_per_client": args.samples_per_client, "local_epochs": LOCAL_EPOCHS,
                 "local_batch": BATCH, "local_steps_per_round": cfg.local_steps,
-                "optimizer": f"SGD(lr={LR})", "aggregation": "FedAvg (sample-weighted)"
+                "optimizer": f"SGD(lr={LR})" if args.optimizer == "sgd" else "Adam(lr=0.001)",
+                "aggregation": "FedAvg (sample-weighted)"
                 + (" + central DP clip/noise" if args.dp else "")
                 + (" + client-side DP-SGD" if args.local_dp else ""),
                 "parallelism": f"clients-dp{args.gpus}", "engine": sim.engine_name,

@@ -115,7 +115,8 @@ class MnistCohortNet:
         self.fuse_conv1_wgrad = os.environ.get("NFB_NO_FUSED_WGRAD1") is None
         self.tc_conv1 = os.environ.get("NFB_NO_TC_CONV1") is None
         # K-OPT also writes the permuted bf16 conv2 weights (needs one w2p buffer for all clients)
-        self.opt_writes_w2p = (self.group == c_all and os.environ.get("NFB_NO_OPT_W2P") is None)
+        self.opt_writes_w2p = (self.group == c_all and os.environ.get("NFB_NO_OPT_W2P") is None
+                               and getattr(cfg, "optimizer", "sgd") == "sgd")
         # DP-SGD on the client (reference PrivateTrainer semantics: clip the batch gradient to C, add
         # N(0, (sigma C)^2) per parameter): every client's gradient norm comes from K-STATS over the
         # gradient slab, the clip factor and the Philox noise are applied inside K-OPT
@@ -124,7 +125,11 @@ class MnistCohortNet:
                            else int.from_bytes(os.urandom(8), "little") >> 1)
         # momentum needs the gradient history in a buffer: only plain SGD is fused; DP needs the
         # complete gradient (its norm) before any of it is applied
-        self.fuse_fc1_sgd = (cfg.momentum == 0.0 and self.local_dp is None
+        # optimizer="adam": the complete gradient is materialised and the fused Adam kernel of K-OPT
+        # runs over the arena (the SGD-specific fusions - fc1 update in its GEMM epilogue, permuted
+        # conv2 weights out of K-OPT - are off)
+        self.adam = getattr(cfg, "optimizer", "sgd") == "adam"
+        self.fuse_fc1_sgd = (cfg.momentum == 0.0 and self.local_dp is None and not self.adam
                              and os.environ.get("NFB_NO_FUSED_SGD") is None)
         # DP with the fc1 update still inside its GEMM: the norm of the (never written) fc1 weight
         # gradient comes from a ghost norm - |sum_b dh_b (x) p_b|^2 = <dh dh^T, p p^T> - so the clip
@@ -139,7 +144,7 @@ class MnistCohortNet:
         # kernels (K-OPT and the fused fc1 update) leave each client's sum of squared parameters in
         # arena.sumsq, so the round runs no K-STATS pass over the client rows.
         # Not with non-finite screening (needs the scan anyway) nor with NFB_FUSED_DP's epilogue.
-        self.emits_sumsq = (getattr(cfg, "privacy", None) is not None
+        self.emits_sumsq = (not self.adam and getattr(cfg, "privacy", None) is not None
                             and not getattr(cfg, "screen_nonfinite", False)
                             and not self.fuse_fc1_dp
                             and os.environ.get("NFB_NO_SUMSQ_SIDE_OUTPUT") is None)
@@ -182,6 +187,18 @@ class MnistCohortNet:
         """One fused K-OPT launch over all clients; also hands the atomically accumulated
         gradient entries (conv1.*, conv2.*) back zeroed for the next step."""
         cfg, a = self.cfg, self.arena
+        if self.adam:
+            if step == 0:                 # fresh optimizer every round
+                a.exp_avg.zero_()
+                a.exp_avg_sq.zero_()
+            ops.fused_adam_(a.slots.view(-1), self.grads.view(-1), a.exp_avg.view(-1),
+                            a.exp_avg_sq.view(-1), step + 1, cfg.learning_rate,
+                            beta1=cfg.adam_betas[0], beta2=cfg.adam_betas[1], eps=cfg.adam_eps,
+                            weight_decay=cfg.weight_decay, lowp_out=a.slots_lowp.view(-1))
+            # entries the next step accumulates into with atomics (conv1.*, conv2.*, fc1.bias, fc2.*)
+            self.grads[:, : self._atomic_prefix].zero_()
+            self.grads[:, self._fc1_range[1] :].zero_()
+            return
         dp_kw: dict[str, Any] = {}
         if emit_sumsq:
             dp_kw["sumsq_out"] = a.sumsq

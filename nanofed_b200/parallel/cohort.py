@@ -59,6 +59,13 @@ class CohortConfig:
     learning_rate: float = 0.1
     momentum: float = 0.0
     weight_decay: float = 0.0
+    # "sgd" (momentum / weight_decay above) or "adam" (torch.optim.Adam semantics: L2 weight decay,
+    # bias correction; fused K-OPT kernel nfb_fused_adam over the whole arena).  Like the momentum
+    # buffer, the Adam moments start from zero every round (the reference's clients build a fresh
+    # optimizer per round, examples/mnist/run_experiment.py:65-73).
+    optimizer: str = "sgd"
+    adam_betas: tuple[float, float] = (0.9, 0.999)
+    adam_eps: float = 1e-8
     compute_dtype: str = "bf16"         # "bf16" | "fp32"
     engine: str = "auto"                # "auto" | "grouped" | "autograd"
     streams_per_gpu: int = 8            # autograd engine: 4 -> 8 streams measured +4 % on ResNet-18
@@ -306,6 +313,9 @@ class AutogradCohort:
         main = torch.cuda.current_stream(self.device) if self.cuda else None
         for step in range(cfg.local_steps):
             arena.grads.zero_()
+            if cfg.optimizer == "adam" and step == 0:      # fresh optimizer every round
+                arena.exp_avg.zero_()
+                arena.exp_avg_sq.zero_()
             if self.cuda:
                 for s in self.streams:
                     s.wait_stream(main)
@@ -329,6 +339,12 @@ class AutogradCohort:
                              step_counter=self._dp_step, row_len=arena.layout.total)
             if self._param_mask is not None:
                 arena.grads.addcmul_(arena.slots, self._param_mask, value=cfg.weight_decay)
+            if cfg.optimizer == "adam":
+                # buffers / padding columns have zero gradients and zero moments: 0 / (0 + eps) = 0
+                ops.fused_adam_(arena.slots.view(-1), arena.grads.view(-1), arena.exp_avg.view(-1),
+                                arena.exp_avg_sq.view(-1), step + 1, cfg.learning_rate,
+                                beta1=cfg.adam_betas[0], beta2=cfg.adam_betas[1], eps=cfg.adam_eps)
+                continue
             ops.fused_sgd_(
                 arena.slots.view(-1), arena.grads.view(-1), cfg.learning_rate,
                 momentum_buf=None if arena.momentum is None else arena.momentum.view(-1),
@@ -426,6 +442,17 @@ class FedSimulation:
             engine = "grouped" if (cfg.model in ("mnist_cnn", "resnet18", "resnet18_gn")
                                    and self.device.type == "cuda"
                                    and _grouped_available()) else "autograd"
+        if cfg.optimizer not in ("sgd", "adam"):
+            raise ValueError(f"optimizer must be 'sgd' or 'adam', got {cfg.optimizer!r}")
+        if cfg.optimizer == "adam":
+            if cfg.local_privacy is not None:
+                raise ValueError("client-side DP-SGD (local_privacy) is defined for optimizer='sgd'")
+            if cfg.model.startswith("resnet18"):
+                # the ResNet grouped engine applies SGD in its weight-gradient epilogues / tap-major
+                # update kernels; Adam runs on the generic engine
+                if cfg.engine == "grouped":
+                    raise ValueError("optimizer='adam' on ResNet-18 runs on engine='autograd'")
+                engine = "autograd"
         if cfg.compute_dtype not in ("bf16", "fp32"):
             raise ValueError(f"compute_dtype must be 'bf16' or 'fp32', got {cfg.compute_dtype!r}")
         if cfg.compute_dtype == "fp32":
@@ -443,9 +470,10 @@ class FedSimulation:
 
         self.arena = Arena(
             self.layout, c, self.device,
-            with_momentum=cfg.momentum != 0.0,
+            with_momentum=cfg.momentum != 0.0 and cfg.optimizer == "sgd",
             with_lowp=(engine == "grouped" and cfg.model == "mnist_cnn"),
             with_grads=(engine == "autograd"),
+            with_adam=cfg.optimizer == "adam",
         )
         self.arena.load_global(template.state_dict())
 

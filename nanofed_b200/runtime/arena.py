@@ -34,6 +34,7 @@ class Arena:
     with_momentum: bool = False
     with_lowp: bool = False
     with_grads: bool = True
+    with_adam: bool = False          # exp_avg / exp_avg_sq rows (reset every round like momentum)
     master: torch.Tensor = field(init=False)
     slots: torch.Tensor = field(init=False)
 
@@ -48,6 +49,8 @@ class Arena:
         )
         self.grads = torch.zeros(c, n, **f32) if self.with_grads else None
         self.momentum = torch.zeros(c, n, **f32) if self.with_momentum else None
+        self.exp_avg = torch.zeros(c, n, **f32) if self.with_adam else None
+        self.exp_avg_sq = torch.zeros(c, n, **f32) if self.with_adam else None
         self.counts = torch.ones(c, **f32)
         self.mask = torch.ones(c, **f32)
         self.sumsq = torch.zeros(c, **f32)
@@ -57,7 +60,8 @@ class Arena:
 
     def nbytes(self) -> int:
         total = 0
-        for name in ("master", "master_lowp", "slots", "slots_lowp", "grads", "momentum"):
+        for name in ("master", "master_lowp", "slots", "slots_lowp", "grads", "momentum", "exp_avg",
+                     "exp_avg_sq"):
             t = getattr(self, name)
             if t is not None:
                 total += t.numel() * t.element_size()

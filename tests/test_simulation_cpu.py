@@ -274,3 +274,51 @@ def test_client_side_dp_sgd_clips_each_clients_batch_gradient_and_adds_masked_no
         torch.testing.assert_close(a.slots[k], want, rtol=1e-4, atol=1e-5)
     out = sim.run_round()
     assert out.agg_metrics["local_privacy_epsilon"] > 0
+
+
+def test_adam_cohort_matches_torch_adam():
+    """``optimizer="adam"``: the fused Adam kernel of K-OPT over the arena rows (moments reset every
+    round) against ``torch.optim.Adam`` with the same betas / eps / L2 weight decay, two local steps
+    of every client; BatchNorm buffers must come out exactly as torch leaves them.  (eps = 1e-3:
+    with the default 1e-8 the first Adam step is lr * sign(g), and entries whose gradient is
+    rounding noise would flip between two fp32 summation orders.)"""
+    import torch.nn.functional as F
+
+    from nanofed_b200 import ops
+    from nanofed_b200.models import ResNet18
+
+    cfg = CohortConfig(model="resnet18", clients_per_gpu=2, samples_per_client=8, batch_size=4,
+                       learning_rate=2e-3, weight_decay=0.05, optimizer="adam",
+                       adam_betas=(0.8, 0.95), adam_eps=1e-3, device="cpu", engine="autograd",
+                       compute_dtype="fp32")
+    sim = FedSimulation(cfg)
+    state0 = sim.global_state()
+    ops.bcast_global(sim.arena.master, sim.arena.slots, sim.arena.slots_lowp, sim.arena.momentum)
+    sim.engine.after_broadcast()
+    sim.engine.local_steps()
+    sim.engine.before_aggregate()
+    for k in range(2):
+        got = sim.layout.unflatten(sim.arena.slots[k].clone())
+        model = ResNet18().train()
+        model.load_state_dict(state0)
+        opt = torch.optim.Adam(model.parameters(), lr=2e-3, betas=(0.8, 0.95), eps=1e-3,
+                               weight_decay=0.05)
+        for s in range(2):
+            x, y = sim.shards.images[k, 4 * s : 4 * s + 4], sim.shards.labels[k, 4 * s : 4 * s + 4]
+            opt.zero_grad()
+            F.cross_entropy(model(x), y).backward()
+            opt.step()
+        want = model.state_dict()
+        for key in ("conv1.weight", "layer2.0.shortcut.0.weight", "bn1.weight", "fc.bias",
+                    "bn1.running_var", "layer1.0.bn1.running_mean"):
+            torch.testing.assert_close(got[key].float(), want[key].float(), rtol=2e-3, atol=2e-5)
+        assert int(got["bn1.num_batches_tracked"]) == 2
+
+
+def test_adam_rejects_combinations_it_does_not_implement():
+    import pytest
+
+    with pytest.raises(ValueError, match="local_privacy"):
+        FedSimulation(_cfg(optimizer="adam", local_privacy=PrivacyConfig(epsilon=8.0)))
+    with pytest.raises(ValueError, match="optimizer"):
+        FedSimulation(_cfg(optimizer="lion"))
