@@ -318,6 +318,67 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
       const int out_pw = args.n_cls > 1 ? (tc_.cls & 1) : args.out_pw;
       const int as = local % C::ACC_STAGES;
       const uint32_t aph = (local / C::ACC_STAGES) & 1;
+      const int h = grp;
+      const int pos0 = mtile * HALVES * 128 + h * 128 + sub * 32;   // within the client
+      int n0, h0;
+      box_origin((g * args.P + pos0) >> 5, 32, args.H, args.W, n0, h0);
+      const long long row = static_cast<long long>(g) * args.P + pos0 + lane;
+      // Coalesced gather of a [32 rows x 128 B] tile whose row r starts at lane r's `rp` into this
+      // warp's staging buffer (same swizzle as the output tile).  Row-per-lane 16-byte loads touch
+      // 32 different lines per instruction (256 tag look-ups per tile and warp: the 64-channel data
+      // gradients were bound by them); here one instruction covers four whole rows.
+      auto gather_rows = [&](const __nv_bfloat16* rp) {
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+        uint4 t[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int rj = j * 4 + (lane >> 3);
+          const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(
+              __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(rp), rj));
+          t[j] = ld_plain(src + (lane & 7) * 8);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int rj = j * 4 + (lane >> 3);
+          st_vec(my_stage + rj * 128 + (((lane & 7) ^ (rj & 7)) * 16), t[j]);
+        }
+        __syncwarp();
+      };
+      // ReLU-backward mask of this warp's rows as 64 bits per chunk: fetched BEFORE the accumulator
+      // is waited for (it does not depend on it), i.e. under the MMAs of this very tile
+      uint32_t mbits[BN / 64][2];
+      if (args.out_mask) {
+        long long moff;
+        if (!args.out_is_parity) {
+          moff = row * args.n_out;
+        } else {   // this row is pixel (2*hh + ph, 2*wh + pw) of the full-resolution output
+          const int hw = args.H * args.W;
+          const int n = static_cast<int>(row / hw), rem = static_cast<int>(row - static_cast<long long>(n) * hw);
+          const int hh = rem / args.W, wh = rem - hh * args.W;
+          moff = ((static_cast<long long>(n) * 2 * args.H + 2 * hh + out_ph) * (2 * args.W) +
+                  2 * wh + out_pw) * args.out_c;
+        }
+        const __nv_bfloat16* mrow = args.out_mask + moff + ntile * BN;
+#pragma unroll
+        for (int c = 0; c < BN / 64; ++c) {
+          gather_rows(mrow + c * 64);
+          uint32_t lo = 0u, hi = 0u;
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            const uint4 m = *reinterpret_cast<const uint4*>(my_stage + lane * 128 + ((p ^ (lane & 7)) * 16));
+            const uint32_t w4[4] = {m.x, m.y, m.z, m.w};
+            uint32_t byte = 0u;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {   // bf16 > 0  <=>  sign clear and magnitude != 0
+              byte |= (((w4[q] & 0x8000u) == 0u && (w4[q] & 0x7fffu) != 0u) ? 1u : 0u) << (2 * q);
+              byte |= (((w4[q] & 0x80000000u) == 0u && (w4[q] & 0x7fff0000u) != 0u) ? 1u : 0u) << (2 * q + 1);
+            }
+            if (p < 4) lo |= byte << (8 * p); else hi |= byte << (8 * (p - 4));
+          }
+          mbits[c][0] = lo; mbits[c][1] = hi;
+        }
+      }
       if (!mbar_wait(&acc_full[as], aph)) { if (lane == 0) *args.status = 1; ok = false; break; }
       tc_fence_after();
       const uint32_t lane_addr =
@@ -326,11 +387,6 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
 #pragma unroll
       for (int j = 0; j < BN / 32; ++j) csum[j] = csq[j] = 0.f;
       {
-        const int h = grp;
-        const int pos0 = mtile * HALVES * 128 + h * 128 + sub * 32;   // within the client
-        int n0, h0;
-        box_origin((g * args.P + pos0) >> 5, 32, args.H, args.W, n0, h0);
-        const long long row = static_cast<long long>(g) * args.P + pos0 + lane;
 #pragma unroll
         for (int c = 0; c < BN / 64; ++c) {
           if (bn_bwd) {
@@ -355,41 +411,31 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
           float v[64];
 #pragma unroll
           for (int j = 0; j < 64; ++j) v[j] = __uint_as_float(r[j]);
-          if (args.residual) {
-            const long long off = row * args.n_out + ntile * BN + c * 64;
+          if (args.residual && !args.res_mask) {
+            gather_rows(args.residual + row * args.n_out + ntile * BN + c * 64);
 #pragma unroll
             for (int p = 0; p < 8; ++p) {
               float rf[8];
-              unpack<__nv_bfloat16>(ld_plain(args.residual + off + p * 8), rf);
-              if (args.res_mask) {
-                float mf[8];
-                unpack<__nv_bfloat16>(ld_plain(args.res_mask + off + p * 8), mf);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) rf[e] = mf[e] > 0.f ? rf[e] : 0.f;
-              }
+              unpack<__nv_bfloat16>(*reinterpret_cast<const uint4*>(
+                                        my_stage + lane * 128 + ((p ^ (lane & 7)) * 16)), rf);
 #pragma unroll
               for (int e = 0; e < 8; ++e) v[p * 8 + e] += rf[e];
             }
-          }
-          if (args.out_mask) {
-            long long moff;
-            if (!args.out_is_parity) {
-              moff = row * args.n_out;
-            } else {   // this row is pixel (2*hh + ph, 2*wh + pw) of the full-resolution output
-              const int hw = args.H * args.W;
-              const int n = static_cast<int>(row / hw), rem = static_cast<int>(row - static_cast<long long>(n) * hw);
-              const int hh = rem / args.W, wh = rem - hh * args.W;
-              moff = ((static_cast<long long>(n) * 2 * args.H + 2 * hh + out_ph) * (2 * args.W) +
-                      2 * wh + out_pw) * args.out_c;
-            }
-            moff += ntile * BN + c * 64;
+          } else if (args.residual) {
+            const long long off = row * args.n_out + ntile * BN + c * 64;
 #pragma unroll
             for (int p = 0; p < 8; ++p) {
-              float mf[8];
-              unpack<__nv_bfloat16>(ld_plain(args.out_mask + moff + p * 8), mf);
+              float rf[8], mf[8];
+              unpack<__nv_bfloat16>(ld_plain(args.residual + off + p * 8), rf);
+              unpack<__nv_bfloat16>(ld_plain(args.res_mask + off + p * 8), mf);
 #pragma unroll
-              for (int e = 0; e < 8; ++e) v[p * 8 + e] = mf[e] > 0.f ? v[p * 8 + e] : 0.f;
+              for (int e = 0; e < 8; ++e) v[p * 8 + e] += mf[e] > 0.f ? rf[e] : 0.f;
             }
+          }
+          if (args.out_mask) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j)
+              v[j] = ((mbits[c][j >> 5] >> (j & 31)) & 1u) ? v[j] : 0.f;
           }
           if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
           __syncwarp();
