@@ -314,8 +314,8 @@ __global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const GnBwdArgs a) {
 
 // position splits per image: enough blocks to fill the machine on the wide early layers, one block
 // per image where an image is a few kilobytes
-static int gn_splits(int HW, int C) {
-  const int rows_per_block = (256 / (C / 8)) * GN_U;
+static int gn_splits(int HW, int C, int iters = 1) {
+  const int rows_per_block = (256 / (C / 8)) * GN_U * iters;
   int s = (HW + rows_per_block - 1) / rows_per_block;
   return s < 1 ? 1 : (s > 8 ? 8 : s);
 }
@@ -330,7 +330,7 @@ int nfb_rn_gn_stats(const void* x, int imgs, int HW, int C, float* stats, void* 
   NFB_REQUIRE(x && stats && imgs >= 1 && HW >= 1, NFB_EINVAL, "rn_gn_stats: bad argument");
   NFB_REQUIRE(C % 64 == 0 && C <= 512 && 256 % (C / 8) == 0, NFB_EINVAL, "rn_gn_stats: bad channels");
   NFB_REQUIRE(imgs <= 65535, NFB_ERANGE, "rn_gn_stats: too many images for one launch");
-  launch_pdl(rn::gn_stats_kernel, dim3(dim3(rn::gn_splits(HW, C), imgs)), dim3(256), 0, as_stream(stream), 
+  launch_pdl(rn::gn_stats_kernel, dim3(dim3(rn::gn_splits(HW, C, 4), imgs)), dim3(256), 0, as_stream(stream), 
       static_cast<const __nv_bfloat16*>(x), HW, C, stats);
   return launch_status("rn_gn_stats");
 }
@@ -352,7 +352,7 @@ int nfb_rn_gn_apply(const void* x, const void* res, void* y, const float* slots,
   a.gn = rn::GnRef{stats, gn_offs[0], gn_offs[1]};
   if (res_stats) a.gn_res = rn::GnRef{res_stats, res_offs[0], res_offs[1]};
   a.HW = HW; a.C = C; a.imgs_per_client = imgs_per_client; a.relu = relu; a.eps = eps;
-  const dim3 grid(rn::gn_splits(HW, C), imgs);
+  const dim3 grid(rn::gn_splits(HW, C, 2), imgs);
   cudaStream_t st = as_stream(stream);
   if (!res) launch_pdl(rn::gn_apply_kernel<false, false>, dim3(grid), dim3(256), 0, st, a);
   else if (!res_stats) launch_pdl(rn::gn_apply_kernel<true, false>, dim3(grid), dim3(256), 0, st, a);
@@ -384,11 +384,14 @@ int nfb_rn_gn_bwd(int apply, const void* dout, const void* x, const void* x2, vo
   if (x2) a.gn2 = rn::GnRef{stats2, gn2_offs[0], gn2_offs[1]};
   a.bsums = bsums; a.bsums2 = bsums2;
   a.HW = HW; a.C = C; a.imgs_per_client = imgs_per_client; a.eps = eps;
-  const dim3 grid(rn::gn_splits(HW, C), imgs);
+  const dim3 grid(rn::gn_splits(HW, C, 2), imgs);
   cudaStream_t st = as_stream(stream);
   if (!apply) {
-    if (x2) launch_pdl(rn::gn_bwd_reduce_kernel<true>, dim3(grid), dim3(256), 0, st, a);
-    else launch_pdl(rn::gn_bwd_reduce_kernel<false>, dim3(grid), dim3(256), 0, st, a);
+    // the reduce pass has a fixed cost per block (moments, two shared-memory reductions, C
+    // atomics): four trips of the load loop per block instead of one
+    const dim3 rgrid(rn::gn_splits(HW, C, 4), imgs);
+    if (x2) launch_pdl(rn::gn_bwd_reduce_kernel<true>, rgrid, dim3(256), 0, st, a);
+    else launch_pdl(rn::gn_bwd_reduce_kernel<false>, rgrid, dim3(256), 0, st, a);
   } else {
     if (x2) launch_pdl(rn::gn_bwd_apply_kernel<true>, dim3(grid), dim3(256), 0, st, a);
     else launch_pdl(rn::gn_bwd_apply_kernel<false>, dim3(grid), dim3(256), 0, st, a);

@@ -12,7 +12,8 @@ from nanofed_b200.ops import native, tc
 from nanofed_b200.parallel.cohort import CohortConfig, FedSimulation
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-sim = FedSimulation(CohortConfig(model="resnet18", clients_per_gpu=8, samples_per_client=128,
+model = sys.argv[2] if len(sys.argv) > 2 else "resnet18"      # or resnet18_gn
+sim = FedSimulation(CohortConfig(model=model, clients_per_gpu=8, samples_per_client=128,
                                  batch_size=64, engine="grouped", use_cuda_graph=False, device="cuda"))
 a = sim.arena
 ops.bcast_global(a.master, a.slots, a.slots_lowp, a.momentum)
