@@ -36,13 +36,15 @@ struct SgdArgs {
   float* sumsq_out;
 };
 
-template <typename G>
+// SUMSQ: instantiation with the sum-of-squares side output (a separate one: its shared-memory
+// array and ten more registers cost the plain kernel 3 us per step when it was a run-time switch)
+template <typename G, bool SUMSQ>
 __global__ void __launch_bounds__(256)
     sgd_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ mom,
                __nv_bfloat16* __restrict__ lowp, int64_t n, SgdArgs a) {
-  __shared__ float s_rowsq[256];       // per-row partial sums of this block (rows <= 256)
-  const int64_t n_rows = a.sumsq_out ? n / a.row_len : 0;
-  if (a.sumsq_out) {
+  __shared__ float s_rowsq[SUMSQ ? 256 : 1];   // per-row partial sums of this block (rows <= 256)
+  const int64_t n_rows = SUMSQ ? n / a.row_len : 0;
+  if constexpr (SUMSQ) {
     s_rowsq[threadIdx.x] = 0.f;
     __syncthreads();
   }
@@ -64,7 +66,7 @@ __global__ void __launch_bounds__(256)
     // row / column of this group for the per-row clip factor and the noise mask: 32-bit division
     // where the buffer allows it (a 64-bit divide per group cost 10 us of a 124 us pass)
     int64_t dp_row = 0, dp_col = 0;
-    if (a.row_sumsq || a.noise_mask || a.sumsq_out) {
+    if (a.row_sumsq || a.noise_mask || SUMSQ) {
       if (n < (1ll << 31)) {
         const uint32_t b32 = static_cast<uint32_t>(base), rl = static_cast<uint32_t>(a.row_len);
         const uint32_t r32 = b32 / rl;
@@ -140,7 +142,7 @@ __global__ void __launch_bounds__(256)
     if (lowp) {
       for (int e = 0; e < cnt; ++e) lowp[base + e] = __float2bfloat16_rn(pv[e]);
     }
-    if (a.sumsq_out) {                     // row_len % 4 == 0: a group never straddles two rows
+    if constexpr (SUMSQ) {                 // row_len % 4 == 0: a group never straddles two rows
       float t = 0.f;
       for (int e = 0; e < cnt; ++e) t = fmaf(pv[e], pv[e], t);
       if (n_rows <= 256) atomicAdd(&s_rowsq[dp_row], t);
@@ -162,7 +164,7 @@ __global__ void __launch_bounds__(256)
       }
     }
   }
-  if (a.sumsq_out && n_rows <= 256) {
+  if (SUMSQ && n_rows <= 256) {
     __syncthreads();
     if (threadIdx.x < n_rows && s_rowsq[threadIdx.x] != 0.f)
       atomicAdd(a.sumsq_out + threadIdx.x, s_rowsq[threadIdx.x]);
@@ -256,8 +258,12 @@ static int fused_sgd_impl(float* p, void* g, int g_dtype, float* momentum_buf, v
   if (work <= 0) return 0;
   return dispatch_dtype(g_dtype, [&](auto tag) {
     using G = decltype(tag);
-    sgd_kernel<G><<<flat_grid((work + 3) / 4), 256, 0, st>>>(
-        p, static_cast<G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
+    if (sumsq_out)
+      sgd_kernel<G, true><<<flat_grid((work + 3) / 4), 256, 0, st>>>(
+          p, static_cast<G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
+    else
+      sgd_kernel<G, false><<<flat_grid((work + 3) / 4), 256, 0, st>>>(
+          p, static_cast<G*>(g), mom, static_cast<__nv_bfloat16*>(lowp_out), n, a);
     return launch_status("fused_sgd");
   });
 }

@@ -10,6 +10,8 @@ b bench_mnist_local_dp --steps 20 --warmup 3 --local-dp
 b bench_resnet18 --model resnet18 --steps 5 --warmup 3
 b bench_resnet18_dp --model resnet18 --steps 5 --warmup 3 --dp
 b bench_resnet18_gn --model resnet18_gn --steps 5 --warmup 3
+b bench_resnet18_gn_local_dp --model resnet18_gn --local-dp --steps 5 --warmup 3
+b bench_mnist_adam --optimizer adam --steps 20 --warmup 3
 b bench_resnet18_gn_autograd --model resnet18_gn --engine autograd --steps 5 --warmup 3
 b bench_resnet18_autograd --model resnet18 --engine autograd --steps 5 --warmup 3
 python tools/rn_prof.py --reps 2 > "$O/rn_prof_step.log" 2>&1; grep "local step" "$O/rn_prof_step.log"
