@@ -209,8 +209,14 @@ class _Lane:
         self.fuse_sgd = (cfg.momentum == 0.0 and self.local_dp is None
                          and os.environ.get("NFB_RN_NO_FUSED_SGD") is None)
         self._ksplit = {c.name: self._pick_ksplit(c) for c in self.convs}
-        ranges = [(c.t_off, c.taps * c.cout * c.cin) for c in self.convs
-                  if not (self.fuse_sgd and self._ksplit[c.name] == 1)]
+        # tap-major ranges updated by tap_sgd, cut into pieces of 8192 elements: one (piece, client)
+        # per block, so a 295 k-element layer and a 4 k-element one do not share one grid shape
+        ranges = []
+        for c in self.convs:
+            if self.fuse_sgd and self._ksplit[c.name] == 1:
+                continue
+            n = c.taps * c.cout * c.cin
+            ranges += [(c.t_off + lo, min(8192, n - lo)) for lo in range(0, n, 8192)]
         self.tap_ranges = torch.tensor(ranges or [(0, 0)], dtype=torch.int64, device=dev)
         self.tap_max = max((r[1] for r in ranges), default=0)
         # BatchNorm backward sums from the dgrad epilogue instead of a reduction pass
