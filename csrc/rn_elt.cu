@@ -44,27 +44,33 @@ __global__ void __launch_bounds__(256)
     im2col3_kernel(const float* __restrict__ x, long long x_gs, int B, __nv_bfloat16* __restrict__ out) {
   pdl_trigger();
   pdl_wait();      // programmatic dependent launch: see common.cuh
-  // one thread = one position x 8 patch entries; entry k = (kh*3 + kw)*3 + ci
+  // one thread = one position x 8 patch entries; entry k = (kh*3 + kw)*3 + ci.  A thread keeps its
+  // entry octet for the whole launch (32 positions per block trip), so the tap / channel of its 8
+  // entries is computed once; octets 4..7 are the zero padding of K = 27 -> 64.
   const int g = blockIdx.y;
-  const long long total = static_cast<long long>(B) * 1024 * 8;
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += gridDim.x * 256ll) {
-    const int oct = static_cast<int>(i & 7);
-    const long long pos = i >> 3;
+  const int oct = threadIdx.x & 7;
+  int coff[8], dh[8], dw[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int k = oct * 8 + e;
+    const int ci = k % 3, tap = k / 3;
+    coff[e] = k < 27 ? ci * 1024 : -1;
+    dh[e] = tap / 3 - 1;
+    dw[e] = tap % 3 - 1;
+  }
+  const long long positions = static_cast<long long>(B) * 1024;
+  for (long long pos = blockIdx.x * 32ll + (threadIdx.x >> 3); pos < positions; pos += gridDim.x * 32ll) {
     const int b = static_cast<int>(pos >> 10), h = static_cast<int>((pos >> 5) & 31),
               w = static_cast<int>(pos & 31);
     const float* img = x + g * x_gs + static_cast<long long>(b) * 3072;
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int k = oct * 8 + e;
-      float val = 0.f;
-      if (k < 27) {
-        const int ci = k % 3, tap = k / 3, hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
-        if (hh >= 0 && hh < 32 && ww >= 0 && ww < 32) val = __ldg(img + ci * 1024 + hh * 32 + ww);
-      }
-      v[e] = val;
+      const int hh = h + dh[e], ww = w + dw[e];
+      const bool in = coff[e] >= 0 && hh >= 0 && hh < 32 && ww >= 0 && ww < 32;
+      v[e] = in ? __ldg(img + coff[e] + hh * 32 + ww) : 0.f;
     }
-    st_vec(out + ((static_cast<long long>(g) * B * 1024 + pos) * 64 + oct * 8), pack<__nv_bfloat16>(v));
+    st_vec(out + ((static_cast<long long>(g) * positions + pos) * 64 + oct * 8), pack<__nv_bfloat16>(v));
   }
 }
 
