@@ -82,9 +82,14 @@ struct Cfg {
   static constexpr int TMEM_NEED = BN * TPS;
   static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64
                                    : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
-  // 4 epilogue warps x [32 rows x 128 B]; EPI 1: two weight buffers per warp (load c+1 while
-  // c is updated) plus a [32 rows x 64 B] bf16 tile per warp
-  static constexpr int STAGING = EPI == 1 ? 4 * (2 * 4096 + 2048) : 4 * 4096;
+  // 4 epilogue warps x [32 rows x 128 B]; EPI 1: WBUF weight buffers per warp plus a
+  // [32 rows x 64 B] bf16 tile per warp.  The fused update is a streaming pass over the fp32 master
+  // (fc1 of the flagship: one k-block of MMAs per 64 KB of weights), so what counts is bytes in
+  // flight: with a single operand stage (K = one k-block) the second stage's 32 KB become two more
+  // buffers per warp and ALL four 32-column chunks of a 128-column tile are requested before the
+  // accumulator is even waited for.
+  static constexpr int WBUF = (EPI == 1 && STAGES == 1) ? 4 : 2;
+  static constexpr int STAGING = EPI == 1 ? 4 * (WBUF * 4096 + 2048) : 4 * 4096;
   static constexpr size_t SMEM = static_cast<size_t>(STAGES) * STAGE + STAGING + 1024 /*align*/ + 256;
   static_assert(A_MN || A_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
   static_assert(B_MN || B_SWZ == BK * 2, "K-major: swizzle span must equal BK bytes");
@@ -136,7 +141,7 @@ __global__ void __launch_bounds__(256, MINB)
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* acc_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
-  uint64_t* w_bar = acc_bar + 2;                        // EPI 1: [4 warps][2 buffers]
+  uint64_t* w_bar = acc_bar + 2;                        // EPI 1: [4 warps][WBUF buffers]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -163,7 +168,7 @@ __global__ void __launch_bounds__(256, MINB)
     if constexpr (EPI == 1) {
       prefetch_tmap(&map_o);
       prefetch_tmap(&map_l);
-      for (int i = 0; i < 8; ++i) mbar_init(&w_bar[i], 1);
+      for (int i = 0; i < 4 * C::WBUF; ++i) mbar_init(&w_bar[i], 1);
     }
     fence_barrier_init();
   }
@@ -234,14 +239,14 @@ __global__ void __launch_bounds__(256, MINB)
     bool ok = true;
     [[maybe_unused]] int sgd_chunks = 0;
     if constexpr (EPI == 1) {
-      // the weight tiles do not depend on the MMA: start fetching the first two 32-column
+      // the weight tiles do not depend on the MMA: start fetching the first WBUF 32-column
       // chunks of this warp's 32 rows before waiting for the accumulator
       sgd_chunks = min(BN, args.n_valid - n0) / 32;
       if (lane == 0) {
-        for (int c = 0; c < 2 && c < sgd_chunks; ++c) {
-          mbar_expect_tx(&w_bar[sub * 2 + c], 4096);
-          tma_load_3d(staging + sub * 8192 + c * 4096, &map_o, &w_bar[sub * 2 + c], n0 + c * 32,
-                      m0 + sub * 32, g);
+        for (int c = 0; c < C::WBUF && c < sgd_chunks; ++c) {
+          mbar_expect_tx(&w_bar[sub * C::WBUF + c], 4096);
+          tma_load_3d(staging + sub * (C::WBUF * 4096) + c * 4096, &map_o,
+                      &w_bar[sub * C::WBUF + c], n0 + c * 32, m0 + sub * 32, g);
         }
       }
     }
@@ -271,7 +276,7 @@ __global__ void __launch_bounds__(256, MINB)
       // buffer, each thread updates its own row in place, and the same buffer is the source of
       // the TMA store back; the bf16 working copy goes out through a 64-byte-swizzled tile.
       // The gradient itself never reaches memory.
-      uint8_t* lstage = staging + 4 * 8192 + sub * 2048;
+      uint8_t* lstage = staging + 4 * (C::WBUF * 4096) + sub * 2048;
       const float lr = args.sgd_lr, wd = args.sgd_wd;
       const bool live = ok && n_iters > 0;
       const float cs = args.dp_ss ? fminf(args.dp_clip / (sqrtf(args.dp_ss[g]) + 1e-6f), 1.f) : 1.f;
@@ -282,14 +287,14 @@ __global__ void __launch_bounds__(256, MINB)
       float wsq = 0.f;
 #pragma unroll 1
       for (int c = 0; c < sgd_chunks; ++c) {
-        const int buf = c & 1;
-        uint8_t* wbuf = staging + sub * 8192 + buf * 4096;
+        const int buf = c % C::WBUF;
+        uint8_t* wbuf = staging + sub * (C::WBUF * 4096) + buf * 4096;
         uint32_t r[32];
         __syncwarp();                         // lane 0 may come late from the refill below
         tmem_ld_32x32b_x16(lane_addr + c * 32, r);
         tmem_ld_32x32b_x16(lane_addr + c * 32 + 16, r + 16);
         tmem_ld_wait();
-        if (!mbar_wait(&w_bar[sub * 2 + buf], (c >> 1) & 1)) { *args.status = 1; break; }
+        if (!mbar_wait(&w_bar[sub * C::WBUF + buf], (c / C::WBUF) & 1)) { *args.status = 1; break; }
         // bf16 tile of the previous chunk must have been read by its store before we overwrite it
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
@@ -329,11 +334,12 @@ __global__ void __launch_bounds__(256, MINB)
               "r"(smem_u32(lstage)), "r"(n0 + c * 32), "r"(m0 + sub * 32), "r"(g)
               : "memory");
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-          if (c + 2 < sgd_chunks) {
-            // refill this buffer with chunk c+2 once the store above has read it
+          if (c + C::WBUF < sgd_chunks) {
+            // refill this buffer with chunk c + WBUF once the store above has read it
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            mbar_expect_tx(&w_bar[sub * 2 + buf], 4096);
-            tma_load_3d(wbuf, &map_o, &w_bar[sub * 2 + buf], n0 + (c + 2) * 32, m0 + sub * 32, g);
+            mbar_expect_tx(&w_bar[sub * C::WBUF + buf], 4096);
+            tma_load_3d(wbuf, &map_o, &w_bar[sub * C::WBUF + buf], n0 + (c + C::WBUF) * 32,
+                        m0 + sub * 32, g);
           }
         }
         if (args.sumsq_out) {   // off the store's critical path: the tile is on its way already
@@ -726,6 +732,10 @@ int nfb_tc_linear_wgrad_sgd(const nfb_tc_operand* A, const nfb_tc_operand* B, in
   g.status = status;
   Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
   Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};
+  if (inner == 1)   // K = one k-block: nothing to pipeline, the smem goes to the weight buffers
+    return launch<true, 128, true, 128, 64, 128, 1, 1, 2, 1>(a, b, (j + BM - 1) / BM,
+                                                           (i + 127) / 128, groups, g,
+                                                           as_stream(stream), w_lowp, lowp_gs);
   return launch<true, 128, true, 128, 64, 128, 1, 2, 2, 1>(a, b, (j + BM - 1) / BM, (i + 127) / 128,
                                                          groups, g, as_stream(stream), w_lowp,
                                                          lowp_gs);
@@ -765,6 +775,10 @@ int nfb_tc_linear_wgrad_sgd_dp(const nfb_tc_operand* A, const nfb_tc_operand* B,
   g.status = status;
   Operand a{A->ptr, A->inner, A->rows, A->groups, A->row_stride, A->group_stride};
   Operand b{B->ptr, B->inner, B->rows, B->groups, B->row_stride, B->group_stride};
+  if (inner == 1)   // K = one k-block: nothing to pipeline, the smem goes to the weight buffers
+    return launch<true, 128, true, 128, 64, 128, 1, 1, 2, 1>(a, b, (j + BM - 1) / BM,
+                                                           (i + 127) / 128, groups, g,
+                                                           as_stream(stream), w_lowp, lowp_gs);
   return launch<true, 128, true, 128, 64, 128, 1, 2, 2, 1>(a, b, (j + BM - 1) / BM, (i + 127) / 128,
                                                          groups, g, as_stream(stream), w_lowp,
                                                          lowp_gs);
