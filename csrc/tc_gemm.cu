@@ -691,7 +691,7 @@ int nfb_tc_gemm(int variant, const nfb_tc_operand* A, const nfb_tc_operand* B, i
     case 2:
       NFB_REQUIRE(taps == 9, NFB_EINVAL, "tc_gemm: conv_wgrad needs 9 taps");
       return launch<true, 128, true, 64, 64, 32, 9, 4>(a, b, m_tiles, n_tiles, groups, g, st);
-    case 3: return launch<false, 128, false, 128, 64, 64, 1, 6>(a, b, m_tiles, n_tiles, groups, g, st);
+    case 3: return launch<false, 128, false, 128, 64, 64, 1, 3, 2>(a, b, m_tiles, n_tiles, groups, g, st);
     case 4: return launch<true, 128, false, 128, 64, 64, 1, 4>(a, b, m_tiles, n_tiles, groups, g, st);
     // variants 5/6 have only 1-2 k-blocks per tile: every CTA is one latency-bound chain
     // (setup -> TMA -> MMA -> epilogue), so two CTAs per SM (2 stages, <=128 registers) are what
