@@ -329,14 +329,17 @@ __global__ void __launch_bounds__(256)
   }
   __syncthreads();
   // logits
-  for (int i = threadIdx.x; i < nb * 10; i += blockDim.x) {
-    const int b = i / 10, k = i % 10;
-    float acc = row[b2_off + k];
-    const float* hb = h + b * 128;
-    const float* wk = w2 + k * 128;
-#pragma unroll 8
-    for (int j = 0; j < 128; ++j) acc = fmaf(hb[j], wk[j], acc);
-    lg[i] = acc;
+  // one warp per (row, class) dot product: lane l takes elements 4l..4l+3 of both vectors (16-byte
+  // conflict-free reads).  One THREAD per dot product read h[b][j] for 16 different b at the same
+  // j - a 16-way bank conflict on every one of its 128 loads.
+  for (int i = threadIdx.x >> 5; i < nb * 10; i += blockDim.x >> 5) {
+    const int b = i / 10, k = i % 10, l4 = (threadIdx.x & 31) * 4;
+    const float4 hv = *reinterpret_cast<const float4*>(h + b * 128 + l4);
+    const float4 wv = *reinterpret_cast<const float4*>(w2 + k * 128 + l4);
+    float acc = fmaf(hv.x, wv.x, fmaf(hv.y, wv.y, fmaf(hv.z, wv.z, hv.w * wv.w)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) lg[i] = acc + row[b2_off + k];
   }
   __syncthreads();
   // softmax / loss / accuracy / dlogits : one thread per sample
@@ -532,7 +535,7 @@ int nfb_mnist_fc_head(float* hpre, const int64_t* labels, int64_t label_stride, 
   NFB_REQUIRE(hpre && labels && slots && grads && dh && stats, NFB_EINVAL,
               "mnist_fc_head: null pointer");
   NFB_REQUIRE(B >= 1 && B <= 256, NFB_ERANGE, "mnist_fc_head: batch %d outside [1, 256]", B);
-  const int splits = B >= 32 ? 4 : 1;
+  const int splits = B >= 64 ? 8 : (B >= 32 ? 4 : 1);   // 256 blocks for 32 clients x batch 64
   const int rows_per = (B + splits - 1) / splits;
   const size_t smem = (static_cast<size_t>(rows_per) * 128 + 1280 +
                        static_cast<size_t>(rows_per) * 10 + 64) * sizeof(float);
