@@ -640,7 +640,9 @@ int nfb_rn_bn_apply(const void* x, const void* res, void* y, float* slots, long 
   }
   a.P = P; a.C = C; a.relu = relu; a.eps = eps; a.momentum = momentum;
   NFB_REQUIRE(256 % (C / 8) == 0, NFB_EINVAL, "rn_bn_apply: C / 8 must divide 256");
-  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / rn::BN_U, clients), clients);
+  // four trips of the load loop per block: with one, the deep layers (4096 or 1024 positions per
+  // client) ran 500-1000 blocks that were mostly prologue (32 coefficient loads per thread)
+  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / (4 * rn::BN_U), clients), clients);
   cudaStream_t st = as_stream(stream);
   if (!res) launch_pdl(rn::bn_apply_kernel<false, false>, dim3(grid), dim3(256), 0, st, a);
   else if (!res_stats) launch_pdl(rn::bn_apply_kernel<true, false>, dim3(grid), dim3(256), 0, st, a);
@@ -683,7 +685,7 @@ int nfb_rn_bn_bwd(int apply, const void* dout, const void* out, const void* x, c
     else launch_pdl(rn::bn_bwd_reduce_kernel<false>, dim3(grid), dim3(256), 0, st, a);
     return launch_status("rn_bn_bwd_reduce");
   }
-  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / rn::BN_U, clients), clients);
+  dim3 grid(rn::blocks_for(static_cast<long long>(P) * C / 8 / (4 * rn::BN_U), clients), clients);
   if (x2) launch_pdl(rn::bn_bwd_apply_kernel<true>, dim3(grid), dim3(256), 0, st, a);
   else launch_pdl(rn::bn_bwd_apply_kernel<false>, dim3(grid), dim3(256), 0, st, a);
   return launch_status("rn_bn_bwd_apply");
