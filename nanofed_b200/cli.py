@@ -25,6 +25,7 @@ def _simulate(args: argparse.Namespace) -> int:
         model=args.model, clients_per_gpu=args.clients_per_gpu,
         samples_per_client=args.samples_per_client, batch_size=args.batch_size,
         local_epochs=args.local_epochs, learning_rate=args.lr, engine=args.engine,
+        optimizer=args.optimizer, momentum=args.momentum, weight_decay=args.weight_decay,
         compute_dtype=args.dtype, device=args.device, round_deadline_ms=args.round_deadline_ms,
         privacy=PrivacyConfig(noise_multiplier=args.noise_multiplier,
                               max_gradient_norm=args.clip_norm) if args.dp else None,
@@ -79,6 +80,9 @@ def main(argv: list[str] | None = None) -> int:
     s.add_argument("--local-epochs", type=int, default=1)
     s.add_argument("--lr", type=float, default=0.1)
     s.add_argument("--rounds", type=int, default=5)
+    s.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"])
+    s.add_argument("--momentum", type=float, default=0.0)
+    s.add_argument("--weight-decay", type=float, default=0.0)
     s.add_argument("--engine", default="auto")
     s.add_argument("--dtype", default="bf16")
     s.add_argument("--device", default=None)
