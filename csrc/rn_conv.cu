@@ -107,6 +107,11 @@ struct GemmArgs {
   // BatchNorm under the masked activation normalises; dense, shape of the output) `stats` receives
   // per channel sum(g) and sum(g * x) of the stored gradient g instead of sum / sum of squares
   const __nv_bfloat16* bn_x;
+  // GroupNorm statistics of a forward convolution: per image and group (n_out / 8 channels) the sum
+  // and the sum of squares of the stored values, [images][8][2] fp32 (accumulated).  A warp's 32
+  // rows lie inside one image (or two, on the 4 x 4 grid), so the column sums of the staged tile
+  // reduce over the lanes of a group and leave with one atomic pair per warp, chunk and group.
+  float* gn_stats;
   int* status;
 };
 
@@ -448,6 +453,32 @@ __global__ void __launch_bounds__(GemmCfg<B_MN, BN, HALVES>::THREADS, 1)
             tma_store_5d(&map_o, my_stage, ntile * BN + c * 64 + out_pw * args.out_c, 0, out_ph, h0,
                          n0);
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          if (!B_MN && args.gn_stats) {
+            const int hw = args.H * args.W;                   // positions per image
+            const int cg = args.n_out >> 3;                   // channels per group (8, 16, 32, 64)
+            const int lpg = cg >> 1;                          // lanes per group (2 columns per lane)
+            const int rpi = hw < 32 ? hw : 32;                // rows of one image in this warp's tile
+            for (int r0 = 0; r0 < 32; r0 += rpi) {
+              float s = 0.f, q = 0.f;
+              for (int rr = r0; rr < r0 + rpi; ++rr) {
+                const uint32_t w = *reinterpret_cast<const uint32_t*>(
+                    my_stage + rr * 128 + (((lane >> 2) ^ (rr & 7)) * 16) + (lane & 3) * 4);
+                const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
+                s += a + b;
+                q = fmaf(a, a, fmaf(b, b, q));
+              }
+              for (int o = 1; o < lpg; o <<= 1) {
+                s += __shfl_xor_sync(0xffffffffu, s, o);
+                q += __shfl_xor_sync(0xffffffffu, q, o);
+              }
+              if ((lane & (lpg - 1)) == 0) {
+                const long long img = (row - lane + r0) / hw;
+                const int grp = (ntile * BN + c * 64 + 2 * lane) / cg;
+                atomicAdd(args.gn_stats + (img * 8 + grp) * 2, s);
+                atomicAdd(args.gn_stats + (img * 8 + grp) * 2 + 1, q);
+              }
+            }
           }
           if (args.stats) {
             // column sums over the ROUNDED values in the staged tile: lane l owns columns 2l, 2l+1
@@ -799,8 +830,8 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
                      int clients, int imgs_per_client, int H, int W, int n_out, int n_taps,
                      const int* taps, const nfb_rn_act* out, int out_ph, int out_pw, float* stats,
                      const void* residual, const void* res_mask, const void* out_mask,
-                     const void* bn_x, int bn_tile, int halves, int n_cls, int* status,
-                     void* stream) {
+                     const void* bn_x, float* gn_stats, int bn_tile, int halves, int n_cls,
+                     int* status, void* stream) {
   using namespace nfb;
   using namespace nfb::rn;
   NFB_REQUIRE(a0 && w0 && w_dims && taps && out && status, NFB_EINVAL, "rn_conv_gemm: null pointer");
@@ -823,6 +854,11 @@ int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, cons
   g.res_mask = static_cast<const __nv_bfloat16*>(res_mask);
   g.out_mask = static_cast<const __nv_bfloat16*>(out_mask);
   g.bn_x = static_cast<const __nv_bfloat16*>(bn_x);
+  g.gn_stats = gn_stats;
+  NFB_REQUIRE(!gn_stats || (!dgrad && !out->parity && out->C == n_out && n_out % 64 == 0 &&
+                            ((H * W) % 32 == 0 || 32 % (H * W) == 0)),
+              NFB_EINVAL, "rn_conv_gemm: GroupNorm statistics need a dense forward output whose "
+              "images are multiples or divisors of 32 positions");
   NFB_REQUIRE(!bn_x || (dgrad && stats && out->C == n_out), NFB_EINVAL,
               "rn_conv_gemm: BatchNorm-backward sums need a data gradient, a stats buffer and a "
               "full-width output");

@@ -373,13 +373,16 @@ typedef struct {
  * tensor of the output's shape) zeroes the stored value where it is not positive (the ReLU
  * backward of the layer the gradient flows into).  bn_x (dgrad, with stats): the raw conv output
  * under that activation's BatchNorm - stats then receives sum(g) and sum(g * x) of the stored
- * gradient (the reduction pass of the BatchNorm backward, folded into this epilogue).          */
+ * gradient (the reduction pass of the BatchNorm backward, folded into this epilogue).
+ * gn_stats (forward, dense output): [images][8][2] GroupNorm(8) sums of the stored values,
+ * accumulated (the statistics pass of nfb_rn_gn_stats folded into this epilogue).             */
 int nfb_rn_conv_gemm(int dgrad, const nfb_rn_act* a0, const nfb_rn_act* a1, const void* w0,
                      const void* w1, const int* w_dims, int clients, int imgs_per_client, int H,
                      int W, int n_out, int n_taps, const int* taps, const nfb_rn_act* out,
                      int out_ph, int out_pw, float* stats, const void* residual,
-                     const void* res_mask, const void* out_mask, const void* bn_x, int bn_tile,
-                     int halves, int n_cls, int* status, void* stream);
+                     const void* res_mask, const void* out_mask, const void* bn_x,
+                     float* gn_stats, int bn_tile, int halves, int n_cls, int* status,
+                     void* stream);
 /* out[client][tap][co][ci] (+)= sum_pos x[pos + tap][ci] * dy[pos][co]; k_split > 1 adds with fp32
  * atomics (the target must then be zero).  With k_split == 1 and sgd_w != NULL the gradient is not
  * written at all: the epilogue applies w -= lr * (dW + wd * w) to the tap-major fp32 master sgd_w

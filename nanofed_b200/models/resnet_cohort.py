@@ -222,6 +222,8 @@ class _Lane:
         # BatchNorm backward sums from the dgrad epilogue instead of a reduction pass
         self.fuse_bn_sums = (self.norm == "batch"
                              and os.environ.get("NFB_RN_NO_FUSED_BN_SUMS") is None)
+        # GroupNorm statistics from the forward conv epilogue instead of a pass over the output
+        self.fuse_gn_stats = os.environ.get("NFB_RN_GN_STATS_KERNEL") is None
         self._tile_override = os.environ.get("NFB_RN_TILE")   # "bn,halves" for experiments
         self._wgrad_posk = int(os.environ.get("NFB_RN_WGRAD_K", "0"))   # 0 = per-layer choice
 
@@ -256,8 +258,9 @@ class _Lane:
         rn.conv_gemm(False, x, self._wref(c), raw, clients=self.g, grid_hw=(c.hout, c.hout),
                      taps=rn.fwd_taps(c.k, c.stride, c.cout), a_parity=c.stride == 2,
                      stats=self._bn_stats(n) if batch else None, n_out=c.cout,
+                     gn_stats=self._bn_stats(n) if not batch and self.fuse_gn_stats else None,
                      tile=self._tile(self.b * c.hout * c.hout, c.cout))
-        if not batch:
+        if not batch and not self.fuse_gn_stats:
             rn.gn_stats(raw, self._bn_stats(n))
 
     def _norm_apply(self, n: _Bn, raw: torch.Tensor, y: torch.Tensor, *, res=None,

@@ -43,7 +43,7 @@ def _lib() -> C.CDLL:
         pa, pi, pll = C.POINTER(_Act), C.POINTER(C.c_int), C.POINTER(C.c_longlong)
         sigs = {
             "nfb_rn_conv_gemm": [i32, pa, pa, vp, vp, pi, i32, i32, i32, i32, i32, i32, pi, pa, i32,
-                                 i32, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp],
+                                 i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp],
             "nfb_rn_conv_wgrad": [pa, pa, i32, i32, i32, pi, vp, ll, i32, i32, i32, vp, vp, f32, f32,
                                   vp, vp],
             "nfb_rn_im2col3": [vp, ll, i32, i32, vp, vp],
@@ -186,7 +186,7 @@ def conv_gemm(
     stats: torch.Tensor | None = None, residual: torch.Tensor | None = None,
     res_mask: torch.Tensor | None = None, out_mask: torch.Tensor | None = None, n_out: int,
     tile: tuple[int, int] | None = None, all_classes: bool = False,
-    bn_x: torch.Tensor | None = None,
+    bn_x: torch.Tensor | None = None, gn_stats: torch.Tensor | None = None,
 ) -> None:
     """``out[pos, n] = Σ_taps A[pos + tap, :] · W`` on tensor cores (see ``csrc/rn_conv.cu``)."""
     lib = _lib()
@@ -207,7 +207,8 @@ def conv_gemm(
         1 if dgrad else 0, C.byref(a0), C.byref(a1s) if a1s is not None else None, w.ptr,
         w1.ptr if w1 is not None else None, dims, clients, imgs, h, wd, n_out, len(taps),
         _tap_array(taps), C.byref(o), oph, opw, _ptr(stats), _ptr(residual), _ptr(res_mask),
-        _ptr(out_mask), _ptr(bn_x), bn, halves, 4 if all_classes else 1, st.data_ptr(), _stream(a))
+        _ptr(out_mask), _ptr(bn_x), _ptr(gn_stats), bn, halves, 4 if all_classes else 1,
+        st.data_ptr(), _stream(a))
     _check(code, "rn_conv_gemm")
 
 

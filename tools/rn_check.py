@@ -81,16 +81,21 @@ def check_layer(cin, cout, h, stride, k, clients=2, batch=16, tol=1.2e-2):
     # ---------------- forward ----------------
     raw, y = guarded((clients * batch, ho, ho, cout), torch.bfloat16)
     stats = torch.zeros(clients, 2, cout, device=DEV)
+    gstats = torch.zeros(clients * batch, 8, 2, device=DEV)      # GroupNorm(8) sums per image
     rn.conv_gemm(False, x, wref, y, clients=clients, grid_hw=(ho, ho),
-                 taps=rn.fwd_taps(k, stride, cout), a_parity=stride == 2, stats=stats, n_out=cout)
+                 taps=rn.fwd_taps(k, stride, cout), a_parity=stride == 2, stats=stats, n_out=cout,
+                 gn_stats=gstats)
     torch.cuda.synchronize()
     e = rel(y, ref_y)
     yf = y.float().view(clients, -1, cout)
     es = rel(stats[:, 0], yf.sum(1))
     eq = rel(stats[:, 1], (yf * yf).sum(1))
-    good = e < tol and es < 1e-3 and eq < 1e-3 and canaries_ok(raw, y.numel())
+    yg = y.float().view(clients * batch, ho * ho, 8, cout // 8)
+    eg = max(rel(gstats[:, :, 0], yg.sum((1, 3))), rel(gstats[:, :, 1], (yg * yg).sum((1, 3))))
+    good = e < tol and es < 1e-3 and eq < 1e-3 and eg < 1e-3 and canaries_ok(raw, y.numel())
     ok &= good
-    print(f"  fwd   {name}: rel {e:.2e}  sum {es:.1e}  sumsq {eq:.1e}  {'ok' if good else 'FAIL'}")
+    print(f"  fwd   {name}: rel {e:.2e}  sum {es:.1e}  sumsq {eq:.1e}  group sums {eg:.1e}  "
+          f"{'ok' if good else 'FAIL'}")
     # ---------------- dgrad ----------------
     raw, dx = guarded((clients * batch, h, h, cin), torch.bfloat16)
     if stride == 1:
